@@ -1,0 +1,185 @@
+"""TEST INFRASTRUCTURE (container only): runs the UNMODIFIED reference on seeded synthetic inputs and
+writes small golden fixtures to tests/golden/. Run: python oracle/make_golden.py
+
+The fixtures pin oracle/restate.py (and through it the CUDA path) to the executed reference:
+  state_dict_spec.json   keys / shapes / trainable flags of the reference Model (1 and 4 baselines)
+  learner_small.pt       rl_learner_forward + compute_loss + backward, T=2 B=2 N=64, fp32 (+fp64 truth)
+  infer_small.pt         compute_logp_action under fixed Gumbel noise, B=3 N=512 (incl. collision / 1-entity obs)
+  scatter_small.pt       scatter_connection on a heavy-collision case
+Inputs and weights are NOT stored: tests regenerate them from the same seeds (applestar_b200/synth.py).
+"""
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle.ref_loader import load_reference  # noqa: E402
+from applestar_b200 import synth, config as C, tables  # noqa: E402
+
+GOLD = os.path.join(ROOT, 'tests', 'golden')
+
+
+def ref_cfg(baselines):
+    from easydict import EasyDict
+    learner = dict(C.DEFAULT_LOSS_CONFIG)
+    learner.update({'use_value_feature': False, 'player_id': 'MP0'})
+    return EasyDict({'common': {'type': 'rl'}, 'model': {'enable_baselines': list(baselines)}, 'learner': learner})
+
+
+def build_ref_model(baselines, seed=0):
+    from distar.agent.default.model.model import Model
+    cfg = ref_cfg(baselines)
+    m = Model(cfg, use_value_network=True)
+    trainable = {k for k, p in m.named_parameters() if p.requires_grad}
+    spec = [(k, list(v.shape), k in trainable) for k, v in m.state_dict().items()]
+    sd = synth.synth_state_dict([(k, s) for k, s, t in spec if t], seed)
+    missing = m.load_state_dict(sd, strict=False)
+    assert not missing.unexpected_keys
+    return m, cfg, spec
+
+
+def grad_summary(model):
+    out = {}
+    for k, p in model.named_parameters():
+        if p.requires_grad:
+            g = p.grad if p.grad is not None else torch.zeros_like(p)
+            out[k] = torch.tensor([g.double().norm().item(), g.double().sum().item()])
+    return out
+
+
+SMALL_GRADS = ['policy.selected_units_head.end_embedding', 'policy.location_head.res.0.UpdateSP',
+               'core_lstm.layers.2.cell.layernorm_c.weight', 'encoder.scatter_project.0.bias',
+               'policy.target_unit_head.query_fc2.0.weight', 'value_networks.winloss.value_fc.0.weight',
+               'encoder.entity_encoder.transformer.layers.0.layernorm1.bias',
+               'encoder.spatial_encoder.project.0.bias', 'policy.action_type_head.action_fc.layer2.0.bias',
+               'encoder.scalar_encoder.encode_modules.home_race.weight']
+
+
+def learner_case(T, B, N, baselines, seed):
+    from distar.agent.default.rl_training.rl_loss import ReinforcementLoss
+    model, cfg, _ = build_ref_model(baselines)
+    data = synth.gen_trajectories(T, B, N, seed)
+    loss_fn = ReinforcementLoss(cfg.learner, 'MP0')
+    out = model.rl_learner_forward(**synth.tree_map(lambda t: t.clone(), data))
+    logits = {k: v.detach().clone() for k, v in out['target_logit'].items()}
+    values = {k: v.detach().clone() for k, v in out['value'].items()}
+    info = loss_fn.compute_loss(out)
+    model.zero_grad()
+    info['total_loss'].backward()
+    res = {'T': T, 'B': B, 'N': N, 'seed': seed, 'baselines': list(baselines),
+           'logit': logits, 'value': values,
+           'loss_info': {k: (float(v) if not isinstance(v, torch.Tensor) else float(v.detach())) for k, v in info.items()},
+           'grad_summary': grad_summary(model),
+           'grads': {k: dict(model.named_parameters())[k].grad.clone() for k in SMALL_GRADS}}
+    # fp64 ground truth of the same forward -> calibrates fp32/bf16 tolerances
+    old_float = torch.Tensor.float
+    torch.set_default_dtype(torch.float64)
+    torch.Tensor.float = lambda self, *a, **k: self.double()
+    try:
+        m64 = model.double()
+        d64 = synth.tree_map(lambda t: t.double() if t.dtype == torch.float32 else t.clone(), data)
+        with torch.no_grad():
+            o64 = m64.rl_learner_forward(**d64)
+        res['logit64'] = {k: v.clone() for k, v in o64['target_logit'].items()}
+        res['value64'] = {k: v.clone() for k, v in o64['value'].items()}
+    finally:
+        torch.Tensor.float = old_float
+        torch.set_default_dtype(torch.float32)
+    # bf16-autocast reference error level: what "bf16 tolerance" means per head
+    model = model.float()
+    import distar.agent.default.model.encoder as enc_mod
+    orig_sc = enc_mod.scatter_connection
+    enc_mod.scatter_connection = lambda shape, pe, loc, dim, typ='add': orig_sc(shape, pe.float(), loc, dim, typ)
+    try:
+        with torch.no_grad(), torch.autocast('cpu', dtype=torch.bfloat16):
+            ob = model.rl_learner_forward(**synth.tree_map(lambda t: t.clone(), data))
+        err = {}
+        for k in logits:
+            valid = res['logit64'][k] > -1e8
+            d = (ob['target_logit'][k].double() - res['logit64'][k])[valid]
+            err[k] = torch.tensor([d.abs().max().item(), d.pow(2).mean().sqrt().item()])
+        for k in values:
+            d = ob['value'][k].double() - res['value64'][k]
+            err['value/' + k] = torch.tensor([d.abs().max().item(), d.pow(2).mean().sqrt().item()])
+        res['bf16_autocast_err'] = err
+    finally:
+        enc_mod.scatter_connection = orig_sc
+    return res
+
+
+def infer_case(B, N, seed):
+    model, cfg, _ = build_ref_model(['winloss'])
+    model.eval()
+    data = synth.gen_observations(B, N, seed, entity_num_range=(N // 2, N), special=True)
+    noise = synth.gen_gumbel(B, seed + 1, N)
+    order = [noise['action_type'], noise['delay'], noise['queued']]
+    state = {'i': 0, 'su': 0}
+
+    def fake_multinomial(p, n, *a, **k):
+        K = p.shape[1]
+        if K == N + 1:
+            g = noise['selected_units'][state['su']]
+            state['su'] += 1
+        elif K == N:
+            g = noise['target_unit']
+        elif K == C.SPATIAL_X * C.SPATIAL_Y:
+            g = noise['target_location']
+        else:
+            g = order[state['i']]
+            state['i'] += 1
+        return (torch.log(p) + g).argmax(1, keepdim=True)
+    real = torch.multinomial
+    torch.multinomial = fake_multinomial
+    try:
+        with torch.no_grad():
+            out = model.compute_logp_action(**synth.tree_map(lambda t: t.clone(), data))
+    finally:
+        torch.multinomial = real
+    return {'B': B, 'N': N, 'seed': seed, 'logit': out['logit'], 'action_info': out['action_info'],
+            'action_logp': out['action_logp'], 'selected_units_num': out['selected_units_num'],
+            'extra_units': out['extra_units'], 'hidden_state': out['hidden_state']}
+
+
+def scatter_case():
+    from distar.agent.default.model.module_utils import scatter_connection
+    g = torch.Generator().manual_seed(5)
+    R, N, D = 4, 512, 32
+    emb = torch.randn(R, N, D, generator=g)
+    x = torch.randint(0, 8, (R, N), generator=g)
+    y = torch.randint(0, 8, (R, N), generator=g)
+    x[1, :50] = 250          # out-of-range -> clamps to 159
+    y[1, :50] = 200          # -> 151
+    loc = torch.stack([x, y], -1)
+    out = {}
+    for typ in ('add', 'cover'):
+        m = scatter_connection((R, 152, 160), emb.clone(), loc.clone(), D, typ)
+        nz = m.permute(0, 2, 3, 1).reshape(R, -1, D)
+        cells = (nz.abs().sum(-1) > 0).nonzero()
+        out[typ] = {'cells': cells, 'vals': nz[cells[:, 0], cells[:, 1]].clone()}
+    return {'seed': 5, 'R': R, 'N': N, 'D': D, 'out': out}
+
+
+def main():
+    load_reference()
+    os.makedirs(GOLD, exist_ok=True)
+    torch.manual_seed(0)
+    torch.set_num_threads(8)
+    specs = {}
+    for name, bl in (('winloss', ['winloss']), ('four', ['winloss', 'build_order', 'built_unit', 'battle'])):
+        _, _, spec = build_ref_model(bl)
+        specs[name] = spec
+    with open(os.path.join(GOLD, 'state_dict_spec.json'), 'w') as f:
+        json.dump(specs, f)
+    torch.save(scatter_case(), os.path.join(GOLD, 'scatter_small.pt'))
+    torch.save(learner_case(2, 2, 64, ['winloss', 'build_order', 'built_unit', 'battle'], 1234),
+               os.path.join(GOLD, 'learner_small.pt'))
+    torch.save(infer_case(3, 512, 4321), os.path.join(GOLD, 'infer_small.pt'))
+    for f in sorted(os.listdir(GOLD)):
+        print(f, os.path.getsize(os.path.join(GOLD, f)))
+
+
+if __name__ == '__main__':
+    main()
