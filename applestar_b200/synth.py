@@ -114,6 +114,8 @@ def gen_trajectories(unroll_len, batch_size, n_entity=C.MAX_ENTITY_NUM, seed=123
     scores = torch.rand((T, B, N), generator=g)
     scores = scores.masked_fill(torch.arange(N).view(1, 1, N) >= entity_num.unsqueeze(-1), 2.0)
     order = scores.argsort(dim=-1)[..., :S]
+    if N < S:
+        order = torch.nn.functional.pad(order, (0, S - N))
     slot = torch.arange(S).view(1, 1, S)
     selected_units = torch.where(slot < (sun - 1).unsqueeze(-1), order, selected_units)
     selected_units = torch.where((slot == (sun - 1).unsqueeze(-1)) & (sun > 0).unsqueeze(-1),

@@ -26,7 +26,8 @@ def ref_cfg(baselines):
     from easydict import EasyDict
     learner = dict(C.DEFAULT_LOSS_CONFIG)
     learner.update({'use_value_feature': False, 'player_id': 'MP0'})
-    return EasyDict({'common': {'type': 'rl'}, 'model': {'enable_baselines': list(baselines)}, 'learner': learner})
+    return EasyDict({'common': {'type': 'rl'}, 'agent': {'extra_units': True},
+                     'model': {'enable_baselines': list(baselines)}, 'learner': learner})
 
 
 def build_ref_model(baselines, seed=0):
