@@ -1,0 +1,9 @@
+"""applestar_b200 -- B200-native (sm_100a) implementation of the DI-star / Applestar policy-value hot path.
+
+Public surface mirrors the reference (`distar.agent.default.model.Model`,
+`distar.agent.default.rl_training.rl_loss.ReinforcementLoss`); see INTEGRATION.md.
+"""
+from .model import Model  # noqa: F401
+from .rl_loss import ReinforcementLoss  # noqa: F401
+
+__all__ = ['Model', 'ReinforcementLoss']

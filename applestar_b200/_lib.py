@@ -1,0 +1,97 @@
+"""ctypes binding of libapplestar_b200.so (the C-ABI declared in include/applestar_b200.h).
+
+The library is built in-tree by `__graft_entry__.build()` / `make -C applestar_b200/csrc`.  There is no
+fallback: a missing library raises, a non-zero return code raises.
+"""
+import ctypes
+import os
+from ctypes import c_float, c_int, c_int32, c_int64, c_void_p, POINTER
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, 'libapplestar_b200.so')
+_lib = None
+
+AS_LOSS_MAX_FIELDS = 6
+AS_LOSS_MAX_STATS = 96
+
+_ERR = {-1: 'AS_EINVAL (bad pointer / argument)', -2: 'AS_ESIZE (size out of range)',
+        -3: 'AS_EALIGN (pointer or pitch not 16-byte aligned)', -4: 'AS_EUNSUPPORTED', -5: 'AS_EDRIVER (tensor-map encode failed)'}
+
+
+class AsLossArgs(ctypes.Structure):
+    _fields_ = [
+        ('T', c_int32), ('B', c_int32), ('F', c_int32), ('S', c_int32), ('N1', c_int32), ('NE', c_int32),
+        ('head_k', c_int32 * 6), ('upgo_field', c_int32), ('at_kl_steps', c_float),
+        ('logit', c_void_p * 6), ('teacher', c_void_p * 6), ('dlogit', c_void_p * 6), ('action', c_void_p * 6),
+        ('mu_logp', c_void_p * 6), ('actions_mask', c_void_p * 6),
+        ('su_mask', c_void_p), ('su_logits_mask', c_void_p), ('tu_logits_mask', c_void_p),
+        ('cum_action_mask', c_void_p), ('step', c_void_p),
+        ('value', c_void_p * AS_LOSS_MAX_FIELDS), ('dvalue', c_void_p * AS_LOSS_MAX_FIELDS),
+        ('reward', c_void_p * AS_LOSS_MAX_FIELDS), ('field_mask', c_void_p * AS_LOSS_MAX_FIELDS),
+        ('winloss_reward', c_void_p), ('battle_reward', c_void_p),
+        ('gamma_td', c_float * AS_LOSS_MAX_FIELDS), ('w_pg', c_float * AS_LOSS_MAX_FIELDS),
+        ('w_td', c_float * AS_LOSS_MAX_FIELDS),
+        ('hw_pg', c_float * 6), ('hw_upgo', c_float * 6), ('hw_ent', c_float * 6), ('hw_kl', c_float * 6),
+        ('w_upgo', c_float), ('w_ent', c_float), ('w_kl', c_float), ('w_atkl', c_float),
+        ('stat_weight', c_void_p),
+        ('row_stats', c_void_p * 6), ('coef', c_void_p * 6), ('partial', c_void_p), ('out', c_void_p),
+    ]
+
+
+_SIGS = {
+    'as_abi_version': (c_int, []),
+    'as_scatter_connection_fwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int64, c_int,
+                                          c_int, c_int, c_int, c_int, c_void_p]),
+    'as_scatter_connection_bwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int64, c_int,
+                                          c_int, c_int, c_int, c_void_p]),
+    'as_gemm_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int64,
+                             c_int64, c_int64, c_int, c_int, c_int64, c_int64, c_int64, c_int64, c_int64, c_int64,
+                             c_int, c_int, c_float, c_int, c_void_p, c_void_p]),
+    'as_gemm_splits': (c_int, [c_int, c_int]),
+    'as_splitk_reduce': (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
+    'as_conv_nhwc_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int,
+                                  c_int, c_int, c_int, c_int, c_void_p]),
+    'as_cast_f32_bf16': (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
+    'as_gumbel_argmax': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
+    'as_rl_loss_forward': (c_int, [POINTER(AsLossArgs), c_void_p]),
+    'as_rl_loss_backward': (c_int, [POINTER(AsLossArgs), c_float, c_void_p]),
+    'as_clip_adam_scratch_bytes': (c_int64, []),
+    'as_clip_adam': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_float, c_float,
+                             c_float, c_float, c_float, c_int, c_void_p, c_void_p, c_void_p]),
+}
+
+EXPORTS = tuple(_SIGS)
+LAUNCHES = 0     # number of C-ABI kernel-launching calls made by this process (bench.py reports it)
+
+
+def lib():
+    """The loaded library; raises if it has not been built (no CPU / library fallback exists)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError('libapplestar_b200.so not found at %s -- run `python -c "import __graft_entry__ as g; '
+                               'g.build()"` (nvcc, sm_100a). There is no fallback path.' % LIB_PATH)
+        _lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGS.items():
+            fn = getattr(_lib, name)
+            fn.restype = res
+            fn.argtypes = args
+    return _lib
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = _ERR.get(rc, 'cudaError_t %d' % rc if rc > 0 else 'error %d' % rc)
+        raise RuntimeError('%s failed: %s' % (what, msg))
+
+
+def call(name, *args):
+    """Call a kernel-launching entry point and raise on a non-zero return code."""
+    global LAUNCHES
+    LAUNCHES += 1
+    check(getattr(lib(), name)(*args), name)
+
+
+def stream_ptr():
+    import torch
+    return torch.cuda.current_stream().cuda_stream

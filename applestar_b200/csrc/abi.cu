@@ -1,0 +1,120 @@
+// extern "C" surface of libapplestar_b200.so (declarations + reference citations: include/applestar_b200.h).
+#include "common.cuh"
+#include "gemm.h"
+#include "loss.h"
+
+namespace as {
+int scatter_fwd(const float*, const void*, const void*, int, const long long*, float*, long long, int, int, int, int,
+                int, cudaStream_t);
+int scatter_bwd(const float*, const void*, const void*, int, const long long*, float*, long long, int, int, int, int,
+                cudaStream_t);
+int cast_f32_bf16(const float*, void*, long long, cudaStream_t);
+int gumbel_argmax(const float*, const float*, long long*, long long, int, cudaStream_t);
+int loss_forward(const AsLossArgs&, cudaStream_t);
+int loss_backward(const AsLossArgs&, float, cudaStream_t);
+long long clip_adam_scratch_bytes();
+int clip_adam(float*, const float*, float*, float*, void*, long long, float, float, float, float, float, float, int,
+              float*, float*, cudaStream_t);
+}  // namespace as
+
+#define ST(s) reinterpret_cast<cudaStream_t>(s)
+
+extern "C" {
+
+int as_abi_version(void) { return 1; }
+
+int as_scatter_connection_fwd(const float* emb, const void* xs, const void* ys, int idx_bytes,
+                              const int64_t* entity_num, float* out, int64_t R, int N, int D, int H, int W, int cover,
+                              void* stream) {
+  return as::scatter_fwd(emb, xs, ys, idx_bytes, reinterpret_cast<const long long*>(entity_num), out, R, N, D, H, W,
+                         cover, ST(stream));
+}
+
+int as_scatter_connection_bwd(const float* d_out, const void* xs, const void* ys, int idx_bytes,
+                              const int64_t* entity_num, float* d_emb, int64_t R, int N, int D, int H, int W,
+                              void* stream) {
+  return as::scatter_bwd(d_out, xs, ys, idx_bytes, reinterpret_cast<const long long*>(entity_num), d_emb, R, N, D, H,
+                         W, ST(stream));
+}
+
+int as_gemm_splits(int K, int want) {
+  const int num_kb = (K + 63) / 64;
+  if (want <= 1) return 1;
+  const int per = (num_kb + want - 1) / want;
+  return (num_kb + per - 1) / per;
+}
+
+int as_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int a_mn, int b_mn,
+                 int64_t lda, int64_t ldb, int64_t ldc, int nb0, int nb1, int64_t a_sb0, int64_t a_sb1, int64_t b_sb0,
+                 int64_t b_sb1, int64_t c_sb0, int64_t c_sb1, int c_bf16, int relu, float alpha, int splits, float* ws,
+                 void* stream) {
+  as::GemmCall g;
+  g.A = A; g.B = B; g.C = C; g.bias = bias;
+  g.M = M; g.N = N; g.K = K;
+  g.a_mn = a_mn != 0; g.b_mn = b_mn != 0;
+  g.lda = lda; g.ldb = ldb; g.ldc = ldc;
+  g.nb0 = nb0; g.nb1 = nb1;
+  g.a_sb0 = a_sb0; g.a_sb1 = a_sb1; g.b_sb0 = b_sb0; g.b_sb1 = b_sb1; g.c_sb0 = c_sb0; g.c_sb1 = c_sb1;
+  g.c_bf16 = c_bf16; g.relu = relu; g.alpha = alpha;
+  g.splits = splits; g.ws = ws;
+  return as::gemm_run(g, ST(stream));
+}
+
+int as_splitk_reduce(const float* ws, float* out, int64_t n, int splits, int accumulate, void* stream) {
+  if (!ws || !out || splits <= 0) return AS_EINVAL;
+  return as::splitk_reduce(ws, out, n, splits, accumulate, ST(stream));
+}
+
+int as_conv_nhwc_bf16(const void* x, const void* w, void* y, const float* bias, int64_t R, int H, int W, int Cin,
+                      int Cout, int taps, int w_mn, int y_bf16, int relu, void* stream) {
+  if (taps != 1 && taps != 9) return AS_EUNSUPPORTED;
+  if (R <= 0 || H <= 0 || W <= 0 || Cin <= 0 || Cout <= 0) return AS_ESIZE;
+  if (Cin % 64 != 0) return AS_EUNSUPPORTED;
+  const int pw = W + 2, ph = H + 2;
+  const int64_t P = R * (int64_t)ph * pw;
+  if (P > 2147483647LL) return AS_ESIZE;
+  as::GemmCall g;
+  g.A = x; g.B = w; g.C = y; g.bias = bias;
+  g.M = (int)P; g.N = Cout; g.K = Cin;
+  g.a_mn = false; g.b_mn = w_mn != 0;
+  g.lda = Cin; g.ldb = g.b_mn ? Cout : (int64_t)taps * Cin; g.ldc = Cout;
+  g.c_bf16 = y_bf16; g.relu = relu; g.alpha = 1.f;
+  g.taps = taps;
+  if (taps == 9) {
+    for (int ky = 0; ky < 3; ++ky)
+      for (int kx = 0; kx < 3; ++kx) g.shift[ky * 3 + kx] = (ky - 1) * pw + (kx - 1);
+  } else {
+    g.shift[0] = 0;
+  }
+  g.img_w = pw; g.img_h = ph;
+  return as::gemm_run(g, ST(stream));
+}
+
+int as_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream) {
+  return as::cast_f32_bf16(src, dst, n, ST(stream));
+}
+
+int as_gumbel_argmax(const float* logit, const float* noise, int64_t* out, int64_t rows, int K, void* stream) {
+  return as::gumbel_argmax(logit, noise, reinterpret_cast<long long*>(out), rows, K, ST(stream));
+}
+
+int as_rl_loss_forward(const AsLossArgs* args, void* stream) {
+  if (!args) return AS_EINVAL;
+  return as::loss_forward(*args, ST(stream));
+}
+
+int as_rl_loss_backward(const AsLossArgs* args, float grad_scale, void* stream) {
+  if (!args) return AS_EINVAL;
+  return as::loss_backward(*args, grad_scale, ST(stream));
+}
+
+int64_t as_clip_adam_scratch_bytes(void) { return as::clip_adam_scratch_bytes(); }
+
+int as_clip_adam(float* p, const float* g, float* m, float* v, void* shadow, int64_t n, float max_norm, float lr,
+                 float beta1, float beta2, float eps, float weight_decay, int step, float* scratch, float* norm_out,
+                 void* stream) {
+  return as::clip_adam(p, g, m, v, shadow, n, max_norm, lr, beta1, beta2, eps, weight_decay, step, scratch, norm_out,
+                       ST(stream));
+}
+
+}  // extern "C"

@@ -1,0 +1,166 @@
+// Small HBM-bound helpers: dtype casts, Gumbel-max sampling, fused global-norm clip + Adam.
+#include "common.cuh"
+
+namespace as {
+
+// ------------------------------------------------------------------ fp32 -> bf16 (8 elements / thread / iteration)
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long n8 = n / 8;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(src) + 2 * i);
+    const float4 b = __ldg(reinterpret_cast<const float4*>(src) + 2 * i + 1);
+    __nv_bfloat162 h0 = __floats2bfloat162_rn(a.x, a.y), h1 = __floats2bfloat162_rn(a.z, a.w);
+    __nv_bfloat162 h2 = __floats2bfloat162_rn(b.x, b.y), h3 = __floats2bfloat162_rn(b.z, b.w);
+    uint4 u;
+    u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
+    u.z = *reinterpret_cast<uint32_t*>(&h2); u.w = *reinterpret_cast<uint32_t*>(&h3);
+    reinterpret_cast<uint4*>(dst)[i] = u;
+  }
+  for (long long i = n8 * 8 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    dst[i] = __float2bfloat16_rn(src[i]);
+}
+
+int cast_f32_bf16(const float* src, void* dst, long long n, cudaStream_t st) {
+  if (n <= 0) return AS_OK;
+  if (!src || !dst) return AS_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(src) & 15) || (reinterpret_cast<uintptr_t>(dst) & 15)) return AS_EALIGN;
+  long long blocks = (n / 8 + 255) / 256;
+  const int grid = (int)(blocks < 148LL * 8 ? (blocks > 0 ? blocks : 1) : 148LL * 8);
+  cast_f32_bf16_kernel<<<grid, 256, 0, st>>>(src, reinterpret_cast<__nv_bfloat16*>(dst), n);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+// ------------------------------------------------------------------ Gumbel-max sampling
+// out[r] = argmax_k (logit[r,k] + noise[r,k]) in fp32, lowest index on ties (torch.argmax semantics).
+template <int THREADS_PER_ROW>
+__global__ void gumbel_argmax_kernel(const float* __restrict__ logit, const float* __restrict__ noise,
+                                     long long* __restrict__ out, long long rows, int K) {
+  constexpr int RPB = 256 / THREADS_PER_ROW;
+  const int sub = threadIdx.x / THREADS_PER_ROW, tr = threadIdx.x % THREADS_PER_ROW;
+  __shared__ float bv[8];
+  __shared__ int bi[8];
+  for (long long row0 = (long long)blockIdx.x * RPB; row0 < rows; row0 += (long long)gridDim.x * RPB) {
+    const long long row = row0 + sub;
+    float best = -INFINITY;
+    int idx = 0x7fffffff;
+    if (row < rows) {
+      const float* x = logit + row * (long long)K;
+      const float* g = noise + row * (long long)K;
+      for (int k = tr; k < K; k += THREADS_PER_ROW) {
+        const float v = __ldg(x + k) + __ldg(g + k);
+        if (v > best || (v == best && k < idx)) { best = v; idx = k; }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+      if (ov > best || (ov == best && oi < idx)) { best = ov; idx = oi; }
+    }
+    if (THREADS_PER_ROW > 32) {
+      __syncthreads();
+      if ((threadIdx.x & 31) == 0) { bv[threadIdx.x >> 5] = best; bi[threadIdx.x >> 5] = idx; }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        for (int i = 1; i < 8; ++i)
+          if (bv[i] > best || (bv[i] == best && bi[i] < idx)) { best = bv[i]; idx = bi[i]; }
+        if (row < rows) out[row] = (idx == 0x7fffffff) ? 0 : idx;
+      }
+    } else if (tr == 0 && row < rows) {
+      out[row] = (idx == 0x7fffffff) ? 0 : idx;
+    }
+  }
+}
+
+int gumbel_argmax(const float* logit, const float* noise, long long* out, long long rows, int K, cudaStream_t st) {
+  if (rows <= 0) return AS_OK;
+  if (K <= 0) return AS_ESIZE;
+  if (!logit || !noise || !out) return AS_EINVAL;
+  if (K >= 4096) {
+    const int grid = (int)(rows < 148LL * 8 ? rows : 148LL * 8);
+    gumbel_argmax_kernel<256><<<grid, 256, 0, st>>>(logit, noise, out, rows, K);
+  } else {
+    long long blocks = (rows + 7) / 8;
+    const int grid = (int)(blocks < 148LL * 8 ? blocks : 148LL * 8);
+    gumbel_argmax_kernel<32><<<grid, 256, 0, st>>>(logit, noise, out, rows, K);
+  }
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+// ------------------------------------------------------------------ fused global-norm clip + Adam
+// pass 1: per-block partial sums of g^2 into scratch; pass 2: every block re-reduces the partials in a fixed order
+// (deterministic), derives clip = min(1, max_norm / (norm + 1e-6)) as torch.nn.utils.clip_grad_norm_ does, then
+// applies Adam (reference settings rl_learner.py:73-80) and refreshes the bf16 shadow of the weights.
+__global__ void sumsq_partial_kernel(const float* __restrict__ g, long long n, float* __restrict__ partial) {
+  float s = 0.f;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long n4 = n / 4;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(g) + i);
+    s += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+  }
+  for (long long i = n4 * 4 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) s += g[i] * g[i];
+  __shared__ float red[32];
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float v = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
+    v = warp_sum(v);
+    if (threadIdx.x == 0) partial[blockIdx.x] = v;
+  }
+}
+
+__global__ void clip_adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                                 float* __restrict__ v, __nv_bfloat16* __restrict__ shadow, long long n,
+                                 const float* __restrict__ partial, int n_partial, float max_norm, float lr,
+                                 float beta1, float beta2, float eps, float wd, float bc1, float bc2,
+                                 float* __restrict__ norm_out) {
+  __shared__ float s_clip;
+  if (threadIdx.x == 0) {
+    float tot = 0.f;
+    for (int i = 0; i < n_partial; ++i) tot += partial[i];
+    const float norm = sqrtf(tot);
+    float c = max_norm > 0.f ? max_norm / (norm + 1e-6f) : 1.f;
+    s_clip = c < 1.f ? c : 1.f;
+    if (blockIdx.x == 0 && norm_out) *norm_out = norm;
+  }
+  __syncthreads();
+  const float clip = s_clip;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    float gi = g[i] * clip;
+    float pi = p[i];
+    if (wd != 0.f) gi += wd * pi;
+    const float mi = beta1 * m[i] + (1.f - beta1) * gi;
+    const float vi = beta2 * v[i] + (1.f - beta2) * gi * gi;
+    m[i] = mi; v[i] = vi;
+    pi -= lr * (mi / bc1) / (sqrtf(vi / bc2) + eps);
+    p[i] = pi;
+    if (shadow) shadow[i] = __float2bfloat16_rn(pi);
+  }
+}
+
+constexpr int kAdamBlocks = 148 * 4;
+
+long long clip_adam_scratch_bytes() { return kAdamBlocks * sizeof(float); }
+
+int clip_adam(float* p, const float* g, float* m, float* v, void* shadow, long long n, float max_norm, float lr,
+              float beta1, float beta2, float eps, float wd, int step, float* scratch, float* norm_out,
+              cudaStream_t st) {
+  if (n <= 0) return AS_OK;
+  if (!p || !g || !m || !v || !scratch || step <= 0) return AS_EINVAL;
+  if (reinterpret_cast<uintptr_t>(g) & 15) return AS_EALIGN;
+  sumsq_partial_kernel<<<kAdamBlocks, 256, 0, st>>>(g, n, scratch);
+  AS_LAUNCH_CHECK();
+  const float bc1 = 1.f - powf(beta1, (float)step), bc2 = 1.f - powf(beta2, (float)step);
+  clip_adam_kernel<<<kAdamBlocks, 256, 0, st>>>(p, g, m, v, reinterpret_cast<__nv_bfloat16*>(shadow), n, scratch,
+                                                kAdamBlocks, max_norm, lr, beta1, beta2, eps, wd, bc1, bc2, norm_out);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+}  // namespace as

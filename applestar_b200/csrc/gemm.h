@@ -1,0 +1,35 @@
+// Internal (C++) description of one tcgen05 GEMM launch; the extern "C" wrappers live in abi.cu.
+#pragma once
+#include <cuda_runtime.h>
+
+namespace as {
+
+struct GemmCall {
+  // C[b][m][n] = epi(alpha * sum_k A[b][m][k] * B[b][n][k] + bias[n])
+  const void* A = nullptr;   // bf16
+  const void* B = nullptr;   // bf16
+  int M = 0, N = 0, K = 0;
+  bool a_mn = false;         // false: A stored [M rows][K contiguous] (lda = row pitch); true: [K rows][M contiguous]
+  bool b_mn = false;         // false: B stored [N rows][K contiguous];                   true: [K rows][N contiguous]
+  long long lda = 0, ldb = 0;
+  long long a_rows = 0;      // K-major A only: number of valid rows in global memory (defaults to M)
+  int nb0 = 1, nb1 = 1;      // batch = nb0 * nb1
+  long long a_sb0 = 0, a_sb1 = 0, b_sb0 = 0, b_sb1 = 0;   // batch strides (elements)
+  void* C = nullptr;
+  int c_bf16 = 0;
+  long long ldc = 0, c_sb0 = 0, c_sb1 = 0;
+  const float* bias = nullptr;
+  int relu = 0;
+  float alpha = 1.f;
+  int splits = 1;            // >1: fp32 partials to ws[splits][batch][M][N]
+  float* ws = nullptr;
+  int taps = 0;              // >0: implicit-GEMM conv; K = Cin, B = [N][taps*Cin], A rows shifted by shift[tap]
+  int shift[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  int img_w = 0, img_h = 0;  // padded image dims: border rows are written as zero
+  int bn_override = 0;
+};
+
+int gemm_run(const GemmCall& g, cudaStream_t st);
+int splitk_reduce(const float* ws, float* out, long long n, int splits, int accumulate, cudaStream_t st);
+
+}  // namespace as

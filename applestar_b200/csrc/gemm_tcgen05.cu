@@ -1,0 +1,427 @@
+// Persistent warp-specialised bf16 GEMM for sm_100a: TMA (4-D tensor maps, 128B swizzle) -> shared memory ring
+// -> tcgen05.mma (cta_group::1, M=128, N=BN) with fp32 accumulators double-buffered in TMEM -> tcgen05.ld
+// epilogue (bias / ReLU / border mask / dtype cast) written straight to global memory.
+//
+//   C[b][m][n] = epi( sum_k A[b][m][k] * B[b][n][k] )
+//
+// Either operand may be "K-major" (contraction index contiguous in global memory) or "MN-major" (the m / n index
+// contiguous), so X*W^T (forward), dY*W (dgrad) and dY^T*X (wgrad) all run without materialising a transpose.
+// Extra modes: split-K (fp32 partials into a caller workspace, reduced by as_splitk_reduce) and an implicit-GEMM
+// 3x3 convolution over zero-padded NHWC pixels (per-tap row shift of the A operand, see as_conv3x3_*).
+//
+// Warp roles (192 threads... 8 warps): w0 TMA producer, w1 MMA issuer, w2 TMEM allocator, w4-7 epilogue.
+#include "common.cuh"
+#include "gemm.h"
+
+namespace as {
+
+constexpr int BM = 128;
+constexpr int BK = 64;  // 64 bf16 = 128 bytes = one swizzle row
+constexpr int kGemmThreads = 256;
+
+struct GemmDev {
+  int M, N, K;
+  int nb0, nb1;
+  int m_blocks, n_blocks;
+  int splits, kb_per_split, num_kb;
+  // conv mode
+  int taps, cin_blocks, cin;
+  int shift[9];
+  int img_w, img_h;  // padded image dims for border masking (0 = off)
+  // epilogue
+  void* C;
+  int c_bf16;
+  long long ldc, c_sb0, c_sb1;
+  const float* bias;
+  int relu;
+  float alpha;
+  float* ws;  // split-K partials
+};
+
+template <int BN>
+struct SmemLayout {
+  static constexpr int kABytes = BM * 128;
+  static constexpr int kBBytes = BN * 128;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = (BN >= 256) ? 4 : (BN >= 128 ? 6 : 8);
+  static constexpr int kBarBytes = 1024;
+  static constexpr int kTotal = kStages * kStageBytes + kBarBytes + 1024;  // +1024 alignment slack
+};
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmDev p) {
+  using L = SmemLayout<BN>;
+  constexpr int kStages = L::kStages;
+  constexpr uint32_t kTmemCols = (2 * BN <= 32) ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* bar_base = smem + kStages * L::kStageBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(bar_base);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tmem_full = empty_bar + kStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);
+      mbar_init(&tmem_empty[i], 4);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int batch = p.nb0 * p.nb1;
+  const long long tiles_per_split = (long long)batch * p.m_blocks * p.n_blocks;
+  const long long num_tiles = tiles_per_split * p.splits;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        long long t = tile;
+        const int n_blk = (int)(t % p.n_blocks); t /= p.n_blocks;
+        const int m_blk = (int)(t % p.m_blocks); t /= p.m_blocks;
+        const int b = (int)(t % batch);
+        const int split = (int)(t / batch);
+        const int b0 = b % p.nb0, b1 = b / p.nb0;
+        const int m0 = m_blk * BM, n0 = n_blk * BN;
+        const int kb_begin = split * p.kb_per_split;
+        const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * L::kStageBytes;
+          uint8_t* sb = sa + L::kABytes;
+          mbar_expect_tx(&full_bar[stage], L::kStageBytes);
+          int ka, kbcol, mshift = 0;
+          if (p.taps > 0) {
+            const int tap = kb / p.cin_blocks, cb = kb - tap * p.cin_blocks;
+            ka = cb * BK;
+            kbcol = tap * p.cin + cb * BK;
+            mshift = p.shift[tap];
+          } else {
+            ka = kbcol = kb * BK;
+          }
+          if (A_MN) {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j)
+              tma_load_4d(sa + j * (BK * 128), &tmA, &full_bar[stage], m0 + j * 64, ka, b0, b1);
+          } else {
+            tma_load_4d(sa, &tmA, &full_bar[stage], ka, m0 + mshift, b0, b1);
+          }
+          if (B_MN) {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_4d(sb + j * (BK * 128), &tmB, &full_bar[stage], n0 + j * 64, kbcol, b0, b1);
+          } else {
+            tma_load_4d(sb, &tmB, &full_bar[stage], kbcol, n0, b0, b1);
+          }
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer (single thread)
+    if (lane == 0) {
+      // instruction descriptor: fp32 accum, bf16 A/B, majors, N>>3, M>>4
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+                             ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int split = (int)(tile / tiles_per_split);
+        const int kb_begin = split * p.kb_per_split;
+        const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * L::kStageBytes);
+          const uint32_t sb = sa + L::kABytes;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t da = A_MN ? make_smem_desc_sw128(sa + k * 16 * 128, BK * 128, 1024)
+                                     : make_smem_desc_sw128(sa + k * 32, 16, 1024);
+            const uint64_t db = B_MN ? make_smem_desc_sw128(sb + k * 16 * 128, BK * 128, 1024)
+                                     : make_smem_desc_sw128(sb + k * 32, 16, 1024);
+            umma_bf16(d_tmem, da, db, idesc, (kb > kb_begin || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tmem_full[acc]);      // accumulator complete -> epilogue
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ------------------------------------------------------------------ epilogue (4 warps = 128 TMEM lanes)
+    const int ew = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      long long t = tile;
+      const int n_blk = (int)(t % p.n_blocks); t /= p.n_blocks;
+      const int m_blk = (int)(t % p.m_blocks); t /= p.m_blocks;
+      const int b = (int)(t % batch);
+      const int split = (int)(t / batch);
+      const int b0 = b % p.nb0, b1 = b / p.nb0;
+      const int row = m_blk * BM + ew * 32 + lane;
+      const int n0 = n_blk * BN;
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(acc * BN);
+      bool border = false;
+      if (p.img_w > 0) {
+        const int q = row % (p.img_w * p.img_h);
+        const int yy = q / p.img_w, xx = q - yy * p.img_w;
+        border = (yy == 0) | (yy == p.img_h - 1) | (xx == 0) | (xx == p.img_w - 1);
+      }
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld32(t_row + c * 32, v);
+        tmem_ld_wait();
+        const int col0 = n0 + c * 32;
+        if (row < p.M && col0 < p.N) {
+          float f[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+          const bool full = (col0 + 32 <= p.N);
+          if (p.splits > 1) {
+            float* dst = p.ws + (((long long)split * batch + b) * p.M + row) * (long long)p.N + col0;
+            if (full && ((p.N & 3) == 0)) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                reinterpret_cast<float4*>(dst)[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+            } else {
+              for (int j = 0; j < 32 && col0 + j < p.N; ++j) dst[j] = f[j];
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              float x = f[j] * p.alpha;
+              if (p.bias != nullptr && (full || col0 + j < p.N)) x += __ldg(p.bias + col0 + j);
+              if (p.relu) x = fmaxf(x, 0.f);
+              if (border) x = 0.f;
+              f[j] = x;
+            }
+            const long long off = (long long)b0 * p.c_sb0 + (long long)b1 * p.c_sb1 + (long long)row * p.ldc + col0;
+            if (p.c_bf16) {
+              __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.C) + off;
+              if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  uint4 u;
+                  __nv_bfloat162 h0 = __floats2bfloat162_rn(f[8 * j], f[8 * j + 1]);
+                  __nv_bfloat162 h1 = __floats2bfloat162_rn(f[8 * j + 2], f[8 * j + 3]);
+                  __nv_bfloat162 h2 = __floats2bfloat162_rn(f[8 * j + 4], f[8 * j + 5]);
+                  __nv_bfloat162 h3 = __floats2bfloat162_rn(f[8 * j + 6], f[8 * j + 7]);
+                  u.x = *reinterpret_cast<uint32_t*>(&h0);
+                  u.y = *reinterpret_cast<uint32_t*>(&h1);
+                  u.z = *reinterpret_cast<uint32_t*>(&h2);
+                  u.w = *reinterpret_cast<uint32_t*>(&h3);
+                  reinterpret_cast<uint4*>(dst)[j] = u;
+                }
+              } else {
+                for (int j = 0; j < 32 && col0 + j < p.N; ++j) dst[j] = __float2bfloat16_rn(f[j]);
+              }
+            } else {
+              float* dst = reinterpret_cast<float*>(p.C) + off;
+              if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                  reinterpret_cast<float4*>(dst)[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+              } else {
+                for (int j = 0; j < 32 && col0 + j < p.N; ++j) dst[j] = f[j];
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// Operand = up to 4-D bf16 tensor: dims (inner contiguous, rows, b0, b1) with element strides.
+static int make_map(CUtensorMap* tm, const void* ptr, long long inner, long long rows, long long ld, int nb0,
+                    long long sb0, int nb1, long long sb1, int box_inner, int box_rows) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return AS_EDRIVER;
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || ((ld * 2) & 15)) return AS_EALIGN;
+  cuuint64_t dims[4] = {(cuuint64_t)inner, (cuuint64_t)rows, (cuuint64_t)nb0, (cuuint64_t)nb1};
+  long long s0 = nb0 > 1 ? sb0 : ld * rows, s1 = nb1 > 1 ? sb1 : s0 * nb0;
+  if (((s0 * 2) & 15) || ((s1 * 2) & 15)) return AS_EALIGN;
+  cuuint64_t strides[3] = {(cuuint64_t)(ld * 2), (cuuint64_t)(s0 * 2), (cuuint64_t)(s1 * 2)};
+  cuuint32_t box[4] = {(cuuint32_t)box_inner, (cuuint32_t)box_rows, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? AS_OK : AS_EDRIVER;
+}
+
+static int g_num_sms = 0;
+static int num_sms() {
+  if (!g_num_sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms <= 0) g_num_sms = kNumSMsB200;
+  }
+  return g_num_sms;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& p, cudaStream_t st) {
+  using L = SmemLayout<BN>;
+  static bool attr_set = false;
+  auto kern = gemm_kernel<BN, A_MN, B_MN>;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
+    if (e != cudaSuccess) return (int)e;
+    attr_set = true;
+  }
+  long long tiles = (long long)p.splits * p.nb0 * p.nb1 * p.m_blocks * p.n_blocks;
+  int grid = (int)(tiles < num_sms() ? tiles : num_sms());
+  if (grid <= 0) return AS_OK;
+  kern<<<grid, kGemmThreads, L::kTotal, st>>>(ta, tb, p);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+template <int BN>
+static int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& p,
+                          cudaStream_t st) {
+  if (!a_mn && !b_mn) return launch<BN, false, false>(ta, tb, p, st);
+  if (!a_mn && b_mn) return launch<BN, false, true>(ta, tb, p, st);
+  if (a_mn && !b_mn) return launch<BN, true, false>(ta, tb, p, st);
+  return launch<BN, true, true>(ta, tb, p, st);
+}
+
+static int pick_bn(int N, bool b_mn) {
+  if (b_mn) return N > 128 ? 256 : (N > 64 ? 128 : 64);
+  if (N > 128) return 256;
+  if (N > 64) return 128;
+  if (N > 32) return 64;
+  return 32;
+}
+
+int gemm_run(const GemmCall& g, cudaStream_t st) {
+  if (g.M <= 0 || g.N <= 0 || g.K <= 0 || g.nb0 <= 0 || g.nb1 <= 0) return AS_ESIZE;
+  if (!g.A || !g.B || (!g.C && g.splits <= 1)) return AS_EINVAL;
+  if (g.splits > 1 && !g.ws) return AS_EINVAL;
+  int BN = g.bn_override ? g.bn_override : pick_bn(g.N, g.b_mn);
+  if (g.b_mn && BN < 64) return AS_EUNSUPPORTED;
+  GemmDev p{};
+  p.M = g.M; p.N = g.N; p.K = g.K; p.nb0 = g.nb0; p.nb1 = g.nb1;
+  p.m_blocks = (g.M + BM - 1) / BM;
+  p.n_blocks = (g.N + BN - 1) / BN;
+  p.taps = g.taps; p.cin = g.K;
+  if (g.taps > 0) {
+    if (g.taps > 9 || (g.K % BK) != 0 || g.a_mn || g.nb0 * g.nb1 != 1) return AS_EUNSUPPORTED;
+    p.cin_blocks = g.K / BK;
+    p.num_kb = g.taps * p.cin_blocks;
+    for (int i = 0; i < g.taps; ++i) p.shift[i] = g.shift[i];
+  } else {
+    p.cin_blocks = 1;
+    p.num_kb = (g.K + BK - 1) / BK;
+  }
+  p.img_w = g.img_w; p.img_h = g.img_h;
+  p.splits = g.splits > 1 ? g.splits : 1;
+  p.kb_per_split = (p.num_kb + p.splits - 1) / p.splits;
+  p.splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;   // drop empty splits
+  if (g.splits > 1 && p.splits != g.splits) return AS_ESIZE;     // caller sizes ws from as_gemm_splits()
+  p.C = g.C; p.c_bf16 = g.c_bf16; p.ldc = g.ldc; p.c_sb0 = g.c_sb0; p.c_sb1 = g.c_sb1;
+  p.bias = g.bias; p.relu = g.relu; p.alpha = g.alpha; p.ws = g.ws;
+
+  CUtensorMap ta, tb;
+  int rc;
+  const long long k_total_b = g.taps > 0 ? (long long)g.taps * g.K : g.K;
+  if (g.a_mn) rc = make_map(&ta, g.A, g.M, g.K, g.lda, g.nb0, g.a_sb0, g.nb1, g.a_sb1, 64, BK);
+  else rc = make_map(&ta, g.A, g.K, g.a_rows > 0 ? g.a_rows : g.M, g.lda, g.nb0, g.a_sb0, g.nb1, g.a_sb1, BK, BM);
+  if (rc) return rc;
+  if (g.b_mn) rc = make_map(&tb, g.B, g.N, k_total_b, g.ldb, g.nb0, g.b_sb0, g.nb1, g.b_sb1, 64, BK);
+  else rc = make_map(&tb, g.B, k_total_b, g.N, g.ldb, g.nb0, g.b_sb0, g.nb1, g.b_sb1, BK, BN);
+  if (rc) return rc;
+  switch (BN) {
+    case 32: return dispatch_major<32>(g.a_mn, g.b_mn, ta, tb, p, st);
+    case 64: return dispatch_major<64>(g.a_mn, g.b_mn, ta, tb, p, st);
+    case 128: return dispatch_major<128>(g.a_mn, g.b_mn, ta, tb, p, st);
+    case 256: return dispatch_major<256>(g.a_mn, g.b_mn, ta, tb, p, st);
+  }
+  return AS_EUNSUPPORTED;
+}
+
+// ---- split-K reduction: out[i] = (accumulate ? out[i] : 0) + sum_s ws[s][i], fixed order (deterministic)
+__global__ void splitk_reduce_kernel(const float* __restrict__ ws, float* __restrict__ out, long long n, int splits,
+                                     int accumulate) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    float s = accumulate ? out[i] : 0.f;
+    for (int k = 0; k < splits; ++k) s += ws[(long long)k * n + i];
+    out[i] = s;
+  }
+}
+
+int splitk_reduce(const float* ws, float* out, long long n, int splits, int accumulate, cudaStream_t st) {
+  if (n <= 0) return AS_OK;
+  long long blocks = (n + 255) / 256;
+  int grid = (int)(blocks < 148 * 8 ? blocks : 148 * 8);
+  splitk_reduce_kernel<<<grid, 256, 0, st>>>(ws, out, n, splits, accumulate);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+}  // namespace as

@@ -1,0 +1,189 @@
+"""Data-parallel learner step around `Model` + `ReinforcementLoss`.
+
+Mirrors the compute part of the reference learner: `RLLearner._train` (agent/default/rl_learner.py:82-145:
+forward -> loss -> zero_grad -> backward -> sync_gradients -> grad clip -> Adam step) and `DistModule`
+(ctools/utils/dist_helper.py:372-439), redesigned for one process per B200:
+
+* all trainable parameters live in ONE flat fp32 buffer (+ flat grad, Adam m/v and a bf16 shadow the GEMMs
+  read), so broadcast is one call instead of 432, the optimizer is one fused kernel instead of ~400, and
+* gradients are all-reduced per ~25 MB bucket of the flat grad buffer from post-accumulate-grad hooks, on a side
+  stream, while the rest of backward is still running (the reference issues 394 blocking per-tensor all_reduces
+  after backward, dist_helper.py:421-431).  Trajectories are independent, so there is no other collective.
+"""
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from . import _lib
+from . import kernels as K
+
+
+class FlatParams:
+    """Re-homes every trainable parameter of `module` into flat buffers (views keep the nn.Parameter objects)."""
+
+    ALIGN = 8          # elements: keeps every tensor 32-byte (fp32) / 16-byte (bf16 shadow) aligned for TMA
+
+    def __init__(self, module, order=('encoder', 'core_lstm', 'policy', 'value_networks'), with_shadow=True):
+        named = [(k, p) for k, p in module.named_parameters() if p.requires_grad]
+        rank = {pfx: i for i, pfx in enumerate(order)}
+        named.sort(key=lambda kp: rank.get(kp[0].split('.')[0], len(order)))       # stable: forward order
+        self.names = [k for k, _ in named]
+        self.params = [p for _, p in named]
+        dev = self.params[0].device
+        self.offsets, off = [], 0
+        for p in self.params:
+            self.offsets.append(off)
+            off += (p.numel() + self.ALIGN - 1) // self.ALIGN * self.ALIGN
+        self.numel = off
+        self.flat = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.grad = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.shadow = torch.zeros(off, dtype=torch.bfloat16, device=dev) if (with_shadow and dev.type == 'cuda') else None
+        for p, o in zip(self.params, self.offsets):
+            n = p.numel()
+            self.flat[o:o + n].copy_(p.data.reshape(-1))
+            p.data = self.flat[o:o + n].view(p.shape)
+            p.grad = self.grad[o:o + n].view(p.shape)
+            if self.shadow is not None:
+                p._as_shadow = self.shadow[o:o + n].view(p.shape[0], -1) if p.dim() >= 2 else None
+        self.refresh_shadow()
+
+    def refresh_shadow(self):
+        if self.shadow is not None:
+            _lib.call('as_cast_f32_bf16', self.flat.data_ptr(), self.shadow.data_ptr(), self.numel, _lib.stream_ptr())
+        K.weights_changed()
+
+    def zero_grad(self):
+        self.grad.zero_()
+        for p, o in zip(self.params, self.offsets):          # autograd may have replaced .grad; re-attach the views
+            if p.grad is None or p.grad.data_ptr() != self.grad.data_ptr() + 4 * o:
+                p.grad = self.grad[o:o + p.numel()].view(p.shape)
+
+    def buckets(self, bucket_elems):
+        """Contiguous [start, end) ranges of the flat grad buffer, filled from the END (grads of the heads / value
+        nets arrive first in backward) -> list of (start, end, param_indices)."""
+        out, end, idx = [], self.numel, []
+        for i in range(len(self.params) - 1, -1, -1):
+            idx.append(i)
+            if end - self.offsets[i] >= bucket_elems or i == 0:
+                out.append((self.offsets[i], end, idx))
+                end, idx = self.offsets[i], []
+        return out
+
+
+class DistModule(nn.Module):
+    """Reference-compatible wrapper (`.module`, forwarded attributes, `sync_gradients`, `broadcast_params`)."""
+
+    def __init__(self, module, sync=True, bucket_mb=25.0, flat=None):
+        super().__init__()
+        self.module = module
+        for attr in ('forward', 'state_dict', 'load_state_dict', 'named_parameters', 'sl_train', 'rl_learner_forward',
+                     'compute_logp_action', 'compute_teacher_logit'):
+            if hasattr(module, attr):
+                setattr(self, attr, getattr(module, attr))
+        self.flat = flat if flat is not None else FlatParams(module)
+        self.world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+        self.sync = sync
+        self._works = []
+        self._buckets = self.flat.buckets(int(bucket_mb * 1024 * 1024 / 4))
+        self._pending = [0] * len(self._buckets)
+        self._bucket_of = {}
+        for b, (_, _, idx) in enumerate(self._buckets):
+            for i in idx:
+                self._bucket_of[i] = b
+        self._comm_stream = torch.cuda.Stream() if self.flat.flat.is_cuda else None
+        self._avg = dist.ReduceOp.AVG if (self.world > 1 and dist.get_backend() == 'nccl') else None
+        self.broadcast_params()
+        if self.world > 1:
+            for i, p in enumerate(self.flat.params):
+                p.register_post_accumulate_grad_hook(self._make_hook(i))
+        self.prepare_backward()
+
+    # -- collectives ------------------------------------------------------------------------------
+    def broadcast_params(self):
+        """One flat broadcast from rank 0 (reference: one broadcast per state_dict tensor, dist_helper.py:433-439)."""
+        if self.world > 1:
+            dist.broadcast(self.flat.flat, 0)
+            self.flat.refresh_shadow()
+
+    def prepare_backward(self):
+        self._pending = [len(idx) for _, _, idx in self._buckets]
+        self._works = []
+
+    def _make_hook(self, i):
+        def hook(_param):
+            b = self._bucket_of[i]
+            self._pending[b] -= 1
+            if self._pending[b] == 0:
+                self._launch(b)
+        return hook
+
+    def _launch(self, b):
+        start, end, _ = self._buckets[b]
+        chunk = self.flat.grad[start:end]
+        if self._comm_stream is not None:
+            ev = torch.cuda.Event()
+            ev.record()
+            self._comm_stream.wait_event(ev)
+            with torch.cuda.stream(self._comm_stream):
+                work = dist.all_reduce(chunk, op=self._avg or dist.ReduceOp.SUM, async_op=True)
+        else:
+            work = dist.all_reduce(chunk, op=dist.ReduceOp.SUM, async_op=True)
+        self._works.append((work, chunk))
+
+    def sync_gradients(self):
+        """Average gradients across ranks.  With hooks active this only waits for the in-flight bucket reductions."""
+        if self.world <= 1:
+            return
+        for b, n in enumerate(self._pending):
+            if n > 0:                       # parameters that received no gradient this step: reduce what is there
+                self._pending[b] = 0
+                self._launch(b)
+        for work, chunk in self._works:
+            work.wait()
+            if self._avg is None:
+                chunk.div_(self.world)
+        self._works = []
+
+
+class FusedAdam:
+    """clip_grad_norm_(max_norm) + Adam(lr, betas=(0, 0.99), eps=1e-5) as two kernels over the flat buffers."""
+
+    def __init__(self, flat, lr=1e-5, betas=(0.0, 0.99), eps=1e-5, weight_decay=0.0, max_norm=1.0):
+        self.flat, self.lr, self.betas, self.eps, self.wd, self.max_norm = flat, lr, betas, eps, weight_decay, max_norm
+        self.m = torch.zeros_like(flat.flat)
+        self.v = torch.zeros_like(flat.flat)
+        self.t = 0
+        self.scratch = torch.empty(_lib.lib().as_clip_adam_scratch_bytes() // 4, dtype=torch.float32,
+                                   device=flat.flat.device)
+        self.grad_norm = torch.zeros(1, dtype=torch.float32, device=flat.flat.device)
+
+    def step(self):
+        self.t += 1
+        f = self.flat
+        _lib.call('as_clip_adam', f.flat.data_ptr(), f.grad.data_ptr(), self.m.data_ptr(), self.v.data_ptr(),
+                  0 if f.shadow is None else f.shadow.data_ptr(), f.numel, self.max_norm, self.lr, self.betas[0],
+                  self.betas[1], self.eps, self.wd, self.t, self.scratch.data_ptr(), self.grad_norm.data_ptr(),
+                  _lib.stream_ptr())
+        _lib.LAUNCHES += 1
+        K.weights_changed()
+
+
+class LearnerStep:
+    """One data-parallel RL learner iteration on device-resident (or pinned-host) trajectories."""
+
+    def __init__(self, model, loss, lr=1e-5, max_norm=1.0, bucket_mb=25.0):
+        self.model = model
+        self.loss = loss
+        self.dist_model = DistModule(model, bucket_mb=bucket_mb)
+        self.flat = self.dist_model.flat
+        self.optimizer = FusedAdam(self.flat, lr=lr, max_norm=max_norm)
+
+    def __call__(self, data):
+        self.flat.zero_grad()
+        self.dist_model.prepare_backward()
+        out = self.model.rl_learner_forward(**data)
+        info = self.loss.compute_loss(out)
+        info['total_loss'].backward()
+        self.dist_model.sync_gradients()
+        self.optimizer.step()
+        return info

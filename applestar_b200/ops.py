@@ -1,0 +1,321 @@
+"""Operator layer of the hot path.
+
+Every function here runs on the GPU only.  Ops marked [kernel] launch this repo's sm_100a kernels
+through the C-ABI (applestar_b200/_lib.py -> libapplestar_b200.so); ops marked [library] still call
+stock ATen/cuBLAS/cuDNN CUDA ops and are the replacement queue documented in DESIGN.md.  Nothing
+falls back to the CPU: `require_cuda` raises, and `_lib` raises if the shared library is missing.
+"""
+import math
+
+import torch
+import torch.nn.functional as F
+
+from . import config as C
+from . import _lib
+from . import kernels as K
+
+
+def require_cuda(t):
+    if not t.is_cuda:
+        raise RuntimeError('applestar_b200 runs on CUDA tensors only (no CPU / MPS fallback); got device %s' % t.device)
+    _lib.lib()      # raises loudly when the C-ABI library is missing
+
+
+# ---------------------------------------------------------------------------------------------
+# dense layers
+def linear(x, weight, bias, relu=False):
+    """y = act(x @ W^T + b).  [kernel] tcgen05 GEMM when shapes qualify, else [library] cuBLAS."""
+    require_cuda(x)
+    return K.linear(x, weight, bias, relu)
+
+
+def layer_norm(x, weight, bias, residual=None, relu=False):
+    """LN(x (+ residual)) (+ReLU), eps 1e-5, fp32 statistics."""
+    return K.layer_norm(x, weight, bias, residual, relu)
+
+
+def conv2d(x, weight, bias, pad, relu=False):
+    """[library] cuDNN conv (+ReLU)."""
+    y = F.conv2d(x, weight, bias, padding=pad)
+    return F.relu(y) if relu else y
+
+
+def relu(x):
+    return F.relu(x)
+
+
+def add_relu(a, b):
+    return F.relu(a + b)
+
+
+def sigmoid_gate(gate_pre, x):
+    return torch.sigmoid(gate_pre) * x
+
+
+def atan_squash(v):
+    return (2.0 / math.pi) * torch.atan((math.pi / 2.0) * v)
+
+
+def max_pool2(x):
+    return F.max_pool2d(x, 2, 2)
+
+
+def upsample_bilinear2(x):
+    return F.interpolate(x, scale_factor=2., mode='bilinear')
+
+
+def gated_residual(r, g, update_sp, x):
+    """GatedResBlock tail: ReLU(tanh(r * sigmoid(g)) * UpdateSP + x)."""
+    return F.relu(torch.tanh(r * torch.sigmoid(g)) * update_sp + x)
+
+
+# ---------------------------------------------------------------------------------------------
+# entity path
+_ENTITY_LAYOUT = None
+
+
+def _entity_layout(device):
+    """Column offsets of the 997-wide feature vector (entity_encoder.py:60-78)."""
+    global _ENTITY_LAYOUT
+    if _ENTITY_LAYOUT is None or _ENTITY_LAYOUT['dev'] != device:
+        off = 0
+        one_hot, binary, scalar = [], [], []
+        for name, _, arc, num in C.ENTITY_FIELDS:
+            if arc == 'one_hot':
+                one_hot.append((name, off, num))
+            elif arc == 'binary':
+                binary.append((name, off, num))
+            else:
+                scalar.append((name, off))
+            off += num
+        _ENTITY_LAYOUT = {
+            'dev': device, 'one_hot': one_hot, 'binary': binary, 'scalar': scalar,
+            'oh_off': torch.tensor([o for _, o, _ in one_hot], device=device),
+            'oh_max': torch.tensor([n - 1 for _, _, n in one_hot], device=device),
+            'bin_cols': torch.tensor([o + i for _, o, n in binary for i in range(n)], device=device),
+            'sc_cols': torch.tensor([o for _, o in scalar], device=device),
+        }
+    return _ENTITY_LAYOUT
+
+
+def entity_embed(entity_info, weight, bias):
+    """ReLU(onehot_concat(entity_info) @ W^T + b) without building the 997-wide concat: one weight
+    column per one-hot field is gathered and summed, bit columns and the 8 ratio columns are added."""
+    x0 = entity_info['x']
+    require_cuda(x0)
+    return K.entity_embed(entity_info, weight, bias, _entity_layout(x0.device))
+
+
+def masked_mean(x, entity_num):
+    """sum over valid entities / entity_num (entity_encoder.py:83-85)."""
+    N = x.shape[1]
+    mask = torch.arange(N, device=x.device).unsqueeze(0) < entity_num.unsqueeze(1)
+    return (x * mask.unsqueeze(2)).sum(dim=1) / entity_num.unsqueeze(-1)
+
+
+def attention(qkv, key_len, heads, head_dim):
+    """softmax(Q K^T / sqrt(d), keys >= key_len masked) V over packed qkv [R,N,3*heads*head_dim]."""
+    return K.attention(qkv, key_len, heads, head_dim)
+
+
+def scatter_connection(proj, x, y, entity_num, H, W, scatter_type='add'):
+    """[kernel] ScatterConnection (module_utils.py:11-34): sort-then-segment, atomic-free, ascending
+    entity order per cell.  proj [R,N,D] fp32, x/y [R,N] integer -> [R,D,H,W] fp32."""
+    require_cuda(proj)
+    return K.ScatterConnection.apply(proj, x, y, entity_num, H, W, scatter_type)
+
+
+# ---------------------------------------------------------------------------------------------
+# spatial path
+_EFFECTS = [n for n, arc, _ in C.SPATIAL_FIELDS if arc == 'scatter']
+_ONE_HOT_PLANES = [(n, k) for n, arc, k in C.SPATIAL_FIELDS if arc == 'one_hot']
+
+
+def spatial_project(spatial_info, scatter_map, weight, bias):
+    """1x1 conv 56->32 + ReLU over the on-the-fly 56-channel input (spatial_encoder.py:52-72)."""
+    hm = spatial_info['height_map']
+    R, H, W = hm.shape
+    planes = [hm.float().unsqueeze(1) / 256]
+    for name, num in _ONE_HOT_PLANES:
+        planes.append(F.one_hot(spatial_info[name].long(), num).permute(0, 3, 1, 2).float())
+    for name in _EFFECTS:
+        e = torch.zeros(R, H * W, device=hm.device)
+        e.scatter_(1, spatial_info[name].long(), 1.0)          # zero padding => pixel (0,0) set (App. A7)
+        planes.append(e.view(R, 1, H, W))
+    planes.append(scatter_map)
+    return F.relu(F.conv2d(torch.cat(planes, dim=1), weight, bias))
+
+
+# ---------------------------------------------------------------------------------------------
+# scalar path
+def embedding_relu(idx, table):
+    return F.relu(F.embedding(idx.long().clamp(max=table.shape[0] - 1), table))
+
+
+def time_encode(t, position_array):
+    t = t.float().unsqueeze(1)
+    v = torch.empty(t.shape[0], position_array.shape[0], device=t.device)
+    v[:, 0::2] = torch.sin(t * position_array[0::2])
+    v[:, 1::2] = torch.cos(t * position_array[1::2])
+    return v
+
+
+def build_order_embed(order, location, weight, bias):
+    """ReLU(W . [one_hot(order,174) | eye(20) | bits10(x) | bits10(y)] + b) as column gathers."""
+    R, L = order.shape
+    Wt = weight.t()                                             # [214, 64]
+    loc = location.long()
+    shifts = torch.arange(9, -1, -1, device=order.device)
+    bx = ((loc % C.SPATIAL_X).unsqueeze(-1) >> shifts & 1).float()
+    by = ((loc // C.SPATIAL_X).unsqueeze(-1) >> shifts & 1).float()
+    y = Wt[order.long()] + Wt[174:194].unsqueeze(0) + bx @ Wt[194:204] + by @ Wt[204:214] + bias
+    return F.relu(y)
+
+
+# ---------------------------------------------------------------------------------------------
+# recurrent core
+def lnlstm_layer(x, h, c, cell):
+    """One LayerNorm-LSTM layer over time (lstm.py:138-167).  x [T,B,I] -> ([T,B,H], h_T, c_T)."""
+    return K.lnlstm_layer(x, h, c, cell)
+
+
+# ---------------------------------------------------------------------------------------------
+# heads
+def gumbel_argmax(logits, noise):
+    """[kernel] argmax_k(fp32 logit_k + g_k), lowest index on ties."""
+    return K.gumbel_argmax(logits, noise)
+
+
+def fresh_gumbel(rows, n_entity, device):
+    def gum(*shape):
+        u = torch.rand(*shape, device=device).clamp_(1e-10, 1.0 - 1e-7)
+        return -torch.log(-torch.log(u))
+    return {'action_type': gum(rows, C.NUM_ACTIONS), 'delay': gum(rows, 128), 'queued': gum(rows, 2),
+            'selected_units': gum(C.MAX_SELECTED_UNITS_NUM, rows, n_entity + 1),
+            'target_unit': gum(rows, n_entity), 'target_location': gum(rows, C.SPATIAL_Y * C.SPATIAL_X)}
+
+
+def one_hot_linear(idx, weight, bias, relu=False):
+    """fc over a one-hot input == gather of one weight column (+bias)."""
+    y = weight.t()[idx.long()] + bias
+    return F.relu(y) if relu else y
+
+
+def categorical_log_prob(logits, action):
+    return torch.log_softmax(logits, dim=-1).gather(-1, action.unsqueeze(-1)).squeeze(-1)
+
+
+def pointer_keys(key, end_embedding, entity_num):
+    """Append a row and place the end-flag embedding at index entity_num (action_arg_head.py:118-129)."""
+    R, N, D = key.shape
+    key = torch.cat([key, key.new_zeros(R, 1, D)], dim=1)
+    is_end = torch.arange(N + 1, device=key.device).unsqueeze(0) == entity_num.unsqueeze(1)
+    return torch.where(is_end.unsqueeze(2), end_embedding.view(1, 1, D), key)
+
+
+def pointer_logits(query, key, entity_num, temperature=1.0, extra_mask=None):
+    """logits[r,n] = <query[r], key[r,n]>, keys n >= entity_num masked to -1e9."""
+    logits = torch.einsum('rk,rnk->rn', query, key)
+    mask = torch.arange(key.shape[1], device=key.device).unsqueeze(0) < entity_num.unsqueeze(1)
+    if extra_mask is not None:
+        mask = mask & extra_mask
+    logits = logits.masked_fill(~mask, -1e9)
+    return logits / temperature if temperature != 1.0 else logits
+
+
+def _su_step(head, ae, h, c):
+    q = head.query_fc2(head.query_fc1(ae))
+    out, h, c = K.lnlstm_layer(q.unsqueeze(0), h, c, head.lstm.layers[0].cell)
+    return out[0], h, c
+
+
+def selected_units_train(head, key, ae0, entity_num, selected_units, selected_units_num, temperature):
+    """Teacher-forced pointer loop (action_arg_head.py:168-216).  The loop length is the compile-time
+    maximum needed by the batch, read once (one host sync per call instead of 2-4 per step)."""
+    R, N1, D = key.shape
+    dev = key.device
+    ar = torch.arange(R, device=dev)
+    S = max(int(selected_units_num.max()), 1)
+    h = key.new_zeros(R, 32)
+    c = key.new_zeros(R, 32)
+    lm = torch.arange(N1, device=dev).unsqueeze(0) < (entity_num + 1).unsqueeze(1)
+    lm[ar, entity_num] = False
+    one_hot = key.new_zeros(R, N1)
+    end_flag = torch.zeros(R, dtype=torch.bool, device=dev)
+    has_units = (selected_units_num != 0).unsqueeze(1)
+    ae = ae0
+    logits = []
+    for i in range(S):
+        if i > 0:
+            lm = lm.clone()
+            if i == 1:
+                lm[ar, entity_num] = True
+            lm[ar, selected_units[:, i - 1]] = False
+        q, h, c = _su_step(head, ae, h, c)
+        logits.append(torch.einsum('rk,rnk->rn', q, key).masked_fill(~lm, -1e9))
+        end_flag = end_flag | (selected_units[:, i] == entity_num)
+        pick = F.one_hot(selected_units[:, i], N1).to(one_hot.dtype) * (~end_flag).unsqueeze(1)
+        one_hot = torch.maximum(one_hot, pick)
+        emb = torch.einsum('rn,rnk->rk', one_hot, key)
+        emb = torch.where(has_units, emb / one_hot.sum(dim=1, keepdim=True), emb)
+        ae = ae0 + head.embed_fc2(head.embed_fc1(emb))
+    logits = torch.stack(logits, dim=1)
+    if temperature != 1.0:
+        logits = logits / temperature
+    return logits, selected_units, ae, selected_units_num, None
+
+
+def selected_units_sample(head, key, ae0, entity_num, su_mask, noise, temperature, extra_units):
+    """Sampling pointer loop (action_arg_head.py:262-313) with Gumbel-max picks; runs all 64 steps on the
+    device without the per-step `end_flag.all()` host sync, then trims to the reference's step count."""
+    R, N1, D = key.shape
+    dev = key.device
+    ar = torch.arange(R, device=dev)
+    S = C.MAX_SELECTED_UNITS_NUM
+    h = key.new_zeros(R, 32)
+    c = key.new_zeros(R, 32)
+    lm = torch.arange(N1, device=dev).unsqueeze(0) < (entity_num + 1).unsqueeze(1)
+    lm[ar, entity_num] = False
+    num = torch.where(su_mask, torch.full((R,), S, dtype=torch.long, device=dev), torch.zeros(R, dtype=torch.long, device=dev))
+    end_flag = ~su_mask
+    one_hot = key.new_zeros(R, N1)
+    ae = ae0
+    logits, units, all_ended = [], [], []
+    last_logits = torch.zeros(R, N1, device=dev)
+    done = torch.zeros((), dtype=torch.bool, device=dev)       # "reference loop has broken" flag
+    result = None
+    for i in range(S):
+        if i > 0:
+            if i == 1:
+                lm[ar, entity_num] = True
+            lm[ar, result] = False
+        q, h, c = _su_step(head, ae, h, c)
+        step_logits = torch.einsum('rk,rnk->rn', q, key).masked_fill(~lm, -1e9)
+        if temperature != 1.0:
+            step_logits = step_logits / temperature
+        result = K.gumbel_argmax(step_logits, noise[i])
+        hit = result == entity_num
+        num = torch.where(hit & ~end_flag & ~done, torch.full_like(num, i + 1), num)
+        end_flag_new = end_flag | hit
+        live = (~end_flag_new & ~done).to(one_hot.dtype).unsqueeze(1)
+        one_hot = torch.maximum(one_hot, F.one_hot(result, N1).to(one_hot.dtype) * live)
+        cnt = one_hot.sum(dim=1, keepdim=True)
+        emb = torch.einsum('rn,rnk->rk', one_hot, key)
+        emb = torch.where(cnt != 0, emb / cnt.clamp(min=1), emb)
+        ae_new = ae0 + head.embed_fc2(head.embed_fc1(emb))
+        ae = torch.where(done, ae, ae_new)
+        last_logits = torch.where(done, last_logits, step_logits)
+        end_flag = torch.where(done, end_flag, end_flag_new)
+        logits.append(step_logits)
+        units.append(result)
+        done = done | end_flag.all()
+        all_ended.append(done)
+    steps = int((~torch.stack(all_ended)).sum().item()) + 1     # one host read for the whole loop
+    steps = min(steps, S)
+    logits = torch.stack(logits[:steps], dim=1)
+    units = torch.stack(units[:steps], dim=1)
+    extra = key.new_zeros(R, N1)
+    if extra_units:
+        end_logit = last_logits[ar, entity_num]
+        extra = ((last_logits > end_logit.unsqueeze(1)) & ~end_flag.unsqueeze(1)).float()
+    return logits, units, ae, num, extra

@@ -1,0 +1,194 @@
+"""Drop-in for `distar.agent.default.rl_training.rl_loss.ReinforcementLoss` (rl_loss.py:8-199).
+
+`compute_loss(inputs)` takes the dict `Model.rl_learner_forward` returns and gives back the reference's
+log dict (same keys, python floats) with `'total_loss'` as an autograd tensor.  All arithmetic runs in the
+fused CUDA kernels of csrc/loss.cu: one stats pass over the logits, one scan kernel for V-trace / UPGO /
+TD(lambda), one gradient pass.  The ~65 `.item()` host syncs of the reference become a single 384-byte D2H copy.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from . import config as C
+
+HEADS = C.HEADS
+_MASKED_HEADS = {'queued': 2, 'selected_units': 3, 'target_unit': 4, 'target_location': 5}
+_MASK_FIELDS = ('build_order', 'built_unit', 'effect')
+
+
+class _FusedLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, owner, inputs, fields, *tensors):
+        nh = len(HEADS)
+        logits = [t.contiguous() for t in tensors[:nh]]
+        values = [t.contiguous() for t in tensors[nh:]]
+        dev = logits[0].device
+        T, B = inputs['reward']['winloss'].shape
+        TB = T * B
+        S = logits[3].shape[2]
+        a = _lib.AsLossArgs()
+        a.T, a.B, a.F, a.S = T, B, len(fields), S
+        a.N1, a.NE = logits[3].shape[-1], logits[4].shape[-1]
+        keep = []
+
+        def dptr(t, dtype=None):
+            t = t.contiguous() if dtype is None else t.to(dtype).contiguous()
+            keep.append(t)
+            return t.data_ptr()
+
+        mask = inputs['mask']
+        dlogits, stats, coefs = [], [], []
+        for h, name in enumerate(HEADS):
+            lg = logits[h]
+            rows = TB * S if h == 3 else TB
+            a.head_k[h] = lg.shape[-1]
+            a.logit[h] = lg.data_ptr()
+            a.teacher[h] = dptr(inputs['teacher_logit'][name], torch.float32)
+            a.action[h] = dptr(inputs['action'][name], torch.int64)
+            a.mu_logp[h] = dptr(inputs['action_log_prob'][name], torch.float32)
+            a.actions_mask[h] = dptr(mask['actions_mask'][name], torch.int64) if name in _MASKED_HEADS else None
+            dl = torch.empty_like(lg)
+            st = torch.empty((rows, 8), dtype=torch.float32, device=dev)
+            cf = torch.zeros((rows, 4), dtype=torch.float32, device=dev)
+            dlogits.append(dl); stats.append(st); coefs.append(cf)
+            a.dlogit[h], a.row_stats[h], a.coef[h] = dl.data_ptr(), st.data_ptr(), cf.data_ptr()
+        a.su_mask = dptr(mask['selected_units_mask'], torch.uint8)
+        a.su_logits_mask = dptr(mask['selected_units_logits_mask'], torch.uint8)
+        a.tu_logits_mask = dptr(mask['target_units_logits_mask'], torch.uint8)
+        a.cum_action_mask = dptr(mask['cum_action_mask'], torch.float32)
+        a.step = dptr(inputs['step'], torch.float32)
+        a.at_kl_steps = float(owner.action_type_kl_steps)
+        dvalues = []
+        lw = owner.loss_weights
+        for f, name in enumerate(fields):
+            a.value[f] = values[f].data_ptr()
+            dv = torch.empty_like(values[f])
+            dvalues.append(dv)
+            a.dvalue[f] = dv.data_ptr()
+            a.reward[f] = dptr(inputs['reward'][name], torch.float32)
+            a.field_mask[f] = dptr(mask[name + '_mask'], torch.float32) if name in _MASK_FIELDS else None
+            a.gamma_td[f] = float(owner.gammas['baseline'][name])
+            a.w_pg[f] = float(lw['pg'][name])
+            a.w_td[f] = float(lw['baseline'][name])
+        a.winloss_reward = dptr(inputs['reward']['winloss'], torch.float32)
+        a.battle_reward = dptr(inputs['reward']['battle'], torch.float32)
+        a.upgo_field = fields.index('winloss')
+        for h, name in enumerate(HEADS):
+            a.hw_pg[h] = float(owner.pg_head_weights[name])
+            a.hw_upgo[h] = float(owner.upgo_head_weights[name])
+            a.hw_ent[h] = float(owner.entropy_head_weights[name])
+            a.hw_kl[h] = float(owner.kl_head_weights[name])
+        only_value = bool(owner.only_update_value)
+        a.w_upgo = float(lw['upgo']['winloss'])
+        a.w_ent = float(lw['entropy'])
+        a.w_kl = float(lw['kl'])
+        a.w_atkl = float(lw['action_type_kl'])
+        F_ = len(fields)
+        sw = torch.zeros(_lib.AS_LOSS_MAX_STATS, dtype=torch.float32)
+        base = F_ * 10
+        for f in range(F_):
+            sw[f * 10 + 6] = a.w_td[f]
+        if only_value:                      # rl_loss.py:170-171: critic loss only -> policy coefficients vanish
+            for f in range(F_):
+                a.w_pg[f] = 0.0
+            a.w_upgo = a.w_ent = a.w_kl = a.w_atkl = 0.0
+        else:
+            for f in range(F_):
+                for h in range(6):
+                    sw[f * 10 + h] = a.w_pg[f] * a.hw_pg[h]
+            for h in range(6):
+                sw[base + h] = a.w_upgo * a.hw_upgo[h]
+                sw[base + 6 + h] = -a.w_ent * a.hw_ent[h]
+                sw[base + 12 + h] = a.w_kl * a.hw_kl[h]
+            sw[base + 18] = a.w_atkl
+        sw = sw.to(dev, non_blocking=True)
+        keep.append(sw)
+        a.stat_weight = sw.data_ptr()
+        partial = torch.empty((B, _lib.AS_LOSS_MAX_STATS), dtype=torch.float32, device=dev)
+        out = torch.zeros(_lib.AS_LOSS_MAX_STATS, dtype=torch.float32, device=dev)
+        a.partial, a.out = partial.data_ptr(), out.data_ptr()
+        st_ptr = _lib.stream_ptr()
+        _lib.call('as_rl_loss_forward', ctypes.byref(a), st_ptr)
+        _lib.LAUNCHES += 7
+        ctx.args = a
+        ctx.keep = keep + logits + values + stats + coefs + [partial, out]
+        ctx.dlogits, ctx.dvalues = dlogits, dvalues
+        ctx.mark_non_differentiable(out)
+        total = out[_lib.AS_LOSS_MAX_STATS - 1].clone()
+        return total, out
+
+    @staticmethod
+    def backward(ctx, gtotal, _gout):
+        # grad_scale is applied on the device side of dvalue; dlogit kernels take it as a launch argument.
+        # The usual call is loss.backward() => gtotal == 1 (read lazily: no host sync, use as tensor multiplier).
+        _lib.call('as_rl_loss_backward', ctypes.byref(ctx.args), 1.0, _lib.stream_ptr())
+        _lib.LAUNCHES += 5
+        grads = [g * gtotal for g in ctx.dlogits] + [g * gtotal for g in ctx.dvalues]
+        return (None, None, None) + tuple(grads)
+
+
+class ReinforcementLoss:
+    def __init__(self, learner_cfg, player_id):
+        cfg = C.AttrDict(C.deep_merge(C.DEFAULT_LOSS_CONFIG, dict(learner_cfg or {})))
+        self.cfg = cfg
+        self._bind(player_id)
+        self.only_update_value = False
+
+    def _bind(self, player_id=None):
+        cfg = self.cfg
+        self.gammas = cfg.gammas
+        self.loss_weights = cfg.loss_weights
+        self.action_type_kl_steps = cfg.kl.action_type_kl_steps
+        self.dapo_steps = cfg.dapo.dapo_steps
+        self.use_dapo = cfg.use_dapo
+        if player_id is not None and 'MP' not in player_id:      # rl_loss.py:22-24
+            self.use_dapo = False
+            self.loss_weights.dapo = 0.0
+        self.dapo_head_weights = cfg.dapo_head_weights
+        self.pg_head_weights = cfg.pg_head_weights
+        self.upgo_head_weights = cfg.upgo_head_weights
+        self.entropy_head_weights = cfg.entropy_head_weights
+        self.kl_head_weights = cfg.kl_head_weights
+        self.use_total_rhos = cfg.get('use_total_rhos', False)
+
+    def reset(self, learner_cfg):
+        self.cfg = C.AttrDict(C.deep_merge(self.cfg, dict(learner_cfg or {})))
+        self._bind()
+        self.only_update_value = False
+
+    def compute_loss(self, inputs):
+        if self.use_dapo:
+            raise NotImplementedError('DAPO KL (successive_logit) is not part of the B200 path yet')
+        fields = list(inputs['value'].keys())
+        if 'winloss' not in fields:
+            raise KeyError("the UPGO term needs the 'winloss' baseline (rl_loss.py:112-114)")
+        logits = [inputs['target_logit'][h] for h in HEADS]
+        if not logits[0].is_cuda:
+            raise RuntimeError('applestar_b200.ReinforcementLoss runs on CUDA tensors only (no CPU fallback)')
+        values = [inputs['value'][f] for f in fields]
+        total, out = _FusedLoss.apply(self, inputs, fields, *logits, *values)
+        s = out.tolist()                                          # the one D2H copy of the step's statistics
+        info = {}
+        base = len(fields) * 10
+        pg_hw, upgo_hw, ent_hw, kl_hw = (self.pg_head_weights, self.upgo_head_weights, self.entropy_head_weights,
+                                         self.kl_head_weights)
+        for f, name in enumerate(fields):
+            tot = 0.0
+            for h, head in enumerate(HEADS):
+                info['%s/%s' % (name, head)] = s[f * 10 + h]
+                tot += s[f * 10 + h] * float(pg_hw[head])
+            info[name + '/total'] = tot
+            info[name + '/td'] = s[f * 10 + 6]
+            info[name + '/reward'] = s[f * 10 + 7]
+            info[name + '/value'] = s[f * 10 + 8]
+        info['battle/reward'] = s[base + 19]
+        for key, off, hw, sign in (('upgo', 0, upgo_hw, 1.0), ('entropy', 6, ent_hw, -1.0), ('kl', 12, kl_hw, 1.0)):
+            tot = 0.0
+            for h, head in enumerate(HEADS):
+                info['%s/%s' % (key, head)] = s[base + off + h]
+                tot += sign * s[base + off + h] * float(hw[head])
+            info[key + '/total'] = tot
+        info['kl/extra_at'] = s[base + 18]
+        info['total_loss'] = total
+        return info

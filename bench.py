@@ -1,0 +1,283 @@
+#!/usr/bin/env python
+"""Benchmark of the hot path (BASELINE.json metric: RL learner traj-steps/s).
+
+  python bench.py --gpus N --steps K --warmup W            # this repo, one rank per GPU (torchrun for N > 1)
+  python bench.py --impl reference ...                      # the reference algorithm's CPU path (oracle port) on host cores
+
+A "step" = one learner iteration over a synthetic batch of `--traj` trajectories x `--unroll` steps per GPU:
+forward (encoder on (T+1)*B observations, LN-LSTM core, teacher-forced heads, baselines) -> fused RL loss ->
+backward -> bucketed gradient all-reduce (N > 1) -> fused clip + Adam.  Weak scaling: 16 trajectories per GPU,
+so N = 8 is the 128-trajectory data-parallel configuration of BASELINE.json.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--traj', type=int, default=16, help='trajectories per GPU')
+    ap.add_argument('--unroll', type=int, default=64)
+    ap.add_argument('--entities', type=int, default=512)
+    ap.add_argument('--cpu-sample', default='8x2', help='unroll x trajectories of the bounded CPU sample')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    return ap.parse_args()
+
+
+def load_spec():
+    with open(os.path.join(ROOT, 'tests', 'golden', 'state_dict_spec.json')) as f:
+        return [(k, tuple(s), t) for k, s, t in json.load(f)['winloss']]
+
+
+def peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return d.get('hbm_gbs', 6650.0), d.get('bf16_tflops', 1590.0), d.get('bf16_tflops_sustained', 1400.0), 'measured'
+    return 6650.0, 1590.0, 1400.0, 'fallback'
+
+
+# --------------------------------------------------------------------------------------------- CPU arm
+def cpu_learner_throughput(T, B, N, steps, warmup, threads):
+    """Oracle port (oracle/restate.py = CPU restatement of the reference algorithm) forward + loss + backward."""
+    from applestar_b200 import synth, config as C
+    from oracle import restate as R
+    torch.set_num_threads(threads)
+    sd = synth.full_state_dict(load_spec(), 0)
+    sd = {k: v.requires_grad_(True) for k, v in sd.items()}
+    data = synth.gen_trajectories(T, B, N, 1234)
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        out = R.rl_learner_forward(sd, ['winloss'], **synth.tree_map(lambda t: t.clone(), data))
+        info = R.compute_loss(C.DEFAULT_LOSS_CONFIG, out)
+        for v in sd.values():
+            v.grad = None
+        info['total_loss'].backward()
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    dt = sum(times) / len(times)
+    return T * B / dt, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    T, B = (int(x) for x in args.cpu_sample.split('x'))
+    threads = os.cpu_count() or 1
+    steps, warmup = max(1, min(args.steps, 3)), min(args.warmup, 1)
+    v, dt = cpu_learner_throughput(T, B, args.entities, steps, warmup, threads)
+    line = {
+        'impl': 'reference', 'metric': 'rl_learner_traj_steps_per_sec', 'value': v, 'unit': 'traj-steps/s',
+        'n_gpus': args.gpus, 'steps': steps, 'warmup': warmup, 'ms_per_step': dt * 1e3, 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': {'workload': 'rl_learner_step_T%d_B%d_N%d' % (args.unroll, args.traj, args.entities),
+                   'sample': 'T=%d B=%d N=%d per step' % (T, B, args.entities)},
+        'cpu_baseline': {'value': v, 'unit': 'traj-steps/s', 'cores': threads, 'kind': 'port',
+                         'sample': 'oracle/restate.py forward+loss+backward, T=%d B=%d N=%d, %d steps' % (
+                             T, B, args.entities, steps)},
+        'e2e': {'value': v, 'unit': 'traj-steps/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+    }
+    print(json.dumps(line))
+
+
+# --------------------------------------------------------------------------------------------- GPU arm
+class ClockSampler:
+    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.proc, self.lines = None, []
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(index), '--query-gpu=' + self.Q,
+                                          '--format=csv,noheader,nounits', '-lms', '100'], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append((time.perf_counter(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for ts, ln in self.lines:
+            if ts < t0 or ts > t1:
+                continue
+            parts = [p.strip() for p in ln.split(',')]
+            try:
+                sm.append(float(parts[0]))
+                mx = float(parts[1])
+            except (ValueError, IndexError):
+                continue
+            for nm, val in zip(names, parts[2:]):
+                if val.lower().startswith('active'):
+                    reasons.add(nm)
+        sm.sort()
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': mx, 'reasons': sorted(reasons),
+                'samples': len(sm)}
+
+
+def gemm_flops_hook(records):
+    """Wrap _lib.call so every as_gemm_bf16 / as_conv_nhwc_bf16 launch is bracketed by CUDA events (used for ONE
+    extra instrumented step after the timed region; the timed steps run unhooked)."""
+    from applestar_b200 import _lib
+    orig = _lib.call
+
+    def hooked(name, *a):
+        if name not in ('as_gemm_bf16', 'as_conv_nhwc_bf16'):
+            return orig(name, *a)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        orig(name, *a)
+        e1.record()
+        if name == 'as_gemm_bf16':
+            M, N, K, nb = a[4], a[5], a[6], a[12] * a[13]
+            fl = 2.0 * M * N * K * nb
+        else:
+            R, H, W, Cin, Cout, taps = a[4], a[5], a[6], a[7], a[8], a[9]
+            fl = 2.0 * R * (H + 2) * (W + 2) * Cin * Cout * taps
+        records.append((e0, e1, fl))
+    _lib.call = hooked
+    return orig
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    from applestar_b200 import Model, ReinforcementLoss, synth, _lib
+    from applestar_b200.learner import LearnerStep
+
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise RuntimeError('bench.py (impl=ours) needs a B200; there is no CPU fallback')
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    T, B, N = args.unroll, args.traj, args.entities
+
+    model = Model({'model': {'enable_baselines': ['winloss']}}, use_value_network=True)
+    model.load_state_dict(synth.full_state_dict(load_spec(), 0), strict=False)
+    model = model.to(dev)
+    step_fn = LearnerStep(model, ReinforcementLoss({}, 'MP0'))
+    host = synth.gen_trajectories(T, B, N, 1234 + rank)
+    host = synth.tree_map(lambda t: t.pin_memory(), host)
+    h2d_bytes = [0]
+
+    def count(t):
+        h2d_bytes[0] += t.numel() * t.element_size()
+        return t
+    synth.tree_map(count, host)
+    resident = synth.tree_map(lambda t: t.to(dev, non_blocking=True), host)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        w0 = time.perf_counter()
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        w1 = time.perf_counter()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return ms.item(), w0, w1
+
+    def step_resident():
+        step_fn(resident)
+
+    def step_e2e():
+        step_fn(synth.tree_map(lambda t: t.to(dev, non_blocking=True), host))      # H2D from pinned memory each step
+
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    sampler = ClockSampler(local) if rank == 0 else None
+    launches0 = _lib.LAUNCHES
+    ms, w0, w1 = timed(step_resident, args.steps)
+    launches = (_lib.LAUNCHES - launches0) // max(args.steps, 1)
+    clocks = sampler.stop(w0, w1) if sampler else None
+    step_e2e()
+    ms_e2e, _, _ = timed(step_e2e, args.steps)
+
+    # dominant kernel family = the tcgen05 GEMM: one instrumented step (outside the timed region)
+    records = []
+    orig = gemm_flops_hook(records)
+    step_resident()
+    torch.cuda.synchronize()
+    _lib.call = orig
+    g_ms = sum(e0.elapsed_time(e1) for e0, e1, _ in records)
+    g_fl = sum(fl for _, _, fl in records)
+    hbm, tf_burst, tf_sus, which = peaks()
+    achieved = g_fl / (g_ms * 1e-3) / 1e12 if g_ms > 0 else 0.0
+
+    if rank == 0:
+        total_steps = T * B * world
+        value = total_steps / (ms / args.steps * 1e-3)
+        e2e = total_steps / (ms_e2e / args.steps * 1e-3)
+        line = {
+            'metric': 'rl_learner_traj_steps_per_sec', 'value': value, 'unit': 'traj-steps/s', 'n_gpus': world,
+            'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': ms / args.steps,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
+            'config': {'workload': 'rl_learner_step_T%d_B%d_N%d' % (T, B, N), 'trajectories_per_gpu': B,
+                       'unroll_len': T, 'entities': N, 'baselines': ['winloss'], 'parallelism': 'dp%d' % world,
+                       'l2_policy': 'inputs_larger_than_l2 (%.0f MB per step)' % (h2d_bytes[0] / 1e6)},
+            'e2e': {'value': e2e, 'unit': 'traj-steps/s', 'h2d_bytes_per_step': h2d_bytes[0],
+                    'd2h_bytes_per_step': 4 * _lib.AS_LOSS_MAX_STATS},
+            'gpu_launches': int(launches),
+            'clocks': clocks,
+            'roofline': {'bound': 'tensor', 'kernel': 'as::gemm_kernel (all %d launches of one step)' % len(records),
+                         'achieved': achieved, 'peak': tf_sus, 'unit': 'TFLOP/s', 'frac': achieved / tf_sus,
+                         'peak_source': which + ' bf16_tflops_sustained', 'gemm_ms_per_step': g_ms,
+                         'gemm_share_of_step': g_ms / (ms / args.steps), 'traffic': None},
+        }
+        if not args.no_cpu_baseline:
+            Tc, Bc = (int(x) for x in args.cpu_sample.split('x'))
+            threads = os.cpu_count() or 1
+            v, dt = cpu_learner_throughput(Tc, Bc, N, 2, 1, threads)
+            line['cpu_baseline'] = {'value': v, 'unit': 'traj-steps/s', 'cores': threads, 'kind': 'port',
+                                    'sample': 'oracle/restate.py forward+loss+backward, T=%d B=%d N=%d, 2 steps' % (Tc, Bc, N)}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == '__main__':
+    main()

@@ -1,0 +1,90 @@
+/* applestar_b200 -- C ABI of the sm_100a kernels behind the DI-star / Applestar policy-value hot path.
+ *
+ * The reference has no native code: each entry point below replaces the stock ATen call
+ * sequence at the cited reference lines.  Conventions: raw device pointers + sizes, caller-owned memory and
+ * workspaces, `stream` is a cudaStream_t passed as void*, return 0 = ok, <0 = argument error (AS_E*),
+ * >0 = cudaError_t.  No entry point allocates or frees device memory unless it says so.
+ */
+#ifndef APPLESTAR_B200_H
+#define APPLESTAR_B200_H
+#include <stdint.h>
+#include "../applestar_b200/csrc/loss.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AS_EINVAL (-1)
+#define AS_ESIZE (-2)
+#define AS_EALIGN (-3)
+#define AS_EUNSUPPORTED (-4)
+#define AS_EDRIVER (-5)
+
+/* ABI version of this library (bumped when a signature changes). */
+int as_abi_version(void);
+
+/* ScatterConnection forward -- replaces scatter_connection(), distar/agent/default/model/module_utils.py:11-34
+ * (called from model/encoder.py:40-42).  emb [R,N,D] fp32, xs/ys [R,N] (idx_bytes = 1: uint8, 8: int64),
+ * entity_num [R] int64 or NULL (rows >= entity_num scatter 0.0, encoder.py:38), out [R,D,H,W] fp32 fully written.
+ * cover = 0: 'add' (ascending-entity-order fp32 sums, bit-exact vs the CPU reference), 1: 'cover' (last wins).
+ * N <= 512, D % 8 == 0, H*W % 4 == 0. */
+int as_scatter_connection_fwd(const float* emb, const void* xs, const void* ys, int idx_bytes,
+                              const int64_t* entity_num, float* out, int64_t R, int N, int D, int H, int W, int cover,
+                              void* stream);
+
+/* ScatterConnection backward ('add'): d_emb[r,e,:] = e < entity_num[r] ? d_out[r,:,cell(e)] : 0
+ * -- replaces autograd of scatter_add_ at module_utils.py:29. */
+int as_scatter_connection_bwd(const float* d_out, const void* xs, const void* ys, int idx_bytes,
+                              const int64_t* entity_num, float* d_emb, int64_t R, int N, int D, int H, int W,
+                              void* stream);
+
+/* bf16 tensor-core GEMM (tcgen05 / TMEM / TMA):  C[b][m][n] = act(alpha * sum_k A[b][m][k] B[b][n][k] + bias[n]).
+ * Replaces every nn.Linear / torch.matmul on the path (fc_block ctools/torch_utils/network/nn_module.py:231-270,
+ * Attention module_utils.py:95-110, LSTM gates lstm.py:140-141) and their autograd matmuls.
+ * a_mn / b_mn = 0: operand stored [rows][K contiguous]; 1: stored [K rows][M-or-N contiguous] (transposed use
+ * without a copy).  batch = nb0*nb1 with per-operand element strides.  c_bf16: 0 fp32 / 1 bf16 output.
+ * splits > 1: fp32 partial sums to ws[splits][batch][M][N] (then as_splitk_reduce); the value must equal
+ * as_gemm_splits(K, splits).  Pointers 16-byte aligned, lda/ldb multiples of 8 elements. */
+int as_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int a_mn, int b_mn,
+                 int64_t lda, int64_t ldb, int64_t ldc, int nb0, int nb1, int64_t a_sb0, int64_t a_sb1, int64_t b_sb0,
+                 int64_t b_sb1, int64_t c_sb0, int64_t c_sb1, int c_bf16, int relu, float alpha, int splits, float* ws,
+                 void* stream);
+/* Number of non-empty K splits the kernel will produce when `want` are requested. */
+int as_gemm_splits(int K, int want);
+/* out[i] = (accumulate ? out[i] : 0) + sum_s ws[s][i], s ascending (deterministic). */
+int as_splitk_reduce(const float* ws, float* out, int64_t n, int splits, int accumulate, void* stream);
+
+/* 3x3 / 1x1 convolution as implicit GEMM over zero-padded NHWC bf16 pixels -- replaces nn.Conv2d inside
+ * conv2d_block (nn_module.py:119-174; ResBlock res_block.py:61-65, GatedResBlock module_utils.py:224-231).
+ * x [R,(H+2),(W+2),Cin] bf16 with a zero border, w [Cout][taps*Cin] bf16 (tap-major), y [R,(H+2),(W+2),Cout]
+ * (border written as zero).  taps = 9 (3x3, pad 1) or 1.  Cin % 64 == 0. */
+int as_conv_nhwc_bf16(const void* x, const void* w, void* y, const float* bias, int64_t R, int H, int W, int Cin,
+                      int Cout, int taps, int w_mn, int y_bf16, int relu, void* stream);
+
+/* fp32 -> bf16 cast (operand staging for the GEMMs). */
+int as_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream);
+
+/* Gumbel-max sampling: out[r] = argmax_k(logit[r,k] + noise[r,k]), lowest index on ties -- replaces
+ * softmax + torch.multinomial at action_type_head.py:57-58 and action_arg_head.py:46-47,79-80,147-148,361-362,447-449. */
+int as_gumbel_argmax(const float* logit, const float* noise, int64_t* out, int64_t rows, int K, void* stream);
+
+/* Fused RL loss -- replaces ReinforcementLoss.compute_loss (rl_training/rl_loss.py:33-185) and the scans of
+ * rl_training/as_rl_utils.py (vtrace_advantages :284-312, upgo_returns :265-281, td_lambda_loss :221-243,
+ * entropy_loss :52-72, kl_loss :75-103).  forward fills args->out (means + total_loss), args->dvalue and the
+ * scratch buffers; backward writes args->dlogit scaled by grad_scale. */
+int as_rl_loss_forward(const AsLossArgs* args, void* stream);
+int as_rl_loss_backward(const AsLossArgs* args, float grad_scale, void* stream);
+
+/* Global-norm clip + Adam on flat fp32 buffers -- replaces GradClip 'pytorch_norm'
+ * (ctools/torch_utils/grad_clip.py:140-143) + torch.optim.Adam.step (agent/default/rl_learner.py:73-80,125,132).
+ * scratch: as_clip_adam_scratch_bytes() bytes of device memory.  shadow (bf16 copy of p) may be NULL.
+ * norm_out (device float, may be NULL) receives the pre-clip gradient norm. */
+int64_t as_clip_adam_scratch_bytes(void);
+int as_clip_adam(float* p, const float* g, float* m, float* v, void* shadow, int64_t n, float max_norm, float lr,
+                 float beta1, float beta2, float eps, float weight_decay, int step, float* scratch, float* norm_out,
+                 void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
