@@ -36,8 +36,7 @@ def _pad8(x):
     return F.pad(x, (0, (-k) % 8))
 
 
-_SHADOW_GEN = [0]          # bumped by the optimizer whenever weights change
-_W16_CACHE = {}
+_SHADOW_GEN = [0]          # bumped by the optimizer whenever weights change through raw pointers
 
 
 def weights_changed():
@@ -45,18 +44,21 @@ def weights_changed():
 
 
 def weight_bf16(w):
-    """bf16 copy of a weight matrix [N, K] (K padded to 8). Uses the flat bf16 shadow kept fresh by the fused
-    Adam kernel when the parameter lives in a FlatParams buffer, else a per-generation cache."""
+    """bf16 copy of a weight matrix [N, K] (K padded to 8).  Parameters that live in a FlatParams buffer carry a
+    view of the flat bf16 shadow the fused Adam kernel keeps fresh; otherwise the copy is cached on the Parameter
+    object itself (never keyed by address: freed addresses get reused by other models)."""
     sh = getattr(w, '_as_shadow', None)
-    if sh is not None and w.shape[-1] % 8 == 0:
+    if sh is not None and w.shape[-1] % 8 == 0 and w.dim() == 2:
         return sh
-    key = w.data_ptr()
-    hit = _W16_CACHE.get(key)
-    tag = (_SHADOW_GEN[0], w._version)
+    tag = (_SHADOW_GEN[0], w._version, w.data_ptr())
+    hit = getattr(w, '_as_w16', None)
     if hit is not None and hit[0] == tag:
         return hit[1]
     w16 = to_bf16(w.detach().reshape(w.shape[0], -1))
-    _W16_CACHE[key] = (tag, w16)
+    try:
+        w._as_w16 = (tag, w16)
+    except AttributeError:
+        pass
     return w16
 
 

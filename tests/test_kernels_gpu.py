@@ -89,7 +89,7 @@ def test_clip_adam_matches_torch():
     n = 100003
     p = torch.randn(n, generator=gen)
     p_ref = p.clone().requires_grad_(True)
-    opt = torch.optim.Adam([p_ref], lr=1e-3, betas=(0, 0.99), eps=1e-5)
+    opt = torch.optim.Adam([p_ref], lr=1e-3, betas=(0.0, 0.99), eps=1e-5)
     pc, m, v = p.cuda(), torch.zeros(n, device='cuda'), torch.zeros(n, device='cuda')
     shadow = torch.empty(n, device='cuda', dtype=torch.bfloat16)
     scratch = torch.empty(_lib.lib().as_clip_adam_scratch_bytes() // 4, device='cuda')
