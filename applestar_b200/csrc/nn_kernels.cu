@@ -1,0 +1,362 @@
+// Row-wise HBM-bound kernels with warp-shuffle reductions: LayerNorm (+residual, +ReLU) forward / backward,
+// masked attention softmax forward / backward, and the bf16 one-hot builder that feeds the entity embedding GEMM.
+#include "common.cuh"
+
+namespace as {
+
+constexpr int kMaxPerLane = 64;   // row width <= 32 * 64 = 2048
+
+// ------------------------------------------------------------------------------------------ LayerNorm
+// y = LN(x (+ res)) * gamma + beta (eps 1e-5, biased variance, fp32 statistics) (+ReLU); optional fp32 and bf16 copies.
+template <int PER_LANE>
+__global__ void __launch_bounds__(256)
+layer_norm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ res, const float* __restrict__ gamma,
+                      const float* __restrict__ beta, float* __restrict__ y32, __nv_bfloat16* __restrict__ y16,
+                      float* __restrict__ stats, long long rows, int C, int relu) {
+  const int lane = threadIdx.x & 31;
+  const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long row = warp_global; row < rows; row += warps_total) {
+    float v[PER_LANE];
+    const float* xr = x + row * C;
+    const float* rr = res ? res + row * C : nullptr;
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < PER_LANE; ++i) {
+      const int c = lane + i * 32;
+      float t = 0.f;
+      if (c < C) { t = __ldg(xr + c); if (rr) t += __ldg(rr + c); }
+      v[i] = t;
+      s += t;
+    }
+    const float mean = warp_sum(s) / (float)C;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < PER_LANE; ++i) {
+      const int c = lane + i * 32;
+      const float d = (c < C) ? v[i] - mean : 0.f;
+      q += d * d;
+    }
+    const float rstd = rsqrtf(warp_sum(q) / (float)C + 1e-5f);
+    if (lane == 0 && stats) { stats[row * 2] = mean; stats[row * 2 + 1] = rstd; }
+#pragma unroll
+    for (int i = 0; i < PER_LANE; ++i) {
+      const int c = lane + i * 32;
+      if (c < C) {
+        float o = (v[i] - mean) * rstd * __ldg(gamma + c) + __ldg(beta + c);
+        if (relu) o = fmaxf(o, 0.f);
+        if (y32) y32[row * C + c] = o;
+        if (y16) y16[row * C + c] = __float2bfloat16_rn(o);
+      }
+    }
+  }
+}
+
+// dx = rstd * (g*gamma - mean(g*gamma) - xhat * mean(g*gamma*xhat)),  g = dy32 + dy16 (masked by ReLU if fused)
+template <int PER_LANE>
+__global__ void __launch_bounds__(256)
+layer_norm_bwd_kernel(const float* __restrict__ dy32, const __nv_bfloat16* __restrict__ dy16,
+                      const float* __restrict__ x, const float* __restrict__ res, const float* __restrict__ gamma,
+                      const float* __restrict__ beta, const float* __restrict__ stats, float* __restrict__ dx,
+                      long long rows, int C, int relu) {
+  const int lane = threadIdx.x & 31;
+  const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long row = warp_global; row < rows; row += warps_total) {
+    const float mean = stats[row * 2], rstd = stats[row * 2 + 1];
+    float xh[PER_LANE], dg[PER_LANE];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < PER_LANE; ++i) {
+      const int c = lane + i * 32;
+      float a = 0.f, b = 0.f;
+      if (c < C) {
+        float t = __ldg(x + row * C + c);
+        if (res) t += __ldg(res + row * C + c);
+        a = (t - mean) * rstd;
+        float g = 0.f;
+        if (dy32) g += __ldg(dy32 + row * C + c);
+        if (dy16) g += __bfloat162float(dy16[row * C + c]);
+        const float gm = __ldg(gamma + c);
+        if (relu && (a * gm + __ldg(beta + c)) <= 0.f) g = 0.f;
+        b = g * gm;
+      }
+      xh[i] = a; dg[i] = b;
+      s1 += b; s2 += a * b;
+    }
+    const float m1 = warp_sum(s1) / (float)C, m2 = warp_sum(s2) / (float)C;
+#pragma unroll
+    for (int i = 0; i < PER_LANE; ++i) {
+      const int c = lane + i * 32;
+      if (c < C) dx[row * C + c] = rstd * (dg[i] - m1 - xh[i] * m2);
+    }
+  }
+}
+
+// dgamma[c] = sum_r g * xhat, dbeta[c] = sum_r g : column-parallel partial sums over row chunks (deterministic).
+__global__ void layer_norm_param_grad_kernel(const float* __restrict__ dy32, const __nv_bfloat16* __restrict__ dy16,
+                                             const float* __restrict__ x, const float* __restrict__ res,
+                                             const float* __restrict__ gamma, const float* __restrict__ beta,
+                                             const float* __restrict__ stats, float* __restrict__ partial,
+                                             long long rows, int C, int relu, int chunks) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int chunk = blockIdx.y;
+  if (c >= C) return;
+  const long long per = (rows + chunks - 1) / chunks;
+  const long long r0 = chunk * per, r1 = (r0 + per < rows) ? r0 + per : rows;
+  const float gm = gamma[c], bt = beta[c];
+  float ag = 0.f, ab = 0.f;
+  for (long long r = r0; r < r1; ++r) {
+    float t = __ldg(x + r * C + c);
+    if (res) t += __ldg(res + r * C + c);
+    const float a = (t - stats[r * 2]) * stats[r * 2 + 1];
+    float g = 0.f;
+    if (dy32) g += __ldg(dy32 + r * C + c);
+    if (dy16) g += __bfloat162float(dy16[r * C + c]);
+    if (relu && (a * gm + bt) <= 0.f) g = 0.f;
+    ag += g * a;
+    ab += g;
+  }
+  partial[((long long)chunk * 2 + 0) * C + c] = ag;
+  partial[((long long)chunk * 2 + 1) * C + c] = ab;
+}
+
+__global__ void layer_norm_param_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dgamma,
+                                               float* __restrict__ dbeta, int C, int chunks) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float ag = 0.f, ab = 0.f;
+  for (int k = 0; k < chunks; ++k) {
+    ag += partial[((long long)k * 2 + 0) * C + c];
+    ab += partial[((long long)k * 2 + 1) * C + c];
+  }
+  dgamma[c] = ag;
+  dbeta[c] = ab;
+}
+
+static int ln_grid(long long rows) {
+  long long blocks = (rows + 7) / 8;
+  const long long cap = 148LL * 8;
+  return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
+}
+
+#define LN_DISPATCH(KERNEL, ...)                                                         \
+  do {                                                                                   \
+    const int per = (C + 31) / 32;                                                       \
+    if (per <= 1) KERNEL<1><<<grid, 256, 0, st>>>(__VA_ARGS__);                          \
+    else if (per <= 4) KERNEL<4><<<grid, 256, 0, st>>>(__VA_ARGS__);                     \
+    else if (per <= 8) KERNEL<8><<<grid, 256, 0, st>>>(__VA_ARGS__);                     \
+    else if (per <= 12) KERNEL<12><<<grid, 256, 0, st>>>(__VA_ARGS__);                   \
+    else if (per <= 32) KERNEL<32><<<grid, 256, 0, st>>>(__VA_ARGS__);                   \
+    else KERNEL<48><<<grid, 256, 0, st>>>(__VA_ARGS__);                                  \
+  } while (0)
+
+int layer_norm_fwd(const float* x, const float* res, const float* gamma, const float* beta, float* y32, void* y16,
+                   float* stats, long long rows, int C, int relu, cudaStream_t st) {
+  if (rows <= 0) return AS_OK;
+  if (C <= 0 || C > 32 * 48) return AS_ESIZE;
+  if (!x || !gamma || !beta || (!y32 && !y16)) return AS_EINVAL;
+  const int grid = ln_grid(rows);
+  LN_DISPATCH(layer_norm_fwd_kernel, x, res, gamma, beta, y32, reinterpret_cast<__nv_bfloat16*>(y16), stats, rows, C, relu);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+constexpr int kLnChunks = 64;
+long long layer_norm_bwd_scratch_floats(int C) { return (long long)kLnChunks * 2 * C; }
+
+int layer_norm_bwd(const float* dy32, const void* dy16, const float* x, const float* res, const float* gamma,
+                   const float* beta, const float* stats, float* dx, float* dgamma, float* dbeta, float* scratch,
+                   long long rows, int C, int relu, cudaStream_t st) {
+  if (rows <= 0) return AS_OK;
+  if (C <= 0 || C > 32 * 48) return AS_ESIZE;
+  if (!x || !gamma || !beta || !stats || (!dy32 && !dy16)) return AS_EINVAL;
+  const __nv_bfloat16* d16 = reinterpret_cast<const __nv_bfloat16*>(dy16);
+  if (dx) {
+    const int grid = ln_grid(rows);
+    LN_DISPATCH(layer_norm_bwd_kernel, dy32, d16, x, res, gamma, beta, stats, dx, rows, C, relu);
+    AS_LAUNCH_CHECK();
+  }
+  if (dgamma && dbeta) {
+    if (!scratch) return AS_EINVAL;
+    const int chunks = rows < kLnChunks ? (int)rows : kLnChunks;
+    dim3 g((C + 127) / 128, chunks);
+    layer_norm_param_grad_kernel<<<g, 128, 0, st>>>(dy32, d16, x, res, gamma, beta, stats, scratch, rows, C, relu, chunks);
+    AS_LAUNCH_CHECK();
+    layer_norm_param_reduce_kernel<<<(C + 127) / 128, 128, 0, st>>>(scratch, dgamma, dbeta, C, chunks);
+    AS_LAUNCH_CHECK();
+  }
+  return AS_OK;
+}
+
+// ------------------------------------------------------------------------------------------ masked softmax
+// scores [G, Nq, Nk] fp32 (already scaled), key j of group g is valid iff j < key_len[g / groups_per_len]
+// (NULL = all valid) -> probabilities bf16, masked keys exactly 0 (== exp(-1e9 - max) in the reference).
+template <int PER_LANE>
+__global__ void __launch_bounds__(256)
+softmax_fwd_kernel(const float* __restrict__ s, const long long* __restrict__ key_len, __nv_bfloat16* __restrict__ p,
+                   long long rows, int Nq, int Nk, int groups_per_len) {
+  const int lane = threadIdx.x & 31;
+  const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long row = warp_global; row < rows; row += warps_total) {
+    int len = Nk;
+    if (key_len) {
+      const long long l = key_len[(row / Nq) / groups_per_len];
+      len = l < Nk ? (int)l : Nk;
+    }
+    float v[PER_LANE];
+    float m = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < PER_LANE; ++i) {
+      const int c = lane + i * 32;
+      v[i] = (c < len) ? __ldg(s + row * Nk + c) : -INFINITY;
+      m = fmaxf(m, v[i]);
+    }
+    m = warp_max(m);
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < PER_LANE; ++i) {
+      const int c = lane + i * 32;
+      v[i] = (c < len) ? expf(v[i] - m) : 0.f;
+      sum += v[i];
+    }
+    const float inv = 1.f / warp_sum(sum);
+#pragma unroll
+    for (int i = 0; i < PER_LANE; ++i) {
+      const int c = lane + i * 32;
+      if (c < Nk) p[row * Nk + c] = __float2bfloat16_rn(v[i] * inv);
+    }
+  }
+}
+
+// ds = p * (dp - sum_j dp_j p_j)   (bf16 out; the 1/sqrt(d) scale is folded into the following GEMMs)
+template <int PER_LANE>
+__global__ void __launch_bounds__(256)
+softmax_bwd_kernel(const __nv_bfloat16* __restrict__ p, const float* __restrict__ dp, __nv_bfloat16* __restrict__ ds,
+                   long long rows, int Nk) {
+  const int lane = threadIdx.x & 31;
+  const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long row = warp_global; row < rows; row += warps_total) {
+    float pv[PER_LANE], dv[PER_LANE];
+    float dot = 0.f;
+#pragma unroll
+    for (int i = 0; i < PER_LANE; ++i) {
+      const int c = lane + i * 32;
+      pv[i] = (c < Nk) ? __bfloat162float(p[row * Nk + c]) : 0.f;
+      dv[i] = (c < Nk) ? __ldg(dp + row * Nk + c) : 0.f;
+      dot += pv[i] * dv[i];
+    }
+    dot = warp_sum(dot);
+#pragma unroll
+    for (int i = 0; i < PER_LANE; ++i) {
+      const int c = lane + i * 32;
+      if (c < Nk) ds[row * Nk + c] = __float2bfloat16_rn(pv[i] * (dv[i] - dot));
+    }
+  }
+}
+
+#define SM_DISPATCH(KERNEL, ...)                                        \
+  do {                                                                  \
+    const int per = (Nk + 31) / 32;                                     \
+    if (per <= 1) KERNEL<1><<<grid, 256, 0, st>>>(__VA_ARGS__);         \
+    else if (per <= 4) KERNEL<4><<<grid, 256, 0, st>>>(__VA_ARGS__);    \
+    else if (per <= 8) KERNEL<8><<<grid, 256, 0, st>>>(__VA_ARGS__);    \
+    else if (per <= 16) KERNEL<16><<<grid, 256, 0, st>>>(__VA_ARGS__);  \
+    else KERNEL<32><<<grid, 256, 0, st>>>(__VA_ARGS__);                 \
+  } while (0)
+
+int softmax_fwd(const float* s, const long long* key_len, void* p, long long groups, int Nq, int Nk,
+                int groups_per_len, cudaStream_t st) {
+  const long long rows = groups * Nq;
+  if (rows <= 0) return AS_OK;
+  if (Nk <= 0 || Nk > 1024 || groups_per_len <= 0) return AS_ESIZE;
+  if (!s || !p) return AS_EINVAL;
+  const int grid = ln_grid(rows);
+  SM_DISPATCH(softmax_fwd_kernel, s, key_len, reinterpret_cast<__nv_bfloat16*>(p), rows, Nq, Nk, groups_per_len);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+int softmax_bwd(const void* p, const float* dp, void* ds, long long rows, int Nk, cudaStream_t st) {
+  if (rows <= 0) return AS_OK;
+  if (Nk <= 0 || Nk > 1024) return AS_ESIZE;
+  if (!p || !dp || !ds) return AS_EINVAL;
+  const int grid = ln_grid(rows);
+  SM_DISPATCH(softmax_bwd_kernel, reinterpret_cast<const __nv_bfloat16*>(p), dp, reinterpret_cast<__nv_bfloat16*>(ds), rows, Nk);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+// ------------------------------------------------------------------------------------------ entity features
+// Builds the bf16 feature matrix the embedding GEMM consumes (entity_encoder.py:60-78): row = entity, 997 real
+// columns + zero padding to `pitch`.  Field table: kind 0 one-hot (clamped to num-1), 1 binary (num bits, MSB first),
+// 2 value.  Each field's data is a separate [rows] array with its own element type.
+struct EntityFieldTable {
+  const void* data[40];
+  int kind[40];
+  int num[40];
+  int col[40];
+  int dtype[40];   // 0 u8, 1 i8, 2 i16, 3 f16, 4 i64, 5 f32
+  int n_fields;
+};
+
+__device__ __forceinline__ float field_value(const void* base, int dtype, long long i) {
+  switch (dtype) {
+    case 0: return (float)reinterpret_cast<const uint8_t*>(base)[i];
+    case 1: return (float)reinterpret_cast<const int8_t*>(base)[i];
+    case 2: return (float)reinterpret_cast<const int16_t*>(base)[i];
+    case 3: return __half2float(reinterpret_cast<const __half*>(base)[i]);
+    case 4: return (float)reinterpret_cast<const long long*>(base)[i];
+    default: return reinterpret_cast<const float*>(base)[i];
+  }
+}
+
+__global__ void entity_features_kernel(const EntityFieldTable tab, __nv_bfloat16* __restrict__ out, long long rows,
+                                       int pitch, int* __restrict__ neg_flag) {
+  // one warp per row: zero the row, then drop the ones / values in
+  const int lane = threadIdx.x & 31;
+  const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long row = warp_global; row < rows; row += warps_total) {
+    __nv_bfloat16* o = out + row * pitch;
+    uint4* o4 = reinterpret_cast<uint4*>(o);
+    for (int i = lane; i < pitch / 8; i += 32) o4[i] = make_uint4(0, 0, 0, 0);
+    __syncwarp();
+    for (int f = lane; f < tab.n_fields; f += 32) {
+      const float v = field_value(tab.data[f], tab.dtype[f], row);
+      if (tab.kind[f] == 0) {
+        int idx = (int)v;
+        if (idx < 0) { atomicExch(neg_flag, 1); idx = 0; }
+        if (idx > tab.num[f] - 1) idx = tab.num[f] - 1;
+        o[tab.col[f] + idx] = __float2bfloat16_rn(1.f);
+      } else if (tab.kind[f] == 1) {
+        const int iv = (int)v;
+        for (int b = 0; b < tab.num[f]; ++b)
+          if ((iv >> (tab.num[f] - 1 - b)) & 1) o[tab.col[f] + b] = __float2bfloat16_rn(1.f);
+      } else {
+        o[tab.col[f]] = __float2bfloat16_rn(v);
+      }
+    }
+  }
+}
+
+int entity_features(const void* const* data, const int* kind, const int* num, const int* col, const int* dtype,
+                    int n_fields, void* out, long long rows, int pitch, int* neg_flag, cudaStream_t st) {
+  if (rows <= 0) return AS_OK;
+  if (n_fields <= 0 || n_fields > 40 || pitch % 8 != 0) return AS_ESIZE;
+  if (!out || !neg_flag) return AS_EINVAL;
+  EntityFieldTable tab;
+  tab.n_fields = n_fields;
+  for (int i = 0; i < n_fields; ++i) {
+    tab.data[i] = data[i]; tab.kind[i] = kind[i]; tab.num[i] = num[i]; tab.col[i] = col[i]; tab.dtype[i] = dtype[i];
+    if (!data[i]) return AS_EINVAL;
+  }
+  const int grid = ln_grid(rows);
+  entity_features_kernel<<<grid, 256, 0, st>>>(tab, reinterpret_cast<__nv_bfloat16*>(out), rows, pitch, neg_flag);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+}  // namespace as
