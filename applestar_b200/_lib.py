@@ -44,13 +44,22 @@ _SIGS = {
                                           c_int, c_int, c_int, c_int, c_void_p]),
     'as_scatter_connection_bwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int64, c_int,
                                           c_int, c_int, c_int, c_void_p]),
-    'as_gemm_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int64,
-                             c_int64, c_int64, c_int, c_int, c_int64, c_int64, c_int64, c_int64, c_int64, c_int64,
-                             c_int, c_int, c_float, c_int, c_void_p, c_void_p]),
+    'as_gemm_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
+                             c_int64, c_int64, c_int64, c_int, c_int, c_int64, c_int64, c_int64, c_int64, c_int64,
+                             c_int64, c_int, c_int, c_float, c_int, c_void_p, c_int, c_void_p]),
     'as_gemm_splits': (c_int, [c_int, c_int]),
     'as_splitk_reduce': (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
     'as_conv_nhwc_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int,
                                   c_int, c_int, c_int, c_int, c_void_p]),
+    'as_layer_norm_fwd': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int,
+                                  c_int, c_void_p]),
+    'as_layer_norm_bwd_scratch_floats': (c_int64, [c_int]),
+    'as_layer_norm_bwd': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                  c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
+    'as_softmax_fwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p]),
+    'as_softmax_bwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
+    'as_entity_features': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int64, c_int,
+                                   c_void_p, c_void_p]),
     'as_cast_f32_bf16': (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     'as_gumbel_argmax': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     'as_rl_loss_forward': (c_int, [POINTER(AsLossArgs), c_void_p]),

@@ -15,13 +15,22 @@ int loss_backward(const AsLossArgs&, float, cudaStream_t);
 long long clip_adam_scratch_bytes();
 int clip_adam(float*, const float*, float*, float*, void*, long long, float, float, float, float, float, float, int,
               float*, float*, cudaStream_t);
+int layer_norm_fwd(const float*, const float*, const float*, const float*, float*, void*, float*, long long, int, int,
+                   cudaStream_t);
+long long layer_norm_bwd_scratch_floats(int);
+int layer_norm_bwd(const float*, const void*, const float*, const float*, const float*, const float*, const float*,
+                   float*, float*, float*, float*, long long, int, int, cudaStream_t);
+int softmax_fwd(const float*, const long long*, void*, long long, int, int, int, cudaStream_t);
+int softmax_bwd(const void*, const float*, void*, long long, int, cudaStream_t);
+int entity_features(const void* const*, const int*, const int*, const int*, const int*, int, void*, long long, int,
+                    int*, cudaStream_t);
 }  // namespace as
 
 #define ST(s) reinterpret_cast<cudaStream_t>(s)
 
 extern "C" {
 
-int as_abi_version(void) { return 1; }
+int as_abi_version(void) { return 2; }
 
 int as_scatter_connection_fwd(const float* emb, const void* xs, const void* ys, int idx_bytes,
                               const int64_t* entity_num, float* out, int64_t R, int N, int D, int H, int W, int cover,
@@ -44,13 +53,15 @@ int as_gemm_splits(int K, int want) {
   return (num_kb + per - 1) / per;
 }
 
-int as_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int a_mn, int b_mn,
+int as_gemm_bf16(const void* A, const void* B, void* C, void* C2, const float* bias, int M, int N, int K, int a_mn,
+                 int b_mn,
                  int64_t lda, int64_t ldb, int64_t ldc, int nb0, int nb1, int64_t a_sb0, int64_t a_sb1, int64_t b_sb0,
                  int64_t b_sb1, int64_t c_sb0, int64_t c_sb1, int c_bf16, int relu, float alpha, int splits, float* ws,
-                 void* stream) {
+                 int b_k_shift, void* stream) {
   as::GemmCall g;
-  g.A = A; g.B = B; g.C = C; g.bias = bias;
+  g.A = A; g.B = B; g.C = C; g.C2 = C2; g.bias = bias;
   g.M = M; g.N = N; g.K = K;
+  g.b_k_shift = b_k_shift;
   g.a_mn = a_mn != 0; g.b_mn = b_mn != 0;
   g.lda = lda; g.ldb = ldb; g.ldc = ldc;
   g.nb0 = nb0; g.nb1 = nb1;
@@ -88,6 +99,36 @@ int as_conv_nhwc_bf16(const void* x, const void* w, void* y, const float* bias, 
   }
   g.img_w = pw; g.img_h = ph;
   return as::gemm_run(g, ST(stream));
+}
+
+int as_layer_norm_fwd(const float* x, const float* res, const float* gamma, const float* beta, float* y32, void* y16,
+                      float* stats, int64_t rows, int C, int relu, void* stream) {
+  return as::layer_norm_fwd(x, res, gamma, beta, y32, y16, stats, rows, C, relu, ST(stream));
+}
+
+int64_t as_layer_norm_bwd_scratch_floats(int C) { return as::layer_norm_bwd_scratch_floats(C); }
+
+int as_layer_norm_bwd(const float* dy32, const void* dy16, const float* x, const float* res, const float* gamma,
+                      const float* beta, const float* stats, float* dx, float* dgamma, float* dbeta, float* scratch,
+                      int64_t rows, int C, int relu, void* stream) {
+  return as::layer_norm_bwd(dy32, dy16, x, res, gamma, beta, stats, dx, dgamma, dbeta, scratch, rows, C, relu,
+                            ST(stream));
+}
+
+int as_softmax_fwd(const float* scores, const int64_t* key_len, void* probs, int64_t groups, int Nq, int Nk,
+                   int groups_per_len, void* stream) {
+  return as::softmax_fwd(scores, reinterpret_cast<const long long*>(key_len), probs, groups, Nq, Nk, groups_per_len,
+                         ST(stream));
+}
+
+int as_softmax_bwd(const void* probs, const float* dprobs, void* dscores, int64_t rows, int Nk, void* stream) {
+  return as::softmax_bwd(probs, dprobs, dscores, rows, Nk, ST(stream));
+}
+
+int as_entity_features(const void* const* data, const int* kind, const int* num, const int* col, const int* dtype,
+                       int n_fields, void* out, int64_t rows, int pitch, int* neg_flag, void* stream) {
+  if (!data || !kind || !num || !col || !dtype) return AS_EINVAL;
+  return as::entity_features(data, kind, num, col, dtype, n_fields, out, rows, pitch, neg_flag, ST(stream));
 }
 
 int as_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream) {

@@ -16,6 +16,7 @@ struct GemmCall {
   int nb0 = 1, nb1 = 1;      // batch = nb0 * nb1
   long long a_sb0 = 0, a_sb1 = 0, b_sb0 = 0, b_sb1 = 0;   // batch strides (elements)
   void* C = nullptr;
+  void* C2 = nullptr;        // optional bf16 copy of C (only when C is fp32)
   int c_bf16 = 0;
   long long ldc = 0, c_sb0 = 0, c_sb1 = 0;
   const float* bias = nullptr;
@@ -26,6 +27,7 @@ struct GemmCall {
   int taps = 0;              // >0: implicit-GEMM conv; K = Cin, B = [N][taps*Cin], A rows shifted by shift[tap]
   int shift[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
   int img_w = 0, img_h = 0;  // padded image dims: border rows are written as zero
+  int b_k_shift = 0;         // MN-major B: offset (rows) added to the contraction coordinate
   int bn_override = 0;
 };
 

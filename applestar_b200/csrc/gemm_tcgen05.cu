@@ -28,8 +28,10 @@ struct GemmDev {
   int taps, cin_blocks, cin;
   int shift[9];
   int img_w, img_h;  // padded image dims for border masking (0 = off)
+  int b_k_shift;     // MN-major B only: row offset added to the contraction coordinate (conv wgrad taps)
   // epilogue
   void* C;
+  void* C2;   // optional bf16 copy of the output (same ldc / batch strides)
   int c_bf16;
   long long ldc, c_sb0, c_sb1;
   const float* bias;
@@ -131,7 +133,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           if (B_MN) {
 #pragma unroll
             for (int j = 0; j < BN / 64; ++j)
-              tma_load_4d(sb + j * (BK * 128), &tmB, &full_bar[stage], n0 + j * 64, kbcol, b0, b1);
+              tma_load_4d(sb + j * (BK * 128), &tmB, &full_bar[stage], n0 + j * 64, kbcol + p.b_k_shift, b0, b1);
           } else {
             tma_load_4d(sb, &tmB, &full_bar[stage], kbcol, n0, b0, b1);
           }
@@ -257,6 +259,26 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               } else {
                 for (int j = 0; j < 32 && col0 + j < p.N; ++j) dst[j] = f[j];
               }
+              if (p.C2 != nullptr) {
+                __nv_bfloat16* d2 = reinterpret_cast<__nv_bfloat16*>(p.C2) + off;
+                if (full && ((reinterpret_cast<uintptr_t>(d2) & 15) == 0)) {
+#pragma unroll
+                  for (int j = 0; j < 4; ++j) {
+                    uint4 u;
+                    __nv_bfloat162 h0 = __floats2bfloat162_rn(f[8 * j], f[8 * j + 1]);
+                    __nv_bfloat162 h1 = __floats2bfloat162_rn(f[8 * j + 2], f[8 * j + 3]);
+                    __nv_bfloat162 h2 = __floats2bfloat162_rn(f[8 * j + 4], f[8 * j + 5]);
+                    __nv_bfloat162 h3 = __floats2bfloat162_rn(f[8 * j + 6], f[8 * j + 7]);
+                    u.x = *reinterpret_cast<uint32_t*>(&h0);
+                    u.y = *reinterpret_cast<uint32_t*>(&h1);
+                    u.z = *reinterpret_cast<uint32_t*>(&h2);
+                    u.w = *reinterpret_cast<uint32_t*>(&h3);
+                    reinterpret_cast<uint4*>(d2)[j] = u;
+                  }
+                } else {
+                  for (int j = 0; j < 32 && col0 + j < p.N; ++j) d2[j] = __float2bfloat16_rn(f[j]);
+                }
+              }
             }
           }
         }
@@ -378,11 +400,12 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
     p.num_kb = (g.K + BK - 1) / BK;
   }
   p.img_w = g.img_w; p.img_h = g.img_h;
+  p.b_k_shift = g.b_mn ? g.b_k_shift : 0;
   p.splits = g.splits > 1 ? g.splits : 1;
   p.kb_per_split = (p.num_kb + p.splits - 1) / p.splits;
   p.splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;   // drop empty splits
   if (g.splits > 1 && p.splits != g.splits) return AS_ESIZE;     // caller sizes ws from as_gemm_splits()
-  p.C = g.C; p.c_bf16 = g.c_bf16; p.ldc = g.ldc; p.c_sb0 = g.c_sb0; p.c_sb1 = g.c_sb1;
+  p.C = g.C; p.C2 = g.C2; p.c_bf16 = g.c_bf16; p.ldc = g.ldc; p.c_sb0 = g.c_sb0; p.c_sb1 = g.c_sb1;
   p.bias = g.bias; p.relu = g.relu; p.alpha = g.alpha; p.ws = g.ws;
 
   CUtensorMap ta, tb;

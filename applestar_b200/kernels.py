@@ -64,15 +64,16 @@ def weight_bf16(w):
 
 # ---------------------------------------------------------------------------------------------
 def gemm(A, B, C, M, N, K, a_mn=False, b_mn=False, lda=None, ldb=None, ldc=None, bias=None, relu=False,
-         alpha=1.0, batch=(1, 1), a_strides=(0, 0), b_strides=(0, 0), c_strides=(0, 0), splits=1, ws=None):
+         alpha=1.0, batch=(1, 1), a_strides=(0, 0), b_strides=(0, 0), c_strides=(0, 0), splits=1, ws=None, C2=None,
+         b_k_shift=0):
     """Raw tcgen05 GEMM launch: C[b][m][n] = act(alpha * sum_k A[b][m][k] B[b][n][k] + bias[n])."""
     lda = lda if lda is not None else (M if a_mn else K)
     ldb = ldb if ldb is not None else (N if b_mn else K)
     ldc = ldc if ldc is not None else N
-    _lib.call('as_gemm_bf16', A.data_ptr(), B.data_ptr(), _ptr(C), _ptr(bias), M, N, K, int(a_mn), int(b_mn),
+    _lib.call('as_gemm_bf16', A.data_ptr(), B.data_ptr(), _ptr(C), _ptr(C2), _ptr(bias), M, N, K, int(a_mn), int(b_mn),
               lda, ldb, ldc, batch[0], batch[1], a_strides[0], a_strides[1], b_strides[0], b_strides[1],
               c_strides[0], c_strides[1], int(C is not None and C.dtype == torch.bfloat16), int(relu), float(alpha),
-              splits, _ptr(ws), _lib.stream_ptr())
+              splits, _ptr(ws), b_k_shift, _lib.stream_ptr())
 
 
 def _wgrad(dy16, x16, n_out, k_in):
@@ -93,54 +94,72 @@ def _wgrad(dy16, x16, n_out, k_in):
 
 
 class LinearFn(torch.autograd.Function):
-    """y = act(x W^T + b): forward, dgrad and wgrad all on the tcgen05 GEMM."""
+    """y = act(x W^T + b): forward, dgrad and wgrad all on the tcgen05 GEMM.  x may be fp32 or bf16.  Returns
+    (y fp32 | None, y bf16 | None): the bf16 copy (written by the same epilogue) feeds a following GEMM directly."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, relu):
+    def forward(ctx, x, weight, bias, relu, want32, want16):
         K = x.shape[-1]
         N = weight.shape[0]
         x2 = x.reshape(-1, K)
         M = x2.shape[0]
         x16 = to_bf16(x2)
         w16 = weight_bf16(weight)
-        y = torch.empty((M, N), dtype=torch.float32, device=x.device)
-        gemm(x16, w16, y, M, N, x16.shape[1], lda=x16.shape[1], ldb=w16.shape[1], bias=bias, relu=relu)
+        y32 = torch.empty((M, N), dtype=torch.float32, device=x.device) if want32 else None
+        y16 = torch.empty((M, N), dtype=torch.bfloat16, device=x.device) if want16 else None
+        if want32:
+            gemm(x16, w16, y32, M, N, x16.shape[1], lda=x16.shape[1], ldb=w16.shape[1], bias=bias, relu=relu, C2=y16)
+        else:
+            gemm(x16, w16, y16, M, N, x16.shape[1], lda=x16.shape[1], ldb=w16.shape[1], bias=bias, relu=relu)
         ctx.relu = relu
-        ctx.k = K
+        ctx.wk = weight.shape[1] if weight.dim() == 2 else x.shape[-1]
+        ctx.xk = K
         ctx.xshape = x.shape
+        ctx.x_bf16 = x.dtype == torch.bfloat16
         ctx.has_bias = bias is not None
-        ctx.save_for_backward(x16, w16, y if relu else None)
-        return y.view(*x.shape[:-1], N)
+        ctx.save_for_backward(x16, w16, (y32 if want32 else y16) if relu else None)
+        shp = (*x.shape[:-1], N)
+        return (None if y32 is None else y32.view(shp)), (None if y16 is None else y16.view(shp))
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy32, dy16):
         x16, w16, y = ctx.saved_tensors
         N = w16.shape[0]
         K8 = w16.shape[1]
+        if dy32 is not None and dy16 is not None:
+            dy = dy32 + dy16
+        else:
+            dy = dy32 if dy32 is not None else dy16
         dy2 = dy.reshape(-1, N)
         if ctx.relu:
             dy2 = dy2 * (y > 0)
         M = dy2.shape[0]
-        dy16 = to_bf16(dy2)                      # [M, N8]
+        dy16b = to_bf16(dy2)                      # [M, N8]
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
-            dx = torch.empty((M, K8), dtype=torch.float32, device=dy.device)
+            dx = torch.empty((M, K8), dtype=torch.bfloat16 if ctx.x_bf16 else torch.float32, device=dy.device)
             # dX[m,k] = sum_n dY[m,n] W[n,k]: A = dY (K-major over n), B = W read MN-major (k contiguous)
-            gemm(dy16, w16, dx, M, K8, N, lda=dy16.shape[1], b_mn=True, ldb=K8)
-            if K8 != ctx.k:
-                dx = dx[:, :ctx.k]
+            gemm(dy16b, w16, dx, M, K8, N, lda=dy16b.shape[1], b_mn=True, ldb=K8)
+            if K8 != ctx.xk:
+                dx = dx[:, :ctx.xk]
             dx = dx.reshape(ctx.xshape)
         if ctx.needs_input_grad[1]:
-            dw = _wgrad(dy16, x16, N, K8)
-            if K8 != ctx.k:
-                dw = dw[:, :ctx.k]
+            dw = _wgrad(dy16b, x16, N, K8)
+            if K8 != ctx.wk:
+                dw = dw[:, :ctx.wk]
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = dy2.sum(dim=0)
-        return dx, dw, db, None
+            db = dy2.sum(dim=0, dtype=torch.float32)
+        return dx, dw, db, None, None, None
 
 
-def linear(x, weight, bias, relu=False):
-    return LinearFn.apply(x, weight, bias, relu)
+def linear(x, weight, bias, relu=False, out_bf16=False):
+    y32, y16 = LinearFn.apply(x, weight, bias, relu, not out_bf16, out_bf16)
+    return y16 if out_bf16 else y32
+
+
+def linear_dual(x, weight, bias, relu=False):
+    """-> (fp32, bf16) copies of the same output."""
+    return LinearFn.apply(x, weight, bias, relu, True, True)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -187,44 +206,169 @@ def gumbel_argmax(logits, noise):
 
 
 # ---------------------------------------------------------------------------------------------
-# [library] pieces still on ATen (replacement queue: DESIGN.md section 6)
+class LayerNormFn(torch.autograd.Function):
+    """LN(x (+ residual)) (+ReLU) with warp-shuffle statistics.  Returns (y fp32, y bf16): the fp32 copy carries the
+    residual stream, the bf16 copy feeds the next GEMM without a separate cast pass.  Either can be skipped."""
+
+    @staticmethod
+    def forward(ctx, x, residual, weight, bias, relu, want32, want16):
+        C = x.shape[-1]
+        x = x.contiguous().float()
+        res = None if residual is None else residual.contiguous().float()
+        rows = x.numel() // C
+        y32 = torch.empty_like(x) if want32 else None
+        y16 = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device) if want16 else None
+        stats = torch.empty((rows, 2), dtype=torch.float32, device=x.device)
+        _lib.call('as_layer_norm_fwd', x.data_ptr(), _ptr(res), weight.data_ptr(), bias.data_ptr(), _ptr(y32),
+                  _ptr(y16), stats.data_ptr(), rows, C, int(relu), _lib.stream_ptr())
+        ctx.relu, ctx.C, ctx.rows = relu, C, rows
+        ctx.has_res = res is not None
+        ctx.save_for_backward(x, res, weight, bias, stats)
+        return y32, y16
+
+    @staticmethod
+    def backward(ctx, dy32, dy16):
+        x, res, weight, bias, stats = ctx.saved_tensors
+        C, rows = ctx.C, ctx.rows
+        dy32 = None if dy32 is None else dy32.contiguous()
+        dy16 = None if dy16 is None else dy16.contiguous()
+        dx = torch.empty_like(x) if (ctx.needs_input_grad[0] or ctx.needs_input_grad[1]) else None
+        need_w = ctx.needs_input_grad[2] or ctx.needs_input_grad[3]
+        dg = torch.empty_like(weight) if need_w else None
+        db = torch.empty_like(bias) if need_w else None
+        scratch = torch.empty(_lib.lib().as_layer_norm_bwd_scratch_floats(C), dtype=torch.float32,
+                              device=x.device) if need_w else None
+        _lib.call('as_layer_norm_bwd', _ptr(dy32), _ptr(dy16), x.data_ptr(), _ptr(res), weight.data_ptr(),
+                  bias.data_ptr(), stats.data_ptr(), _ptr(dx), _ptr(dg), _ptr(db), _ptr(scratch), rows, C,
+                  int(ctx.relu), _lib.stream_ptr())
+        return dx, (dx if ctx.has_res else None), dg, db, None, None, None
+
+
 def layer_norm(x, weight, bias, residual=None, relu=False):
-    if residual is not None:
-        x = x + residual
-    y = F.layer_norm(x, (x.shape[-1],), weight, bias, 1e-5)
-    return F.relu(y) if relu else y
+    return LayerNormFn.apply(x, residual, weight, bias, relu, True, False)[0]
+
+
+def layer_norm_dual(x, weight, bias, residual=None, relu=False):
+    """-> (fp32, bf16) copies of the same normalised rows."""
+    return LayerNormFn.apply(x, residual, weight, bias, relu, True, True)
+
+
+class AttentionFn(torch.autograd.Function):
+    """softmax(Q K^T / sqrt(d), keys >= key_len masked) V over a packed bf16 qkv buffer [R, N, 3*H*D].
+    Q K^T, P V and the four backward products are batched tcgen05 GEMMs reading Q/K/V (and dO) in place through
+    strided / MN-major tensor maps; the softmax (forward and backward) is a warp-shuffle kernel."""
+
+    @staticmethod
+    def forward(ctx, qkv, key_len, heads, head_dim):
+        R, N, _ = qkv.shape
+        H, D = heads, head_dim
+        ld = 3 * H * D
+        qkv = qkv.contiguous()
+        q, k, v = qkv[:, :, :H * D], qkv[:, :, H * D:2 * H * D], qkv[:, :, 2 * H * D:]
+        scale = 1.0 / math.sqrt(D)
+        Np = (N + 7) // 8 * 8                       # pitch of the score rows (bf16 P must be 16-byte pitched)
+        S = torch.empty((R, H, N, Np), dtype=torch.float32, device=qkv.device)
+        gemm(q, k, S, N, N, D, lda=ld, ldb=ld, ldc=Np, batch=(H, R), a_strides=(D, N * ld), b_strides=(D, N * ld),
+             c_strides=(N * Np, H * N * Np), alpha=scale)
+        P = torch.empty((R, H, N, Np), dtype=torch.bfloat16, device=qkv.device)
+        if Np != N:
+            P.zero_()
+        kl = None if key_len is None else key_len.contiguous().long()
+        _softmax_rows(S, kl, P, R * H, N, N, Np, H)
+        O = torch.empty((R, N, H * D), dtype=torch.bfloat16, device=qkv.device)
+        gemm(P, v, O, N, D, N, lda=Np, b_mn=True, ldb=ld, ldc=H * D, batch=(H, R),
+             a_strides=(N * Np, H * N * Np), b_strides=(D, N * ld), c_strides=(D, N * H * D))
+        ctx.dims = (R, N, Np, H, D)
+        ctx.save_for_backward(qkv, P)
+        return O
+
+    @staticmethod
+    def backward(ctx, dO):
+        qkv, P = ctx.saved_tensors
+        R, N, Np, H, D = ctx.dims
+        ld = 3 * H * D
+        scale = 1.0 / math.sqrt(D)
+        dO = to_bf16(dO.contiguous().reshape(R * N, H * D)).view(R, N, H * D)
+        q, k, v = qkv[:, :, :H * D], qkv[:, :, H * D:2 * H * D], qkv[:, :, 2 * H * D:]
+        dqkv = torch.empty_like(qkv)
+        dq, dk, dv = dqkv[:, :, :H * D], dqkv[:, :, H * D:2 * H * D], dqkv[:, :, 2 * H * D:]
+        sP, sO = (N * Np, H * N * Np), (D, N * H * D)
+        sQ = (D, N * ld)
+        # dP = dO V^T
+        dP = torch.empty((R, H, N, Np), dtype=torch.float32, device=qkv.device)
+        gemm(dO, v, dP, N, N, D, lda=H * D, ldb=ld, ldc=Np, batch=(H, R), a_strides=sO, b_strides=sQ, c_strides=sP)
+        # dV = P^T dO   (both operands MN-major)
+        gemm(P, dO, dv, N, D, N, a_mn=True, lda=Np, b_mn=True, ldb=H * D, ldc=ld, batch=(H, R), a_strides=sP,
+             b_strides=sO, c_strides=sQ)
+        dS = torch.empty((R, H, N, Np), dtype=torch.bfloat16, device=qkv.device)
+        if Np != N:
+            dS.zero_()
+        _softmax_bwd_rows(P, dP, dS, R * H * N, N, Np)
+        # dQ = scale * dS K ; dK = scale * dS^T Q
+        gemm(dS, k, dq, N, D, N, lda=Np, b_mn=True, ldb=ld, ldc=ld, batch=(H, R), a_strides=sP, b_strides=sQ,
+             c_strides=sQ, alpha=scale)
+        gemm(dS, q, dk, N, D, N, a_mn=True, lda=Np, b_mn=True, ldb=ld, ldc=ld, batch=(H, R), a_strides=sP,
+             b_strides=sQ, c_strides=sQ, alpha=scale)
+        return dqkv, None, None, None
+
+
+def _softmax_rows(S, key_len, P, groups, Nq, Nk, pitch, groups_per_len):
+    if pitch == Nk:
+        _lib.call('as_softmax_fwd', S.data_ptr(), _ptr(key_len), P.data_ptr(), groups, Nq, Nk, groups_per_len,
+                  _lib.stream_ptr())
+    else:   # padded pitch: treat the pad columns as masked keys
+        kl = key_len if key_len is not None else torch.full((groups // groups_per_len,), Nk, dtype=torch.int64,
+                                                            device=S.device)
+        _lib.call('as_softmax_fwd', S.data_ptr(), kl.data_ptr(), P.data_ptr(), groups, Nq, pitch, groups_per_len,
+                  _lib.stream_ptr())
+
+
+def _softmax_bwd_rows(P, dP, dS, rows, Nk, pitch):
+    _lib.call('as_softmax_bwd', P.data_ptr(), dP.data_ptr(), dS.data_ptr(), rows, pitch, _lib.stream_ptr())
 
 
 def attention(qkv, key_len, heads, head_dim):
-    R, N, _ = qkv.shape
-    q, k, v = qkv.chunk(3, dim=2)
-    q = q.view(R, N, heads, head_dim).permute(0, 2, 1, 3)
-    k = k.view(R, N, heads, head_dim).permute(0, 2, 3, 1)
-    v = v.view(R, N, heads, head_dim).permute(0, 2, 1, 3)
-    s = torch.matmul(q, k) / math.sqrt(head_dim)
-    if key_len is not None:
-        mask = torch.arange(N, device=qkv.device).view(1, 1, 1, N) < key_len.view(R, 1, 1, 1)
-        s = s.masked_fill(~mask, -1e9)
-    o = torch.matmul(torch.softmax(s, dim=-1), v)
-    return o.permute(0, 2, 1, 3).reshape(R, N, heads * head_dim)
+    if qkv.dtype != torch.bfloat16:
+        qkv = to_bf16(qkv.reshape(-1, qkv.shape[-1])).view(qkv.shape)
+    return AttentionFn.apply(qkv, key_len, heads, head_dim)
+
+
+_DT_CODE = {torch.uint8: 0, torch.int8: 1, torch.int16: 2, torch.float16: 3, torch.int64: 4, torch.float32: 5}
+_KIND = {'one_hot': 0, 'binary': 1, 'unsqueeze': 2}
+
+
+def entity_features(entity_info, fields, pitch):
+    """bf16 [R*N, pitch] feature rows (997 real columns) straight from the narrow per-field arrays."""
+    import ctypes
+    n = len(fields)
+    first = entity_info[fields[0][0]]
+    rows = first.numel()
+    keep, col = [], 0
+    data = (ctypes.c_void_p * n)()
+    kind, num, cols, dts = (ctypes.c_int * n)(), (ctypes.c_int * n)(), (ctypes.c_int * n)(), (ctypes.c_int * n)()
+    for i, (name, _, arc, k) in enumerate(fields):
+        t = entity_info[name].contiguous()
+        if t.dtype not in _DT_CODE:
+            t = t.float()
+        keep.append(t)
+        data[i], kind[i], num[i], cols[i], dts[i] = t.data_ptr(), _KIND[arc], k, col, _DT_CODE[t.dtype]
+        col += k
+    out = torch.empty((rows, pitch), dtype=torch.bfloat16, device=first.device)
+    neg = torch.zeros(1, dtype=torch.int32, device=first.device)
+    _lib.call('as_entity_features', data, kind, num, cols, dts, n, out.data_ptr(), rows, pitch, neg.data_ptr(),
+              _lib.stream_ptr())
+    return out, neg
 
 
 def entity_embed(entity_info, weight, bias, layout):
-    Wt = weight.t()                                               # [997, 256]
-    idx = torch.stack([entity_info[n].long() for n, _, _ in layout['one_hot']], dim=-1)
-    if (idx < 0).any():
-        raise RuntimeError('negative one-hot index in entity_info')          # entity_encoder.py:68-71
-    idx = torch.minimum(idx, layout['oh_max']) + layout['oh_off']
-    R, N, Fh = idx.shape
-    y = F.embedding_bag(idx.view(R * N, Fh), Wt, mode='sum')
-    bits = []
-    for n, _, nb in layout['binary']:
-        shifts = torch.arange(nb - 1, -1, -1, device=idx.device)
-        bits.append(((entity_info[n].long().unsqueeze(-1) >> shifts) & 1).float())
-    y = y + torch.cat(bits, dim=-1).view(R * N, -1) @ Wt[layout['bin_cols']]
-    sc = torch.stack([entity_info[n].float() for n, _ in layout['scalar']], dim=-1)
-    y = y + sc.view(R * N, -1) @ Wt[layout['sc_cols']]
-    return F.relu(y + bias).view(R, N, -1)
+    """ReLU(features @ W^T + b) -> (fp32, bf16) [R, N, 256].  The one-hot concat exists only as a bf16 GEMM operand."""
+    from . import config as C
+    first = entity_info['x']
+    R, N = first.shape
+    feats, neg = entity_features(entity_info, C.ENTITY_FIELDS, 1000)
+    entity_embed.last_neg_flag = neg          # checked lazily by the caller (no host sync on the hot path)
+    y32, y16 = linear_dual(feats, weight, bias, relu=True)
+    return y32.view(R, N, -1), y16.view(R, N, -1)
 
 
 def lnlstm_layer(x, h, c, cell):

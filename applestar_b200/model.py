@@ -28,13 +28,13 @@ def _xavier_normal(w):
 class FC(nn.Sequential):
     """fc_block: `.0` = Linear; ReLU fused into the GEMM epilogue when `relu`."""
 
-    def __init__(self, cin, cout, relu=False):
+    def __init__(self, cin, cout, relu=False, out_bf16=False):
         super().__init__(nn.Linear(cin, cout))
         _xavier_normal(self[0].weight)
-        self.relu = relu
+        self.relu, self.out_bf16 = relu, out_bf16
 
     def forward(self, x):
-        return ops.linear(x, self[0].weight, self[0].bias, self.relu)
+        return ops.linear(x, self[0].weight, self[0].bias, self.relu, self.out_bf16)
 
 
 class FCLN(nn.Sequential):
@@ -89,7 +89,7 @@ class Attention(nn.Module):
     def __init__(self, dim, head_dim, head_num):
         super().__init__()
         self.head_num, self.head_dim = head_num, head_dim
-        self.attention_pre = FC(dim, head_dim * head_num * 3)
+        self.attention_pre = FC(dim, head_dim * head_num * 3, out_bf16=True)
         self.project = FC(head_dim * head_num, dim)
 
     def forward(self, x, key_len):
@@ -102,19 +102,21 @@ class TransformerLayer(nn.Module):
         super().__init__()
         self.attention = Attention(dim, head_dim, head_num)
         self.layernorm1 = nn.LayerNorm(dim)
-        self.mlp = nn.Sequential(FC(dim, hidden_dim, relu=True), FC(hidden_dim, dim, relu=True))
+        self.mlp = nn.Sequential(FC(dim, hidden_dim, relu=True, out_bf16=True), FC(hidden_dim, dim, relu=True))
         self.layernorm2 = nn.LayerNorm(dim)
         self.post_ln = post_ln
 
-    def forward(self, x, key_len):
+    def forward(self, x32, x16, key_len, final_relu=False):
+        """(fp32 residual stream, bf16 GEMM operand) in and out."""
         l1, l2 = self.layernorm1, self.layernorm2
         if self.post_ln:     # module_utils.py:133-139
-            x = ops.layer_norm(self.attention(x, key_len), l1.weight, l1.bias, residual=x)
-            x = ops.layer_norm(self.mlp(x), l2.weight, l2.bias, residual=x)
+            x32, x16 = ops.layer_norm_dual(self.attention(x16, key_len), l1.weight, l1.bias, residual=x32)
+            x32, x16 = ops.layer_norm_dual(self.mlp(x16), l2.weight, l2.bias, residual=x32, relu=final_relu)
         else:                # :140-148
-            x = x + self.attention(ops.layer_norm(x, l1.weight, l1.bias), key_len)
-            x = x + self.mlp(ops.layer_norm(x, l2.weight, l2.bias))
-        return x
+            x32 = x32 + self.attention(ops.layer_norm_dual(x32, l1.weight, l1.bias)[1], key_len)
+            x32 = x32 + self.mlp(ops.layer_norm_dual(x32, l2.weight, l2.bias)[1])
+            x16 = None
+        return x32, x16
 
 
 class Transformer(nn.Module):
@@ -126,10 +128,10 @@ class Transformer(nn.Module):
         self.layers = nn.ModuleList([TransformerLayer(output_dim, head_dim, hidden_dim, head_num, post_ln)
                                      for _ in range(layer_num)])
 
-    def run_layers(self, x, key_len=None):
-        for layer in self.layers:
-            x = layer(x, key_len)
-        return x
+    def run_layers(self, x32, x16, key_len=None, final_relu=False):
+        for i, layer in enumerate(self.layers):
+            x32, x16 = layer(x32, x16, key_len, final_relu and i == len(self.layers) - 1)
+        return x32, x16
 
 
 class EntityEncoder(nn.Module):
@@ -145,16 +147,17 @@ class EntityEncoder(nn.Module):
             elif arc == 'binary':
                 self.encode_modules[name] = _binary_table(num)
         self.transformer = Transformer(C.ENTITY_INPUT_DIM, 128, 1024, 256, 2, 3, post_ln=True)
-        self.entity_fc = FC(256, 256, relu=True)
+        self.entity_fc = FC(256, 256, relu=True, out_bf16=True)
         self.embed_fc = FC(256, 256, relu=True)
 
     def forward(self, entity_info, entity_num):
         emb = self.transformer.embedding[0]
-        x = ops.entity_embed(entity_info, emb.weight, emb.bias)           # [R,N,256], ReLU applied
-        x = self.transformer.run_layers(x, entity_num)
-        x = ops.relu(x)                                                    # in-place ReLU feeds the mean too (A1)
-        entity_embeddings = self.entity_fc(x)
-        pooled = ops.masked_mean(x, entity_num)
+        x32, x16 = ops.entity_embed(entity_info, emb.weight, emb.bias)    # [R,N,256], ReLU applied
+        # the reference's in-place ReLU after the transformer feeds both entity_fc and the mean (A1): fused
+        # into the last LayerNorm
+        x32, x16 = self.transformer.run_layers(x32, x16, entity_num, final_relu=True)
+        entity_embeddings = self.entity_fc(x16)                           # bf16: consumed only by GEMMs
+        pooled = ops.masked_mean(x32, entity_num)
         return entity_embeddings, self.embed_fc(pooled)
 
 
@@ -205,7 +208,7 @@ class BeginningBuildOrderEncoder(nn.Module):
     def forward(self, order, location):
         emb = self.transformer.embedding[0]
         x = ops.build_order_embed(order, location, emb.weight, emb.bias)   # [R,20,64], ReLU applied
-        x = self.transformer.run_layers(x, None)
+        x, _ = self.transformer.run_layers(x, None, None)
         return self.embedd_fc(x.mean(dim=1))
 
 
@@ -559,6 +562,7 @@ class Model(nn.Module):
         return noise
 
     def _encode_core(self, spatial_info, entity_info, scalar_info, entity_num, hidden_state):
+        ops.raise_if_negative_index()
         lstm_input, ctx, base, ent, skip = self.encoder(spatial_info, entity_info, scalar_info, entity_num)
         out, state = self.core_lstm(lstm_input.unsqueeze(0), hidden_state)
         return out.squeeze(0), state, ctx, base, ent, skip
@@ -592,6 +596,7 @@ class Model(nn.Module):
                            selected_units_num, behaviour_logp, teacher_logit, mask, reward, step, batch_size,
                            unroll_len, **kwargs):
         B, T = batch_size, unroll_len
+        ops.raise_if_negative_index()
         flat_action = {k: v.flatten(0, 1) for k, v in action_info.items()}
         lstm_input, ctx, base, ent, skip = self.encoder(spatial_info, entity_info, scalar_info, entity_num)
         hs = hidden_state[0][0].shape[-1]

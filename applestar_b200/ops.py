@@ -23,15 +23,20 @@ def require_cuda(t):
 
 # ---------------------------------------------------------------------------------------------
 # dense layers
-def linear(x, weight, bias, relu=False):
-    """y = act(x @ W^T + b).  [kernel] tcgen05 GEMM when shapes qualify, else [library] cuBLAS."""
+def linear(x, weight, bias, relu=False, out_bf16=False):
+    """[kernel] y = act(x @ W^T + b) on the tcgen05 GEMM (fp32 or bf16 output)."""
     require_cuda(x)
-    return K.linear(x, weight, bias, relu)
+    return K.linear(x, weight, bias, relu, out_bf16)
 
 
 def layer_norm(x, weight, bias, residual=None, relu=False):
-    """LN(x (+ residual)) (+ReLU), eps 1e-5, fp32 statistics."""
+    """[kernel] LN(x (+ residual)) (+ReLU), eps 1e-5, fp32 statistics."""
     return K.layer_norm(x, weight, bias, residual, relu)
+
+
+def layer_norm_dual(x, weight, bias, residual=None, relu=False):
+    """[kernel] same, returning (fp32, bf16) copies."""
+    return K.layer_norm_dual(x, weight, bias, residual, relu)
 
 
 def conv2d(x, weight, bias, pad, relu=False):
@@ -99,11 +104,21 @@ def _entity_layout(device):
 
 
 def entity_embed(entity_info, weight, bias):
-    """ReLU(onehot_concat(entity_info) @ W^T + b) without building the 997-wide concat: one weight
-    column per one-hot field is gathered and summed, bit columns and the 8 ratio columns are added."""
+    """[kernel] ReLU(onehot_concat(entity_info) @ W^T + b) -> (fp32, bf16).  The 997-wide concat exists only as a
+    bf16 GEMM operand written by one kernel from the narrow per-field arrays (never as 2 MB/obs of fp32)."""
     x0 = entity_info['x']
     require_cuda(x0)
     return K.entity_embed(entity_info, weight, bias, _entity_layout(x0.device))
+
+
+def raise_if_negative_index():
+    """Deferred form of the reference's RuntimeError on a negative one-hot index (entity_encoder.py:68-71): the flag
+    of the previous call is inspected at the next entry point, so the hot path never waits on the host."""
+    flag = getattr(K.entity_embed, 'last_neg_flag', None)
+    if flag is not None:
+        K.entity_embed.last_neg_flag = None
+        if int(flag.item()) != 0:
+            raise RuntimeError('negative one-hot index in entity_info')
 
 
 def masked_mean(x, entity_num):

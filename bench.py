@@ -153,7 +153,7 @@ def gemm_flops_hook(records):
         orig(name, *a)
         e1.record()
         if name == 'as_gemm_bf16':
-            M, N, K, nb = a[4], a[5], a[6], a[12] * a[13]
+            M, N, K, nb = a[5], a[6], a[7], a[13] * a[14]
             fl = 2.0 * M * N * K * nb
         else:
             R, H, W, Cin, Cout, taps = a[4], a[5], a[6], a[7], a[8], a[9]

@@ -41,14 +41,17 @@ int as_scatter_connection_bwd(const float* d_out, const void* xs, const void* ys
 /* bf16 tensor-core GEMM (tcgen05 / TMEM / TMA):  C[b][m][n] = act(alpha * sum_k A[b][m][k] B[b][n][k] + bias[n]).
  * Replaces every nn.Linear / torch.matmul on the path (fc_block ctools/torch_utils/network/nn_module.py:231-270,
  * Attention module_utils.py:95-110, LSTM gates lstm.py:140-141) and their autograd matmuls.
+ * C2 (optional, NULL to skip): bf16 copy of a fp32 C written by the same epilogue.  b_k_shift: rows added to the
+ * contraction coordinate of an MN-major B (used by the convolution wgrad taps; 0 otherwise).
  * a_mn / b_mn = 0: operand stored [rows][K contiguous]; 1: stored [K rows][M-or-N contiguous] (transposed use
  * without a copy).  batch = nb0*nb1 with per-operand element strides.  c_bf16: 0 fp32 / 1 bf16 output.
  * splits > 1: fp32 partial sums to ws[splits][batch][M][N] (then as_splitk_reduce); the value must equal
  * as_gemm_splits(K, splits).  Pointers 16-byte aligned, lda/ldb multiples of 8 elements. */
-int as_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int a_mn, int b_mn,
+int as_gemm_bf16(const void* A, const void* B, void* C, void* C2, const float* bias, int M, int N, int K, int a_mn,
+                 int b_mn,
                  int64_t lda, int64_t ldb, int64_t ldc, int nb0, int nb1, int64_t a_sb0, int64_t a_sb1, int64_t b_sb0,
                  int64_t b_sb1, int64_t c_sb0, int64_t c_sb1, int c_bf16, int relu, float alpha, int splits, float* ws,
-                 void* stream);
+                 int b_k_shift, void* stream);
 /* Number of non-empty K splits the kernel will produce when `want` are requested. */
 int as_gemm_splits(int K, int want);
 /* out[i] = (accumulate ? out[i] : 0) + sum_s ws[s][i], s ascending (deterministic). */
@@ -60,6 +63,35 @@ int as_splitk_reduce(const float* ws, float* out, int64_t n, int splits, int acc
  * (border written as zero).  taps = 9 (3x3, pad 1) or 1.  Cin % 64 == 0. */
 int as_conv_nhwc_bf16(const void* x, const void* w, void* y, const float* bias, int64_t R, int H, int W, int Cin,
                       int Cout, int taps, int w_mn, int y_bf16, int relu, void* stream);
+
+/* LayerNorm(x (+ residual)) * gamma + beta, eps 1e-5, optional fused ReLU -- replaces nn.LayerNorm at
+ * module_utils.py:135,139 (Transformer), lstm.py:140-151 (LN-LSTM), res_block.py:68-141 (ResFCBlock/ResFCBlock2).
+ * x/res [rows, C] fp32 (res may be NULL); outputs y32 fp32 and/or y16 bf16 (either may be NULL);
+ * stats [rows, 2] = (mean, rstd) saved for backward (may be NULL).  C <= 1536. */
+int as_layer_norm_fwd(const float* x, const float* res, const float* gamma, const float* beta, float* y32, void* y16,
+                      float* stats, int64_t rows, int C, int relu, void* stream);
+/* Backward: upstream gradient = dy32 (fp32, may be NULL) + dy16 (bf16, may be NULL).  dx (also the residual's
+ * gradient) may be NULL; dgamma/dbeta need `scratch` of as_layer_norm_bwd_scratch_floats(C) floats. */
+int64_t as_layer_norm_bwd_scratch_floats(int C);
+int as_layer_norm_bwd(const float* dy32, const void* dy16, const float* x, const float* res, const float* gamma,
+                      const float* beta, const float* stats, float* dx, float* dgamma, float* dbeta, float* scratch,
+                      int64_t rows, int C, int relu, void* stream);
+
+/* Masked attention softmax with warp-shuffle reductions -- replaces masked_fill_ + F.softmax at
+ * module_utils.py:100-104.  scores [groups, Nq, Nk] fp32 (already scaled by 1/sqrt(d)); key j of group g is valid
+ * iff j < key_len[g / groups_per_len] (key_len NULL = no mask); probs bf16 with masked keys exactly 0.  Nk <= 1024. */
+int as_softmax_fwd(const float* scores, const int64_t* key_len, void* probs, int64_t groups, int Nq, int Nk,
+                   int groups_per_len, void* stream);
+/* dscores (bf16) = probs * (dprobs - rowsum(dprobs * probs)). */
+int as_softmax_bwd(const void* probs, const float* dprobs, void* dscores, int64_t rows, int Nk, void* stream);
+
+/* bf16 feature rows for the entity embedding GEMM -- replaces the 28 embedding lookups + torch.cat at
+ * obs_encoder/entity_encoder.py:60-78.  Per field f: data[f] = device array [rows] of element type dtype[f]
+ * (0 u8, 1 i8, 2 i16, 3 f16, 4 i64, 5 f32), kind[f] (0 one-hot clamped to num-1, 1 num-bit binary MSB first,
+ * 2 raw value), col[f] = first output column.  out [rows, pitch] bf16 (pitch % 8 == 0, zero padded).
+ * *neg_flag (device int) is set to 1 if a one-hot index is negative (the reference raises, :68-71). */
+int as_entity_features(const void* const* data, const int* kind, const int* num, const int* col, const int* dtype,
+                       int n_fields, void* out, int64_t rows, int pitch, int* neg_flag, void* stream);
 
 /* fp32 -> bf16 cast (operand staging for the GEMMs). */
 int as_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream);
