@@ -51,6 +51,27 @@ _SIGS = {
     'as_splitk_reduce': (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
     'as_conv_nhwc_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int,
                                   c_int, c_int, c_int, c_int, c_void_p]),
+    'as_conv_wgrad_nhwc_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int,
+                                        c_int, c_int, c_void_p]),
+    'as_nchw_to_pnhwc': (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    'as_pnhwc_to_nchw': (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p]),
+    'as_add_act_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
+    'as_relu_bwd_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
+    'as_gated_fwd_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
+    'as_gated_scratch_floats': (c_int64, []),
+    'as_gated_bwd_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                  c_void_p, c_void_p, c_int64, c_void_p]),
+    'as_upsample2_fwd_bf16': (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p]),
+    'as_upsample2_bwd_bf16': (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p]),
+    'as_loc_cat_fwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p]),
+    'as_loc_cat_bwd': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int,
+                               c_void_p]),
+    'as_conv_c32_1_fwd': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_float, c_void_p]),
+    'as_conv_c32_1_scratch_floats': (c_int64, []),
+    'as_conv_c32_1_bwd': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64,
+                                  c_int, c_int, c_float, c_void_p]),
+    'as_colsum_scratch_floats': (c_int64, [c_int]),
+    'as_colsum_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     'as_layer_norm_fwd': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int,
                                   c_int, c_void_p]),
     'as_layer_norm_bwd_scratch_floats': (c_int64, [c_int]),

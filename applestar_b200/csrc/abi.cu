@@ -24,6 +24,24 @@ int softmax_fwd(const float*, const long long*, void*, long long, int, int, int,
 int softmax_bwd(const void*, const float*, void*, long long, int, cudaStream_t);
 int entity_features(const void* const*, const int*, const int*, const int*, const int*, int, void*, long long, int,
                     int*, cudaStream_t);
+int nchw_to_pnhwc(const float*, void*, long long, int, int, int, int, int, cudaStream_t);
+int pnhwc_to_nchw(const void*, float*, long long, int, int, int, int, cudaStream_t);
+int add_act(const void*, const void*, void*, long long, int, cudaStream_t);
+int relu_bwd(const void*, const void*, void*, long long, cudaStream_t);
+int gated_fwd(const void*, const void*, const void*, const float*, void*, long long, cudaStream_t);
+long long gated_scratch_floats();
+int gated_bwd(const void*, const void*, const void*, const void*, const float*, void*, void*, void*, float*, float*,
+              long long, cudaStream_t);
+int up2_fwd(const void*, void*, long long, int, int, int, cudaStream_t);
+int up2_bwd(const void*, void*, long long, int, int, int, cudaStream_t);
+int loc_cat_fwd(const float*, const void*, void*, long long, int, int, int, int, cudaStream_t);
+int loc_cat_bwd(const void*, const float*, const void*, float*, void*, long long, int, int, int, int, cudaStream_t);
+int conv_c32_1_fwd(const void*, const float*, const float*, float*, long long, int, int, float, cudaStream_t);
+long long conv_c32_1_scratch_floats();
+int conv_c32_1_bwd(const float*, const void*, const float*, void*, float*, float*, float*, long long, int, int, float,
+                   cudaStream_t);
+long long colsum_scratch_floats(int);
+int colsum_bf16(const void*, float*, float*, long long, int, cudaStream_t);
 }  // namespace as
 
 #define ST(s) reinterpret_cast<cudaStream_t>(s)
@@ -80,7 +98,7 @@ int as_conv_nhwc_bf16(const void* x, const void* w, void* y, const float* bias, 
                       int Cout, int taps, int w_mn, int y_bf16, int relu, void* stream) {
   if (taps != 1 && taps != 9) return AS_EUNSUPPORTED;
   if (R <= 0 || H <= 0 || W <= 0 || Cin <= 0 || Cout <= 0) return AS_ESIZE;
-  if (Cin % 64 != 0) return AS_EUNSUPPORTED;
+  if (Cin % 8 != 0) return AS_EUNSUPPORTED;
   const int pw = W + 2, ph = H + 2;
   const int64_t P = R * (int64_t)ph * pw;
   if (P > 2147483647LL) return AS_ESIZE;
@@ -99,6 +117,83 @@ int as_conv_nhwc_bf16(const void* x, const void* w, void* y, const float* bias, 
   }
   g.img_w = pw; g.img_h = ph;
   return as::gemm_run(g, ST(stream));
+}
+
+int as_conv_wgrad_nhwc_bf16(const void* dy, const void* x, float* dw, float* ws, int64_t R, int H, int W, int Cin,
+                            int Cout, int taps, int splits, void* stream) {
+  if (taps != 1 && taps != 9) return AS_EUNSUPPORTED;
+  if (R <= 0 || H <= 0 || W <= 0 || Cin <= 0 || Cout <= 0) return AS_ESIZE;
+  if ((Cin % 8) || (Cout % 8)) return AS_EALIGN;
+  const int pw = W + 2, ph = H + 2;
+  const int64_t P = R * (int64_t)ph * pw;
+  if (P > 2147483647LL) return AS_ESIZE;
+  as::GemmCall g;
+  g.A = dy; g.B = x;
+  g.M = Cout; g.N = Cin; g.K = (int)P;
+  g.a_mn = true; g.b_mn = true;
+  g.lda = Cout; g.ldb = Cin;
+  g.nb0 = taps; g.nb1 = 1;
+  g.wgrad_taps = taps;
+  if (taps == 9) {
+    for (int ky = 0; ky < 3; ++ky)
+      for (int kx = 0; kx < 3; ++kx) g.shift[ky * 3 + kx] = (ky - 1) * pw + (kx - 1);
+  } else {
+    g.shift[0] = 0;
+  }
+  g.C = dw; g.ldc = Cin; g.c_sb0 = (int64_t)Cout * Cin; g.c_bf16 = 0;
+  g.splits = splits; g.ws = ws;
+  int rc = as::gemm_run(g, ST(stream));
+  if (rc) return rc;
+  if (splits > 1) return as::splitk_reduce(ws, dw, (int64_t)taps * Cout * Cin, splits, 0, ST(stream));
+  return AS_OK;
+}
+
+int as_nchw_to_pnhwc(const float* src, void* dst, int64_t R, int C, int Cp, int H, int W, int relu, void* stream) {
+  return as::nchw_to_pnhwc(src, dst, R, C, Cp, H, W, relu, ST(stream));
+}
+int as_pnhwc_to_nchw(const void* src, float* dst, int64_t R, int C, int Cp, int H, int W, void* stream) {
+  return as::pnhwc_to_nchw(src, dst, R, C, Cp, H, W, ST(stream));
+}
+int as_add_act_bf16(const void* a, const void* b, void* y, int64_t n, int mode, void* stream) {
+  return as::add_act(a, b, y, n, mode, ST(stream));
+}
+int as_relu_bwd_bf16(const void* dy, const void* y, void* dz, int64_t n, void* stream) {
+  return as::relu_bwd(dy, y, dz, n, ST(stream));
+}
+int as_gated_fwd_bf16(const void* r, const void* g, const void* x, const float* update_sp, void* y, int64_t n,
+                      void* stream) {
+  return as::gated_fwd(r, g, x, update_sp, y, n, ST(stream));
+}
+int64_t as_gated_scratch_floats(void) { return as::gated_scratch_floats(); }
+int as_gated_bwd_bf16(const void* dy, const void* y, const void* r, const void* g, const float* update_sp, void* dr,
+                      void* dg, void* dx, float* d_update_sp, float* scratch, int64_t n, void* stream) {
+  return as::gated_bwd(dy, y, r, g, update_sp, dr, dg, dx, d_update_sp, scratch, n, ST(stream));
+}
+int as_upsample2_fwd_bf16(const void* in, void* out, int64_t R, int H, int W, int C, void* stream) {
+  return as::up2_fwd(in, out, R, H, W, C, ST(stream));
+}
+int as_upsample2_bwd_bf16(const void* dout, void* din, int64_t R, int H, int W, int C, void* stream) {
+  return as::up2_bwd(dout, din, R, H, W, C, ST(stream));
+}
+int as_loc_cat_fwd(const float* emb, const void* skip, void* out, int64_t R, int H, int W, int Cs, int Cp, void* stream) {
+  return as::loc_cat_fwd(emb, skip, out, R, H, W, Cs, Cp, ST(stream));
+}
+int as_loc_cat_bwd(const void* dcat, const float* emb, const void* skip, float* d_emb, void* d_skip, int64_t R, int H,
+                   int W, int Cs, int Cp, void* stream) {
+  return as::loc_cat_bwd(dcat, emb, skip, d_emb, d_skip, R, H, W, Cs, Cp, ST(stream));
+}
+int as_conv_c32_1_fwd(const void* in, const float* w, const float* bias, float* logits, int64_t R, int H, int W,
+                      float inv_temperature, void* stream) {
+  return as::conv_c32_1_fwd(in, w, bias, logits, R, H, W, inv_temperature, ST(stream));
+}
+int64_t as_conv_c32_1_scratch_floats(void) { return as::conv_c32_1_scratch_floats(); }
+int as_conv_c32_1_bwd(const float* dlogits, const void* in, const float* w, void* d_in, float* dw, float* db,
+                      float* scratch, int64_t R, int H, int W, float inv_temperature, void* stream) {
+  return as::conv_c32_1_bwd(dlogits, in, w, d_in, dw, db, scratch, R, H, W, inv_temperature, ST(stream));
+}
+int64_t as_colsum_scratch_floats(int C) { return as::colsum_scratch_floats(C); }
+int as_colsum_bf16(const void* x, float* out, float* scratch, int64_t rows, int C, void* stream) {
+  return as::colsum_bf16(x, out, scratch, rows, C, ST(stream));
 }
 
 int as_layer_norm_fwd(const float* x, const float* res, const float* gamma, const float* beta, float* y32, void* y16,

@@ -28,6 +28,7 @@ struct GemmCall {
   int shift[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
   int img_w = 0, img_h = 0;  // padded image dims: border rows are written as zero
   int b_k_shift = 0;         // MN-major B: offset (rows) added to the contraction coordinate
+  int wgrad_taps = 0;        // >0: conv weight-gradient mode, batch dim 0 = tap (see gemm_tcgen05.cu)
   int bn_override = 0;
 };
 

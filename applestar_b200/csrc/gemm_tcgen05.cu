@@ -28,7 +28,8 @@ struct GemmDev {
   int taps, cin_blocks, cin;
   int shift[9];
   int img_w, img_h;  // padded image dims for border masking (0 = off)
-  int b_k_shift;     // MN-major B only: row offset added to the contraction coordinate (conv wgrad taps)
+  int b_k_shift;     // MN-major B only: row offset added to the contraction coordinate
+  int wgrad_taps;    // >0: batch index b0 = conv tap; A and B are shared by all taps, B rows shifted by shift[b0]
   // epilogue
   void* C;
   void* C2;   // optional bf16 copy of the output (same ldc / batch strides)
@@ -123,19 +124,21 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           } else {
             ka = kbcol = kb * BK;
           }
+          const int ob0 = p.wgrad_taps > 0 ? 0 : b0;                       // operands shared by all taps
+          const int kshift = p.wgrad_taps > 0 ? p.shift[b0] : p.b_k_shift;
           if (A_MN) {
 #pragma unroll
             for (int j = 0; j < BM / 64; ++j)
-              tma_load_4d(sa + j * (BK * 128), &tmA, &full_bar[stage], m0 + j * 64, ka, b0, b1);
+              tma_load_4d(sa + j * (BK * 128), &tmA, &full_bar[stage], m0 + j * 64, ka, ob0, b1);
           } else {
-            tma_load_4d(sa, &tmA, &full_bar[stage], ka, m0 + mshift, b0, b1);
+            tma_load_4d(sa, &tmA, &full_bar[stage], ka, m0 + mshift, ob0, b1);
           }
           if (B_MN) {
 #pragma unroll
             for (int j = 0; j < BN / 64; ++j)
-              tma_load_4d(sb + j * (BK * 128), &tmB, &full_bar[stage], n0 + j * 64, kbcol + p.b_k_shift, b0, b1);
+              tma_load_4d(sb + j * (BK * 128), &tmB, &full_bar[stage], n0 + j * 64, kbcol + kshift, ob0, b1);
           } else {
-            tma_load_4d(sb, &tmB, &full_bar[stage], kbcol, n0, b0, b1);
+            tma_load_4d(sb, &tmB, &full_bar[stage], kbcol, n0, ob0, b1);
           }
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
@@ -391,8 +394,10 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
   p.n_blocks = (g.N + BN - 1) / BN;
   p.taps = g.taps; p.cin = g.K;
   if (g.taps > 0) {
-    if (g.taps > 9 || (g.K % BK) != 0 || g.a_mn || g.nb0 * g.nb1 != 1) return AS_EUNSUPPORTED;
-    p.cin_blocks = g.K / BK;
+    // Cin need not be a multiple of 64: the A box is zero-filled past Cin, which also cancels whatever the B box
+    // picks up from the next tap's columns.
+    if (g.taps > 9 || (g.K % 8) != 0 || g.a_mn || g.nb0 * g.nb1 != 1) return AS_EUNSUPPORTED;
+    p.cin_blocks = (g.K + BK - 1) / BK;
     p.num_kb = g.taps * p.cin_blocks;
     for (int i = 0; i < g.taps; ++i) p.shift[i] = g.shift[i];
   } else {
@@ -401,6 +406,11 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
   }
   p.img_w = g.img_w; p.img_h = g.img_h;
   p.b_k_shift = g.b_mn ? g.b_k_shift : 0;
+  p.wgrad_taps = g.wgrad_taps;
+  if (g.wgrad_taps > 0) {
+    if (g.wgrad_taps > 9 || g.nb0 != g.wgrad_taps || !g.b_mn || g.taps > 0) return AS_EUNSUPPORTED;
+    for (int i = 0; i < g.wgrad_taps; ++i) p.shift[i] = g.shift[i];
+  }
   p.splits = g.splits > 1 ? g.splits : 1;
   p.kb_per_split = (p.num_kb + p.splits - 1) / p.splits;
   p.splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;   // drop empty splits
@@ -411,11 +421,12 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
   CUtensorMap ta, tb;
   int rc;
   const long long k_total_b = g.taps > 0 ? (long long)g.taps * g.K : g.K;
-  if (g.a_mn) rc = make_map(&ta, g.A, g.M, g.K, g.lda, g.nb0, g.a_sb0, g.nb1, g.a_sb1, 64, BK);
-  else rc = make_map(&ta, g.A, g.K, g.a_rows > 0 ? g.a_rows : g.M, g.lda, g.nb0, g.a_sb0, g.nb1, g.a_sb1, BK, BM);
+  const int onb0 = g.wgrad_taps > 0 ? 1 : g.nb0;      // tensor-map extent of the first batch dim
+  if (g.a_mn) rc = make_map(&ta, g.A, g.M, g.K, g.lda, onb0, g.a_sb0, g.nb1, g.a_sb1, 64, BK);
+  else rc = make_map(&ta, g.A, g.K, g.a_rows > 0 ? g.a_rows : g.M, g.lda, onb0, g.a_sb0, g.nb1, g.a_sb1, BK, BM);
   if (rc) return rc;
-  if (g.b_mn) rc = make_map(&tb, g.B, g.N, k_total_b, g.ldb, g.nb0, g.b_sb0, g.nb1, g.b_sb1, 64, BK);
-  else rc = make_map(&tb, g.B, k_total_b, g.N, g.ldb, g.nb0, g.b_sb0, g.nb1, g.b_sb1, BK, BN);
+  if (g.b_mn) rc = make_map(&tb, g.B, g.N, k_total_b, g.ldb, onb0, g.b_sb0, g.nb1, g.b_sb1, 64, BK);
+  else rc = make_map(&tb, g.B, k_total_b, g.N, g.ldb, onb0, g.b_sb0, g.nb1, g.b_sb1, BK, BN);
   if (rc) return rc;
   switch (BN) {
     case 32: return dispatch_major<32>(g.a_mn, g.b_mn, ta, tb, p, st);

@@ -1,0 +1,560 @@
+// HBM-bound kernels of the spatial path on zero-padded NHWC bf16 feature maps [R, H+2, W+2, C]:
+// layout conversion, residual / gated-residual tails, 2x bilinear upsampling, the 132-channel location-head input,
+// the final 32->1 convolution, and column sums (bias gradients).  The convolutions themselves are implicit GEMMs on
+// the tcgen05 kernel (gemm_tcgen05.cu); every kernel here keeps the one-pixel border at exactly zero so that the
+// next convolution sees correct zero padding.
+#include "common.cuh"
+
+namespace as {
+
+__device__ __forceinline__ float bf2f(__nv_bfloat16 v) { return __bfloat162float(v); }
+__device__ __forceinline__ __nv_bfloat16 f2bf(float v) { return __float2bfloat16_rn(v); }
+
+static int ew_grid(long long n, int per_thread) {
+  long long blocks = (n / per_thread + 255) / 256;
+  const long long cap = 148LL * 16;
+  return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
+}
+
+// ------------------------------------------------------------------------------------------ layout conversion
+// NCHW fp32 [R,C,H,W] -> padded NHWC bf16 [R,H+2,W+2,Cp] (channels >= C and the border are zero).  One block per
+// (r, y); a [Cp][W] tile goes through shared memory so both sides are coalesced.
+__global__ void nchw_to_pnhwc_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int C, int Cp,
+                                     int H, int W, int relu) {
+  extern __shared__ float tile[];                 // [C][W+1]
+  const int r = blockIdx.x / (H + 2), yy = blockIdx.x % (H + 2);
+  __nv_bfloat16* drow = dst + ((long long)r * (H + 2) + yy) * (W + 2) * Cp;
+  const int n_out = (W + 2) * Cp;
+  if (yy == 0 || yy == H + 1) {
+    for (int i = threadIdx.x; i < n_out; i += blockDim.x) drow[i] = f2bf(0.f);
+    return;
+  }
+  const int y = yy - 1;
+  for (int i = threadIdx.x; i < C * W; i += blockDim.x) {
+    const int c = i / W, x = i - c * W;
+    float v = src[(((long long)r * C + c) * H + y) * W + x];
+    tile[c * (W + 1) + x] = relu ? fmaxf(v, 0.f) : v;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < n_out; i += blockDim.x) {
+    const int xx = i / Cp, c = i - xx * Cp;
+    float v = 0.f;
+    if (xx >= 1 && xx <= W && c < C) v = tile[c * (W + 1) + xx - 1];
+    drow[i] = f2bf(v);
+  }
+}
+
+// padded NHWC bf16 -> NCHW fp32 (interior only, first C channels)
+__global__ void pnhwc_to_nchw_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, int C, int Cp,
+                                     int H, int W) {
+  extern __shared__ float tile[];                 // [C][W+1]
+  const int r = blockIdx.x / H, y = blockIdx.x % H;
+  const __nv_bfloat16* srow = src + (((long long)r * (H + 2) + y + 1) * (W + 2) + 1) * Cp;
+  for (int i = threadIdx.x; i < W * C; i += blockDim.x) {
+    const int x = i / C, c = i - x * C;
+    tile[c * (W + 1) + x] = bf2f(srow[(long long)x * Cp + c]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C * W; i += blockDim.x) {
+    const int c = i / W, x = i - c * W;
+    dst[(((long long)r * C + c) * H + y) * W + x] = tile[c * (W + 1) + x];
+  }
+}
+
+int nchw_to_pnhwc(const float* src, void* dst, long long R, int C, int Cp, int H, int W, int relu, cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (C <= 0 || Cp < C || H <= 0 || W <= 0) return AS_ESIZE;
+  const int smem = C * (W + 1) * 4;
+  if (smem > 96 * 1024) return AS_ESIZE;
+  static bool attr = false;
+  if (!attr) { cudaFuncSetAttribute(nchw_to_pnhwc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); attr = true; }
+  nchw_to_pnhwc_kernel<<<(unsigned)(R * (H + 2)), 256, smem, st>>>(src, reinterpret_cast<__nv_bfloat16*>(dst), C, Cp, H, W, relu);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+int pnhwc_to_nchw(const void* src, float* dst, long long R, int C, int Cp, int H, int W, cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (C <= 0 || Cp < C || H <= 0 || W <= 0) return AS_ESIZE;
+  const int smem = C * (W + 1) * 4;
+  if (smem > 96 * 1024) return AS_ESIZE;
+  static bool attr = false;
+  if (!attr) { cudaFuncSetAttribute(pnhwc_to_nchw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); attr = true; }
+  pnhwc_to_nchw_kernel<<<(unsigned)(R * H), 256, smem, st>>>(reinterpret_cast<const __nv_bfloat16*>(src), dst, C, Cp, H, W);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+// ------------------------------------------------------------------------------------------ residual tails
+union BF8 { uint4 u; __nv_bfloat16 h[8]; };
+
+// mode 0: y = a + b;  mode 1: y = relu(a + b)
+__global__ void add_act_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, uint4* __restrict__ y,
+                               long long n8, int mode) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    BF8 va, vb, vy;
+    va.u = __ldg(a + i); vb.u = __ldg(b + i);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float s = bf2f(va.h[j]) + bf2f(vb.h[j]);
+      if (mode == 1) s = fmaxf(s, 0.f);
+      vy.h[j] = f2bf(s);
+    }
+    y[i] = vy.u;
+  }
+}
+// dz = dy * (y > 0)
+__global__ void relu_bwd_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y, uint4* __restrict__ dz,
+                                long long n8) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    BF8 vd, vy, vo;
+    vd.u = __ldg(dy + i); vy.u = __ldg(y + i);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) vo.h[j] = bf2f(vy.h[j]) > 0.f ? vd.h[j] : f2bf(0.f);
+    dz[i] = vo.u;
+  }
+}
+
+int add_act(const void* a, const void* b, void* y, long long n, int mode, cudaStream_t st) {
+  if (n <= 0) return AS_OK;
+  if (n % 8) return AS_ESIZE;
+  if (!a || !b || !y) return AS_EINVAL;
+  add_act_kernel<<<ew_grid(n, 8), 256, 0, st>>>((const uint4*)a, (const uint4*)b, (uint4*)y, n / 8, mode);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+int relu_bwd(const void* dy, const void* y, void* dz, long long n, cudaStream_t st) {
+  if (n <= 0) return AS_OK;
+  if (n % 8) return AS_ESIZE;
+  if (!dy || !y || !dz) return AS_EINVAL;
+  relu_bwd_kernel<<<ew_grid(n, 8), 256, 0, st>>>((const uint4*)dy, (const uint4*)y, (uint4*)dz, n / 8);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+// GatedResBlock tail (module_utils.py:227-229): y = relu(tanh(r * sigmoid(g)) * sp + x)
+__global__ void gated_fwd_kernel(const uint4* __restrict__ r, const uint4* __restrict__ g, const uint4* __restrict__ x,
+                                 const float* __restrict__ sp, uint4* __restrict__ y, long long n8) {
+  const float s = *sp;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    BF8 vr, vg, vx, vy;
+    vr.u = __ldg(r + i); vg.u = __ldg(g + i); vx.u = __ldg(x + i);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float sg = 1.f / (1.f + expf(-bf2f(vg.h[j])));
+      const float t = tanhf(bf2f(vr.h[j]) * sg);
+      vy.h[j] = f2bf(fmaxf(t * s + bf2f(vx.h[j]), 0.f));
+    }
+    y[i] = vy.u;
+  }
+}
+// dz = dy (y>0); dx = dz; t = tanh(r s(g)); dsp = sum dz t; du = dz sp (1-t^2); dr = du s(g); dg = du r s(g)(1-s(g))
+__global__ void gated_bwd_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y, const uint4* __restrict__ r,
+                                 const uint4* __restrict__ g, const float* __restrict__ sp, uint4* __restrict__ dr,
+                                 uint4* __restrict__ dg, uint4* __restrict__ dx, float* __restrict__ dsp_partial,
+                                 long long n8) {
+  const float s = *sp;
+  float acc = 0.f;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    BF8 vd, vy, vr, vg, odr, odg, odx;
+    vd.u = __ldg(dy + i); vy.u = __ldg(y + i); vr.u = __ldg(r + i); vg.u = __ldg(g + i);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float dz = bf2f(vy.h[j]) > 0.f ? bf2f(vd.h[j]) : 0.f;
+      const float rv = bf2f(vr.h[j]);
+      const float sg = 1.f / (1.f + expf(-bf2f(vg.h[j])));
+      const float t = tanhf(rv * sg);
+      acc += dz * t;
+      const float du = dz * s * (1.f - t * t);
+      odr.h[j] = f2bf(du * sg);
+      odg.h[j] = f2bf(du * rv * sg * (1.f - sg));
+      odx.h[j] = f2bf(dz);
+    }
+    dr[i] = odr.u; dg[i] = odg.u; dx[i] = odx.u;
+  }
+  __shared__ float red[8];
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int i = 0; i < 8; ++i) t += red[i];
+    dsp_partial[blockIdx.x] = t;
+  }
+}
+__global__ void sum_partials_kernel(const float* __restrict__ partial, int n, float* __restrict__ out) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    float s = 0.f;
+    for (int i = 0; i < n; ++i) s += partial[i];
+    *out = s;
+  }
+}
+
+constexpr int kGatedBlocks = 148 * 8;
+long long gated_scratch_floats() { return kGatedBlocks; }
+
+int gated_fwd(const void* r, const void* g, const void* x, const float* sp, void* y, long long n, cudaStream_t st) {
+  if (n <= 0) return AS_OK;
+  if (n % 8) return AS_ESIZE;
+  if (!r || !g || !x || !sp || !y) return AS_EINVAL;
+  gated_fwd_kernel<<<ew_grid(n, 8), 256, 0, st>>>((const uint4*)r, (const uint4*)g, (const uint4*)x, sp, (uint4*)y, n / 8);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+int gated_bwd(const void* dy, const void* y, const void* r, const void* g, const float* sp, void* dr, void* dg, void* dx,
+              float* dsp, float* scratch, long long n, cudaStream_t st) {
+  if (n <= 0) return AS_OK;
+  if (n % 8) return AS_ESIZE;
+  if (!dy || !y || !r || !g || !sp || !dr || !dg || !dx || !dsp || !scratch) return AS_EINVAL;
+  gated_bwd_kernel<<<kGatedBlocks, 256, 0, st>>>((const uint4*)dy, (const uint4*)y, (const uint4*)r, (const uint4*)g, sp,
+                                                 (uint4*)dr, (uint4*)dg, (uint4*)dx, scratch, n / 8);
+  AS_LAUNCH_CHECK();
+  sum_partials_kernel<<<1, 32, 0, st>>>(scratch, kGatedBlocks, dsp);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+// ------------------------------------------------------------------------------------------ bilinear x2 (align_corners=False)
+// out[2i] = .25 in[i-1] + .75 in[i], out[2i+1] = .75 in[i] + .25 in[i+1], indices clamped (== F.interpolate).
+__device__ __forceinline__ void up2_src(int o, int n_in, int* i0, int* i1, float* w1) {
+  float s = (o + 0.5f) * 0.5f - 0.5f;
+  if (s < 0.f) s = 0.f;
+  const int a = (int)s;
+  *i0 = a;
+  *i1 = a + 1 < n_in ? a + 1 : n_in - 1;
+  *w1 = s - (float)a;
+}
+
+__global__ void up2_fwd_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, long long R, int H,
+                               int W, int C) {
+  const int H2 = 2 * H, W2 = 2 * W, C8 = C / 8;
+  const long long total = R * (H2 + 2) * (long long)(W2 + 2) * C8;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int c8 = (int)(i % C8);
+    long long p = i / C8;
+    const int xx = (int)(p % (W2 + 2)); p /= (W2 + 2);
+    const int yy = (int)(p % (H2 + 2));
+    const long long r = p / (H2 + 2);
+    BF8 o;
+    if (xx == 0 || xx == W2 + 1 || yy == 0 || yy == H2 + 1) {
+      o.u = make_uint4(0, 0, 0, 0);
+    } else {
+      int y0, y1, x0, x1; float wy, wx;
+      up2_src(yy - 1, H, &y0, &y1, &wy);
+      up2_src(xx - 1, W, &x0, &x1, &wx);
+      const __nv_bfloat16* base = in + (r * (H + 2)) * (long long)(W + 2) * C + c8 * 8;
+      BF8 a, b, c, d;
+      a.u = *reinterpret_cast<const uint4*>(base + ((long long)(y0 + 1) * (W + 2) + x0 + 1) * C);
+      b.u = *reinterpret_cast<const uint4*>(base + ((long long)(y0 + 1) * (W + 2) + x1 + 1) * C);
+      c.u = *reinterpret_cast<const uint4*>(base + ((long long)(y1 + 1) * (W + 2) + x0 + 1) * C);
+      d.u = *reinterpret_cast<const uint4*>(base + ((long long)(y1 + 1) * (W + 2) + x1 + 1) * C);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float top = bf2f(a.h[j]) * (1.f - wx) + bf2f(b.h[j]) * wx;
+        const float bot = bf2f(c.h[j]) * (1.f - wx) + bf2f(d.h[j]) * wx;
+        o.h[j] = f2bf(top * (1.f - wy) + bot * wy);
+      }
+    }
+    *reinterpret_cast<uint4*>(out + i * 8) = o.u;
+  }
+}
+
+// gather form of the transpose: each input pixel collects from the <=4x4 output pixels that read it
+__global__ void up2_bwd_kernel(const __nv_bfloat16* __restrict__ dout, __nv_bfloat16* __restrict__ din, long long R,
+                               int H, int W, int C) {
+  const int H2 = 2 * H, W2 = 2 * W, C8 = C / 8;
+  const long long total = R * (H + 2) * (long long)(W + 2) * C8;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int c8 = (int)(i % C8);
+    long long p = i / C8;
+    const int xx = (int)(p % (W + 2)); p /= (W + 2);
+    const int yy = (int)(p % (H + 2));
+    const long long r = p / (H + 2);
+    BF8 o;
+    if (xx == 0 || xx == W + 1 || yy == 0 || yy == H + 1) {
+      o.u = make_uint4(0, 0, 0, 0);
+    } else {
+      const int y = yy - 1, x = xx - 1;
+      float acc[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+      const __nv_bfloat16* base = dout + (r * (H2 + 2)) * (long long)(W2 + 2) * C + c8 * 8;
+      for (int oy = 2 * y - 1; oy <= 2 * y + 2; ++oy) {
+        if (oy < 0 || oy >= H2) continue;
+        int y0, y1; float wy;
+        up2_src(oy, H, &y0, &y1, &wy);
+        const float cy = (y0 == y ? 1.f - wy : 0.f) + (y1 == y ? wy : 0.f);
+        if (cy == 0.f) continue;
+        for (int ox = 2 * x - 1; ox <= 2 * x + 2; ++ox) {
+          if (ox < 0 || ox >= W2) continue;
+          int x0, x1; float wx;
+          up2_src(ox, W, &x0, &x1, &wx);
+          const float cx = (x0 == x ? 1.f - wx : 0.f) + (x1 == x ? wx : 0.f);
+          if (cx == 0.f) continue;
+          BF8 v;
+          v.u = *reinterpret_cast<const uint4*>(base + ((long long)(oy + 1) * (W2 + 2) + ox + 1) * C);
+          const float w = cy * cx;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] += w * bf2f(v.h[j]);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o.h[j] = f2bf(acc[j]);
+    }
+    *reinterpret_cast<uint4*>(din + i * 8) = o.u;
+  }
+}
+
+int up2_fwd(const void* in, void* out, long long R, int H, int W, int C, cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (C % 8 || H <= 0 || W <= 0) return AS_ESIZE;
+  if (!in || !out) return AS_EINVAL;
+  const long long total = R * (2 * H + 2) * (long long)(2 * W + 2) * (C / 8);
+  up2_fwd_kernel<<<ew_grid(total, 1), 256, 0, st>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, R, H, W, C);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+int up2_bwd(const void* dout, void* din, long long R, int H, int W, int C, cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (C % 8 || H <= 0 || W <= 0) return AS_ESIZE;
+  if (!dout || !din) return AS_EINVAL;
+  const long long total = R * (H + 2) * (long long)(W + 2) * (C / 8);
+  up2_bwd_kernel<<<ew_grid(total, 1), 256, 0, st>>>((const __nv_bfloat16*)dout, (__nv_bfloat16*)din, R, H, W, C);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+// ------------------------------------------------------------------------------------------ location-head input
+// x1 = relu(cat[reshape(emb,[4,H,W]), skip]) (action_arg_head.py:419-422) as padded NHWC bf16 with Cp = 192 channels
+// (0-3 embedding, 4-131 skip, rest zero).  emb fp32 [R, 4*H*W] (post-ReLU), skip padded NHWC bf16 [R,H+2,W+2,128].
+__global__ void loc_cat_fwd_kernel(const float* __restrict__ emb, const __nv_bfloat16* __restrict__ skip,
+                                   __nv_bfloat16* __restrict__ out, long long R, int H, int W, int Cs, int Cp) {
+  const long long total = R * (H + 2) * (long long)(W + 2) * Cp;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int c = (int)(i % Cp);
+    long long p = i / Cp;
+    const int xx = (int)(p % (W + 2)); p /= (W + 2);
+    const int yy = (int)(p % (H + 2));
+    const long long r = p / (H + 2);
+    float v = 0.f;
+    if (xx >= 1 && xx <= W && yy >= 1 && yy <= H) {
+      if (c < 4) v = fmaxf(emb[(r * 4 + c) * (long long)(H * W) + (yy - 1) * W + xx - 1], 0.f);
+      else if (c < 4 + Cs) v = fmaxf(bf2f(skip[((r * (H + 2) + yy) * (long long)(W + 2) + xx) * Cs + c - 4]), 0.f);
+    }
+    out[i] = f2bf(v);
+  }
+}
+__global__ void loc_cat_bwd_kernel(const __nv_bfloat16* __restrict__ dcat, const float* __restrict__ emb,
+                                   const __nv_bfloat16* __restrict__ skip, float* __restrict__ demb,
+                                   __nv_bfloat16* __restrict__ dskip, long long R, int H, int W, int Cs, int Cp) {
+  const long long total = R * (H + 2) * (long long)(W + 2) * (4 + Cs);
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int c = (int)(i % (4 + Cs));
+    long long p = i / (4 + Cs);
+    const int xx = (int)(p % (W + 2)); const long long q = p / (W + 2);
+    const int yy = (int)(q % (H + 2));
+    const long long r = q / (H + 2);
+    const bool inner = xx >= 1 && xx <= W && yy >= 1 && yy <= H;
+    const float g = inner ? bf2f(dcat[p * Cp + c]) : 0.f;
+    if (c < 4) {
+      if (inner) {
+        const long long e = (r * 4 + c) * (long long)(H * W) + (yy - 1) * W + xx - 1;
+        demb[e] = emb[e] > 0.f ? g : 0.f;
+      }
+    } else {
+      const long long s = p * Cs + c - 4;
+      dskip[s] = (inner && bf2f(skip[s]) > 0.f) ? f2bf(g) : f2bf(0.f);
+    }
+  }
+}
+
+int loc_cat_fwd(const float* emb, const void* skip, void* out, long long R, int H, int W, int Cs, int Cp, cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (Cp < 4 + Cs) return AS_ESIZE;
+  if (!emb || !skip || !out) return AS_EINVAL;
+  const long long total = R * (H + 2) * (long long)(W + 2) * Cp;
+  loc_cat_fwd_kernel<<<ew_grid(total, 1), 256, 0, st>>>(emb, (const __nv_bfloat16*)skip, (__nv_bfloat16*)out, R, H, W, Cs, Cp);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+int loc_cat_bwd(const void* dcat, const float* emb, const void* skip, float* demb, void* dskip, long long R, int H, int W,
+                int Cs, int Cp, cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (!dcat || !emb || !skip || !demb || !dskip) return AS_EINVAL;
+  const long long total = R * (H + 2) * (long long)(W + 2) * (4 + Cs);
+  loc_cat_bwd_kernel<<<ew_grid(total, 1), 256, 0, st>>>((const __nv_bfloat16*)dcat, emb, (const __nv_bfloat16*)skip, demb,
+                                                       (__nv_bfloat16*)dskip, R, H, W, Cs, Cp);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+// ------------------------------------------------------------------------------------------ final 3x3 conv, 32 -> 1
+// y[r,y,x] = b + sum_{tap,c} w[tap][c] * in[r, y+ky, x+kx, c]   (in padded NHWC bf16, C = 32; y fp32 unpadded = logits)
+// One warp per output pixel group: lane = channel, 9 taps in registers, warp-shuffle reduction over channels.
+__global__ void conv_c32_1_fwd_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict__ w,
+                                      const float* __restrict__ bias, float* __restrict__ out, long long R, int H, int W,
+                                      float inv_temp) {
+  const int lane = threadIdx.x & 31;
+  float wk[9];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) wk[t] = w[t * 32 + lane];
+  const float b = bias ? bias[0] : 0.f;
+  const long long total = R * (long long)H * W;
+  const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long p = warp_global; p < total; p += warps_total) {
+    const int x = (int)(p % W);
+    const long long q = p / W;
+    const int y = (int)(q % H);
+    const long long r = q / H;
+    const __nv_bfloat16* base = in + ((r * (H + 2) + y) * (long long)(W + 2) + x) * 32 + lane;
+    float acc = 0.f;
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) acc += wk[ky * 3 + kx] * bf2f(base[((long long)ky * (W + 2) + kx) * 32]);
+    acc = warp_sum(acc);
+    if (lane == 0) out[p] = (acc + b) * inv_temp;
+  }
+}
+// din[r,yy,xx,c] = sum_tap w[tap][c] * dy[r, yy-ky, xx-kx]  (interior; border 0), dy fp32 unpadded [R,H,W]
+__global__ void conv_c32_1_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w,
+                                        __nv_bfloat16* __restrict__ din, long long R, int H, int W, float inv_temp) {
+  const int lane = threadIdx.x & 31;
+  float wk[9];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) wk[t] = w[t * 32 + lane] * inv_temp;
+  const long long total = R * (long long)(H + 2) * (W + 2);
+  const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long p = warp_global; p < total; p += warps_total) {
+    const int xx = (int)(p % (W + 2));
+    const long long q = p / (W + 2);
+    const int yy = (int)(q % (H + 2));
+    const long long r = q / (H + 2);
+    float acc = 0.f;
+    if (xx >= 1 && xx <= W && yy >= 1 && yy <= H) {
+#pragma unroll
+      for (int ky = 0; ky < 3; ++ky) {
+        const int oy = yy - ky;                 // output row (unpadded) that read this input row with tap ky
+        if (oy < 0 || oy >= H) continue;
+#pragma unroll
+        for (int kx = 0; kx < 3; ++kx) {
+          const int ox = xx - kx;
+          if (ox < 0 || ox >= W) continue;
+          acc += wk[ky * 3 + kx] * __ldg(dy + (r * H + oy) * (long long)W + ox);
+        }
+      }
+    }
+    din[p * 32 + lane] = f2bf(acc);
+  }
+}
+// dw[tap][c] = sum_p dy[p] in[p+tap][c];  db = sum dy  -> per-block partials [blocks][9*32+1]
+__global__ void conv_c32_1_wgrad_kernel(const float* __restrict__ dy, const __nv_bfloat16* __restrict__ in,
+                                        float* __restrict__ partial, long long R, int H, int W, float inv_temp) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  float acc[9], accb = 0.f;
+#pragma unroll
+  for (int t = 0; t < 9; ++t) acc[t] = 0.f;
+  const long long total = R * (long long)H * W;
+  const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long p = warp_global; p < total; p += warps_total) {
+    const int x = (int)(p % W);
+    const long long q = p / W;
+    const int y = (int)(q % H);
+    const long long r = q / H;
+    const float g = __ldg(dy + p) * inv_temp;
+    accb += g;
+    const __nv_bfloat16* base = in + ((r * (H + 2) + y) * (long long)(W + 2) + x) * 32 + lane;
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) acc[ky * 3 + kx] += g * bf2f(base[((long long)ky * (W + 2) + kx) * 32]);
+  }
+  __shared__ float red[8][9 * 32 + 1];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) red[wid][t * 32 + lane] = acc[t];
+  if (lane == 0) red[wid][288] = accb;
+  __syncthreads();
+  for (int i = threadIdx.x; i < 289; i += blockDim.x) {
+    float s = 0.f;
+    for (int k = 0; k < 8; ++k) s += red[k][i];
+    partial[(long long)blockIdx.x * 289 + i] = s;
+  }
+}
+__global__ void conv_c32_1_wreduce_kernel(const float* __restrict__ partial, int blocks, float* __restrict__ dw,
+                                          float* __restrict__ db) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 289) return;
+  float s = 0.f;
+  for (int k = 0; k < blocks; ++k) s += partial[(long long)k * 289 + i];
+  if (i < 288) dw[i] = s; else if (db) db[0] = s;
+}
+
+constexpr int kC321Blocks = 148 * 4;
+long long conv_c32_1_scratch_floats() { return (long long)kC321Blocks * 289; }
+
+int conv_c32_1_fwd(const void* in, const float* w, const float* bias, float* out, long long R, int H, int W, float inv_temp,
+                   cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (!in || !w || !out) return AS_EINVAL;
+  conv_c32_1_fwd_kernel<<<148 * 8, 256, 0, st>>>((const __nv_bfloat16*)in, w, bias, out, R, H, W, inv_temp);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+int conv_c32_1_bwd(const float* dy, const void* in, const float* w, void* din, float* dw, float* db, float* scratch,
+                   long long R, int H, int W, float inv_temp, cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (!dy || !in || !w || !din || !dw || !scratch) return AS_EINVAL;
+  conv_c32_1_dgrad_kernel<<<148 * 8, 256, 0, st>>>(dy, w, (__nv_bfloat16*)din, R, H, W, inv_temp);
+  AS_LAUNCH_CHECK();
+  conv_c32_1_wgrad_kernel<<<kC321Blocks, 256, 0, st>>>(dy, (const __nv_bfloat16*)in, scratch, R, H, W, inv_temp);
+  AS_LAUNCH_CHECK();
+  conv_c32_1_wreduce_kernel<<<3, 128, 0, st>>>(scratch, kC321Blocks, dw, db);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+// ------------------------------------------------------------------------------------------ column sums (bias grads)
+// out[c] = sum_r x[r][c] for bf16 x [rows, C]; two-stage, fixed order.
+__global__ void colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ partial, long long rows,
+                                      int C, int chunks) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const long long per = (rows + chunks - 1) / chunks;
+  const long long r0 = blockIdx.y * per, r1 = (r0 + per < rows) ? r0 + per : rows;
+  float s = 0.f;
+  for (long long r = r0; r < r1; ++r) s += bf2f(x[r * C + c]);
+  partial[(long long)blockIdx.y * C + c] = s;
+}
+__global__ void colsum_reduce_kernel(const float* __restrict__ partial, float* __restrict__ out, int C, int chunks) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float s = 0.f;
+  for (int k = 0; k < chunks; ++k) s += partial[(long long)k * C + c];
+  out[c] = s;
+}
+constexpr int kColsumChunks = 256;
+long long colsum_scratch_floats(int C) { return (long long)kColsumChunks * C; }
+int colsum_bf16(const void* x, float* out, float* scratch, long long rows, int C, cudaStream_t st) {
+  if (rows <= 0 || C <= 0) return AS_ESIZE;
+  if (!x || !out || !scratch) return AS_EINVAL;
+  const int chunks = rows < kColsumChunks ? (int)rows : kColsumChunks;
+  dim3 g((C + 63) / 64, chunks);
+  colsum_partial_kernel<<<g, 64, 0, st>>>((const __nv_bfloat16*)x, scratch, rows, C, chunks);
+  AS_LAUNCH_CHECK();
+  colsum_reduce_kernel<<<(C + 63) / 64, 64, 0, st>>>(scratch, out, C, chunks);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+}  // namespace as

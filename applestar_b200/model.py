@@ -16,7 +16,7 @@ import torch
 import torch.nn as nn
 
 from . import config as C
-from . import ops, tables
+from . import ops, spatial, tables
 
 
 # ----------------------------------------------------------------------------------------------
@@ -51,14 +51,17 @@ class FCLN(nn.Sequential):
 
 
 class Conv(nn.Sequential):
-    """conv2d_block (no norm): `.0` = Conv2d."""
+    """conv2d_block (no norm): `.0` = Conv2d.  `nhwc=True`: implicit GEMM on the tcgen05 kernel over a zero-padded
+    NHWC bf16 map (spatial.py); otherwise the [library] NCHW path."""
 
-    def __init__(self, cin, cout, k, pad, relu=False):
+    def __init__(self, cin, cout, k, pad, relu=False, nhwc=False):
         super().__init__(nn.Conv2d(cin, cout, k, 1, pad))
         _xavier_normal(self[0].weight)
-        self.relu, self.pad = relu, pad
+        self.relu, self.pad, self.nhwc = relu, pad, nhwc
 
     def forward(self, x):
+        if self.nhwc:
+            return spatial.conv(x, self[0].weight, self[0].bias, self.relu)
         return ops.conv2d(x, self[0].weight, self[0].bias, self.pad, self.relu)
 
 
@@ -164,11 +167,11 @@ class EntityEncoder(nn.Module):
 class ResBlock(nn.Module):
     def __init__(self, ch):
         super().__init__()
-        self.conv1 = Conv(ch, ch, 3, 1, relu=True)
-        self.conv2 = Conv(ch, ch, 3, 1)
+        self.conv1 = Conv(ch, ch, 3, 1, relu=True, nhwc=True)
+        self.conv2 = Conv(ch, ch, 3, 1, nhwc=True)
 
     def forward(self, x):
-        return ops.add_relu(self.conv2(self.conv1(x)), x)
+        return spatial.add_relu(self.conv2(self.conv1(x)), x)
 
 
 class SpatialEncoder(nn.Module):
@@ -178,20 +181,27 @@ class SpatialEncoder(nn.Module):
         super().__init__()
         self.project = Conv(56, 32, 1, 0, relu=True)
         self.encode_modules = nn.ModuleDict({n: _eye_table(k) for n, arc, k in C.SPATIAL_FIELDS if arc == 'one_hot'})
-        self.downsample = nn.ModuleList([Conv(32, 64, 3, 1, True), Conv(64, 128, 3, 1, True), Conv(128, 128, 3, 1, True)])
+        self.downsample = nn.ModuleList([Conv(32, 64, 3, 1, True), Conv(64, 128, 3, 1, True),
+                                         Conv(128, 128, 3, 1, True, nhwc=True)])
         self.res = nn.ModuleList([ResBlock(128) for _ in range(4)])
         self.fc = FC(128 * (C.SPATIAL_Y // 8) * (C.SPATIAL_X // 8), 256, relu=True)
 
     def forward(self, spatial_info, scatter_map):
+        """-> (embedded_spatial [R,256], map_skip).  map_skip[0..2] (pre-pool maps, only read by the U-Net variant
+        of the location head, which the default config disables) are not kept; map_skip[3..6] are the 19x20x128
+        maps as zero-padded NHWC bf16."""
         x = ops.spatial_project(spatial_info, scatter_map, self.project[0].weight, self.project[0].bias)
-        skip = []
-        for conv in self.downsample:
-            skip.append(x)
-            x = conv(ops.max_pool2(x))
+        skip = [None, None, None]
+        x = self.downsample[0](ops.max_pool2(x))
+        x = self.downsample[1](ops.max_pool2(x))
+        x = spatial.to_pnhwc(ops.max_pool2(x))                    # [R, 21, 22, 128] bf16, zero border
+        x = self.downsample[2](x)
         for block in self.res:
             skip.append(x)
             x = block(x)
-        return self.fc(x.reshape(x.shape[0], -1)), skip
+        H8, W8 = C.SPATIAL_Y // 8, C.SPATIAL_X // 8
+        w = spatial.spatial_fc_weight(self.fc[0].weight, 128, H8, W8)
+        return ops.linear(x.reshape(x.shape[0], -1), w, self.fc[0].bias, True), skip
 
 
 class BeginningBuildOrderEncoder(nn.Module):
@@ -419,14 +429,14 @@ class GatedResBlock(nn.Module):
 
     def __init__(self, ch):
         super().__init__()
-        self.conv1 = Conv(ch, ch, 3, 1, relu=True)
-        self.conv2 = Conv(ch, ch, 3, 1)
-        self.GateWeightG = nn.Sequential(Conv(ch, ch, 1, 0, True), Conv(ch, ch, 1, 0, True), Conv(ch, ch, 1, 0, True),
-                                         Conv(ch, ch, 1, 0))
+        self.conv1 = Conv(ch, ch, 3, 1, relu=True, nhwc=True)
+        self.conv2 = Conv(ch, ch, 3, 1, nhwc=True)
+        self.GateWeightG = nn.Sequential(Conv(ch, ch, 1, 0, True, nhwc=True), Conv(ch, ch, 1, 0, True, nhwc=True),
+                                         Conv(ch, ch, 1, 0, True, nhwc=True), Conv(ch, ch, 1, 0, nhwc=True))
         self.UpdateSP = nn.Parameter(torch.full((1,), 0.1))
 
     def forward(self, x):
-        return ops.gated_residual(self.conv2(self.conv1(x)), self.GateWeightG(x), self.UpdateSP, x)
+        return spatial.gated_residual(self.conv2(self.conv1(x)), self.GateWeightG(x), self.UpdateSP, x)
 
 
 class LocationHead(nn.Module):
@@ -434,22 +444,22 @@ class LocationHead(nn.Module):
 
     def __init__(self):
         super().__init__()
-        self.conv1 = Conv(128 + 4, 128, 1, 0, relu=True)
+        self.conv1 = Conv(128 + 4, 128, 1, 0, relu=True, nhwc=True)
         self.project_embed = FC(1024, (C.SPATIAL_Y // 8) * (C.SPATIAL_X // 8) * 4, relu=True)
         self.res = nn.ModuleList([GatedResBlock(128) for _ in range(4)])
-        self.upsample = nn.ModuleList([Conv(128, 64, 3, 1, True), Conv(64, 32, 3, 1, True), Conv(32, 1, 3, 1)])
+        self.upsample = nn.ModuleList([Conv(128, 64, 3, 1, True, nhwc=True), Conv(64, 32, 3, 1, True, nhwc=True),
+                                       Conv(32, 1, 3, 1)])
 
     def forward(self, embedding, map_skip, temperature, location=None, noise=None):
-        R = embedding.shape[0]
-        x = self.project_embed(embedding).reshape(R, 4, C.SPATIAL_Y // 8, C.SPATIAL_X // 8)
-        x = self.conv1(ops.relu(torch.cat([x, map_skip[-1]], dim=1)))
+        # relu(cat[reshape(project_embed), map_skip[-1]]) as a 192-channel padded NHWC map (132 real channels)
+        x = spatial.loc_cat(self.project_embed(embedding), map_skip[-1], 192)
+        x = self.conv1(x)
         for i, block in enumerate(self.res):
-            x = block(x + map_skip[len(map_skip) - i - 1])
-        for conv in self.upsample:
-            x = conv(ops.upsample_bilinear2(x))
-        logits = x.reshape(R, -1)
-        if temperature != 1.0:
-            logits = logits / temperature
+            x = block(spatial.add(x, map_skip[len(map_skip) - i - 1]))
+        x = self.upsample[0](spatial.upsample2(x))
+        x = self.upsample[1](spatial.upsample2(x))
+        last = self.upsample[2][0]                                # 3x3, 32 -> 1, flatten, 1/temperature: one kernel
+        logits = spatial.conv_c32_to_1(spatial.upsample2(x), last.weight, last.bias, 1.0 / temperature)
         if location is None:
             location = ops.gumbel_argmax(logits, noise)
         return logits, location
@@ -603,7 +613,7 @@ class Model(nn.Module):
         state0 = [tuple(s.view(-1, B, hs)[0] for s in layer) for layer in hidden_state]     # t=0 state only (A12)
         out, _ = self.core_lstm(lstm_input.view(-1, B, lstm_input.shape[-1]), state0)
         out = out.reshape(-1, out.shape[-1])
-        _, _, logits = self.policy.train_forward(out[:-B], ent[:-B], [m[:-B] for m in skip], ctx[:-B],
+        _, _, logits = self.policy.train_forward(out[:-B], ent[:-B], [None if m is None else m[:-B] for m in skip], ctx[:-B],
                                                  entity_num[:-B], flat_action, selected_units_num.flatten(0, 1),
                                                  self.cfg.temperature)
         critic_input = out.detach() if self.only_update_baseline else out

@@ -1,0 +1,273 @@
+"""Spatial path on zero-padded NHWC bf16 feature maps ([R, H+2, W+2, C], border == 0).
+
+Every 3x3 / 1x1 convolution of the 19x20 ResBlocks and of the location head is an implicit GEMM on the tcgen05
+kernel (forward, data-gradient and weight-gradient); the tails (residual ReLU, gated residual, bilinear x2, the
+132-channel concat, the final 32->1 convolution) are bf16 HBM-bound kernels that preserve the zero border.
+Reference modules: ResBlock (ctools/torch_utils/network/res_block.py:13-65), GatedResBlock
+(model/module_utils.py:204-231), LocationHead (model/head/action_arg_head.py:366-450).
+"""
+import torch
+import torch.nn.functional as F
+
+from . import _lib
+from . import kernels as K
+
+_ptr = K._ptr
+
+
+def _conv_weights(weight, cin_pad):
+    """bf16 operand layouts of a Conv2d weight [Cout, Cin, k, k]: forward [Cout][tap][ci] and data-gradient
+    [ci][flipped tap][Cout]; cached on the Parameter per optimizer generation."""
+    tag = (K._SHADOW_GEN[0], weight._version, weight.data_ptr(), cin_pad)
+    hit = getattr(weight, '_as_conv16', None)
+    if hit is not None and hit[0] == tag:
+        return hit[1], hit[2]
+    w = weight.detach()
+    cout, cin, kh, kw = w.shape
+    if cin_pad > cin:
+        w = F.pad(w, (0, 0, 0, 0, 0, cin_pad - cin))
+    w_fwd = w.permute(0, 2, 3, 1).reshape(cout, kh * kw * cin_pad).contiguous().to(torch.bfloat16)
+    w_dg = w.flip(2, 3).permute(1, 2, 3, 0).reshape(cin_pad, kh * kw * cout).contiguous().to(torch.bfloat16)
+    try:
+        weight._as_conv16 = (tag, w_fwd, w_dg)
+    except AttributeError:
+        pass
+    return w_fwd, w_dg
+
+
+def _conv_call(x, w2, y, bias, R, H, W, cin, cout, taps, relu):
+    _lib.call('as_conv_nhwc_bf16', x.data_ptr(), w2.data_ptr(), y.data_ptr(), _ptr(bias), R, H, W, cin, cout, taps, 0,
+              1, int(relu), _lib.stream_ptr())
+
+
+class ConvNHWC(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, relu):
+        R, ph, pw, cin_p = x.shape
+        H, W = ph - 2, pw - 2
+        cout, cin, kh, _ = weight.shape
+        taps = kh * kh
+        w_fwd, w_dg = _conv_weights(weight, cin_p)
+        x = x.contiguous()
+        y = torch.empty((R, ph, pw, cout), dtype=torch.bfloat16, device=x.device)
+        _conv_call(x, w_fwd, y, bias, R, H, W, cin_p, cout, taps, relu)
+        ctx.dims = (R, H, W, cin, cin_p, cout, taps, kh)
+        ctx.relu = relu
+        ctx.has_bias = bias is not None
+        ctx.save_for_backward(x, w_dg, y if relu else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w_dg, y = ctx.saved_tensors
+        R, H, W, cin, cin_p, cout, taps, kh = ctx.dims
+        dy = dy.contiguous()
+        st = _lib.stream_ptr()
+        if ctx.relu:
+            dz = torch.empty_like(dy)
+            _lib.call('as_relu_bwd_bf16', dy.data_ptr(), y.data_ptr(), dz.data_ptr(), dy.numel(), st)
+            dy = dz
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x)
+            _conv_call(dy, w_dg, dx, None, R, H, W, cout, cin_p, taps, False)
+        if ctx.needs_input_grad[1]:
+            P = R * (H + 2) * (W + 2)
+            tiles = taps * ((cout + 127) // 128) * max(1, (cin_p + 255) // 256)
+            want = max(1, min((P + 63) // 64, (2 * K.NUM_SMS) // tiles))
+            splits = _lib.lib().as_gemm_splits(P, want)
+            dw9 = torch.empty((taps, cout, cin_p), dtype=torch.float32, device=x.device)
+            ws = torch.empty((splits, taps, cout, cin_p), dtype=torch.float32, device=x.device) if splits > 1 else None
+            _lib.call('as_conv_wgrad_nhwc_bf16', dy.data_ptr(), x.data_ptr(), dw9.data_ptr(), _ptr(ws), R, H, W, cin_p,
+                      cout, taps, splits, st)
+            dw = dw9[:, :, :cin].permute(1, 2, 0).reshape(cout, cin, kh, kh)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = torch.empty(cout, dtype=torch.float32, device=x.device)
+            scratch = torch.empty(_lib.lib().as_colsum_scratch_floats(cout), dtype=torch.float32, device=x.device)
+            _lib.call('as_colsum_bf16', dy.data_ptr(), db.data_ptr(), scratch.data_ptr(), R * (H + 2) * (W + 2), cout, st)
+        return dx, dw, db, None
+
+
+def conv(x, weight, bias, relu=False):
+    return ConvNHWC.apply(x, weight, bias, relu)
+
+
+class AddAct(torch.autograd.Function):
+    """mode 0: a + b; mode 1: relu(a + b) on bf16 maps."""
+
+    @staticmethod
+    def forward(ctx, a, b, mode):
+        a, b = a.contiguous(), b.contiguous()
+        y = torch.empty_like(a)
+        _lib.call('as_add_act_bf16', a.data_ptr(), b.data_ptr(), y.data_ptr(), a.numel(), mode, _lib.stream_ptr())
+        ctx.mode = mode
+        ctx.save_for_backward(y if mode == 1 else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        if ctx.mode == 1:
+            dy = dy.contiguous()
+            dz = torch.empty_like(dy)
+            _lib.call('as_relu_bwd_bf16', dy.data_ptr(), y.data_ptr(), dz.data_ptr(), dy.numel(), _lib.stream_ptr())
+            dy = dz
+        return dy, dy, None
+
+
+def add(a, b):
+    return AddAct.apply(a, b, 0)
+
+
+def add_relu(a, b):
+    return AddAct.apply(a, b, 1)
+
+
+class Gated(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, r, g, x, sp):
+        r, g, x = r.contiguous(), g.contiguous(), x.contiguous()
+        y = torch.empty_like(x)
+        _lib.call('as_gated_fwd_bf16', r.data_ptr(), g.data_ptr(), x.data_ptr(), sp.data_ptr(), y.data_ptr(), x.numel(),
+                  _lib.stream_ptr())
+        ctx.save_for_backward(r, g, y, sp)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        r, g, y, sp = ctx.saved_tensors
+        dy = dy.contiguous()
+        dr, dg, dx = torch.empty_like(r), torch.empty_like(g), torch.empty_like(y)
+        dsp = torch.empty(1, dtype=torch.float32, device=y.device)
+        scratch = torch.empty(_lib.lib().as_gated_scratch_floats(), dtype=torch.float32, device=y.device)
+        _lib.call('as_gated_bwd_bf16', dy.data_ptr(), y.data_ptr(), r.data_ptr(), g.data_ptr(), sp.data_ptr(),
+                  dr.data_ptr(), dg.data_ptr(), dx.data_ptr(), dsp.data_ptr(), scratch.data_ptr(), y.numel(),
+                  _lib.stream_ptr())
+        return dr, dg, dx, dsp
+
+
+def gated_residual(r, g, update_sp, x):
+    return Gated.apply(r, g, x, update_sp)
+
+
+class Up2(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        R, ph, pw, Cc = x.shape
+        H, W = ph - 2, pw - 2
+        x = x.contiguous()
+        y = torch.empty((R, 2 * H + 2, 2 * W + 2, Cc), dtype=torch.bfloat16, device=x.device)
+        _lib.call('as_upsample2_fwd_bf16', x.data_ptr(), y.data_ptr(), R, H, W, Cc, _lib.stream_ptr())
+        ctx.dims = (R, H, W, Cc)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        R, H, W, Cc = ctx.dims
+        dy = dy.contiguous()
+        dx = torch.empty((R, H + 2, W + 2, Cc), dtype=torch.bfloat16, device=dy.device)
+        _lib.call('as_upsample2_bwd_bf16', dy.data_ptr(), dx.data_ptr(), R, H, W, Cc, _lib.stream_ptr())
+        return dx
+
+
+def upsample2(x):
+    return Up2.apply(x)
+
+
+class ToPNHWC(torch.autograd.Function):
+    """NCHW fp32 -> padded NHWC bf16 (optionally zero-padding the channel count)."""
+
+    @staticmethod
+    def forward(ctx, x, cpad):
+        R, Cc, H, W = x.shape
+        x = x.contiguous().float()
+        y = torch.empty((R, H + 2, W + 2, cpad), dtype=torch.bfloat16, device=x.device)
+        _lib.call('as_nchw_to_pnhwc', x.data_ptr(), y.data_ptr(), R, Cc, cpad, H, W, 0, _lib.stream_ptr())
+        ctx.dims = (R, Cc, H, W, cpad)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        R, Cc, H, W, cpad = ctx.dims
+        dy = dy.contiguous()
+        dx = torch.empty((R, Cc, H, W), dtype=torch.float32, device=dy.device)
+        _lib.call('as_pnhwc_to_nchw', dy.data_ptr(), dx.data_ptr(), R, Cc, cpad, H, W, _lib.stream_ptr())
+        return dx, None
+
+
+def to_pnhwc(x, cpad=None):
+    return ToPNHWC.apply(x, cpad or x.shape[1])
+
+
+class LocCat(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, emb, skip, cpad):
+        R, ph, pw, Cs = skip.shape
+        H, W = ph - 2, pw - 2
+        emb = emb.contiguous().float()
+        skip = skip.contiguous()
+        out = torch.empty((R, ph, pw, cpad), dtype=torch.bfloat16, device=skip.device)
+        _lib.call('as_loc_cat_fwd', emb.data_ptr(), skip.data_ptr(), out.data_ptr(), R, H, W, Cs, cpad, _lib.stream_ptr())
+        ctx.dims = (R, H, W, Cs, cpad)
+        ctx.save_for_backward(emb, skip)
+        return out
+
+    @staticmethod
+    def backward(ctx, dcat):
+        emb, skip = ctx.saved_tensors
+        R, H, W, Cs, cpad = ctx.dims
+        dcat = dcat.contiguous()
+        demb = torch.empty_like(emb)
+        dskip = torch.empty_like(skip)
+        _lib.call('as_loc_cat_bwd', dcat.data_ptr(), emb.data_ptr(), skip.data_ptr(), demb.data_ptr(), dskip.data_ptr(),
+                  R, H, W, Cs, cpad, _lib.stream_ptr())
+        return demb, dskip, None
+
+
+def loc_cat(emb, skip, cpad=192):
+    return LocCat.apply(emb, skip, cpad)
+
+
+class ConvC32To1(torch.autograd.Function):
+    """3x3 conv 32 -> 1 + flatten + 1/temperature -> fp32 logits [R, H*W]."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, inv_temp):
+        R, ph, pw, Cc = x.shape
+        H, W = ph - 2, pw - 2
+        assert Cc == 32 and tuple(weight.shape) == (1, 32, 3, 3)
+        x = x.contiguous()
+        w9 = weight.detach().permute(0, 2, 3, 1).reshape(9, 32).contiguous().float()
+        out = torch.empty((R, H * W), dtype=torch.float32, device=x.device)
+        _lib.call('as_conv_c32_1_fwd', x.data_ptr(), w9.data_ptr(), _ptr(bias), out.data_ptr(), R, H, W, float(inv_temp),
+                  _lib.stream_ptr())
+        ctx.dims = (R, H, W)
+        ctx.inv_temp = float(inv_temp)
+        ctx.save_for_backward(x, w9)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w9 = ctx.saved_tensors
+        R, H, W = ctx.dims
+        dy = dy.contiguous().float()
+        dx = torch.empty_like(x)
+        dw = torch.empty((9, 32), dtype=torch.float32, device=x.device)
+        db = torch.empty(1, dtype=torch.float32, device=x.device)
+        scratch = torch.empty(_lib.lib().as_conv_c32_1_scratch_floats(), dtype=torch.float32, device=x.device)
+        _lib.call('as_conv_c32_1_bwd', dy.data_ptr(), x.data_ptr(), w9.data_ptr(), dx.data_ptr(), dw.data_ptr(),
+                  db.data_ptr(), scratch.data_ptr(), R, H, W, ctx.inv_temp, _lib.stream_ptr())
+        return dx, dw.view(3, 3, 32).permute(2, 0, 1).reshape(1, 32, 3, 3), db, None
+
+
+def conv_c32_to_1(x, weight, bias, inv_temp=1.0):
+    return ConvC32To1.apply(x, weight, bias, inv_temp)
+
+
+def spatial_fc_weight(weight, ch, H, W):
+    """Linear weight over the NCHW flatten (index c*H*W + y*W + x, spatial_encoder.py:88) re-indexed for the padded
+    NHWC flatten ((y+1)*(W+2) + (x+1))*ch + c with zero columns on the border.  Differentiable torch view ops."""
+    out = weight.shape[0]
+    w = weight.view(out, ch, H, W).permute(0, 2, 3, 1)
+    w = F.pad(w, (0, 0, 1, 1, 1, 1))
+    return w.reshape(out, (H + 2) * (W + 2) * ch)

@@ -60,9 +60,59 @@ int as_splitk_reduce(const float* ws, float* out, int64_t n, int splits, int acc
 /* 3x3 / 1x1 convolution as implicit GEMM over zero-padded NHWC bf16 pixels -- replaces nn.Conv2d inside
  * conv2d_block (nn_module.py:119-174; ResBlock res_block.py:61-65, GatedResBlock module_utils.py:224-231).
  * x [R,(H+2),(W+2),Cin] bf16 with a zero border, w [Cout][taps*Cin] bf16 (tap-major), y [R,(H+2),(W+2),Cout]
- * (border written as zero).  taps = 9 (3x3, pad 1) or 1.  Cin % 64 == 0. */
+ * (border written as zero).  taps = 9 (3x3, pad 1) or 1.  Cin % 8 == 0. */
 int as_conv_nhwc_bf16(const void* x, const void* w, void* y, const float* bias, int64_t R, int H, int W, int Cin,
                       int Cout, int taps, int w_mn, int y_bf16, int relu, void* stream);
+
+/* Weight gradient of the NHWC convolution above: dw[tap][co][ci] = sum_p dy[p][co] * x[p + shift(tap)][ci] as one
+ * tap-batched, split-K tcgen05 GEMM with both operands read MN-major.  dy [R,(H+2),(W+2),Cout] bf16 (zero border),
+ * x [R,(H+2),(W+2),Cin] bf16; dw fp32 [taps][Cout][Cin]; ws: splits*taps*Cout*Cin floats when splits > 1
+ * (splits must equal as_gemm_splits(R*(H+2)*(W+2), want)).  Replaces autograd of nn.Conv2d (nn_module.py:166-168). */
+int as_conv_wgrad_nhwc_bf16(const void* dy, const void* x, float* dw, float* ws, int64_t R, int H, int W, int Cin,
+                            int Cout, int taps, int splits, void* stream);
+
+/* Layout conversion between the reference's NCHW fp32 maps and the padded NHWC bf16 maps the convolutions use:
+ * dst [R,H+2,W+2,Cp] (border and channels >= C zero; relu != 0 applies ReLU on the way) / its inverse (interior,
+ * first C channels). */
+int as_nchw_to_pnhwc(const float* src, void* dst, int64_t R, int C, int Cp, int H, int W, int relu, void* stream);
+int as_pnhwc_to_nchw(const void* src, float* dst, int64_t R, int C, int Cp, int H, int W, void* stream);
+
+/* bf16 element-wise tails (n % 8 == 0): mode 0 y = a + b (skip add, action_arg_head.py:429); mode 1
+ * y = relu(a + b) (ResBlock tail, res_block.py:64); as_relu_bwd_bf16: dz = dy * (y > 0). */
+int as_add_act_bf16(const void* a, const void* b, void* y, int64_t n, int mode, void* stream);
+int as_relu_bwd_bf16(const void* dy, const void* y, void* dz, int64_t n, void* stream);
+
+/* GatedResBlock tail y = relu(tanh(r * sigmoid(g)) * UpdateSP + x) (module_utils.py:227-229), bf16 maps, fp32 math.
+ * Backward also yields d UpdateSP (device float) through `scratch` of as_gated_scratch_floats() floats. */
+int as_gated_fwd_bf16(const void* r, const void* g, const void* x, const float* update_sp, void* y, int64_t n,
+                      void* stream);
+int64_t as_gated_scratch_floats(void);
+int as_gated_bwd_bf16(const void* dy, const void* y, const void* r, const void* g, const float* update_sp, void* dr,
+                      void* dg, void* dx, float* d_update_sp, float* scratch, int64_t n, void* stream);
+
+/* 2x bilinear upsampling (F.interpolate(scale_factor=2, mode='bilinear'), action_arg_head.py:440) on padded NHWC
+ * bf16 maps: in [R,H+2,W+2,C] -> out [R,2H+2,2W+2,C]; backward is the exact transpose in gather form. C % 8 == 0. */
+int as_upsample2_fwd_bf16(const void* in, void* out, int64_t R, int H, int W, int C, void* stream);
+int as_upsample2_bwd_bf16(const void* dout, void* din, int64_t R, int H, int W, int C, void* stream);
+
+/* Location-head input relu(cat[reshape(project_embed), map_skip[-1]]) (action_arg_head.py:419-422) as a padded NHWC
+ * bf16 map with Cp (>= 4 + Cs) channels, and its backward (d_emb fp32 [R,4*H*W], d_skip bf16 like skip). */
+int as_loc_cat_fwd(const float* emb, const void* skip, void* out, int64_t R, int H, int W, int Cs, int Cp, void* stream);
+int as_loc_cat_bwd(const void* dcat, const float* emb, const void* skip, float* d_emb, void* d_skip, int64_t R, int H,
+                   int W, int Cs, int Cp, void* stream);
+
+/* Final location-head convolution 3x3, 32 -> 1 (upsample.2, action_arg_head.py:443) fused with the flatten and the
+ * temperature division (:445-446): in padded NHWC bf16 [R,H+2,W+2,32], w fp32 [9][32], logits fp32 [R,H*W].
+ * Backward: d_in (bf16, zero border), dw [9][32], db [1]; scratch of as_conv_c32_1_scratch_floats() floats. */
+int as_conv_c32_1_fwd(const void* in, const float* w, const float* bias, float* logits, int64_t R, int H, int W,
+                      float inv_temperature, void* stream);
+int64_t as_conv_c32_1_scratch_floats(void);
+int as_conv_c32_1_bwd(const float* dlogits, const void* in, const float* w, void* d_in, float* dw, float* db,
+                      float* scratch, int64_t R, int H, int W, float inv_temperature, void* stream);
+
+/* out[c] = sum_r x[r][c] for bf16 x [rows, C] (bias gradients); scratch of as_colsum_scratch_floats(C) floats. */
+int64_t as_colsum_scratch_floats(int C);
+int as_colsum_bf16(const void* x, float* out, float* scratch, int64_t rows, int C, void* stream);
 
 /* LayerNorm(x (+ residual)) * gamma + beta, eps 1e-5, optional fused ReLU -- replaces nn.LayerNorm at
  * module_utils.py:135,139 (Transformer), lstm.py:140-151 (LN-LSTM), res_block.py:68-141 (ResFCBlock/ResFCBlock2).
