@@ -1,0 +1,146 @@
+"""GPU parity of the padded-NHWC bf16 spatial kernels against plain PyTorch fp32 references (same bf16-rounded
+inputs).  Tolerances are stated per assertion; they are bf16 storage rounding (2^-8 relative) of the outputs."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand(shape, seed, scale=1.0):
+    return (torch.randn(shape, generator=torch.Generator().manual_seed(seed)) * scale).cuda()
+
+
+def _to_p(x):
+    from applestar_b200 import spatial
+    return spatial.to_pnhwc(x)
+
+
+def _from_p(p):
+    return p[:, 1:-1, 1:-1].permute(0, 3, 1, 2).float()
+
+
+def _border_zero(p):
+    return (p[:, 0].abs().max() == 0 and p[:, -1].abs().max() == 0 and p[:, :, 0].abs().max() == 0
+            and p[:, :, -1].abs().max() == 0)
+
+
+def test_layout_round_trip_and_channel_pad():
+    from applestar_b200 import spatial
+    x = _rand((3, 20, 19, 20), 1).requires_grad_(True)
+    p = spatial.to_pnhwc(x, 64)
+    assert p.shape == (3, 21, 22, 64) and _border_zero(p) and p[..., 20:].abs().max() == 0
+    assert torch.equal(_from_p(p)[:, :20], x.detach().to(torch.bfloat16).float())
+    g = _rand(p.shape, 2).to(torch.bfloat16)
+    p.backward(g)
+    assert torch.equal(x.grad, _from_p(g)[:, :20])
+
+
+@pytest.mark.parametrize('cin,cout,k,H,W', [(128, 128, 3, 19, 20), (128, 64, 3, 38, 40), (64, 32, 3, 76, 80),
+                                             (128, 128, 1, 19, 20)])
+def test_conv_nhwc_forward_backward(cin, cout, k, H, W):
+    from applestar_b200 import spatial
+    R = 3
+    x = _rand((R, cin, H, W), 3).requires_grad_(True)
+    w = _rand((cout, cin, k, k), 4, 0.05).requires_grad_(True)
+    b = _rand((cout,), 5).requires_grad_(True)
+    y = spatial.conv(_to_p(x), w, b, relu=True)
+    assert _border_zero(y)
+    gy = torch.zeros_like(y)
+    gy[:, 1:-1, 1:-1] = _rand((R, H, W, cout), 6).to(torch.bfloat16)
+    y.backward(gy)
+    xr = x.detach().to(torch.bfloat16).float().requires_grad_(True)
+    wr = w.detach().to(torch.bfloat16).float().requires_grad_(True)
+    br = b.detach().clone().requires_grad_(True)
+    yr = F.relu(F.conv2d(xr, wr, br, padding=k // 2))
+    yr.backward(_from_p(gy))
+    scale = yr.abs().max().item()
+    assert (_from_p(y) - yr).abs().max().item() < 0.01 * scale + 1e-2
+    assert (x.grad - xr.grad).abs().max().item() < 0.02 * xr.grad.abs().max().item() + 1e-3
+    assert (w.grad - wr.grad).abs().max().item() < 0.02 * wr.grad.abs().max().item() + 1e-2
+    assert (b.grad - br.grad).abs().max().item() < 0.01 * br.grad.abs().max().item() + 1e-2
+
+
+def test_conv1_padded_input_channels():
+    """location-head conv1: 132 real channels carried in a 192-channel map."""
+    from applestar_b200 import spatial
+    R, H, W = 2, 19, 20
+    emb = torch.relu(_rand((R, 4 * H * W), 7)).requires_grad_(True)
+    skip_nchw = _rand((R, 128, H, W), 8).requires_grad_(True)
+    w = _rand((128, 132, 1, 1), 9, 0.05).requires_grad_(True)
+    cat = spatial.loc_cat(emb, _to_p(skip_nchw), 192)
+    assert _border_zero(cat) and cat[..., 132:].abs().max() == 0
+    y = spatial.conv(cat, w, None, relu=False)
+    gy = torch.zeros_like(y)
+    gy[:, 1:-1, 1:-1] = _rand((R, H, W, 128), 10).to(torch.bfloat16)
+    y.backward(gy)
+    er = emb.detach().clone().requires_grad_(True)
+    sr = skip_nchw.detach().to(torch.bfloat16).float().requires_grad_(True)
+    wr = w.detach().to(torch.bfloat16).float().requires_grad_(True)
+    catr = F.relu(torch.cat([er.view(R, 4, H, W), sr], dim=1))
+    yr = F.conv2d(catr, wr)
+    yr.backward(_from_p(gy))
+    assert (_from_p(y) - yr).abs().max().item() < 0.02 * yr.abs().max().item() + 1e-2
+    assert (emb.grad - er.grad).abs().max().item() < 0.02 * er.grad.abs().max().item() + 1e-3
+    assert (skip_nchw.grad - sr.grad).abs().max().item() < 0.02 * sr.grad.abs().max().item() + 1e-3
+    assert (w.grad - wr.grad).abs().max().item() < 0.02 * wr.grad.abs().max().item() + 1e-2
+
+
+def test_residual_tails():
+    from applestar_b200 import spatial
+    a = _rand((2, 21, 22, 128), 11).to(torch.bfloat16).requires_grad_(True)
+    b = _rand((2, 21, 22, 128), 12).to(torch.bfloat16).requires_grad_(True)
+    g = _rand((2, 21, 22, 128), 13).to(torch.bfloat16)
+    y = spatial.add_relu(a, b)
+    y.backward(g)
+    ref = F.relu(a.detach().float() + b.detach().float())
+    assert torch.equal(y.float(), ref.to(torch.bfloat16).float())
+    assert torch.equal(a.grad.float(), (g.float() * (ref > 0)).to(torch.bfloat16).float()) and torch.equal(a.grad, b.grad)
+    # gated residual
+    r, gg, x = (_rand((2, 21, 22, 128), s).to(torch.bfloat16).requires_grad_(True) for s in (14, 15, 16))
+    sp = torch.full((1,), 0.1, device='cuda', requires_grad=True)
+    y = spatial.gated_residual(r, gg, sp, x)
+    y.backward(g)
+    rr, gr, xr = (t.detach().float().requires_grad_(True) for t in (r, gg, x))
+    spr = sp.detach().clone().requires_grad_(True)
+    yr = F.relu(torch.tanh(rr * torch.sigmoid(gr)) * spr + xr)
+    yr.backward(g.float())
+    assert (y.float() - yr).abs().max().item() < 0.02
+    for got, want in ((r.grad, rr.grad), (gg.grad, gr.grad), (x.grad, xr.grad)):
+        assert (got.float() - want).abs().max().item() < 0.01 * want.abs().max().item() + 1e-3
+    assert abs(sp.grad.item() - spr.grad.item()) < 0.01 * abs(spr.grad.item()) + 1e-2
+
+
+@pytest.mark.parametrize('H,W,Cc', [(19, 20, 128), (38, 40, 64)])
+def test_bilinear_upsample_fwd_bwd(H, W, Cc):
+    from applestar_b200 import spatial
+    x = _rand((2, Cc, H, W), 17).requires_grad_(True)
+    y = spatial.upsample2(_to_p(x))
+    assert y.shape == (2, 2 * H + 2, 2 * W + 2, Cc) and _border_zero(y)
+    gy = torch.zeros_like(y)
+    gy[:, 1:-1, 1:-1] = _rand((2, 2 * H, 2 * W, Cc), 18).to(torch.bfloat16)
+    y.backward(gy)
+    xr = x.detach().to(torch.bfloat16).float().requires_grad_(True)
+    yr = F.interpolate(xr, scale_factor=2., mode='bilinear')
+    yr.backward(_from_p(gy))
+    assert (_from_p(y) - yr).abs().max().item() < 0.02
+    assert (x.grad - xr.grad).abs().max().item() < 0.02 * xr.grad.abs().max().item() + 1e-3
+
+
+def test_final_conv_32_to_1():
+    from applestar_b200 import spatial
+    R, H, W = 2, 152, 160
+    x = _rand((R, 32, H, W), 19).requires_grad_(True)
+    w = _rand((1, 32, 3, 3), 20, 0.1).requires_grad_(True)
+    b = _rand((1,), 21).requires_grad_(True)
+    logits = spatial.conv_c32_to_1(_to_p(x), w, b, 1.0 / 0.8)
+    g = _rand((R, H * W), 22)
+    logits.backward(g)
+    xr = x.detach().to(torch.bfloat16).float().requires_grad_(True)
+    wr, br = w.detach().clone().requires_grad_(True), b.detach().clone().requires_grad_(True)
+    lr = (F.conv2d(xr, wr, br, padding=1) / 0.8).reshape(R, -1)
+    lr.backward(g)
+    assert (logits - lr).abs().max().item() < 1e-4
+    assert (x.grad - xr.grad).abs().max().item() < 0.01 * xr.grad.abs().max().item() + 1e-3
+    assert (w.grad - wr.grad).abs().max().item() < 1e-3 * wr.grad.abs().max().item() + 1e-2
+    assert abs(b.grad.item() - br.grad.item()) < 1e-3 * abs(br.grad.item()) + 1e-2
