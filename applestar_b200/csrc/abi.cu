@@ -42,6 +42,11 @@ int conv_c32_1_bwd(const float*, const void*, const float*, void*, float*, float
                    cudaStream_t);
 long long colsum_scratch_floats(int);
 int colsum_bf16(const void*, float*, float*, long long, int, cudaStream_t);
+int lnlstm_fwd(const float*, const float*, const float*, const void*, const float*, const float*, const float*,
+               const float*, float*, float*, float*, float*, float*, int, int, int, cudaStream_t);
+int lnlstm_bwd(const float*, const float*, const float*, const float*, const float*, const float*, const float*,
+               const float*, const void*, const float*, const float*, const float*, const float*, const float*,
+               const float*, const float*, float*, float*, float*, float*, float*, int, int, int, cudaStream_t);
 }  // namespace as
 
 #define ST(s) reinterpret_cast<cudaStream_t>(s)
@@ -208,6 +213,21 @@ int as_layer_norm_bwd(const float* dy32, const void* dy16, const float* x, const
                       int64_t rows, int C, int relu, void* stream) {
   return as::layer_norm_bwd(dy32, dy16, x, res, gamma, beta, stats, dx, dgamma, dbeta, scratch, rows, C, relu,
                             ST(stream));
+}
+
+int as_lnlstm_fwd(const float* gi, const float* h0, const float* c0, const void* whh, const float* ln_h_w,
+                  const float* ln_h_b, const float* ln_c_w, const float* ln_c_b, float* y, float* c_all, float* u_all,
+                  float* z_all, float* stats, int T, int B, int H, void* stream) {
+  return as::lnlstm_fwd(gi, h0, c0, whh, ln_h_w, ln_h_b, ln_c_w, ln_c_b, y, c_all, u_all, z_all, stats, T, B, H,
+                        ST(stream));
+}
+int as_lnlstm_bwd(const float* gi, const float* h0, const float* c0, const float* y, const float* c_all,
+                  const float* u_all, const float* z_all, const float* stats, const void* whh_t, const float* ln_h_w,
+                  const float* ln_h_b, const float* ln_c_w, const float* ln_c_b, const float* dy, const float* dhT,
+                  const float* dcT, float* dgi, float* du, float* dh0, float* dc0, float* dparam, int T, int B, int H,
+                  void* stream) {
+  return as::lnlstm_bwd(gi, h0, c0, y, c_all, u_all, z_all, stats, whh_t, ln_h_w, ln_h_b, ln_c_w, ln_c_b, dy, dhT, dcT,
+                        dgi, du, dh0, dc0, dparam, T, B, H, ST(stream));
 }
 
 int as_softmax_fwd(const float* scores, const int64_t* key_len, void* probs, int64_t groups, int Nq, int Nk,

@@ -93,32 +93,45 @@ layer_norm_bwd_kernel(const float* __restrict__ dy32, const __nv_bfloat16* __res
   }
 }
 
-// dgamma[c] = sum_r g * xhat, dbeta[c] = sum_r g : column-parallel partial sums over row chunks (deterministic).
-__global__ void layer_norm_param_grad_kernel(const float* __restrict__ dy32, const __nv_bfloat16* __restrict__ dy16,
-                                             const float* __restrict__ x, const float* __restrict__ res,
-                                             const float* __restrict__ gamma, const float* __restrict__ beta,
-                                             const float* __restrict__ stats, float* __restrict__ partial,
-                                             long long rows, int C, int relu, int chunks) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+// dgamma[c] = sum_r g * xhat, dbeta[c] = sum_r g.  Block = 32 columns x 8 row lanes over one row chunk (128-byte
+// coalesced row segments), shared-memory reduce over the row lanes, per-chunk partials, then a fixed-order reduce
+// over chunks (deterministic, no atomics).
+__global__ void __launch_bounds__(256)
+layer_norm_param_grad_kernel(const float* __restrict__ dy32, const __nv_bfloat16* __restrict__ dy16,
+                             const float* __restrict__ x, const float* __restrict__ res,
+                             const float* __restrict__ gamma, const float* __restrict__ beta,
+                             const float* __restrict__ stats, float* __restrict__ partial,
+                             long long rows, int C, int relu, int chunks) {
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + cx;
   const int chunk = blockIdx.y;
-  if (c >= C) return;
   const long long per = (rows + chunks - 1) / chunks;
   const long long r0 = chunk * per, r1 = (r0 + per < rows) ? r0 + per : rows;
-  const float gm = gamma[c], bt = beta[c];
   float ag = 0.f, ab = 0.f;
-  for (long long r = r0; r < r1; ++r) {
-    float t = __ldg(x + r * C + c);
-    if (res) t += __ldg(res + r * C + c);
-    const float a = (t - stats[r * 2]) * stats[r * 2 + 1];
-    float g = 0.f;
-    if (dy32) g += __ldg(dy32 + r * C + c);
-    if (dy16) g += __bfloat162float(dy16[r * C + c]);
-    if (relu && (a * gm + bt) <= 0.f) g = 0.f;
-    ag += g * a;
-    ab += g;
+  if (c < C) {
+    const float gm = gamma[c], bt = beta[c];
+    for (long long r = r0 + ry; r < r1; r += 8) {
+      float t = __ldg(x + r * C + c);
+      if (res) t += __ldg(res + r * C + c);
+      const float a = (t - __ldg(stats + r * 2)) * __ldg(stats + r * 2 + 1);
+      float g = 0.f;
+      if (dy32) g += __ldg(dy32 + r * C + c);
+      if (dy16) g += __bfloat162float(dy16[r * C + c]);
+      if (relu && (a * gm + bt) <= 0.f) g = 0.f;
+      ag += g * a;
+      ab += g;
+    }
   }
-  partial[((long long)chunk * 2 + 0) * C + c] = ag;
-  partial[((long long)chunk * 2 + 1) * C + c] = ab;
+  __shared__ float sg[8][33], sb[8][33];
+  sg[ry][cx] = ag; sb[ry][cx] = ab;
+  __syncthreads();
+  if (ry == 0 && c < C) {
+    float tg = 0.f, tb = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { tg += sg[i][cx]; tb += sb[i][cx]; }
+    partial[((long long)chunk * 2 + 0) * C + c] = tg;
+    partial[((long long)chunk * 2 + 1) * C + c] = tb;
+  }
 }
 
 __global__ void layer_norm_param_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dgamma,
@@ -162,7 +175,7 @@ int layer_norm_fwd(const float* x, const float* res, const float* gamma, const f
   return AS_OK;
 }
 
-constexpr int kLnChunks = 64;
+constexpr int kLnChunks = 1024;
 long long layer_norm_bwd_scratch_floats(int C) { return (long long)kLnChunks * 2 * C; }
 
 int layer_norm_bwd(const float* dy32, const void* dy16, const float* x, const float* res, const float* gamma,
@@ -179,9 +192,10 @@ int layer_norm_bwd(const float* dy32, const void* dy16, const float* x, const fl
   }
   if (dgamma && dbeta) {
     if (!scratch) return AS_EINVAL;
-    const int chunks = rows < kLnChunks ? (int)rows : kLnChunks;
-    dim3 g((C + 127) / 128, chunks);
-    layer_norm_param_grad_kernel<<<g, 128, 0, st>>>(dy32, d16, x, res, gamma, beta, stats, scratch, rows, C, relu, chunks);
+    long long want = (rows + 255) / 256;
+    const int chunks = (int)(want < 1 ? 1 : (want > kLnChunks ? kLnChunks : want));
+    dim3 g((C + 31) / 32, chunks);
+    layer_norm_param_grad_kernel<<<g, 256, 0, st>>>(dy32, d16, x, res, gamma, beta, stats, scratch, rows, C, relu, chunks);
     AS_LAUNCH_CHECK();
     layer_norm_param_reduce_kernel<<<(C + 127) / 128, 128, 0, st>>>(scratch, dgamma, dbeta, C, chunks);
     AS_LAUNCH_CHECK();

@@ -526,15 +526,30 @@ int conv_c32_1_bwd(const float* dy, const void* in, const float* w, void* din, f
 
 // ------------------------------------------------------------------------------------------ column sums (bias grads)
 // out[c] = sum_r x[r][c] for bf16 x [rows, C]; two-stage, fixed order.
-__global__ void colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ partial, long long rows,
-                                      int C, int chunks) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
+__global__ void __launch_bounds__(256)
+colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ partial, long long rows, int C,
+                      int chunks) {
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;      // 32 column pairs x 8 row lanes
+  const int c = (blockIdx.x * 32 + cx) * 2;
   const long long per = (rows + chunks - 1) / chunks;
   const long long r0 = blockIdx.y * per, r1 = (r0 + per < rows) ? r0 + per : rows;
-  float s = 0.f;
-  for (long long r = r0; r < r1; ++r) s += bf2f(x[r * C + c]);
-  partial[(long long)blockIdx.y * C + c] = s;
+  float s0 = 0.f, s1 = 0.f;
+  if (c < C) {
+    for (long long r = r0 + ry; r < r1; r += 8) {
+      const float2 v = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(x + r * C + c));
+      s0 += v.x; s1 += v.y;
+    }
+  }
+  __shared__ float sa[8][33], sb[8][33];
+  sa[ry][cx] = s0; sb[ry][cx] = s1;
+  __syncthreads();
+  if (ry == 0 && c < C) {
+    float t0 = 0.f, t1 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { t0 += sa[i][cx]; t1 += sb[i][cx]; }
+    partial[(long long)blockIdx.y * C + c] = t0;
+    partial[(long long)blockIdx.y * C + c + 1] = t1;
+  }
 }
 __global__ void colsum_reduce_kernel(const float* __restrict__ partial, float* __restrict__ out, int C, int chunks) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -543,14 +558,15 @@ __global__ void colsum_reduce_kernel(const float* __restrict__ partial, float* _
   for (int k = 0; k < chunks; ++k) s += partial[(long long)k * C + c];
   out[c] = s;
 }
-constexpr int kColsumChunks = 256;
+constexpr int kColsumChunks = 1024;
 long long colsum_scratch_floats(int C) { return (long long)kColsumChunks * C; }
 int colsum_bf16(const void* x, float* out, float* scratch, long long rows, int C, cudaStream_t st) {
-  if (rows <= 0 || C <= 0) return AS_ESIZE;
+  if (rows <= 0 || C <= 0 || (C % 2) != 0) return AS_ESIZE;
   if (!x || !out || !scratch) return AS_EINVAL;
-  const int chunks = rows < kColsumChunks ? (int)rows : kColsumChunks;
+  long long want = (rows + 255) / 256;
+  const int chunks = (int)(want < 1 ? 1 : (want > kColsumChunks ? kColsumChunks : want));
   dim3 g((C + 63) / 64, chunks);
-  colsum_partial_kernel<<<g, 64, 0, st>>>((const __nv_bfloat16*)x, scratch, rows, C, chunks);
+  colsum_partial_kernel<<<g, 256, 0, st>>>((const __nv_bfloat16*)x, scratch, rows, C, chunks);
   AS_LAUNCH_CHECK();
   colsum_reduce_kernel<<<(C + 63) / 64, 64, 0, st>>>(scratch, out, C, chunks);
   AS_LAUNCH_CHECK();

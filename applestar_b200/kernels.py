@@ -371,17 +371,63 @@ def entity_embed(entity_info, weight, bias, layout):
     return y32.view(R, N, -1), y16.view(R, N, -1)
 
 
+class LNLSTMLayerFn(torch.autograd.Function):
+    """One LayerNorm-LSTM layer over the whole unroll in a single persistent kernel (one CTA per trajectory)."""
+
+    @staticmethod
+    def forward(ctx, gi, h0, c0, whh, gh_w, gh_b, gc_w, gc_b):
+        T, B, G = gi.shape
+        H = G // 4
+        gi, h0, c0 = gi.contiguous(), h0.contiguous().float(), c0.contiguous().float()
+        whh16 = weight_bf16(whh)
+        dev = gi.device
+        y = torch.empty((T, B, H), dtype=torch.float32, device=dev)
+        c_all = torch.empty((T, B, H), dtype=torch.float32, device=dev)
+        u_all = torch.empty((T, B, G), dtype=torch.float32, device=dev)
+        z_all = torch.empty((T, B, H), dtype=torch.float32, device=dev)
+        stats = torch.empty((T, B, 4), dtype=torch.float32, device=dev)
+        _lib.call('as_lnlstm_fwd', gi.data_ptr(), h0.data_ptr(), c0.data_ptr(), whh16.data_ptr(), gh_w.data_ptr(),
+                  gh_b.data_ptr(), gc_w.data_ptr(), gc_b.data_ptr(), y.data_ptr(), c_all.data_ptr(), u_all.data_ptr(),
+                  z_all.data_ptr(), stats.data_ptr(), T, B, H, _lib.stream_ptr())
+        ctx.dims = (T, B, H)
+        ctx.save_for_backward(gi, h0, c0, y, c_all, u_all, z_all, stats, whh, gh_w, gh_b, gc_w, gc_b)
+        return y, y[-1].clone(), c_all[-1].clone()
+
+    @staticmethod
+    def backward(ctx, dy, dhT, dcT):
+        gi, h0, c0, y, c_all, u_all, z_all, stats, whh, gh_w, gh_b, gc_w, gc_b = ctx.saved_tensors
+        T, B, H = ctx.dims
+        G = 4 * H
+        dev = gi.device
+        tag = (_SHADOW_GEN[0], whh._version, whh.data_ptr())
+        hit = getattr(whh, '_as_wt16', None)
+        if hit is None or hit[0] != tag:
+            hit = (tag, whh.detach().t().contiguous().to(torch.bfloat16))
+            try:
+                whh._as_wt16 = hit
+            except AttributeError:
+                pass
+        whh_t16 = hit[1]
+        dy = None if dy is None else dy.contiguous().float()
+        dhT = None if dhT is None else dhT.contiguous().float()
+        dcT = None if dcT is None else dcT.contiguous().float()
+        dgi = torch.empty_like(gi)
+        du = torch.empty_like(gi)
+        dh0 = torch.empty_like(h0)
+        dc0 = torch.empty_like(c0)
+        dparam = torch.empty((B, 10 * H), dtype=torch.float32, device=dev)
+        _lib.call('as_lnlstm_bwd', gi.data_ptr(), h0.data_ptr(), c0.data_ptr(), y.data_ptr(), c_all.data_ptr(),
+                  u_all.data_ptr(), z_all.data_ptr(), stats.data_ptr(), whh_t16.data_ptr(), gh_w.data_ptr(),
+                  gh_b.data_ptr(), gc_w.data_ptr(), gc_b.data_ptr(), _ptr(dy), _ptr(dhT), _ptr(dcT), dgi.data_ptr(),
+                  du.data_ptr(), dh0.data_ptr(), dc0.data_ptr(), dparam.data_ptr(), T, B, H, _lib.stream_ptr())
+        dp = dparam.sum(dim=0)
+        hprev = torch.cat([h0.unsqueeze(0), y[:-1]], dim=0).view(T * B, H)
+        dwhh = _wgrad(to_bf16(du.view(T * B, G)), to_bf16(hprev), G, H)
+        return (dgi, dh0, dc0, dwhh, dp[:G], dp[G:2 * G], dp[2 * G:2 * G + H], dp[2 * G + H:])
+
+
 def lnlstm_layer(x, h, c, cell):
-    T = x.shape[0]
-    wi, wh = cell.weight_ih, cell.weight_hh
+    """x [T,B,I] -> (y [T,B,H], h_T, c_T).  Input projection for all timesteps = one GEMM + one LayerNorm launch."""
     li, lh, lc = cell.layernorm_i, cell.layernorm_h, cell.layernorm_c
-    Hs = h.shape[-1]
-    gi_all = F.layer_norm(linear(x, wi, None), (4 * Hs,), li.weight, li.bias, 1e-5)   # all timesteps at once
-    ys = []
-    for t in range(T):
-        gh = F.layer_norm(h @ wh.t(), (4 * Hs,), lh.weight, lh.bias, 1e-5)
-        i, f, g, o = (gi_all[t] + gh).chunk(4, 1)
-        c = F.layer_norm(torch.sigmoid(f) * c + torch.sigmoid(i) * torch.tanh(g), (Hs,), lc.weight, lc.bias, 1e-5)
-        h = torch.sigmoid(o) * torch.tanh(c)
-        ys.append(h)
-    return torch.stack(ys), h, c
+    gi = layer_norm(linear(x, cell.weight_ih, None), li.weight, li.bias)
+    return LNLSTMLayerFn.apply(gi, h, c, cell.weight_hh, lh.weight, lh.bias, lc.weight, lc.bias)

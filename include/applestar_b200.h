@@ -127,6 +127,23 @@ int as_layer_norm_bwd(const float* dy32, const void* dy16, const float* x, const
                       const float* beta, const float* stats, float* dx, float* dgamma, float* dbeta, float* scratch,
                       int64_t rows, int C, int relu, void* stream);
 
+/* LayerNorm-LSTM recurrence over a whole unroll, one CTA per trajectory -- replaces the Python time loop of
+ * LSTMLayer / LayerNormLSTMCell (model/lstm.py:138-167; 65 x 3 cell calls per learner step).
+ * gi [T,B,4H] = LN_i(x W_ih^T) for all t (computed by as_gemm_bf16 + as_layer_norm_fwd), h0/c0 [B,H],
+ * whh bf16 [4H,H]; outputs y [T,B,H] (h_t) and c_all [T,B,H]; u_all [T,B,4H], z_all [T,B,H], stats [T,B,4] are
+ * saved for backward (pass NULL for inference).  H % 8 == 0, H <= 1024. */
+int as_lnlstm_fwd(const float* gi, const float* h0, const float* c0, const void* whh, const float* ln_h_w,
+                  const float* ln_h_b, const float* ln_c_w, const float* ln_c_b, float* y, float* c_all, float* u_all,
+                  float* z_all, float* stats, int T, int B, int H, void* stream);
+/* Reverse-time twin.  whh_t = W_hh^T bf16 [H,4H]; dy [T,B,H] / dhT / dcT [B,H] may be NULL.  Outputs: dgi [T,B,4H],
+ * du [T,B,4H] (dW_hh = sum_{t,b} du h_{t-1}^T is a GEMM the caller runs), dh0/dc0 [B,H] (may be NULL), and dparam
+ * [B, 10H] = per-trajectory partial gradients of (ln_h_w, ln_h_b, ln_c_w, ln_c_b). */
+int as_lnlstm_bwd(const float* gi, const float* h0, const float* c0, const float* y, const float* c_all,
+                  const float* u_all, const float* z_all, const float* stats, const void* whh_t, const float* ln_h_w,
+                  const float* ln_h_b, const float* ln_c_w, const float* ln_c_b, const float* dy, const float* dhT,
+                  const float* dcT, float* dgi, float* du, float* dh0, float* dc0, float* dparam, int T, int B, int H,
+                  void* stream);
+
 /* Masked attention softmax with warp-shuffle reductions -- replaces masked_fill_ + F.softmax at
  * module_utils.py:100-104.  scores [groups, Nq, Nk] fp32 (already scaled by 1/sqrt(d)); key j of group g is valid
  * iff j < key_len[g / groups_per_len] (key_len NULL = no mask); probs bf16 with masked keys exactly 0.  Nk <= 1024. */

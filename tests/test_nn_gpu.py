@@ -77,3 +77,48 @@ def test_entity_features_match_oracle_concat():
     dev['alliance'][0, 0] = -1
     _, neg = K.entity_features(dev, C.ENTITY_FIELDS, 1000)
     assert int(neg.item()) == 1                                           # the reference raises here
+
+
+@pytest.mark.parametrize('T,B,I,H', [(5, 3, 64, 384), (1, 4, 32, 32), (9, 2, 384, 384)])
+def test_lnlstm_layer_fwd_bwd_vs_oracle_cell(T, B, I, H):
+    """Persistent LN-LSTM kernel vs the oracle's per-step cell (lstm.py:138-153 restated).  W_hh and the input GEMM
+    run in bf16 -> tolerance 3e-2 abs on O(1) outputs, 8% of max on gradients."""
+    from applestar_b200 import kernels as K
+    from applestar_b200.model import LayerNormLSTMCell
+    g = torch.Generator().manual_seed(T * 100 + H)
+    cell = LayerNormLSTMCell(I, H)
+    with torch.no_grad():
+        for p in cell.parameters():
+            if p.dim() == 1:
+                p.add_(0.1 * torch.randn(p.shape, generator=g))
+    cell = cell.cuda()
+    x = torch.randn(T, B, I, generator=g).cuda().requires_grad_(True)
+    h0 = (0.1 * torch.randn(B, H, generator=g)).cuda().requires_grad_(True)
+    c0 = (0.1 * torch.randn(B, H, generator=g)).cuda().requires_grad_(True)
+    y, hT, cT = K.lnlstm_layer(x, h0, c0, cell)
+    gy = torch.randn(T, B, H, generator=g).cuda()
+    gc = torch.randn(B, H, generator=g).cuda()
+    torch.autograd.backward([y, cT], [gy, gc])
+
+    sd = {'c.' + k: v.detach().cpu().clone().requires_grad_(True) for k, v in cell.state_dict().items()}
+    xr = x.detach().cpu().clone().requires_grad_(True)
+    hr, cr = h0.detach().cpu().clone().requires_grad_(True), c0.detach().cpu().clone().requires_grad_(True)
+    h, c, ys = hr, cr, []
+    for t in range(T):
+        h, c = R.lnlstm_cell(sd, 'c', xr[t], h, c)
+        ys.append(h)
+    yr = torch.stack(ys)
+    torch.autograd.backward([yr, c], [gy.cpu(), gc.cpu()])
+    assert (y.cpu() - yr).abs().max().item() < 3e-2
+    assert (cT.cpu() - c).abs().max().item() < 5e-2
+    assert torch.equal(hT, y[-1])
+    for got, want, name in ((x.grad, xr.grad, 'x'), (h0.grad, hr.grad, 'h0'), (c0.grad, cr.grad, 'c0'),
+                            (cell.weight_hh.grad, sd['c.weight_hh'].grad, 'whh'),
+                            (cell.weight_ih.grad, sd['c.weight_ih'].grad, 'wih'),
+                            (cell.layernorm_h.weight.grad, sd['c.layernorm_h.weight'].grad, 'lnh.w'),
+                            (cell.layernorm_h.bias.grad, sd['c.layernorm_h.bias'].grad, 'lnh.b'),
+                            (cell.layernorm_c.weight.grad, sd['c.layernorm_c.weight'].grad, 'lnc.w'),
+                            (cell.layernorm_c.bias.grad, sd['c.layernorm_c.bias'].grad, 'lnc.b'),
+                            (cell.layernorm_i.weight.grad, sd['c.layernorm_i.weight'].grad, 'lni.w')):
+        err = (got.cpu() - want).abs().max().item()
+        assert err < 0.08 * want.abs().max().item() + 2e-3, (name, err, want.abs().max().item())

@@ -6,6 +6,10 @@ import torch.nn.functional as F
 
 pytestmark = pytest.mark.gpu
 
+# the PyTorch references here must be true fp32 (cuDNN would otherwise use TF32 for convolutions)
+torch.backends.cudnn.allow_tf32 = False
+torch.backends.cuda.matmul.allow_tf32 = False
+
 
 def _rand(shape, seed, scale=1.0):
     return (torch.randn(shape, generator=torch.Generator().manual_seed(seed)) * scale).cuda()
