@@ -30,4 +30,8 @@ torch.cuda.synchronize()
 with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
     step(data)
     torch.cuda.synchronize()
-print(prof.key_averages().table(sort_by='cuda_time_total', row_limit=a.rows, max_name_column_width=90))
+ka = prof.key_averages()
+n_kernels = sum(e.count for e in ka if e.device_type == torch.autograd.DeviceType.CUDA)
+print('CUDA kernel launches in one step: %d' % n_kernels)
+print(ka.table(sort_by='cuda_time_total', row_limit=a.rows, max_name_column_width=90))
+print(ka.table(sort_by='self_cpu_time_total', row_limit=40, max_name_column_width=70))
