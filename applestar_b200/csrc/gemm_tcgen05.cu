@@ -18,6 +18,7 @@ namespace as {
 constexpr int BM = 128;
 constexpr int BK = 64;  // 64 bf16 = 128 bytes = one swizzle row
 constexpr int kGemmThreads = 256;
+constexpr int kStgPitch = 36;   // floats per staged row: 16-byte aligned rows, conflict-free float4 access
 
 struct GemmDev {
   int M, N, K;
@@ -48,7 +49,8 @@ struct SmemLayout {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = (BN >= 256) ? 4 : (BN >= 128 ? 6 : 8);
   static constexpr int kBarBytes = 1024;
-  static constexpr int kTotal = kStages * kStageBytes + kBarBytes + 1024;  // +1024 alignment slack
+  static constexpr int kStgBytes = 4 * 32 * 36 * 4;                          // per-warp epilogue staging tiles
+  static constexpr int kTotal = kStages * kStageBytes + kBarBytes + kStgBytes + 1024;  // +1024 alignment slack
 };
 
 template <int BN, bool A_MN, bool B_MN>
@@ -183,7 +185,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   } else if (warp >= 4) {
     // ------------------------------------------------------------------ epilogue (4 warps = 128 TMEM lanes)
+    // tcgen05.ld gives each lane one accumulator row (32 columns at a time).  The chunk is staged through a per-warp
+    // shared-memory tile so that global stores are row-contiguous (full 32-byte sectors, 64-128 B per row segment);
+    // bias / ReLU / border mask / dtype conversion happen on the way out.  All register arrays are indexed statically.
     const int ew = warp & 3;
+    float* stg = reinterpret_cast<float*>(bar_base + L::kBarBytes) + ew * (32 * kStgPitch);
     int acc = 0;
     uint32_t acc_phase = 0;
     for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -193,98 +199,123 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const int b = (int)(t % batch);
       const int split = (int)(t / batch);
       const int b0 = b % p.nb0, b1 = b / p.nb0;
-      const int row = m_blk * BM + ew * 32 + lane;
+      const int row_base = m_blk * BM + ew * 32;
       const int n0 = n_blk * BN;
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(acc * BN);
-      bool border = false;
-      if (p.img_w > 0) {
-        const int q = row % (p.img_w * p.img_h);
-        const int yy = q / p.img_w, xx = q - yy * p.img_w;
-        border = (yy == 0) | (yy == p.img_h - 1) | (xx == 0) | (xx == p.img_w - 1);
-      }
+      const bool to_ws = p.splits > 1;
+      const long long out_off = to_ws ? (((long long)split * batch + b) * p.M) * (long long)p.N
+                                      : (long long)b0 * p.c_sb0 + (long long)b1 * p.c_sb1;
+      const long long ldo = to_ws ? (long long)p.N : p.ldc;
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         uint32_t v[32];
         tmem_ld32(t_row + c * 32, v);
         tmem_ld_wait();
         const int col0 = n0 + c * 32;
-        if (row < p.M && col0 < p.N) {
-          float f[32];
+        if (col0 >= p.N) continue;                       // warp-uniform
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-          const bool full = (col0 + 32 <= p.N);
-          if (p.splits > 1) {
-            float* dst = p.ws + (((long long)split * batch + b) * p.M + row) * (long long)p.N + col0;
-            if (full && ((p.N & 3) == 0)) {
+        for (int q = 0; q < 8; ++q)
+          *reinterpret_cast<float4*>(stg + lane * kStgPitch + q * 4) =
+              make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]), __uint_as_float(v[4 * q + 2]),
+                          __uint_as_float(v[4 * q + 3]));
+        __syncwarp();
+        if (to_ws || !p.c_bf16) {
+          // fp32 output: 8 lanes cover one 128-byte row segment, 4 rows per instruction
+          const int cq = (lane & 7) * 4;
+          const int gcol = col0 + cq;
+          float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (!to_ws && p.bias != nullptr) {
+            if (gcol < p.N) bv.x = __ldg(p.bias + gcol);
+            if (gcol + 1 < p.N) bv.y = __ldg(p.bias + gcol + 1);
+            if (gcol + 2 < p.N) bv.z = __ldg(p.bias + gcol + 2);
+            if (gcol + 3 < p.N) bv.w = __ldg(p.bias + gcol + 3);
+          }
 #pragma unroll
-              for (int j = 0; j < 8; ++j)
-                reinterpret_cast<float4*>(dst)[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
-            } else {
-              for (int j = 0; j < 32 && col0 + j < p.N; ++j) dst[j] = f[j];
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              float x = f[j] * p.alpha;
-              if (p.bias != nullptr && (full || col0 + j < p.N)) x += __ldg(p.bias + col0 + j);
-              if (p.relu) x = fmaxf(x, 0.f);
-              if (border) x = 0.f;
-              f[j] = x;
-            }
-            const long long off = (long long)b0 * p.c_sb0 + (long long)b1 * p.c_sb1 + (long long)row * p.ldc + col0;
-            if (p.c_bf16) {
-              __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.C) + off;
-              if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                  uint4 u;
-                  __nv_bfloat162 h0 = __floats2bfloat162_rn(f[8 * j], f[8 * j + 1]);
-                  __nv_bfloat162 h1 = __floats2bfloat162_rn(f[8 * j + 2], f[8 * j + 3]);
-                  __nv_bfloat162 h2 = __floats2bfloat162_rn(f[8 * j + 4], f[8 * j + 5]);
-                  __nv_bfloat162 h3 = __floats2bfloat162_rn(f[8 * j + 6], f[8 * j + 7]);
-                  u.x = *reinterpret_cast<uint32_t*>(&h0);
-                  u.y = *reinterpret_cast<uint32_t*>(&h1);
-                  u.z = *reinterpret_cast<uint32_t*>(&h2);
-                  u.w = *reinterpret_cast<uint32_t*>(&h3);
-                  reinterpret_cast<uint4*>(dst)[j] = u;
-                }
-              } else {
-                for (int j = 0; j < 32 && col0 + j < p.N; ++j) dst[j] = __float2bfloat16_rn(f[j]);
+          for (int it = 0; it < 8; ++it) {
+            const int r = it * 4 + (lane >> 3);
+            const int grow = row_base + r;
+            float4 a = *reinterpret_cast<const float4*>(stg + r * kStgPitch + cq);
+            if (!to_ws) {
+              a.x = a.x * p.alpha + bv.x; a.y = a.y * p.alpha + bv.y; a.z = a.z * p.alpha + bv.z; a.w = a.w * p.alpha + bv.w;
+              if (p.relu) { a.x = fmaxf(a.x, 0.f); a.y = fmaxf(a.y, 0.f); a.z = fmaxf(a.z, 0.f); a.w = fmaxf(a.w, 0.f); }
+              if (p.img_w > 0) {
+                const int q = grow % (p.img_w * p.img_h);
+                const int yy = q / p.img_w, xx = q - yy * p.img_w;
+                if ((yy == 0) | (yy == p.img_h - 1) | (xx == 0) | (xx == p.img_w - 1)) a = make_float4(0.f, 0.f, 0.f, 0.f);
               }
-            } else {
-              float* dst = reinterpret_cast<float*>(p.C) + off;
-              if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
-#pragma unroll
-                for (int j = 0; j < 8; ++j)
-                  reinterpret_cast<float4*>(dst)[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+            }
+            if (grow < p.M && gcol < p.N) {
+              float* dst = (to_ws ? p.ws : reinterpret_cast<float*>(p.C)) + out_off + (long long)grow * ldo + gcol;
+              if (gcol + 4 <= p.N && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+                *reinterpret_cast<float4*>(dst) = a;
               } else {
-                for (int j = 0; j < 32 && col0 + j < p.N; ++j) dst[j] = f[j];
+                dst[0] = a.x;
+                if (gcol + 1 < p.N) dst[1] = a.y;
+                if (gcol + 2 < p.N) dst[2] = a.z;
+                if (gcol + 3 < p.N) dst[3] = a.w;
               }
-              if (p.C2 != nullptr) {
-                __nv_bfloat16* d2 = reinterpret_cast<__nv_bfloat16*>(p.C2) + off;
-                if (full && ((reinterpret_cast<uintptr_t>(d2) & 15) == 0)) {
-#pragma unroll
-                  for (int j = 0; j < 4; ++j) {
-                    uint4 u;
-                    __nv_bfloat162 h0 = __floats2bfloat162_rn(f[8 * j], f[8 * j + 1]);
-                    __nv_bfloat162 h1 = __floats2bfloat162_rn(f[8 * j + 2], f[8 * j + 3]);
-                    __nv_bfloat162 h2 = __floats2bfloat162_rn(f[8 * j + 4], f[8 * j + 5]);
-                    __nv_bfloat162 h3 = __floats2bfloat162_rn(f[8 * j + 6], f[8 * j + 7]);
-                    u.x = *reinterpret_cast<uint32_t*>(&h0);
-                    u.y = *reinterpret_cast<uint32_t*>(&h1);
-                    u.z = *reinterpret_cast<uint32_t*>(&h2);
-                    u.w = *reinterpret_cast<uint32_t*>(&h3);
-                    reinterpret_cast<uint4*>(d2)[j] = u;
-                  }
+              if (!to_ws && p.C2 != nullptr) {
+                __nv_bfloat16* d2 = reinterpret_cast<__nv_bfloat16*>(p.C2) + out_off + (long long)grow * ldo + gcol;
+                if (gcol + 4 <= p.N && (reinterpret_cast<uintptr_t>(d2) & 7) == 0) {
+                  __nv_bfloat162 h0 = __floats2bfloat162_rn(a.x, a.y), h1 = __floats2bfloat162_rn(a.z, a.w);
+                  uint2 u;
+                  u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
+                  *reinterpret_cast<uint2*>(d2) = u;
                 } else {
-                  for (int j = 0; j < 32 && col0 + j < p.N; ++j) d2[j] = __float2bfloat16_rn(f[j]);
+                  d2[0] = __float2bfloat16_rn(a.x);
+                  if (gcol + 1 < p.N) d2[1] = __float2bfloat16_rn(a.y);
+                  if (gcol + 2 < p.N) d2[2] = __float2bfloat16_rn(a.z);
+                  if (gcol + 3 < p.N) d2[3] = __float2bfloat16_rn(a.w);
                 }
               }
             }
           }
+        } else {
+          // bf16 output: 4 lanes cover one 64-byte row segment, 8 rows per instruction
+          const int cq = (lane & 3) * 8;
+          const int gcol = col0 + cq;
+          float bv[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) bv[e] = (p.bias != nullptr && gcol + e < p.N) ? __ldg(p.bias + gcol + e) : 0.f;
+#pragma unroll
+          for (int it = 0; it < 4; ++it) {
+            const int r = it * 8 + (lane >> 2);
+            const int grow = row_base + r;
+            const float4 a0 = *reinterpret_cast<const float4*>(stg + r * kStgPitch + cq);
+            const float4 a1 = *reinterpret_cast<const float4*>(stg + r * kStgPitch + cq + 4);
+            float f[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            bool border = false;
+            if (p.img_w > 0) {
+              const int q = grow % (p.img_w * p.img_h);
+              const int yy = q / p.img_w, xx = q - yy * p.img_w;
+              border = (yy == 0) | (yy == p.img_h - 1) | (xx == 0) | (xx == p.img_w - 1);
+            }
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              float x = f[e] * p.alpha + bv[e];
+              if (p.relu) x = fmaxf(x, 0.f);
+              f[e] = border ? 0.f : x;
+            }
+            if (grow < p.M && gcol < p.N) {
+              __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.C) + out_off + (long long)grow * ldo + gcol;
+              if (gcol + 8 <= p.N && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+                __nv_bfloat162 h0 = __floats2bfloat162_rn(f[0], f[1]), h1 = __floats2bfloat162_rn(f[2], f[3]);
+                __nv_bfloat162 h2 = __floats2bfloat162_rn(f[4], f[5]), h3 = __floats2bfloat162_rn(f[6], f[7]);
+                uint4 u;
+                u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
+                u.z = *reinterpret_cast<uint32_t*>(&h2); u.w = *reinterpret_cast<uint32_t*>(&h3);
+                *reinterpret_cast<uint4*>(dst) = u;
+              } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                  if (gcol + e < p.N) dst[e] = __float2bfloat16_rn(f[e]);
+              }
+            }
+          }
         }
+        __syncwarp();                                    // staging tile is reused by the next chunk
       }
       tc_fence_before();
       __syncwarp();
