@@ -9,7 +9,7 @@
 // Extra modes: split-K (fp32 partials into a caller workspace, reduced by as_splitk_reduce) and an implicit-GEMM
 // 3x3 convolution over zero-padded NHWC pixels (per-tap row shift of the A operand, see as_conv3x3_*).
 //
-// Warp roles (192 threads... 8 warps): w0 TMA producer, w1 MMA issuer, w2 TMEM allocator, w4-7 epilogue.
+// Warp roles (12 warps): w0 TMA producer, w1 MMA issuer, w2 TMEM allocator, w4-11 epilogue.
 #include "common.cuh"
 #include "gemm.h"
 
@@ -17,8 +17,9 @@ namespace as {
 
 constexpr int BM = 128;
 constexpr int BK = 64;  // 64 bf16 = 128 bytes = one swizzle row
-constexpr int kGemmThreads = 256;
-constexpr int kStgPitch = 36;   // floats per staged row: 16-byte aligned rows, conflict-free float4 access
+constexpr int kEpiWarps = 8;
+constexpr int kGemmThreads = 128 + 32 * kEpiWarps;
+constexpr int kStgPitch = 20;   // floats per staged row (16 columns + pad): 16-byte aligned, conflict-free float4 access
 
 struct GemmDev {
   int M, N, K;
@@ -49,7 +50,7 @@ struct SmemLayout {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = (BN >= 256) ? 4 : (BN >= 128 ? 6 : 8);
   static constexpr int kBarBytes = 1024;
-  static constexpr int kStgBytes = 4 * 32 * 36 * 4;                          // per-warp epilogue staging tiles
+  static constexpr int kStgBytes = kEpiWarps * 32 * kStgPitch * 4;            // per-warp epilogue staging tiles
   static constexpr int kTotal = kStages * kStageBytes + kBarBytes + kStgBytes + 1024;  // +1024 alignment slack
 };
 
@@ -61,7 +62,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   constexpr uint32_t kTmemCols = (2 * BN <= 32) ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
 
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // 1024-byte alignment for the 128B swizzle; pointer arithmetic (not an integer round trip) keeps the shared
+  // address space visible to the compiler
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* bar_base = smem + kStages * L::kStageBytes;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(bar_base);
   uint64_t* empty_bar = full_bar + kStages;
@@ -83,7 +86,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full[i], 1);
-      mbar_init(&tmem_empty[i], 4);
+      mbar_init(&tmem_empty[i], kEpiWarps);
     }
     mbar_fence_init();
   }
@@ -184,12 +187,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       }
     }
   } else if (warp >= 4) {
-    // ------------------------------------------------------------------ epilogue (4 warps = 128 TMEM lanes)
-    // tcgen05.ld gives each lane one accumulator row (32 columns at a time).  The chunk is staged through a per-warp
-    // shared-memory tile so that global stores are row-contiguous (full 32-byte sectors, 64-128 B per row segment);
-    // bias / ReLU / border mask / dtype conversion happen on the way out.  All register arrays are indexed statically.
-    const int ew = warp & 3;
-    float* stg = reinterpret_cast<float*>(bar_base + L::kBarBytes) + ew * (32 * kStgPitch);
+    // ------------------------------------------------------------------ epilogue (8 warps)
+    // Warp e reads TMEM lanes 32*(e%4).. (its hardware quarter) and the column half e/4 of the tile, so two warps per
+    // scheduler hide each other's fixed-latency stalls.  tcgen05.ld gives each lane one accumulator row (32 columns);
+    // the chunk goes through a per-warp shared-memory tile 16 columns at a time so that global stores are
+    // row-contiguous full sectors; bias / ReLU / border mask / dtype conversion happen on the way out.
+    const int e = warp - 4;
+    const int ew = e & 3;
+    const int half = e >> 2;
+    float* stg = reinterpret_cast<float*>(bar_base + L::kBarBytes) + e * (32 * kStgPitch);
+    constexpr int kChunks = BN / 32;
+    constexpr int kPerHalf = kChunks >= 2 ? kChunks / 2 : 1;
+    const int c_begin = half * kPerHalf;
+    const int c_end = (kChunks >= 2) ? c_begin + kPerHalf : (half == 0 ? 1 : 0);
     int acc = 0;
     uint32_t acc_phase = 0;
     for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -208,114 +218,122 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const long long out_off = to_ws ? (((long long)split * batch + b) * p.M) * (long long)p.N
                                       : (long long)b0 * p.c_sb0 + (long long)b1 * p.c_sb1;
       const long long ldo = to_ws ? (long long)p.N : p.ldc;
+      const bool f32_out = to_ws || !p.c_bf16;
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
+      for (int c = c_begin; c < c_end; ++c) {
         uint32_t v[32];
         tmem_ld32(t_row + c * 32, v);
         tmem_ld_wait();
-        const int col0 = n0 + c * 32;
-        if (col0 >= p.N) continue;                       // warp-uniform
+        if (n0 + c * 32 >= p.N) continue;                // warp-uniform
 #pragma unroll
-        for (int q = 0; q < 8; ++q)
-          *reinterpret_cast<float4*>(stg + lane * kStgPitch + q * 4) =
-              make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]), __uint_as_float(v[4 * q + 2]),
-                          __uint_as_float(v[4 * q + 3]));
-        __syncwarp();
-        if (to_ws || !p.c_bf16) {
-          // fp32 output: 8 lanes cover one 128-byte row segment, 4 rows per instruction
-          const int cq = (lane & 7) * 4;
-          const int gcol = col0 + cq;
-          float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (!to_ws && p.bias != nullptr) {
-            if (gcol < p.N) bv.x = __ldg(p.bias + gcol);
-            if (gcol + 1 < p.N) bv.y = __ldg(p.bias + gcol + 1);
-            if (gcol + 2 < p.N) bv.z = __ldg(p.bias + gcol + 2);
-            if (gcol + 3 < p.N) bv.w = __ldg(p.bias + gcol + 3);
-          }
+        for (int sub = 0; sub < 2; ++sub) {
+          const int col0 = n0 + c * 32 + sub * 16;
 #pragma unroll
-          for (int it = 0; it < 8; ++it) {
-            const int r = it * 4 + (lane >> 3);
-            const int grow = row_base + r;
-            float4 a = *reinterpret_cast<const float4*>(stg + r * kStgPitch + cq);
-            if (!to_ws) {
-              a.x = a.x * p.alpha + bv.x; a.y = a.y * p.alpha + bv.y; a.z = a.z * p.alpha + bv.z; a.w = a.w * p.alpha + bv.w;
-              if (p.relu) { a.x = fmaxf(a.x, 0.f); a.y = fmaxf(a.y, 0.f); a.z = fmaxf(a.z, 0.f); a.w = fmaxf(a.w, 0.f); }
-              if (p.img_w > 0) {
-                const int q = grow % (p.img_w * p.img_h);
-                const int yy = q / p.img_w, xx = q - yy * p.img_w;
-                if ((yy == 0) | (yy == p.img_h - 1) | (xx == 0) | (xx == p.img_w - 1)) a = make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int q = 0; q < 4; ++q)
+            *reinterpret_cast<float4*>(stg + lane * kStgPitch + q * 4) =
+                make_float4(__uint_as_float(v[sub * 16 + 4 * q]), __uint_as_float(v[sub * 16 + 4 * q + 1]),
+                            __uint_as_float(v[sub * 16 + 4 * q + 2]), __uint_as_float(v[sub * 16 + 4 * q + 3]));
+          __syncwarp();
+          if (col0 < p.N) {
+            if (f32_out) {
+              // fp32: 4 lanes cover one 64-byte row segment, 8 rows per instruction
+              const int cq = (lane & 3) * 4;
+              const int gcol = col0 + cq;
+              float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (!to_ws && p.bias != nullptr) {
+                if (gcol < p.N) bv.x = __ldg(p.bias + gcol);
+                if (gcol + 1 < p.N) bv.y = __ldg(p.bias + gcol + 1);
+                if (gcol + 2 < p.N) bv.z = __ldg(p.bias + gcol + 2);
+                if (gcol + 3 < p.N) bv.w = __ldg(p.bias + gcol + 3);
               }
-            }
-            if (grow < p.M && gcol < p.N) {
-              float* dst = (to_ws ? p.ws : reinterpret_cast<float*>(p.C)) + out_off + (long long)grow * ldo + gcol;
-              if (gcol + 4 <= p.N && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
-                *reinterpret_cast<float4*>(dst) = a;
-              } else {
-                dst[0] = a.x;
-                if (gcol + 1 < p.N) dst[1] = a.y;
-                if (gcol + 2 < p.N) dst[2] = a.z;
-                if (gcol + 3 < p.N) dst[3] = a.w;
+              float* obase = (to_ws ? p.ws : reinterpret_cast<float*>(p.C)) + out_off + gcol;
+#pragma unroll
+              for (int it = 0; it < 4; ++it) {
+                const int r = it * 8 + (lane >> 2);
+                const int grow = row_base + r;
+                float4 a = *reinterpret_cast<const float4*>(stg + r * kStgPitch + cq);
+                if (!to_ws) {
+                  a.x = a.x * p.alpha + bv.x; a.y = a.y * p.alpha + bv.y; a.z = a.z * p.alpha + bv.z; a.w = a.w * p.alpha + bv.w;
+                  if (p.relu) { a.x = fmaxf(a.x, 0.f); a.y = fmaxf(a.y, 0.f); a.z = fmaxf(a.z, 0.f); a.w = fmaxf(a.w, 0.f); }
+                  if (p.img_w > 0) {
+                    const int q = grow % (p.img_w * p.img_h);
+                    const int yy = q / p.img_w, xx = q - yy * p.img_w;
+                    if ((yy == 0) | (yy == p.img_h - 1) | (xx == 0) | (xx == p.img_w - 1)) a = make_float4(0.f, 0.f, 0.f, 0.f);
+                  }
+                }
+                if (grow < p.M && gcol < p.N) {
+                  float* dst = obase + (long long)grow * ldo;
+                  if (gcol + 4 <= p.N && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+                    *reinterpret_cast<float4*>(dst) = a;
+                  } else {
+                    dst[0] = a.x;
+                    if (gcol + 1 < p.N) dst[1] = a.y;
+                    if (gcol + 2 < p.N) dst[2] = a.z;
+                    if (gcol + 3 < p.N) dst[3] = a.w;
+                  }
+                  if (!to_ws && p.C2 != nullptr) {
+                    __nv_bfloat16* d2 = reinterpret_cast<__nv_bfloat16*>(p.C2) + out_off + (long long)grow * ldo + gcol;
+                    if (gcol + 4 <= p.N && (reinterpret_cast<uintptr_t>(d2) & 7) == 0) {
+                      __nv_bfloat162 h0 = __floats2bfloat162_rn(a.x, a.y), h1 = __floats2bfloat162_rn(a.z, a.w);
+                      uint2 u;
+                      u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
+                      *reinterpret_cast<uint2*>(d2) = u;
+                    } else {
+                      d2[0] = __float2bfloat16_rn(a.x);
+                      if (gcol + 1 < p.N) d2[1] = __float2bfloat16_rn(a.y);
+                      if (gcol + 2 < p.N) d2[2] = __float2bfloat16_rn(a.z);
+                      if (gcol + 3 < p.N) d2[3] = __float2bfloat16_rn(a.w);
+                    }
+                  }
+                }
               }
-              if (!to_ws && p.C2 != nullptr) {
-                __nv_bfloat16* d2 = reinterpret_cast<__nv_bfloat16*>(p.C2) + out_off + (long long)grow * ldo + gcol;
-                if (gcol + 4 <= p.N && (reinterpret_cast<uintptr_t>(d2) & 7) == 0) {
-                  __nv_bfloat162 h0 = __floats2bfloat162_rn(a.x, a.y), h1 = __floats2bfloat162_rn(a.z, a.w);
-                  uint2 u;
-                  u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
-                  *reinterpret_cast<uint2*>(d2) = u;
-                } else {
-                  d2[0] = __float2bfloat16_rn(a.x);
-                  if (gcol + 1 < p.N) d2[1] = __float2bfloat16_rn(a.y);
-                  if (gcol + 2 < p.N) d2[2] = __float2bfloat16_rn(a.z);
-                  if (gcol + 3 < p.N) d2[3] = __float2bfloat16_rn(a.w);
+            } else {
+              // bf16: 2 lanes cover one 32-byte row segment, 16 rows per instruction
+              const int cq = (lane & 1) * 8;
+              const int gcol = col0 + cq;
+              float bv[8];
+#pragma unroll
+              for (int k = 0; k < 8; ++k) bv[k] = (p.bias != nullptr && gcol + k < p.N) ? __ldg(p.bias + gcol + k) : 0.f;
+              __nv_bfloat16* obase = reinterpret_cast<__nv_bfloat16*>(p.C) + out_off + gcol;
+#pragma unroll
+              for (int it = 0; it < 2; ++it) {
+                const int r = it * 16 + (lane >> 1);
+                const int grow = row_base + r;
+                const float4 a0 = *reinterpret_cast<const float4*>(stg + r * kStgPitch + cq);
+                const float4 a1 = *reinterpret_cast<const float4*>(stg + r * kStgPitch + cq + 4);
+                float f[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+                bool border = false;
+                if (p.img_w > 0) {
+                  const int q = grow % (p.img_w * p.img_h);
+                  const int yy = q / p.img_w, xx = q - yy * p.img_w;
+                  border = (yy == 0) | (yy == p.img_h - 1) | (xx == 0) | (xx == p.img_w - 1);
+                }
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                  float x = f[k] * p.alpha + bv[k];
+                  if (p.relu) x = fmaxf(x, 0.f);
+                  f[k] = border ? 0.f : x;
+                }
+                if (grow < p.M && gcol < p.N) {
+                  __nv_bfloat16* dst = obase + (long long)grow * ldo;
+                  if (gcol + 8 <= p.N && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+                    __nv_bfloat162 h0 = __floats2bfloat162_rn(f[0], f[1]), h1 = __floats2bfloat162_rn(f[2], f[3]);
+                    __nv_bfloat162 h2 = __floats2bfloat162_rn(f[4], f[5]), h3 = __floats2bfloat162_rn(f[6], f[7]);
+                    uint4 u;
+                    u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
+                    u.z = *reinterpret_cast<uint32_t*>(&h2); u.w = *reinterpret_cast<uint32_t*>(&h3);
+                    *reinterpret_cast<uint4*>(dst) = u;
+                  } else {
+#pragma unroll
+                    for (int k = 0; k < 8; ++k)
+                      if (gcol + k < p.N) dst[k] = __float2bfloat16_rn(f[k]);
+                  }
                 }
               }
             }
           }
-        } else {
-          // bf16 output: 4 lanes cover one 64-byte row segment, 8 rows per instruction
-          const int cq = (lane & 3) * 8;
-          const int gcol = col0 + cq;
-          float bv[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) bv[e] = (p.bias != nullptr && gcol + e < p.N) ? __ldg(p.bias + gcol + e) : 0.f;
-#pragma unroll
-          for (int it = 0; it < 4; ++it) {
-            const int r = it * 8 + (lane >> 2);
-            const int grow = row_base + r;
-            const float4 a0 = *reinterpret_cast<const float4*>(stg + r * kStgPitch + cq);
-            const float4 a1 = *reinterpret_cast<const float4*>(stg + r * kStgPitch + cq + 4);
-            float f[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-            bool border = false;
-            if (p.img_w > 0) {
-              const int q = grow % (p.img_w * p.img_h);
-              const int yy = q / p.img_w, xx = q - yy * p.img_w;
-              border = (yy == 0) | (yy == p.img_h - 1) | (xx == 0) | (xx == p.img_w - 1);
-            }
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              float x = f[e] * p.alpha + bv[e];
-              if (p.relu) x = fmaxf(x, 0.f);
-              f[e] = border ? 0.f : x;
-            }
-            if (grow < p.M && gcol < p.N) {
-              __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.C) + out_off + (long long)grow * ldo + gcol;
-              if (gcol + 8 <= p.N && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
-                __nv_bfloat162 h0 = __floats2bfloat162_rn(f[0], f[1]), h1 = __floats2bfloat162_rn(f[2], f[3]);
-                __nv_bfloat162 h2 = __floats2bfloat162_rn(f[4], f[5]), h3 = __floats2bfloat162_rn(f[6], f[7]);
-                uint4 u;
-                u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
-                u.z = *reinterpret_cast<uint32_t*>(&h2); u.w = *reinterpret_cast<uint32_t*>(&h3);
-                *reinterpret_cast<uint4*>(dst) = u;
-              } else {
-#pragma unroll
-                for (int e = 0; e < 8; ++e)
-                  if (gcol + e < p.N) dst[e] = __float2bfloat16_rn(f[e]);
-              }
-            }
-          }
+          __syncwarp();                                  // staging tile is reused by the next half chunk
         }
-        __syncwarp();                                    // staging tile is reused by the next chunk
       }
       tc_fence_before();
       __syncwarp();
