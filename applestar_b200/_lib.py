@@ -89,7 +89,7 @@ _SIGS = {
     'as_rl_loss_backward': (c_int, [POINTER(AsLossArgs), c_float, c_void_p]),
     'as_clip_adam_scratch_bytes': (c_int64, []),
     'as_clip_adam': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_float, c_float,
-                             c_float, c_float, c_float, c_int, c_void_p, c_void_p, c_void_p]),
+                             c_float, c_float, c_float, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
 }
 
 EXPORTS = tuple(_SIGS)

@@ -14,7 +14,7 @@ int loss_forward(const AsLossArgs&, cudaStream_t);
 int loss_backward(const AsLossArgs&, float, cudaStream_t);
 long long clip_adam_scratch_bytes();
 int clip_adam(float*, const float*, float*, float*, void*, long long, float, float, float, float, float, float, int,
-              float*, float*, cudaStream_t);
+              int*, float*, float*, cudaStream_t);
 int layer_norm_fwd(const float*, const float*, const float*, const float*, float*, void*, float*, long long, int, int,
                    cudaStream_t);
 long long layer_norm_bwd_scratch_floats(int);
@@ -267,10 +267,10 @@ int as_rl_loss_backward(const AsLossArgs* args, float grad_scale, void* stream) 
 int64_t as_clip_adam_scratch_bytes(void) { return as::clip_adam_scratch_bytes(); }
 
 int as_clip_adam(float* p, const float* g, float* m, float* v, void* shadow, int64_t n, float max_norm, float lr,
-                 float beta1, float beta2, float eps, float weight_decay, int step, float* scratch, float* norm_out,
-                 void* stream) {
-  return as::clip_adam(p, g, m, v, shadow, n, max_norm, lr, beta1, beta2, eps, weight_decay, step, scratch, norm_out,
-                       ST(stream));
+                 float beta1, float beta2, float eps, float weight_decay, int step, int* step_dev, float* scratch,
+                 float* norm_out, void* stream) {
+  return as::clip_adam(p, g, m, v, shadow, n, max_norm, lr, beta1, beta2, eps, weight_decay, step, step_dev, scratch,
+                       norm_out, ST(stream));
 }
 
 }  // extern "C"

@@ -94,7 +94,9 @@ int gumbel_argmax(const float* logit, const float* noise, long long* out, long l
 // pass 1: per-block partial sums of g^2 into scratch; pass 2: every block re-reduces the partials in a fixed order
 // (deterministic), derives clip = min(1, max_norm / (norm + 1e-6)) as torch.nn.utils.clip_grad_norm_ does, then
 // applies Adam (reference settings rl_learner.py:73-80) and refreshes the bf16 shadow of the weights.
-__global__ void sumsq_partial_kernel(const float* __restrict__ g, long long n, float* __restrict__ partial) {
+__global__ void sumsq_partial_kernel(const float* __restrict__ g, long long n, float* __restrict__ partial,
+                                     int* __restrict__ step_dev) {
+  if (step_dev != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *step_dev += 1;   // device-side step counter (graph replay)
   float s = 0.f;
   const long long stride = (long long)gridDim.x * blockDim.x;
   const long long n4 = n / 4;
@@ -118,8 +120,13 @@ __global__ void clip_adam_kernel(float* __restrict__ p, const float* __restrict_
                                  float* __restrict__ v, __nv_bfloat16* __restrict__ shadow, long long n,
                                  const float* __restrict__ partial, int n_partial, float max_norm, float lr,
                                  float beta1, float beta2, float eps, float wd, float bc1, float bc2,
-                                 float* __restrict__ norm_out) {
+                                 const int* __restrict__ step_dev, float* __restrict__ norm_out) {
   __shared__ float s_clip;
+  if (step_dev != nullptr) {                      // bias corrections from the device counter
+    const float t = (float)(*step_dev);
+    bc1 = 1.f - powf(beta1, t);
+    bc2 = 1.f - powf(beta2, t);
+  }
   if (threadIdx.x == 0) {
     float tot = 0.f;
     for (int i = 0; i < n_partial; ++i) tot += partial[i];
@@ -149,16 +156,17 @@ constexpr int kAdamBlocks = 148 * 4;
 long long clip_adam_scratch_bytes() { return kAdamBlocks * sizeof(float); }
 
 int clip_adam(float* p, const float* g, float* m, float* v, void* shadow, long long n, float max_norm, float lr,
-              float beta1, float beta2, float eps, float wd, int step, float* scratch, float* norm_out,
+              float beta1, float beta2, float eps, float wd, int step, int* step_dev, float* scratch, float* norm_out,
               cudaStream_t st) {
   if (n <= 0) return AS_OK;
-  if (!p || !g || !m || !v || !scratch || step <= 0) return AS_EINVAL;
+  if (!p || !g || !m || !v || !scratch || (step <= 0 && !step_dev)) return AS_EINVAL;
   if (reinterpret_cast<uintptr_t>(g) & 15) return AS_EALIGN;
-  sumsq_partial_kernel<<<kAdamBlocks, 256, 0, st>>>(g, n, scratch);
+  sumsq_partial_kernel<<<kAdamBlocks, 256, 0, st>>>(g, n, scratch, step_dev);
   AS_LAUNCH_CHECK();
-  const float bc1 = 1.f - powf(beta1, (float)step), bc2 = 1.f - powf(beta2, (float)step);
+  const float bc1 = 1.f - powf(beta1, (float)(step > 0 ? step : 1)), bc2 = 1.f - powf(beta2, (float)(step > 0 ? step : 1));
   clip_adam_kernel<<<kAdamBlocks, 256, 0, st>>>(p, g, m, v, reinterpret_cast<__nv_bfloat16*>(shadow), n, scratch,
-                                                kAdamBlocks, max_norm, lr, beta1, beta2, eps, wd, bc1, bc2, norm_out);
+                                                kAdamBlocks, max_norm, lr, beta1, beta2, eps, wd, bc1, bc2, step_dev,
+                                                norm_out);
   AS_LAUNCH_CHECK();
   return AS_OK;
 }

@@ -153,37 +153,128 @@ class FusedAdam:
         self.m = torch.zeros_like(flat.flat)
         self.v = torch.zeros_like(flat.flat)
         self.t = 0
+        self.t_dev = torch.zeros(1, dtype=torch.int32, device=flat.flat.device)
         self.scratch = torch.empty(_lib.lib().as_clip_adam_scratch_bytes() // 4, dtype=torch.float32,
                                    device=flat.flat.device)
         self.grad_norm = torch.zeros(1, dtype=torch.float32, device=flat.flat.device)
 
     def step(self):
+        """One optimizer step.  The step count lives on the device (incremented by the kernel) so that a captured
+        CUDA graph of the learner step replays with correct Adam bias corrections."""
         self.t += 1
         f = self.flat
         _lib.call('as_clip_adam', f.flat.data_ptr(), f.grad.data_ptr(), self.m.data_ptr(), self.v.data_ptr(),
                   0 if f.shadow is None else f.shadow.data_ptr(), f.numel, self.max_norm, self.lr, self.betas[0],
-                  self.betas[1], self.eps, self.wd, self.t, self.scratch.data_ptr(), self.grad_norm.data_ptr(),
-                  _lib.stream_ptr())
+                  self.betas[1], self.eps, self.wd, 0, self.t_dev.data_ptr(), self.scratch.data_ptr(),
+                  self.grad_norm.data_ptr(), _lib.stream_ptr())
         _lib.LAUNCHES += 1
         K.weights_changed()
 
 
-class LearnerStep:
-    """One data-parallel RL learner iteration on device-resident (or pinned-host) trajectories."""
+def _tree_copy_(dst, src):
+    """In-place copy of every tensor of `src` into the same-structured `dst` (H2D when src is pinned host memory)."""
+    if isinstance(dst, torch.Tensor):
+        dst.copy_(src, non_blocking=True)
+    elif isinstance(dst, dict):
+        for k in dst:
+            _tree_copy_(dst[k], src[k])
+    elif isinstance(dst, (list, tuple)):
+        for d, s_ in zip(dst, src):
+            _tree_copy_(d, s_)
 
-    def __init__(self, model, loss, lr=1e-5, max_norm=1.0, bucket_mb=25.0):
+
+def _tree_to(x, dev):
+    if isinstance(x, torch.Tensor):
+        return x.to(dev, non_blocking=True).clone() if x.device == dev else x.to(dev, non_blocking=True)
+    if isinstance(x, dict):
+        return {k: _tree_to(v, dev) for k, v in x.items()}
+    if isinstance(x, (list, tuple)):
+        return type(x)(_tree_to(v, dev) for v in x)
+    return x
+
+
+class LearnerStep:
+    """One data-parallel RL learner iteration: forward -> fused loss -> backward -> bucketed all-reduce -> fused
+    clip + Adam.  With `use_graph` the whole iteration is captured once per selected-units loop length into a CUDA
+    graph and replayed (fixed shapes, no host synchronisation inside), which removes the Python / launch overhead
+    of the ~1.4 k kernel launches of a step; inputs are copied into the graph's static buffers each call."""
+
+    def __init__(self, model, loss, lr=1e-5, max_norm=1.0, bucket_mb=25.0, use_graph=True):
         self.model = model
         self.loss = loss
         self.dist_model = DistModule(model, bucket_mb=bucket_mb)
         self.flat = self.dist_model.flat
         self.optimizer = FusedAdam(self.flat, lr=lr, max_norm=max_norm)
+        self.use_graph = use_graph and self.flat.flat.is_cuda
+        self._graphs = {}
+        self._pool = None
+        self.launches_per_step = None
 
-    def __call__(self, data):
+    # -- eager ----------------------------------------------------------------------------------------
+    def _run(self, data, defer_checks=False):
         self.flat.zero_grad()
         self.dist_model.prepare_backward()
-        out = self.model.rl_learner_forward(**data)
+        out = self.model.rl_learner_forward(**data, defer_checks=defer_checks)
         info = self.loss.compute_loss(out)
         info['total_loss'].backward()
         self.dist_model.sync_gradients()
         self.optimizer.step()
         return info
+
+    # -- graph ----------------------------------------------------------------------------------------
+    @staticmethod
+    def _key(data):
+        su = data.get('selected_units_max')
+        return None if su is None else (int(su), int(data['batch_size']), int(data['unroll_len']),
+                                        tuple(data['entity_info']['x'].shape))
+
+    def _capture(self, data, key):
+        dev = self.flat.flat.device
+        static = _tree_to(data, dev)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):                        # warm-up on a side stream (allocator, lazy inits)
+            for _ in range(2):
+                self._run(static, defer_checks=True)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        n0 = _lib.LAUNCHES
+        with torch.cuda.graph(graph, pool=self._pool):
+            info = self._run(static, defer_checks=True)
+        self.launches_per_step = _lib.LAUNCHES - n0
+        if self._pool is None:
+            self._pool = graph.pool()
+        entry = (graph, static, info)
+        self._graphs[key] = entry
+        return entry
+
+    def __call__(self, data):
+        key = self._key(data) if self.use_graph else None
+        if key is None:
+            return self._run(data)
+        entry = self._graphs.get(key)
+        if entry is None:
+            try:
+                entry = self._capture(data, key)
+            except Exception as exc:                          # e.g. a collective that cannot be captured
+                import warnings
+                warnings.warn('CUDA-graph capture of the learner step failed (%r); running eagerly' % (exc,))
+                torch.cuda.synchronize()
+                self.use_graph = False
+                return self._run(data)
+        graph, static, info = entry
+        if data is not static:
+            _tree_copy_(static, data)
+        graph.replay()
+        from .rl_loss import LossInfo
+        return LossInfo(self.loss, list(self.model.value_networks.keys()), info['total_loss'], info.stats_tensor())
+
+    def static_inputs(self, data):
+        """The graph's own input buffers for `data`'s shape (captures on first use): callers that fill them in place
+        (e.g. with H2D copies from pinned memory) skip one device-to-device copy per step."""
+        key = self._key(data)
+        if key is None or not self.use_graph:
+            return None
+        entry = self._graphs.get(key) or self._capture(data, key)
+        return entry[1]

@@ -606,16 +606,21 @@ class Model(nn.Module):
                            selected_units_num, behaviour_logp, teacher_logit, mask, reward, step, batch_size,
                            unroll_len, **kwargs):
         B, T = batch_size, unroll_len
-        ops.raise_if_negative_index()
+        if not kwargs.get('defer_checks', False):
+            ops.raise_if_negative_index()
         flat_action = {k: v.flatten(0, 1) for k, v in action_info.items()}
         lstm_input, ctx, base, ent, skip = self.encoder(spatial_info, entity_info, scalar_info, entity_num)
         hs = hidden_state[0][0].shape[-1]
         state0 = [tuple(s.view(-1, B, hs)[0] for s in layer) for layer in hidden_state]     # t=0 state only (A12)
         out, _ = self.core_lstm(lstm_input.view(-1, B, lstm_input.shape[-1]), state0)
         out = out.reshape(-1, out.shape[-1])
-        _, _, logits = self.policy.train_forward(out[:-B], ent[:-B], [None if m is None else m[:-B] for m in skip], ctx[:-B],
-                                                 entity_num[:-B], flat_action, selected_units_num.flatten(0, 1),
-                                                 self.cfg.temperature)
+        ops.SU_STEPS_HINT = kwargs.get('selected_units_max')       # optional host-side int: avoids a device sync
+        try:
+            _, _, logits = self.policy.train_forward(out[:-B], ent[:-B], [None if m is None else m[:-B] for m in skip],
+                                                     ctx[:-B], entity_num[:-B], flat_action,
+                                                     selected_units_num.flatten(0, 1), self.cfg.temperature)
+        finally:
+            ops.SU_STEPS_HINT = None
         critic_input = out.detach() if self.only_update_baseline else out
         values = {k: v(critic_input).view(T + 1, B) for k, v in self.value_networks.items()}
         logits = {k: v.view(T, B, *v.shape[1:]) for k, v in logits.items()}

@@ -244,13 +244,20 @@ def _su_step(head, ae, h, c):
     return out[0], h, c
 
 
+SU_STEPS_HINT = None     # host-side max(selected_units_num) supplied by the caller (e.g. the collate step, which has it
+                         # on the CPU for free); lets the learner step run without any device->host sync
+
+
 def selected_units_train(head, key, ae0, entity_num, selected_units, selected_units_num, temperature):
-    """Teacher-forced pointer loop (action_arg_head.py:168-216).  The loop length is the compile-time
-    maximum needed by the batch, read once (one host sync per call instead of 2-4 per step)."""
+    """Teacher-forced pointer loop (action_arg_head.py:168-216).  The loop length is the maximum needed by the
+    batch: taken from SU_STEPS_HINT when the caller knows it on the host, else read once from the device (one
+    sync per call instead of the reference's 2-4 per step).  Any length >= max(selected_units_num) gives identical
+    valid logits and embedding (ended rows keep a frozen selection)."""
     R, N1, D = key.shape
     dev = key.device
     ar = torch.arange(R, device=dev)
-    S = max(int(selected_units_num.max()), 1)
+    S = int(SU_STEPS_HINT) if SU_STEPS_HINT is not None else max(int(selected_units_num.max()), 1)
+    S = max(1, min(S, selected_units.shape[1]))
     h = key.new_zeros(R, 32)
     c = key.new_zeros(R, 32)
     lm = torch.arange(N1, device=dev).unsqueeze(0) < (entity_num + 1).unsqueeze(1)

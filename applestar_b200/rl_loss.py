@@ -102,7 +102,12 @@ class _FusedLoss(torch.autograd.Function):
                 sw[base + 6 + h] = -a.w_ent * a.hw_ent[h]
                 sw[base + 12 + h] = a.w_kl * a.hw_kl[h]
             sw[base + 18] = a.w_atkl
-        sw = sw.to(dev, non_blocking=True)
+        key = (str(dev), tuple(sw.tolist()))
+        cache = owner._sw_cache
+        if key not in cache:                       # uploaded once: no H2D copy inside a captured step
+            cache.clear()
+            cache[key] = sw.to(dev)
+        sw = cache[key]
         keep.append(sw)
         a.stat_weight = sw.data_ptr()
         partial = torch.empty((B, _lib.AS_LOSS_MAX_STATS), dtype=torch.float32, device=dev)
@@ -128,12 +133,76 @@ class _FusedLoss(torch.autograd.Function):
         return (None, None, None) + tuple(grads)
 
 
+class LossInfo(dict):
+    """The reference's log dict, filled lazily: `['total_loss']` is available at once (autograd tensor); the ~63
+    python floats are fetched with ONE device->host copy the first time any other key is read (e.g. when the
+    learner does `log_buffer.update(info)` after launching backward), so nothing blocks between forward and backward."""
+
+    def __init__(self, owner, fields, total, stats):
+        super().__init__()
+        dict.__setitem__(self, 'total_loss', total)
+        self._pending = (owner, fields, total, stats)
+        self._stats_keep = stats
+
+    def stats_tensor(self):
+        return self._stats_keep
+
+    def _fill(self):
+        if self._pending is not None:
+            owner, fields, total, stats = self._pending
+            self._pending = None
+            dict.update(self, owner._unpack(fields, total, stats.tolist()))   # the one D2H copy of the step
+
+    def __getitem__(self, k):
+        if k != 'total_loss':
+            self._fill()
+        return dict.__getitem__(self, k)
+
+    def get(self, k, default=None):
+        if k != 'total_loss':
+            self._fill()
+        return dict.get(self, k, default)
+
+    def __contains__(self, k):
+        self._fill()
+        return dict.__contains__(self, k)
+
+    def __iter__(self):
+        self._fill()
+        return dict.__iter__(self)
+
+    def __len__(self):
+        self._fill()
+        return dict.__len__(self)
+
+    def keys(self):
+        self._fill()
+        return dict.keys(self)
+
+    def items(self):
+        self._fill()
+        return dict.items(self)
+
+    def values(self):
+        self._fill()
+        return dict.values(self)
+
+    def __eq__(self, other):
+        self._fill()
+        return dict.__eq__(self, other)
+
+    def __repr__(self):
+        self._fill()
+        return dict.__repr__(self)
+
+
 class ReinforcementLoss:
     def __init__(self, learner_cfg, player_id):
         cfg = C.AttrDict(C.deep_merge(C.DEFAULT_LOSS_CONFIG, dict(learner_cfg or {})))
         self.cfg = cfg
         self._bind(player_id)
         self.only_update_value = False
+        self._sw_cache = {}
 
     def _bind(self, player_id=None):
         cfg = self.cfg
@@ -168,7 +237,9 @@ class ReinforcementLoss:
             raise RuntimeError('applestar_b200.ReinforcementLoss runs on CUDA tensors only (no CPU fallback)')
         values = [inputs['value'][f] for f in fields]
         total, out = _FusedLoss.apply(self, inputs, fields, *logits, *values)
-        s = out.tolist()                                          # the one D2H copy of the step's statistics
+        return LossInfo(self, fields, total, out)
+
+    def _unpack(self, fields, total, s):
         info = {}
         base = len(fields) * 10
         pg_hw, upgo_hw, ent_hw, kl_hw = (self.pg_head_weights, self.upgo_head_weights, self.entropy_head_weights,

@@ -187,6 +187,9 @@ def gen_trajectories(unroll_len, batch_size, n_entity=C.MAX_ENTITY_NUM, seed=123
         'teacher_logit': teacher_logit, 'mask': mask, 'reward': reward,
         'step': torch.rand((T, B), generator=g) * 20000.0,
         'batch_size': B, 'unroll_len': T, 'aux_type': B,
+        # host-side max(selected_units_num): the collate step has it on the CPU for free; lets the learner step run
+        # without a device->host sync (optional key, ignored by the reference through **kwargs)
+        'selected_units_max': max(int(sun.max()), 1),
     })
     return data
 

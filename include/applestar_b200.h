@@ -177,11 +177,13 @@ int as_rl_loss_backward(const AsLossArgs* args, float grad_scale, void* stream);
 /* Global-norm clip + Adam on flat fp32 buffers -- replaces GradClip 'pytorch_norm'
  * (ctools/torch_utils/grad_clip.py:140-143) + torch.optim.Adam.step (agent/default/rl_learner.py:73-80,125,132).
  * scratch: as_clip_adam_scratch_bytes() bytes of device memory.  shadow (bf16 copy of p) may be NULL.
- * norm_out (device float, may be NULL) receives the pre-clip gradient norm. */
+ * norm_out (device float, may be NULL) receives the pre-clip gradient norm.  step_dev (device int, may be NULL):
+ * when given, the kernel increments it and derives the bias corrections from it (so a captured CUDA graph of the
+ * step replays with the right step count); otherwise the host `step` (>= 1) is used. */
 int64_t as_clip_adam_scratch_bytes(void);
 int as_clip_adam(float* p, const float* g, float* m, float* v, void* shadow, int64_t n, float max_norm, float lr,
-                 float beta1, float beta2, float eps, float weight_decay, int step, float* scratch, float* norm_out,
-                 void* stream);
+                 float beta1, float beta2, float eps, float weight_decay, int step, int* step_dev, float* scratch,
+                 float* norm_out, void* stream);
 
 #ifdef __cplusplus
 }

@@ -94,13 +94,15 @@ def test_clip_adam_matches_torch():
     shadow = torch.empty(n, device='cuda', dtype=torch.bfloat16)
     scratch = torch.empty(_lib.lib().as_clip_adam_scratch_bytes() // 4, device='cuda')
     norm = torch.zeros(1, device='cuda')
+    step_dev = torch.full((1,), 2, dtype=torch.int32, device='cuda')     # third step uses the device-side counter
     for step in range(1, 4):
         g = torch.randn(n, generator=gen) * 0.05
         p_ref.grad = g.clone()
         tn = torch.nn.utils.clip_grad_norm_([p_ref], 1.0)
         opt.step()
         _lib.call('as_clip_adam', pc.data_ptr(), g.cuda().data_ptr(), m.data_ptr(), v.data_ptr(), shadow.data_ptr(), n,
-                  1.0, 1e-3, 0.0, 0.99, 1e-5, 0.0, step, scratch.data_ptr(), norm.data_ptr(), _lib.stream_ptr())
+                  1.0, 1e-3, 0.0, 0.99, 1e-5, 0.0, step if step < 3 else 0, 0 if step < 3 else step_dev.data_ptr(),
+                  scratch.data_ptr(), norm.data_ptr(), _lib.stream_ptr())
         assert abs(norm.item() - tn.item()) < 1e-4 * tn.item()
         assert (pc.cpu() - p_ref.detach()).abs().max().item() < 2e-6
     assert torch.equal(shadow.cpu(), pc.cpu().to(torch.bfloat16))
