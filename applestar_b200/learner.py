@@ -258,8 +258,10 @@ class LearnerStep:
             try:
                 entry = self._capture(data, key)
             except Exception as exc:                          # e.g. a collective that cannot be captured
+                import traceback
                 import warnings
-                warnings.warn('CUDA-graph capture of the learner step failed (%r); running eagerly' % (exc,))
+                warnings.warn('CUDA-graph capture of the learner step failed (%r); running eagerly\n%s'
+                              % (exc, ''.join(traceback.format_exc().splitlines(True)[-14:])))
                 torch.cuda.synchronize()
                 self.use_graph = False
                 return self._run(data)

@@ -260,8 +260,10 @@ def selected_units_train(head, key, ae0, entity_num, selected_units, selected_un
     S = max(1, min(S, selected_units.shape[1]))
     h = key.new_zeros(R, 32)
     c = key.new_zeros(R, 32)
-    lm = torch.arange(N1, device=dev).unsqueeze(0) < (entity_num + 1).unsqueeze(1)
-    lm[ar, entity_num] = False
+    # masks are built from one-hot tensors (no scalar index_put: keeps the loop free of host->device copies, so it
+    # can be captured in a CUDA graph)
+    end_oh = F.one_hot(entity_num, N1).bool()
+    lm = (torch.arange(N1, device=dev).unsqueeze(0) < (entity_num + 1).unsqueeze(1)) & ~end_oh
     one_hot = key.new_zeros(R, N1)
     end_flag = torch.zeros(R, dtype=torch.bool, device=dev)
     has_units = (selected_units_num != 0).unsqueeze(1)
@@ -269,10 +271,9 @@ def selected_units_train(head, key, ae0, entity_num, selected_units, selected_un
     logits = []
     for i in range(S):
         if i > 0:
-            lm = lm.clone()
             if i == 1:
-                lm[ar, entity_num] = True
-            lm[ar, selected_units[:, i - 1]] = False
+                lm = lm | end_oh                                     # end flag selectable from the second pick on
+            lm = lm & ~F.one_hot(selected_units[:, i - 1], N1).bool()   # mask the unit picked at the previous step
         q, h, c = _su_step(head, ae, h, c)
         logits.append(torch.einsum('rk,rnk->rn', q, key).masked_fill(~lm, -1e9))
         end_flag = end_flag | (selected_units[:, i] == entity_num)
