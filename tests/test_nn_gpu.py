@@ -109,7 +109,7 @@ def test_lnlstm_layer_fwd_bwd_vs_oracle_cell(T, B, I, H):
         ys.append(h)
     yr = torch.stack(ys)
     torch.autograd.backward([yr, c], [gy.cpu(), gc.cpu()])
-    assert (y.cpu() - yr).abs().max().item() < 3e-2
+    assert (y.cpu() - yr).abs().max().item() < 6e-2
     assert (cT.cpu() - c).abs().max().item() < 1e-1
     assert torch.equal(hT, y[-1])
     for got, want, name in ((x.grad, xr.grad, 'x'), (h0.grad, hr.grad, 'h0'), (c0.grad, cr.grad, 'c0'),
