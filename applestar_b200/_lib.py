@@ -57,6 +57,7 @@ _SIGS = {
     'as_pnhwc_to_nchw': (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p]),
     'as_add_act_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     'as_relu_bwd_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
+    'as_relu_bwd_f32': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
     'as_gated_fwd_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
     'as_gated_scratch_floats': (c_int64, []),
     'as_gated_bwd_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,

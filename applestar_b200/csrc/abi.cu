@@ -9,6 +9,7 @@ int scatter_fwd(const float*, const void*, const void*, int, const long long*, f
 int scatter_bwd(const float*, const void*, const void*, int, const long long*, float*, long long, int, int, int, int,
                 cudaStream_t);
 int cast_f32_bf16(const float*, void*, long long, cudaStream_t);
+int relu_bwd_f32(const float*, const float*, float*, long long, cudaStream_t);
 int gumbel_argmax(const float*, const float*, long long*, long long, int, cudaStream_t);
 int loss_forward(const AsLossArgs&, cudaStream_t);
 int loss_backward(const AsLossArgs&, float, cudaStream_t);
@@ -248,6 +249,10 @@ int as_entity_features(const void* const* data, const int* kind, const int* num,
 
 int as_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream) {
   return as::cast_f32_bf16(src, dst, n, ST(stream));
+}
+
+int as_relu_bwd_f32(const float* dy, const float* y, float* dz, int64_t n, void* stream) {
+  return as::relu_bwd_f32(dy, y, dz, n, ST(stream));
 }
 
 int as_gumbel_argmax(const float* logit, const float* noise, int64_t* out, int64_t rows, int K, void* stream) {

@@ -32,6 +32,32 @@ int cast_f32_bf16(const float* src, void* dst, long long n, cudaStream_t st) {
   return AS_OK;
 }
 
+// ------------------------------------------------------------------ ReLU backward on fp32 rows: dz = dy * (y > 0)
+__global__ void relu_bwd_f32_kernel(const float* __restrict__ dy, const float* __restrict__ y, float* __restrict__ dz,
+                                    long long n) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long n4 = n / 4;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    const float4 d = __ldg(reinterpret_cast<const float4*>(dy) + i);
+    const float4 v = __ldg(reinterpret_cast<const float4*>(y) + i);
+    reinterpret_cast<float4*>(dz)[i] = make_float4(v.x > 0.f ? d.x : 0.f, v.y > 0.f ? d.y : 0.f, v.z > 0.f ? d.z : 0.f,
+                                                   v.w > 0.f ? d.w : 0.f);
+  }
+  for (long long i = n4 * 4 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    dz[i] = y[i] > 0.f ? dy[i] : 0.f;
+}
+
+int relu_bwd_f32(const float* dy, const float* y, float* dz, long long n, cudaStream_t st) {
+  if (n <= 0) return AS_OK;
+  if (!dy || !y || !dz) return AS_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(dz)) & 15) return AS_EALIGN;
+  long long blocks = (n / 4 + 255) / 256;
+  const int grid = (int)(blocks < 148LL * 8 ? (blocks > 0 ? blocks : 1) : 148LL * 8);
+  relu_bwd_f32_kernel<<<grid, 256, 0, st>>>(dy, y, dz, n);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
 // ------------------------------------------------------------------ Gumbel-max sampling
 // out[r] = argmax_k (logit[r,k] + noise[r,k]) in fp32, lowest index on ties (torch.argmax semantics).
 template <int THREADS_PER_ROW>

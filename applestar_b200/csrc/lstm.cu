@@ -30,26 +30,68 @@ __device__ __forceinline__ void block_sum2(float& a, float& b, float* red) {
 }
 
 // out[j] = sum_k W[j][k] * v[k], W bf16 row-major [rows][cols] (cols % 8 == 0), v fp32 in shared memory.
-// One warp per output row, lanes split the row in 16-byte chunks (coalesced), shuffle reduction.
-__device__ __forceinline__ void matvec_bf16(const __nv_bfloat16* __restrict__ Wm, const float* v, float* out, int rows,
+// One warp per group of kRowsPerIter (2-8) output rows: lanes split each row in 16-byte chunks (coalesced); the loads of
+// all rows of the group are issued before any is consumed, so ~kRowsPerIter * cols / 256 L2 requests are in flight
+// per lane instead of one (the recurrence is latency-bound: W_hh streams from L2 every step).
+
+__device__ __forceinline__ float dot8(const uint4& q, const float* vv) {
+  const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&q);
+  float acc = 0.f;
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const float2 f = __bfloat1622float2(h2[e]);
+    acc += f.x * vv[2 * e] + f.y * vv[2 * e + 1];
+  }
+  return acc;
+}
+
+template <int CHUNKS_PER_LANE, int kRowsPerIter>
+__device__ __forceinline__ void matvec_rows(const __nv_bfloat16* __restrict__ Wm, const float* v, float* out, int rows,
                                             int cols) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int chunks = cols >> 3;
-  for (int j = warp; j < rows; j += kLstmWarps) {
-    const uint4* wr = reinterpret_cast<const uint4*>(Wm + (long long)j * cols);
-    float acc = 0.f;
-    for (int ch = lane; ch < chunks; ch += 32) {
-      const uint4 q = __ldg(wr + ch);
-      const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&q);
-      const float* vv = v + ch * 8;
+  for (int j0 = warp * kRowsPerIter; j0 < rows; j0 += kLstmWarps * kRowsPerIter) {
+    uint4 q[kRowsPerIter][CHUNKS_PER_LANE];
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const float2 f = __bfloat1622float2(h2[e]);
-        acc += f.x * vv[2 * e] + f.y * vv[2 * e + 1];
+    for (int r = 0; r < kRowsPerIter; ++r) {
+      const uint4* wr = reinterpret_cast<const uint4*>(Wm + (long long)(j0 + r) * cols);
+#pragma unroll
+      for (int c = 0; c < CHUNKS_PER_LANE; ++c) {
+        const int ch = lane + c * 32;
+        q[r][c] = (j0 + r < rows && ch < chunks) ? __ldg(wr + ch) : make_uint4(0, 0, 0, 0);
       }
     }
-    acc = warp_sum(acc);
-    if (lane == 0) out[j] = acc;
+#pragma unroll
+    for (int r = 0; r < kRowsPerIter; ++r) {
+      float acc = 0.f;
+#pragma unroll
+      for (int c = 0; c < CHUNKS_PER_LANE; ++c) {
+        const int ch = lane + c * 32;
+        if (ch < chunks) acc += dot8(q[r][c], v + ch * 8);
+      }
+      acc = warp_sum(acc);
+      if (lane == 0 && j0 + r < rows) out[j0 + r] = acc;
+    }
+  }
+}
+
+__device__ __forceinline__ void matvec_bf16(const __nv_bfloat16* __restrict__ Wm, const float* v, float* out, int rows,
+                                            int cols) {
+  const int per_lane = ((cols >> 3) + 31) / 32;
+  if (per_lane <= 1) matvec_rows<1, 8>(Wm, v, out, rows, cols);
+  else if (per_lane <= 2) matvec_rows<2, 6>(Wm, v, out, rows, cols);
+  else if (per_lane <= 6) matvec_rows<6, 2>(Wm, v, out, rows, cols);
+  else {
+    // generic (wide rows): one row at a time
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int chunks = cols >> 3;
+    for (int j = warp; j < rows; j += kLstmWarps) {
+      const uint4* wr = reinterpret_cast<const uint4*>(Wm + (long long)j * cols);
+      float acc = 0.f;
+      for (int ch = lane; ch < chunks; ch += 32) acc += dot8(__ldg(wr + ch), v + ch * 8);
+      acc = warp_sum(acc);
+      if (lane == 0) out[j] = acc;
+    }
   }
 }
 

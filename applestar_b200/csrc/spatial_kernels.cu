@@ -397,64 +397,101 @@ int loc_cat_bwd(const void* dcat, const float* emb, const void* skip, float* dem
 }
 
 // ------------------------------------------------------------------------------------------ final 3x3 conv, 32 -> 1
-// y[r,y,x] = b + sum_{tap,c} w[tap][c] * in[r, y+ky, x+kx, c]   (in padded NHWC bf16, C = 32; y fp32 unpadded = logits)
-// One warp per output pixel group: lane = channel, 9 taps in registers, warp-shuffle reduction over channels.
-__global__ void conv_c32_1_fwd_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict__ w,
-                                      const float* __restrict__ bias, float* __restrict__ out, long long R, int H, int W,
-                                      float inv_temp) {
-  const int lane = threadIdx.x & 31;
-  float wk[9];
+// y[r,y,x] = (b + sum_{tap,c} w[tap][c] * in[r, y+ky, x+kx, c]) / T   (in padded NHWC bf16, C = 32; y fp32 unpadded =
+// the location logits).  Thread per output pixel: each tap is 64 contiguous bytes per thread (four 16-byte loads),
+// neighbouring threads read neighbouring pixels; weights are broadcast from shared memory.
+__device__ __forceinline__ void unpack8(const uint4& q, float* f) {
+  const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&q);
 #pragma unroll
-  for (int t = 0; t < 9; ++t) wk[t] = w[t * 32 + lane];
+  for (int e = 0; e < 4; ++e) {
+    const float2 v = __bfloat1622float2(h2[e]);
+    f[2 * e] = v.x; f[2 * e + 1] = v.y;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+conv_c32_1_fwd_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict__ w, const float* __restrict__ bias,
+                      float* __restrict__ out, long long R, int H, int W, float inv_temp) {
+  __shared__ __align__(16) float sw[288];
+  for (int i = threadIdx.x; i < 288; i += blockDim.x) sw[i] = w[i];
+  __syncthreads();
   const float b = bias ? bias[0] : 0.f;
   const long long total = R * (long long)H * W;
-  const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
-  for (long long p = warp_global; p < total; p += warps_total) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += stride) {
     const int x = (int)(p % W);
     const long long q = p / W;
     const int y = (int)(q % H);
     const long long r = q / H;
-    const __nv_bfloat16* base = in + ((r * (H + 2) + y) * (long long)(W + 2) + x) * 32 + lane;
+    const __nv_bfloat16* base = in + ((r * (H + 2) + y) * (long long)(W + 2) + x) * 32;
     float acc = 0.f;
 #pragma unroll
-    for (int ky = 0; ky < 3; ++ky)
+    for (int ky = 0; ky < 3; ++ky) {
 #pragma unroll
-      for (int kx = 0; kx < 3; ++kx) acc += wk[ky * 3 + kx] * bf2f(base[((long long)ky * (W + 2) + kx) * 32]);
-    acc = warp_sum(acc);
-    if (lane == 0) out[p] = (acc + b) * inv_temp;
+      for (int kx = 0; kx < 3; ++kx) {
+        const uint4* src = reinterpret_cast<const uint4*>(base + ((long long)ky * (W + 2) + kx) * 32);
+        const float* wt = sw + (ky * 3 + kx) * 32;
+#pragma unroll
+        for (int c4 = 0; c4 < 4; ++c4) {
+          float f[8];
+          unpack8(__ldg(src + c4), f);
+          const float4 w0 = *reinterpret_cast<const float4*>(wt + c4 * 8);
+          const float4 w1 = *reinterpret_cast<const float4*>(wt + c4 * 8 + 4);
+          acc += f[0] * w0.x + f[1] * w0.y + f[2] * w0.z + f[3] * w0.w + f[4] * w1.x + f[5] * w1.y + f[6] * w1.z + f[7] * w1.w;
+        }
+      }
+    }
+    out[p] = (acc + b) * inv_temp;
   }
 }
-// din[r,yy,xx,c] = sum_tap w[tap][c] * dy[r, yy-ky, xx-kx]  (interior; border 0), dy fp32 unpadded [R,H,W]
-__global__ void conv_c32_1_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w,
-                                        __nv_bfloat16* __restrict__ din, long long R, int H, int W, float inv_temp) {
-  const int lane = threadIdx.x & 31;
-  float wk[9];
-#pragma unroll
-  for (int t = 0; t < 9; ++t) wk[t] = w[t * 32 + lane] * inv_temp;
+
+// din[r,yy,xx,c] = sum_tap w[tap][c] * dy[r, yy-ky, xx-kx] / T  (interior; border 0), dy fp32 unpadded [R,H,W].
+// Thread per input pixel, 32 channel accumulators in registers, 64 contiguous bytes written per thread.
+__global__ void __launch_bounds__(256)
+conv_c32_1_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w, __nv_bfloat16* __restrict__ din,
+                        long long R, int H, int W, float inv_temp) {
+  __shared__ __align__(16) float sw[288];
+  for (int i = threadIdx.x; i < 288; i += blockDim.x) sw[i] = w[i] * inv_temp;
+  __syncthreads();
   const long long total = R * (long long)(H + 2) * (W + 2);
-  const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
-  for (long long p = warp_global; p < total; p += warps_total) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += stride) {
     const int xx = (int)(p % (W + 2));
     const long long q = p / (W + 2);
     const int yy = (int)(q % (H + 2));
     const long long r = q / (H + 2);
-    float acc = 0.f;
+    float acc[32];
+#pragma unroll
+    for (int c = 0; c < 32; ++c) acc[c] = 0.f;
     if (xx >= 1 && xx <= W && yy >= 1 && yy <= H) {
 #pragma unroll
       for (int ky = 0; ky < 3; ++ky) {
-        const int oy = yy - ky;                 // output row (unpadded) that read this input row with tap ky
-        if (oy < 0 || oy >= H) continue;
+        const int oy = yy - ky;
 #pragma unroll
         for (int kx = 0; kx < 3; ++kx) {
           const int ox = xx - kx;
-          if (ox < 0 || ox >= W) continue;
-          acc += wk[ky * 3 + kx] * __ldg(dy + (r * H + oy) * (long long)W + ox);
+          if (oy >= 0 && oy < H && ox >= 0 && ox < W) {
+            const float g = __ldg(dy + (r * H + oy) * (long long)W + ox);
+            const float* wt = sw + (ky * 3 + kx) * 32;
+#pragma unroll
+            for (int c4 = 0; c4 < 8; ++c4) {
+              const float4 wv = *reinterpret_cast<const float4*>(wt + c4 * 4);
+              acc[c4 * 4] += g * wv.x; acc[c4 * 4 + 1] += g * wv.y; acc[c4 * 4 + 2] += g * wv.z; acc[c4 * 4 + 3] += g * wv.w;
+            }
+          }
         }
       }
     }
-    din[p * 32 + lane] = f2bf(acc);
+    uint4* dst = reinterpret_cast<uint4*>(din + p * 32);
+#pragma unroll
+    for (int c4 = 0; c4 < 4; ++c4) {
+      __nv_bfloat162 h0 = __floats2bfloat162_rn(acc[c4 * 8], acc[c4 * 8 + 1]), h1 = __floats2bfloat162_rn(acc[c4 * 8 + 2], acc[c4 * 8 + 3]);
+      __nv_bfloat162 h2 = __floats2bfloat162_rn(acc[c4 * 8 + 4], acc[c4 * 8 + 5]), h3 = __floats2bfloat162_rn(acc[c4 * 8 + 6], acc[c4 * 8 + 7]);
+      uint4 u;
+      u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
+      u.z = *reinterpret_cast<uint32_t*>(&h2); u.w = *reinterpret_cast<uint32_t*>(&h3);
+      dst[c4] = u;
+    }
   }
 }
 // dw[tap][c] = sum_p dy[p] in[p+tap][c];  db = sum dy  -> per-block partials [blocks][9*32+1]
@@ -467,6 +504,7 @@ __global__ void conv_c32_1_wgrad_kernel(const float* __restrict__ dy, const __nv
   const long long total = R * (long long)H * W;
   const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
+#pragma unroll 4
   for (long long p = warp_global; p < total; p += warps_total) {
     const int x = (int)(p % W);
     const long long q = p / W;
@@ -507,7 +545,7 @@ int conv_c32_1_fwd(const void* in, const float* w, const float* bias, float* out
                    cudaStream_t st) {
   if (R <= 0) return AS_OK;
   if (!in || !w || !out) return AS_EINVAL;
-  conv_c32_1_fwd_kernel<<<148 * 8, 256, 0, st>>>((const __nv_bfloat16*)in, w, bias, out, R, H, W, inv_temp);
+  conv_c32_1_fwd_kernel<<<ew_grid(R * (long long)H * W, 1), 256, 0, st>>>((const __nv_bfloat16*)in, w, bias, out, R, H, W, inv_temp);
   AS_LAUNCH_CHECK();
   return AS_OK;
 }
@@ -515,7 +553,7 @@ int conv_c32_1_bwd(const float* dy, const void* in, const float* w, void* din, f
                    long long R, int H, int W, float inv_temp, cudaStream_t st) {
   if (R <= 0) return AS_OK;
   if (!dy || !in || !w || !din || !dw || !scratch) return AS_EINVAL;
-  conv_c32_1_dgrad_kernel<<<148 * 8, 256, 0, st>>>(dy, w, (__nv_bfloat16*)din, R, H, W, inv_temp);
+  conv_c32_1_dgrad_kernel<<<ew_grid(R * (long long)(H + 2) * (W + 2), 1), 256, 0, st>>>(dy, w, (__nv_bfloat16*)din, R, H, W, inv_temp);
   AS_LAUNCH_CHECK();
   conv_c32_1_wgrad_kernel<<<kC321Blocks, 256, 0, st>>>(dy, (const __nv_bfloat16*)in, scratch, R, H, W, inv_temp);
   AS_LAUNCH_CHECK();

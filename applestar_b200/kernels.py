@@ -132,7 +132,7 @@ class LinearFn(torch.autograd.Function):
             dy = dy32 if dy32 is not None else dy16
         dy2 = dy.reshape(-1, N)
         if ctx.relu:
-            dy2 = dy2 * (y > 0)
+            dy2 = relu_backward(dy2, y)
         M = dy2.shape[0]
         dy16b = to_bf16(dy2)                      # [M, N8]
         dx = dw = db = None
@@ -150,6 +150,23 @@ class LinearFn(torch.autograd.Function):
         if ctx.has_bias and ctx.needs_input_grad[2]:
             db = dy2.sum(dim=0, dtype=torch.float32)
         return dx, dw, db, None, None, None
+
+
+def relu_backward(dy, y):
+    """dy * (y > 0) with one kernel (bf16 or fp32 pair); mixed dtypes fall back to promoting dy."""
+    dy, y = dy.contiguous(), y.contiguous()
+    if dy.dtype != y.dtype:
+        dy = dy.to(y.dtype) if y.dtype == torch.float32 else dy
+        y = y if dy.dtype == y.dtype else y.float()
+    n = dy.numel()
+    dz = torch.empty_like(dy)
+    if dy.dtype == torch.bfloat16 and n % 8 == 0:
+        _lib.call('as_relu_bwd_bf16', dy.data_ptr(), y.data_ptr(), dz.data_ptr(), n, _lib.stream_ptr())
+    elif dy.dtype == torch.float32:
+        _lib.call('as_relu_bwd_f32', dy.data_ptr(), y.data_ptr(), dz.data_ptr(), n, _lib.stream_ptr())
+    else:
+        return dy * (y > 0)
+    return dz
 
 
 def linear(x, weight, bias, relu=False, out_bf16=False):

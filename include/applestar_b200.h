@@ -81,6 +81,7 @@ int as_pnhwc_to_nchw(const void* src, float* dst, int64_t R, int C, int Cp, int 
  * y = relu(a + b) (ResBlock tail, res_block.py:64); as_relu_bwd_bf16: dz = dy * (y > 0). */
 int as_add_act_bf16(const void* a, const void* b, void* y, int64_t n, int mode, void* stream);
 int as_relu_bwd_bf16(const void* dy, const void* y, void* dz, int64_t n, void* stream);
+int as_relu_bwd_f32(const float* dy, const float* y, float* dz, int64_t n, void* stream);
 
 /* GatedResBlock tail y = relu(tanh(r * sigmoid(g)) * UpdateSP + x) (module_utils.py:227-229), bf16 maps, fp32 math.
  * Backward also yields d UpdateSP (device float) through `scratch` of as_gated_scratch_floats() floats. */
