@@ -48,6 +48,12 @@ int lnlstm_fwd(const float*, const float*, const float*, const void*, const floa
 int lnlstm_bwd(const float*, const float*, const float*, const float*, const float*, const float*, const float*,
                const float*, const void*, const float*, const float*, const float*, const float*, const float*,
                const float*, const float*, float*, float*, float*, float*, float*, int, int, int, cudaStream_t);
+int spatial_features(const void* const*, const void* const*, int, const float*, void*, long long, int, int, int,
+                     cudaStream_t);
+int scatter_bwd_pnhwc(const void*, const void*, const void*, int, const long long*, float*, long long, int, int, int,
+                      int, int, int, cudaStream_t);
+int maxpool2_fwd(const void*, void*, long long, int, int, int, cudaStream_t);
+int maxpool2_bwd(const void*, const void*, void*, long long, int, int, int, cudaStream_t);
 }  // namespace as
 
 #define ST(s) reinterpret_cast<cudaStream_t>(s)
@@ -200,6 +206,23 @@ int as_conv_c32_1_bwd(const float* dlogits, const void* in, const float* w, void
 int64_t as_colsum_scratch_floats(int C) { return as::colsum_scratch_floats(C); }
 int as_colsum_bf16(const void* x, float* out, float* scratch, int64_t rows, int C, void* stream) {
   return as::colsum_bf16(x, out, scratch, rows, C, ST(stream));
+}
+
+int as_spatial_features(const void* const* planes, const void* const* effects, int n_eff, const float* scatter_map,
+                        void* out, int64_t R, int H, int W, int Cs, void* stream) {
+  return as::spatial_features(planes, effects, n_eff, scatter_map, out, R, H, W, Cs, ST(stream));
+}
+int as_scatter_connection_bwd_pnhwc(const void* d_feat, const void* xs, const void* ys, int idx_bytes,
+                                    const int64_t* entity_num, float* d_emb, int64_t R, int N, int D, int H, int W,
+                                    int Cp, int ch0, void* stream) {
+  return as::scatter_bwd_pnhwc(d_feat, xs, ys, idx_bytes, reinterpret_cast<const long long*>(entity_num), d_emb, R, N,
+                               D, H, W, Cp, ch0, ST(stream));
+}
+int as_maxpool2_fwd_bf16(const void* in, void* out, int64_t R, int H, int W, int C, void* stream) {
+  return as::maxpool2_fwd(in, out, R, H, W, C, ST(stream));
+}
+int as_maxpool2_bwd_bf16(const void* in, const void* dout, void* din, int64_t R, int H, int W, int C, void* stream) {
+  return as::maxpool2_bwd(in, dout, din, R, H, W, C, ST(stream));
 }
 
 int as_layer_norm_fwd(const float* x, const float* res, const float* gamma, const float* beta, float* y32, void* y16,

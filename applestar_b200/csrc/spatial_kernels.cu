@@ -612,3 +612,268 @@ int colsum_bf16(const void* x, float* out, float* scratch, long long rows, int C
 }
 
 }  // namespace as
+
+namespace as {
+
+// ------------------------------------------------------------------------------------------ spatial input features
+// The 56-channel spatial input of the reference (spatial_encoder.py:52-71, channel order App. A8: height/256,
+// visibility(4), creep(2), player_relative(5), alerts(2), pathable(2), buildable(2), 6 effect planes, 32 scatter
+// channels) written once as a zero-padded NHWC bf16 map with Cp = 64 channels, ready for the 1x1 project GEMM.
+// CTA = (observation, band of rows); the effect index lists become a per-band bitmap in shared memory (a zero
+// padded list sets pixel 0, App. A7).  Thread = pixel: 128 contiguous bytes written per thread.
+struct SpatialPlanes {
+  const uint8_t* plane[7];     // height_map, visibility_map, creep, player_relative, alerts, pathable, buildable [R,H,W]
+  const int16_t* effect[6];    // [R, n_eff] flat pixel ids
+  int n_eff;
+};
+
+constexpr int kFeatBand = 8;   // rows per CTA
+
+__global__ void __launch_bounds__(256)
+spatial_features_kernel(const SpatialPlanes sp, const float* __restrict__ scatter_map, __nv_bfloat16* __restrict__ out,
+                        int H, int W, int Cs) {
+  __shared__ unsigned int effbits[kFeatBand * 256];      // one byte-sized bit set per pixel, W <= 1024/… (W*band <= 1024*… checked on host)
+  const int r = blockIdx.x;
+  const int band = blockIdx.y;                            // padded row band: rows [band*kFeatBand, +kFeatBand) of H+2
+  const int HW = H * W;
+  const int n_pix = kFeatBand * W;
+  for (int i = threadIdx.x; i < (n_pix + 3) / 4; i += blockDim.x) effbits[i] = 0u;
+  __syncthreads();
+  const int y_lo = band * kFeatBand - 1;                  // first interior row (unpadded coords) of the band
+  for (int e = 0; e < 6; ++e) {
+    const int16_t* ids = sp.effect[e] + (long long)r * sp.n_eff;
+    for (int i = threadIdx.x; i < sp.n_eff; i += blockDim.x) {
+      const int id = (int)ids[i];
+      if (id < 0 || id >= HW) continue;
+      const int y = id / W - y_lo;
+      if (y >= 0 && y < kFeatBand) {
+        const int local = y * W + id % W;
+        atomicOr(&effbits[local >> 2], (1u << e) << ((local & 3) * 8));
+      }
+    }
+  }
+  __syncthreads();
+  const int Cp = 64;
+  for (int i = threadIdx.x; i < kFeatBand * (W + 2); i += blockDim.x) {
+    const int yy = band * kFeatBand + i / (W + 2);
+    const int xx = i % (W + 2);
+    if (yy >= H + 2) continue;
+    uint4* dst = reinterpret_cast<uint4*>(out + (((long long)r * (H + 2) + yy) * (W + 2) + xx) * Cp);
+    if (yy == 0 || yy == H + 1 || xx == 0 || xx == W + 1) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) dst[q] = make_uint4(0, 0, 0, 0);
+      continue;
+    }
+    const int y = yy - 1, x = xx - 1;
+    const long long pix = ((long long)r * H + y) * W + x;
+    float f[64];
+#pragma unroll
+    for (int c = 0; c < 64; ++c) f[c] = 0.f;
+    f[0] = (float)sp.plane[0][pix] * (1.f / 256.f);
+    {
+      int v;
+      v = sp.plane[1][pix]; v = v > 3 ? 3 : v;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) f[1 + k] = (v == k) ? 1.f : 0.f;
+      v = sp.plane[2][pix]; v = v > 1 ? 1 : v;
+      f[5] = (v == 0) ? 1.f : 0.f; f[6] = (v == 1) ? 1.f : 0.f;
+      v = sp.plane[3][pix]; v = v > 4 ? 4 : v;
+#pragma unroll
+      for (int k = 0; k < 5; ++k) f[7 + k] = (v == k) ? 1.f : 0.f;
+      v = sp.plane[4][pix]; v = v > 1 ? 1 : v;
+      f[12] = (v == 0) ? 1.f : 0.f; f[13] = (v == 1) ? 1.f : 0.f;
+      v = sp.plane[5][pix]; v = v > 1 ? 1 : v;
+      f[14] = (v == 0) ? 1.f : 0.f; f[15] = (v == 1) ? 1.f : 0.f;
+      v = sp.plane[6][pix]; v = v > 1 ? 1 : v;
+      f[16] = (v == 0) ? 1.f : 0.f; f[17] = (v == 1) ? 1.f : 0.f;
+    }
+    {
+      const int local = (y - y_lo) * W + x;
+      const unsigned int bits = (effbits[local >> 2] >> ((local & 3) * 8)) & 0xFFu;
+#pragma unroll
+      for (int e = 0; e < 6; ++e) f[18 + e] = ((bits >> e) & 1u) ? 1.f : 0.f;
+    }
+    const float* sm = scatter_map + (long long)r * Cs * HW + (long long)y * W + x;
+#pragma unroll
+    for (int k = 0; k < 32; ++k) f[24 + k] = (k < Cs) ? __ldg(sm + (long long)k * HW) : 0.f;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      __nv_bfloat162 h0 = __floats2bfloat162_rn(f[8 * q], f[8 * q + 1]), h1 = __floats2bfloat162_rn(f[8 * q + 2], f[8 * q + 3]);
+      __nv_bfloat162 h2 = __floats2bfloat162_rn(f[8 * q + 4], f[8 * q + 5]), h3 = __floats2bfloat162_rn(f[8 * q + 6], f[8 * q + 7]);
+      uint4 u;
+      u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
+      u.z = *reinterpret_cast<uint32_t*>(&h2); u.w = *reinterpret_cast<uint32_t*>(&h3);
+      dst[q] = u;
+    }
+  }
+}
+
+int spatial_features(const void* const* planes, const void* const* effects, int n_eff, const float* scatter_map,
+                     void* out, long long R, int H, int W, int Cs, cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (H <= 0 || W <= 0 || W > 256 || Cs != 32 || n_eff <= 0) return AS_ESIZE;
+  if (!planes || !effects || !scatter_map || !out) return AS_EINVAL;
+  SpatialPlanes sp;
+  for (int i = 0; i < 7; ++i) { sp.plane[i] = reinterpret_cast<const uint8_t*>(planes[i]); if (!planes[i]) return AS_EINVAL; }
+  for (int i = 0; i < 6; ++i) { sp.effect[i] = reinterpret_cast<const int16_t*>(effects[i]); if (!effects[i]) return AS_EINVAL; }
+  sp.n_eff = n_eff;
+  dim3 grid((unsigned)R, (unsigned)((H + 2 + kFeatBand - 1) / kFeatBand));
+  spatial_features_kernel<<<grid, 256, 0, st>>>(sp, scatter_map, reinterpret_cast<__nv_bfloat16*>(out), H, W, Cs);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+// ScatterConnection backward straight from the gradient of the padded NHWC feature map:
+// d_emb[r,e,d] = e < entity_num[r] ? d_feat[r, y(e)+1, x(e)+1, ch0 + d] : 0
+template <typename IdxT>
+__global__ void scatter_bwd_pnhwc_kernel(const __nv_bfloat16* __restrict__ dfeat, const IdxT* __restrict__ xs,
+                                         const IdxT* __restrict__ ys, const long long* __restrict__ entity_num,
+                                         float* __restrict__ demb, long long R, int N, int D, int H, int W, int Cp,
+                                         int ch0) {
+  const long long total = R * N * (long long)D;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int d = (int)(i % D);
+    const long long re = i / D;
+    const int e = (int)(re % N);
+    const long long r = re / N;
+    const long long en = entity_num ? entity_num[r] : (long long)N;
+    float g = 0.f;
+    if ((long long)e < en) {
+      long long x = (long long)xs[re], y = (long long)ys[re];
+      x = x < 0 ? 0 : (x > W - 1 ? W - 1 : x);
+      y = y < 0 ? 0 : (y > H - 1 ? H - 1 : y);
+      g = bf2f(dfeat[((r * (H + 2) + y + 1) * (long long)(W + 2) + x + 1) * Cp + ch0 + d]);
+    }
+    demb[i] = g;
+  }
+}
+
+int scatter_bwd_pnhwc(const void* dfeat, const void* xs, const void* ys, int idx_bytes, const long long* en, float* demb,
+                      long long R, int N, int D, int H, int W, int Cp, int ch0, cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (!dfeat || !xs || !ys || !demb) return AS_EINVAL;
+  const long long total = R * N * (long long)D;
+  const int grid = ew_grid(total, 1);
+  if (idx_bytes == 1)
+    scatter_bwd_pnhwc_kernel<uint8_t><<<grid, 256, 0, st>>>((const __nv_bfloat16*)dfeat, (const uint8_t*)xs, (const uint8_t*)ys, en, demb, R, N, D, H, W, Cp, ch0);
+  else if (idx_bytes == 8)
+    scatter_bwd_pnhwc_kernel<long long><<<grid, 256, 0, st>>>((const __nv_bfloat16*)dfeat, (const long long*)xs, (const long long*)ys, en, demb, R, N, D, H, W, Cp, ch0);
+  else
+    return AS_EUNSUPPORTED;
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+// ------------------------------------------------------------------------------------------ 2x2 max-pool, padded NHWC bf16
+// forward: out[r,py,px,c] = max over the 2x2 window; backward: gradient to the FIRST maximum in row-major window
+// order (torch.nn.functional.max_pool2d semantics), zero elsewhere and on the border.
+__global__ void maxpool2_fwd_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, long long R,
+                                    int H, int W, int C) {
+  const int Ho = H / 2, Wo = W / 2, C8 = C / 8;
+  const long long total = R * (long long)(Ho + 2) * (Wo + 2) * C8;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int c8 = (int)(i % C8);
+    long long p = i / C8;
+    const int xx = (int)(p % (Wo + 2)); p /= (Wo + 2);
+    const int yy = (int)(p % (Ho + 2));
+    const long long r = p / (Ho + 2);
+    BF8 o;
+    if (xx == 0 || xx == Wo + 1 || yy == 0 || yy == Ho + 1) {
+      o.u = make_uint4(0, 0, 0, 0);
+    } else {
+      const __nv_bfloat16* base = in + ((r * (H + 2) + 2 * (yy - 1) + 1) * (long long)(W + 2) + 2 * (xx - 1) + 1) * C + c8 * 8;
+      BF8 a, b, c, d;
+      a.u = *reinterpret_cast<const uint4*>(base);
+      b.u = *reinterpret_cast<const uint4*>(base + C);
+      c.u = *reinterpret_cast<const uint4*>(base + (long long)(W + 2) * C);
+      d.u = *reinterpret_cast<const uint4*>(base + (long long)(W + 2) * C + C);
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        o.h[j] = f2bf(fmaxf(fmaxf(bf2f(a.h[j]), bf2f(b.h[j])), fmaxf(bf2f(c.h[j]), bf2f(d.h[j]))));
+    }
+    *reinterpret_cast<uint4*>(out + i * 8) = o.u;
+  }
+}
+
+__global__ void maxpool2_bwd_kernel(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict__ dout,
+                                    __nv_bfloat16* __restrict__ din, long long R, int H, int W, int C) {
+  // thread per (pooled pixel incl. border ring handled separately, 8 channels): writes the four input pixels
+  const int Ho = H / 2, Wo = W / 2, C8 = C / 8;
+  const long long total = R * (long long)Ho * Wo * C8;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int c8 = (int)(i % C8);
+    long long p = i / C8;
+    const int px = (int)(p % Wo); p /= Wo;
+    const int py = (int)(p % Ho);
+    const long long r = p / Ho;
+    const long long ibase = ((r * (H + 2) + 2 * py + 1) * (long long)(W + 2) + 2 * px + 1) * C + c8 * 8;
+    BF8 a, b, c, d, g, oa, ob, oc, od;
+    a.u = *reinterpret_cast<const uint4*>(in + ibase);
+    b.u = *reinterpret_cast<const uint4*>(in + ibase + C);
+    c.u = *reinterpret_cast<const uint4*>(in + ibase + (long long)(W + 2) * C);
+    d.u = *reinterpret_cast<const uint4*>(in + ibase + (long long)(W + 2) * C + C);
+    g.u = *reinterpret_cast<const uint4*>(dout + ((r * (Ho + 2) + py + 1) * (long long)(Wo + 2) + px + 1) * C + c8 * 8);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float va = bf2f(a.h[j]), vb = bf2f(b.h[j]), vc = bf2f(c.h[j]), vd = bf2f(d.h[j]);
+      int best = 0; float m = va;
+      if (vb > m) { m = vb; best = 1; }
+      if (vc > m) { m = vc; best = 2; }
+      if (vd > m) { m = vd; best = 3; }
+      const __nv_bfloat16 z = f2bf(0.f);
+      oa.h[j] = best == 0 ? g.h[j] : z; ob.h[j] = best == 1 ? g.h[j] : z;
+      oc.h[j] = best == 2 ? g.h[j] : z; od.h[j] = best == 3 ? g.h[j] : z;
+    }
+    *reinterpret_cast<uint4*>(din + ibase) = oa.u;
+    *reinterpret_cast<uint4*>(din + ibase + C) = ob.u;
+    *reinterpret_cast<uint4*>(din + ibase + (long long)(W + 2) * C) = oc.u;
+    *reinterpret_cast<uint4*>(din + ibase + (long long)(W + 2) * C + C) = od.u;
+  }
+}
+
+// zero the one-pixel border ring of a padded NHWC map
+__global__ void zero_border_kernel(__nv_bfloat16* __restrict__ x, long long R, int H, int W, int C) {
+  const int C8 = C / 8;
+  const int ring = 2 * (W + 2) + 2 * H;
+  const long long total = R * (long long)ring * C8;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int c8 = (int)(i % C8);
+    long long p = i / C8;
+    const int k = (int)(p % ring);
+    const long long r = p / ring;
+    int yy, xx;
+    if (k < W + 2) { yy = 0; xx = k; }
+    else if (k < 2 * (W + 2)) { yy = H + 1; xx = k - (W + 2); }
+    else { const int q = k - 2 * (W + 2); yy = 1 + q / 2; xx = (q & 1) ? W + 1 : 0; }
+    *reinterpret_cast<uint4*>(x + ((r * (H + 2) + yy) * (long long)(W + 2) + xx) * C + c8 * 8) = make_uint4(0, 0, 0, 0);
+  }
+}
+
+int maxpool2_fwd(const void* in, void* out, long long R, int H, int W, int C, cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if ((C % 8) || (H % 2) || (W % 2) || H <= 0 || W <= 0) return AS_ESIZE;
+  if (!in || !out) return AS_EINVAL;
+  const long long total = R * (long long)(H / 2 + 2) * (W / 2 + 2) * (C / 8);
+  maxpool2_fwd_kernel<<<ew_grid(total, 1), 256, 0, st>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, R, H, W, C);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+int maxpool2_bwd(const void* in, const void* dout, void* din, long long R, int H, int W, int C, cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if ((C % 8) || (H % 2) || (W % 2) || H <= 0 || W <= 0) return AS_ESIZE;
+  if (!in || !dout || !din) return AS_EINVAL;
+  const long long total = R * (long long)(H / 2) * (W / 2) * (C / 8);
+  maxpool2_bwd_kernel<<<ew_grid(total, 1), 256, 0, st>>>((const __nv_bfloat16*)in, (const __nv_bfloat16*)dout, (__nv_bfloat16*)din, R, H, W, C);
+  AS_LAUNCH_CHECK();
+  const long long ring = R * (long long)(2 * (W + 2) + 2 * H) * (C / 8);
+  zero_border_kernel<<<ew_grid(ring, 1), 256, 0, st>>>((__nv_bfloat16*)din, R, H, W, C);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+}  // namespace as

@@ -179,23 +179,22 @@ class SpatialEncoder(nn.Module):
 
     def __init__(self):
         super().__init__()
-        self.project = Conv(56, 32, 1, 0, relu=True)
+        self.project = Conv(56, 32, 1, 0, relu=True, nhwc=True)
         self.encode_modules = nn.ModuleDict({n: _eye_table(k) for n, arc, k in C.SPATIAL_FIELDS if arc == 'one_hot'})
-        self.downsample = nn.ModuleList([Conv(32, 64, 3, 1, True), Conv(64, 128, 3, 1, True),
+        self.downsample = nn.ModuleList([Conv(32, 64, 3, 1, True, nhwc=True), Conv(64, 128, 3, 1, True, nhwc=True),
                                          Conv(128, 128, 3, 1, True, nhwc=True)])
         self.res = nn.ModuleList([ResBlock(128) for _ in range(4)])
         self.fc = FC(128 * (C.SPATIAL_Y // 8) * (C.SPATIAL_X // 8), 256, relu=True)
 
-    def forward(self, spatial_info, scatter_map):
-        """-> (embedded_spatial [R,256], map_skip).  map_skip[0..2] (pre-pool maps, only read by the U-Net variant
-        of the location head, which the default config disables) are not kept; map_skip[3..6] are the 19x20x128
-        maps as zero-padded NHWC bf16."""
-        x = ops.spatial_project(spatial_info, scatter_map, self.project[0].weight, self.project[0].bias)
+    def forward(self, spatial_info, x):
+        """`x` = output of the 1x1 project conv + ReLU as a padded NHWC bf16 map (spatial.spatial_project, which also
+        holds the ScatterConnection and the 56-channel input build).
+        -> (embedded_spatial [R,256], map_skip).  map_skip[0..2] (pre-pool maps, only read by the U-Net variant of
+        the location head, which the default config disables) are not kept; map_skip[3..6] are the 19x20x128 maps
+        as zero-padded NHWC bf16.  Every convolution is an implicit GEMM on the tcgen05 kernel."""
         skip = [None, None, None]
-        x = self.downsample[0](ops.max_pool2(x))
-        x = self.downsample[1](ops.max_pool2(x))
-        x = spatial.to_pnhwc(ops.max_pool2(x))                    # [R, 21, 22, 128] bf16, zero border
-        x = self.downsample[2](x)
+        for conv in self.downsample:                              # 3 x (2x2 max-pool, 3x3 conv + ReLU)
+            x = conv(spatial.max_pool2(x))
         for block in self.res:
             skip.append(x)
             x = block(x)
@@ -274,9 +273,11 @@ class Encoder(nn.Module):
         embedded_scalar, scalar_context, baseline_feature = self.scalar_encoder(scalar_info)
         entity_embeddings, embedded_entity = self.entity_encoder(entity_info, entity_num)
         proj = self.scatter_project(entity_embeddings)
-        scatter_map = ops.scatter_connection(proj, entity_info['x'], entity_info['y'], entity_num,
-                                             C.SPATIAL_Y, C.SPATIAL_X, 'add')
-        embedded_spatial, map_skip = self.spatial_encoder(spatial_info, scatter_map)
+        # ScatterConnection ('add') + one-hot / effect planes + 1x1 project conv + ReLU in padded NHWC bf16
+        pw = self.spatial_encoder.project[0]
+        projected = spatial.spatial_project(proj, entity_info['x'], entity_info['y'], entity_num, spatial_info,
+                                            pw.weight, pw.bias)
+        embedded_spatial, map_skip = self.spatial_encoder(spatial_info, projected)
         lstm_input = torch.cat([embedded_scalar, embedded_entity, embedded_spatial], dim=-1)
         return lstm_input, scalar_context, baseline_feature, entity_embeddings, map_skip
 

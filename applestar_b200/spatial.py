@@ -271,3 +271,115 @@ def spatial_fc_weight(weight, ch, H, W):
     w = weight.view(out, ch, H, W).permute(0, 2, 3, 1)
     w = F.pad(w, (0, 0, 1, 1, 1, 1))
     return w.reshape(out, (H + 2) * (W + 2) * ch)
+
+
+class MaxPool2(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        R, ph, pw, Cc = x.shape
+        H, W = ph - 2, pw - 2
+        x = x.contiguous()
+        y = torch.empty((R, H // 2 + 2, W // 2 + 2, Cc), dtype=torch.bfloat16, device=x.device)
+        _lib.call('as_maxpool2_fwd_bf16', x.data_ptr(), y.data_ptr(), R, H, W, Cc, _lib.stream_ptr())
+        ctx.dims = (R, H, W, Cc)
+        ctx.save_for_backward(x)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        R, H, W, Cc = ctx.dims
+        dy = dy.contiguous()
+        dx = torch.empty_like(x)
+        _lib.call('as_maxpool2_bwd_bf16', x.data_ptr(), dy.data_ptr(), dx.data_ptr(), R, H, W, Cc, _lib.stream_ptr())
+        return dx
+
+
+def max_pool2(x):
+    return MaxPool2.apply(x)
+
+
+_PLANES = ('height_map', 'visibility_map', 'creep', 'player_relative', 'alerts', 'pathable', 'buildable')
+_EFFECTS = ('effect_PsiStorm', 'effect_NukeDot', 'effect_LiberatorDefenderZone', 'effect_BlindingCloud',
+            'effect_CorrosiveBile', 'effect_LurkerSpines')
+
+
+def _build_features(proj, x, y, entity_num, spatial_info):
+    import ctypes
+    R, N, D = proj.shape
+    hm = spatial_info['height_map']
+    H, W = hm.shape[1], hm.shape[2]
+    smap = K.ScatterConnection.apply(proj.detach(), x, y, entity_num, H, W, 'add')     # dense map: temporary
+    planes = (ctypes.c_void_p * 7)()
+    effects = (ctypes.c_void_p * 6)()
+    keep = []
+    for i, k in enumerate(_PLANES):
+        t = spatial_info[k].contiguous()
+        if t.dtype != torch.uint8:
+            t = t.to(torch.uint8)
+        keep.append(t)
+        planes[i] = t.data_ptr()
+    n_eff = spatial_info[_EFFECTS[0]].shape[1]
+    for i, k in enumerate(_EFFECTS):
+        t = spatial_info[k].contiguous()
+        if t.dtype != torch.int16:
+            t = t.to(torch.int16)
+        keep.append(t)
+        effects[i] = t.data_ptr()
+    out = torch.empty((R, H + 2, W + 2, 64), dtype=torch.bfloat16, device=proj.device)
+    _lib.call('as_spatial_features', planes, effects, n_eff, smap.data_ptr(), out.data_ptr(), R, H, W, D,
+              _lib.stream_ptr())
+    return out, H, W
+
+
+class SpatialProject(torch.autograd.Function):
+    """ScatterConnection ('add') + 56-channel spatial input + 1x1 project conv (56 -> 32) + ReLU
+    (encoder.py:37-42, spatial_encoder.py:52-72) -> zero-padded NHWC bf16 [R,H+2,W+2,32].
+    Backward: weight / bias gradients by the tap-batched wgrad GEMM; the only data gradient that exists (towards the
+    entity projections) is gathered at the <=512 entity cells and multiplied by the 32x32 scatter block of the
+    weight, so the 3.3 GB full-resolution data gradient of the conv is never formed."""
+
+    @staticmethod
+    def forward(ctx, proj, x, y, entity_num, spatial_info, weight, bias):
+        feats, H, W = _build_features(proj, x, y, entity_num, spatial_info)
+        R, N, D = proj.shape
+        cout = weight.shape[0]
+        w_fwd, _ = _conv_weights(weight, 64)
+        out = torch.empty((R, H + 2, W + 2, cout), dtype=torch.bfloat16, device=proj.device)
+        _conv_call(feats, w_fwd, out, bias, R, H, W, 64, cout, 1, True)
+        xs, ys = x.contiguous(), y.contiguous()
+        if xs.dtype not in (torch.uint8, torch.int64):
+            xs, ys = xs.long(), ys.long()
+        en = None if entity_num is None else entity_num.contiguous().long()
+        ctx.dims = (R, N, D, H, W, cout, weight.shape[1])
+        ctx.save_for_backward(feats, out, xs, ys, en, weight)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        feats, out, xs, ys, en, weight = ctx.saved_tensors
+        R, N, D, H, W, cout, cin = ctx.dims
+        st = _lib.stream_ptr()
+        dy = dy.contiguous()
+        dz = torch.empty_like(dy)
+        _lib.call('as_relu_bwd_bf16', dy.data_ptr(), out.data_ptr(), dz.data_ptr(), dy.numel(), st)
+        P = R * (H + 2) * (W + 2)
+        splits = _lib.lib().as_gemm_splits(P, 2 * K.NUM_SMS)
+        dw1 = torch.empty((1, cout, 64), dtype=torch.float32, device=dy.device)
+        ws = torch.empty((splits, 1, cout, 64), dtype=torch.float32, device=dy.device) if splits > 1 else None
+        _lib.call('as_conv_wgrad_nhwc_bf16', dz.data_ptr(), feats.data_ptr(), dw1.data_ptr(), _ptr(ws), R, H, W, 64, cout,
+                  1, splits, st)
+        dw = dw1[0, :, :cin].reshape(cout, cin, 1, 1)
+        db = torch.empty(cout, dtype=torch.float32, device=dy.device)
+        scratch = torch.empty(_lib.lib().as_colsum_scratch_floats(cout), dtype=torch.float32, device=dy.device)
+        _lib.call('as_colsum_bf16', dz.data_ptr(), db.data_ptr(), scratch.data_ptr(), P, cout, st)
+        g = torch.empty((R, N, cout), dtype=torch.float32, device=dy.device)       # dz rows at the entity cells
+        _lib.call('as_scatter_connection_bwd_pnhwc', dz.data_ptr(), xs.data_ptr(), ys.data_ptr(), xs.element_size(),
+                  _ptr(en), g.data_ptr(), R, N, cout, H, W, cout, 0, st)
+        w_s = weight.detach()[:, 24:24 + D, 0, 0]                                  # [cout, D] scatter block
+        dproj = (g.view(R * N, cout) @ w_s).view(R, N, D)
+        return dproj, None, None, None, None, dw, db
+
+
+def spatial_project(proj, x, y, entity_num, spatial_info, weight, bias):
+    return SpatialProject.apply(proj, x, y, entity_num, spatial_info, weight, bias)

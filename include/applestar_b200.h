@@ -115,6 +115,23 @@ int as_conv_c32_1_bwd(const float* dlogits, const void* in, const float* w, void
 int64_t as_colsum_scratch_floats(int C);
 int as_colsum_bf16(const void* x, float* out, float* scratch, int64_t rows, int C, void* stream);
 
+/* Spatial input features -- replaces the one-hot embeddings, the effect index_put and torch.cat of
+ * SpatialEncoder.forward (obs_encoder/spatial_encoder.py:52-71): planes[7] = height_map, visibility_map, creep,
+ * player_relative, alerts, pathable, buildable (uint8 [R,H,W]); effects[6] = int16 [R,n_eff] flat pixel ids
+ * (zero padding sets pixel 0, as in the reference); scatter_map fp32 [R,32,H,W].  out: zero-padded NHWC bf16
+ * [R,H+2,W+2,64] (56 real channels in the reference order, 8 zero), the A operand of the 1x1 project GEMM. */
+int as_spatial_features(const void* const* planes, const void* const* effects, int n_eff, const float* scatter_map,
+                        void* out, int64_t R, int H, int W, int Cs, void* stream);
+/* ScatterConnection backward reading the gradient of that feature map directly (channels ch0 .. ch0+D-1). */
+int as_scatter_connection_bwd_pnhwc(const void* d_feat, const void* xs, const void* ys, int idx_bytes,
+                                    const int64_t* entity_num, float* d_emb, int64_t R, int N, int D, int H, int W,
+                                    int Cp, int ch0, void* stream);
+
+/* 2x2 max-pool on padded NHWC bf16 maps -- replaces F.max_pool2d (spatial_encoder.py:79).  in [R,H+2,W+2,C] ->
+ * out [R,H/2+2,W/2+2,C]; backward routes to the first maximum of the window (torch semantics), border zero. */
+int as_maxpool2_fwd_bf16(const void* in, void* out, int64_t R, int H, int W, int C, void* stream);
+int as_maxpool2_bwd_bf16(const void* in, const void* dout, void* din, int64_t R, int H, int W, int C, void* stream);
+
 /* LayerNorm(x (+ residual)) * gamma + beta, eps 1e-5, optional fused ReLU -- replaces nn.LayerNorm at
  * module_utils.py:135,139 (Transformer), lstm.py:140-151 (LN-LSTM), res_block.py:68-141 (ResFCBlock/ResFCBlock2).
  * x/res [rows, C] fp32 (res may be NULL); outputs y32 fp32 and/or y16 bf16 (either may be NULL);

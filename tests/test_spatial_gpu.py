@@ -148,3 +148,50 @@ def test_final_conv_32_to_1():
     assert (x.grad - xr.grad).abs().max().item() < 0.01 * xr.grad.abs().max().item() + 1e-3
     assert (w.grad - wr.grad).abs().max().item() < 1e-3 * wr.grad.abs().max().item() + 1e-2
     assert abs(b.grad.item() - br.grad.item()) < 1e-3 * abs(br.grad.item()) + 1e-2
+
+
+def test_maxpool_fwd_bwd():
+    from applestar_b200 import spatial
+    x = torch.relu(_rand((2, 32, 76, 80), 23)).requires_grad_(True)      # post-ReLU: many exact ties at 0
+    y = spatial.max_pool2(_to_p(x))
+    assert y.shape == (2, 40, 42, 32) and _border_zero(y)
+    gy = torch.zeros_like(y)
+    gy[:, 1:-1, 1:-1] = _rand((2, 38, 40, 32), 24).to(torch.bfloat16)
+    y.backward(gy)
+    xr = x.detach().to(torch.bfloat16).float().requires_grad_(True)
+    yr = F.max_pool2d(xr, 2, 2)
+    yr.backward(_from_p(gy))
+    assert torch.equal(_from_p(y), yr)
+    assert torch.equal(x.grad, xr.grad)                                   # first-max routing == torch
+
+
+def test_spatial_project_matches_reference_front():
+    """scatter + 56-channel input + 1x1 project conv + ReLU (+ its backward) vs the oracle's fp32 front end."""
+    from applestar_b200 import spatial, synth
+    from oracle import restate as R
+    obs = synth.gen_observations(3, 512, 31, special=True)
+    g = torch.Generator().manual_seed(32)
+    proj = torch.relu(torch.randn(3, 512, 32, generator=g))
+    w = torch.randn(32, 56, 1, 1, generator=g) * 0.2
+    b = torch.randn(32, generator=g) * 0.1
+    en = obs['entity_num']
+    mask = (torch.arange(512).unsqueeze(0) < en.unsqueeze(1)).unsqueeze(2)
+    pr = proj.clone().requires_grad_(True)
+    wr, br = w.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    smap = R.scatter_connection(pr * mask, obs['entity_info']['x'], obs['entity_info']['y'], 'add')
+    ref = torch.relu(F.conv2d(R.spatial_input(obs['spatial_info'], smap), wr, br))
+    gout = torch.randn(ref.shape, generator=g)
+    ref.backward(gout)
+
+    pd = proj.cuda().requires_grad_(True)
+    wd, bd = w.cuda().requires_grad_(True), b.cuda().requires_grad_(True)
+    sp = {k: v.cuda() for k, v in obs['spatial_info'].items()}
+    out = spatial.spatial_project(pd, obs['entity_info']['x'].cuda(), obs['entity_info']['y'].cuda(), en.cuda(), sp, wd, bd)
+    assert out.shape == (3, 154, 162, 32) and _border_zero(out)
+    gy = torch.zeros_like(out)
+    gy[:, 1:-1, 1:-1] = gout.permute(0, 2, 3, 1).cuda().to(torch.bfloat16)
+    out.backward(gy)
+    assert (_from_p(out).cpu() - ref).abs().max().item() < 0.02 * ref.abs().max().item() + 2e-2
+    assert (pd.grad.cpu() - pr.grad).abs().max().item() < 0.03 * pr.grad.abs().max().item() + 1e-2
+    assert (wd.grad.cpu() - wr.grad).abs().max().item() < 0.02 * wr.grad.abs().max().item() + 0.5
+    assert (bd.grad.cpu() - br.grad).abs().max().item() < 0.02 * br.grad.abs().max().item() + 0.5
