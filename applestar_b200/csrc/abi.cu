@@ -62,6 +62,10 @@ extern "C" {
 
 int as_abi_version(void) { return 2; }
 
+namespace as { extern int g_gemm_debug; }
+// diagnostics only (not part of the public header): 0 normal, 1 GEMM epilogue skips global stores, 2 only drains TMEM
+int as_debug_gemm_mode(int mode) { as::g_gemm_debug = mode; return 0; }
+
 int as_scatter_connection_fwd(const float* emb, const void* xs, const void* ys, int idx_bytes,
                               const int64_t* entity_num, float* out, int64_t R, int N, int D, int H, int W, int cover,
                               void* stream) {

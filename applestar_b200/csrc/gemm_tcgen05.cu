@@ -41,6 +41,7 @@ struct GemmDev {
   int relu;
   float alpha;
   float* ws;  // split-K partials
+  int debug;  // diagnostics: 1 = epilogue skips global stores, 2 = epilogue only drains TMEM
 };
 
 template <int BN>
@@ -224,7 +225,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         uint32_t v[32];
         tmem_ld32(t_row + c * 32, v);
         tmem_ld_wait();
-        if (n0 + c * 32 >= p.N) continue;                // warp-uniform
+        if (n0 + c * 32 >= p.N || p.debug == 2) continue; // warp-uniform
 #pragma unroll
         for (int sub = 0; sub < 2; ++sub) {
           const int col0 = n0 + c * 32 + sub * 16;
@@ -261,7 +262,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                     if ((yy == 0) | (yy == p.img_h - 1) | (xx == 0) | (xx == p.img_w - 1)) a = make_float4(0.f, 0.f, 0.f, 0.f);
                   }
                 }
-                if (grow < p.M && gcol < p.N) {
+                if (grow < p.M && gcol < p.N && p.debug == 0) {
                   float* dst = obase + (long long)grow * ldo;
                   if (gcol + 4 <= p.N && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
                     *reinterpret_cast<float4*>(dst) = a;
@@ -314,7 +315,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                   if (p.relu) x = fmaxf(x, 0.f);
                   f[k] = border ? 0.f : x;
                 }
-                if (grow < p.M && gcol < p.N) {
+                if (grow < p.M && gcol < p.N && p.debug == 0) {
                   __nv_bfloat16* dst = obase + (long long)grow * ldo;
                   if (gcol + 8 <= p.N && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
                     __nv_bfloat162 h0 = __floats2bfloat162_rn(f[0], f[1]), h1 = __floats2bfloat162_rn(f[2], f[3]);
@@ -431,6 +432,8 @@ static int pick_bn(int N, bool b_mn) {
   return 32;
 }
 
+int g_gemm_debug = 0;
+
 int gemm_run(const GemmCall& g, cudaStream_t st) {
   if (g.M <= 0 || g.N <= 0 || g.K <= 0 || g.nb0 <= 0 || g.nb1 <= 0) return AS_ESIZE;
   if (!g.A || !g.B || (!g.C && g.splits <= 1)) return AS_EINVAL;
@@ -466,6 +469,7 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
   if (g.splits > 1 && p.splits != g.splits) return AS_ESIZE;     // caller sizes ws from as_gemm_splits()
   p.C = g.C; p.C2 = g.C2; p.c_bf16 = g.c_bf16; p.ldc = g.ldc; p.c_sb0 = g.c_sb0; p.c_sb1 = g.c_sb1;
   p.bias = g.bias; p.relu = g.relu; p.alpha = g.alpha; p.ws = g.ws;
+  p.debug = g_gemm_debug;
 
   CUtensorMap ta, tb;
   int rc;

@@ -45,11 +45,20 @@ __device__ __forceinline__ float dot8(const uint4& q, const float* vv) {
   return acc;
 }
 
+// A lane always multiplies the same 8-element slices of v (chunk index = lane + 32 c), whatever the row: they are
+// read from shared memory ONCE per mat-vec into registers (a per-row read would be an 8-way bank conflict).
 template <int CHUNKS_PER_LANE, int kRowsPerIter>
 __device__ __forceinline__ void matvec_rows(const __nv_bfloat16* __restrict__ Wm, const float* v, float* out, int rows,
                                             int cols) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int chunks = cols >> 3;
+  float vr[CHUNKS_PER_LANE][8];
+#pragma unroll
+  for (int c = 0; c < CHUNKS_PER_LANE; ++c) {
+    const int ch = lane + c * 32;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) vr[c][e] = (ch < chunks) ? v[ch * 8 + e] : 0.f;
+  }
   for (int j0 = warp * kRowsPerIter; j0 < rows; j0 += kLstmWarps * kRowsPerIter) {
     uint4 q[kRowsPerIter][CHUNKS_PER_LANE];
 #pragma unroll
@@ -65,10 +74,7 @@ __device__ __forceinline__ void matvec_rows(const __nv_bfloat16* __restrict__ Wm
     for (int r = 0; r < kRowsPerIter; ++r) {
       float acc = 0.f;
 #pragma unroll
-      for (int c = 0; c < CHUNKS_PER_LANE; ++c) {
-        const int ch = lane + c * 32;
-        if (ch < chunks) acc += dot8(q[r][c], v + ch * 8);
-      }
+      for (int c = 0; c < CHUNKS_PER_LANE; ++c) acc += dot8(q[r][c], vr[c]);
       acc = warp_sum(acc);
       if (lane == 0 && j0 + r < rows) out[j0 + r] = acc;
     }

@@ -1,0 +1,20 @@
+"""Diagnostics: where does a small-K GEMM spend its time?  Times one shape with the epilogue progressively disabled."""
+import os, sys, ctypes
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+from applestar_b200 import _lib, kernels as K
+lib = _lib.lib()
+lib.as_debug_gemm_mode.argtypes = [ctypes.c_int]
+def t(M, N, Kd, bf16, mode, iters=5):
+    A = torch.randn(M, Kd, device='cuda').to(torch.bfloat16); B = torch.randn(N, Kd, device='cuda').to(torch.bfloat16)
+    C = torch.empty((M, N), device='cuda', dtype=torch.bfloat16 if bf16 else torch.float32)
+    lib.as_debug_gemm_mode(mode)
+    for _ in range(2): K.gemm(A, B, C, M, N, Kd)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters): K.gemm(A, B, C, M, N, Kd)
+    e1.record(); torch.cuda.synchronize(); lib.as_debug_gemm_mode(0)
+    return e0.elapsed_time(e1) / iters
+for (M, N, Kd, bf) in [(532480, 768, 256, True), (532480, 256, 256, False), (532480, 1024, 256, True), (532480, 768, 64, True), (532480, 768, 1024, True)]:
+    print(M, N, Kd, 'bf16' if bf else 'f32', ' full %.3f  no-store %.3f  drain-only %.3f ms' % (t(M, N, Kd, bf, 0), t(M, N, Kd, bf, 1), t(M, N, Kd, bf, 2)))
