@@ -4,6 +4,8 @@
 #include "loss.h"
 
 namespace as {
+extern int g_gemm_debug;
+extern int g_gemm_no_tma_store;
 int scatter_fwd(const float*, const void*, const void*, int, const long long*, float*, long long, int, int, int, int,
                 int, cudaStream_t);
 int scatter_bwd(const float*, const void*, const void*, int, const long long*, float*, long long, int, int, int, int,
@@ -62,9 +64,8 @@ extern "C" {
 
 int as_abi_version(void) { return 2; }
 
-namespace as { extern int g_gemm_debug; }
 // diagnostics only (not part of the public header): 0 normal, 1 GEMM epilogue skips global stores, 2 only drains TMEM
-int as_debug_gemm_mode(int mode) { as::g_gemm_debug = mode; return 0; }
+int as_debug_gemm_mode(int mode) { as::g_gemm_debug = mode & 3; as::g_gemm_no_tma_store = (mode >> 2) & 1; return 0; }
 
 int as_scatter_connection_fwd(const float* emb, const void* xs, const void* ys, int idx_bytes,
                               const int64_t* entity_num, float* out, int64_t R, int N, int D, int H, int W, int cover,

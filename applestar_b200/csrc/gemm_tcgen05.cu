@@ -41,6 +41,7 @@ struct GemmDev {
   int relu;
   float alpha;
   float* ws;  // split-K partials
+  int tma_store;   // 1: C (and C2) are written with TMA bulk stores from a swizzled staging tile
   int debug;  // diagnostics: 1 = epilogue skips global stores, 2 = epilogue only drains TMEM
 };
 
@@ -51,13 +52,14 @@ struct SmemLayout {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = (BN >= 256) ? 4 : (BN >= 128 ? 6 : 8);
   static constexpr int kBarBytes = 1024;
-  static constexpr int kStgBytes = kEpiWarps * 32 * kStgPitch * 4;            // per-warp epilogue staging tiles
+  static constexpr int kStgBytes = kEpiWarps * 4096;                         // per-warp epilogue staging tiles (32 rows x 128 B)
   static constexpr int kTotal = kStages * kStageBytes + kBarBytes + kStgBytes + 1024;  // +1024 alignment slack
 };
 
 template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
-gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmDev p) {
+gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+            const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2, const GemmDev p) {
   using L = SmemLayout<BN>;
   constexpr int kStages = L::kStages;
   constexpr uint32_t kTmemCols = (2 * BN <= 32) ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
@@ -220,6 +222,88 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                                       : (long long)b0 * p.c_sb0 + (long long)b1 * p.c_sb1;
       const long long ldo = to_ws ? (long long)p.N : p.ldc;
       const bool f32_out = to_ws || !p.c_bf16;
+      if (p.tma_store && !to_ws) {
+        // ---- TMA-store path: lane = accumulator row.  Each 128-byte row segment (32 fp32 or 64 bf16 columns) goes to
+        // the warp's 128B-swizzled staging tile with eight conflict-free 16-byte stores; one bulk tensor store per
+        // warp then sends the 32-row x 128-byte box (tile / matrix edges are clipped by the TMA unit).
+        uint8_t* sbuf = bar_base + L::kBarBytes + e * 4096;
+        const int grow = row_base + lane;
+        bool border = false;
+        if (p.img_w > 0) {
+          const int q = grow % (p.img_w * p.img_h);
+          const int yy = q / p.img_w, xx = q - yy * p.img_w;
+          border = (yy == 0) | (yy == p.img_h - 1) | (xx == 0) | (xx == p.img_w - 1);
+        }
+        constexpr int kHalfCols = (BN >= 128) ? BN / 2 : BN;          // narrow tiles: one warp set takes all columns
+        const int col_begin = (BN >= 128) ? half * kHalfCols : 0;
+        const int col_end = (BN >= 128) ? col_begin + kHalfCols : (half == 0 ? BN : 0);
+        const bool need_bf16 = !f32_out || p.C2 != nullptr;
+        const CUtensorMap* map16 = f32_out ? &tmC2 : &tmC;
+#pragma unroll 1
+        for (int col = col_begin; col < col_end; col += 64) {
+          uint32_t packed[32];
+          int halves = 0;
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int c = col + h * 32;
+            if (c < col_end && n0 + c < p.N) {                        // warp-uniform
+              uint32_t v[32];
+              tmem_ld32(t_row + c, v);
+              tmem_ld_wait();
+              if (p.debug != 2) {
+                float bl = 0.f;
+                if (p.bias != nullptr && n0 + c + lane < p.N) bl = __ldg(p.bias + n0 + c + lane);
+                float f[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                  float x = __uint_as_float(v[j]) * p.alpha;
+                  if (p.bias != nullptr) x += __shfl_sync(0xffffffffu, bl, j);
+                  if (p.relu) x = fmaxf(x, 0.f);
+                  f[j] = border ? 0.f : x;
+                }
+                if (f32_out) {
+                  if (lane == 0) tma_store_wait_read();               // previous box has left the staging tile
+                  __syncwarp();
+#pragma unroll
+                  for (int j = 0; j < 8; ++j)
+                    *reinterpret_cast<float4*>(sbuf + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+                        make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+                  fence_proxy_async_smem();
+                  __syncwarp();
+                  if (lane == 0 && p.debug == 0) {
+                    tma_store_4d(&tmC, sbuf, n0 + c, row_base, b0, b1);
+                    tma_store_commit();
+                  }
+                }
+                if (need_bf16) {
+#pragma unroll
+                  for (int j = 0; j < 16; ++j) {
+                    __nv_bfloat162 hv = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
+                    packed[h * 16 + j] = *reinterpret_cast<uint32_t*>(&hv);
+                  }
+                }
+                halves = h + 1;
+              }
+            }
+          }
+          if (need_bf16 && halves > 0) {
+            if (lane == 0) tma_store_wait_read();
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              if (j < halves * 4)
+                *reinterpret_cast<uint4*>(sbuf + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+                    make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0 && p.debug == 0) {
+              tma_store_4d(map16, sbuf, n0 + col, row_base, b0, b1);
+              tma_store_commit();
+            }
+          }
+        }
+      } else
 #pragma unroll 1
       for (int c = c_begin; c < c_end; ++c) {
         uint32_t v[32];
@@ -343,6 +427,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   }
 
+  if (warp >= 4 && lane == 0) tma_store_wait_all();     // bulk stores must have drained before shared memory goes away
   tc_fence_before();
   __syncthreads();
   if (warp == 2) {
@@ -370,17 +455,18 @@ static EncodeTiledFn get_encode() {
 
 // Operand = up to 4-D bf16 tensor: dims (inner contiguous, rows, b0, b1) with element strides.
 static int make_map(CUtensorMap* tm, const void* ptr, long long inner, long long rows, long long ld, int nb0,
-                    long long sb0, int nb1, long long sb1, int box_inner, int box_rows) {
+                    long long sb0, int nb1, long long sb1, int box_inner, int box_rows, int es = 2) {
   EncodeTiledFn enc = get_encode();
   if (!enc) return AS_EDRIVER;
-  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || ((ld * 2) & 15)) return AS_EALIGN;
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || ((ld * es) & 15)) return AS_EALIGN;
   cuuint64_t dims[4] = {(cuuint64_t)inner, (cuuint64_t)rows, (cuuint64_t)nb0, (cuuint64_t)nb1};
   long long s0 = nb0 > 1 ? sb0 : ld * rows, s1 = nb1 > 1 ? sb1 : s0 * nb0;
-  if (((s0 * 2) & 15) || ((s1 * 2) & 15)) return AS_EALIGN;
-  cuuint64_t strides[3] = {(cuuint64_t)(ld * 2), (cuuint64_t)(s0 * 2), (cuuint64_t)(s1 * 2)};
+  if (((s0 * es) & 15) || ((s1 * es) & 15)) return AS_EALIGN;
+  cuuint64_t strides[3] = {(cuuint64_t)(ld * es), (cuuint64_t)(s0 * es), (cuuint64_t)(s1 * es)};
   cuuint32_t box[4] = {(cuuint32_t)box_inner, (cuuint32_t)box_rows, 1, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
-  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, estr,
+  CUresult r = enc(tm, es == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4,
+                   const_cast<void*>(ptr), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? AS_OK : AS_EDRIVER;
@@ -398,7 +484,8 @@ static int num_sms() {
 }
 
 template <int BN, bool A_MN, bool B_MN>
-static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& p, cudaStream_t st) {
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const CUtensorMap& tc2,
+                  const GemmDev& p, cudaStream_t st) {
   using L = SmemLayout<BN>;
   static bool attr_set = false;
   auto kern = gemm_kernel<BN, A_MN, B_MN>;
@@ -410,18 +497,18 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& p
   long long tiles = (long long)p.splits * p.nb0 * p.nb1 * p.m_blocks * p.n_blocks;
   int grid = (int)(tiles < num_sms() ? tiles : num_sms());
   if (grid <= 0) return AS_OK;
-  kern<<<grid, kGemmThreads, L::kTotal, st>>>(ta, tb, p);
+  kern<<<grid, kGemmThreads, L::kTotal, st>>>(ta, tb, tc, tc2, p);
   AS_LAUNCH_CHECK();
   return AS_OK;
 }
 
 template <int BN>
-static int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& p,
-                          cudaStream_t st) {
-  if (!a_mn && !b_mn) return launch<BN, false, false>(ta, tb, p, st);
-  if (!a_mn && b_mn) return launch<BN, false, true>(ta, tb, p, st);
-  if (a_mn && !b_mn) return launch<BN, true, false>(ta, tb, p, st);
-  return launch<BN, true, true>(ta, tb, p, st);
+static int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
+                          const CUtensorMap& tc2, const GemmDev& p, cudaStream_t st) {
+  if (!a_mn && !b_mn) return launch<BN, false, false>(ta, tb, tc, tc2, p, st);
+  if (!a_mn && b_mn) return launch<BN, false, true>(ta, tb, tc, tc2, p, st);
+  if (a_mn && !b_mn) return launch<BN, true, false>(ta, tb, tc, tc2, p, st);
+  return launch<BN, true, true>(ta, tb, tc, tc2, p, st);
 }
 
 static int pick_bn(int N, bool b_mn) {
@@ -433,6 +520,7 @@ static int pick_bn(int N, bool b_mn) {
 }
 
 int g_gemm_debug = 0;
+int g_gemm_no_tma_store = 0;
 
 int gemm_run(const GemmCall& g, cudaStream_t st) {
   if (g.M <= 0 || g.N <= 0 || g.K <= 0 || g.nb0 <= 0 || g.nb1 <= 0) return AS_ESIZE;
@@ -481,11 +569,24 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
   if (g.b_mn) rc = make_map(&tb, g.B, g.N, k_total_b, g.ldb, onb0, g.b_sb0, g.nb1, g.b_sb1, 64, BK);
   else rc = make_map(&tb, g.B, k_total_b, g.N, g.ldb, onb0, g.b_sb0, g.nb1, g.b_sb1, BK, BN);
   if (rc) return rc;
+  // output tensor maps for the TMA-store epilogue (fall back to register stores when C is not 16-byte pitched)
+  CUtensorMap tc = ta, tc2 = ta;
+  p.tma_store = 0;
+  if (p.splits == 1 && g.C != nullptr && !g_gemm_no_tma_store) {
+    const int es = g.c_bf16 ? 2 : 4;
+    const long long c_rows = (long long)p.m_blocks * BM;      // rows beyond M are clipped through the map's extent
+    (void)c_rows;
+    int ok = make_map(&tc, g.C, g.N, g.M, g.ldc, g.nb0, g.c_sb0, g.nb1, g.c_sb1, 128 / es, 32, es) == AS_OK;
+    if (ok && g.C2 != nullptr) ok = make_map(&tc2, g.C2, g.N, g.M, g.ldc, g.nb0, g.c_sb0, g.nb1, g.c_sb1, 64, 32, 2) == AS_OK;
+    // a bf16 box is 64 columns wide: with 32-wide tiles it would spill into the neighbouring column tile
+    if ((g.c_bf16 || g.C2 != nullptr) && BN < 64 && p.n_blocks > 1) ok = 0;
+    p.tma_store = ok;
+  }
   switch (BN) {
-    case 32: return dispatch_major<32>(g.a_mn, g.b_mn, ta, tb, p, st);
-    case 64: return dispatch_major<64>(g.a_mn, g.b_mn, ta, tb, p, st);
-    case 128: return dispatch_major<128>(g.a_mn, g.b_mn, ta, tb, p, st);
-    case 256: return dispatch_major<256>(g.a_mn, g.b_mn, ta, tb, p, st);
+    case 32: return dispatch_major<32>(g.a_mn, g.b_mn, ta, tb, tc, tc2, p, st);
+    case 64: return dispatch_major<64>(g.a_mn, g.b_mn, ta, tb, tc, tc2, p, st);
+    case 128: return dispatch_major<128>(g.a_mn, g.b_mn, ta, tb, tc, tc2, p, st);
+    case 256: return dispatch_major<256>(g.a_mn, g.b_mn, ta, tb, tc, tc2, p, st);
   }
   return AS_EUNSUPPORTED;
 }
