@@ -195,5 +195,5 @@ def test_spatial_project_matches_reference_front():
     # bf16 features can flip a ReLU whose pre-activation is ~0 (obs 0 piles 512 entities on one cell), which toggles that
     # pixel's whole contribution: compare in relative L2, not max
     assert ((pd.grad.cpu() - pr.grad).norm() / pr.grad.norm()).item() < 0.05
-    assert (wd.grad.cpu() - wr.grad).abs().max().item() < 0.02 * wr.grad.abs().max().item() + 0.5
-    assert (bd.grad.cpu() - br.grad).abs().max().item() < 0.02 * br.grad.abs().max().item() + 0.5
+    assert ((wd.grad.cpu() - wr.grad).norm() / wr.grad.norm()).item() < 0.05
+    assert ((bd.grad.cpu() - br.grad).norm() / br.grad.norm()).item() < 0.05
