@@ -45,6 +45,7 @@ int conv_c32_1_bwd(const float*, const void*, const float*, void*, float*, float
                    cudaStream_t);
 long long colsum_scratch_floats(int);
 int colsum_bf16(const void*, float*, float*, long long, int, cudaStream_t);
+int colsum_bf16_static(const void*, float*, long long, int, cudaStream_t);
 int lnlstm_fwd(const float*, const float*, const float*, const void*, const float*, const float*, const float*,
                const float*, float*, float*, float*, float*, float*, int, int, int, cudaStream_t);
 int lnlstm_bwd(const float*, const float*, const float*, const float*, const float*, const float*, const float*,
@@ -228,6 +229,10 @@ int as_maxpool2_fwd_bf16(const void* in, void* out, int64_t R, int H, int W, int
 }
 int as_maxpool2_bwd_bf16(const void* in, const void* dout, void* din, int64_t R, int H, int W, int C, void* stream) {
   return as::maxpool2_bwd(in, dout, din, R, H, W, C, ST(stream));
+}
+
+int as_colsum_bf16_static(const void* x, float* out, int64_t rows, int C, void* stream) {
+  return as::colsum_bf16_static(x, out, rows, C, ST(stream));
 }
 
 int as_layer_norm_fwd(const float* x, const float* res, const float* gamma, const float* beta, float* y32, void* y16,

@@ -877,3 +877,42 @@ int maxpool2_bwd(const void* in, const void* dout, void* din, long long R, int H
 }
 
 }  // namespace as
+
+// ------------------------------------------------------------------------------------------ column sums without any allocation
+// as_colsum_bf16 needs a caller-provided scratch buffer for its per-chunk partial sums.  Some hosts cannot provide
+// one: processes that hand their whole device-memory budget to an arena at start-up and forbid any later cudaMalloc,
+// and step loops in which the device-wide synchronisation that cudaMalloc / cudaFree imply would stall every other
+// stream.  For them the same two kernels run on a fixed scratch area that lives in the library image itself.
+//
+// The area is a file-scope __device__ array, so every GPU that loads the library carries it (1 MiB) until the
+// process exits.  In host code the array's NAME is only a host-side handle, not a device address: the address is
+// looked up once per device with cudaGetSymbolAddress (with that device current) and that pointer is what the
+// kernels receive.
+namespace as {
+
+constexpr int kStaticColsumMaxC = 256;                                   // widest row the static scratch can serve
+static __device__ __align__(256) float g_colsum_static_scratch[kColsumChunks * kStaticColsumMaxC];
+
+static float* g_colsum_static_ptr[64] = {nullptr};                       // per-device address of the array above
+
+int colsum_bf16_static(const void* x, float* out, long long rows, int C, cudaStream_t st) {
+  if (rows <= 0 || C <= 0 || (C % 2) != 0) return AS_ESIZE;
+  if (C > kStaticColsumMaxC) return AS_ESIZE;                            // beyond the built-in scratch: use as_colsum_bf16
+  if (!x || !out) return AS_EINVAL;
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= 64) return AS_EUNSUPPORTED;
+  if (g_colsum_static_ptr[dev] == nullptr) {                             // set-up: first call on this device
+    float* p = nullptr;
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_colsum_static_scratch);
+    if (e != cudaSuccess) return (int)e;
+    if (p == nullptr) return AS_EDRIVER;
+    g_colsum_static_ptr[dev] = p;
+  }
+  // every partial the reduce kernel reads is written by the partial kernel of the same call, so nothing in the
+  // shared area has to be cleared between calls
+  return colsum_bf16(x, out, g_colsum_static_ptr[dev], rows, C, st);
+}
+
+}  // namespace as

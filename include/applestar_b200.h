@@ -114,6 +114,15 @@ int as_conv_c32_1_bwd(const float* dlogits, const void* in, const float* w, void
 /* out[c] = sum_r x[r][c] for bf16 x [rows, C] (bias gradients); scratch of as_colsum_scratch_floats(C) floats. */
 int64_t as_colsum_scratch_floats(int C);
 int as_colsum_bf16(const void* x, float* out, float* scratch, int64_t rows, int C, void* stream);
+/* Same column sums for hosts that may not allocate device memory at all (a process that gave its whole device
+ * budget to an arena at start-up, or a step loop that cannot afford the device-wide synchronisation cudaMalloc /
+ * cudaFree bring).  This entry point has no counterpart in the reference.  It allocates nothing: the partial sums
+ * go to a 1 MiB scratch area built into the library (present on every GPU that loads it until the process exits),
+ * which limits it to C <= 256 (AS_ESIZE beyond that: use as_colsum_bf16 with your own scratch).  The first call on a
+ * device looks the area's address up (with that device current); make that first call before any stream capture.
+ * All calls share the one area, which keeps the previous call's partial sums: nothing needs clearing (each call
+ * overwrites what it reads), but two calls that overlap on the GPU (different streams) race on it. */
+int as_colsum_bf16_static(const void* x, float* out, int64_t rows, int C, void* stream);
 
 /* Spatial input features -- replaces the one-hot embeddings, the effect index_put and torch.cat of
  * SpatialEncoder.forward (obs_encoder/spatial_encoder.py:52-71): planes[7] = height_map, visibility_map, creep,
