@@ -280,7 +280,14 @@ def run_ours(args):
                                     'sample': 'oracle/restate.py forward+loss+backward, T=%d B=%d N=%d, 2 steps' % (Tc, Bc, N)}
         print(json.dumps(line))
     if world > 1:
-        dist.destroy_process_group()
+        # tear-down: captured NCCL kernels inside CUDA graphs can stall destroy_process_group(); the numbers are out,
+        # so synchronise, drop the graphs and leave without the collective tear-down
+        dist.barrier()
+        torch.cuda.synchronize()
+        step_fn._graphs.clear()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def main():
