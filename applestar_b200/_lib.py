@@ -73,6 +73,7 @@ _SIGS = {
                                   c_int, c_int, c_float, c_void_p]),
     'as_colsum_scratch_floats': (c_int64, [c_int]),
     'as_colsum_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
+    'as_colsum_f32': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     'as_colsum_bf16_static': (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     'as_spatial_features': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
                                     c_void_p]),

@@ -46,6 +46,7 @@ int conv_c32_1_bwd(const float*, const void*, const float*, void*, float*, float
 long long colsum_scratch_floats(int);
 int colsum_bf16(const void*, float*, float*, long long, int, cudaStream_t);
 int colsum_bf16_static(const void*, float*, long long, int, cudaStream_t);
+int colsum_f32(const float*, float*, float*, long long, int, cudaStream_t);
 int lnlstm_fwd(const float*, const float*, const float*, const void*, const float*, const float*, const float*,
                const float*, float*, float*, float*, float*, float*, int, int, int, cudaStream_t);
 int lnlstm_bwd(const float*, const float*, const float*, const float*, const float*, const float*, const float*,
@@ -231,6 +232,9 @@ int as_maxpool2_bwd_bf16(const void* in, const void* dout, void* din, int64_t R,
   return as::maxpool2_bwd(in, dout, din, R, H, W, C, ST(stream));
 }
 
+int as_colsum_f32(const float* x, float* out, float* scratch, int64_t rows, int C, void* stream) {
+  return as::colsum_f32(x, out, scratch, rows, C, ST(stream));
+}
 int as_colsum_bf16_static(const void* x, float* out, int64_t rows, int C, void* stream) {
   return as::colsum_bf16_static(x, out, rows, C, ST(stream));
 }

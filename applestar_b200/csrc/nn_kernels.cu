@@ -93,6 +93,106 @@ layer_norm_bwd_kernel(const float* __restrict__ dy32, const __nv_bfloat16* __res
   }
 }
 
+// 128-bit variants for C % 128 == 0 (256 / 384 / 1536): each lane owns float4 columns lane + 32 i.
+template <int V>
+__global__ void __launch_bounds__(256)
+layer_norm_fwd_v4_kernel(const float* __restrict__ x, const float* __restrict__ res, const float* __restrict__ gamma,
+                         const float* __restrict__ beta, float* __restrict__ y32, __nv_bfloat16* __restrict__ y16,
+                         float* __restrict__ stats, long long rows, int C, int relu) {
+  const int lane = threadIdx.x & 31;
+  const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long row = warp_global; row < rows; row += warps_total) {
+    float4 v[V];
+    const float4* xr = reinterpret_cast<const float4*>(x + row * C);
+    const float4* rr = res ? reinterpret_cast<const float4*>(res + row * C) : nullptr;
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      float4 t = __ldg(xr + lane + i * 32);
+      if (rr) { const float4 u = __ldg(rr + lane + i * 32); t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w; }
+      v[i] = t;
+      s += t.x + t.y + t.z + t.w;
+    }
+    const float mean = warp_sum(s) / (float)C;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      const float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+      q += a * a + b * b + c * c + d * d;
+    }
+    const float rstd = rsqrtf(warp_sum(q) / (float)C + 1e-5f);
+    if (lane == 0 && stats) { stats[row * 2] = mean; stats[row * 2 + 1] = rstd; }
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      const float4 g = __ldg(reinterpret_cast<const float4*>(gamma) + lane + i * 32);
+      const float4 b = __ldg(reinterpret_cast<const float4*>(beta) + lane + i * 32);
+      float4 o;
+      o.x = (v[i].x - mean) * rstd * g.x + b.x; o.y = (v[i].y - mean) * rstd * g.y + b.y;
+      o.z = (v[i].z - mean) * rstd * g.z + b.z; o.w = (v[i].w - mean) * rstd * g.w + b.w;
+      if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+      if (y32) reinterpret_cast<float4*>(y32 + row * C)[lane + i * 32] = o;
+      if (y16) {
+        __nv_bfloat162 h0 = __floats2bfloat162_rn(o.x, o.y), h1 = __floats2bfloat162_rn(o.z, o.w);
+        uint2 u;
+        u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
+        reinterpret_cast<uint2*>(y16 + row * C)[lane + i * 32] = u;
+      }
+    }
+  }
+}
+
+template <int V>
+__global__ void __launch_bounds__(256)
+layer_norm_bwd_v4_kernel(const float* __restrict__ dy32, const __nv_bfloat16* __restrict__ dy16,
+                         const float* __restrict__ x, const float* __restrict__ res, const float* __restrict__ gamma,
+                         const float* __restrict__ beta, const float* __restrict__ stats, float* __restrict__ dx,
+                         long long rows, int C, int relu) {
+  const int lane = threadIdx.x & 31;
+  const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long row = warp_global; row < rows; row += warps_total) {
+    const float mean = stats[row * 2], rstd = stats[row * 2 + 1];
+    float4 xh[V], dg[V];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      const int idx = lane + i * 32;
+      float4 t = __ldg(reinterpret_cast<const float4*>(x + row * C) + idx);
+      if (res) { const float4 u = __ldg(reinterpret_cast<const float4*>(res + row * C) + idx); t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w; }
+      float4 a = make_float4((t.x - mean) * rstd, (t.y - mean) * rstd, (t.z - mean) * rstd, (t.w - mean) * rstd);
+      float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (dy32) g = __ldg(reinterpret_cast<const float4*>(dy32 + row * C) + idx);
+      if (dy16) {
+        const uint2 u = *(reinterpret_cast<const uint2*>(dy16 + row * C) + idx);
+        const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.x));
+        const float2 f1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.y));
+        g.x += f0.x; g.y += f0.y; g.z += f1.x; g.w += f1.y;
+      }
+      const float4 gm = __ldg(reinterpret_cast<const float4*>(gamma) + idx);
+      if (relu) {
+        const float4 bt = __ldg(reinterpret_cast<const float4*>(beta) + idx);
+        if (a.x * gm.x + bt.x <= 0.f) g.x = 0.f;
+        if (a.y * gm.y + bt.y <= 0.f) g.y = 0.f;
+        if (a.z * gm.z + bt.z <= 0.f) g.z = 0.f;
+        if (a.w * gm.w + bt.w <= 0.f) g.w = 0.f;
+      }
+      const float4 b = make_float4(g.x * gm.x, g.y * gm.y, g.z * gm.z, g.w * gm.w);
+      xh[i] = a; dg[i] = b;
+      s1 += b.x + b.y + b.z + b.w;
+      s2 += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
+    }
+    const float m1 = warp_sum(s1) / (float)C, m2 = warp_sum(s2) / (float)C;
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      float4 o;
+      o.x = rstd * (dg[i].x - m1 - xh[i].x * m2); o.y = rstd * (dg[i].y - m1 - xh[i].y * m2);
+      o.z = rstd * (dg[i].z - m1 - xh[i].z * m2); o.w = rstd * (dg[i].w - m1 - xh[i].w * m2);
+      reinterpret_cast<float4*>(dx + row * C)[lane + i * 32] = o;
+    }
+  }
+}
+
 // dgamma[c] = sum_r g * xhat, dbeta[c] = sum_r g.  Block = 32 columns x 8 row lanes over one row chunk (128-byte
 // coalesced row segments), shared-memory reduce over the row lanes, per-chunk partials, then a fixed-order reduce
 // over chunks (deterministic, no atomics).
@@ -170,6 +270,14 @@ int layer_norm_fwd(const float* x, const float* res, const float* gamma, const f
   if (C <= 0 || C > 32 * 48) return AS_ESIZE;
   if (!x || !gamma || !beta || (!y32 && !y16)) return AS_EINVAL;
   const int grid = ln_grid(rows);
+  const bool al = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(res) | reinterpret_cast<uintptr_t>(y32) |
+                    reinterpret_cast<uintptr_t>(gamma) | reinterpret_cast<uintptr_t>(beta)) & 15) == 0 &&
+                  (reinterpret_cast<uintptr_t>(y16) & 7) == 0;
+  __nv_bfloat16* y16b = reinterpret_cast<__nv_bfloat16*>(y16);
+  if (al && C == 256) layer_norm_fwd_v4_kernel<2><<<grid, 256, 0, st>>>(x, res, gamma, beta, y32, y16b, stats, rows, C, relu);
+  else if (al && C == 384) layer_norm_fwd_v4_kernel<3><<<grid, 256, 0, st>>>(x, res, gamma, beta, y32, y16b, stats, rows, C, relu);
+  else if (al && C == 1536) layer_norm_fwd_v4_kernel<12><<<grid, 256, 0, st>>>(x, res, gamma, beta, y32, y16b, stats, rows, C, relu);
+  else
   LN_DISPATCH(layer_norm_fwd_kernel, x, res, gamma, beta, y32, reinterpret_cast<__nv_bfloat16*>(y16), stats, rows, C, relu);
   AS_LAUNCH_CHECK();
   return AS_OK;
@@ -187,6 +295,13 @@ int layer_norm_bwd(const float* dy32, const void* dy16, const float* x, const fl
   const __nv_bfloat16* d16 = reinterpret_cast<const __nv_bfloat16*>(dy16);
   if (dx) {
     const int grid = ln_grid(rows);
+    const bool al = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(res) | reinterpret_cast<uintptr_t>(dy32) |
+                      reinterpret_cast<uintptr_t>(gamma) | reinterpret_cast<uintptr_t>(beta) | reinterpret_cast<uintptr_t>(dx)) & 15) == 0 &&
+                    (reinterpret_cast<uintptr_t>(dy16) & 7) == 0;
+    if (al && C == 256) layer_norm_bwd_v4_kernel<2><<<grid, 256, 0, st>>>(dy32, d16, x, res, gamma, beta, stats, dx, rows, C, relu);
+    else if (al && C == 384) layer_norm_bwd_v4_kernel<3><<<grid, 256, 0, st>>>(dy32, d16, x, res, gamma, beta, stats, dx, rows, C, relu);
+    else if (al && C == 1536) layer_norm_bwd_v4_kernel<12><<<grid, 256, 0, st>>>(dy32, d16, x, res, gamma, beta, stats, dx, rows, C, relu);
+    else
     LN_DISPATCH(layer_norm_bwd_kernel, dy32, d16, x, res, gamma, beta, stats, dx, rows, C, relu);
     AS_LAUNCH_CHECK();
   }

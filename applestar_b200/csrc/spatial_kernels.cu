@@ -504,19 +504,35 @@ __global__ void conv_c32_1_wgrad_kernel(const float* __restrict__ dy, const __nv
   const long long total = R * (long long)H * W;
   const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
-#pragma unroll 4
-  for (long long p = warp_global; p < total; p += warps_total) {
-    const int x = (int)(p % W);
-    const long long q = p / W;
-    const int y = (int)(q % H);
-    const long long r = q / H;
-    const float g = __ldg(dy + p) * inv_temp;
-    accb += g;
-    const __nv_bfloat16* base = in + ((r * (H + 2) + y) * (long long)(W + 2) + x) * 32 + lane;
+  // two pixels per iteration: 18 independent 64-byte row reads in flight per warp
+  for (long long p0 = warp_global * 2; p0 < total; p0 += warps_total * 2) {
+    float g[2];
+    const __nv_bfloat16* base[2];
 #pragma unroll
-    for (int ky = 0; ky < 3; ++ky)
+    for (int u = 0; u < 2; ++u) {
+      const long long p = p0 + u;
+      const bool ok = p < total;
+      const long long pc = ok ? p : 0;
+      const int x = (int)(pc % W);
+      const long long q = pc / W;
+      const int y = (int)(q % H);
+      const long long r = q / H;
+      g[u] = ok ? __ldg(dy + pc) * inv_temp : 0.f;
+      base[u] = in + ((r * (H + 2) + y) * (long long)(W + 2) + x) * 32 + lane;
+    }
+    float v[2][9];
 #pragma unroll
-      for (int kx = 0; kx < 3; ++kx) acc[ky * 3 + kx] += g * bf2f(base[((long long)ky * (W + 2) + kx) * 32]);
+    for (int u = 0; u < 2; ++u)
+#pragma unroll
+      for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+        for (int kx = 0; kx < 3; ++kx) v[u][ky * 3 + kx] = bf2f(base[u][((long long)ky * (W + 2) + kx) * 32]);
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      accb += g[u];
+#pragma unroll
+      for (int t = 0; t < 9; ++t) acc[t] += g[u] * v[u][t];
+    }
   }
   __shared__ float red[8][9 * 32 + 1];
 #pragma unroll
@@ -538,7 +554,7 @@ __global__ void conv_c32_1_wreduce_kernel(const float* __restrict__ partial, int
   if (i < 288) dw[i] = s; else if (db) db[0] = s;
 }
 
-constexpr int kC321Blocks = 148 * 4;
+constexpr int kC321Blocks = 148 * 16;
 long long conv_c32_1_scratch_floats() { return (long long)kC321Blocks * 289; }
 
 int conv_c32_1_fwd(const void* in, const float* w, const float* bias, float* out, long long R, int H, int W, float inv_temp,
@@ -589,6 +605,26 @@ colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ p
     partial[(long long)blockIdx.y * C + c + 1] = t1;
   }
 }
+__global__ void __launch_bounds__(256)
+colsum_partial_f32_kernel(const float* __restrict__ x, float* __restrict__ partial, long long rows, int C, int chunks) {
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + cx;
+  const long long per = (rows + chunks - 1) / chunks;
+  const long long r0 = blockIdx.y * per, r1 = (r0 + per < rows) ? r0 + per : rows;
+  float s0 = 0.f;
+  if (c < C)
+    for (long long r = r0 + ry; r < r1; r += 8) s0 += __ldg(x + r * C + c);
+  __shared__ float sa[8][33];
+  sa[ry][cx] = s0;
+  __syncthreads();
+  if (ry == 0 && c < C) {
+    float t0 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t0 += sa[i][cx];
+    partial[(long long)blockIdx.y * C + c] = t0;
+  }
+}
+
 __global__ void colsum_reduce_kernel(const float* __restrict__ partial, float* __restrict__ out, int C, int chunks) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
@@ -872,6 +908,19 @@ int maxpool2_bwd(const void* in, const void* dout, void* din, long long R, int H
   AS_LAUNCH_CHECK();
   const long long ring = R * (long long)(2 * (W + 2) + 2 * H) * (C / 8);
   zero_border_kernel<<<ew_grid(ring, 1), 256, 0, st>>>((__nv_bfloat16*)din, R, H, W, C);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+int colsum_f32(const float* x, float* out, float* scratch, long long rows, int C, cudaStream_t st) {
+  if (rows <= 0 || C <= 0) return AS_ESIZE;
+  if (!x || !out || !scratch) return AS_EINVAL;
+  long long want = (rows + 255) / 256;
+  const int chunks = (int)(want < 1 ? 1 : (want > kColsumChunks ? kColsumChunks : want));
+  dim3 g((C + 31) / 32, chunks);
+  colsum_partial_f32_kernel<<<g, 256, 0, st>>>(x, scratch, rows, C, chunks);
+  AS_LAUNCH_CHECK();
+  colsum_reduce_kernel<<<(C + 63) / 64, 64, 0, st>>>(scratch, out, C, chunks);
   AS_LAUNCH_CHECK();
   return AS_OK;
 }

@@ -148,8 +148,23 @@ class LinearFn(torch.autograd.Function):
             if K8 != ctx.wk:
                 dw = dw[:, :ctx.wk]
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = dy2.sum(dim=0, dtype=torch.float32)
+            db = column_sum(dy2)
         return dx, dw, db, None, None, None
+
+
+def column_sum(x):
+    """fp32 column sums of a [rows, C] fp32 / bf16 matrix (bias gradients), deterministic two-stage reduction."""
+    x = x.contiguous()
+    rows, Cc = x.shape
+    if x.dtype == torch.bfloat16 and Cc % 2:
+        return x.sum(dim=0, dtype=torch.float32)
+    out = torch.empty(Cc, dtype=torch.float32, device=x.device)
+    scratch = torch.empty(_lib.lib().as_colsum_scratch_floats(Cc), dtype=torch.float32, device=x.device)
+    name = 'as_colsum_bf16' if x.dtype == torch.bfloat16 else 'as_colsum_f32'
+    if x.dtype not in (torch.bfloat16, torch.float32):
+        x = x.float()
+    _lib.call(name, x.data_ptr(), out.data_ptr(), scratch.data_ptr(), rows, Cc, _lib.stream_ptr())
+    return out
 
 
 def relu_backward(dy, y):
