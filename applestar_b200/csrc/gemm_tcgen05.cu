@@ -62,7 +62,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2, const GemmDev p) {
   using L = SmemLayout<BN>;
   constexpr int kStages = L::kStages;
-  constexpr uint32_t kTmemCols = (2 * BN <= 32) ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
+  // accumulator ring in TMEM: narrow tiles have few k-blocks per tile, so the MMA issuer may run up to 8 tiles ahead
+  // of the epilogue; for BN < 128 the two epilogue warp sets also alternate tiles instead of splitting columns
+  constexpr int kAcc = (BN >= 256) ? 2 : (BN >= 128 ? 4 : 8);
+  constexpr bool kSplitCols = BN >= 128;
+  constexpr uint32_t kTmemCols = kAcc * BN;
+  static_assert(kTmemCols == 512 || kTmemCols == 256, "TMEM allocation must be a power of two <= 512");
 
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment for the 128B swizzle; pointer arithmetic (not an integer round trip) keeps the shared
@@ -72,8 +77,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(bar_base);
   uint64_t* empty_bar = full_bar + kStages;
   uint64_t* tmem_full = empty_bar + kStages;
-  uint64_t* tmem_empty = tmem_full + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* tmem_empty = tmem_full + kAcc;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + kAcc);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -87,9 +92,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
     }
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < kAcc; ++i) {
       mbar_init(&tmem_full[i], 1);
-      mbar_init(&tmem_empty[i], kEpiWarps);
+      mbar_init(&tmem_empty[i], kSplitCols ? kEpiWarps : kEpiWarps / 2);
     }
     mbar_fence_init();
   }
@@ -160,9 +165,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                              ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
       int stage = 0;
       uint32_t phase = 0;
-      int acc = 0;
-      uint32_t acc_phase = 0;
-      for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      uint32_t it = 0;
+      for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        const int acc = (int)(it % kAcc);
+        const uint32_t acc_phase = (it / kAcc) & 1u;
         const int split = (int)(tile / tiles_per_split);
         const int kb_begin = split * p.kb_per_split;
         const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
@@ -186,7 +192,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
         umma_commit(&tmem_full[acc]);      // accumulator complete -> epilogue
-        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
   } else if (warp >= 4) {
@@ -200,12 +205,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int half = e >> 2;
     float* stg = reinterpret_cast<float*>(bar_base + L::kBarBytes) + e * (32 * kStgPitch);
     constexpr int kChunks = BN / 32;
-    constexpr int kPerHalf = kChunks >= 2 ? kChunks / 2 : 1;
-    const int c_begin = half * kPerHalf;
-    const int c_end = (kChunks >= 2) ? c_begin + kPerHalf : (half == 0 ? 1 : 0);
-    int acc = 0;
-    uint32_t acc_phase = 0;
-    for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    const int c_begin = kSplitCols ? half * (kChunks / 2) : 0;
+    const int c_end = kSplitCols ? c_begin + kChunks / 2 : kChunks;
+    uint32_t it = 0;
+    for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      if (!kSplitCols && (int)(it & 1u) != half) continue;     // narrow tiles: this tile belongs to the other warp set
+      const int acc = (int)(it % kAcc);
+      const uint32_t acc_phase = (it / kAcc) & 1u;
       long long t = tile;
       const int n_blk = (int)(t % p.n_blocks); t /= p.n_blocks;
       const int m_blk = (int)(t % p.m_blocks); t /= p.m_blocks;
@@ -234,9 +240,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           const int yy = q / p.img_w, xx = q - yy * p.img_w;
           border = (yy == 0) | (yy == p.img_h - 1) | (xx == 0) | (xx == p.img_w - 1);
         }
-        constexpr int kHalfCols = (BN >= 128) ? BN / 2 : BN;          // narrow tiles: one warp set takes all columns
-        const int col_begin = (BN >= 128) ? half * kHalfCols : 0;
-        const int col_end = (BN >= 128) ? col_begin + kHalfCols : (half == 0 ? BN : 0);
+        constexpr int kHalfCols = kSplitCols ? BN / 2 : BN;           // narrow tiles: one warp set takes all columns
+        const int col_begin = kSplitCols ? half * kHalfCols : 0;
+        const int col_end = col_begin + kHalfCols;
         const bool need_bf16 = !f32_out || p.C2 != nullptr;
         const CUtensorMap* map16 = f32_out ? &tmC2 : &tmC;
 #pragma unroll 1
@@ -423,7 +429,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[acc]);
-      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   }
 

@@ -158,7 +158,7 @@ def gemm_flops_hook(records):
         else:
             R, H, W, Cin, Cout, taps = a[4], a[5], a[6], a[7], a[8], a[9]
             fl = 2.0 * R * (H + 2) * (W + 2) * Cin * Cout * taps
-        records.append((e0, e1, fl))
+        records.append((e0, e1, fl, (name,) + tuple(a[4:16])))
     _lib.call = hooked
     return orig
 
@@ -246,8 +246,16 @@ def run_ours(args):
     step_fn._run(resident)                                # eager (un-captured) so that every launch can be bracketed
     torch.cuda.synchronize()
     _lib.call = orig
-    g_ms = sum(e0.elapsed_time(e1) for e0, e1, _ in records)
-    g_fl = sum(fl for _, _, fl in records)
+    g_ms = sum(r[0].elapsed_time(r[1]) for r in records)
+    g_fl = sum(r[2] for r in records)
+    if os.environ.get('APPLESTAR_GEMM_DUMP') and rank == 0:
+        agg = {}
+        for r in records:
+            k = r[3]
+            t = agg.setdefault(k, [0, 0.0, 0.0])
+            t[0] += 1; t[1] += r[0].elapsed_time(r[1]); t[2] += r[2]
+        for k, t in sorted(agg.items(), key=lambda kv: -kv[1][1])[:45]:
+            print('GEMM %-22s args=%s n=%d ms=%.3f TF/s=%.0f' % (k[0], k[1:], t[0], t[1], t[2] / t[1] / 1e9), file=sys.stderr)
     hbm, tf_burst, tf_sus, which = peaks()
     achieved = g_fl / (g_ms * 1e-3) / 1e12 if g_ms > 0 else 0.0
 
