@@ -49,8 +49,9 @@ int colsum_bf16_static(const void*, float*, long long, int, cudaStream_t);
 int colsum_f32(const float*, float*, float*, long long, int, cudaStream_t);
 int lnlstm_fwd(const float*, const float*, const float*, const void*, const float*, const float*, const float*,
                const float*, float*, float*, float*, float*, float*, int, int, int, cudaStream_t);
+bool lnlstm_cluster_ok(int);
 int lnlstm_bwd(const float*, const float*, const float*, const float*, const float*, const float*, const float*,
-               const float*, const void*, const float*, const float*, const float*, const float*, const float*,
+               const float*, const void*, const void*, const float*, const float*, const float*, const float*, const float*,
                const float*, const float*, float*, float*, float*, float*, float*, int, int, int, cudaStream_t);
 int spatial_features(const void* const*, const void* const*, int, const float*, void*, long long, int, int, int,
                      cudaStream_t);
@@ -64,10 +65,10 @@ int maxpool2_bwd(const void*, const void*, void*, long long, int, int, int, cuda
 
 extern "C" {
 
-int as_abi_version(void) { return 2; }
+int as_abi_version(void) { return 3; }
 
 // diagnostics only (not part of the public header): 0 normal, 1 GEMM epilogue skips global stores, 2 only drains TMEM
-int as_debug_gemm_mode(int mode) { as::g_gemm_debug = mode & 3; as::g_gemm_no_tma_store = (mode >> 2) & 1; return 0; }
+int as_debug_gemm_mode(int mode) { as::g_gemm_debug = mode & 7; as::g_gemm_no_tma_store = (mode >> 3) & 1; return 0; }
 
 int as_scatter_connection_fwd(const float* emb, const void* xs, const void* ys, int idx_bytes,
                               const int64_t* entity_num, float* out, int64_t R, int N, int D, int H, int W, int cover,
@@ -260,13 +261,14 @@ int as_lnlstm_fwd(const float* gi, const float* h0, const float* c0, const void*
                         ST(stream));
 }
 int as_lnlstm_bwd(const float* gi, const float* h0, const float* c0, const float* y, const float* c_all,
-                  const float* u_all, const float* z_all, const float* stats, const void* whh_t, const float* ln_h_w,
-                  const float* ln_h_b, const float* ln_c_w, const float* ln_c_b, const float* dy, const float* dhT,
-                  const float* dcT, float* dgi, float* du, float* dh0, float* dc0, float* dparam, int T, int B, int H,
-                  void* stream) {
-  return as::lnlstm_bwd(gi, h0, c0, y, c_all, u_all, z_all, stats, whh_t, ln_h_w, ln_h_b, ln_c_w, ln_c_b, dy, dhT, dcT,
-                        dgi, du, dh0, dc0, dparam, T, B, H, ST(stream));
+                  const float* u_all, const float* z_all, const float* stats, const void* whh_t, const void* whh,
+                  const float* ln_h_w, const float* ln_h_b, const float* ln_c_w, const float* ln_c_b, const float* dy,
+                  const float* dhT, const float* dcT, float* dgi, float* du, float* dh0, float* dc0, float* dparam, int T,
+                  int B, int H, void* stream) {
+  return as::lnlstm_bwd(gi, h0, c0, y, c_all, u_all, z_all, stats, whh_t, whh, ln_h_w, ln_h_b, ln_c_w, ln_c_b, dy, dhT,
+                        dcT, dgi, du, dh0, dc0, dparam, T, B, H, ST(stream));
 }
+int as_lnlstm_cluster_ok(int H) { return as::lnlstm_cluster_ok(H) ? 1 : 0; }
 
 int as_softmax_fwd(const float* scores, const int64_t* key_len, void* probs, int64_t groups, int Nq, int Nk,
                    int groups_per_len, void* stream) {

@@ -245,63 +245,117 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         const int col_end = col_begin + kHalfCols;
         const bool need_bf16 = !f32_out || p.C2 != nullptr;
         const CUtensorMap* map16 = f32_out ? &tmC2 : &tmC;
+        // Software pipeline over 64-column steps: the tcgen05.ld pair of the NEXT step is issued as soon as the
+        // current step's accumulators have been consumed, so its latency hides behind the staging writes and stores.
+        uint32_t v0[32], v1[32];
+        auto issue = [&](int col) {
+          if (col < col_end && n0 + col < p.N) tmem_ld32(t_row + col, v0);
+          if (col + 32 < col_end && n0 + col + 32 < p.N) tmem_ld32(t_row + col + 32, v1);
+        };
+        // alpha / bias / ReLU / border on one 32-column chunk.  Every runtime option is tested once per chunk (warp
+        // uniform), never per element.
+        auto finish = [&](const uint32_t (&v)[32], int c, float (&f)[32]) {
+          const int gc = n0 + c;
+          if (p.bias == nullptr) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
+          } else if (gc + 32 <= p.N && (reinterpret_cast<uintptr_t>(p.bias) & 15) == 0) {
+            const float4* b4 = reinterpret_cast<const float4*>(p.bias + gc);    // same address in every lane: broadcast
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              const float4 bq = __ldg(b4 + q);
+              f[4 * q] = fmaf(__uint_as_float(v[4 * q]), p.alpha, bq.x);
+              f[4 * q + 1] = fmaf(__uint_as_float(v[4 * q + 1]), p.alpha, bq.y);
+              f[4 * q + 2] = fmaf(__uint_as_float(v[4 * q + 2]), p.alpha, bq.z);
+              f[4 * q + 3] = fmaf(__uint_as_float(v[4 * q + 3]), p.alpha, bq.w);
+            }
+          } else {
+            const float bl = (gc + lane < p.N) ? __ldg(p.bias + gc + lane) : 0.f;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = fmaf(__uint_as_float(v[j]), p.alpha, __shfl_sync(0xffffffffu, bl, j));
+          }
+          if (p.relu) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+          }
+          if (p.img_w > 0) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = border ? 0.f : f[j];
+          }
+        };
+        auto stage32 = [&](const float (&f)[32], int c) {
+          if (p.debug >= 4) return;
+          if (lane == 0) tma_store_wait_read();                       // previous box has left the staging tile
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(sbuf + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+                make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+          if (p.debug < 3) fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0 && p.debug == 0) {
+            tma_store_4d(&tmC, sbuf, n0 + c, row_base, b0, b1);
+            tma_store_commit();
+          }
+        };
+        issue(col_begin);
 #pragma unroll 1
         for (int col = col_begin; col < col_end; col += 64) {
+          const bool has0 = n0 + col < p.N, has1 = (col + 32 < col_end) && (n0 + col + 32 < p.N);   // warp-uniform
+          tmem_ld_wait();
+          if (p.debug == 2 || !has0) { issue(col + 64); continue; }
           uint32_t packed[32];
-          int halves = 0;
+          if (!f32_out) {
+            float f[32];
+            finish(v0, col, f);
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const int c = col + h * 32;
-            if (c < col_end && n0 + c < p.N) {                        // warp-uniform
-              uint32_t v[32];
-              tmem_ld32(t_row + c, v);
-              tmem_ld_wait();
-              if (p.debug != 2) {
-                float bl = 0.f;
-                if (p.bias != nullptr && n0 + c + lane < p.N) bl = __ldg(p.bias + n0 + c + lane);
-                float f[32];
+            for (int j = 0; j < 16; ++j) {
+              __nv_bfloat162 hv = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
+              packed[j] = *reinterpret_cast<uint32_t*>(&hv);
+            }
+            if (has1) {
+              finish(v1, col + 32, f);
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                  float x = __uint_as_float(v[j]) * p.alpha;
-                  if (p.bias != nullptr) x += __shfl_sync(0xffffffffu, bl, j);
-                  if (p.relu) x = fmaxf(x, 0.f);
-                  f[j] = border ? 0.f : x;
-                }
-                if (f32_out) {
-                  if (lane == 0) tma_store_wait_read();               // previous box has left the staging tile
-                  __syncwarp();
-#pragma unroll
-                  for (int j = 0; j < 8; ++j)
-                    *reinterpret_cast<float4*>(sbuf + lane * 128 + ((j ^ (lane & 7)) << 4)) =
-                        make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
-                  fence_proxy_async_smem();
-                  __syncwarp();
-                  if (lane == 0 && p.debug == 0) {
-                    tma_store_4d(&tmC, sbuf, n0 + c, row_base, b0, b1);
-                    tma_store_commit();
-                  }
-                }
-                if (need_bf16) {
-#pragma unroll
-                  for (int j = 0; j < 16; ++j) {
-                    __nv_bfloat162 hv = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
-                    packed[h * 16 + j] = *reinterpret_cast<uint32_t*>(&hv);
-                  }
-                }
-                halves = h + 1;
+              for (int j = 0; j < 16; ++j) {
+                __nv_bfloat162 hv = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
+                packed[16 + j] = *reinterpret_cast<uint32_t*>(&hv);
               }
             }
+            issue(col + 64);
+          } else {
+            float f[32];
+            finish(v0, col, f);
+            if (need_bf16) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                __nv_bfloat162 hv = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
+                packed[j] = *reinterpret_cast<uint32_t*>(&hv);
+              }
+            }
+            stage32(f, col);
+            if (has1) {
+              finish(v1, col + 32, f);
+              if (need_bf16) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                  __nv_bfloat162 hv = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
+                  packed[16 + j] = *reinterpret_cast<uint32_t*>(&hv);
+                }
+              }
+              stage32(f, col + 32);
+            }
+            issue(col + 64);
           }
-          if (need_bf16 && halves > 0) {
+          if (need_bf16 && p.debug < 4) {
             if (lane == 0) tma_store_wait_read();
             __syncwarp();
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-              if (j < halves * 4)
+              if (j < 4 || has1)
                 *reinterpret_cast<uint4*>(sbuf + lane * 128 + ((j ^ (lane & 7)) << 4)) =
                     make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
             }
-            fence_proxy_async_smem();
+            if (p.debug < 3) fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0 && p.debug == 0) {
               tma_store_4d(map16, sbuf, n0 + col, row_base, b0, b1);

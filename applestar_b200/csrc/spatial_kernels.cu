@@ -398,8 +398,8 @@ int loc_cat_bwd(const void* dcat, const float* emb, const void* skip, float* dem
 
 // ------------------------------------------------------------------------------------------ final 3x3 conv, 32 -> 1
 // y[r,y,x] = (b + sum_{tap,c} w[tap][c] * in[r, y+ky, x+kx, c]) / T   (in padded NHWC bf16, C = 32; y fp32 unpadded =
-// the location logits).  Thread per output pixel: each tap is 64 contiguous bytes per thread (four 16-byte loads),
-// neighbouring threads read neighbouring pixels; weights are broadcast from shared memory.
+// the location logits).  Four threads per output pixel, eight channels each: every tap is ONE 16-byte load per thread
+// and a warp's load covers 512 contiguous bytes (8 pixels); two xor-shuffles finish the channel sum.
 __device__ __forceinline__ void unpack8(const uint4& q, float* f) {
   const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&q);
 #pragma unroll
@@ -412,36 +412,42 @@ __device__ __forceinline__ void unpack8(const uint4& q, float* f) {
 __global__ void __launch_bounds__(256)
 conv_c32_1_fwd_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict__ w, const float* __restrict__ bias,
                       float* __restrict__ out, long long R, int H, int W, float inv_temp) {
-  __shared__ __align__(16) float sw[288];
-  for (int i = threadIdx.x; i < 288; i += blockDim.x) sw[i] = w[i];
-  __syncthreads();
+  const int cg = threadIdx.x & 3;
+  float wr[9][8];                                              // this thread's 8 channels of every tap
+#pragma unroll
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int c = 0; c < 8; ++c) wr[t][c] = __ldg(w + t * 32 + cg * 8 + c);
   const float b = bias ? bias[0] : 0.f;
   const long long total = R * (long long)H * W;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += stride) {
-    const int x = (int)(p % W);
-    const long long q = p / W;
+  const long long stride = ((long long)gridDim.x * blockDim.x) >> 2;
+  const long long first = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 2;
+  const long long total_pad = (total + 7) & ~7LL;              // whole warps stay in the loop for the shuffles
+  for (long long p = first; p < total_pad; p += stride) {
+    const bool ok = p < total;
+    const long long pc = ok ? p : 0;
+    const int x = (int)(pc % W);
+    const long long q = pc / W;
     const int y = (int)(q % H);
     const long long r = q / H;
-    const __nv_bfloat16* base = in + ((r * (H + 2) + y) * (long long)(W + 2) + x) * 32;
+    const __nv_bfloat16* base = in + ((r * (H + 2) + y) * (long long)(W + 2) + x) * 32 + cg * 8;
+    uint4 v[9];
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx)
+        v[ky * 3 + kx] = __ldg(reinterpret_cast<const uint4*>(base + ((long long)ky * (W + 2) + kx) * 32));
     float acc = 0.f;
 #pragma unroll
-    for (int ky = 0; ky < 3; ++ky) {
+    for (int t = 0; t < 9; ++t) {
+      float f[8];
+      unpack8(v[t], f);
 #pragma unroll
-      for (int kx = 0; kx < 3; ++kx) {
-        const uint4* src = reinterpret_cast<const uint4*>(base + ((long long)ky * (W + 2) + kx) * 32);
-        const float* wt = sw + (ky * 3 + kx) * 32;
-#pragma unroll
-        for (int c4 = 0; c4 < 4; ++c4) {
-          float f[8];
-          unpack8(__ldg(src + c4), f);
-          const float4 w0 = *reinterpret_cast<const float4*>(wt + c4 * 8);
-          const float4 w1 = *reinterpret_cast<const float4*>(wt + c4 * 8 + 4);
-          acc += f[0] * w0.x + f[1] * w0.y + f[2] * w0.z + f[3] * w0.w + f[4] * w1.x + f[5] * w1.y + f[6] * w1.z + f[7] * w1.w;
-        }
-      }
+      for (int c = 0; c < 8; ++c) acc += f[c] * wr[t][c];
     }
-    out[p] = (acc + b) * inv_temp;
+    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+    if (ok && cg == 0) out[p] = (acc + b) * inv_temp;
   }
 }
 
@@ -494,49 +500,56 @@ conv_c32_1_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ 
     }
   }
 }
-// dw[tap][c] = sum_p dy[p] in[p+tap][c];  db = sum dy  -> per-block partials [blocks][9*32+1]
-__global__ void conv_c32_1_wgrad_kernel(const float* __restrict__ dy, const __nv_bfloat16* __restrict__ in,
-                                        float* __restrict__ partial, long long R, int H, int W, float inv_temp) {
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  float acc[9], accb = 0.f;
+// dw[tap][c] = sum_p dy[p] in[p+tap][c];  db = sum dy  -> per-block partials [blocks][9*32+1].  Same thread mapping as
+// the forward (pixel slot x 8-channel group): 72 fp32 accumulators per thread, coalesced 16-byte tap loads, then a
+// shuffle reduction over the warp's eight pixel slots and a shared-memory reduction over the block's warps.
+__global__ void __launch_bounds__(256)
+conv_c32_1_wgrad_kernel(const float* __restrict__ dy, const __nv_bfloat16* __restrict__ in,
+                        float* __restrict__ partial, long long R, int H, int W, float inv_temp) {
+  const int cg = threadIdx.x & 3, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  float acc[9][8], accb = 0.f;
 #pragma unroll
-  for (int t = 0; t < 9; ++t) acc[t] = 0.f;
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int c = 0; c < 8; ++c) acc[t][c] = 0.f;
   const long long total = R * (long long)H * W;
-  const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
-  // two pixels per iteration: 18 independent 64-byte row reads in flight per warp
-  for (long long p0 = warp_global * 2; p0 < total; p0 += warps_total * 2) {
-    float g[2];
-    const __nv_bfloat16* base[2];
+  const long long stride = ((long long)gridDim.x * blockDim.x) >> 2;
+  for (long long p = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 2; p < total; p += stride) {
+    const int x = (int)(p % W);
+    const long long q = p / W;
+    const int y = (int)(q % H);
+    const long long r = q / H;
+    const float g = __ldg(dy + p) * inv_temp;
+    const __nv_bfloat16* base = in + ((r * (H + 2) + y) * (long long)(W + 2) + x) * 32 + cg * 8;
+    uint4 v[9];
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
-      const long long p = p0 + u;
-      const bool ok = p < total;
-      const long long pc = ok ? p : 0;
-      const int x = (int)(pc % W);
-      const long long q = pc / W;
-      const int y = (int)(q % H);
-      const long long r = q / H;
-      g[u] = ok ? __ldg(dy + pc) * inv_temp : 0.f;
-      base[u] = in + ((r * (H + 2) + y) * (long long)(W + 2) + x) * 32 + lane;
-    }
-    float v[2][9];
+    for (int ky = 0; ky < 3; ++ky)
 #pragma unroll
-    for (int u = 0; u < 2; ++u)
+      for (int kx = 0; kx < 3; ++kx)
+        v[ky * 3 + kx] = __ldg(reinterpret_cast<const uint4*>(base + ((long long)ky * (W + 2) + kx) * 32));
+    accb += g;
 #pragma unroll
-      for (int ky = 0; ky < 3; ++ky)
+    for (int t = 0; t < 9; ++t) {
+      float f[8];
+      unpack8(v[t], f);
 #pragma unroll
-        for (int kx = 0; kx < 3; ++kx) v[u][ky * 3 + kx] = bf2f(base[u][((long long)ky * (W + 2) + kx) * 32]);
-#pragma unroll
-    for (int u = 0; u < 2; ++u) {
-      accb += g[u];
-#pragma unroll
-      for (int t = 0; t < 9; ++t) acc[t] += g[u] * v[u][t];
+      for (int c = 0; c < 8; ++c) acc[t][c] += g * f[c];
     }
   }
   __shared__ float red[8][9 * 32 + 1];
 #pragma unroll
-  for (int t = 0; t < 9; ++t) red[wid][t * 32 + lane] = acc[t];
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      float a = acc[t][c];
+      a += __shfl_xor_sync(0xffffffffu, a, 4);
+      a += __shfl_xor_sync(0xffffffffu, a, 8);
+      a += __shfl_xor_sync(0xffffffffu, a, 16);
+      if (lane < 4) red[wid][t * 32 + cg * 8 + c] = a;
+    }
+  accb += __shfl_xor_sync(0xffffffffu, accb, 4);
+  accb += __shfl_xor_sync(0xffffffffu, accb, 8);
+  accb += __shfl_xor_sync(0xffffffffu, accb, 16);
   if (lane == 0) red[wid][288] = accb;
   __syncthreads();
   for (int i = threadIdx.x; i < 289; i += blockDim.x) {
@@ -554,14 +567,14 @@ __global__ void conv_c32_1_wreduce_kernel(const float* __restrict__ partial, int
   if (i < 288) dw[i] = s; else if (db) db[0] = s;
 }
 
-constexpr int kC321Blocks = 148 * 16;
+constexpr int kC321Blocks = 148 * 8;
 long long conv_c32_1_scratch_floats() { return (long long)kC321Blocks * 289; }
 
 int conv_c32_1_fwd(const void* in, const float* w, const float* bias, float* out, long long R, int H, int W, float inv_temp,
                    cudaStream_t st) {
   if (R <= 0) return AS_OK;
   if (!in || !w || !out) return AS_EINVAL;
-  conv_c32_1_fwd_kernel<<<ew_grid(R * (long long)H * W, 1), 256, 0, st>>>((const __nv_bfloat16*)in, w, bias, out, R, H, W, inv_temp);
+  conv_c32_1_fwd_kernel<<<ew_grid(R * (long long)H * W * 4, 1), 256, 0, st>>>((const __nv_bfloat16*)in, w, bias, out, R, H, W, inv_temp);
   AS_LAUNCH_CHECK();
   return AS_OK;
 }
@@ -579,7 +592,60 @@ int conv_c32_1_bwd(const float* dy, const void* in, const float* w, void* din, f
 }
 
 // ------------------------------------------------------------------------------------------ column sums (bias grads)
-// out[c] = sum_r x[r][c] for bf16 x [rows, C]; two-stage, fixed order.
+// out[c] = sum_r x[r][c] for bf16 x [rows, C]; two-stage, fixed order.  C % 8 == 0: a thread owns 8 columns (one
+// 16-byte load per row), 16 threads span 128 columns, 16 row lanes per block with four loads in flight each.
+__global__ void __launch_bounds__(256)
+colsum_partial_v8_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ partial, long long rows, int C,
+                         int chunks) {
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  const int c = (blockIdx.x * 16 + tx) * 8;
+  const long long per = (rows + chunks - 1) / chunks;
+  const long long r0 = blockIdx.y * per, r1 = (r0 + per < rows) ? r0 + per : rows;
+  float s[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = 0.f;
+  if (c < C) {
+    const __nv_bfloat16* col = x + c;
+    long long r = r0 + ty;
+    for (; r + 48 < r1; r += 64) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = __ldg(reinterpret_cast<const uint4*>(col + (r + 16 * u) * C));
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&v[u]);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 f = __bfloat1622float2(h2[e]);
+          s[2 * e] += f.x; s[2 * e + 1] += f.y;
+        }
+      }
+    }
+    for (; r < r1; r += 16) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(col + r * C));
+      const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 f = __bfloat1622float2(h2[e]);
+        s[2 * e] += f.x; s[2 * e + 1] += f.y;
+      }
+    }
+  }
+  __shared__ float sm[16][132];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) sm[ty][tx * 8 + j] = s[j];
+  __syncthreads();
+  if (threadIdx.x < 128) {
+    const int cc = blockIdx.x * 128 + threadIdx.x;
+    if (cc < C) {
+      float t = 0.f;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) t += sm[i][threadIdx.x];
+      partial[(long long)blockIdx.y * C + cc] = t;
+    }
+  }
+}
+// any even C: 32 column pairs x 8 row lanes
 __global__ void __launch_bounds__(256)
 colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ partial, long long rows, int C,
                       int chunks) {
@@ -625,24 +691,41 @@ colsum_partial_f32_kernel(const float* __restrict__ x, float* __restrict__ parti
   }
 }
 
-__global__ void colsum_reduce_kernel(const float* __restrict__ partial, float* __restrict__ out, int C, int chunks) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
+// second stage: 32 columns x 8 chunk lanes per block, fixed summation order
+__global__ void __launch_bounds__(256)
+colsum_reduce_kernel(const float* __restrict__ partial, float* __restrict__ out, int C, int chunks) {
+  const int cx = threadIdx.x & 31, ky = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + cx;
   float s = 0.f;
-  for (int k = 0; k < chunks; ++k) s += partial[(long long)k * C + c];
-  out[c] = s;
+  if (c < C)
+    for (int k = ky; k < chunks; k += 8) s += partial[(long long)k * C + c];
+  __shared__ float sa[8][33];
+  sa[ky][cx] = s;
+  __syncthreads();
+  if (ky == 0 && c < C) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += sa[i][cx];
+    out[c] = t;
+  }
 }
-constexpr int kColsumChunks = 1024;
+constexpr int kColsumChunks = 1024;          // scratch rows the callers provide (as_colsum_scratch_floats)
+constexpr int kColsumMaxUsed = 148 * 4;      // chunks actually launched: four row chunks per SM
 long long colsum_scratch_floats(int C) { return (long long)kColsumChunks * C; }
 int colsum_bf16(const void* x, float* out, float* scratch, long long rows, int C, cudaStream_t st) {
   if (rows <= 0 || C <= 0 || (C % 2) != 0) return AS_ESIZE;
   if (!x || !out || !scratch) return AS_EINVAL;
   long long want = (rows + 255) / 256;
-  const int chunks = (int)(want < 1 ? 1 : (want > kColsumChunks ? kColsumChunks : want));
-  dim3 g((C + 63) / 64, chunks);
-  colsum_partial_kernel<<<g, 256, 0, st>>>((const __nv_bfloat16*)x, scratch, rows, C, chunks);
+  const int chunks = (int)(want < 1 ? 1 : (want > kColsumMaxUsed ? kColsumMaxUsed : want));
+  if (C % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0) {
+    dim3 g((C + 127) / 128, chunks);
+    colsum_partial_v8_kernel<<<g, 256, 0, st>>>((const __nv_bfloat16*)x, scratch, rows, C, chunks);
+  } else {
+    dim3 g((C + 63) / 64, chunks);
+    colsum_partial_kernel<<<g, 256, 0, st>>>((const __nv_bfloat16*)x, scratch, rows, C, chunks);
+  }
   AS_LAUNCH_CHECK();
-  colsum_reduce_kernel<<<(C + 63) / 64, 64, 0, st>>>(scratch, out, C, chunks);
+  colsum_reduce_kernel<<<(C + 31) / 32, 256, 0, st>>>(scratch, out, C, chunks);
   AS_LAUNCH_CHECK();
   return AS_OK;
 }
@@ -920,7 +1003,7 @@ int colsum_f32(const float* x, float* out, float* scratch, long long rows, int C
   dim3 g((C + 31) / 32, chunks);
   colsum_partial_f32_kernel<<<g, 256, 0, st>>>(x, scratch, rows, C, chunks);
   AS_LAUNCH_CHECK();
-  colsum_reduce_kernel<<<(C + 63) / 64, 64, 0, st>>>(scratch, out, C, chunks);
+  colsum_reduce_kernel<<<(C + 31) / 32, 256, 0, st>>>(scratch, out, C, chunks);
   AS_LAUNCH_CHECK();
   return AS_OK;
 }

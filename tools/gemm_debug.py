@@ -16,5 +16,6 @@ def t(M, N, Kd, bf16, mode, iters=5):
     for _ in range(iters): K.gemm(A, B, C, M, N, Kd)
     e1.record(); torch.cuda.synchronize(); lib.as_debug_gemm_mode(0)
     return e0.elapsed_time(e1) / iters
-for (M, N, Kd, bf) in [(532480, 768, 256, True), (532480, 256, 256, False), (532480, 1024, 256, True), (532480, 768, 64, True), (532480, 768, 1024, True)]:
-    print(M, N, Kd, 'bf16' if bf else 'f32', ' full %.3f  no-store %.3f  drain-only %.3f ms' % (t(M, N, Kd, bf, 0), t(M, N, Kd, bf, 1), t(M, N, Kd, bf, 2)))
+for (M, N, Kd, bf) in [(532480, 768, 256, True), (532480, 256, 256, False), (532480, 1024, 256, True), (532480, 768, 64, True), (532480, 768, 1024, True),
+                      (8192, 8192, 8192, True)]:
+    print(M, N, Kd, 'bf16' if bf else 'f32', ' full %.3f  no-store %.3f  no-fence %.3f  legacy-store %.3f  drain-only %.3f ms' % tuple(t(M, N, Kd, bf, m) for m in (0, 1, 3, 8, 2)), flush=True)

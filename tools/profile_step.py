@@ -35,3 +35,8 @@ n_kernels = sum(e.count for e in ka if e.device_type == torch.autograd.DeviceTyp
 print('CUDA kernel launches in one step: %d' % n_kernels)
 print(ka.table(sort_by='cuda_time_total', row_limit=a.rows, max_name_column_width=90))
 print(ka.table(sort_by='self_cpu_time_total', row_limit=40, max_name_column_width=70))
+if os.environ.get('EACH'):
+    pats = os.environ['EACH'].split(',')
+    for e in prof.events():
+        if e.device_type == torch.autograd.DeviceType.CUDA and any(p in e.name for p in pats):
+            print('EACH %-60s %10.1f us' % (e.name[:60], e.device_time_total))
