@@ -50,8 +50,10 @@ int colsum_f32(const float*, float*, float*, long long, int, cudaStream_t);
 int lnlstm_fwd(const float*, const float*, const float*, const void*, const float*, const float*, const float*,
                const float*, float*, float*, float*, float*, float*, int, int, int, cudaStream_t);
 bool lnlstm_cluster_ok(int);
+int lnlstm_cluster_max_active(int);
+int lnlstm_set_profile(long long*);
 int lnlstm_bwd(const float*, const float*, const float*, const float*, const float*, const float*, const float*,
-               const float*, const void*, const void*, const float*, const float*, const float*, const float*, const float*,
+               const float*, const void*, const float*, const float*, const float*, const float*, const float*,
                const float*, const float*, float*, float*, float*, float*, float*, int, int, int, cudaStream_t);
 int spatial_features(const void* const*, const void* const*, int, const float*, void*, long long, int, int, int,
                      cudaStream_t);
@@ -261,14 +263,17 @@ int as_lnlstm_fwd(const float* gi, const float* h0, const float* c0, const void*
                         ST(stream));
 }
 int as_lnlstm_bwd(const float* gi, const float* h0, const float* c0, const float* y, const float* c_all,
-                  const float* u_all, const float* z_all, const float* stats, const void* whh_t, const void* whh,
-                  const float* ln_h_w, const float* ln_h_b, const float* ln_c_w, const float* ln_c_b, const float* dy,
-                  const float* dhT, const float* dcT, float* dgi, float* du, float* dh0, float* dc0, float* dparam, int T,
-                  int B, int H, void* stream) {
-  return as::lnlstm_bwd(gi, h0, c0, y, c_all, u_all, z_all, stats, whh_t, whh, ln_h_w, ln_h_b, ln_c_w, ln_c_b, dy, dhT,
-                        dcT, dgi, du, dh0, dc0, dparam, T, B, H, ST(stream));
+                  const float* u_all, const float* z_all, const float* stats, const void* whh_t, const float* ln_h_w,
+                  const float* ln_h_b, const float* ln_c_w, const float* ln_c_b, const float* dy, const float* dhT,
+                  const float* dcT, float* dgi, float* du, float* dh0, float* dc0, float* dparam, int T, int B, int H,
+                  void* stream) {
+  return as::lnlstm_bwd(gi, h0, c0, y, c_all, u_all, z_all, stats, whh_t, ln_h_w, ln_h_b, ln_c_w, ln_c_b, dy, dhT, dcT,
+                        dgi, du, dh0, dc0, dparam, T, B, H, ST(stream));
 }
 int as_lnlstm_cluster_ok(int H) { return as::lnlstm_cluster_ok(H) ? 1 : 0; }
+// diagnostics only (not part of the public header)
+int as_debug_lstm_max_clusters(int H) { return as::lnlstm_cluster_max_active(H); }
+int as_debug_lstm_profile(void* buf) { return as::lnlstm_set_profile(reinterpret_cast<long long*>(buf)); }
 
 int as_softmax_fwd(const float* scores, const int64_t* key_len, void* probs, int64_t groups, int Nq, int Nk,
                    int groups_per_len, void* stream) {

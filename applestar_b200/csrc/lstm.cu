@@ -301,17 +301,15 @@ int lnlstm_fwd(const float* gi, const float* h0, const float* c0, const void* wh
 }
 
 int lnlstm_bwd(const float* gi, const float* h0, const float* c0, const float* y, const float* c_all, const float* u_all,
-               const float* z_all, const float* stats, const void* whh_t, const void* whh, const float* gh_w,
-               const float* gh_b, const float* gc_w, const float* gc_b, const float* dy, const float* dhT,
-               const float* dcT, float* dgi, float* du, float* dh0, float* dc0, float* dparam, int T, int B, int H,
-               cudaStream_t st) {
+               const float* z_all, const float* stats, const void* whh_t, const float* gh_w, const float* gh_b,
+               const float* gc_w, const float* gc_b, const float* dy, const float* dhT, const float* dcT, float* dgi,
+               float* du, float* dh0, float* dc0, float* dparam, int T, int B, int H, cudaStream_t st) {
   if (T <= 0 || B <= 0) return AS_OK;
   if (H <= 0 || (H % 8) != 0 || H > 2 * kLstmThreads) return AS_ESIZE;
-  if (!gi || !c0 || !c_all || !u_all || !z_all || !stats || !dgi || !du || !dparam) return AS_EINVAL;
-  if (whh && lnlstm_cluster_ok(H))
-    return lnlstm_bwd_cluster(gi, c0, c_all, u_all, z_all, stats, whh, gh_w, gh_b, gc_w, gc_b, dy, dhT, dcT, dgi, du, dh0,
-                              dc0, dparam, T, B, H, st);
-  if (!whh_t) return AS_EINVAL;
+  if (!gi || !c0 || !c_all || !u_all || !z_all || !stats || !whh_t || !dgi || !du || !dparam) return AS_EINVAL;
+  if (lnlstm_cluster_ok(H))
+    return lnlstm_bwd_cluster(gi, c0, c_all, u_all, z_all, stats, whh_t, gh_w, gh_b, gc_w, gc_b, dy, dhT, dcT, dgi, du,
+                              dh0, dc0, dparam, T, B, H, st);
   LstmBwd p{gi, h0, c0, y, c_all, u_all, z_all, stats, reinterpret_cast<const __nv_bfloat16*>(whh_t), gh_w, gh_b, gc_w, gc_b,
             dy, dhT, dcT, dgi, du, dh0, dc0, dparam, T, B, H};
   const int smem = (2 * H + 4 * H + 8 * H + 2 * H + 2 * kLstmWarps) * 4;

@@ -1,15 +1,21 @@
-// LayerNorm-LSTM recurrence on a thread-block CLUSTER (reference: distar/agent/default/model/lstm.py:138-167).
+// LayerNorm-LSTM recurrence on thread-block CLUSTERS (reference: distar/agent/default/model/lstm.py:138-167).
 //
 // The one-CTA-per-trajectory kernels in lstm.cu stream W_hh (1.2 MB for the core LSTM) from L2 at every time step and
-// keep only 16 of 148 SMs busy at 16 trajectories.  Here a cluster of 8 CTAs owns one trajectory: CTA r holds the
-// 4 x H/8 gate rows of W_hh that belong to hidden units [r H/8, (r+1) H/8) in shared memory for the WHOLE unroll
-// (147 KB of bf16 at H = 384), so a step reads weights only from shared memory.  What crosses CTAs per step goes
-// through distributed shared memory: two LayerNorm statistics exchanges (eight (mean, M2) pairs each, merged with
-// the parallel-variance formula) and the new h slice (forward) or the partial W_hh^T du products (backward,
-// a reduce-scatter).  Three cluster barriers per step.
+// keep only 16 of 148 SMs busy at 16 trajectories.  Here a cluster of 8 CTAs owns one or two trajectories and keeps
+// W_hh in shared memory for the WHOLE unroll: CTA r holds the rows that produce hidden units [r H/8, (r+1) H/8)
+// (forward: the 4 x H/8 gate rows of W_hh, backward: the H/8 rows of W_hh^T; 147 KB of bf16 at H = 384).
 //
-// Both directions use the same row slice of W_hh: forward computes u = W h (row dot products), backward computes
-// dh = W^T du (column sums over the CTA's rows, then summed over the cluster).
+// Per time step there is ONE exchange through distributed shared memory and ONE cluster barrier:
+//   forward : every CTA computes its slice of u = W_hh h_{t-1}, stores it into the u buffer of all 8 CTAs (all-gather),
+//             and after the barrier every CTA redundantly runs LN_h, the gates, LN_c and h_t for ALL units -- so h_t is
+//             already complete in local shared memory for the next mat-vec.
+//   backward: every CTA redundantly runs the cell / LayerNorm backward for all units (inputs are saved tensors that
+//             do not depend on the recurrence, prefetched before the barrier), obtains the full du, computes its
+//             slice of dh_{t-1} = W_hh^T du and all-gathers that slice.
+// Thread t owns hidden unit t (H <= 384 threads) in the element-wise phases.  In the mat-vec, eight lanes share a
+// weight row (interleaved 16-byte chunks: a quarter warp reads 128 contiguous bytes, conflict free) and combine with
+// three shuffles.  B200 fits 15 such clusters at once (cudaOccupancyMaxActiveClusters), hence two trajectories per
+// cluster when B > 15: the weight reads and every synchronisation are shared between the two.
 #include <cooperative_groups.h>
 
 #include "common.cuh"
@@ -18,32 +24,71 @@ namespace cg = cooperative_groups;
 
 namespace as {
 
-constexpr int kCS = 8;        // CTAs per cluster (= per trajectory)
+constexpr int kCS = 8;        // CTAs per cluster
 constexpr int kNT = 384;      // threads per CTA
 constexpr int kNW = kNT / 32;
 
-__device__ __forceinline__ float sigm(float x) { return 1.f / (1.f + expf(-x)); }
+// MUFU.TANH (abs. error ~5e-4, far inside the bf16 W_hh budget): one instruction instead of ~30 on the serial path
+__device__ __forceinline__ float tanh_fast(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float sigm(float x) { return fmaf(tanh_fast(0.5f * x), 0.5f, 0.5f); }
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 
-// block-wide sums of two values; every thread gets both results.  `red` holds 2 * kNW floats.
-__device__ __forceinline__ void cta_sum2(float& a, float& b, float* red) {
-  a = warp_sum(a); b = warp_sum(b);
+// block-wide sums of N values; every thread gets all results.  `red` holds N * kNW floats; consecutive calls must
+// alternate between two buffers (the single barrier inside then also protects the buffer's previous use).
+template <int N>
+__device__ __forceinline__ void cta_sum(float (&v)[N], float* red) {
   const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-  __syncthreads();                                 // previous use of `red` is over
-  if (l == 0) { red[w] = a; red[kNW + w] = b; }
-  __syncthreads();
-  float sa = 0.f, sb = 0.f;
 #pragma unroll
-  for (int i = 0; i < kNW; ++i) { sa += red[i]; sb += red[kNW + i]; }
-  a = sa; b = sb;
+  for (int i = 0; i < N; ++i) {
+    v[i] = warp_sum(v[i]);
+    if (l == 0) red[i * kNW + w] = v[i];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < kNW; ++k) s += red[i * kNW + k];
+    v[i] = s;
+  }
 }
 
-__device__ __forceinline__ float dot8s(const uint4& q, const float* vv) {
+__device__ __forceinline__ void unpack8f(const uint4& q, float* f) {
   const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&q);
-  const float4 v0 = *reinterpret_cast<const float4*>(vv), v1 = *reinterpret_cast<const float4*>(vv + 4);
-  const float2 a = __bfloat1622float2(h2[0]), b = __bfloat1622float2(h2[1]), c = __bfloat1622float2(h2[2]),
-               d = __bfloat1622float2(h2[3]);
-  return a.x * v0.x + a.y * v0.y + b.x * v0.z + b.y * v0.w + c.x * v1.x + c.y * v1.y + d.x * v1.z + d.y * v1.w;
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const float2 v = __bfloat1622float2(h2[e]);
+    f[2 * e] = v.x; f[2 * e + 1] = v.y;
+  }
 }
+// v0 / v1 = logical first / second half of one 8-float chunk of the vector
+__device__ __forceinline__ float dot8f(const float* w, const float4& v0, const float4& v1) {
+  return w[0] * v0.x + w[1] * v0.y + w[2] * v0.z + w[3] * v0.w + w[4] * v1.x + w[5] * v1.y + w[6] * v1.z + w[7] * v1.w;
+}
+// The mat-vec operand vectors (h, du) live in shared memory with the two 16-byte halves of every second group of four
+// 32-byte chunks exchanged.  Lane pt of an octet reads chunk pt + 8c: lanes 0-3 fetch physical half 0 first, lanes
+// 4-7 physical half 1 first -- both are the chunk's LOGICAL first half -- so one load instruction of the octet
+// touches eight distinct bank groups instead of four.
+__device__ __forceinline__ int swz(int e) { return e ^ ((e >> 3) & 4); }
+
+__device__ __forceinline__ float sum8lanes(float v) {
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  return v;
+}
+
+// diagnostics: per-CTA cycle counts of the forward phases (as_debug_lstm_profile); nullptr in normal operation
+__device__ long long* g_lstm_prof = nullptr;
+#define LSTM_TICK(i)                                                    \
+  do {                                                                  \
+    if (prof && threadIdx.x == 0) { const long long now = clock64(); pacc[i] += now - tick; tick = now; } \
+  } while (0)
 
 struct LstmClFwd {
   const float* gi; const float* h0; const float* c0; const __nv_bfloat16* whh;
@@ -53,318 +98,368 @@ struct LstmClFwd {
 };
 struct LstmClBwd {
   const float* gi; const float* c0; const float* c_all; const float* u_all; const float* z_all; const float* stats;
-  const __nv_bfloat16* whh;
+  const __nv_bfloat16* whh_t;
   const float* gh_w; const float* gh_b; const float* gc_w; const float* gc_b;
   const float* dy; const float* dhT; const float* dcT;
   float* dgi; float* du; float* dh0; float* dc0; float* dparam;
   int T, B, H;
 };
 
-// shared-memory carve-up shared by both kernels: the W_hh slice first (row pitch 2H + 16 bytes keeps 16-byte row
-// reads of consecutive rows on distinct banks), then fp32 scratch
-__device__ __forceinline__ void load_w_slice(uint8_t* sW, const __nv_bfloat16* whh, int H, int HS, int r, int pitchB) {
-  const int rows = 4 * HS, chunks = H >> 3;
-  for (int i = threadIdx.x; i < rows * chunks; i += kNT) {
-    const int lr = i / chunks, ch = i - lr * chunks;
-    const int g = lr / HS, kk = lr - g * HS;
-    const long long j = (long long)g * H + r * HS + kk;
-    *reinterpret_cast<uint4*>(sW + (long long)lr * pitchB + ch * 16) =
-        __ldg(reinterpret_cast<const uint4*>(whh + j * H) + ch);
-  }
-}
-
-// merge kCS (mean, M2) pairs of equal count n into (mean, rstd) over kCS * n values
-__device__ __forceinline__ void merge_stats(const float* st, float n, float& mean, float& rstd) {
-  float m = 0.f;
-#pragma unroll
-  for (int q = 0; q < kCS; ++q) m += st[2 * q];
-  m *= (1.f / kCS);
-  float M2 = 0.f;
-#pragma unroll
-  for (int q = 0; q < kCS; ++q) { const float d = st[2 * q] - m; M2 += st[2 * q + 1] + n * d * d; }
-  mean = m;
-  rstd = rsqrtf(M2 / (n * kCS) + 1e-5f);
-}
-
+// ---------------------------------------------------------------------------------------------------- forward
+template <int NB, int H>
 __global__ void __launch_bounds__(kNT, 1) lnlstm_fwd_cluster_kernel(const LstmClFwd p) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
   cg::cluster_group cluster = cg::this_cluster();
   const int r = (int)cluster.block_rank();
-  const int b = blockIdx.x / kCS;
-  const int H = p.H, G = 4 * H, HS = H / kCS, rows = 4 * HS;
-  const int pitchB = 2 * H + 16;
-  const int parts = kNT / rows, chunks = H >> 3, cpp = chunks / parts;
-  uint8_t* sW = smem_raw;
-  float* s_h = reinterpret_cast<float*>(sW + (long long)rows * pitchB);   // [H]   h_{t-1}, written by all CTAs
-  float* s_up = s_h + H;                 // [parts][rows] partial dot products
-  float* s_a = s_up + parts * rows;      // [rows] gate pre-activations
-  float* s_c = s_a + rows;               // [HS]   cell state slice
-  float* s_st = s_c + HS;                // [kCS][2] LN_h partial statistics (written by peers)
-  float* s_stc = s_st + 2 * kCS;         // [kCS][2] LN_c partial statistics
-  float* red = s_stc + 2 * kCS;          // [2 kNW]
+  const int b0 = (blockIdx.x / kCS) * NB;             // first trajectory of this cluster
+  constexpr int G = 4 * H, HS = H / kCS, rows = 4 * HS;
+  constexpr int chunks = H >> 3, cpl = chunks >> 3;    // 16-byte chunks per weight row, per lane
+  static_assert(H <= kNT && H % 64 == 0 && HS * 8 <= kNT && HS % 4 == 0, "unsupported hidden size");
+  uint8_t* sW = smem_raw;                              // [rows][H] bf16: rows g*HS + us  <->  W_hh[g*H + r*HS + us]
+  float* s_h = reinterpret_cast<float*>(sW + (long long)rows * H * 2);   // [NB][H]   h_{t-1}
+  float* s_uf = s_h + NB * H;                          // [2][NB][G] all-gathered u, double buffered (written by peers)
+  float* s_sl = s_uf + 2 * NB * G;                     // [NB][4][HS] this CTA's u slice, staged for vector stores
+  float* redA = s_sl + NB * rows;                      // [2 NB kNW]
+  float* redB = redA + 2 * NB * kNW;
   const int t_id = threadIdx.x;
 
-  load_w_slice(sW, p.whh, H, HS, r, pitchB);
-  for (int k = t_id; k < H; k += kNT) s_h[k] = p.h0[(long long)b * H + k];
-  if (t_id < HS) s_c[t_id] = p.c0[(long long)b * H + r * HS + t_id];
-  // per-thread constants: thread t < rows owns gate row t of the slice, thread t < HS owns hidden unit t
-  const int lr = t_id % rows, part = t_id / rows;
-  const int g_of = lr / HS, kk_of = lr - g_of * HS;
-  const long long j_row = (long long)g_of * H + r * HS + kk_of;
-  float ghw = 0.f, ghb = 0.f, gcw = 0.f, gcb = 0.f;
-  if (t_id < rows) { ghw = p.gh_w[j_row]; ghb = p.gh_b[j_row]; }
-  if (t_id < HS) { gcw = p.gc_w[r * HS + t_id]; gcb = p.gc_b[r * HS + t_id]; }
-  cluster.sync();                                   // every CTA of the cluster is resident, s_h / sW are ready
+  for (int i = t_id; i < rows * chunks; i += kNT) {
+    const int lr = i / chunks, ch = i - lr * chunks;
+    const int g = lr / HS, us = lr - g * HS;
+    reinterpret_cast<uint4*>(sW)[i] = __ldg(reinterpret_cast<const uint4*>(p.whh + ((long long)g * H + r * HS + us) * H) + ch);
+  }
+  // element-wise role: thread t = hidden unit t (all NB trajectories)
+  const bool unit = t_id < H;
+  const bool owner = unit && (t_id / HS == r);         // this CTA writes the saved tensors of its own units
+  float ghw[4], ghb[4], gcw = 0.f, gcb = 0.f, c_reg[NB];
+#pragma unroll
+  for (int g = 0; g < 4; ++g) { ghw[g] = unit ? p.gh_w[g * H + t_id] : 0.f; ghb[g] = unit ? p.gh_b[g * H + t_id] : 0.f; }
+  if (unit) { gcw = p.gc_w[t_id]; gcb = p.gc_b[t_id]; }
+#pragma unroll
+  for (int nb = 0; nb < NB; ++nb) {
+    const int b = min(b0 + nb, p.B - 1);               // a padding trajectory repeats the last one (never stored)
+    c_reg[nb] = unit ? p.c0[(long long)b * H + t_id] : 0.f;
+    if (unit) s_h[nb * H + swz(t_id)] = p.h0[(long long)b * H + t_id];
+  }
+  // mat-vec role: unit slot us (its four gate rows), lane part pt
+  const int us = t_id >> 3, pt = t_id & 7, hs4 = pt & 4;
+  long long* prof = g_lstm_prof;
+  long long pacc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tick = 0;
+  cluster.sync();                                      // all CTAs resident; sW / s_h ready
+  if (prof) tick = clock64();
 
   for (int t = 0; t < p.T; ++t) {
-    const long long tb = (long long)t * p.B + b;
-    // ---- u = W_slice h  (thread = (row, column part))
-    if (part < parts) {
-      const uint4* wrow = reinterpret_cast<const uint4*>(sW + (long long)lr * pitchB) + part * cpp;
-      const float* hv = s_h + part * cpp * 8;
-      float acc0 = 0.f, acc1 = 0.f;
-      int c = 0;
-      for (; c + 1 < cpp; c += 2) { acc0 += dot8s(wrow[c], hv + c * 8); acc1 += dot8s(wrow[c + 1], hv + c * 8 + 8); }
-      if (c < cpp) acc0 += dot8s(wrow[c], hv + c * 8);
-      s_up[part * rows + lr] = acc0 + acc1;
-    }
-    __syncthreads();
-    float u = 0.f;
-    if (t_id < rows)
-      for (int pp = 0; pp < parts; ++pp) u += s_up[pp * rows + t_id];
-    // ---- LN_h statistics: local (sum, sum of squares) -> (mean, M2) -> all CTAs of the cluster
-    float s1 = (t_id < rows) ? u : 0.f, s2 = (t_id < rows) ? u * u : 0.f;
-    cta_sum2(s1, s2, red);
-    if (t_id < kCS) {
-      const float ml = s1 / (float)rows;
-      float* dst = cluster.map_shared_rank(s_st, t_id);
-      dst[2 * r] = ml;
-      dst[2 * r + 1] = fmaxf(s2 - s1 * ml, 0.f);
-    }
-    cluster.sync();                                                            // (1)
-    float mean_h, rstd_h;
-    merge_stats(s_st, (float)rows, mean_h, rstd_h);
-    if (t_id < rows) {
-      if (p.u_all) p.u_all[tb * G + j_row] = u;
-      s_a[t_id] = __ldg(p.gi + tb * G + j_row) + (u - mean_h) * rstd_h * ghw + ghb;
-    }
-    __syncthreads();
-    // ---- cell: z = s(f) c + s(i) tanh(g); LN_c over all H units
-    float z = 0.f;
-    if (t_id < HS) {
-      z = sigm(s_a[HS + t_id]) * s_c[t_id] + sigm(s_a[t_id]) * tanhf(s_a[2 * HS + t_id]);
-      if (p.z_all) p.z_all[tb * H + r * HS + t_id] = z;
-    }
-    float z1 = (t_id < HS) ? z : 0.f, z2 = (t_id < HS) ? z * z : 0.f;
-    cta_sum2(z1, z2, red);
-    if (t_id < kCS) {
-      const float ml = z1 / (float)HS;
-      float* dst = cluster.map_shared_rank(s_stc, t_id);
-      dst[2 * r] = ml;
-      dst[2 * r + 1] = fmaxf(z2 - z1 * ml, 0.f);
-    }
-    cluster.sync();                                                            // (2)
-    float mean_c, rstd_c;
-    merge_stats(s_stc, (float)HS, mean_c, rstd_c);
-    if (t_id < HS) {
-      const float c = (z - mean_c) * rstd_c * gcw + gcb;
-      const float h = sigm(s_a[3 * HS + t_id]) * tanhf(c);
-      s_c[t_id] = c;
-      p.y[tb * H + r * HS + t_id] = h;
-      p.c_all[tb * H + r * HS + t_id] = c;
+    const int buf = t & 1;
+    // prefetch this step's input projections (independent of the recurrence)
+    float gi_r[NB][4];
 #pragma unroll
-      for (int q = 0; q < kCS; ++q) cluster.map_shared_rank(s_h, q)[r * HS + t_id] = h;
+    for (int nb = 0; nb < NB; ++nb) {
+      const int b = min(b0 + nb, p.B - 1);
+#pragma unroll
+      for (int g = 0; g < 4; ++g) gi_r[nb][g] = unit ? __ldg(p.gi + ((long long)t * p.B + b) * G + g * H + t_id) : 0.f;
     }
-    if (t_id == 0 && r == 0 && p.stats) {
-      p.stats[tb * 4 + 0] = mean_h; p.stats[tb * 4 + 1] = rstd_h; p.stats[tb * 4 + 2] = mean_c; p.stats[tb * 4 + 3] = rstd_c;
+    // ---- u slice = W_slice h
+    float acc[4][NB];
+#pragma unroll
+    for (int g = 0; g < 4; ++g)
+#pragma unroll
+      for (int nb = 0; nb < NB; ++nb) acc[g][nb] = 0.f;
+    if (us < HS) {
+      const uint4* w4 = reinterpret_cast<const uint4*>(sW) + us * chunks + pt;          // + g*HS*chunks + 8c
+      const float4* h4 = reinterpret_cast<const float4*>(s_h) + 2 * pt + (hs4 >> 2);    // + nb*H/4 + 16c, ^1 = 2nd half
+#pragma unroll
+      for (int c = 0; c < cpl; ++c) {
+        float w[4][8];
+#pragma unroll
+        for (int g = 0; g < 4; ++g) unpack8f(w4[g * HS * chunks + 8 * c], w[g]);
+#pragma unroll
+        for (int nb = 0; nb < NB; ++nb) {
+          const float4* hp = h4 + nb * (H / 4) + 16 * c;
+          const float4 v0 = hp[0], v1 = hp[1 - (hs4 >> 1)];
+#pragma unroll
+          for (int g = 0; g < 4; ++g) acc[g][nb] += dot8f(w[g], v0, v1);
+        }
+      }
     }
-    cluster.sync();                                                            // (3) h_t complete everywhere
+#pragma unroll
+    for (int g = 0; g < 4; ++g)
+#pragma unroll
+      for (int nb = 0; nb < NB; ++nb) acc[g][nb] = sum8lanes(acc[g][nb]);
+    LSTM_TICK(0);
+    if (us < HS && pt == 0) {
+#pragma unroll
+      for (int nb = 0; nb < NB; ++nb)
+#pragma unroll
+        for (int g = 0; g < 4; ++g) s_sl[(nb * 4 + g) * HS + us] = acc[g][nb];
+    }
+    __syncthreads();
+    LSTM_TICK(1);
+    // all-gather: 16-byte stores of the slice into s_uf[buf][nb][g*H + r*HS ..] of every CTA of the cluster
+    {
+      const int q4 = HS >> 2, per_peer = NB * 4 * q4;
+      for (int i = t_id; i < kCS * per_peer; i += kNT) {
+        const int peer = i / per_peer, k = i - peer * per_peer;
+        const int ng = k / q4, x4 = k - ng * q4;       // ng = nb * 4 + g
+        const int nb = ng >> 2, g = ng & 3;
+        float* dst = cluster.map_shared_rank(s_uf, peer) + (buf * NB + nb) * G + g * H + r * HS + x4 * 4;
+        *reinterpret_cast<float4*>(dst) = *reinterpret_cast<const float4*>(s_sl + ng * HS + x4 * 4);
+      }
+    }
+    LSTM_TICK(2);
+    cluster_arrive();
+    cluster_wait();
+    LSTM_TICK(3);
+    // ---- LN_h over all 4H gate rows, per trajectory: one block reduction of (sum, sum of squares).  The inputs are
+    // O(1) with |mean| no larger than the spread, so the single-pass variance loses nothing visible in fp32.
+    float u[NB][4], s[2 * NB];
+#pragma unroll
+    for (int nb = 0; nb < NB; ++nb) {
+      s[2 * nb] = 0.f; s[2 * nb + 1] = 0.f;
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        u[nb][g] = unit ? s_uf[(buf * NB + nb) * G + g * H + t_id] : 0.f;
+        s[2 * nb] += u[nb][g];
+        s[2 * nb + 1] += u[nb][g] * u[nb][g];
+      }
+    }
+    cta_sum(s, redA);
+    LSTM_TICK(4);
+    float mean_h[NB], rstd_h[NB], z[NB], a_o[NB];
+#pragma unroll
+    for (int nb = 0; nb < NB; ++nb) {
+      mean_h[nb] = s[2 * nb] * (1.f / G);
+      rstd_h[nb] = rsqrtf(fmaxf(s[2 * nb + 1] * (1.f / G) - mean_h[nb] * mean_h[nb], 0.f) + 1e-5f);
+      float a[4];
+#pragma unroll
+      for (int g = 0; g < 4; ++g) a[g] = gi_r[nb][g] + (u[nb][g] - mean_h[nb]) * rstd_h[nb] * ghw[g] + ghb[g];
+      z[nb] = unit ? sigm(a[1]) * c_reg[nb] + sigm(a[0]) * tanh_fast(a[2]) : 0.f;
+      a_o[nb] = a[3];
+      s[2 * nb] = z[nb];
+      s[2 * nb + 1] = z[nb] * z[nb];
+    }
+    cta_sum(s, redB);
+    float mean_c[NB];
+#pragma unroll
+    for (int nb = 0; nb < NB; ++nb) {
+      mean_c[nb] = s[2 * nb] * (1.f / H);
+      const float rstd_c = rsqrtf(fmaxf(s[2 * nb + 1] * (1.f / H) - mean_c[nb] * mean_c[nb], 0.f) + 1e-5f);
+      const float c = (z[nb] - mean_c[nb]) * rstd_c * gcw + gcb;
+      const float h = sigm(a_o[nb]) * tanh_fast(c);
+      c_reg[nb] = c;
+      if (unit) s_h[nb * H + swz(t_id)] = h;
+      const int b = b0 + nb;
+      if (owner && b < p.B) {
+        const long long tb = (long long)t * p.B + b;
+        p.y[tb * H + t_id] = h;
+        p.c_all[tb * H + t_id] = c;
+        if (p.z_all) p.z_all[tb * H + t_id] = z[nb];
+        if (p.u_all) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) p.u_all[tb * G + g * H + t_id] = u[nb][g];
+        }
+      }
+      if (t_id == 0 && r == 0 && p.stats && b < p.B) {
+        float* st = p.stats + ((long long)t * p.B + b) * 4;
+        st[0] = mean_h[nb]; st[1] = rstd_h[nb]; st[2] = mean_c[nb]; st[3] = rstd_c;
+      }
+    }
+    __syncthreads();                                   // h_t complete in local shared memory
+    LSTM_TICK(5);
   }
+  if (prof && threadIdx.x == 0)
+    for (int i = 0; i < 8; ++i) prof[blockIdx.x * 8 + i] = pacc[i];
+  cluster.sync();                                      // nobody exits while a peer may still address its shared memory
 }
 
+// ---------------------------------------------------------------------------------------------------- backward
+template <int NB, int H>
 __global__ void __launch_bounds__(kNT, 1) lnlstm_bwd_cluster_kernel(const LstmClBwd p) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
   cg::cluster_group cluster = cg::this_cluster();
   const int r = (int)cluster.block_rank();
-  const int b = blockIdx.x / kCS;
-  const int H = p.H, G = 4 * H, HS = H / kCS, rows = 4 * HS;
-  const int pitchB = 2 * H + 16;
-  const int cpairs = H >> 1, rparts = kNT / cpairs, rpp = rows / rparts;
-  uint8_t* sW = smem_raw;
-  float* s_dh = reinterpret_cast<float*>(sW + (long long)rows * pitchB);   // [HS] recurrent dh slice
-  float* s_dc = s_dh + HS;               // [HS]
-  float* s_ap = s_dc + HS;               // [rows] gate pre-activations (recomputed)
-  float* s_uh = s_ap + rows;             // [rows] normalised u
-  float* s_da = s_uh + rows;             // [rows] d pre-activation
-  float* s_du = s_da + rows;             // [rows] d u
-  float* s_tp = s_du + rows;             // [rparts][H] partial W^T du over row parts
-  float* s_dhp = s_tp + rparts * H;      // [kCS][HS] partial dh slices from every CTA (written by peers)
-  float* s_x1 = s_dhp + kCS * HS;        // [kCS][2] LN_c backward sums
-  float* s_x2 = s_x1 + 2 * kCS;          // [kCS][2] LN_h backward sums
-  float* red = s_x2 + 2 * kCS;           // [2 kNW]
+  const int b0 = (blockIdx.x / kCS) * NB;
+  constexpr int G = 4 * H, HS = H / kCS;
+  constexpr int chunks = G >> 3, cpl = chunks >> 3;    // chunks per W_hh^T row, per lane
+  uint8_t* sW = smem_raw;                              // [HS][G] bf16: row us <-> W_hh^T[r*HS + us]
+  float* s_du = reinterpret_cast<float*>(sW + (long long)HS * G * 2);    // [NB][G] full du of this step
+  float* s_dhf = s_du + NB * G;                        // [2][NB][H] all-gathered dh_{t-1}, double buffered
+  float* s_sl = s_dhf + 2 * NB * H;                    // [NB][HS] this CTA's dh slice, staged for vector stores
+  float* redA = s_sl + NB * HS;                        // [2 NB kNW]
+  float* redB = redA + 2 * NB * kNW;
   const int t_id = threadIdx.x;
 
-  load_w_slice(sW, p.whh, H, HS, r, pitchB);
-  if (t_id < HS) {
-    s_dh[t_id] = p.dhT ? p.dhT[(long long)b * H + r * HS + t_id] : 0.f;
-    s_dc[t_id] = p.dcT ? p.dcT[(long long)b * H + r * HS + t_id] : 0.f;
+  for (int i = t_id; i < HS * chunks; i += kNT) {
+    const int us = i / chunks, ch = i - us * chunks;
+    reinterpret_cast<uint4*>(sW)[i] = __ldg(reinterpret_cast<const uint4*>(p.whh_t + (long long)(r * HS + us) * G) + ch);
   }
-  const int lr = t_id % rows;
-  const int g_of = lr / HS, kk_of = lr - g_of * HS;
-  const long long j_row = (long long)g_of * H + r * HS + kk_of;
-  const int k_unit = r * HS + t_id;              // valid for t_id < HS
-  float ghw = 0.f, ghb = 0.f, gcw = 0.f, gcb = 0.f;
-  if (t_id < rows) { ghw = p.gh_w[j_row]; ghb = p.gh_b[j_row]; }
-  if (t_id < HS) { gcw = p.gc_w[k_unit]; gcb = p.gc_b[k_unit]; }
-  float pg_w = 0.f, pg_b = 0.f, pg_cw = 0.f, pg_cb = 0.f;    // LayerNorm parameter gradients owned by this thread
-  const int cp = t_id % cpairs, rpart = t_id / cpairs;
+  const bool unit = t_id < H;
+  const bool owner = unit && (t_id / HS == r);
+  float ghw[4], ghb[4], gcw = 0.f, gcb = 0.f;
+#pragma unroll
+  for (int g = 0; g < 4; ++g) { ghw[g] = unit ? p.gh_w[g * H + t_id] : 0.f; ghb[g] = unit ? p.gh_b[g * H + t_id] : 0.f; }
+  if (unit) { gcw = p.gc_w[t_id]; gcb = p.gc_b[t_id]; }
+  float dc_reg[NB], pg_w[NB][4], pg_b[NB][4], pg_cw[NB], pg_cb[NB];
+#pragma unroll
+  for (int nb = 0; nb < NB; ++nb) {
+    const int b = min(b0 + nb, p.B - 1);
+    dc_reg[nb] = (unit && p.dcT) ? p.dcT[(long long)b * H + t_id] : 0.f;
+    if (unit) s_dhf[(((p.T - 1) & 1) * NB + nb) * H + t_id] = p.dhT ? p.dhT[(long long)b * H + t_id] : 0.f;
+    pg_cw[nb] = 0.f; pg_cb[nb] = 0.f;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) { pg_w[nb][g] = 0.f; pg_b[nb][g] = 0.f; }
+  }
+  const int us = t_id >> 3, pt = t_id & 7, hs4 = pt & 4;
   cluster.sync();
 
   for (int t = p.T - 1; t >= 0; --t) {
-    const long long tb = (long long)t * p.B + b;
-    const float mean_h = __ldg(p.stats + tb * 4), rstd_h = __ldg(p.stats + tb * 4 + 1);
-    const float mean_c = __ldg(p.stats + tb * 4 + 2), rstd_c = __ldg(p.stats + tb * 4 + 3);
-    if (t_id < rows) {
-      const float uh = (__ldg(p.u_all + tb * G + j_row) - mean_h) * rstd_h;
-      s_uh[t_id] = uh;
-      s_ap[t_id] = __ldg(p.gi + tb * G + j_row) + uh * ghw + ghb;
-    }
-    __syncthreads();
-    // ---- cell backward for the CTA's hidden units
-    float dzh = 0.f, zhat = 0.f, da_o = 0.f;
-    if (t_id < HS) {
-      const float dh = s_dh[t_id] + (p.dy ? __ldg(p.dy + tb * H + k_unit) : 0.f);
-      const float o = sigm(s_ap[3 * HS + t_id]);
-      zhat = (__ldg(p.z_all + tb * H + k_unit) - mean_c) * rstd_c;
-      const float tc = tanhf(zhat * gcw + gcb);
-      da_o = dh * tc * o * (1.f - o);
-      const float dc = s_dc[t_id] + dh * o * (1.f - tc * tc);
-      pg_cw += dc * zhat;
-      pg_cb += dc;
-      dzh = dc * gcw;
-    }
-    float m1 = dzh, m2 = dzh * zhat;
-    cta_sum2(m1, m2, red);
-    if (t_id < kCS) {
-      float* dst = cluster.map_shared_rank(s_x1, t_id);
-      dst[2 * r] = m1; dst[2 * r + 1] = m2;
-    }
-    cluster.sync();                                                            // (A)
-    m1 = 0.f; m2 = 0.f;
+    const int buf = t & 1;                             // dh_t lives in s_dhf[buf]; dh_{t-1} goes to s_dhf[buf ^ 1]
+    // ---- saved tensors of this step (independent of the recurrence): issued before the barrier wait
+    float gi_r[NB][4], u_r[NB][4], z_r[NB], cprev[NB], dy_r[NB], st[NB][4];
 #pragma unroll
-    for (int q = 0; q < kCS; ++q) { m1 += s_x1[2 * q]; m2 += s_x1[2 * q + 1]; }
-    m1 /= (float)H; m2 /= (float)H;
-    if (t_id < HS) {
-      const float dz = rstd_c * (dzh - m1 - zhat * m2);
-      const float i = sigm(s_ap[t_id]), f = sigm(s_ap[HS + t_id]), g = tanhf(s_ap[2 * HS + t_id]);
-      const float cprev = t > 0 ? __ldg(p.c_all + ((long long)(t - 1) * p.B + b) * H + k_unit) : __ldg(p.c0 + (long long)b * H + k_unit);
-      s_da[t_id] = dz * g * i * (1.f - i);
-      s_da[HS + t_id] = dz * cprev * f * (1.f - f);
-      s_da[2 * HS + t_id] = dz * i * (1.f - g * g);
-      s_da[3 * HS + t_id] = da_o;
-      s_dc[t_id] = dz * f;
-    }
-    __syncthreads();
-    // ---- LN_h backward over all 4H rows
-    float da = 0.f, uh = 0.f, a1 = 0.f, a2 = 0.f;
-    if (t_id < rows) {
-      da = s_da[t_id]; uh = s_uh[t_id];
-      p.dgi[tb * G + j_row] = da;
-      pg_w += da * uh;
-      pg_b += da;
-      const float d = da * ghw;
-      a1 = d; a2 = d * uh;
-    }
-    cta_sum2(a1, a2, red);
-    if (t_id < kCS) {
-      float* dst = cluster.map_shared_rank(s_x2, t_id);
-      dst[2 * r] = a1; dst[2 * r + 1] = a2;
-    }
-    cluster.sync();                                                            // (B)
-    a1 = 0.f; a2 = 0.f;
+    for (int nb = 0; nb < NB; ++nb) {
+      const int b = min(b0 + nb, p.B - 1);
+      const long long tb = (long long)t * p.B + b;
 #pragma unroll
-    for (int q = 0; q < kCS; ++q) { a1 += s_x2[2 * q]; a2 += s_x2[2 * q + 1]; }
-    a1 /= (float)G; a2 /= (float)G;
-    if (t_id < rows) {
-      const float d = rstd_h * (da * ghw - a1 - uh * a2);
-      s_du[t_id] = d;
-      p.du[tb * G + j_row] = d;
-    }
-    __syncthreads();
-    // ---- partial dh_{t-1} = W_slice^T du  (thread = (column pair, row part)), then reduce-scatter over the cluster
-    if (rpart < rparts) {
-      const uint8_t* wcol = sW + (long long)(rpart * rpp) * pitchB + cp * 4;
-      const float* dv = s_du + rpart * rpp;
-      float acc0 = 0.f, acc1 = 0.f;
-#pragma unroll 8
-      for (int i = 0; i < rpp; ++i) {
-        const float2 w = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(wcol + (long long)i * pitchB));
-        const float d = dv[i];
-        acc0 += w.x * d; acc1 += w.y * d;
+      for (int g = 0; g < 4; ++g) {
+        gi_r[nb][g] = unit ? __ldg(p.gi + tb * G + g * H + t_id) : 0.f;
+        u_r[nb][g] = unit ? __ldg(p.u_all + tb * G + g * H + t_id) : 0.f;
+        st[nb][g] = __ldg(p.stats + tb * 4 + g);
       }
-      s_tp[rpart * H + 2 * cp] = acc0;
-      s_tp[rpart * H + 2 * cp + 1] = acc1;
+      z_r[nb] = unit ? __ldg(p.z_all + tb * H + t_id) : 0.f;
+      dy_r[nb] = (unit && p.dy) ? __ldg(p.dy + tb * H + t_id) : 0.f;
+      cprev[nb] = !unit ? 0.f : (t > 0 ? __ldg(p.c_all + ((long long)(t - 1) * p.B + b) * H + t_id) : __ldg(p.c0 + (long long)b * H + t_id));
+    }
+    if (t != p.T - 1) cluster_wait();                  // dh_t from every CTA has landed
+    // ---- cell backward for all units
+    float uh[NB][4], da[NB][4], dzh[NB], zhat[NB], gate_i[NB], gate_f[NB], gate_g[NB], s[2 * NB];
+#pragma unroll
+    for (int nb = 0; nb < NB; ++nb) {
+      float a[4];
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        uh[nb][g] = (u_r[nb][g] - st[nb][0]) * st[nb][1];
+        a[g] = gi_r[nb][g] + uh[nb][g] * ghw[g] + ghb[g];
+      }
+      gate_i[nb] = sigm(a[0]); gate_f[nb] = sigm(a[1]); gate_g[nb] = tanh_fast(a[2]);
+      const float o = sigm(a[3]);
+      zhat[nb] = (z_r[nb] - st[nb][2]) * st[nb][3];
+      const float tc = tanh_fast(zhat[nb] * gcw + gcb);
+      const float dh = (unit ? s_dhf[(buf * NB + nb) * H + t_id] : 0.f) + dy_r[nb];
+      da[nb][3] = dh * tc * o * (1.f - o);
+      const float dc = dc_reg[nb] + dh * o * (1.f - tc * tc);
+      pg_cw[nb] += dc * zhat[nb];
+      pg_cb[nb] += dc;
+      dzh[nb] = unit ? dc * gcw : 0.f;
+      s[2 * nb] = dzh[nb];
+      s[2 * nb + 1] = dzh[nb] * zhat[nb];
+    }
+    cta_sum(s, redA);
+#pragma unroll
+    for (int nb = 0; nb < NB; ++nb) {
+      const float m1 = s[2 * nb] / (float)H, m2 = s[2 * nb + 1] / (float)H;
+      const float dz = st[nb][3] * (dzh[nb] - m1 - zhat[nb] * m2);
+      const float i = gate_i[nb], f = gate_f[nb], g = gate_g[nb];
+      da[nb][0] = dz * g * i * (1.f - i);
+      da[nb][1] = dz * cprev[nb] * f * (1.f - f);
+      da[nb][2] = dz * i * (1.f - g * g);
+      dc_reg[nb] = dz * f;
+      float a1 = 0.f, a2 = 0.f;
+#pragma unroll
+      for (int gg = 0; gg < 4; ++gg) {
+        if (!unit) da[nb][gg] = 0.f;
+        pg_w[nb][gg] += da[nb][gg] * uh[nb][gg];
+        pg_b[nb][gg] += da[nb][gg];
+        const float d = da[nb][gg] * ghw[gg];
+        a1 += d; a2 += d * uh[nb][gg];
+      }
+      s[2 * nb] = a1; s[2 * nb + 1] = a2;
+    }
+    cta_sum(s, redB);
+#pragma unroll
+    for (int nb = 0; nb < NB; ++nb) {
+      const float a1 = s[2 * nb] / (float)G, a2 = s[2 * nb + 1] / (float)G;
+      const int b = b0 + nb;
+      const long long tb = (long long)t * p.B + b;
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const float d = st[nb][1] * (da[nb][g] * ghw[g] - a1 - uh[nb][g] * a2);
+        if (unit) s_du[nb * G + swz(g * H + t_id)] = d;
+        if (owner && b < p.B) {
+          p.dgi[tb * G + g * H + t_id] = da[nb][g];
+          p.du[tb * G + g * H + t_id] = d;
+        }
+      }
     }
     __syncthreads();
-    for (int k = t_id; k < H; k += kNT) {
-      float v = 0.f;
-      for (int rp = 0; rp < rparts; ++rp) v += s_tp[rp * H + k];
-      const int q = k / HS;
-      cluster.map_shared_rank(s_dhp, q)[r * HS + (k - q * HS)] = v;
-    }
-    cluster.sync();                                                            // (C)
-    if (t_id < HS) {
-      float v = 0.f;
+    // ---- dh_{t-1} slice = W_hh^T[r*HS + us, :] . du, all-gathered into s_dhf[buf ^ 1] of every CTA
+    float acc[NB];
 #pragma unroll
-      for (int q = 0; q < kCS; ++q) v += s_dhp[q * HS + t_id];
-      s_dh[t_id] = v;
+    for (int nb = 0; nb < NB; ++nb) acc[nb] = 0.f;
+    if (us < HS) {
+      const uint4* w4 = reinterpret_cast<const uint4*>(sW) + us * chunks + pt;
+      const float4* d4 = reinterpret_cast<const float4*>(s_du) + 2 * pt + (hs4 >> 2);
+#pragma unroll 8
+      for (int c = 0; c < cpl; ++c) {
+        float w[8];
+        unpack8f(w4[8 * c], w);
+#pragma unroll
+        for (int nb = 0; nb < NB; ++nb) {
+          const float4* dp = d4 + nb * (G / 4) + 16 * c;
+          acc[nb] += dot8f(w, dp[0], dp[1 - (hs4 >> 1)]);
+        }
+      }
     }
-    // s_dh is next read by the same threads; s_dhp is rewritten only after two more cluster barriers
+#pragma unroll
+    for (int nb = 0; nb < NB; ++nb) acc[nb] = sum8lanes(acc[nb]);
+    if (us < HS && pt == 0) {
+#pragma unroll
+      for (int nb = 0; nb < NB; ++nb) s_sl[nb * HS + us] = acc[nb];
+    }
+    __syncthreads();
+    {
+      const int q4 = HS >> 2, per_peer = NB * q4;
+      for (int i = t_id; i < kCS * per_peer; i += kNT) {
+        const int peer = i / per_peer, k = i - peer * per_peer;
+        const int nb = k / q4, x4 = k - nb * q4;
+        float* dst = cluster.map_shared_rank(s_dhf, peer) + ((buf ^ 1) * NB + nb) * H + r * HS + x4 * 4;
+        *reinterpret_cast<float4*>(dst) = *reinterpret_cast<const float4*>(s_sl + nb * HS + x4 * 4);
+      }
+    }
+    cluster_arrive();
   }
-  if (t_id < HS) {
-    if (p.dh0) p.dh0[(long long)b * H + k_unit] = s_dh[t_id];
-    if (p.dc0) p.dc0[(long long)b * H + k_unit] = s_dc[t_id];
-    float* dp = p.dparam + (long long)b * (2 * G + 2 * H);
-    dp[2 * G + k_unit] = pg_cw;
-    dp[2 * G + H + k_unit] = pg_cb;
+  cluster_wait();                                      // dh_{-1} (= d h0) complete
+  const int fin = ((0 & 1) ^ 1);                       // buffer written at t = 0
+#pragma unroll
+  for (int nb = 0; nb < NB; ++nb) {
+    const int b = b0 + nb;
+    if (b >= p.B) continue;
+    if (owner) {
+      if (p.dh0) p.dh0[(long long)b * H + t_id] = s_dhf[(fin * NB + nb) * H + t_id];
+      if (p.dc0) p.dc0[(long long)b * H + t_id] = dc_reg[nb];
+      float* dp = p.dparam + (long long)b * (2 * G + 2 * H);
+#pragma unroll
+      for (int g = 0; g < 4; ++g) { dp[g * H + t_id] = pg_w[nb][g]; dp[G + g * H + t_id] = pg_b[nb][g]; }
+      dp[2 * G + t_id] = pg_cw[nb];
+      dp[2 * G + H + t_id] = pg_cb[nb];
+    }
   }
-  if (t_id < rows) {
-    float* dp = p.dparam + (long long)b * (2 * G + 2 * H);
-    dp[j_row] = pg_w;
-    dp[G + j_row] = pg_b;
-  }
-  cluster.sync();          // no CTA may exit while a peer can still write into its shared memory
+  cluster.sync();
 }
 
-static int fwd_smem_bytes(int H) {
-  const int HS = H / kCS, rows = 4 * HS, parts = kNT / rows;
-  return rows * (2 * H + 16) + (H + parts * rows + rows + HS + 4 * kCS + 2 * kNW) * 4;
-}
-static int bwd_smem_bytes(int H) {
-  const int HS = H / kCS, rows = 4 * HS, rparts = kNT / (H / 2);
-  return rows * (2 * H + 16) + (2 * HS + 4 * rows + rparts * H + kCS * HS + 4 * kCS + 2 * kNW) * 4;
-}
+static int fwd_smem_bytes(int H, int NB) { return 4 * (H / kCS) * H * 2 + (NB * H + 2 * NB * 4 * H + NB * 4 * (H / kCS) + 4 * NB * kNW) * 4; }
+static int bwd_smem_bytes(int H, int NB) { return (H / kCS) * 4 * H * 2 + (NB * 4 * H + 2 * NB * H + NB * (H / kCS) + 4 * NB * kNW) * 4; }
 
-// shapes the cluster kernels take: H splits into 8 slices of whole 16-byte chunks, one thread per gate row, and the
-// W_hh slice fits in shared memory
-bool lnlstm_cluster_ok(int H) {
-  if (H <= 0 || H % (8 * kCS) != 0) return false;
-  const int HS = H / kCS, rows = 4 * HS;
-  if (rows > kNT || kNT % rows != 0) return false;
-  const int parts = kNT / rows;
-  if ((H / 8) % parts != 0) return false;
-  if (H / 2 > kNT || kNT % (H / 2) != 0) return false;
-  const int rparts = kNT / (H / 2);
-  if (rows % rparts != 0) return false;
-  return fwd_smem_bytes(H) <= 220 * 1024 && bwd_smem_bytes(H) <= 220 * 1024;
-}
+// The kernels are written for any H <= 384 with H % 64 == 0 (one thread per hidden unit, one lane octet per unit of
+// the CTA's slice, weight rows made of whole octets of 16-byte chunks) but are instantiated for the core LSTM only.
+constexpr int kClusterH = 384;      // the instantiated hidden size (core LSTM); other sizes take the lstm.cu kernels
+bool lnlstm_cluster_ok(int H) { return H == kClusterH; }
 
 template <typename Params>
-static int launch_cluster(void (*kern)(const Params), const Params& p, int B, int smem, cudaStream_t st) {
+static int launch_cluster(void (*kern)(const Params), const Params& p, int clusters, int smem, cudaStream_t st) {
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return (int)e;
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(B * kCS);
+  cfg.gridDim = dim3(clusters * kCS);
   cfg.blockDim = dim3(kNT);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
@@ -378,20 +473,46 @@ static int launch_cluster(void (*kern)(const Params), const Params& p, int B, in
   return AS_OK;
 }
 
+// diagnostics: how many clusters of the forward kernel can be resident at once on the current device
+int lnlstm_cluster_max_active(int H) {
+  const int smem = fwd_smem_bytes(H, 2);
+  if (cudaFuncSetAttribute(lnlstm_fwd_cluster_kernel<2, kClusterH>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(64 * kCS);
+  cfg.blockDim = dim3(kNT);
+  cfg.dynamicSmemBytes = smem;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = kCS; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, lnlstm_fwd_cluster_kernel<2, kClusterH>, &cfg) != cudaSuccess) return -2;
+  return n;
+}
+
+int lnlstm_set_profile(long long* buf) {
+  return (int)cudaMemcpyToSymbol(g_lstm_prof, &buf, sizeof(buf));
+}
+
+constexpr int kOneWaveClusters = 15;   // measured on B200 for this footprint (as_debug_lstm_max_clusters)
+
 int lnlstm_fwd_cluster(const float* gi, const float* h0, const float* c0, const void* whh, const float* gh_w,
                        const float* gh_b, const float* gc_w, const float* gc_b, float* y, float* c_all, float* u_all,
                        float* z_all, float* stats, int T, int B, int H, cudaStream_t st) {
   LstmClFwd p{gi, h0, c0, reinterpret_cast<const __nv_bfloat16*>(whh), gh_w, gh_b, gc_w, gc_b, y, c_all, u_all, z_all, stats, T, B, H};
-  return launch_cluster(lnlstm_fwd_cluster_kernel, p, B, fwd_smem_bytes(H), st);
+  if (B <= kOneWaveClusters) return launch_cluster(lnlstm_fwd_cluster_kernel<1, kClusterH>, p, B, fwd_smem_bytes(H, 1), st);
+  return launch_cluster(lnlstm_fwd_cluster_kernel<2, kClusterH>, p, (B + 1) / 2, fwd_smem_bytes(H, 2), st);
 }
 
 int lnlstm_bwd_cluster(const float* gi, const float* c0, const float* c_all, const float* u_all, const float* z_all,
-                       const float* stats, const void* whh, const float* gh_w, const float* gh_b, const float* gc_w,
+                       const float* stats, const void* whh_t, const float* gh_w, const float* gh_b, const float* gc_w,
                        const float* gc_b, const float* dy, const float* dhT, const float* dcT, float* dgi, float* du,
                        float* dh0, float* dc0, float* dparam, int T, int B, int H, cudaStream_t st) {
-  LstmClBwd p{gi, c0, c_all, u_all, z_all, stats, reinterpret_cast<const __nv_bfloat16*>(whh), gh_w, gh_b, gc_w, gc_b,
+  LstmClBwd p{gi, c0, c_all, u_all, z_all, stats, reinterpret_cast<const __nv_bfloat16*>(whh_t), gh_w, gh_b, gc_w, gc_b,
               dy, dhT, dcT, dgi, du, dh0, dc0, dparam, T, B, H};
-  return launch_cluster(lnlstm_bwd_cluster_kernel, p, B, bwd_smem_bytes(H), st);
+  if (B <= kOneWaveClusters) return launch_cluster(lnlstm_bwd_cluster_kernel<1, kClusterH>, p, B, bwd_smem_bytes(H, 1), st);
+  return launch_cluster(lnlstm_bwd_cluster_kernel<2, kClusterH>, p, (B + 1) / 2, bwd_smem_bytes(H, 2), st);
 }
 
 }  // namespace as

@@ -431,18 +431,15 @@ class LNLSTMLayerFn(torch.autograd.Function):
         T, B, H = ctx.dims
         G = 4 * H
         dev = gi.device
-        if _lib.lib().as_lnlstm_cluster_ok(H):
-            whh16, whh_t16 = weight_bf16(whh), None                 # cluster kernels read W_hh row slices only
-        else:
-            tag = (_SHADOW_GEN[0], whh._version, whh.data_ptr())
-            hit = getattr(whh, '_as_wt16', None)
-            if hit is None or hit[0] != tag:
-                hit = (tag, whh.detach().t().contiguous().to(torch.bfloat16))
-                try:
-                    whh._as_wt16 = hit
-                except AttributeError:
-                    pass
-            whh16, whh_t16 = None, hit[1]
+        tag = (_SHADOW_GEN[0], whh._version, whh.data_ptr())
+        hit = getattr(whh, '_as_wt16', None)
+        if hit is None or hit[0] != tag:
+            hit = (tag, whh.detach().t().contiguous().to(torch.bfloat16))
+            try:
+                whh._as_wt16 = hit
+            except AttributeError:
+                pass
+        whh_t16 = hit[1]
         dy = None if dy is None else dy.contiguous().float()
         dhT = None if dhT is None else dhT.contiguous().float()
         dcT = None if dcT is None else dcT.contiguous().float()
@@ -452,7 +449,7 @@ class LNLSTMLayerFn(torch.autograd.Function):
         dc0 = torch.empty_like(c0)
         dparam = torch.empty((B, 10 * H), dtype=torch.float32, device=dev)
         _lib.call('as_lnlstm_bwd', gi.data_ptr(), h0.data_ptr(), c0.data_ptr(), y.data_ptr(), c_all.data_ptr(),
-                  u_all.data_ptr(), z_all.data_ptr(), stats.data_ptr(), _ptr(whh_t16), _ptr(whh16), gh_w.data_ptr(),
+                  u_all.data_ptr(), z_all.data_ptr(), stats.data_ptr(), whh_t16.data_ptr(), gh_w.data_ptr(),
                   gh_b.data_ptr(), gc_w.data_ptr(), gc_b.data_ptr(), _ptr(dy), _ptr(dhT), _ptr(dcT), dgi.data_ptr(),
                   du.data_ptr(), dh0.data_ptr(), dc0.data_ptr(), dparam.data_ptr(), T, B, H, _lib.stream_ptr())
         dp = dparam.sum(dim=0)

@@ -163,19 +163,19 @@ int as_layer_norm_bwd(const float* dy32, const void* dy16, const float* x, const
 int as_lnlstm_fwd(const float* gi, const float* h0, const float* c0, const void* whh, const float* ln_h_w,
                   const float* ln_h_b, const float* ln_c_w, const float* ln_c_b, float* y, float* c_all, float* u_all,
                   float* z_all, float* stats, int T, int B, int H, void* stream);
-/* Reverse-time twin.  whh_t = W_hh^T bf16 [H,4H], whh = W_hh bf16 [4H,H]; dy [T,B,H] / dhT / dcT [B,H] may be NULL.
- * Outputs: dgi [T,B,4H], du [T,B,4H] (dW_hh = sum_{t,b} du h_{t-1}^T is a GEMM the caller runs), dh0/dc0 [B,H] (may
- * be NULL), and dparam [B, 10H] = per-trajectory partial gradients of (ln_h_w, ln_h_b, ln_c_w, ln_c_b).
- * When as_lnlstm_cluster_ok(H) both directions run on clusters of 8 CTAs per trajectory with their W_hh row slices
- * resident in shared memory for the whole unroll (H = 384: the core LSTM); that path reads only `whh`, so `whh_t` may
- * be NULL there.  Otherwise one CTA per trajectory streams `whh` (forward) / `whh_t` (backward) from L2 and `whh` may
- * be NULL in the backward call. */
-int as_lnlstm_cluster_ok(int H);
+/* Reverse-time twin.  whh_t = W_hh^T bf16 [H,4H]; dy [T,B,H] / dhT / dcT [B,H] may be NULL.  Outputs: dgi [T,B,4H],
+ * du [T,B,4H] (dW_hh = sum_{t,b} du h_{t-1}^T is a GEMM the caller runs), dh0/dc0 [B,H] (may be NULL), and dparam
+ * [B, 10H] = per-trajectory partial gradients of (ln_h_w, ln_h_b, ln_c_w, ln_c_b). */
 int as_lnlstm_bwd(const float* gi, const float* h0, const float* c0, const float* y, const float* c_all,
-                  const float* u_all, const float* z_all, const float* stats, const void* whh_t, const void* whh,
-                  const float* ln_h_w, const float* ln_h_b, const float* ln_c_w, const float* ln_c_b, const float* dy,
-                  const float* dhT, const float* dcT, float* dgi, float* du, float* dh0, float* dc0, float* dparam, int T,
-                  int B, int H, void* stream);
+                  const float* u_all, const float* z_all, const float* stats, const void* whh_t, const float* ln_h_w,
+                  const float* ln_h_b, const float* ln_c_w, const float* ln_c_b, const float* dy, const float* dhT,
+                  const float* dcT, float* dgi, float* du, float* dh0, float* dc0, float* dparam, int T, int B, int H,
+                  void* stream);
+/* 1 when both directions run for this H on clusters of 8 CTAs (one or two trajectories per cluster) that keep their
+ * W_hh / W_hh^T row slices in shared memory for the whole unroll and exchange u / dh slices through distributed
+ * shared memory once per step (H = 384, the core LSTM); 0 when one CTA per trajectory streams the weights from L2.
+ * Same arguments and results either way. */
+int as_lnlstm_cluster_ok(int H);
 
 /* Masked attention softmax with warp-shuffle reductions -- replaces masked_fill_ + F.softmax at
  * module_utils.py:100-104.  scores [groups, Nq, Nk] fp32 (already scaled by 1/sqrt(d)); key j of group g is valid
