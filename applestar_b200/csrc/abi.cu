@@ -6,6 +6,7 @@
 namespace as {
 extern int g_gemm_debug;
 extern int g_gemm_no_tma_store;
+extern int g_gemm_no_slab;
 int scatter_fwd(const float*, const void*, const void*, int, const long long*, float*, long long, int, int, int, int,
                 int, cudaStream_t);
 int scatter_bwd(const float*, const void*, const void*, int, const long long*, float*, long long, int, int, int, int,
@@ -70,7 +71,12 @@ extern "C" {
 int as_abi_version(void) { return 3; }
 
 // diagnostics only (not part of the public header): 0 normal, 1 GEMM epilogue skips global stores, 2 only drains TMEM
-int as_debug_gemm_mode(int mode) { as::g_gemm_debug = mode & 7; as::g_gemm_no_tma_store = (mode >> 3) & 1; return 0; }
+// bit 3: register-store epilogue, bit 4: per-tap convolution mode
+int as_debug_gemm_mode(int mode) {
+  as::g_gemm_debug = mode & 7; as::g_gemm_no_tma_store = (mode >> 3) & 1;
+  as::g_gemm_no_slab = (mode >> 4) & 1;
+  return 0;
+}
 
 int as_scatter_connection_fwd(const float* emb, const void* xs, const void* ys, int idx_bytes,
                               const int64_t* entity_num, float* out, int64_t R, int N, int D, int H, int W, int cover,

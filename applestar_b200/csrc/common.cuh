@@ -138,6 +138,20 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint
       ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// Warp-uniform variants: the WHOLE warp executes the call with identical operands and only the lane with
+// leader != 0 issues the instruction.  Keeping the surrounding loop free of lane-divergent control flow lets the
+// compiler hold descriptors and addresses in uniform registers; under `if (lane == 0)` it emits an
+// elect / R2UR.BROADCAST / branch loop per instruction instead, which makes the issuing thread the bottleneck
+// for small tiles.
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate);
+__device__ __forceinline__ void umma_commit(uint64_t* bar);
+__device__ __forceinline__ void umma_bf16_lead(uint32_t leader, uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                               uint32_t idesc, uint32_t accumulate) {
+  if (leader) umma_bf16(tmem_d, desc_a, desc_b, idesc, accumulate);
+}
+__device__ __forceinline__ void umma_commit_lead(uint32_t leader, uint64_t* bar) {
+  if (leader) umma_commit(bar);
+}
 // arrive on an mbarrier once all previously issued tcgen05.mma of this thread have completed
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))

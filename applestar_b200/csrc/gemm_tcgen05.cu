@@ -8,8 +8,14 @@
 // contiguous), so X*W^T (forward), dY*W (dgrad) and dY^T*X (wgrad) all run without materialising a transpose.
 // Extra modes: split-K (fp32 partials into a caller workspace, reduced by as_splitk_reduce) and an implicit-GEMM
 // 3x3 convolution over zero-padded NHWC pixels (per-tap row shift of the A operand, see as_conv3x3_*).
+// Multi-tap convolutions normally run in SLAB mode: one CTA step covers 256 consecutive pixels (two accumulators);
+// per 64-channel block the pixels plus a halo of +-(row pitch + 1) are loaded ONCE, and each tap's A operand is a
+// shared-memory descriptor whose start address is offset by whole 128-byte rows into that slab.  That cuts the L2 -> shared-memory traffic of A by ~9x and of the weights by 2x; the per-tap
+// mode re-reads A for every tap and is L2-bandwidth bound (measured 190-730 TFLOP/s).
 //
 // Warp roles (12 warps): w0 TMA producer, w1 MMA issuer, w2 TMEM allocator, w4-11 epilogue.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "gemm.h"
 
@@ -32,6 +38,8 @@ struct GemmDev {
   int img_w, img_h;  // padded image dims for border masking (0 = off)
   int b_k_shift;     // MN-major B only: row offset added to the contraction coordinate
   int wgrad_taps;    // >0: batch index b0 = conv tap; A and B are shared by all taps, B rows shifted by shift[b0]
+  // slab mode (multi-tap conv): 256-row steps, A slab = 2 TMA boxes of slab_box rows starting at row m0 - halo
+  int slab, halo, slab_box, slab_bytes, slab_slots, b_slots, tpb, b_resident;
   // epilogue
   void* C;
   void* C2;   // optional bf16 copy of the output (same ldc / batch strides)
@@ -51,9 +59,11 @@ struct SmemLayout {
   static constexpr int kBBytes = BN * 128;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = (BN >= 256) ? 4 : (BN >= 128 ? 6 : 8);
+  static constexpr int kRingBytes = 192 * 1024;                              // operand ring (>= kStages * kStageBytes); slab mode re-carves it
+  static_assert(kStages * kStageBytes <= kRingBytes, "ring too small");
   static constexpr int kBarBytes = 1024;
   static constexpr int kStgBytes = kEpiWarps * 4096;                         // per-warp epilogue staging tiles (32 rows x 128 B)
-  static constexpr int kTotal = kStages * kStageBytes + kBarBytes + kStgBytes + 1024;  // +1024 alignment slack
+  static constexpr int kTotal = kRingBytes + kBarBytes + kStgBytes + 1024;   // +1024 alignment slack
 };
 
 template <int BN, bool A_MN, bool B_MN>
@@ -73,12 +83,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   // 1024-byte alignment for the 128B swizzle; pointer arithmetic (not an integer round trip) keeps the shared
   // address space visible to the compiler
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-  uint8_t* bar_base = smem + kStages * L::kStageBytes;
+  uint8_t* bar_base = smem + L::kRingBytes;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(bar_base);
   uint64_t* empty_bar = full_bar + kStages;
   uint64_t* tmem_full = empty_bar + kStages;
   uint64_t* tmem_empty = tmem_full + kAcc;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + kAcc);
+  uint64_t* slab_full = tmem_empty + kAcc;            // slab mode: 3 A slabs
+  uint64_t* slab_empty = slab_full + 3;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(slab_empty + 3);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -96,6 +108,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       mbar_init(&tmem_full[i], 1);
       mbar_init(&tmem_empty[i], kSplitCols ? kEpiWarps : kEpiWarps / 2);
     }
+    for (int i = 0; i < 3; ++i) {
+      mbar_init(&slab_full[i], 1);
+      mbar_init(&slab_empty[i], 1);
+    }
     mbar_fence_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, kTmemCols);
@@ -108,7 +124,120 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const long long tiles_per_split = (long long)batch * p.m_blocks * p.n_blocks;
   const long long num_tiles = tiles_per_split * p.splits;
 
-  if (warp == 0) {
+  // slab mode: work item = (n block, pair of m blocks); shared memory = the A slabs followed by the weight tiles
+  // (a ring of per-tap tiles, or -- when they all fit -- every tile of the convolution, loaded once)
+  const long long num_work = p.slab ? (long long)((p.m_blocks + 1) / 2) * p.n_blocks : num_tiles;
+  uint8_t* b_ring = smem + p.slab_slots * p.slab_bytes;
+
+  if (warp == 0 && p.slab) {
+    // ------------------------------------------------------------------ TMA producer, slab mode
+    if (lane == 0 && !A_MN && !B_MN) {
+      // chunk = (work item, 64-channel block).  The slab of chunk i+1 is requested before the weight tiles of chunk i.
+      const long long my_work = (num_work - blockIdx.x + gridDim.x - 1) / gridDim.x;
+      const long long chunks = my_work * p.cin_blocks;
+      const int nsl = p.slab_slots;
+      int bslot = 0; uint32_t bphase = 0;
+      auto load_slab = [&](long long ci) {
+        const long long w = blockIdx.x + (ci / p.cin_blocks) * gridDim.x;
+        const int cb = (int)(ci % p.cin_blocks);
+        const int m0 = (int)(w / p.n_blocks) * (2 * BM);
+        const int sl = (int)(ci % nsl);
+        const uint32_t ph = (uint32_t)((ci / nsl) & 1);
+        mbar_wait(&slab_empty[sl], ph ^ 1);
+        uint8_t* dst = smem + sl * p.slab_bytes;
+        mbar_expect_tx(&slab_full[sl], 2 * p.slab_box * 128);
+        tma_load_4d(dst, &tmA, &slab_full[sl], cb * BK, m0 - p.halo, 0, 0);
+        tma_load_4d(dst + p.slab_box * 128, &tmA, &slab_full[sl], cb * BK, m0 - p.halo + p.slab_box, 0, 0);
+      };
+      if (p.b_resident) {
+        // all weight tiles of the convolution (n_blocks == 1): one barrier, loaded once per CTA
+        mbar_expect_tx(&full_bar[0], p.cin_blocks * p.taps * L::kBBytes);
+        for (int cb = 0; cb < p.cin_blocks; ++cb)
+          for (int tap = 0; tap < p.taps; ++tap)
+            tma_load_4d(b_ring + (cb * p.taps + tap) * L::kBBytes, &tmB, &full_bar[0], tap * p.cin + cb * BK, 0, 0, 0);
+        for (long long ci = 0; ci < chunks; ++ci) load_slab(ci);
+      } else {
+        if (chunks > 0) load_slab(0);
+        for (long long ci = 0; ci < chunks; ++ci) {
+          if (ci + 1 < chunks) load_slab(ci + 1);
+          const long long w = blockIdx.x + (ci / p.cin_blocks) * gridDim.x;
+          const int cb = (int)(ci % p.cin_blocks);
+          const int n0 = (int)(w % p.n_blocks) * BN;
+          for (int tap = 0; tap < p.taps; tap += p.tpb) {
+            mbar_wait(&empty_bar[bslot], bphase ^ 1);
+            mbar_expect_tx(&full_bar[bslot], p.tpb * L::kBBytes);
+            for (int j = 0; j < p.tpb; ++j)
+              tma_load_4d(b_ring + (bslot * p.tpb + j) * L::kBBytes, &tmB, &full_bar[bslot], (tap + j) * p.cin + cb * BK, n0, 0, 0);
+            if (++bslot == p.b_slots) { bslot = 0; bphase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1 && p.slab) {
+    // ------------------------------------------------------------------ MMA issuer, slab mode (warp-uniform loop,
+    // lane 0 issues: see umma_bf16_lead)
+    if (!A_MN && !B_MN) {
+      const uint32_t leader = lane == 0 ? 1u : 0u;
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+      // descriptor = constant high word | (lbo << 16) | (address >> 4): per MMA only the low word changes, by an
+      // immediate (the issuing thread is the critical path when N is small)
+      constexpr uint32_t kDescHi = (1024u >> 4) | (1u << 14) | (2u << 29);
+      constexpr uint32_t kDescLbo = (16u >> 4) << 16;
+      const int nsl = p.slab_slots;
+      int bslot = 0; uint32_t bphase = 0;
+      long long ci = 0;
+      uint32_t it2 = 0;
+      if (p.b_resident) { mbar_wait(&full_bar[0], 0); tc_fence_after(); }
+      for (long long w = blockIdx.x; w < num_work; w += gridDim.x, ++it2) {
+        const int acc0 = (int)((2 * it2) % kAcc);
+        const uint32_t acc_phase = ((2 * it2) / kAcc) & 1u;
+        mbar_wait(&tmem_empty[acc0], acc_phase ^ 1);
+        mbar_wait(&tmem_empty[acc0 + 1], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d0 = __shfl_sync(0xffffffffu, tmem_base + (uint32_t)(acc0 * BN), 0);
+        for (int cb = 0; cb < p.cin_blocks; ++cb, ++ci) {
+          const int sl = (int)(ci % nsl);
+          mbar_wait(&slab_full[sl], (uint32_t)((ci / nsl) & 1));
+          tc_fence_after();
+          const uint32_t slab_lo = kDescLbo | ((smem_u32(smem + sl * p.slab_bytes) >> 4) + (uint32_t)(p.halo * 8));
+          for (int tap = 0; tap < p.taps; tap += p.tpb) {
+            uint32_t b_lo;
+            if (p.b_resident) {
+              b_lo = kDescLbo | (smem_u32(b_ring + (cb * p.taps + tap) * L::kBBytes) >> 4);
+            } else {
+              mbar_wait(&full_bar[bslot], bphase);
+              tc_fence_after();
+              b_lo = kDescLbo | (smem_u32(b_ring + bslot * p.tpb * L::kBBytes) >> 4);
+            }
+            for (int j = 0; j < p.tpb; ++j) {
+              // the 128-byte swizzle is a function of the absolute shared-memory address, so a start address that
+              // is only 128-byte aligned needs no descriptor base offset (verified against the per-tap mode)
+              // shuffles from lane 0 mark the operands as warp-uniform for the compiler (uniform-register operands)
+              const uint32_t a_lo = __shfl_sync(0xffffffffu, slab_lo + (uint32_t)(p.shift[tap + j] * 8), 0);
+              const uint32_t bj_lo = __shfl_sync(0xffffffffu, b_lo + (uint32_t)(j * (L::kBBytes >> 4)), 0);
+              const uint32_t first = (cb > 0 || tap + j > 0) ? 1u : 0u;
+#pragma unroll
+              for (int sub = 0; sub < 2; ++sub) {
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k) {
+                  const uint64_t da = ((uint64_t)kDescHi << 32) | (a_lo + (uint32_t)(sub * (BM * 128 / 16) + k * 2));
+                  const uint64_t db = ((uint64_t)kDescHi << 32) | (bj_lo + (uint32_t)(k * 2));
+                  umma_bf16_lead(leader, d0 + (uint32_t)(sub * BN), da, db, idesc, k > 0 ? 1u : first);
+                }
+              }
+            }
+            if (!p.b_resident) {
+              umma_commit_lead(leader, &empty_bar[bslot]);
+              if (++bslot == p.b_slots) { bslot = 0; bphase ^= 1; }
+            }
+          }
+          umma_commit_lead(leader, &slab_empty[sl]);
+        }
+        umma_commit_lead(leader, &tmem_full[acc0]);
+        umma_commit_lead(leader, &tmem_full[acc0 + 1]);
+      }
+    }
+  } else if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
       int stage = 0;
@@ -158,8 +287,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       }
     }
   } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer (single thread)
-    if (lane == 0) {
+    // ------------------------------------------------------------------ MMA issuer (warp-uniform loop, lane 0 issues)
+    {
+      const uint32_t leader = lane == 0 ? 1u : 0u;
       // instruction descriptor: fp32 accum, bf16 A/B, majors, N>>3, M>>4
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
                              ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
@@ -174,24 +304,28 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        const uint32_t d_tmem = __shfl_sync(0xffffffffu, tmem_base + (uint32_t)(acc * BN), 0);
         for (int kb = kb_begin; kb < kb_end; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + stage * L::kStageBytes);
           const uint32_t sb = sa + L::kABytes;
+          // descriptor low word = (lbo << 16) | (address >> 4); the high word is constant, so per MMA the low words
+          // only advance by an immediate
+          constexpr uint32_t kDescHi = (1024u >> 4) | (1u << 14) | (2u << 29);
+          const uint32_t a_lo = __shfl_sync(0xffffffffu, ((A_MN ? (uint32_t)(BK * 128) : 16u) >> 4 << 16) | (sa >> 4), 0);
+          const uint32_t b_lo = __shfl_sync(0xffffffffu, ((B_MN ? (uint32_t)(BK * 128) : 16u) >> 4 << 16) | (sb >> 4), 0);
+          const uint32_t first = kb > kb_begin ? 1u : 0u;
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
-            const uint64_t da = A_MN ? make_smem_desc_sw128(sa + k * 16 * 128, BK * 128, 1024)
-                                     : make_smem_desc_sw128(sa + k * 32, 16, 1024);
-            const uint64_t db = B_MN ? make_smem_desc_sw128(sb + k * 16 * 128, BK * 128, 1024)
-                                     : make_smem_desc_sw128(sb + k * 32, 16, 1024);
-            umma_bf16(d_tmem, da, db, idesc, (kb > kb_begin || k > 0) ? 1u : 0u);
+            const uint64_t da = ((uint64_t)kDescHi << 32) | (a_lo + (uint32_t)(k * (A_MN ? 16 * 128 / 16 : 2)));
+            const uint64_t db = ((uint64_t)kDescHi << 32) | (b_lo + (uint32_t)(k * (B_MN ? 16 * 128 / 16 : 2)));
+            umma_bf16_lead(leader, d_tmem, da, db, idesc, k > 0 ? 1u : first);
           }
-          umma_commit(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
+          umma_commit_lead(leader, &empty_bar[stage]);  // frees the smem slot when these MMAs retire
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tmem_full[acc]);      // accumulator complete -> epilogue
+        umma_commit_lead(leader, &tmem_full[acc]);      // accumulator complete -> epilogue
       }
     }
   } else if (warp >= 4) {
@@ -208,15 +342,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int c_begin = kSplitCols ? half * (kChunks / 2) : 0;
     const int c_end = kSplitCols ? c_begin + kChunks / 2 : kChunks;
     uint32_t it = 0;
-    for (long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    const int subs = p.slab ? 2 : 1;
+    for (long long tile = blockIdx.x; tile < num_work; tile += gridDim.x)
+    for (int sub = 0; sub < subs; ++sub, ++it) {
       if (!kSplitCols && (int)(it & 1u) != half) continue;     // narrow tiles: this tile belongs to the other warp set
       const int acc = (int)(it % kAcc);
       const uint32_t acc_phase = (it / kAcc) & 1u;
       long long t = tile;
       const int n_blk = (int)(t % p.n_blocks); t /= p.n_blocks;
-      const int m_blk = (int)(t % p.m_blocks); t /= p.m_blocks;
-      const int b = (int)(t % batch);
-      const int split = (int)(t / batch);
+      int m_blk, b, split;
+      if (p.slab) { m_blk = (int)t * 2 + sub; b = 0; split = 0; }
+      else { m_blk = (int)(t % p.m_blocks); t /= p.m_blocks; b = (int)(t % batch); split = (int)(t / batch); }
       const int b0 = b % p.nb0, b1 = b / p.nb0;
       const int row_base = m_blk * BM + ew * 32;
       const int n0 = n_blk * BN;
@@ -554,6 +690,7 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMa
     attr_set = true;
   }
   long long tiles = (long long)p.splits * p.nb0 * p.nb1 * p.m_blocks * p.n_blocks;
+  if (p.slab) tiles = (long long)((p.m_blocks + 1) / 2) * p.n_blocks;
   int grid = (int)(tiles < num_sms() ? tiles : num_sms());
   if (grid <= 0) return AS_OK;
   kern<<<grid, kGemmThreads, L::kTotal, st>>>(ta, tb, tc, tc2, p);
@@ -580,6 +717,7 @@ static int pick_bn(int N, bool b_mn) {
 
 int g_gemm_debug = 0;
 int g_gemm_no_tma_store = 0;
+int g_gemm_no_slab = 0;       // diagnostics: force the per-tap convolution mode
 
 int gemm_run(const GemmCall& g, cudaStream_t st) {
   if (g.M <= 0 || g.N <= 0 || g.K <= 0 || g.nb0 <= 0 || g.nb1 <= 0) return AS_ESIZE;
@@ -617,13 +755,45 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
   p.C = g.C; p.C2 = g.C2; p.c_bf16 = g.c_bf16; p.ldc = g.ldc; p.c_sb0 = g.c_sb0; p.c_sb1 = g.c_sb1;
   p.bias = g.bias; p.relu = g.relu; p.alpha = g.alpha; p.ws = g.ws;
   p.debug = g_gemm_debug;
+  // slab mode for multi-tap convolutions (see the header comment): needs the halo'd slab of a 256-row step to fit two
+  // TMA boxes of <= 256 rows and three slabs plus >= 3 weight tiles to fit the operand ring
+  p.slab = 0;
+  int a_box_rows = BM;
+  if (g.taps > 1 && !g.a_mn && !g.b_mn && BN <= 128 && !g_gemm_no_slab) {
+    int halo = 0;
+    for (int i = 0; i < g.taps; ++i) halo = halo > abs(g.shift[i]) ? halo : abs(g.shift[i]);
+    const int rows = 2 * BM + 2 * halo;
+    const int box = (((rows + 1) / 2) + 7) & ~7;
+    const int slab_bytes = 2 * box * 128;                 // multiple of 2048
+    const int ring = 192 * 1024;
+    const int b_bytes = BN * 128;
+    const int max_slots = (BN >= 128) ? 6 : 8;            // = kStages of the instantiation (barrier array size)
+    const int cin_blocks = (g.K + BK - 1) / BK;
+    const long long all_b = (long long)cin_blocks * g.taps * b_bytes;
+    if (box <= 256) {
+      if (p.n_blocks == 1 && 2 * slab_bytes + all_b <= ring && !getenv("AS_SLAB_NO_RESIDENT")) {
+        // every weight tile stays in shared memory for the whole kernel; two slabs double-buffer the pixels
+        p.slab = 1; p.slab_slots = 2; p.b_resident = 1; p.tpb = 1; p.b_slots = 1;
+      } else {
+        // ring of weight tiles, `tpb` taps per slot (one barrier round trip per slot) and three slabs
+        int tpb = BN >= 128 ? 1 : 3;
+        if (g.taps % tpb != 0) tpb = 1;
+        int slots = (ring - 3 * slab_bytes) / (tpb * b_bytes);
+        if (slots < 3 && tpb > 1) { tpb = 1; slots = (ring - 3 * slab_bytes) / b_bytes; }
+        if (slots > max_slots) slots = max_slots;
+        if (const char* e = getenv("AS_SLAB_BSLOTS")) { const int v = atoi(e); if (v >= 2 && v < slots) slots = v; }
+        if (slots >= 2) { p.slab = 1; p.slab_slots = 3; p.b_resident = 0; p.tpb = tpb; p.b_slots = slots; }
+      }
+      if (p.slab) { p.halo = halo; p.slab_box = box; p.slab_bytes = slab_bytes; a_box_rows = box; }
+    }
+  }
 
   CUtensorMap ta, tb;
   int rc;
   const long long k_total_b = g.taps > 0 ? (long long)g.taps * g.K : g.K;
   const int onb0 = g.wgrad_taps > 0 ? 1 : g.nb0;      // tensor-map extent of the first batch dim
   if (g.a_mn) rc = make_map(&ta, g.A, g.M, g.K, g.lda, onb0, g.a_sb0, g.nb1, g.a_sb1, 64, BK);
-  else rc = make_map(&ta, g.A, g.K, g.a_rows > 0 ? g.a_rows : g.M, g.lda, onb0, g.a_sb0, g.nb1, g.a_sb1, BK, BM);
+  else rc = make_map(&ta, g.A, g.K, g.a_rows > 0 ? g.a_rows : g.M, g.lda, onb0, g.a_sb0, g.nb1, g.a_sb1, BK, a_box_rows);
   if (rc) return rc;
   if (g.b_mn) rc = make_map(&tb, g.B, g.N, k_total_b, g.ldb, onb0, g.b_sb0, g.nb1, g.b_sb1, 64, BK);
   else rc = make_map(&tb, g.B, k_total_b, g.N, g.ldb, onb0, g.b_sb0, g.nb1, g.b_sb1, BK, BN);
