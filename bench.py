@@ -78,6 +78,18 @@ def run_reference(args):
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
+    if 'WORLD_SIZE' in os.environ or 'OMP_NUM_THREADS' in os.environ:
+        # torchrun pins OMP_NUM_THREADS=1 in its workers: time the CPU arm in a child with the launcher's variables
+        # removed so that it can use every host core
+        import subprocess
+        drop = ('RANK', 'LOCAL_RANK', 'WORLD_SIZE', 'LOCAL_WORLD_SIZE', 'GROUP_RANK', 'ROLE_RANK', 'ROLE_WORLD_SIZE',
+                'MASTER_ADDR', 'MASTER_PORT', 'OMP_NUM_THREADS', 'GROUP_WORLD_SIZE', 'ROLE_NAME')
+        env = {k: v for k, v in os.environ.items() if k not in drop and not k.startswith('TORCHELASTIC')}
+        out = subprocess.run([sys.executable, os.path.abspath(__file__)] + sys.argv[1:], env=env, capture_output=True, text=True)
+        sys.stderr.write(out.stderr[-2000:])
+        sys.stdout.write(out.stdout)
+        sys.stdout.flush()
+        return
     T, B = (int(x) for x in args.cpu_sample.split('x'))
     threads = os.cpu_count() or 1
     steps, warmup = max(1, min(args.steps, 3)), min(args.warmup, 1)
@@ -280,7 +292,7 @@ def run_ours(args):
                          'peak_source': which + ' bf16_tflops_sustained', 'gemm_ms_per_step': g_ms,
                          'gemm_share_of_step': g_ms / (ms / args.steps), 'traffic': None},
         }
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:      # the CPU baseline is an N = 1 figure
             Tc, Bc = (int(x) for x in args.cpu_sample.split('x'))
             threads = os.cpu_count() or 1
             v, dt = cpu_learner_throughput(Tc, Bc, N, 2, 1, threads)
