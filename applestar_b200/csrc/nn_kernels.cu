@@ -142,15 +142,23 @@ layer_norm_fwd_v4_kernel(const float* __restrict__ x, const float* __restrict__ 
   }
 }
 
-template <int V>
+template <int V, bool PG>
 __global__ void __launch_bounds__(256)
 layer_norm_bwd_v4_kernel(const float* __restrict__ dy32, const __nv_bfloat16* __restrict__ dy16,
                          const float* __restrict__ x, const float* __restrict__ res, const float* __restrict__ gamma,
                          const float* __restrict__ beta, const float* __restrict__ stats, float* __restrict__ dx,
-                         long long rows, int C, int relu) {
+                         long long rows, int C, int relu, float* __restrict__ pgrad) {
+  // pgrad != NULL (PG): the parameter gradients are accumulated in the same pass -- every lane owns 4V fixed columns,
+  // sums g*xhat and g over the rows of its warp, the block's 8 warps are combined in shared memory and one partial
+  // row [2][C] per block goes to pgrad (reduced in fixed order by layer_norm_param_reduce_kernel).
   const int lane = threadIdx.x & 31;
   const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
+  float4 pg[PG ? V : 1], pb[PG ? V : 1];
+  if (PG) {
+#pragma unroll
+    for (int i = 0; i < V; ++i) { pg[i] = make_float4(0.f, 0.f, 0.f, 0.f); pb[i] = make_float4(0.f, 0.f, 0.f, 0.f); }
+  }
   for (long long row = warp_global; row < rows; row += warps_total) {
     const float mean = stats[row * 2], rstd = stats[row * 2 + 1];
     float4 xh[V], dg[V];
@@ -177,6 +185,10 @@ layer_norm_bwd_v4_kernel(const float* __restrict__ dy32, const __nv_bfloat16* __
         if (a.z * gm.z + bt.z <= 0.f) g.z = 0.f;
         if (a.w * gm.w + bt.w <= 0.f) g.w = 0.f;
       }
+      if (PG) {
+        pg[i].x += g.x * a.x; pg[i].y += g.y * a.y; pg[i].z += g.z * a.z; pg[i].w += g.w * a.w;
+        pb[i].x += g.x; pb[i].y += g.y; pb[i].z += g.z; pb[i].w += g.w;
+      }
       const float4 b = make_float4(g.x * gm.x, g.y * gm.y, g.z * gm.z, g.w * gm.w);
       xh[i] = a; dg[i] = b;
       s1 += b.x + b.y + b.z + b.w;
@@ -189,6 +201,26 @@ layer_norm_bwd_v4_kernel(const float* __restrict__ dy32, const __nv_bfloat16* __
       o.x = rstd * (dg[i].x - m1 - xh[i].x * m2); o.y = rstd * (dg[i].y - m1 - xh[i].y * m2);
       o.z = rstd * (dg[i].z - m1 - xh[i].z * m2); o.w = rstd * (dg[i].w - m1 - xh[i].w * m2);
       reinterpret_cast<float4*>(dx + row * C)[lane + i * 32] = o;
+    }
+  }
+  if (PG) {
+    extern __shared__ float4 s_pg[];                     // [8 warps][2][V*32] float4
+    const int w = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      s_pg[(w * 2 + 0) * (V * 32) + lane + i * 32] = pg[i];
+      s_pg[(w * 2 + 1) * (V * 32) + lane + i * 32] = pb[i];
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < 2 * V * 32; j += blockDim.x) {
+      const int which = j / (V * 32), col4 = j - which * (V * 32);
+      float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float4 u = s_pg[(k * 2 + which) * (V * 32) + col4];
+        t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
+      }
+      reinterpret_cast<float4*>(pgrad + ((long long)blockIdx.x * 2 + which) * C)[col4] = t;
     }
   }
 }
@@ -234,17 +266,28 @@ layer_norm_param_grad_kernel(const float* __restrict__ dy32, const __nv_bfloat16
   }
 }
 
-__global__ void layer_norm_param_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dgamma,
-                                               float* __restrict__ dbeta, int C, int chunks) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
+// fixed-order reduction of the per-chunk partials: 32 columns x 8 chunk lanes per block
+__global__ void __launch_bounds__(256)
+layer_norm_param_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dgamma,
+                               float* __restrict__ dbeta, int C, int chunks) {
+  const int cx = threadIdx.x & 31, ky = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + cx;
   float ag = 0.f, ab = 0.f;
-  for (int k = 0; k < chunks; ++k) {
-    ag += partial[((long long)k * 2 + 0) * C + c];
-    ab += partial[((long long)k * 2 + 1) * C + c];
+  if (c < C)
+    for (int k = ky; k < chunks; k += 8) {
+      ag += partial[((long long)k * 2 + 0) * C + c];
+      ab += partial[((long long)k * 2 + 1) * C + c];
+    }
+  __shared__ float sg[8][33], sb[8][33];
+  sg[ky][cx] = ag; sb[ky][cx] = ab;
+  __syncthreads();
+  if (ky == 0 && c < C) {
+    float tg = 0.f, tb = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { tg += sg[i][cx]; tb += sb[i][cx]; }
+    dgamma[c] = tg;
+    dbeta[c] = tb;
   }
-  dgamma[c] = ag;
-  dbeta[c] = ab;
 }
 
 static int ln_grid(long long rows) {
@@ -283,7 +326,7 @@ int layer_norm_fwd(const float* x, const float* res, const float* gamma, const f
   return AS_OK;
 }
 
-constexpr int kLnChunks = 1024;
+constexpr int kLnChunks = 148 * 8;      // = the largest grid of the fused backward (one partial row per block)
 long long layer_norm_bwd_scratch_floats(int C) { return (long long)kLnChunks * 2 * C; }
 
 int layer_norm_bwd(const float* dy32, const void* dy16, const float* x, const float* res, const float* gamma,
@@ -293,26 +336,39 @@ int layer_norm_bwd(const float* dy32, const void* dy16, const float* x, const fl
   if (C <= 0 || C > 32 * 48) return AS_ESIZE;
   if (!x || !gamma || !beta || !stats || (!dy32 && !dy16)) return AS_EINVAL;
   const __nv_bfloat16* d16 = reinterpret_cast<const __nv_bfloat16*>(dy16);
+  bool pg_done = false;
   if (dx) {
     const int grid = ln_grid(rows);
     const bool al = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(res) | reinterpret_cast<uintptr_t>(dy32) |
                       reinterpret_cast<uintptr_t>(gamma) | reinterpret_cast<uintptr_t>(beta) | reinterpret_cast<uintptr_t>(dx)) & 15) == 0 &&
                     (reinterpret_cast<uintptr_t>(dy16) & 7) == 0;
-    if (al && C == 256) layer_norm_bwd_v4_kernel<2><<<grid, 256, 0, st>>>(dy32, d16, x, res, gamma, beta, stats, dx, rows, C, relu);
-    else if (al && C == 384) layer_norm_bwd_v4_kernel<3><<<grid, 256, 0, st>>>(dy32, d16, x, res, gamma, beta, stats, dx, rows, C, relu);
-    else if (al && C == 1536) layer_norm_bwd_v4_kernel<12><<<grid, 256, 0, st>>>(dy32, d16, x, res, gamma, beta, stats, dx, rows, C, relu);
+    const bool fuse = dgamma && dbeta && scratch && (reinterpret_cast<uintptr_t>(scratch) & 15) == 0;
+    if (al && C == 256 && fuse) {
+      layer_norm_bwd_v4_kernel<2, true><<<grid, 256, 8 * 2 * 64 * 16, st>>>(dy32, d16, x, res, gamma, beta, stats, dx, rows, C, relu, scratch);
+      pg_done = true;
+    } else if (al && C == 384 && fuse) {
+      layer_norm_bwd_v4_kernel<3, true><<<grid, 256, 8 * 2 * 96 * 16, st>>>(dy32, d16, x, res, gamma, beta, stats, dx, rows, C, relu, scratch);
+      pg_done = true;
+    }
+    else if (al && C == 256) layer_norm_bwd_v4_kernel<2, false><<<grid, 256, 0, st>>>(dy32, d16, x, res, gamma, beta, stats, dx, rows, C, relu, nullptr);
+    else if (al && C == 384) layer_norm_bwd_v4_kernel<3, false><<<grid, 256, 0, st>>>(dy32, d16, x, res, gamma, beta, stats, dx, rows, C, relu, nullptr);
+    else if (al && C == 1536) layer_norm_bwd_v4_kernel<12, false><<<grid, 256, 0, st>>>(dy32, d16, x, res, gamma, beta, stats, dx, rows, C, relu, nullptr);
     else
     LN_DISPATCH(layer_norm_bwd_kernel, dy32, d16, x, res, gamma, beta, stats, dx, rows, C, relu);
     AS_LAUNCH_CHECK();
+    if (pg_done) {
+      layer_norm_param_reduce_kernel<<<(C + 31) / 32, 256, 0, st>>>(scratch, dgamma, dbeta, C, grid);
+      AS_LAUNCH_CHECK();
+    }
   }
-  if (dgamma && dbeta) {
+  if (dgamma && dbeta && !pg_done) {
     if (!scratch) return AS_EINVAL;
     long long want = (rows + 255) / 256;
     const int chunks = (int)(want < 1 ? 1 : (want > kLnChunks ? kLnChunks : want));
     dim3 g((C + 31) / 32, chunks);
     layer_norm_param_grad_kernel<<<g, 256, 0, st>>>(dy32, d16, x, res, gamma, beta, stats, scratch, rows, C, relu, chunks);
     AS_LAUNCH_CHECK();
-    layer_norm_param_reduce_kernel<<<(C + 127) / 128, 128, 0, st>>>(scratch, dgamma, dbeta, C, chunks);
+    layer_norm_param_reduce_kernel<<<(C + 31) / 32, 256, 0, st>>>(scratch, dgamma, dbeta, C, chunks);
     AS_LAUNCH_CHECK();
   }
   return AS_OK;

@@ -995,6 +995,83 @@ int maxpool2_bwd(const void* in, const void* dout, void* din, long long R, int H
   return AS_OK;
 }
 
+// dz = dy * (y > 0) AND out[c] = sum_r dz[r][c] in one pass (the ReLU backward and the bias gradient of a
+// convolution read the same tensor; fusing them saves one full read of dz).  Same thread mapping as
+// colsum_partial_v8_kernel: C % 8 == 0, 16-byte loads / stores.
+__global__ void __launch_bounds__(256)
+relu_bwd_colsum_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
+                       __nv_bfloat16* __restrict__ dz, float* __restrict__ partial, long long rows, int C, int chunks) {
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  const int c = (blockIdx.x * 16 + tx) * 8;
+  const long long per = (rows + chunks - 1) / chunks;
+  const long long r0 = blockIdx.y * per, r1 = (r0 + per < rows) ? r0 + per : rows;
+  float s[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = 0.f;
+  if (c < C) {
+    long long r = r0 + ty;
+    for (; r + 16 < r1; r += 32) {
+      BF8 vd[2], vy[2], vo[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        vd[u].u = __ldg(reinterpret_cast<const uint4*>(dy + (r + 16 * u) * C + c));
+        vy[u].u = __ldg(reinterpret_cast<const uint4*>(y + (r + 16 * u) * C + c));
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const bool on = bf2f(vy[u].h[j]) > 0.f;
+          vo[u].h[j] = on ? vd[u].h[j] : f2bf(0.f);
+          s[j] += on ? bf2f(vd[u].h[j]) : 0.f;
+        }
+        *reinterpret_cast<uint4*>(dz + (r + 16 * u) * C + c) = vo[u].u;
+      }
+    }
+    for (; r < r1; r += 16) {
+      BF8 vd, vy, vo;
+      vd.u = __ldg(reinterpret_cast<const uint4*>(dy + r * C + c));
+      vy.u = __ldg(reinterpret_cast<const uint4*>(y + r * C + c));
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const bool on = bf2f(vy.h[j]) > 0.f;
+        vo.h[j] = on ? vd.h[j] : f2bf(0.f);
+        s[j] += on ? bf2f(vd.h[j]) : 0.f;
+      }
+      *reinterpret_cast<uint4*>(dz + r * C + c) = vo.u;
+    }
+  }
+  __shared__ float sm[16][132];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) sm[ty][tx * 8 + j] = s[j];
+  __syncthreads();
+  if (threadIdx.x < 128) {
+    const int cc = blockIdx.x * 128 + threadIdx.x;
+    if (cc < C) {
+      float t = 0.f;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) t += sm[i][threadIdx.x];
+      partial[(long long)blockIdx.y * C + cc] = t;
+    }
+  }
+}
+
+int relu_bwd_colsum(const void* dy, const void* y, void* dz, float* out, float* scratch, long long rows, int C,
+                    cudaStream_t st) {
+  if (rows <= 0 || C <= 0 || (C % 8) != 0) return AS_ESIZE;
+  if (!dy || !y || !dz || !out || !scratch) return AS_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(dz)) & 15) return AS_EALIGN;
+  long long want = (rows + 127) / 128;
+  const int chunks = (int)(want < 1 ? 1 : (want > 1024 ? 1024 : want));   // scratch: as_colsum_scratch_floats(C) = 1024 * C floats
+  dim3 g((C + 127) / 128, chunks);
+  relu_bwd_colsum_kernel<<<g, 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, (__nv_bfloat16*)dz, scratch,
+                                            rows, C, chunks);
+  AS_LAUNCH_CHECK();
+  colsum_reduce_kernel<<<(C + 31) / 32, 256, 0, st>>>(scratch, out, C, chunks);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
 int colsum_f32(const float* x, float* out, float* scratch, long long rows, int C, cudaStream_t st) {
   if (rows <= 0 || C <= 0) return AS_ESIZE;
   if (!x || !out || !scratch) return AS_EINVAL;

@@ -63,11 +63,19 @@ class ConvNHWC(torch.autograd.Function):
         R, H, W, cin, cin_p, cout, taps, kh = ctx.dims
         dy = dy.contiguous()
         st = _lib.stream_ptr()
+        dx = dw = db = None
+        want_db = ctx.has_bias and ctx.needs_input_grad[2]
         if ctx.relu:
             dz = torch.empty_like(dy)
-            _lib.call('as_relu_bwd_bf16', dy.data_ptr(), y.data_ptr(), dz.data_ptr(), dy.numel(), st)
+            if want_db and cout % 8 == 0:       # ReLU mask and bias gradient in one pass
+                db = torch.empty(cout, dtype=torch.float32, device=x.device)
+                scratch = torch.empty(_lib.lib().as_colsum_scratch_floats(cout), dtype=torch.float32, device=x.device)
+                _lib.call('as_relu_bwd_colsum_bf16', dy.data_ptr(), y.data_ptr(), dz.data_ptr(), db.data_ptr(),
+                          scratch.data_ptr(), R * (H + 2) * (W + 2), cout, st)
+                want_db = False
+            else:
+                _lib.call('as_relu_bwd_bf16', dy.data_ptr(), y.data_ptr(), dz.data_ptr(), dy.numel(), st)
             dy = dz
-        dx = dw = db = None
         if ctx.needs_input_grad[0]:
             dx = torch.empty_like(x)
             _conv_call(dy, w_dg, dx, None, R, H, W, cout, cin_p, taps, False)
@@ -81,7 +89,7 @@ class ConvNHWC(torch.autograd.Function):
             _lib.call('as_conv_wgrad_nhwc_bf16', dy.data_ptr(), x.data_ptr(), dw9.data_ptr(), _ptr(ws), R, H, W, cin_p,
                       cout, taps, splits, st)
             dw = dw9[:, :, :cin].permute(1, 2, 0).reshape(cout, cin, kh, kh)
-        if ctx.has_bias and ctx.needs_input_grad[2]:
+        if want_db:
             db = torch.empty(cout, dtype=torch.float32, device=x.device)
             scratch = torch.empty(_lib.lib().as_colsum_scratch_floats(cout), dtype=torch.float32, device=x.device)
             _lib.call('as_colsum_bf16', dy.data_ptr(), db.data_ptr(), scratch.data_ptr(), R * (H + 2) * (W + 2), cout, st)
@@ -362,17 +370,17 @@ class SpatialProject(torch.autograd.Function):
         st = _lib.stream_ptr()
         dy = dy.contiguous()
         dz = torch.empty_like(dy)
-        _lib.call('as_relu_bwd_bf16', dy.data_ptr(), out.data_ptr(), dz.data_ptr(), dy.numel(), st)
         P = R * (H + 2) * (W + 2)
+        db = torch.empty(cout, dtype=torch.float32, device=dy.device)
+        scratch = torch.empty(_lib.lib().as_colsum_scratch_floats(cout), dtype=torch.float32, device=dy.device)
+        _lib.call('as_relu_bwd_colsum_bf16', dy.data_ptr(), out.data_ptr(), dz.data_ptr(), db.data_ptr(),
+                  scratch.data_ptr(), P, cout, st)
         splits = _lib.lib().as_gemm_splits(P, 2 * K.NUM_SMS)
         dw1 = torch.empty((1, cout, 64), dtype=torch.float32, device=dy.device)
         ws = torch.empty((splits, 1, cout, 64), dtype=torch.float32, device=dy.device) if splits > 1 else None
         _lib.call('as_conv_wgrad_nhwc_bf16', dz.data_ptr(), feats.data_ptr(), dw1.data_ptr(), _ptr(ws), R, H, W, 64, cout,
                   1, splits, st)
         dw = dw1[0, :, :cin].reshape(cout, cin, 1, 1)
-        db = torch.empty(cout, dtype=torch.float32, device=dy.device)
-        scratch = torch.empty(_lib.lib().as_colsum_scratch_floats(cout), dtype=torch.float32, device=dy.device)
-        _lib.call('as_colsum_bf16', dz.data_ptr(), db.data_ptr(), scratch.data_ptr(), P, cout, st)
         g = torch.empty((R, N, cout), dtype=torch.float32, device=dy.device)       # dz rows at the entity cells
         _lib.call('as_scatter_connection_bwd_pnhwc', dz.data_ptr(), xs.data_ptr(), ys.data_ptr(), xs.element_size(),
                   _ptr(en), g.data_ptr(), R, N, cout, H, W, cout, 0, st)

@@ -114,7 +114,12 @@ int as_conv_c32_1_bwd(const float* dlogits, const void* in, const float* w, void
 /* out[c] = sum_r x[r][c] for bf16 x [rows, C] (bias gradients); scratch of as_colsum_scratch_floats(C) floats. */
 int64_t as_colsum_scratch_floats(int C);
 int as_colsum_bf16(const void* x, float* out, float* scratch, int64_t rows, int C, void* stream);
-int as_colsum_f32(const float* x, float* out, float* scratch, int64_t rows, int C, void* stream);   /* fp32 rows, same scratch size */
+int as_colsum_f32(const float* x, float* out, float* scratch, int64_t rows, int C, void* stream);
+/* ReLU backward and bias gradient of a convolution in one pass over bf16 rows [rows, C] (C % 8 == 0, 16-byte aligned):
+ * dz = dy * (y > 0), colsum[c] = sum_r dz[r][c] -- the `dy * (y > 0)` and `.sum` passes autograd runs for
+ * conv2d_block's ReLU + bias (nn_module.py:119-174).  scratch: as_colsum_scratch_floats(C) floats. */
+int as_relu_bwd_colsum_bf16(const void* dy, const void* y, void* dz, float* colsum, float* scratch, int64_t rows, int C,
+                            void* stream);   /* fp32 rows, same scratch size */
 /* Same column sums for hosts that may not allocate device memory at all (a process that gave its whole device
  * budget to an arena at start-up, or a step loop that cannot afford the device-wide synchronisation cudaMalloc /
  * cudaFree bring).  This entry point has no counterpart in the reference.  It allocates nothing: the partial sums
