@@ -596,9 +596,10 @@ int conv_c32_1_bwd(const float* dy, const void* in, const float* w, void* din, f
 // 16-byte load per row), 16 threads span 128 columns, 16 row lanes per block with four loads in flight each.
 __global__ void __launch_bounds__(256)
 colsum_partial_v8_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ partial, long long rows, int C,
-                         int chunks) {
-  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-  const int c = (blockIdx.x * 16 + tx) * 8;
+                         int chunks, int txn) {
+  // txn (4, 8 or 16) threads span the columns of a block (8 columns each), 256 / txn row lanes
+  const int tx = threadIdx.x & (txn - 1), ty = threadIdx.x / txn, tyn = 256 / txn;
+  const int c = (blockIdx.x * txn + tx) * 8;
   const long long per = (rows + chunks - 1) / chunks;
   const long long r0 = blockIdx.y * per, r1 = (r0 + per < rows) ? r0 + per : rows;
   float s[8];
@@ -607,10 +608,10 @@ colsum_partial_v8_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict_
   if (c < C) {
     const __nv_bfloat16* col = x + c;
     long long r = r0 + ty;
-    for (; r + 48 < r1; r += 64) {
+    for (; r + 3 * tyn < r1; r += 4 * tyn) {
       uint4 v[4];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) v[u] = __ldg(reinterpret_cast<const uint4*>(col + (r + 16 * u) * C));
+      for (int u = 0; u < 4; ++u) v[u] = __ldg(reinterpret_cast<const uint4*>(col + (r + (long long)tyn * u) * C));
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&v[u]);
@@ -621,7 +622,7 @@ colsum_partial_v8_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict_
         }
       }
     }
-    for (; r < r1; r += 16) {
+    for (; r < r1; r += tyn) {
       const uint4 v = __ldg(reinterpret_cast<const uint4*>(col + r * C));
       const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&v);
 #pragma unroll
@@ -631,16 +632,16 @@ colsum_partial_v8_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict_
       }
     }
   }
-  __shared__ float sm[16][132];
+  __shared__ float sm[64 * 36];                    // [tyn][txn * 8 + 4]
+  const int pitch = txn * 8 + 4;
 #pragma unroll
-  for (int j = 0; j < 8; ++j) sm[ty][tx * 8 + j] = s[j];
+  for (int j = 0; j < 8; ++j) sm[ty * pitch + tx * 8 + j] = s[j];
   __syncthreads();
-  if (threadIdx.x < 128) {
-    const int cc = blockIdx.x * 128 + threadIdx.x;
+  if (threadIdx.x < txn * 8) {
+    const int cc = blockIdx.x * txn * 8 + threadIdx.x;
     if (cc < C) {
       float t = 0.f;
-#pragma unroll
-      for (int i = 0; i < 16; ++i) t += sm[i][threadIdx.x];
+      for (int i = 0; i < tyn; ++i) t += sm[i * pitch + threadIdx.x];
       partial[(long long)blockIdx.y * C + cc] = t;
     }
   }
@@ -718,8 +719,9 @@ int colsum_bf16(const void* x, float* out, float* scratch, long long rows, int C
   long long want = (rows + 255) / 256;
   const int chunks = (int)(want < 1 ? 1 : (want > kColsumMaxUsed ? kColsumMaxUsed : want));
   if (C % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0) {
-    dim3 g((C + 127) / 128, chunks);
-    colsum_partial_v8_kernel<<<g, 256, 0, st>>>((const __nv_bfloat16*)x, scratch, rows, C, chunks);
+    const int txn = C >= 128 ? 16 : (C >= 64 ? 8 : 4);
+    dim3 g((C + txn * 8 - 1) / (txn * 8), chunks);
+    colsum_partial_v8_kernel<<<g, 256, 0, st>>>((const __nv_bfloat16*)x, scratch, rows, C, chunks, txn);
   } else {
     dim3 g((C + 63) / 64, chunks);
     colsum_partial_kernel<<<g, 256, 0, st>>>((const __nv_bfloat16*)x, scratch, rows, C, chunks);
@@ -1000,9 +1002,10 @@ int maxpool2_bwd(const void* in, const void* dout, void* din, long long R, int H
 // colsum_partial_v8_kernel: C % 8 == 0, 16-byte loads / stores.
 __global__ void __launch_bounds__(256)
 relu_bwd_colsum_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
-                       __nv_bfloat16* __restrict__ dz, float* __restrict__ partial, long long rows, int C, int chunks) {
-  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-  const int c = (blockIdx.x * 16 + tx) * 8;
+                       __nv_bfloat16* __restrict__ dz, float* __restrict__ partial, long long rows, int C, int chunks,
+                       int txn) {
+  const int tx = threadIdx.x & (txn - 1), ty = threadIdx.x / txn, tyn = 256 / txn;
+  const int c = (blockIdx.x * txn + tx) * 8;
   const long long per = (rows + chunks - 1) / chunks;
   const long long r0 = blockIdx.y * per, r1 = (r0 + per < rows) ? r0 + per : rows;
   float s[8];
@@ -1010,25 +1013,26 @@ relu_bwd_colsum_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16
   for (int j = 0; j < 8; ++j) s[j] = 0.f;
   if (c < C) {
     long long r = r0 + ty;
-    for (; r + 16 < r1; r += 32) {
-      BF8 vd[2], vy[2], vo[2];
+    for (; r + 3 * tyn < r1; r += 4 * tyn) {
+      BF8 vd[4], vy[4];
 #pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        vd[u].u = __ldg(reinterpret_cast<const uint4*>(dy + (r + 16 * u) * C + c));
-        vy[u].u = __ldg(reinterpret_cast<const uint4*>(y + (r + 16 * u) * C + c));
+      for (int u = 0; u < 4; ++u) {
+        vd[u].u = __ldg(reinterpret_cast<const uint4*>(dy + (r + (long long)tyn * u) * C + c));
+        vy[u].u = __ldg(reinterpret_cast<const uint4*>(y + (r + (long long)tyn * u) * C + c));
       }
 #pragma unroll
-      for (int u = 0; u < 2; ++u) {
+      for (int u = 0; u < 4; ++u) {
+        BF8 vo;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const bool on = bf2f(vy[u].h[j]) > 0.f;
-          vo[u].h[j] = on ? vd[u].h[j] : f2bf(0.f);
+          vo.h[j] = on ? vd[u].h[j] : f2bf(0.f);
           s[j] += on ? bf2f(vd[u].h[j]) : 0.f;
         }
-        *reinterpret_cast<uint4*>(dz + (r + 16 * u) * C + c) = vo[u].u;
+        *reinterpret_cast<uint4*>(dz + (r + (long long)tyn * u) * C + c) = vo.u;
       }
     }
-    for (; r < r1; r += 16) {
+    for (; r < r1; r += tyn) {
       BF8 vd, vy, vo;
       vd.u = __ldg(reinterpret_cast<const uint4*>(dy + r * C + c));
       vy.u = __ldg(reinterpret_cast<const uint4*>(y + r * C + c));
@@ -1041,16 +1045,16 @@ relu_bwd_colsum_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16
       *reinterpret_cast<uint4*>(dz + r * C + c) = vo.u;
     }
   }
-  __shared__ float sm[16][132];
+  __shared__ float sm[64 * 36];
+  const int pitch = txn * 8 + 4;
 #pragma unroll
-  for (int j = 0; j < 8; ++j) sm[ty][tx * 8 + j] = s[j];
+  for (int j = 0; j < 8; ++j) sm[ty * pitch + tx * 8 + j] = s[j];
   __syncthreads();
-  if (threadIdx.x < 128) {
-    const int cc = blockIdx.x * 128 + threadIdx.x;
+  if (threadIdx.x < txn * 8) {
+    const int cc = blockIdx.x * txn * 8 + threadIdx.x;
     if (cc < C) {
       float t = 0.f;
-#pragma unroll
-      for (int i = 0; i < 16; ++i) t += sm[i][threadIdx.x];
+      for (int i = 0; i < tyn; ++i) t += sm[i * pitch + threadIdx.x];
       partial[(long long)blockIdx.y * C + cc] = t;
     }
   }
@@ -1063,9 +1067,10 @@ int relu_bwd_colsum(const void* dy, const void* y, void* dz, float* out, float* 
   if ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(dz)) & 15) return AS_EALIGN;
   long long want = (rows + 127) / 128;
   const int chunks = (int)(want < 1 ? 1 : (want > 1024 ? 1024 : want));   // scratch: as_colsum_scratch_floats(C) = 1024 * C floats
-  dim3 g((C + 127) / 128, chunks);
+  const int txn = C >= 128 ? 16 : (C >= 64 ? 8 : 4);
+  dim3 g((C + txn * 8 - 1) / (txn * 8), chunks);
   relu_bwd_colsum_kernel<<<g, 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, (__nv_bfloat16*)dz, scratch,
-                                            rows, C, chunks);
+                                            rows, C, chunks, txn);
   AS_LAUNCH_CHECK();
   colsum_reduce_kernel<<<(C + 31) / 32, 256, 0, st>>>(scratch, out, C, chunks);
   AS_LAUNCH_CHECK();
