@@ -48,6 +48,7 @@ long long colsum_scratch_floats(int);
 int colsum_bf16(const void*, float*, float*, long long, int, cudaStream_t);
 int colsum_bf16_static(const void*, float*, long long, int, cudaStream_t);
 int relu_bwd_colsum(const void*, const void*, void*, float*, float*, long long, int, cudaStream_t);
+int linear_bwd_prep(const float*, const float*, const void*, void*, float*, float*, long long, int, cudaStream_t);
 int colsum_f32(const float*, float*, float*, long long, int, cudaStream_t);
 int lnlstm_fwd(const float*, const float*, const float*, const void*, const float*, const float*, const float*,
                const float*, float*, float*, float*, float*, float*, int, int, int, cudaStream_t);
@@ -248,6 +249,10 @@ int as_colsum_f32(const float* x, float* out, float* scratch, int64_t rows, int 
 int as_relu_bwd_colsum_bf16(const void* dy, const void* y, void* dz, float* colsum, float* scratch, int64_t rows, int C,
                             void* stream) {
   return as::relu_bwd_colsum(dy, y, dz, colsum, scratch, rows, C, ST(stream));
+}
+int as_linear_bwd_prep(const float* dy, const float* y32, const void* y16, void* dz16, float* colsum, float* scratch,
+                       int64_t rows, int C, void* stream) {
+  return as::linear_bwd_prep(dy, y32, y16, dz16, colsum, scratch, rows, C, ST(stream));
 }
 int as_colsum_bf16_static(const void* x, float* out, int64_t rows, int C, void* stream) {
   return as::colsum_bf16_static(x, out, rows, C, ST(stream));

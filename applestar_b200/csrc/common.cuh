@@ -28,6 +28,27 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// Division by a launch-time constant as multiply-high + shift (Granlund-Montgomery), for index decomposition in the
+// element-wise kernels: a 64-bit `/` or `%` costs ~100 instructions per thread and made several HBM-bound kernels
+// ALU-bound.  Valid for dividends below 2^31.
+struct FastDiv { uint32_t d, m, s; };
+inline FastDiv make_fastdiv(uint32_t d) {
+  uint32_t L = 0;
+  while ((1ull << L) < d) ++L;
+  const uint64_t m = ((1ull << 32) * ((1ull << L) - d)) / d + 1;
+  return FastDiv{d, (uint32_t)m, L};
+}
+__device__ __forceinline__ uint32_t fd_div(uint32_t n, const FastDiv& f) { return (__umulhi(n, f.m) + n) >> f.s; }
+// i -> (i % a, (i / a) % b, (i / (a b)) % c, i / (a b c))
+struct Dec3 { FastDiv a, b, c; };
+inline Dec3 make_dec3(uint32_t a, uint32_t b, uint32_t c) { return Dec3{make_fastdiv(a), make_fastdiv(b), make_fastdiv(c)}; }
+__device__ __forceinline__ void dec3(uint32_t i, const Dec3& k, int& ia, int& ib, int& ic, int& rest) {
+  uint32_t q = fd_div(i, k.a); ia = (int)(i - q * k.a.d);
+  uint32_t q2 = fd_div(q, k.b); ib = (int)(q - q2 * k.b.d);
+  uint32_t q3 = fd_div(q2, k.c); ic = (int)(q2 - q3 * k.c.d);
+  rest = (int)q3;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

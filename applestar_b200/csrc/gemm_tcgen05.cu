@@ -823,6 +823,33 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
 // ---- split-K reduction: out[i] = (accumulate ? out[i] : 0) + sum_s ws[s][i], fixed order (deterministic)
 __global__ void splitk_reduce_kernel(const float* __restrict__ ws, float* __restrict__ out, long long n, int splits,
                                      int accumulate) {
+  // 16-byte loads, four splits in flight per thread; summation order over splits is fixed
+  const long long n4 = n >> 2;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    float4 s = accumulate ? reinterpret_cast<const float4*>(out)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+    int k = 0;
+    for (; k + 4 <= splits; k += 4) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = __ldg(reinterpret_cast<const float4*>(ws + (long long)(k + u) * n) + i);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
+    }
+    for (; k < splits; ++k) {
+      const float4 v = __ldg(reinterpret_cast<const float4*>(ws + (long long)k * n) + i);
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    reinterpret_cast<float4*>(out)[i] = s;
+  }
+  for (long long i = n4 * 4 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    float s = accumulate ? out[i] : 0.f;
+    for (int k = 0; k < splits; ++k) s += ws[(long long)k * n + i];
+    out[i] = s;
+  }
+}
+__global__ void splitk_reduce_scalar_kernel(const float* __restrict__ ws, float* __restrict__ out, long long n, int splits,
+                                            int accumulate) {
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (; i < n; i += stride) {
@@ -834,9 +861,11 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ ws, float* __rest
 
 int splitk_reduce(const float* ws, float* out, long long n, int splits, int accumulate, cudaStream_t st) {
   if (n <= 0) return AS_OK;
-  long long blocks = (n + 255) / 256;
-  int grid = (int)(blocks < 148 * 8 ? blocks : 148 * 8);
-  splitk_reduce_kernel<<<grid, 256, 0, st>>>(ws, out, n, splits, accumulate);
+  const bool vec = (n % 4 == 0) && ((reinterpret_cast<uintptr_t>(ws) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+  long long blocks = ((vec ? n / 4 : n) + 127) / 128;
+  int grid = (int)(blocks < 148 * 8 ? (blocks > 0 ? blocks : 1) : 148 * 8);
+  if (vec) splitk_reduce_kernel<<<grid, 128, 0, st>>>(ws, out, n, splits, accumulate);
+  else splitk_reduce_scalar_kernel<<<grid, 128, 0, st>>>(ws, out, n, splits, accumulate);
   AS_LAUNCH_CHECK();
   return AS_OK;
 }

@@ -87,22 +87,27 @@ scatter_fwd_kernel(const float* __restrict__ emb, const IdxT* __restrict__ xs, c
     }
   }
   __syncthreads();
-  // 4. stream the planes
+  // 4. stream the planes: one cell-map read per group of 4 cells serves all DG channels (no index division in the
+  //    loop, one shared-memory read per 16 * DG bytes written); each channel's store is 512 contiguous bytes per warp
   const int q4 = HW / 4;                                                     // HW % 4 == 0 checked on host
-  for (int idx = tid; idx < DG * q4; idx += kScatterThreads) {
-    const int c = idx / q4;
-    const int p4 = idx - c * q4;
+  float* obase = out + ((long long)r * D + d0) * HW;
+  for (int p4 = tid; p4 < q4; p4 += kScatterThreads) {
     const uint2 m = *reinterpret_cast<const uint2*>(cellmap + p4 * 4);
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if ((m.x | m.y) != 0u) {
+    if ((m.x | m.y) == 0u) {
+#pragma unroll
+      for (int c = 0; c < DG; ++c) __stcs(reinterpret_cast<float4*>(obase + (long long)c * HW) + p4, make_float4(0.f, 0.f, 0.f, 0.f));
+    } else {
       const uint32_t m0 = m.x & 0xFFFFu, m1 = m.x >> 16, m2 = m.y & 0xFFFFu, m3 = m.y >> 16;
-      if (m0) v.x = segsum[(m0 - 1) * DG + c];
-      if (m1) v.y = segsum[(m1 - 1) * DG + c];
-      if (m2) v.z = segsum[(m2 - 1) * DG + c];
-      if (m3) v.w = segsum[(m3 - 1) * DG + c];
+#pragma unroll
+      for (int c = 0; c < DG; ++c) {
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (m0) v.x = segsum[(m0 - 1) * DG + c];
+        if (m1) v.y = segsum[(m1 - 1) * DG + c];
+        if (m2) v.z = segsum[(m2 - 1) * DG + c];
+        if (m3) v.w = segsum[(m3 - 1) * DG + c];
+        __stcs(reinterpret_cast<float4*>(obase + (long long)c * HW) + p4, v);
+      }
     }
-    float4* dst = reinterpret_cast<float4*>(out + ((long long)r * D + d0 + c) * HW) + p4;
-    __stcs(dst, v);
   }
 }
 

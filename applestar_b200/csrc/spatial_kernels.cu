@@ -230,16 +230,14 @@ __device__ __forceinline__ void up2_src(int o, int n_in, int* i0, int* i1, float
 }
 
 __global__ void up2_fwd_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, long long R, int H,
-                               int W, int C) {
+                               int W, int C, const Dec3 dec) {
   const int H2 = 2 * H, W2 = 2 * W, C8 = C / 8;
-  const long long total = R * (H2 + 2) * (long long)(W2 + 2) * C8;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int c8 = (int)(i % C8);
-    long long p = i / C8;
-    const int xx = (int)(p % (W2 + 2)); p /= (W2 + 2);
-    const int yy = (int)(p % (H2 + 2));
-    const long long r = p / (H2 + 2);
+  const uint32_t total = (uint32_t)(R * (H2 + 2) * (long long)(W2 + 2) * C8);
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    int c8, xx, yy, ri;
+    dec3(i, dec, c8, xx, yy, ri);
+    const long long r = ri;
     BF8 o;
     if (xx == 0 || xx == W2 + 1 || yy == 0 || yy == H2 + 1) {
       o.u = make_uint4(0, 0, 0, 0);
@@ -266,16 +264,14 @@ __global__ void up2_fwd_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat
 
 // gather form of the transpose: each input pixel collects from the <=4x4 output pixels that read it
 __global__ void up2_bwd_kernel(const __nv_bfloat16* __restrict__ dout, __nv_bfloat16* __restrict__ din, long long R,
-                               int H, int W, int C) {
+                               int H, int W, int C, const Dec3 dec) {
   const int H2 = 2 * H, W2 = 2 * W, C8 = C / 8;
-  const long long total = R * (H + 2) * (long long)(W + 2) * C8;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int c8 = (int)(i % C8);
-    long long p = i / C8;
-    const int xx = (int)(p % (W + 2)); p /= (W + 2);
-    const int yy = (int)(p % (H + 2));
-    const long long r = p / (H + 2);
+  const uint32_t total = (uint32_t)(R * (H + 2) * (long long)(W + 2) * C8);
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    int c8, xx, yy, ri;
+    dec3(i, dec, c8, xx, yy, ri);
+    const long long r = ri;
     BF8 o;
     if (xx == 0 || xx == W + 1 || yy == 0 || yy == H + 1) {
       o.u = make_uint4(0, 0, 0, 0);
@@ -307,7 +303,7 @@ __global__ void up2_bwd_kernel(const __nv_bfloat16* __restrict__ dout, __nv_bflo
 #pragma unroll
       for (int j = 0; j < 8; ++j) o.h[j] = f2bf(acc[j]);
     }
-    *reinterpret_cast<uint4*>(din + i * 8) = o.u;
+    *reinterpret_cast<uint4*>(din + (long long)i * 8) = o.u;
   }
 }
 
@@ -316,7 +312,9 @@ int up2_fwd(const void* in, void* out, long long R, int H, int W, int C, cudaStr
   if (C % 8 || H <= 0 || W <= 0) return AS_ESIZE;
   if (!in || !out) return AS_EINVAL;
   const long long total = R * (2 * H + 2) * (long long)(2 * W + 2) * (C / 8);
-  up2_fwd_kernel<<<ew_grid(total, 1), 256, 0, st>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, R, H, W, C);
+  if (total >= (1LL << 31)) return AS_ESIZE;
+  up2_fwd_kernel<<<ew_grid(total, 1), 256, 0, st>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, R, H, W, C,
+                                                    make_dec3(C / 8, 2 * W + 2, 2 * H + 2));
   AS_LAUNCH_CHECK();
   return AS_OK;
 }
@@ -325,7 +323,9 @@ int up2_bwd(const void* dout, void* din, long long R, int H, int W, int C, cudaS
   if (C % 8 || H <= 0 || W <= 0) return AS_ESIZE;
   if (!dout || !din) return AS_EINVAL;
   const long long total = R * (H + 2) * (long long)(W + 2) * (C / 8);
-  up2_bwd_kernel<<<ew_grid(total, 1), 256, 0, st>>>((const __nv_bfloat16*)dout, (__nv_bfloat16*)din, R, H, W, C);
+  if (total >= (1LL << 31)) return AS_ESIZE;
+  up2_bwd_kernel<<<ew_grid(total, 1), 256, 0, st>>>((const __nv_bfloat16*)dout, (__nv_bfloat16*)din, R, H, W, C,
+                                                    make_dec3(C / 8, W + 2, H + 2));
   AS_LAUNCH_CHECK();
   return AS_OK;
 }
@@ -409,15 +409,15 @@ __device__ __forceinline__ void unpack8(const uint4& q, float* f) {
   }
 }
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 3)
 conv_c32_1_fwd_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict__ w, const float* __restrict__ bias,
-                      float* __restrict__ out, long long R, int H, int W, float inv_temp) {
+                      float* __restrict__ out, long long R, int H, int W, float inv_temp, const Dec3 dec) {
+  // weights stay in shared memory (broadcast 16-byte reads): holding them in registers costs 72 registers per thread
+  // and leaves one CTA per SM, far too few loads in flight for an HBM-bound kernel
+  __shared__ __align__(16) float sw[288];
+  for (int i = threadIdx.x; i < 288; i += blockDim.x) sw[i] = w[i];
+  __syncthreads();
   const int cg = threadIdx.x & 3;
-  float wr[9][8];                                              // this thread's 8 channels of every tap
-#pragma unroll
-  for (int t = 0; t < 9; ++t)
-#pragma unroll
-    for (int c = 0; c < 8; ++c) wr[t][c] = __ldg(w + t * 32 + cg * 8 + c);
   const float b = bias ? bias[0] : 0.f;
   const long long total = R * (long long)H * W;
   const long long stride = ((long long)gridDim.x * blockDim.x) >> 2;
@@ -426,24 +426,25 @@ conv_c32_1_fwd_kernel(const __nv_bfloat16* __restrict__ in, const float* __restr
   for (long long p = first; p < total_pad; p += stride) {
     const bool ok = p < total;
     const long long pc = ok ? p : 0;
-    const int x = (int)(pc % W);
-    const long long q = pc / W;
-    const int y = (int)(q % H);
-    const long long r = q / H;
+    int x, y, ri, unused;
+    dec3((uint32_t)pc, dec, x, y, ri, unused);
+    const long long r = ri;
     const __nv_bfloat16* base = in + ((r * (H + 2) + y) * (long long)(W + 2) + x) * 32 + cg * 8;
-    uint4 v[9];
-#pragma unroll
-    for (int ky = 0; ky < 3; ++ky)
-#pragma unroll
-      for (int kx = 0; kx < 3; ++kx)
-        v[ky * 3 + kx] = __ldg(reinterpret_cast<const uint4*>(base + ((long long)ky * (W + 2) + kx) * 32));
     float acc = 0.f;
 #pragma unroll
-    for (int t = 0; t < 9; ++t) {
-      float f[8];
-      unpack8(v[t], f);
+    for (int ky = 0; ky < 3; ++ky) {
+      uint4 v[3];
 #pragma unroll
-      for (int c = 0; c < 8; ++c) acc += f[c] * wr[t][c];
+      for (int kx = 0; kx < 3; ++kx)
+        v[kx] = __ldg(reinterpret_cast<const uint4*>(base + ((long long)ky * (W + 2) + kx) * 32));
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        float f[8];
+        unpack8(v[kx], f);
+        const float4 w0 = *reinterpret_cast<const float4*>(sw + (ky * 3 + kx) * 32 + cg * 8);
+        const float4 w1 = *reinterpret_cast<const float4*>(sw + (ky * 3 + kx) * 32 + cg * 8 + 4);
+        acc += f[0] * w0.x + f[1] * w0.y + f[2] * w0.z + f[3] * w0.w + f[4] * w1.x + f[5] * w1.y + f[6] * w1.z + f[7] * w1.w;
+      }
     }
     acc += __shfl_xor_sync(0xffffffffu, acc, 1);
     acc += __shfl_xor_sync(0xffffffffu, acc, 2);
@@ -455,17 +456,16 @@ conv_c32_1_fwd_kernel(const __nv_bfloat16* __restrict__ in, const float* __restr
 // Thread per input pixel, 32 channel accumulators in registers, 64 contiguous bytes written per thread.
 __global__ void __launch_bounds__(256)
 conv_c32_1_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w, __nv_bfloat16* __restrict__ din,
-                        long long R, int H, int W, float inv_temp) {
+                        long long R, int H, int W, float inv_temp, const Dec3 dec) {
   __shared__ __align__(16) float sw[288];
   for (int i = threadIdx.x; i < 288; i += blockDim.x) sw[i] = w[i] * inv_temp;
   __syncthreads();
   const long long total = R * (long long)(H + 2) * (W + 2);
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += stride) {
-    const int xx = (int)(p % (W + 2));
-    const long long q = p / (W + 2);
-    const int yy = (int)(q % (H + 2));
-    const long long r = q / (H + 2);
+    int xx, yy, ri, unused;
+    dec3((uint32_t)p, dec, xx, yy, ri, unused);
+    const long long r = ri;
     float acc[32];
 #pragma unroll
     for (int c = 0; c < 32; ++c) acc[c] = 0.f;
@@ -503,42 +503,39 @@ conv_c32_1_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ 
 // dw[tap][c] = sum_p dy[p] in[p+tap][c];  db = sum dy  -> per-block partials [blocks][9*32+1].  Same thread mapping as
 // the forward (pixel slot x 8-channel group): 72 fp32 accumulators per thread, coalesced 16-byte tap loads, then a
 // shuffle reduction over the warp's eight pixel slots and a shared-memory reduction over the block's warps.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 3)
 conv_c32_1_wgrad_kernel(const float* __restrict__ dy, const __nv_bfloat16* __restrict__ in,
-                        float* __restrict__ partial, long long R, int H, int W, float inv_temp) {
-  const int cg = threadIdx.x & 3, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  float acc[9][8], accb = 0.f;
+                        float* __restrict__ partial, long long R, int H, int W, float inv_temp, const Dec3 dec) {
+  // blockIdx.y = tap row ky: 24 accumulators per thread instead of 72, so three CTAs fit per SM
+  const int cg = threadIdx.x & 3, lane = threadIdx.x & 31, wid = threadIdx.x >> 5, ky = blockIdx.y;
+  float acc[3][8], accb = 0.f;
 #pragma unroll
-  for (int t = 0; t < 9; ++t)
+  for (int t = 0; t < 3; ++t)
 #pragma unroll
     for (int c = 0; c < 8; ++c) acc[t][c] = 0.f;
   const long long total = R * (long long)H * W;
   const long long stride = ((long long)gridDim.x * blockDim.x) >> 2;
   for (long long p = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 2; p < total; p += stride) {
-    const int x = (int)(p % W);
-    const long long q = p / W;
-    const int y = (int)(q % H);
-    const long long r = q / H;
+    int x, y, ri, unused;
+    dec3((uint32_t)p, dec, x, y, ri, unused);
+    const long long r = ri;
     const float g = __ldg(dy + p) * inv_temp;
-    const __nv_bfloat16* base = in + ((r * (H + 2) + y) * (long long)(W + 2) + x) * 32 + cg * 8;
-    uint4 v[9];
+    const __nv_bfloat16* base = in + ((r * (H + 2) + y + ky) * (long long)(W + 2) + x) * 32 + cg * 8;
+    uint4 v[3];
 #pragma unroll
-    for (int ky = 0; ky < 3; ++ky)
-#pragma unroll
-      for (int kx = 0; kx < 3; ++kx)
-        v[ky * 3 + kx] = __ldg(reinterpret_cast<const uint4*>(base + ((long long)ky * (W + 2) + kx) * 32));
+    for (int kx = 0; kx < 3; ++kx) v[kx] = __ldg(reinterpret_cast<const uint4*>(base + kx * 32));
     accb += g;
 #pragma unroll
-    for (int t = 0; t < 9; ++t) {
+    for (int t = 0; t < 3; ++t) {
       float f[8];
       unpack8(v[t], f);
 #pragma unroll
       for (int c = 0; c < 8; ++c) acc[t][c] += g * f[c];
     }
   }
-  __shared__ float red[8][9 * 32 + 1];
+  __shared__ float red[8][3 * 32 + 1];
 #pragma unroll
-  for (int t = 0; t < 9; ++t)
+  for (int t = 0; t < 3; ++t)
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
       float a = acc[t][c];
@@ -550,12 +547,13 @@ conv_c32_1_wgrad_kernel(const float* __restrict__ dy, const __nv_bfloat16* __res
   accb += __shfl_xor_sync(0xffffffffu, accb, 4);
   accb += __shfl_xor_sync(0xffffffffu, accb, 8);
   accb += __shfl_xor_sync(0xffffffffu, accb, 16);
-  if (lane == 0) red[wid][288] = accb;
+  if (lane == 0) red[wid][96] = accb;
   __syncthreads();
-  for (int i = threadIdx.x; i < 289; i += blockDim.x) {
+  for (int i = threadIdx.x; i < 97; i += blockDim.x) {
+    if (i == 96 && ky != 0) continue;                           // the bias gradient is counted once
     float s = 0.f;
     for (int k = 0; k < 8; ++k) s += red[k][i];
-    partial[(long long)blockIdx.x * 289 + i] = s;
+    partial[(long long)blockIdx.x * 289 + (i == 96 ? 288 : ky * 96 + i)] = s;
   }
 }
 __global__ void conv_c32_1_wreduce_kernel(const float* __restrict__ partial, int blocks, float* __restrict__ dw,
@@ -574,7 +572,9 @@ int conv_c32_1_fwd(const void* in, const float* w, const float* bias, float* out
                    cudaStream_t st) {
   if (R <= 0) return AS_OK;
   if (!in || !w || !out) return AS_EINVAL;
-  conv_c32_1_fwd_kernel<<<ew_grid(R * (long long)H * W * 4, 1), 256, 0, st>>>((const __nv_bfloat16*)in, w, bias, out, R, H, W, inv_temp);
+  if (R * (long long)(H + 2) * (W + 2) >= (1LL << 31)) return AS_ESIZE;
+  conv_c32_1_fwd_kernel<<<ew_grid(R * (long long)H * W * 4, 1), 256, 0, st>>>((const __nv_bfloat16*)in, w, bias, out, R, H, W, inv_temp,
+                                                                              make_dec3(W, H, 1u << 30));
   AS_LAUNCH_CHECK();
   return AS_OK;
 }
@@ -582,9 +582,11 @@ int conv_c32_1_bwd(const float* dy, const void* in, const float* w, void* din, f
                    long long R, int H, int W, float inv_temp, cudaStream_t st) {
   if (R <= 0) return AS_OK;
   if (!dy || !in || !w || !din || !dw || !scratch) return AS_EINVAL;
-  conv_c32_1_dgrad_kernel<<<ew_grid(R * (long long)(H + 2) * (W + 2), 1), 256, 0, st>>>(dy, w, (__nv_bfloat16*)din, R, H, W, inv_temp);
+  if (R * (long long)(H + 2) * (W + 2) >= (1LL << 31)) return AS_ESIZE;
+  conv_c32_1_dgrad_kernel<<<ew_grid(R * (long long)(H + 2) * (W + 2), 1), 256, 0, st>>>(dy, w, (__nv_bfloat16*)din, R, H, W, inv_temp,
+                                                                                        make_dec3(W + 2, H + 2, 1u << 30));
   AS_LAUNCH_CHECK();
-  conv_c32_1_wgrad_kernel<<<kC321Blocks, 256, 0, st>>>(dy, (const __nv_bfloat16*)in, scratch, R, H, W, inv_temp);
+  conv_c32_1_wgrad_kernel<<<dim3(kC321Blocks, 3), 256, 0, st>>>(dy, (const __nv_bfloat16*)in, scratch, R, H, W, inv_temp, make_dec3(W, H, 1u << 30));
   AS_LAUNCH_CHECK();
   conv_c32_1_wreduce_kernel<<<3, 128, 0, st>>>(scratch, kC321Blocks, dw, db);
   AS_LAUNCH_CHECK();
@@ -890,16 +892,14 @@ int scatter_bwd_pnhwc(const void* dfeat, const void* xs, const void* ys, int idx
 // forward: out[r,py,px,c] = max over the 2x2 window; backward: gradient to the FIRST maximum in row-major window
 // order (torch.nn.functional.max_pool2d semantics), zero elsewhere and on the border.
 __global__ void maxpool2_fwd_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, long long R,
-                                    int H, int W, int C) {
+                                    int H, int W, int C, const Dec3 dec) {
   const int Ho = H / 2, Wo = W / 2, C8 = C / 8;
-  const long long total = R * (long long)(Ho + 2) * (Wo + 2) * C8;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int c8 = (int)(i % C8);
-    long long p = i / C8;
-    const int xx = (int)(p % (Wo + 2)); p /= (Wo + 2);
-    const int yy = (int)(p % (Ho + 2));
-    const long long r = p / (Ho + 2);
+  const uint32_t total = (uint32_t)(R * (long long)(Ho + 2) * (Wo + 2) * C8);
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    int c8, xx, yy, ri;
+    dec3(i, dec, c8, xx, yy, ri);
+    const long long r = ri;
     BF8 o;
     if (xx == 0 || xx == Wo + 1 || yy == 0 || yy == Ho + 1) {
       o.u = make_uint4(0, 0, 0, 0);
@@ -914,22 +914,20 @@ __global__ void maxpool2_fwd_kernel(const __nv_bfloat16* __restrict__ in, __nv_b
       for (int j = 0; j < 8; ++j)
         o.h[j] = f2bf(fmaxf(fmaxf(bf2f(a.h[j]), bf2f(b.h[j])), fmaxf(bf2f(c.h[j]), bf2f(d.h[j]))));
     }
-    *reinterpret_cast<uint4*>(out + i * 8) = o.u;
+    *reinterpret_cast<uint4*>(out + (long long)i * 8) = o.u;
   }
 }
 
 __global__ void maxpool2_bwd_kernel(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict__ dout,
-                                    __nv_bfloat16* __restrict__ din, long long R, int H, int W, int C) {
+                                    __nv_bfloat16* __restrict__ din, long long R, int H, int W, int C, const Dec3 dec) {
   // thread per (pooled pixel incl. border ring handled separately, 8 channels): writes the four input pixels
   const int Ho = H / 2, Wo = W / 2, C8 = C / 8;
-  const long long total = R * (long long)Ho * Wo * C8;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int c8 = (int)(i % C8);
-    long long p = i / C8;
-    const int px = (int)(p % Wo); p /= Wo;
-    const int py = (int)(p % Ho);
-    const long long r = p / Ho;
+  const uint32_t total = (uint32_t)(R * (long long)Ho * Wo * C8);
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    int c8, px, py, ri;
+    dec3(i, dec, c8, px, py, ri);
+    const long long r = ri;
     const long long ibase = ((r * (H + 2) + 2 * py + 1) * (long long)(W + 2) + 2 * px + 1) * C + c8 * 8;
     BF8 a, b, c, d, g, oa, ob, oc, od;
     a.u = *reinterpret_cast<const uint4*>(in + ibase);
@@ -979,7 +977,9 @@ int maxpool2_fwd(const void* in, void* out, long long R, int H, int W, int C, cu
   if ((C % 8) || (H % 2) || (W % 2) || H <= 0 || W <= 0) return AS_ESIZE;
   if (!in || !out) return AS_EINVAL;
   const long long total = R * (long long)(H / 2 + 2) * (W / 2 + 2) * (C / 8);
-  maxpool2_fwd_kernel<<<ew_grid(total, 1), 256, 0, st>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, R, H, W, C);
+  if (total >= (1LL << 31)) return AS_ESIZE;
+  maxpool2_fwd_kernel<<<ew_grid(total, 1), 256, 0, st>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, R, H, W, C,
+                                                         make_dec3(C / 8, W / 2 + 2, H / 2 + 2));
   AS_LAUNCH_CHECK();
   return AS_OK;
 }
@@ -989,7 +989,9 @@ int maxpool2_bwd(const void* in, const void* dout, void* din, long long R, int H
   if ((C % 8) || (H % 2) || (W % 2) || H <= 0 || W <= 0) return AS_ESIZE;
   if (!in || !dout || !din) return AS_EINVAL;
   const long long total = R * (long long)(H / 2) * (W / 2) * (C / 8);
-  maxpool2_bwd_kernel<<<ew_grid(total, 1), 256, 0, st>>>((const __nv_bfloat16*)in, (const __nv_bfloat16*)dout, (__nv_bfloat16*)din, R, H, W, C);
+  if (total >= (1LL << 31)) return AS_ESIZE;
+  maxpool2_bwd_kernel<<<ew_grid(total, 1), 256, 0, st>>>((const __nv_bfloat16*)in, (const __nv_bfloat16*)dout, (__nv_bfloat16*)din, R, H, W, C,
+                                                         make_dec3(C / 8, W / 2, H / 2));
   AS_LAUNCH_CHECK();
   const long long ring = R * (long long)(2 * (W + 2) + 2 * H) * (C / 8);
   zero_border_kernel<<<ew_grid(ring, 1), 256, 0, st>>>((__nv_bfloat16*)din, R, H, W, C);
@@ -1074,6 +1076,85 @@ int relu_bwd_colsum(const void* dy, const void* y, void* dz, float* out, float* 
   AS_LAUNCH_CHECK();
   colsum_reduce_kernel<<<(C + 31) / 32, 256, 0, st>>>(scratch, out, C, chunks);
   AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+// Backward "prologue" of a linear layer in ONE pass over the fp32 upstream gradient [rows, C] (C % 8 == 0):
+//   dz = dy * (y > 0)   (y fp32 or bf16, optional)   ->  bf16 copy for the dgrad / wgrad GEMMs
+//   colsum[c] = sum_r dz[r][c]                         ->  bias gradient (optional)
+// replaces three passes (ReLU mask, fp32 -> bf16 cast, column sum).  Same thread mapping as colsum_partial_v8_kernel.
+__global__ void __launch_bounds__(256)
+linear_bwd_prep_kernel(const float* __restrict__ dy, const float* __restrict__ y32, const __nv_bfloat16* __restrict__ y16,
+                       __nv_bfloat16* __restrict__ dz, float* __restrict__ partial, long long rows, int C, int chunks,
+                       int txn) {
+  const int tx = threadIdx.x & (txn - 1), ty = threadIdx.x / txn, tyn = 256 / txn;
+  const int c = (blockIdx.x * txn + tx) * 8;
+  const long long per = (rows + chunks - 1) / chunks;
+  const long long r0 = blockIdx.y * per, r1 = (r0 + per < rows) ? r0 + per : rows;
+  float s[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = 0.f;
+  if (c < C) {
+    for (long long r = r0 + ty; r < r1; r += 2 * tyn) {
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const long long rr = r + (long long)u * tyn;
+        if (rr >= r1) break;
+        const float4 a = __ldg(reinterpret_cast<const float4*>(dy + rr * C + c));
+        const float4 b = __ldg(reinterpret_cast<const float4*>(dy + rr * C + c) + 1);
+        float f[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        if (y32) {
+          const float4 ya = __ldg(reinterpret_cast<const float4*>(y32 + rr * C + c));
+          const float4 yb = __ldg(reinterpret_cast<const float4*>(y32 + rr * C + c) + 1);
+          const float yy[8] = {ya.x, ya.y, ya.z, ya.w, yb.x, yb.y, yb.z, yb.w};
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] = yy[j] > 0.f ? f[j] : 0.f;
+        } else if (y16) {
+          BF8 yv;
+          yv.u = __ldg(reinterpret_cast<const uint4*>(y16 + rr * C + c));
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] = bf2f(yv.h[j]) > 0.f ? f[j] : 0.f;
+        }
+        BF8 o;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { o.h[j] = f2bf(f[j]); s[j] += f[j]; }
+        *reinterpret_cast<uint4*>(dz + rr * C + c) = o.u;
+      }
+    }
+  }
+  if (partial == nullptr) return;
+  __shared__ float sm[64 * 36];
+  const int pitch = txn * 8 + 4;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) sm[ty * pitch + tx * 8 + j] = s[j];
+  __syncthreads();
+  if (threadIdx.x < txn * 8) {
+    const int cc = blockIdx.x * txn * 8 + threadIdx.x;
+    if (cc < C) {
+      float t = 0.f;
+      for (int i = 0; i < tyn; ++i) t += sm[i * pitch + threadIdx.x];
+      partial[(long long)blockIdx.y * C + cc] = t;
+    }
+  }
+}
+
+int linear_bwd_prep(const float* dy, const float* y32, const void* y16, void* dz, float* colsum, float* scratch,
+                    long long rows, int C, cudaStream_t st) {
+  if (rows <= 0 || C <= 0 || (C % 8) != 0) return AS_ESIZE;
+  if (!dy || !dz || (colsum && !scratch)) return AS_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(y32) | reinterpret_cast<uintptr_t>(y16) |
+       reinterpret_cast<uintptr_t>(dz)) & 15) return AS_EALIGN;
+  long long want = (rows + 63) / 64;
+  const int chunks = (int)(want < 1 ? 1 : (want > 1024 ? 1024 : want));   // scratch: as_colsum_scratch_floats(C) = 1024 * C floats
+  const int txn = C >= 128 ? 16 : (C >= 64 ? 8 : 4);
+  dim3 g((C + txn * 8 - 1) / (txn * 8), chunks);
+  linear_bwd_prep_kernel<<<g, 256, 0, st>>>(dy, y32, (const __nv_bfloat16*)y16, (__nv_bfloat16*)dz, colsum ? scratch : nullptr,
+                                            rows, C, chunks, txn);
+  AS_LAUNCH_CHECK();
+  if (colsum) {
+    colsum_reduce_kernel<<<(C + 31) / 32, 256, 0, st>>>(scratch, colsum, C, chunks);
+    AS_LAUNCH_CHECK();
+  }
   return AS_OK;
 }
 

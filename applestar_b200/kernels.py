@@ -131,11 +131,24 @@ class LinearFn(torch.autograd.Function):
         else:
             dy = dy32 if dy32 is not None else dy16
         dy2 = dy.reshape(-1, N)
-        if ctx.relu:
-            dy2 = relu_backward(dy2, y)
         M = dy2.shape[0]
-        dy16b = to_bf16(dy2)                      # [M, N8]
         dx = dw = db = None
+        want_db = ctx.has_bias and ctx.needs_input_grad[2]
+        if dy2.dtype == torch.float32 and N % 8 == 0 and dy2.is_contiguous() and (y is None or y.is_contiguous()):
+            # ReLU mask + bf16 cast + bias gradient in one pass over dy
+            dy16b = torch.empty((M, N), dtype=torch.bfloat16, device=dy.device)
+            y32 = y if (y is not None and y.dtype == torch.float32) else None
+            y16 = y if (y is not None and y.dtype == torch.bfloat16) else None
+            if want_db:
+                db = torch.empty(N, dtype=torch.float32, device=dy.device)
+                scratch = torch.empty(_lib.lib().as_colsum_scratch_floats(N), dtype=torch.float32, device=dy.device)
+            _lib.call('as_linear_bwd_prep', dy2.data_ptr(), _ptr(y32), _ptr(y16), dy16b.data_ptr(), _ptr(db),
+                      _ptr(scratch) if want_db else 0, M, N, _lib.stream_ptr())
+            want_db = False
+        else:
+            if ctx.relu:
+                dy2 = relu_backward(dy2, y)
+            dy16b = to_bf16(dy2)                      # [M, N8]
         if ctx.needs_input_grad[0]:
             dx = torch.empty((M, K8), dtype=torch.bfloat16 if ctx.x_bf16 else torch.float32, device=dy.device)
             # dX[m,k] = sum_n dY[m,n] W[n,k]: A = dY (K-major over n), B = W read MN-major (k contiguous)
@@ -147,7 +160,7 @@ class LinearFn(torch.autograd.Function):
             dw = _wgrad(dy16b, x16, N, K8)
             if K8 != ctx.wk:
                 dw = dw[:, :ctx.wk]
-        if ctx.has_bias and ctx.needs_input_grad[2]:
+        if want_db:
             db = column_sum(dy2)
         return dx, dw, db, None, None, None
 

@@ -119,7 +119,13 @@ int as_colsum_f32(const float* x, float* out, float* scratch, int64_t rows, int 
  * dz = dy * (y > 0), colsum[c] = sum_r dz[r][c] -- the `dy * (y > 0)` and `.sum` passes autograd runs for
  * conv2d_block's ReLU + bias (nn_module.py:119-174).  scratch: as_colsum_scratch_floats(C) floats. */
 int as_relu_bwd_colsum_bf16(const void* dy, const void* y, void* dz, float* colsum, float* scratch, int64_t rows, int C,
-                            void* stream);   /* fp32 rows, same scratch size */
+                            void* stream);
+/* Backward prologue of fc_block (nn_module.py:231-270) in one pass over the fp32 upstream gradient [rows, C],
+ * C % 8 == 0: dz16 = bf16(dy * (y > 0)) for the dgrad / wgrad GEMMs (y32 or y16 = the layer's ReLU output, both NULL =
+ * no activation) and colsum[c] = sum_r dy*(y>0) = the bias gradient (colsum NULL = no bias).  Replaces autograd's
+ * threshold_backward, the dtype cast and the `.sum(0)`.  scratch: as_colsum_scratch_floats(C) floats. */
+int as_linear_bwd_prep(const float* dy, const float* y32, const void* y16, void* dz16, float* colsum, float* scratch,
+                       int64_t rows, int C, void* stream);   /* fp32 rows, same scratch size */
 /* Same column sums for hosts that may not allocate device memory at all (a process that gave its whole device
  * budget to an arena at start-up, or a step loop that cannot afford the device-wide synchronisation cudaMalloc /
  * cudaFree bring).  This entry point has no counterpart in the reference.  It allocates nothing: the partial sums
