@@ -498,32 +498,44 @@ __device__ __forceinline__ float field_value(const void* base, int dtype, long l
   }
 }
 
-__global__ void entity_features_kernel(const EntityFieldTable tab, __nv_bfloat16* __restrict__ out, long long rows,
-                                       int pitch, int* __restrict__ neg_flag) {
-  // one warp per row: zero the row, then drop the ones / values in
-  const int lane = threadIdx.x & 31;
-  const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
-  for (long long row = warp_global; row < rows; row += warps_total) {
-    __nv_bfloat16* o = out + row * pitch;
-    uint4* o4 = reinterpret_cast<uint4*>(o);
-    for (int i = lane; i < pitch / 8; i += 32) o4[i] = make_uint4(0, 0, 0, 0);
-    __syncwarp();
-    for (int f = lane; f < tab.n_fields; f += 32) {
-      const float v = field_value(tab.data[f], tab.dtype[f], row);
-      if (tab.kind[f] == 0) {
-        int idx = (int)v;
-        if (idx < 0) { atomicExch(neg_flag, 1); idx = 0; }
-        if (idx > tab.num[f] - 1) idx = tab.num[f] - 1;
-        o[tab.col[f] + idx] = __float2bfloat16_rn(1.f);
-      } else if (tab.kind[f] == 1) {
-        const int iv = (int)v;
-        for (int b = 0; b < tab.num[f]; ++b)
-          if ((iv >> (tab.num[f] - 1 - b)) & 1) o[tab.col[f] + b] = __float2bfloat16_rn(1.f);
-      } else {
-        o[tab.col[f]] = __float2bfloat16_rn(v);
+constexpr int kEfRows = 32;     // rows per CTA
+__global__ void __launch_bounds__(256)
+entity_features_kernel(const EntityFieldTable tab, __nv_bfloat16* __restrict__ out, long long rows, int pitch,
+                       int* __restrict__ neg_flag) {
+  // A CTA assembles kEfRows consecutive rows in shared memory (zeros, then the ones / values of every field; field
+  // arrays are read 32 consecutive rows at a time = coalesced) and streams them out with 16-byte stores.
+  extern __shared__ __align__(16) uint8_t ef_smem[];
+  __nv_bfloat16* srow = reinterpret_cast<__nv_bfloat16*>(ef_smem);       // [kEfRows][pitch]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int n16 = kEfRows * pitch / 8;
+  for (long long row0 = (long long)blockIdx.x * kEfRows; row0 < rows; row0 += (long long)gridDim.x * kEfRows) {
+    for (int i = threadIdx.x; i < n16; i += blockDim.x) reinterpret_cast<uint4*>(srow)[i] = make_uint4(0, 0, 0, 0);
+    __syncthreads();
+    const long long row = row0 + lane;
+    if (row < rows) {
+      __nv_bfloat16* o = srow + lane * pitch;
+      for (int f = warp; f < tab.n_fields; f += 8) {
+        const float v = field_value(tab.data[f], tab.dtype[f], row);
+        if (tab.kind[f] == 0) {
+          int idx = (int)v;
+          if (idx < 0) { atomicExch(neg_flag, 1); idx = 0; }
+          if (idx > tab.num[f] - 1) idx = tab.num[f] - 1;
+          o[tab.col[f] + idx] = __float2bfloat16_rn(1.f);
+        } else if (tab.kind[f] == 1) {
+          const int iv = (int)v;
+          for (int b = 0; b < tab.num[f]; ++b)
+            if ((iv >> (tab.num[f] - 1 - b)) & 1) o[tab.col[f] + b] = __float2bfloat16_rn(1.f);
+        } else {
+          o[tab.col[f]] = __float2bfloat16_rn(v);
+        }
       }
     }
+    __syncthreads();
+    const long long left = rows - row0;
+    const int nvalid = (int)((left < kEfRows ? left : kEfRows) * (pitch / 8));
+    uint4* dst = reinterpret_cast<uint4*>(out + row0 * pitch);
+    for (int i = threadIdx.x; i < nvalid; i += blockDim.x) dst[i] = reinterpret_cast<const uint4*>(srow)[i];
+    __syncthreads();
   }
 }
 
@@ -538,8 +550,17 @@ int entity_features(const void* const* data, const int* kind, const int* num, co
     tab.data[i] = data[i]; tab.kind[i] = kind[i]; tab.num[i] = num[i]; tab.col[i] = col[i]; tab.dtype[i] = dtype[i];
     if (!data[i]) return AS_EINVAL;
   }
-  const int grid = ln_grid(rows);
-  entity_features_kernel<<<grid, 256, 0, st>>>(tab, reinterpret_cast<__nv_bfloat16*>(out), rows, pitch, neg_flag);
+  const int smem = kEfRows * pitch * 2;
+  if (smem > 200 * 1024 || (reinterpret_cast<uintptr_t>(out) & 15)) return AS_ESIZE;
+  static int attr_smem = 0;
+  if (smem > attr_smem) {
+    cudaError_t e = cudaFuncSetAttribute(entity_features_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return (int)e;
+    attr_smem = smem;
+  }
+  long long blocks = (rows + kEfRows - 1) / kEfRows;
+  const int grid = (int)(blocks < 148LL * 12 ? blocks : 148LL * 12);
+  entity_features_kernel<<<grid, 256, smem, st>>>(tab, reinterpret_cast<__nv_bfloat16*>(out), rows, pitch, neg_flag);
   AS_LAUNCH_CHECK();
   return AS_OK;
 }

@@ -229,105 +229,176 @@ __device__ __forceinline__ void up2_src(int o, int n_in, int* i0, int* i1, float
   *w1 = s - (float)a;
 }
 
-__global__ void up2_fwd_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, long long R, int H,
-                               int W, int C, const Dec3 dec) {
-  const int H2 = 2 * H, W2 = 2 * W, C8 = C / 8;
-  const uint32_t total = (uint32_t)(R * (H2 + 2) * (long long)(W2 + 2) * C8);
+// Forward: one thread = one SOURCE pixel (8 channels) -> its 2x2 block of outputs.  With scale 2 and half-pixel
+// centres the even / odd outputs are 0.25 * left + 0.75 * centre and 0.75 * centre + 0.25 * right (indices clamped at
+// the edges, which reproduces F.interpolate's clamping), so a 3x3 neighbourhood is loaded once for four outputs.
+__global__ void __launch_bounds__(256)
+up2_fwd_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, long long R, int H, int W, int C,
+               const Dec3 dec) {
+  const int C8 = C / 8, W2 = 2 * W, H2 = 2 * H;
+  const uint32_t total = (uint32_t)(R * (long long)H * W * C8);
   const uint32_t stride = gridDim.x * blockDim.x;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    int c8, xx, yy, ri;
-    dec3(i, dec, c8, xx, yy, ri);
+    int c8, xs, ys, ri;
+    dec3(i, dec, c8, xs, ys, ri);
     const long long r = ri;
-    BF8 o;
-    if (xx == 0 || xx == W2 + 1 || yy == 0 || yy == H2 + 1) {
-      o.u = make_uint4(0, 0, 0, 0);
-    } else {
-      int y0, y1, x0, x1; float wy, wx;
-      up2_src(yy - 1, H, &y0, &y1, &wy);
-      up2_src(xx - 1, W, &x0, &x1, &wx);
-      const __nv_bfloat16* base = in + (r * (H + 2)) * (long long)(W + 2) * C + c8 * 8;
-      BF8 a, b, c, d;
-      a.u = *reinterpret_cast<const uint4*>(base + ((long long)(y0 + 1) * (W + 2) + x0 + 1) * C);
-      b.u = *reinterpret_cast<const uint4*>(base + ((long long)(y0 + 1) * (W + 2) + x1 + 1) * C);
-      c.u = *reinterpret_cast<const uint4*>(base + ((long long)(y1 + 1) * (W + 2) + x0 + 1) * C);
-      d.u = *reinterpret_cast<const uint4*>(base + ((long long)(y1 + 1) * (W + 2) + x1 + 1) * C);
+    const int ym = ys > 0 ? ys - 1 : 0, yp = ys < H - 1 ? ys + 1 : H - 1;
+    const int xm = xs > 0 ? xs - 1 : 0, xp = xs < W - 1 ? xs + 1 : W - 1;
+    const __nv_bfloat16* base = in + (r * (H + 2)) * (long long)(W + 2) * C + c8 * 8;
+    const int rows[3] = {ym + 1, ys + 1, yp + 1};
+    float he[3][8], ho[3][8];                       // horizontally interpolated even / odd output columns per source row
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+      const __nv_bfloat16* rowp = base + (long long)rows[q] * (W + 2) * C;
+      BF8 l, m, n;
+      l.u = __ldg(reinterpret_cast<const uint4*>(rowp + (long long)(xm + 1) * C));
+      m.u = __ldg(reinterpret_cast<const uint4*>(rowp + (long long)(xs + 1) * C));
+      n.u = __ldg(reinterpret_cast<const uint4*>(rowp + (long long)(xp + 1) * C));
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const float top = bf2f(a.h[j]) * (1.f - wx) + bf2f(b.h[j]) * wx;
-        const float bot = bf2f(c.h[j]) * (1.f - wx) + bf2f(d.h[j]) * wx;
-        o.h[j] = f2bf(top * (1.f - wy) + bot * wy);
+        const float c = 0.75f * bf2f(m.h[j]);
+        he[q][j] = 0.25f * bf2f(l.h[j]) + c;
+        ho[q][j] = c + 0.25f * bf2f(n.h[j]);
       }
     }
-    *reinterpret_cast<uint4*>(out + i * 8) = o.u;
+    BF8 o00, o01, o10, o11;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      o00.h[j] = f2bf(0.25f * he[0][j] + 0.75f * he[1][j]);
+      o01.h[j] = f2bf(0.25f * ho[0][j] + 0.75f * ho[1][j]);
+      o10.h[j] = f2bf(0.75f * he[1][j] + 0.25f * he[2][j]);
+      o11.h[j] = f2bf(0.75f * ho[1][j] + 0.25f * ho[2][j]);
+    }
+    __nv_bfloat16* ob = out + ((r * (H2 + 2) + 2 * ys + 1) * (long long)(W2 + 2) + 2 * xs + 1) * C + c8 * 8;
+    *reinterpret_cast<uint4*>(ob) = o00.u;
+    *reinterpret_cast<uint4*>(ob + C) = o01.u;
+    *reinterpret_cast<uint4*>(ob + (long long)(W2 + 2) * C) = o10.u;
+    *reinterpret_cast<uint4*>(ob + (long long)(W2 + 2) * C + C) = o11.u;
   }
 }
-
-// gather form of the transpose: each input pixel collects from the <=4x4 output pixels that read it
-__global__ void up2_bwd_kernel(const __nv_bfloat16* __restrict__ dout, __nv_bfloat16* __restrict__ din, long long R,
-                               int H, int W, int C, const Dec3 dec) {
-  const int H2 = 2 * H, W2 = 2 * W, C8 = C / 8;
-  const uint32_t total = (uint32_t)(R * (H + 2) * (long long)(W + 2) * C8);
-  const uint32_t stride = gridDim.x * blockDim.x;
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    int c8, xx, yy, ri;
-    dec3(i, dec, c8, xx, yy, ri);
-    const long long r = ri;
-    BF8 o;
-    if (xx == 0 || xx == W + 1 || yy == 0 || yy == H + 1) {
-      o.u = make_uint4(0, 0, 0, 0);
-    } else {
-      const int y = yy - 1, x = xx - 1;
+// Backward (exact transpose): one thread = a 2x2 block of INPUT pixels (8 channels), gathering the 6x6 window of
+// output gradients that touch it.  Input index y receives from output rows 2y-1 .. 2y+2 with weights
+// {0.25, 0.75, 0.75, 0.25}; at the first / last index the missing outer row's weight folds into its neighbour (1.0).
+__device__ __forceinline__ void up2_tw(int y, int n, float* w) {
+  w[0] = y > 0 ? 0.25f : 0.f; w[1] = y > 0 ? 0.75f : 1.f;
+  w[2] = y < n - 1 ? 0.75f : 1.f; w[3] = y < n - 1 ? 0.25f : 0.f;
+}
+constexpr int kUp2Ty = 4;     // input rows per CTA in the backward
+// Separable in shared memory: a CTA owns kUp2Ty input rows of one image.  Phase 1 combines the four output rows that
+// touch each input row (vertical taps) for every OUTPUT column into fp32 V[ty][ox][c]; phase 2 combines four columns
+// of V per input pixel.  Each output gradient is read ~1.25 times (rows shared by neighbouring tiles) instead of
+// nine times from L1/L2 in a per-pixel gather.
+__global__ void __launch_bounds__(512)
+up2_bwd_kernel(const __nv_bfloat16* __restrict__ dout, __nv_bfloat16* __restrict__ din, int H, int W, int C, int nty,
+               const Dec3 d1, const Dec3 d2) {
+  extern __shared__ __align__(16) float sV[];        // [kUp2Ty][2W][C + 4]  (+4: column stride off the bank period)
+  const int Cp = C + 4;
+  const int C8 = C / 8, W2 = 2 * W, H2 = 2 * H;
+  const long long r = blockIdx.x / nty;
+  const int y0 = (blockIdx.x % nty) * kUp2Ty;
+  const __nv_bfloat16* base = dout + (r * (H2 + 2)) * (long long)(W2 + 2) * C;
+  const int n1 = kUp2Ty * W2 * C8;
+  // phase 1 in batches of kB items per thread: all 4 * kB loads are issued before any is consumed (the kernel is
+  // bound by the number of bytes in flight, not by arithmetic)
+  constexpr int kB = 5;
+  for (int i0 = threadIdx.x; i0 < n1; i0 += kB * blockDim.x) {
+    uint4 v[kB][4];
+    float wy[kB][4];
+    int so[kB];
+#pragma unroll
+    for (int u = 0; u < kB; ++u) {
+      const int i = i0 + u * blockDim.x;
+      so[u] = -1;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { v[u][k] = make_uint4(0, 0, 0, 0); wy[u][k] = 0.f; }
+      if (i < n1) {
+        int c8, ox, ty, unused;
+        dec3((uint32_t)i, d1, c8, ox, ty, unused);
+        const int y = y0 + ty;
+        if (y < H) {
+          up2_tw(y, H, wy[u]);
+          so[u] = (ty * W2 + ox) * Cp + c8 * 8;
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            if (wy[u][k] != 0.f)                     // also excludes the rows outside the image
+              v[u][k] = __ldg(reinterpret_cast<const uint4*>(base + ((long long)(2 * y + k) * (W2 + 2) + ox + 1) * C + c8 * 8));
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kB; ++u) {
+      if (so[u] < 0) continue;
       float acc[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-      const __nv_bfloat16* base = dout + (r * (H2 + 2)) * (long long)(W2 + 2) * C + c8 * 8;
-      for (int oy = 2 * y - 1; oy <= 2 * y + 2; ++oy) {
-        if (oy < 0 || oy >= H2) continue;
-        int y0, y1; float wy;
-        up2_src(oy, H, &y0, &y1, &wy);
-        const float cy = (y0 == y ? 1.f - wy : 0.f) + (y1 == y ? wy : 0.f);
-        if (cy == 0.f) continue;
-        for (int ox = 2 * x - 1; ox <= 2 * x + 2; ++ox) {
-          if (ox < 0 || ox >= W2) continue;
-          int x0, x1; float wx;
-          up2_src(ox, W, &x0, &x1, &wx);
-          const float cx = (x0 == x ? 1.f - wx : 0.f) + (x1 == x ? wx : 0.f);
-          if (cx == 0.f) continue;
-          BF8 v;
-          v.u = *reinterpret_cast<const uint4*>(base + ((long long)(oy + 1) * (W2 + 2) + ox + 1) * C);
-          const float w = cy * cx;
 #pragma unroll
-          for (int j = 0; j < 8; ++j) acc[j] += w * bf2f(v.h[j]);
-        }
+      for (int k = 0; k < 4; ++k) {
+        BF8 t;
+        t.u = v[u][k];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += wy[u][k] * bf2f(t.h[j]);
       }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) o.h[j] = f2bf(acc[j]);
+      float4* dst = reinterpret_cast<float4*>(sV + so[u]);
+      dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+      dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
     }
-    *reinterpret_cast<uint4*>(din + (long long)i * 8) = o.u;
+  }
+  __syncthreads();
+  const int n2 = kUp2Ty * W * C8;
+  for (int i = threadIdx.x; i < n2; i += blockDim.x) {
+    int c8, x, ty, unused;
+    dec3((uint32_t)i, d2, c8, x, ty, unused);
+    const int y = y0 + ty;
+    if (y >= H) continue;
+    float wx[4];
+    up2_tw(x, W, wx);
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (wx[k] == 0.f) continue;
+      const float4* src = reinterpret_cast<const float4*>(sV + ((long long)ty * W2 + 2 * x - 1 + k) * Cp + c8 * 8);
+      const float4 a = src[0], b = src[1];
+      acc[0] += wx[k] * a.x; acc[1] += wx[k] * a.y; acc[2] += wx[k] * a.z; acc[3] += wx[k] * a.w;
+      acc[4] += wx[k] * b.x; acc[5] += wx[k] * b.y; acc[6] += wx[k] * b.z; acc[7] += wx[k] * b.w;
+    }
+    BF8 o;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o.h[j] = f2bf(acc[j]);
+    *reinterpret_cast<uint4*>(din + ((r * (H + 2) + y + 1) * (long long)(W + 2) + x + 1) * C + c8 * 8) = o.u;
   }
 }
 
+int zero_border(void* x, long long R, int H, int W, int C, cudaStream_t st);
 int up2_fwd(const void* in, void* out, long long R, int H, int W, int C, cudaStream_t st) {
   if (R <= 0) return AS_OK;
   if (C % 8 || H <= 0 || W <= 0) return AS_ESIZE;
   if (!in || !out) return AS_EINVAL;
-  const long long total = R * (2 * H + 2) * (long long)(2 * W + 2) * (C / 8);
+  const long long total = R * (long long)H * W * (C / 8);
   if (total >= (1LL << 31)) return AS_ESIZE;
   up2_fwd_kernel<<<ew_grid(total, 1), 256, 0, st>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, R, H, W, C,
-                                                    make_dec3(C / 8, 2 * W + 2, 2 * H + 2));
+                                                    make_dec3(C / 8, W, H));
   AS_LAUNCH_CHECK();
-  return AS_OK;
+  return zero_border(out, R, 2 * H, 2 * W, C, st);
 }
 int up2_bwd(const void* dout, void* din, long long R, int H, int W, int C, cudaStream_t st) {
   if (R <= 0) return AS_OK;
   if (C % 8 || H <= 0 || W <= 0) return AS_ESIZE;
   if (!dout || !din) return AS_EINVAL;
-  const long long total = R * (H + 2) * (long long)(W + 2) * (C / 8);
-  if (total >= (1LL << 31)) return AS_ESIZE;
-  up2_bwd_kernel<<<ew_grid(total, 1), 256, 0, st>>>((const __nv_bfloat16*)dout, (__nv_bfloat16*)din, R, H, W, C,
-                                                    make_dec3(C / 8, W + 2, H + 2));
+  const int nty = (H + kUp2Ty - 1) / kUp2Ty;
+  const int smem = kUp2Ty * 2 * W * (C + 4) * 4;
+  if (smem > 200 * 1024 || R * nty >= (1LL << 31)) return AS_ESIZE;
+  static int attr_smem = 0;
+  if (smem > attr_smem) {
+    cudaError_t e = cudaFuncSetAttribute(up2_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return (int)e;
+    attr_smem = smem;
+  }
+  up2_bwd_kernel<<<(unsigned)(R * nty), 512, smem, st>>>((const __nv_bfloat16*)dout, (__nv_bfloat16*)din, H, W, C, nty,
+                                                       make_dec3(C / 8, 2 * W, kUp2Ty), make_dec3(C / 8, W, kUp2Ty));
   AS_LAUNCH_CHECK();
-  return AS_OK;
+  return zero_border(din, R, H, W, C, st);
 }
 
 // ------------------------------------------------------------------------------------------ location-head input
@@ -972,6 +1043,12 @@ __global__ void zero_border_kernel(__nv_bfloat16* __restrict__ x, long long R, i
   }
 }
 
+int zero_border(void* x, long long R, int H, int W, int C, cudaStream_t st) {
+  const long long ring = R * (long long)(2 * (W + 2) + 2 * H) * (C / 8);
+  zero_border_kernel<<<ew_grid(ring, 1), 256, 0, st>>>((__nv_bfloat16*)x, R, H, W, C);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
 int maxpool2_fwd(const void* in, void* out, long long R, int H, int W, int C, cudaStream_t st) {
   if (R <= 0) return AS_OK;
   if ((C % 8) || (H % 2) || (W % 2) || H <= 0 || W <= 0) return AS_ESIZE;
