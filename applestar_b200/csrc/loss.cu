@@ -116,61 +116,114 @@ __device__ __forceinline__ float head_mask_at(const AsLossArgs& a, int h, long l
   return a.actions_mask[h] ? (float)a.actions_mask[h][step] : 1.f;
 }
 
-__global__ void __launch_bounds__(64) loss_scan_kernel(const AsLossArgs a) {
-  const int b = blockIdx.x;
-  const int T = a.T, B = a.B, F = a.F;
-  extern __shared__ float sm[];
-  // shared columns: logp_a[6][T], mu[6][T], value[F][T+1], reward[F][T]
-  float* s_lp = sm;
-  float* s_rho = s_lp + 6 * T;
-  float* s_v = s_rho + 6 * T;
-  float* s_r = s_v + F * (T + 1);
-  const float inv_tb = 1.f / (float)(T * B);
+// One CTA per trajectory, three stages:
+//   A  (all 256 threads) gather everything the scans need into shared memory with coalesced / warp-parallel reads:
+//      per-step log-probs, importance ratios, head and field masks, values, rewards, the per-step sums over the
+//      selected-units rows and the valid-logit counts of the two pointer heads (513 / 512 mask bytes per step);
+//   B  (one thread per (head | field | term) job) the time recurrences, reading shared memory only;
+//   C  (all threads) coalesced write-out of the backward coefficients.
+// The earlier version ran every loop of A and C inside the single-thread jobs (4096 dependent global accesses per
+// selected-units job): 1.43 ms; this one is bound by the 64-step recurrences themselves.
+constexpr int kScanThreads = 256;
 
-  for (int t = threadIdx.x; t < T; t += blockDim.x) {
+__global__ void __launch_bounds__(kScanThreads) loss_scan_kernel(const AsLossArgs a) {
+  const int b = blockIdx.x;
+  const int T = a.T, B = a.B, F = a.F, S = a.S;
+  extern __shared__ float sm[];
+  float* s_lp = sm;                       // [6][T]  log pi(a) per head (selected units: sum over valid rows)
+  float* s_rho = s_lp + 6 * T;            // [6][T]  min(1, pi / mu)
+  float* s_hm = s_rho + 6 * T;            // [6][T]  head masks
+  float* s_st2 = s_hm + 6 * T;            // [6][T]  entropy statistic (selected units: sum over valid rows)
+  float* s_st4 = s_st2 + 6 * T;           // [6][T]  KL statistic
+  float* s_c0 = s_st4 + 6 * T;            // [6][T]  out: policy-gradient + UPGO coefficient
+  float* s_c1 = s_c0 + 6 * T;             // [6][T]  out: entropy coefficient (per valid row for selected units)
+  float* s_c2 = s_c1 + 6 * T;             // [6][T]  out: KL coefficient
+  float* s_v = s_c2 + 6 * T;              // [F][T+1]
+  float* s_r = s_v + F * (T + 1);         // [F][T]
+  float* s_fm = s_r + F * T;              // [F][T]  field masks
+  float* s_dv = s_fm + F * T;             // [F][T]  out: d value
+  float* s_cnt = s_dv + F * T;            // [T] valid selected-units rows
+  float* s_nlsu = s_cnt + T;              // [T] valid selected-units logits
+  float* s_nltu = s_nlsu + T;             // [T] valid target-unit logits
+  float* s_atm = s_nltu + T;              // [T] action-type extra-KL mask
+  float* s_br = s_atm + T;                // [T] battle reward
+  const float inv_tb = 1.f / (float)(T * B);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = kScanThreads / 32;
+
+  // ---- A1: per-step scalars, thread = (t, item)
+  for (int i = tid; i < T * 6; i += kScanThreads) {
+    const int h = i / T, t = i - h * T;
     const long long step = (long long)t * B + b;
-    for (int h = 0; h < 6; ++h) {
-      float lp, lr;
-      if (h == 3) {
-        lp = 0.f; lr = 0.f;
-        for (int j = 0; j < a.S; ++j) {
-          const long long row = step * a.S + j;
-          if (a.su_mask[row]) {
-            const float l = a.row_stats[3][row * kStatStride + 1];
-            lp += l;
-            lr += l - a.mu_logp[3][row];
-          }
-        }
-      } else {
-        lp = a.row_stats[h][step * kStatStride + 1];
-        lr = lp - a.mu_logp[h][step];
-      }
-      s_lp[h * T + t] = lp;
-      s_rho[h * T + t] = fminf(expf(lr), 1.f);
+    s_hm[i] = head_mask_at(a, h, step);
+    s_c0[i] = 0.f;
+    if (h != 3) {
+      const float lp = a.row_stats[h][step * kStatStride + 1];
+      s_lp[i] = lp;
+      s_rho[i] = fminf(expf(lp - a.mu_logp[h][step]), 1.f);
+      s_st2[i] = a.row_stats[h][step * kStatStride + 2];
+      s_st4[i] = a.row_stats[h][step * kStatStride + 4];
     }
-    for (int f = 0; f < F; ++f) s_r[f * T + t] = a.reward[f][step];
   }
-  for (int t = threadIdx.x; t <= T; t += blockDim.x) {
-    for (int f = 0; f < F; ++f) {
-      float v = a.value[f][(long long)t * B + b];
-      if (t == T) v *= (a.winloss_reward[(long long)(T - 1) * B + b] == 0.f) ? 1.f : 0.f;   // rl_loss.py:47-49
-      s_v[f * (T + 1) + t] = v;
+  for (int i = tid; i < T * F; i += kScanThreads) {
+    const int f = i / T, t = i - f * T;
+    const long long step = (long long)t * B + b;
+    s_r[i] = a.reward[f][step];
+    s_fm[i] = a.field_mask[f] ? a.field_mask[f][step] : 1.f;
+  }
+  for (int i = tid; i < (T + 1) * F; i += kScanThreads) {
+    const int f = i / (T + 1), t = i - f * (T + 1);
+    float v = a.value[f][(long long)t * B + b];
+    if (t == T) v *= (a.winloss_reward[(long long)(T - 1) * B + b] == 0.f) ? 1.f : 0.f;   // rl_loss.py:47-49
+    s_v[i] = v;
+  }
+  for (int t = tid; t < T; t += kScanThreads) {
+    const long long step = (long long)t * B + b;
+    s_atm[t] = ((a.step[step] < a.at_kl_steps) ? 1.f : 0.f) * a.cum_action_mask[step];
+    s_br[t] = a.battle_reward[step];
+  }
+  // ---- A2: warp per step: sums over the selected-units rows and the pointer-head logit masks
+  for (int t = warp; t < T; t += nwarp) {
+    const long long step = (long long)t * B + b;
+    float lp = 0.f, lr = 0.f, e2 = 0.f, k4 = 0.f, cnt = 0.f, nsu = 0.f, ntu = 0.f;
+    for (int j = lane; j < S; j += 32) {
+      const long long row = step * S + j;
+      if (a.su_mask[row]) {
+        const float l = a.row_stats[3][row * kStatStride + 1];
+        lp += l;
+        lr += l - a.mu_logp[3][row];
+        e2 += a.row_stats[3][row * kStatStride + 2];
+        k4 += a.row_stats[3][row * kStatStride + 4];
+        cnt += 1.f;
+      }
+    }
+    for (int j = lane; j < a.N1; j += 32) nsu += a.su_logits_mask[step * a.N1 + j] ? 1.f : 0.f;
+    for (int j = lane; j < a.NE; j += 32) ntu += a.tu_logits_mask[step * a.NE + j] ? 1.f : 0.f;
+    lp = warp_sum(lp); lr = warp_sum(lr); e2 = warp_sum(e2); k4 = warp_sum(k4);
+    cnt = warp_sum(cnt); nsu = warp_sum(nsu); ntu = warp_sum(ntu);
+    if (lane == 0) {
+      s_lp[3 * T + t] = lp;
+      s_rho[3 * T + t] = fminf(expf(lr), 1.f);
+      s_st2[3 * T + t] = e2;
+      s_st4[3 * T + t] = k4;
+      s_cnt[t] = cnt; s_nlsu[t] = nsu; s_nltu[t] = ntu;
     }
   }
   __syncthreads();
 
+  // ---- B: recurrences (shared memory only)
   float* part = a.partial + (long long)b * AS_LOSS_MAX_STATS;
   const int base = F * 10;
-  const int lane = threadIdx.x;
-  if (lane < 6) {
-    // ---- head job: V-trace per field (gamma = lambda = 1, rl_loss.py:102-103) + UPGO on winloss
-    const int h = lane;
+  if (tid < 6) {
+    // head job: V-trace per field (gamma = lambda = 1, rl_loss.py:102-103) + UPGO on winloss
+    const int h = tid;
     const float* rho = s_rho + h * T;
     const float* lp = s_lp + h * T;
-    for (int t = 0; t < T; ++t) a.coef[h][((long long)t * B + b) * kCoefStride + 0] = 0.f;
+    const float* hm = s_hm + h * T;
+    float* c0 = s_c0 + h * T;
     for (int f = 0; f < F; ++f) {
       const float* v = s_v + f * (T + 1);
       const float* r = s_r + f * T;
+      const float* fm = s_fm + f * T;
       float acc = 0.f;
       float vs_next = v[T];
       for (int t = T - 1; t >= 0; --t) {
@@ -178,11 +231,9 @@ __global__ void __launch_bounds__(64) loss_scan_kernel(const AsLossArgs a) {
         const float vs = v[t] + delta + rho[t] * (vs_next - v[t + 1]);
         const float adv = rho[t] * (r[t] + vs_next - v[t]);
         vs_next = vs;
-        const long long step = (long long)t * B + b;
-        float m = head_mask_at(a, h, step);
-        if (a.field_mask[f]) m *= a.field_mask[f][step];
+        const float m = hm[t] * fm[t];
         acc += -adv * lp[t] * m;
-        a.coef[h][step * kCoefStride + 0] += -adv * m * a.w_pg[f] * a.hw_pg[h] * inv_tb;
+        c0[t] += -adv * m * a.w_pg[f] * a.hw_pg[h] * inv_tb;
       }
       part[f * 10 + h] = acc;
     }
@@ -202,16 +253,14 @@ __global__ void __launch_bounds__(64) loss_scan_kernel(const AsLossArgs a) {
         }
         g_next = g;
         const float adv = rho[t] * (g - v[t]);
-        const long long step = (long long)t * B + b;
-        const float m = head_mask_at(a, h, step);
-        acc += -adv * lp[t] * m;
-        a.coef[h][step * kCoefStride + 0] += -adv * m * a.w_upgo * a.hw_upgo[h] * inv_tb;
+        acc += -adv * lp[t] * hm[t];
+        c0[t] += -adv * hm[t] * a.w_upgo * a.hw_upgo[h] * inv_tb;
       }
       part[base + h] = acc;
     }
-  } else if (lane < 6 + F) {
-    // ---- TD(lambda = 0.8) per field (as_rl_utils.py:221-243)
-    const int f = lane - 6;
+  } else if (tid >= 32 && tid < 32 + F) {
+    // TD(lambda = 0.8) per field (as_rl_utils.py:221-243)
+    const int f = tid - 32;
     const float* v = s_v + f * (T + 1);
     const float* r = s_r + f * T;
     const float gamma = a.gamma_td[f], lam = 0.8f;
@@ -225,90 +274,84 @@ __global__ void __launch_bounds__(64) loss_scan_kernel(const AsLossArgs a) {
         g = r[t] + d * g_next + (gamma - d) * v[t + 1];
       }
       g_next = g;
-      const long long step = (long long)t * B + b;
-      const float m = a.field_mask[f] ? a.field_mask[f][step] : 1.f;
+      const float m = s_fm[f * T + t];
       const float diff = g - v[t];
       acc += 0.5f * diff * diff * m;
       racc += r[t];
       vacc += v[t];
-      a.dvalue[f][step] = -diff * m * a.w_td[f] * inv_tb;
+      s_dv[f * T + t] = -diff * m * a.w_td[f] * inv_tb;
     }
-    a.dvalue[f][(long long)T * B + b] = 0.f;
     part[f * 10 + 6] = acc;
     part[f * 10 + 7] = racc;
     part[f * 10 + 8] = vacc * ((float)T / (float)(T + 1));      // finalize multiplies by 1/(T*B); mean is over (T+1)*B
     part[f * 10 + 9] = 0.f;
-  } else if (lane >= 16 && lane < 22) {
-    // ---- entropy per head (as_rl_utils.py:52-72) and its backward coefficient
-    const int h = lane - 16;
+  } else if (tid >= 64 && tid < 70) {
+    // entropy per head (as_rl_utils.py:52-72) and its backward coefficient
+    const int h = tid - 64;
     float acc = 0.f;
     for (int t = 0; t < T; ++t) {
-      const long long step = (long long)t * B + b;
-      const float hm = head_mask_at(a, h, step);
-      float e = 0.f;
+      const float hm = s_hm[h * T + t];
+      float e;
       if (h == 3) {
-        float cnt = 0.f, nl = 0.f;
-        for (int j = 0; j < a.N1; ++j) nl += a.su_logits_mask[step * a.N1 + j] ? 1.f : 0.f;
-        for (int j = 0; j < a.S; ++j) cnt += a.su_mask[step * a.S + j] ? 1.f : 0.f;
-        const float norm = 1e-9f + logf(nl + 1.f);
-        const float denom = cnt + 1e-9f;
-        for (int j = 0; j < a.S; ++j) {
-          const long long row = step * a.S + j;
-          const bool on = a.su_mask[row];
-          if (on) e += a.row_stats[3][row * kStatStride + 2] / norm;
-          a.coef[3][row * kCoefStride + 1] = on ? (-a.w_ent * a.hw_ent[3] * hm * inv_tb / (norm * denom)) : 0.f;
-        }
-        e /= denom;
+        const float norm = 1e-9f + logf(s_nlsu[t] + 1.f);
+        const float denom = s_cnt[t] + 1e-9f;
+        e = s_st2[3 * T + t] / norm / denom;
+        s_c1[3 * T + t] = -a.w_ent * a.hw_ent[3] * hm * inv_tb / (norm * denom);
       } else {
-        float norm;
-        if (h == 4) {
-          float nl = 0.f;
-          for (int j = 0; j < a.NE; ++j) nl += a.tu_logits_mask[step * a.NE + j] ? 1.f : 0.f;
-          norm = 1e-9f + logf(nl + 1.f);
-        } else {
-          norm = logf((float)a.head_k[h]);
-        }
-        e = a.row_stats[h][step * kStatStride + 2] / norm;
-        a.coef[h][step * kCoefStride + 1] = -a.w_ent * a.hw_ent[h] * hm * inv_tb / norm;
+        const float norm = (h == 4) ? 1e-9f + logf(s_nltu[t] + 1.f) : logf((float)a.head_k[h]);
+        e = s_st2[h * T + t] / norm;
+        s_c1[h * T + t] = -a.w_ent * a.hw_ent[h] * hm * inv_tb / norm;
       }
       acc += e * hm;
     }
     part[base + 6 + h] = acc;
-  } else if (lane >= 24 && lane < 30) {
-    // ---- KL(teacher || pi) per head (as_rl_utils.py:75-103) and its backward coefficient
-    const int h = lane - 24;
+  } else if (tid >= 96 && tid < 102) {
+    // KL(teacher || pi) per head (as_rl_utils.py:75-103) and its backward coefficient
+    const int h = tid - 96;
     float acc = 0.f, acc_at = 0.f;
     for (int t = 0; t < T; ++t) {
-      const long long step = (long long)t * B + b;
-      const float hm = head_mask_at(a, h, step);
+      const float hm = s_hm[h * T + t];
       float ck = a.w_kl * a.hw_kl[h] * hm * inv_tb;
-      float kl = 0.f;
-      if (h == 3) {
-        for (int j = 0; j < a.S; ++j) {
-          const long long row = step * a.S + j;
-          const bool on = a.su_mask[row];
-          if (on) kl += a.row_stats[3][row * kStatStride + 4];
-          a.coef[3][row * kCoefStride + 2] = on ? ck : 0.f;
-        }
-      } else {
-        kl = a.row_stats[h][step * kStatStride + 4];
-        if (h == 0) {
-          const float flag = (a.step[step] < a.at_kl_steps) ? 1.f : 0.f;
-          const float m = flag * a.cum_action_mask[step];
-          acc_at += kl * m;
-          ck += a.w_atkl * m * inv_tb;
-        }
-        a.coef[h][step * kCoefStride + 2] = ck;
+      const float kl = s_st4[h * T + t];
+      if (h == 0) {
+        const float m = s_atm[t];
+        acc_at += kl * m;
+        ck += a.w_atkl * m * inv_tb;
       }
+      s_c2[h * T + t] = ck;
       acc += kl * hm;
     }
     part[base + 12 + h] = acc;
     if (h == 0) part[base + 18] = acc_at;
-  } else if (lane == 30) {
+  } else if (tid == 128) {
     float acc = 0.f;
-    for (int t = 0; t < T; ++t) acc += a.battle_reward[(long long)t * B + b];
+    for (int t = 0; t < T; ++t) acc += s_br[t];
     part[base + 19] = acc;
   }
+  __syncthreads();
+
+  // ---- C: coefficients and value gradients, coalesced
+  for (int i = tid; i < T * 6; i += kScanThreads) {
+    const int h = i / T, t = i - h * T;
+    const long long step = (long long)t * B + b;
+    a.coef[h][step * kCoefStride + 0] = s_c0[i];
+    if (h != 3) {
+      a.coef[h][step * kCoefStride + 1] = s_c1[i];
+      a.coef[h][step * kCoefStride + 2] = s_c2[i];
+    }
+  }
+  for (int i = tid; i < T * S; i += kScanThreads) {
+    const int t = i / S, j = i - t * S;
+    const long long row = ((long long)t * B + b) * S + j;
+    const bool on = a.su_mask[row];
+    a.coef[3][row * kCoefStride + 1] = on ? s_c1[3 * T + t] : 0.f;
+    a.coef[3][row * kCoefStride + 2] = on ? s_c2[3 * T + t] : 0.f;
+  }
+  for (int i = tid; i < T * F; i += kScanThreads) {
+    const int f = i / T, t = i - f * T;
+    a.dvalue[f][(long long)t * B + b] = s_dv[i];
+  }
+  if (tid < F) a.dvalue[tid][(long long)T * B + b] = 0.f;
 }
 
 // ---------------------------------------------------------------------------------------------- K3
@@ -389,9 +432,9 @@ int loss_forward(const AsLossArgs& a, cudaStream_t st) {
     else loss_row_stats_kernel<32><<<stats_grid(rows, 8), 256, 0, st>>>(a, h, rows, K);
     AS_LAUNCH_CHECK();
   }
-  const int smem = (12 * a.T + a.F * (2 * a.T + 1)) * 4;
+  const int smem = (48 * a.T + a.F * (4 * a.T + 1) + 5 * a.T) * 4;
   if (smem > 48 * 1024) return AS_ESIZE;
-  loss_scan_kernel<<<a.B, 64, smem, st>>>(a);
+  loss_scan_kernel<<<a.B, kScanThreads, smem, st>>>(a);
   AS_LAUNCH_CHECK();
   loss_finalize_kernel<<<1, 64, 0, st>>>(a);
   AS_LAUNCH_CHECK();

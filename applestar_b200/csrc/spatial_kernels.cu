@@ -480,46 +480,63 @@ __device__ __forceinline__ void unpack8(const uint4& q, float* f) {
   }
 }
 
-__global__ void __launch_bounds__(256, 3)
+// These three kernels are bound by the L1 / LSU data pipe, not by HBM, when every output re-loads its nine taps
+// (ncu: 14.3 GB through L1 for 1.66 GB of input, lsu wavefronts at 84 % of peak).  So: four lanes (8 channels each)
+// own one pixel COLUMN and walk down a segment of rows with a sliding 3x3 window in registers -- three 16-byte loads
+// per output instead of nine, and a warp's load is still 512 contiguous bytes.
+constexpr int kC32Seg = 38;      // rows per thread segment (152 = 4 * 38)
+
+__device__ __forceinline__ float dot8w(const uint4& q, const float (&wt)[8]) {
+  float f[8];
+  unpack8(q, f);
+  return f[0] * wt[0] + f[1] * wt[1] + f[2] * wt[2] + f[3] * wt[3] + f[4] * wt[4] + f[5] * wt[5] + f[6] * wt[6] + f[7] * wt[7];
+}
+
+__global__ void __launch_bounds__(256, 2)
 conv_c32_1_fwd_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict__ w, const float* __restrict__ bias,
-                      float* __restrict__ out, long long R, int H, int W, float inv_temp, const Dec3 dec) {
-  // weights stay in shared memory (broadcast 16-byte reads): holding them in registers costs 72 registers per thread
-  // and leaves one CTA per SM, far too few loads in flight for an HBM-bound kernel
-  __shared__ __align__(16) float sw[288];
-  for (int i = threadIdx.x; i < 288; i += blockDim.x) sw[i] = w[i];
-  __syncthreads();
+                      float* __restrict__ out, long long R, int H, int W, float inv_temp, int nseg, const Dec3 dec) {
   const int cg = threadIdx.x & 3;
+  float sw[9][8];                                   // this lane's 8 channels of every tap, in registers (shared-memory
+#pragma unroll                                      // reads would share the LSU pipe with the pixel loads)
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int c = 0; c < 8; ++c) sw[t][c] = __ldg(w + t * 32 + cg * 8 + c);
   const float b = bias ? bias[0] : 0.f;
-  const long long total = R * (long long)H * W;
+  const long long total = R * (long long)nseg * W;                 // pixel columns x row segments
+  const long long total_pad = (total + 7) & ~7LL;                  // whole warps stay in the loop for the shuffles
   const long long stride = ((long long)gridDim.x * blockDim.x) >> 2;
-  const long long first = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 2;
-  const long long total_pad = (total + 7) & ~7LL;              // whole warps stay in the loop for the shuffles
-  for (long long p = first; p < total_pad; p += stride) {
-    const bool ok = p < total;
-    const long long pc = ok ? p : 0;
-    int x, y, ri, unused;
-    dec3((uint32_t)pc, dec, x, y, ri, unused);
+  for (long long col = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 2; col < total_pad; col += stride) {
+    const bool ok = col < total;
+    int x, seg, ri, unused;
+    dec3((uint32_t)(ok ? col : 0), dec, x, seg, ri, unused);
     const long long r = ri;
-    const __nv_bfloat16* base = in + ((r * (H + 2) + y) * (long long)(W + 2) + x) * 32 + cg * 8;
-    float acc = 0.f;
+    const int y0 = seg * kC32Seg, y1 = min(H, y0 + kC32Seg);
+    const long long pitch = (long long)(W + 2) * 32;
+    const __nv_bfloat16* p = in + ((r * (H + 2) + y0) * (long long)(W + 2) + x) * 32 + cg * 8;
+    uint4 r0[3], r1[3], r2[3];
 #pragma unroll
-    for (int ky = 0; ky < 3; ++ky) {
-      uint4 v[3];
+    for (int kx = 0; kx < 3; ++kx) {
+      r0[kx] = __ldg(reinterpret_cast<const uint4*>(p + kx * 32));
+      r1[kx] = __ldg(reinterpret_cast<const uint4*>(p + pitch + kx * 32));
+    }
+    for (int y = y0; y < y1; ++y) {
+      const __nv_bfloat16* pr = p + (long long)(y - y0 + 2) * pitch;
 #pragma unroll
-      for (int kx = 0; kx < 3; ++kx)
-        v[kx] = __ldg(reinterpret_cast<const uint4*>(base + ((long long)ky * (W + 2) + kx) * 32));
+      for (int kx = 0; kx < 3; ++kx) r2[kx] = __ldg(reinterpret_cast<const uint4*>(pr + kx * 32));
+      float a0 = 0.f, a1 = 0.f, a2 = 0.f;             // three independent chains
 #pragma unroll
       for (int kx = 0; kx < 3; ++kx) {
-        float f[8];
-        unpack8(v[kx], f);
-        const float4 w0 = *reinterpret_cast<const float4*>(sw + (ky * 3 + kx) * 32 + cg * 8);
-        const float4 w1 = *reinterpret_cast<const float4*>(sw + (ky * 3 + kx) * 32 + cg * 8 + 4);
-        acc += f[0] * w0.x + f[1] * w0.y + f[2] * w0.z + f[3] * w0.w + f[4] * w1.x + f[5] * w1.y + f[6] * w1.z + f[7] * w1.w;
+        a0 += dot8w(r0[kx], sw[0 * 3 + kx]);
+        a1 += dot8w(r1[kx], sw[1 * 3 + kx]);
+        a2 += dot8w(r2[kx], sw[2 * 3 + kx]);
       }
+      float acc = a0 + a1 + a2;
+      acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+      acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+      if (ok && cg == 0) out[(r * H + y) * (long long)W + x] = (acc + b) * inv_temp;
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) { r0[kx] = r1[kx]; r1[kx] = r2[kx]; }
     }
-    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
-    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
-    if (ok && cg == 0) out[p] = (acc + b) * inv_temp;
   }
 }
 
@@ -571,42 +588,59 @@ conv_c32_1_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ 
     }
   }
 }
-// dw[tap][c] = sum_p dy[p] in[p+tap][c];  db = sum dy  -> per-block partials [blocks][9*32+1].  Same thread mapping as
-// the forward (pixel slot x 8-channel group): 72 fp32 accumulators per thread, coalesced 16-byte tap loads, then a
-// shuffle reduction over the warp's eight pixel slots and a shared-memory reduction over the block's warps.
-__global__ void __launch_bounds__(256, 3)
+// dw[tap][c] = sum_p dy[p] in[p+tap][c];  db = sum dy  -> per-block partials [blocks][9*32+1].  Same column-walking
+// thread mapping as the forward: 72 fp32 accumulators per thread, three 16-byte loads per pixel, then a shuffle
+// reduction over the warp's eight pixel columns and a shared-memory reduction over the block's warps.
+__global__ void __launch_bounds__(256, 2)
 conv_c32_1_wgrad_kernel(const float* __restrict__ dy, const __nv_bfloat16* __restrict__ in,
-                        float* __restrict__ partial, long long R, int H, int W, float inv_temp, const Dec3 dec) {
-  // blockIdx.y = tap row ky: 24 accumulators per thread instead of 72, so three CTAs fit per SM
-  const int cg = threadIdx.x & 3, lane = threadIdx.x & 31, wid = threadIdx.x >> 5, ky = blockIdx.y;
-  float acc[3][8], accb = 0.f;
+                        float* __restrict__ partial, long long R, int H, int W, float inv_temp, int nseg, const Dec3 dec) {
+  const int cg = threadIdx.x & 3, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  float acc[9][8], accb = 0.f;
 #pragma unroll
-  for (int t = 0; t < 3; ++t)
+  for (int t = 0; t < 9; ++t)
 #pragma unroll
     for (int c = 0; c < 8; ++c) acc[t][c] = 0.f;
-  const long long total = R * (long long)H * W;
+  const long long total = R * (long long)nseg * W;
   const long long stride = ((long long)gridDim.x * blockDim.x) >> 2;
-  for (long long p = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 2; p < total; p += stride) {
-    int x, y, ri, unused;
-    dec3((uint32_t)p, dec, x, y, ri, unused);
+  for (long long col = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 2; col < total; col += stride) {
+    int x, seg, ri, unused;
+    dec3((uint32_t)col, dec, x, seg, ri, unused);
     const long long r = ri;
-    const float g = __ldg(dy + p) * inv_temp;
-    const __nv_bfloat16* base = in + ((r * (H + 2) + y + ky) * (long long)(W + 2) + x) * 32 + cg * 8;
-    uint4 v[3];
+    const int y0 = seg * kC32Seg, y1 = min(H, y0 + kC32Seg);
+    const long long pitch = (long long)(W + 2) * 32;
+    const __nv_bfloat16* p = in + ((r * (H + 2) + y0) * (long long)(W + 2) + x) * 32 + cg * 8;
+    uint4 r0[3], r1[3], r2[3];
 #pragma unroll
-    for (int kx = 0; kx < 3; ++kx) v[kx] = __ldg(reinterpret_cast<const uint4*>(base + kx * 32));
-    accb += g;
+    for (int kx = 0; kx < 3; ++kx) {
+      r0[kx] = __ldg(reinterpret_cast<const uint4*>(p + kx * 32));
+      r1[kx] = __ldg(reinterpret_cast<const uint4*>(p + pitch + kx * 32));
+    }
+    for (int y = y0; y < y1; ++y) {
+      const __nv_bfloat16* pr = p + (long long)(y - y0 + 2) * pitch;
 #pragma unroll
-    for (int t = 0; t < 3; ++t) {
-      float f[8];
-      unpack8(v[t], f);
+      for (int kx = 0; kx < 3; ++kx) r2[kx] = __ldg(reinterpret_cast<const uint4*>(pr + kx * 32));
+      const float g = __ldg(dy + (r * H + y) * (long long)W + x) * inv_temp;
+      accb += g;
 #pragma unroll
-      for (int c = 0; c < 8; ++c) acc[t][c] += g * f[c];
+      for (int kx = 0; kx < 3; ++kx) {
+        float f[8];
+        unpack8(r0[kx], f);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[kx][c] += g * f[c];
+        unpack8(r1[kx], f);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[3 + kx][c] += g * f[c];
+        unpack8(r2[kx], f);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[6 + kx][c] += g * f[c];
+      }
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) { r0[kx] = r1[kx]; r1[kx] = r2[kx]; }
     }
   }
-  __shared__ float red[8][3 * 32 + 1];
+  __shared__ float red[8][9 * 32 + 1];
 #pragma unroll
-  for (int t = 0; t < 3; ++t)
+  for (int t = 0; t < 9; ++t)
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
       float a = acc[t][c];
@@ -618,13 +652,12 @@ conv_c32_1_wgrad_kernel(const float* __restrict__ dy, const __nv_bfloat16* __res
   accb += __shfl_xor_sync(0xffffffffu, accb, 4);
   accb += __shfl_xor_sync(0xffffffffu, accb, 8);
   accb += __shfl_xor_sync(0xffffffffu, accb, 16);
-  if (lane == 0) red[wid][96] = accb;
+  if (lane == 0) red[wid][288] = accb;
   __syncthreads();
-  for (int i = threadIdx.x; i < 97; i += blockDim.x) {
-    if (i == 96 && ky != 0) continue;                           // the bias gradient is counted once
+  for (int i = threadIdx.x; i < 289; i += blockDim.x) {
     float s = 0.f;
     for (int k = 0; k < 8; ++k) s += red[k][i];
-    partial[(long long)blockIdx.x * 289 + (i == 96 ? 288 : ky * 96 + i)] = s;
+    partial[(long long)blockIdx.x * 289 + i] = s;
   }
 }
 __global__ void conv_c32_1_wreduce_kernel(const float* __restrict__ partial, int blocks, float* __restrict__ dw,
@@ -643,9 +676,11 @@ int conv_c32_1_fwd(const void* in, const float* w, const float* bias, float* out
                    cudaStream_t st) {
   if (R <= 0) return AS_OK;
   if (!in || !w || !out) return AS_EINVAL;
+  const int nseg = (H + kC32Seg - 1) / kC32Seg;
+  const long long cols = R * (long long)nseg * W;
   if (R * (long long)(H + 2) * (W + 2) >= (1LL << 31)) return AS_ESIZE;
-  conv_c32_1_fwd_kernel<<<ew_grid(R * (long long)H * W * 4, 1), 256, 0, st>>>((const __nv_bfloat16*)in, w, bias, out, R, H, W, inv_temp,
-                                                                              make_dec3(W, H, 1u << 30));
+  conv_c32_1_fwd_kernel<<<ew_grid(cols * 4, 1), 256, 0, st>>>((const __nv_bfloat16*)in, w, bias, out, R, H, W, inv_temp, nseg,
+                                                             make_dec3(W, nseg, 1u << 30));
   AS_LAUNCH_CHECK();
   return AS_OK;
 }
@@ -655,9 +690,11 @@ int conv_c32_1_bwd(const float* dy, const void* in, const float* w, void* din, f
   if (!dy || !in || !w || !din || !dw || !scratch) return AS_EINVAL;
   if (R * (long long)(H + 2) * (W + 2) >= (1LL << 31)) return AS_ESIZE;
   conv_c32_1_dgrad_kernel<<<ew_grid(R * (long long)(H + 2) * (W + 2), 1), 256, 0, st>>>(dy, w, (__nv_bfloat16*)din, R, H, W, inv_temp,
-                                                                                        make_dec3(W + 2, H + 2, 1u << 30));
+                                                                                            make_dec3(W + 2, H + 2, 1u << 30));
   AS_LAUNCH_CHECK();
-  conv_c32_1_wgrad_kernel<<<dim3(kC321Blocks, 3), 256, 0, st>>>(dy, (const __nv_bfloat16*)in, scratch, R, H, W, inv_temp, make_dec3(W, H, 1u << 30));
+  const int nseg = (H + kC32Seg - 1) / kC32Seg;
+  conv_c32_1_wgrad_kernel<<<kC321Blocks, 256, 0, st>>>(dy, (const __nv_bfloat16*)in, scratch, R, H, W, inv_temp, nseg,
+                                                       make_dec3(W, nseg, 1u << 30));
   AS_LAUNCH_CHECK();
   conv_c32_1_wreduce_kernel<<<3, 128, 0, st>>>(scratch, kC321Blocks, dw, db);
   AS_LAUNCH_CHECK();
