@@ -91,8 +91,8 @@ _SIGS = {
     'as_lnlstm_fwd': (c_int, [c_void_p] * 13 + [c_int, c_int, c_int, c_void_p]),
     'as_lnlstm_bwd': (c_int, [c_void_p] * 21 + [c_int, c_int, c_int, c_void_p]),
     'as_lnlstm_cluster_ok': (c_int, [c_int]),
-    'as_softmax_fwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p]),
-    'as_softmax_bwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
+    'as_softmax_fwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p]),
+    'as_softmax_bwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
     'as_entity_features': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int64, c_int,
                                    c_void_p, c_void_p]),
     'as_cast_f32_bf16': (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),

@@ -24,8 +24,8 @@ int layer_norm_fwd(const float*, const float*, const float*, const float*, float
 long long layer_norm_bwd_scratch_floats(int);
 int layer_norm_bwd(const float*, const void*, const float*, const float*, const float*, const float*, const float*,
                    float*, float*, float*, float*, long long, int, int, cudaStream_t);
-int softmax_fwd(const float*, const long long*, void*, long long, int, int, int, cudaStream_t);
-int softmax_bwd(const void*, const float*, void*, long long, int, cudaStream_t);
+int softmax_fwd(const void*, const long long*, void*, long long, int, int, int, int, cudaStream_t);
+int softmax_bwd(const void*, const void*, void*, long long, int, int, cudaStream_t);
 int entity_features(const void* const*, const int*, const int*, const int*, const int*, int, void*, long long, int,
                     int*, cudaStream_t);
 int nchw_to_pnhwc(const float*, void*, long long, int, int, int, int, int, cudaStream_t);
@@ -70,7 +70,7 @@ int maxpool2_bwd(const void*, const void*, void*, long long, int, int, int, cuda
 
 extern "C" {
 
-int as_abi_version(void) { return 3; }
+int as_abi_version(void) { return 4; }
 
 // diagnostics only (not part of the public header): 0 normal, 1 GEMM epilogue skips global stores, 2 only drains TMEM
 // bit 3: register-store epilogue, bit 4: per-tap convolution mode
@@ -291,14 +291,15 @@ int as_lnlstm_cluster_ok(int H) { return as::lnlstm_cluster_ok(H) ? 1 : 0; }
 int as_debug_lstm_max_clusters(int H) { return as::lnlstm_cluster_max_active(H); }
 int as_debug_lstm_profile(void* buf) { return as::lnlstm_set_profile(reinterpret_cast<long long*>(buf)); }
 
-int as_softmax_fwd(const float* scores, const int64_t* key_len, void* probs, int64_t groups, int Nq, int Nk,
-                   int groups_per_len, void* stream) {
+int as_softmax_fwd(const void* scores, const int64_t* key_len, void* probs, int64_t groups, int Nq, int Nk,
+                   int groups_per_len, int scores_bf16, void* stream) {
   return as::softmax_fwd(scores, reinterpret_cast<const long long*>(key_len), probs, groups, Nq, Nk, groups_per_len,
-                         ST(stream));
+                         scores_bf16, ST(stream));
 }
 
-int as_softmax_bwd(const void* probs, const float* dprobs, void* dscores, int64_t rows, int Nk, void* stream) {
-  return as::softmax_bwd(probs, dprobs, dscores, rows, Nk, ST(stream));
+int as_softmax_bwd(const void* probs, const void* dprobs, void* dscores, int64_t rows, int Nk, int dprobs_bf16,
+                   void* stream) {
+  return as::softmax_bwd(probs, dprobs, dscores, rows, Nk, dprobs_bf16, ST(stream));
 }
 
 int as_entity_features(const void* const* data, const int* kind, const int* num, const int* col, const int* dtype,

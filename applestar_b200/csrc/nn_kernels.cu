@@ -377,9 +377,12 @@ int layer_norm_bwd(const float* dy32, const void* dy16, const float* x, const fl
 // ------------------------------------------------------------------------------------------ masked softmax
 // scores [G, Nq, Nk] fp32 (already scaled), key j of group g is valid iff j < key_len[g / groups_per_len]
 // (NULL = all valid) -> probabilities bf16, masked keys exactly 0 (== exp(-1e9 - max) in the reference).
-template <int PER_LANE>
+__device__ __forceinline__ float ld_score(const float* p) { return __ldg(p); }
+__device__ __forceinline__ float ld_score(const __nv_bfloat16* p) { return __bfloat162float(*p); }
+
+template <int PER_LANE, typename ST>
 __global__ void __launch_bounds__(256)
-softmax_fwd_kernel(const float* __restrict__ s, const long long* __restrict__ key_len, __nv_bfloat16* __restrict__ p,
+softmax_fwd_kernel(const ST* __restrict__ s, const long long* __restrict__ key_len, __nv_bfloat16* __restrict__ p,
                    long long rows, int Nq, int Nk, int groups_per_len) {
   const int lane = threadIdx.x & 31;
   const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -395,7 +398,7 @@ softmax_fwd_kernel(const float* __restrict__ s, const long long* __restrict__ ke
 #pragma unroll
     for (int i = 0; i < PER_LANE; ++i) {
       const int c = lane + i * 32;
-      v[i] = (c < len) ? __ldg(s + row * Nk + c) : -INFINITY;
+      v[i] = (c < len) ? ld_score(s + row * Nk + c) : -INFINITY;
       m = fmaxf(m, v[i]);
     }
     m = warp_max(m);
@@ -416,9 +419,9 @@ softmax_fwd_kernel(const float* __restrict__ s, const long long* __restrict__ ke
 }
 
 // ds = p * (dp - sum_j dp_j p_j)   (bf16 out; the 1/sqrt(d) scale is folded into the following GEMMs)
-template <int PER_LANE>
+template <int PER_LANE, typename ST>
 __global__ void __launch_bounds__(256)
-softmax_bwd_kernel(const __nv_bfloat16* __restrict__ p, const float* __restrict__ dp, __nv_bfloat16* __restrict__ ds,
+softmax_bwd_kernel(const __nv_bfloat16* __restrict__ p, const ST* __restrict__ dp, __nv_bfloat16* __restrict__ ds,
                    long long rows, int Nk) {
   const int lane = threadIdx.x & 31;
   const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -430,7 +433,7 @@ softmax_bwd_kernel(const __nv_bfloat16* __restrict__ p, const float* __restrict_
     for (int i = 0; i < PER_LANE; ++i) {
       const int c = lane + i * 32;
       pv[i] = (c < Nk) ? __bfloat162float(p[row * Nk + c]) : 0.f;
-      dv[i] = (c < Nk) ? __ldg(dp + row * Nk + c) : 0.f;
+      dv[i] = (c < Nk) ? ld_score(dp + row * Nk + c) : 0.f;
       dot += pv[i] * dv[i];
     }
     dot = warp_sum(dot);
@@ -442,34 +445,36 @@ softmax_bwd_kernel(const __nv_bfloat16* __restrict__ p, const float* __restrict_
   }
 }
 
-#define SM_DISPATCH(KERNEL, ...)                                        \
-  do {                                                                  \
-    const int per = (Nk + 31) / 32;                                     \
-    if (per <= 1) KERNEL<1><<<grid, 256, 0, st>>>(__VA_ARGS__);         \
-    else if (per <= 4) KERNEL<4><<<grid, 256, 0, st>>>(__VA_ARGS__);    \
-    else if (per <= 8) KERNEL<8><<<grid, 256, 0, st>>>(__VA_ARGS__);    \
-    else if (per <= 16) KERNEL<16><<<grid, 256, 0, st>>>(__VA_ARGS__);  \
-    else KERNEL<32><<<grid, 256, 0, st>>>(__VA_ARGS__);                 \
+#define SM_DISPATCH(KERNEL, ST, ...)                                        \
+  do {                                                                      \
+    const int per = (Nk + 31) / 32;                                         \
+    if (per <= 1) KERNEL<1, ST><<<grid, 256, 0, st>>>(__VA_ARGS__);         \
+    else if (per <= 4) KERNEL<4, ST><<<grid, 256, 0, st>>>(__VA_ARGS__);    \
+    else if (per <= 8) KERNEL<8, ST><<<grid, 256, 0, st>>>(__VA_ARGS__);    \
+    else if (per <= 16) KERNEL<16, ST><<<grid, 256, 0, st>>>(__VA_ARGS__);  \
+    else KERNEL<32, ST><<<grid, 256, 0, st>>>(__VA_ARGS__);                 \
   } while (0)
 
-int softmax_fwd(const float* s, const long long* key_len, void* p, long long groups, int Nq, int Nk,
-                int groups_per_len, cudaStream_t st) {
+int softmax_fwd(const void* s, const long long* key_len, void* p, long long groups, int Nq, int Nk,
+                int groups_per_len, int scores_bf16, cudaStream_t st) {
   const long long rows = groups * Nq;
   if (rows <= 0) return AS_OK;
   if (Nk <= 0 || Nk > 1024 || groups_per_len <= 0) return AS_ESIZE;
   if (!s || !p) return AS_EINVAL;
   const int grid = ln_grid(rows);
-  SM_DISPATCH(softmax_fwd_kernel, s, key_len, reinterpret_cast<__nv_bfloat16*>(p), rows, Nq, Nk, groups_per_len);
+  if (scores_bf16) SM_DISPATCH(softmax_fwd_kernel, __nv_bfloat16, reinterpret_cast<const __nv_bfloat16*>(s), key_len, reinterpret_cast<__nv_bfloat16*>(p), rows, Nq, Nk, groups_per_len);
+  else SM_DISPATCH(softmax_fwd_kernel, float, reinterpret_cast<const float*>(s), key_len, reinterpret_cast<__nv_bfloat16*>(p), rows, Nq, Nk, groups_per_len);
   AS_LAUNCH_CHECK();
   return AS_OK;
 }
 
-int softmax_bwd(const void* p, const float* dp, void* ds, long long rows, int Nk, cudaStream_t st) {
+int softmax_bwd(const void* p, const void* dp, void* ds, long long rows, int Nk, int dprobs_bf16, cudaStream_t st) {
   if (rows <= 0) return AS_OK;
   if (Nk <= 0 || Nk > 1024) return AS_ESIZE;
   if (!p || !dp || !ds) return AS_EINVAL;
   const int grid = ln_grid(rows);
-  SM_DISPATCH(softmax_bwd_kernel, reinterpret_cast<const __nv_bfloat16*>(p), dp, reinterpret_cast<__nv_bfloat16*>(ds), rows, Nk);
+  if (dprobs_bf16) SM_DISPATCH(softmax_bwd_kernel, __nv_bfloat16, reinterpret_cast<const __nv_bfloat16*>(p), reinterpret_cast<const __nv_bfloat16*>(dp), reinterpret_cast<__nv_bfloat16*>(ds), rows, Nk);
+  else SM_DISPATCH(softmax_bwd_kernel, float, reinterpret_cast<const __nv_bfloat16*>(p), reinterpret_cast<const float*>(dp), reinterpret_cast<__nv_bfloat16*>(ds), rows, Nk);
   AS_LAUNCH_CHECK();
   return AS_OK;
 }

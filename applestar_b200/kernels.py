@@ -4,6 +4,7 @@ Tensors stay torch tensors only so that torch owns device memory, streams and th
 function here hands raw `data_ptr()`s to `libapplestar_b200.so` on `torch.cuda.current_stream()`.
 """
 import math
+import os
 
 import torch
 import torch.nn.functional as F
@@ -298,6 +299,11 @@ def layer_norm_dual(x, weight, bias, residual=None, relu=False):
     return LayerNormFn.apply(x, residual, weight, bias, relu, True, True)
 
 
+# dtype of the materialised attention scores S = QK^T/sqrt(d) and of dP = dO V^T.  fp32 keeps the reference's fp32
+# scores; bf16 (what the reference's own autocast path stores) halves the HBM traffic of four passes per layer.
+SCORE_DTYPE = torch.bfloat16 if os.environ.get('APPLESTAR_ATTN_BF16_SCORES', '1') == '1' else torch.float32
+
+
 class AttentionFn(torch.autograd.Function):
     """softmax(Q K^T / sqrt(d), keys >= key_len masked) V over a packed bf16 qkv buffer [R, N, 3*H*D].
     Q K^T, P V and the four backward products are batched tcgen05 GEMMs reading Q/K/V (and dO) in place through
@@ -312,7 +318,7 @@ class AttentionFn(torch.autograd.Function):
         q, k, v = qkv[:, :, :H * D], qkv[:, :, H * D:2 * H * D], qkv[:, :, 2 * H * D:]
         scale = 1.0 / math.sqrt(D)
         Np = (N + 7) // 8 * 8                       # pitch of the score rows (bf16 P must be 16-byte pitched)
-        S = torch.empty((R, H, N, Np), dtype=torch.float32, device=qkv.device)
+        S = torch.empty((R, H, N, Np), dtype=SCORE_DTYPE, device=qkv.device)
         gemm(q, k, S, N, N, D, lda=ld, ldb=ld, ldc=Np, batch=(H, R), a_strides=(D, N * ld), b_strides=(D, N * ld),
              c_strides=(N * Np, H * N * Np), alpha=scale)
         P = torch.empty((R, H, N, Np), dtype=torch.bfloat16, device=qkv.device)
@@ -340,7 +346,7 @@ class AttentionFn(torch.autograd.Function):
         sP, sO = (N * Np, H * N * Np), (D, N * H * D)
         sQ = (D, N * ld)
         # dP = dO V^T
-        dP = torch.empty((R, H, N, Np), dtype=torch.float32, device=qkv.device)
+        dP = torch.empty((R, H, N, Np), dtype=SCORE_DTYPE, device=qkv.device)
         gemm(dO, v, dP, N, N, D, lda=H * D, ldb=ld, ldc=Np, batch=(H, R), a_strides=sO, b_strides=sQ, c_strides=sP)
         # dV = P^T dO   (both operands MN-major)
         gemm(P, dO, dv, N, D, N, a_mn=True, lda=Np, b_mn=True, ldb=H * D, ldc=ld, batch=(H, R), a_strides=sP,
@@ -360,16 +366,17 @@ class AttentionFn(torch.autograd.Function):
 def _softmax_rows(S, key_len, P, groups, Nq, Nk, pitch, groups_per_len):
     if pitch == Nk:
         _lib.call('as_softmax_fwd', S.data_ptr(), _ptr(key_len), P.data_ptr(), groups, Nq, Nk, groups_per_len,
-                  _lib.stream_ptr())
+                  int(S.dtype == torch.bfloat16), _lib.stream_ptr())
     else:   # padded pitch: treat the pad columns as masked keys
         kl = key_len if key_len is not None else torch.full((groups // groups_per_len,), Nk, dtype=torch.int64,
                                                             device=S.device)
         _lib.call('as_softmax_fwd', S.data_ptr(), kl.data_ptr(), P.data_ptr(), groups, Nq, pitch, groups_per_len,
-                  _lib.stream_ptr())
+                  int(S.dtype == torch.bfloat16), _lib.stream_ptr())
 
 
 def _softmax_bwd_rows(P, dP, dS, rows, Nk, pitch):
-    _lib.call('as_softmax_bwd', P.data_ptr(), dP.data_ptr(), dS.data_ptr(), rows, pitch, _lib.stream_ptr())
+    _lib.call('as_softmax_bwd', P.data_ptr(), dP.data_ptr(), dS.data_ptr(), rows, pitch, int(dP.dtype == torch.bfloat16),
+              _lib.stream_ptr())
 
 
 def attention(qkv, key_len, heads, head_dim):

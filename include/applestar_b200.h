@@ -189,12 +189,14 @@ int as_lnlstm_bwd(const float* gi, const float* h0, const float* c0, const float
 int as_lnlstm_cluster_ok(int H);
 
 /* Masked attention softmax with warp-shuffle reductions -- replaces masked_fill_ + F.softmax at
- * module_utils.py:100-104.  scores [groups, Nq, Nk] fp32 (already scaled by 1/sqrt(d)); key j of group g is valid
- * iff j < key_len[g / groups_per_len] (key_len NULL = no mask); probs bf16 with masked keys exactly 0.  Nk <= 1024. */
-int as_softmax_fwd(const float* scores, const int64_t* key_len, void* probs, int64_t groups, int Nq, int Nk,
-                   int groups_per_len, void* stream);
-/* dscores (bf16) = probs * (dprobs - rowsum(dprobs * probs)). */
-int as_softmax_bwd(const void* probs, const float* dprobs, void* dscores, int64_t rows, int Nk, void* stream);
+ * module_utils.py:100-104.  scores [groups, Nq, Nk] fp32 or bf16 (scores_bf16 = 1; already scaled by 1/sqrt(d)); key j
+ * of group g is valid iff j < key_len[g / groups_per_len] (key_len NULL = no mask); probs bf16 with masked keys
+ * exactly 0.  Nk <= 1024.  The arithmetic is fp32 either way. */
+int as_softmax_fwd(const void* scores, const int64_t* key_len, void* probs, int64_t groups, int Nq, int Nk,
+                   int groups_per_len, int scores_bf16, void* stream);
+/* dscores (bf16) = probs * (dprobs - rowsum(dprobs * probs)); dprobs fp32 or bf16 (dprobs_bf16 = 1). */
+int as_softmax_bwd(const void* probs, const void* dprobs, void* dscores, int64_t rows, int Nk, int dprobs_bf16,
+                   void* stream);
 
 /* bf16 feature rows for the entity embedding GEMM -- replaces the 28 embedding lookups + torch.cat at
  * obs_encoder/entity_encoder.py:60-78.  Per field f: data[f] = device array [rows] of element type dtype[f]
