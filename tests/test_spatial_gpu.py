@@ -41,7 +41,8 @@ def test_layout_round_trip_and_channel_pad():
 
 
 @pytest.mark.parametrize('cin,cout,k,H,W', [(128, 128, 3, 19, 20), (128, 64, 3, 38, 40), (64, 32, 3, 76, 80),
-                                             (128, 128, 1, 19, 20)])
+                                             (128, 128, 1, 19, 20), (32, 64, 3, 76, 80), (64, 128, 3, 38, 40),
+                                             (192, 128, 3, 19, 20), (32, 32, 3, 11, 14)])
 def test_conv_nhwc_forward_backward(cin, cout, k, H, W):
     from applestar_b200 import spatial
     R = 3
@@ -197,3 +198,40 @@ def test_spatial_project_matches_reference_front():
     assert ((pd.grad.cpu() - pr.grad).norm() / pr.grad.norm()).item() < 0.05
     assert ((wd.grad.cpu() - wr.grad).norm() / wr.grad.norm()).item() < 0.05
     assert ((bd.grad.cpu() - br.grad).norm() / br.grad.norm()).item() < 0.05
+
+
+@pytest.mark.parametrize('rows,C', [(1000, 256), (4097, 40), (77, 128), (25000, 32)])
+@pytest.mark.parametrize('ykind', ['none', 'f32', 'bf16'])
+def test_linear_bwd_prep(rows, C, ykind):
+    """as_linear_bwd_prep: bf16(dy * (y > 0)) bit-exact, bias gradient = fp32 column sums of the masked gradient."""
+    from applestar_b200 import _lib
+    dy = _rand((rows, C), 41)
+    y = torch.relu(_rand((rows, C), 42))
+    y32 = y if ykind == 'f32' else None
+    y16 = y.to(torch.bfloat16) if ykind == 'bf16' else None
+    dz = torch.empty((rows, C), dtype=torch.bfloat16, device='cuda')
+    db = torch.empty(C, dtype=torch.float32, device='cuda')
+    scratch = torch.empty(_lib.lib().as_colsum_scratch_floats(C), dtype=torch.float32, device='cuda')
+    _lib.call('as_linear_bwd_prep', dy.data_ptr(), 0 if y32 is None else y32.data_ptr(), 0 if y16 is None else y16.data_ptr(),
+              dz.data_ptr(), db.data_ptr(), scratch.data_ptr(), rows, C, _lib.stream_ptr())
+    mask = torch.ones_like(dy, dtype=torch.bool) if ykind == 'none' else ((y32 if y32 is not None else y16.float()) > 0)
+    want = dy * mask
+    assert torch.equal(dz, want.to(torch.bfloat16))
+    ref = want.double().sum(0)
+    assert (db.double() - ref).abs().max().item() <= 1e-5 * want.abs().sum(0).max().item() + 1e-5
+
+
+@pytest.mark.parametrize('rows,C', [(480480 // 8, 128), (12345, 32), (999, 64)])
+def test_relu_bwd_colsum_bf16(rows, C):
+    from applestar_b200 import _lib
+    dy = _rand((rows, C), 43).to(torch.bfloat16)
+    y = torch.relu(_rand((rows, C), 44)).to(torch.bfloat16)
+    dz = torch.empty_like(dy)
+    db = torch.empty(C, dtype=torch.float32, device='cuda')
+    scratch = torch.empty(_lib.lib().as_colsum_scratch_floats(C), dtype=torch.float32, device='cuda')
+    _lib.call('as_relu_bwd_colsum_bf16', dy.data_ptr(), y.data_ptr(), dz.data_ptr(), db.data_ptr(), scratch.data_ptr(),
+              rows, C, _lib.stream_ptr())
+    want = torch.where(y.float() > 0, dy, torch.zeros_like(dy))
+    assert torch.equal(dz, want)
+    ref = want.double().sum(0)
+    assert (db.double() - ref).abs().max().item() <= 1e-5 * want.float().abs().sum(0).max().item() + 1e-5
