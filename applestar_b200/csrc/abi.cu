@@ -7,6 +7,7 @@ namespace as {
 extern int g_gemm_debug;
 extern int g_gemm_no_tma_store;
 extern int g_gemm_no_slab;
+int gemm_set_profile(long long*);
 int scatter_fwd(const float*, const void*, const void*, int, const long long*, float*, long long, int, int, int, int,
                 int, cudaStream_t);
 int scatter_bwd(const float*, const void*, const void*, int, const long long*, float*, long long, int, int, int, int,
@@ -288,6 +289,7 @@ int as_lnlstm_bwd(const float* gi, const float* h0, const float* c0, const float
 }
 int as_lnlstm_cluster_ok(int H) { return as::lnlstm_cluster_ok(H) ? 1 : 0; }
 // diagnostics only (not part of the public header)
+int as_debug_gemm_profile(void* buf) { return as::gemm_set_profile(reinterpret_cast<long long*>(buf)); }
 int as_debug_lstm_max_clusters(int H) { return as::lnlstm_cluster_max_active(H); }
 int as_debug_lstm_profile(void* buf) { return as::lnlstm_set_profile(reinterpret_cast<long long*>(buf)); }
 

@@ -136,6 +136,27 @@ __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bu
 // make generic-proxy shared-memory writes visible to the async proxy (TMA) before a bulk store reads them
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// multicast variant: the box lands at the same CTA-relative offset in every CTA of `mask`, and each destination CTA's
+// mbarrier (same offset) receives the complete_tx
+__device__ __forceinline__ void tma_load_4d_mc(void* smem_dst, const CUtensorMap* tm, uint64_t* bar, int c0, int c1,
+                                               int c2, int c3, uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], %7;"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2),
+      "r"(c3), "h"(mask)
+      : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
 // ---------------------------------------------------------------- tcgen05 / TMEM
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)),
@@ -166,12 +187,24 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint
 // for small tiles.
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate);
 __device__ __forceinline__ void umma_commit(uint64_t* bar);
+// elect_one() (elect.sync): true in exactly one lane of a converged warp; ptxas knows that the guarded block runs in a
+// single thread
 __device__ __forceinline__ void umma_bf16_lead(uint32_t leader, uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
                                                uint32_t idesc, uint32_t accumulate) {
-  if (leader) umma_bf16(tmem_d, desc_a, desc_b, idesc, accumulate);
+  (void)leader;
+  if (elect_one()) umma_bf16(tmem_d, desc_a, desc_b, idesc, accumulate);
 }
 __device__ __forceinline__ void umma_commit_lead(uint32_t leader, uint64_t* bar) {
-  if (leader) umma_commit(bar);
+  (void)leader;
+  if (elect_one()) umma_commit(bar);
+}
+// arrive on the mbarrier at this offset in every CTA of `mask` (shared operand tiles of a CTA pair)
+__device__ __forceinline__ void umma_commit_mc_lead(uint32_t leader, uint64_t* bar, uint16_t mask) {
+  (void)leader;
+  if (elect_one())
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"(mask)
+                 : "memory");
 }
 // arrive on an mbarrier once all previously issued tcgen05.mma of this thread have completed
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {

@@ -40,6 +40,7 @@ struct GemmDev {
   int wgrad_taps;    // >0: batch index b0 = conv tap; A and B are shared by all taps, B rows shifted by shift[b0]
   // slab mode (multi-tap conv): 256-row steps, A slab = 2 TMA boxes of slab_box rows starting at row m0 - halo
   int slab, halo, slab_box, slab_bytes, slab_slots, b_slots, tpb, b_resident;
+  int mc;            // slab ring mode on CTA pairs: each CTA loads half of every weight tile and multicasts it to both
   // epilogue
   void* C;
   void* C2;   // optional bf16 copy of the output (same ldc / batch strides)
@@ -52,6 +53,9 @@ struct GemmDev {
   int tma_store;   // 1: C (and C2) are written with TMA bulk stores from a swizzled staging tile
   int debug;  // diagnostics: 1 = epilogue skips global stores, 2 = epilogue only drains TMEM
 };
+
+// diagnostics: cycles the slab-mode MMA issuer spends in each wait (as_debug_gemm_profile); nullptr normally
+__device__ long long* g_gemm_prof = nullptr;
 
 template <int BN>
 struct SmemLayout {
@@ -69,7 +73,8 @@ struct SmemLayout {
 template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-            const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2, const GemmDev p) {
+            const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2,
+            const __grid_constant__ CUtensorMap tmB2, const GemmDev p) {
   using L = SmemLayout<BN>;
   constexpr int kStages = L::kStages;
   // accumulator ring in TMEM: narrow tiles have few k-blocks per tile, so the MMA issuer may run up to 8 tiles ahead
@@ -102,7 +107,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kStages; ++i) {
       mbar_init(&full_bar[i], 1);
-      mbar_init(&empty_bar[i], 1);
+      mbar_init(&empty_bar[i], p.mc ? 2 : 1);       // CTA pair: a weight slot is free when BOTH issuers are done with it
     }
     for (int i = 0; i < kAcc; ++i) {
       mbar_init(&tmem_full[i], 1);
@@ -117,6 +122,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   if (warp == 2) tmem_alloc(tmem_slot, kTmemCols);
   tc_fence_before();
   __syncthreads();
+  if (p.mc) cluster_sync_all();                     // the peer's barriers are initialised before anything targets them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -126,7 +132,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
   // slab mode: work item = (n block, pair of m blocks); shared memory = the A slabs followed by the weight tiles
   // (a ring of per-tap tiles, or -- when they all fit -- every tile of the convolution, loaded once)
-  const long long num_work = p.slab ? (long long)((p.m_blocks + 1) / 2) * p.n_blocks : num_tiles;
+  long long num_work = p.slab ? (long long)((p.m_blocks + 1) / 2) * p.n_blocks : num_tiles;
+  if (p.mc) num_work = (num_work + 1) & ~1LL;       // both CTAs of a pair run the same number of steps (a phantom one is all zeros)
+  const uint32_t crank = p.mc ? cluster_ctarank() : 0u;
   uint8_t* b_ring = smem + p.slab_slots * p.slab_bytes;
 
   if (warp == 0 && p.slab) {
@@ -166,8 +174,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           for (int tap = 0; tap < p.taps; tap += p.tpb) {
             mbar_wait(&empty_bar[bslot], bphase ^ 1);
             mbar_expect_tx(&full_bar[bslot], p.tpb * L::kBBytes);
-            for (int j = 0; j < p.tpb; ++j)
-              tma_load_4d(b_ring + (bslot * p.tpb + j) * L::kBBytes, &tmB, &full_bar[bslot], (tap + j) * p.cin + cb * BK, n0, 0, 0);
+            for (int j = 0; j < p.tpb; ++j) {
+              uint8_t* dstb = b_ring + (bslot * p.tpb + j) * L::kBBytes;
+              const int kc = (tap + j) * p.cin + cb * BK;
+              if (p.mc)   // this CTA's half of the tile (rows crank*BN/2 ..) goes to both CTAs of the pair
+                tma_load_4d_mc(dstb + crank * (L::kBBytes / 2), &tmB2, &full_bar[bslot], kc, n0 + (int)crank * (BN / 2), 0, 0, (uint16_t)3);
+              else
+                tma_load_4d(dstb, &tmB, &full_bar[bslot], kc, n0, 0, 0);
+            }
             if (++bslot == p.b_slots) { bslot = 0; bphase ^= 1; }
           }
         }
@@ -188,16 +202,22 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       long long ci = 0;
       uint32_t it2 = 0;
       if (p.b_resident) { mbar_wait(&full_bar[0], 0); tc_fence_after(); }
+      long long* prof = g_gemm_prof;
+      long long t_acc = 0, t_slab = 0, t_b = 0, t_all = prof ? clock64() : 0, tk;
       for (long long w = blockIdx.x; w < num_work; w += gridDim.x, ++it2) {
         const int acc0 = (int)((2 * it2) % kAcc);
         const uint32_t acc_phase = ((2 * it2) / kAcc) & 1u;
+        if (prof) tk = clock64();
         mbar_wait(&tmem_empty[acc0], acc_phase ^ 1);
         mbar_wait(&tmem_empty[acc0 + 1], acc_phase ^ 1);
+        if (prof) t_acc += clock64() - tk;
         tc_fence_after();
         const uint32_t d0 = __shfl_sync(0xffffffffu, tmem_base + (uint32_t)(acc0 * BN), 0);
         for (int cb = 0; cb < p.cin_blocks; ++cb, ++ci) {
           const int sl = (int)(ci % nsl);
+          if (prof) tk = clock64();
           mbar_wait(&slab_full[sl], (uint32_t)((ci / nsl) & 1));
+          if (prof) t_slab += clock64() - tk;
           tc_fence_after();
           const uint32_t slab_lo = kDescLbo | ((smem_u32(smem + sl * p.slab_bytes) >> 4) + (uint32_t)(p.halo * 8));
           for (int tap = 0; tap < p.taps; tap += p.tpb) {
@@ -205,7 +225,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             if (p.b_resident) {
               b_lo = kDescLbo | (smem_u32(b_ring + (cb * p.taps + tap) * L::kBBytes) >> 4);
             } else {
+              if (prof) tk = clock64();
               mbar_wait(&full_bar[bslot], bphase);
+              if (prof) t_b += clock64() - tk;
               tc_fence_after();
               b_lo = kDescLbo | (smem_u32(b_ring + bslot * p.tpb * L::kBBytes) >> 4);
             }
@@ -227,7 +249,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               }
             }
             if (!p.b_resident) {
-              umma_commit_lead(leader, &empty_bar[bslot]);
+              if (p.mc) umma_commit_mc_lead(leader, &empty_bar[bslot], (uint16_t)3);
+              else umma_commit_lead(leader, &empty_bar[bslot]);
               if (++bslot == p.b_slots) { bslot = 0; bphase ^= 1; }
             }
           }
@@ -235,6 +258,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
         umma_commit_lead(leader, &tmem_full[acc0]);
         umma_commit_lead(leader, &tmem_full[acc0 + 1]);
+      }
+      if (prof && lane == 0) {
+        prof[blockIdx.x * 4 + 0] = clock64() - t_all; prof[blockIdx.x * 4 + 1] = t_acc;
+        prof[blockIdx.x * 4 + 2] = t_slab; prof[blockIdx.x * 4 + 3] = t_b;
       }
     }
   } else if (warp == 0) {
@@ -429,7 +456,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
           if (p.debug < 3) fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0 && p.debug == 0) {
+          if (lane == 0 && p.debug == 0 && row_base < p.M) {
             tma_store_4d(&tmC, sbuf, n0 + c, row_base, b0, b1);
             tma_store_commit();
           }
@@ -493,7 +520,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
             if (p.debug < 3) fence_proxy_async_smem();
             __syncwarp();
-            if (lane == 0 && p.debug == 0) {
+            if (lane == 0 && p.debug == 0 && row_base < p.M) {
               tma_store_4d(map16, sbuf, n0 + col, row_base, b0, b1);
               tma_store_commit();
             }
@@ -625,6 +652,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   if (warp >= 4 && lane == 0) tma_store_wait_all();     // bulk stores must have drained before shared memory goes away
   tc_fence_before();
   __syncthreads();
+  if (p.mc) cluster_sync_all();                          // the peer may still multicast into / arrive on this CTA
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, kTmemCols);
@@ -680,7 +708,7 @@ static int num_sms() {
 
 template <int BN, bool A_MN, bool B_MN>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const CUtensorMap& tc2,
-                  const GemmDev& p, cudaStream_t st) {
+                  const CUtensorMap& tb2, const GemmDev& p, cudaStream_t st) {
   using L = SmemLayout<BN>;
   static bool attr_set = false;
   auto kern = gemm_kernel<BN, A_MN, B_MN>;
@@ -693,18 +721,35 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMa
   if (p.slab) tiles = (long long)((p.m_blocks + 1) / 2) * p.n_blocks;
   int grid = (int)(tiles < num_sms() ? tiles : num_sms());
   if (grid <= 0) return AS_OK;
-  kern<<<grid, kGemmThreads, L::kTotal, st>>>(ta, tb, tc, tc2, p);
+  if (p.mc) {
+    // CTA pairs (thread-block clusters of 2): blockIdx.x = 2 * pair + rank, both ranks walk the step list in lockstep
+    grid = (int)(((tiles + 1) & ~1LL) < num_sms() ? ((tiles + 1) & ~1LL) : (num_sms() & ~1));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = L::kTotal;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, tc2, tb2, p);
+    if (e != cudaSuccess) return (int)e;
+    return AS_OK;
+  }
+  kern<<<grid, kGemmThreads, L::kTotal, st>>>(ta, tb, tc, tc2, tb2, p);
   AS_LAUNCH_CHECK();
   return AS_OK;
 }
 
 template <int BN>
 static int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
-                          const CUtensorMap& tc2, const GemmDev& p, cudaStream_t st) {
-  if (!a_mn && !b_mn) return launch<BN, false, false>(ta, tb, tc, tc2, p, st);
-  if (!a_mn && b_mn) return launch<BN, false, true>(ta, tb, tc, tc2, p, st);
-  if (a_mn && !b_mn) return launch<BN, true, false>(ta, tb, tc, tc2, p, st);
-  return launch<BN, true, true>(ta, tb, tc, tc2, p, st);
+                          const CUtensorMap& tc2, const CUtensorMap& tb2, const GemmDev& p, cudaStream_t st) {
+  if (!a_mn && !b_mn) return launch<BN, false, false>(ta, tb, tc, tc2, tb2, p, st);
+  if (!a_mn && b_mn) return launch<BN, false, true>(ta, tb, tc, tc2, tb2, p, st);
+  if (a_mn && !b_mn) return launch<BN, true, false>(ta, tb, tc, tc2, tb2, p, st);
+  return launch<BN, true, true>(ta, tb, tc, tc2, tb2, p, st);
 }
 
 static int pick_bn(int N, bool b_mn) {
@@ -714,6 +759,8 @@ static int pick_bn(int N, bool b_mn) {
   if (N > 32) return 64;
   return 32;
 }
+
+int gemm_set_profile(long long* buf) { return (int)cudaMemcpyToSymbol(g_gemm_prof, &buf, sizeof(buf)); }
 
 int g_gemm_debug = 0;
 int g_gemm_no_tma_store = 0;
@@ -783,6 +830,8 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
         if (slots > max_slots) slots = max_slots;
         if (const char* e = getenv("AS_SLAB_BSLOTS")) { const int v = atoi(e); if (v >= 2 && v < slots) slots = v; }
         if (slots >= 2) { p.slab = 1; p.slab_slots = 3; p.b_resident = 0; p.tpb = tpb; p.b_slots = slots; }
+        // weight multicast across a CTA pair: halves the L2 -> SM weight stream that bounds the 128-channel convs
+        if (p.slab && p.n_blocks == 1 && BN >= 64 && (p.m_blocks + 1) / 2 >= 2 && !getenv("AS_SLAB_NO_MC")) p.mc = 1;
       }
       if (p.slab) { p.halo = halo; p.slab_box = box; p.slab_bytes = slab_bytes; a_box_rows = box; }
     }
@@ -798,6 +847,11 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
   if (g.b_mn) rc = make_map(&tb, g.B, g.N, k_total_b, g.ldb, onb0, g.b_sb0, g.nb1, g.b_sb1, 64, BK);
   else rc = make_map(&tb, g.B, k_total_b, g.N, g.ldb, onb0, g.b_sb0, g.nb1, g.b_sb1, BK, BN);
   if (rc) return rc;
+  CUtensorMap tb2 = tb;                              // half-tile box for the multicast loads of a CTA pair
+  if (p.mc) {
+    rc = make_map(&tb2, g.B, k_total_b, g.N, g.ldb, onb0, g.b_sb0, g.nb1, g.b_sb1, BK, BN / 2);
+    if (rc) return rc;
+  }
   // output tensor maps for the TMA-store epilogue (fall back to register stores when C is not 16-byte pitched)
   CUtensorMap tc = ta, tc2 = ta;
   p.tma_store = 0;
@@ -812,10 +866,10 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
     p.tma_store = ok;
   }
   switch (BN) {
-    case 32: return dispatch_major<32>(g.a_mn, g.b_mn, ta, tb, tc, tc2, p, st);
-    case 64: return dispatch_major<64>(g.a_mn, g.b_mn, ta, tb, tc, tc2, p, st);
-    case 128: return dispatch_major<128>(g.a_mn, g.b_mn, ta, tb, tc, tc2, p, st);
-    case 256: return dispatch_major<256>(g.a_mn, g.b_mn, ta, tb, tc, tc2, p, st);
+    case 32: return dispatch_major<32>(g.a_mn, g.b_mn, ta, tb, tc, tc2, tb2, p, st);
+    case 64: return dispatch_major<64>(g.a_mn, g.b_mn, ta, tb, tc, tc2, tb2, p, st);
+    case 128: return dispatch_major<128>(g.a_mn, g.b_mn, ta, tb, tc, tc2, tb2, p, st);
+    case 256: return dispatch_major<256>(g.a_mn, g.b_mn, ta, tb, tc, tc2, tb2, p, st);
   }
   return AS_EUNSUPPORTED;
 }

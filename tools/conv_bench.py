@@ -17,7 +17,7 @@ def bench(x, w, b, iters=10):
             spatial.conv(x, w, b, relu=True)
         e1.record(); torch.cuda.synchronize()
     return e0.elapsed_time(e1) / iters
-variants = [('slab', 0, {}), ('slab ring', 0, {'AS_SLAB_NO_RESIDENT': '1'}), ('slab ring 3 slots', 0, {'AS_SLAB_NO_RESIDENT': '1', 'AS_SLAB_BSLOTS': '3'}),
+variants = [('slab', 0, {}), ('slab no-multicast', 0, {'AS_SLAB_NO_MC': '1'}),
             ('per-tap', 16, {})]
 for (R, H, W, Cin, Cout, k) in [(1040, 19, 20, 128, 128, 3), (1024, 38, 40, 128, 64, 3), (1024, 38, 40, 64, 128, 3), (1040, 76, 80, 64, 32, 3), (1040, 76, 80, 32, 64, 3)]:
     x = torch.randn(R, H + 2, W + 2, Cin, device='cuda').to(torch.bfloat16)
@@ -27,7 +27,7 @@ for (R, H, W, Cin, Cout, k) in [(1040, 19, 20, 128, 128, 3), (1024, 38, 40, 128,
     fl = 2.0 * R * (H + 2) * (W + 2) * Cin * Cout * k * k
     out = []
     for name, mode, env in variants:
-        for kk in ('AS_SLAB_NO_RESIDENT', 'AS_SLAB_BSLOTS'):
+        for kk in ('AS_SLAB_NO_RESIDENT', 'AS_SLAB_BSLOTS', 'AS_SLAB_NO_MC'):
             os.environ.pop(kk, None)
         os.environ.update(env)
         lib.as_debug_gemm_mode(mode)
