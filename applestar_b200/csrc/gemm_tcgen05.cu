@@ -830,8 +830,9 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
         if (slots > max_slots) slots = max_slots;
         if (const char* e = getenv("AS_SLAB_BSLOTS")) { const int v = atoi(e); if (v >= 2 && v < slots) slots = v; }
         if (slots >= 2) { p.slab = 1; p.slab_slots = 3; p.b_resident = 0; p.tpb = tpb; p.b_slots = slots; }
-        // weight multicast across a CTA pair: halves the L2 -> SM weight stream that bounds the 128-channel convs
-        if (p.slab && p.n_blocks == 1 && BN >= 64 && (p.m_blocks + 1) / 2 >= 2 && !getenv("AS_SLAB_NO_MC")) p.mc = 1;
+        // weight multicast across a CTA pair halves the L2 -> SM weight stream, but measured 4 % SLOWER than independent
+        // CTAs on the 128-channel convs (the issuer, not the weight stream, is the limit there): opt-in only
+        if (p.slab && p.n_blocks == 1 && BN >= 64 && (p.m_blocks + 1) / 2 >= 2 && getenv("AS_SLAB_MC")) p.mc = 1;
       }
       if (p.slab) { p.halo = halo; p.slab_box = box; p.slab_bytes = slab_bytes; a_box_rows = box; }
     }
