@@ -238,10 +238,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               const uint32_t a_lo = __shfl_sync(0xffffffffu, slab_lo + (uint32_t)(p.shift[tap + j] * 8), 0);
               const uint32_t bj_lo = __shfl_sync(0xffffffffu, b_lo + (uint32_t)(j * (L::kBBytes >> 4)), 0);
               const uint32_t first = (cb > 0 || tap + j > 0) ? 1u : 0u;
+              // consecutive MMAs alternate between the two accumulators (no back-to-back dependent accumulation)
 #pragma unroll
-              for (int sub = 0; sub < 2; ++sub) {
+              for (int k = 0; k < BK / 16; ++k) {
 #pragma unroll
-                for (int k = 0; k < BK / 16; ++k) {
+                for (int sub = 0; sub < 2; ++sub) {
                   const uint64_t da = ((uint64_t)kDescHi << 32) | (a_lo + (uint32_t)(sub * (BM * 128 / 16) + k * 2));
                   const uint64_t db = ((uint64_t)kDescHi << 32) | (bj_lo + (uint32_t)(k * 2));
                   umma_bf16_lead(leader, d0 + (uint32_t)(sub * BN), da, db, idesc, k > 0 ? 1u : first);
