@@ -404,55 +404,95 @@ int up2_bwd(const void* dout, void* din, long long R, int H, int W, int C, cudaS
 // ------------------------------------------------------------------------------------------ location-head input
 // x1 = relu(cat[reshape(emb,[4,H,W]), skip]) (action_arg_head.py:419-422) as padded NHWC bf16 with Cp = 192 channels
 // (0-3 embedding, 4-131 skip, rest zero).  emb fp32 [R, 4*H*W] (post-ReLU), skip padded NHWC bf16 [R,H+2,W+2,128].
-__global__ void loc_cat_fwd_kernel(const float* __restrict__ emb, const __nv_bfloat16* __restrict__ skip,
-                                   __nv_bfloat16* __restrict__ out, long long R, int H, int W, int Cs, int Cp) {
-  const long long total = R * (H + 2) * (long long)(W + 2) * Cp;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int c = (int)(i % Cp);
-    long long p = i / Cp;
-    const int xx = (int)(p % (W + 2)); p /= (W + 2);
-    const int yy = (int)(p % (H + 2));
-    const long long r = p / (H + 2);
-    float v = 0.f;
+// thread = (padded pixel, group of 8 output channels): one 16-byte store; the skip channels arrive shifted by four
+// channels, i.e. as two 8-byte loads
+__global__ void __launch_bounds__(256)
+loc_cat_fwd_kernel(const float* __restrict__ emb, const __nv_bfloat16* __restrict__ skip, __nv_bfloat16* __restrict__ out,
+                   long long R, int H, int W, int Cs, int Cp, const Dec3 dec) {
+  const int G = Cp / 8;
+  const uint32_t total = (uint32_t)(R * (H + 2) * (long long)(W + 2) * G);
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    int g, xx, yy, ri;
+    dec3(i, dec, g, xx, yy, ri);
+    const long long r = ri;
+    const long long p = (r * (H + 2) + yy) * (long long)(W + 2) + xx;
+    BF8 o;
+    o.u = make_uint4(0, 0, 0, 0);
     if (xx >= 1 && xx <= W && yy >= 1 && yy <= H) {
-      if (c < 4) v = fmaxf(emb[(r * 4 + c) * (long long)(H * W) + (yy - 1) * W + xx - 1], 0.f);
-      else if (c < 4 + Cs) v = fmaxf(bf2f(skip[((r * (H + 2) + yy) * (long long)(W + 2) + xx) * Cs + c - 4]), 0.f);
+      const int c0 = g * 8;                                        // output channels c0 .. c0+7
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const int c = c0 + half * 4;                               // four channels at a time
+        if (c == 0) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            o.h[j] = f2bf(fmaxf(__ldg(emb + (r * 4 + j) * (long long)(H * W) + (yy - 1) * W + xx - 1), 0.f));
+        } else if (c - 4 + 4 <= Cs) {
+          const uint2 v = __ldg(reinterpret_cast<const uint2*>(skip + p * Cs + c - 4));
+          const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            const float2 f = __bfloat1622float2(h2[j]);
+            o.h[half * 4 + 2 * j] = f2bf(fmaxf(f.x, 0.f));
+            o.h[half * 4 + 2 * j + 1] = f2bf(fmaxf(f.y, 0.f));
+          }
+        }
+      }
     }
-    out[i] = f2bf(v);
+    *reinterpret_cast<uint4*>(out + p * Cp + g * 8) = o.u;
   }
 }
-__global__ void loc_cat_bwd_kernel(const __nv_bfloat16* __restrict__ dcat, const float* __restrict__ emb,
-                                   const __nv_bfloat16* __restrict__ skip, float* __restrict__ demb,
-                                   __nv_bfloat16* __restrict__ dskip, long long R, int H, int W, int Cs, int Cp) {
-  const long long total = R * (H + 2) * (long long)(W + 2) * (4 + Cs);
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int c = (int)(i % (4 + Cs));
-    long long p = i / (4 + Cs);
-    const int xx = (int)(p % (W + 2)); const long long q = p / (W + 2);
-    const int yy = (int)(q % (H + 2));
-    const long long r = q / (H + 2);
+// thread = (padded pixel, group of 8 skip channels); the group-0 thread also scatters the four embedding gradients
+__global__ void __launch_bounds__(256)
+loc_cat_bwd_kernel(const __nv_bfloat16* __restrict__ dcat, const float* __restrict__ emb,
+                   const __nv_bfloat16* __restrict__ skip, float* __restrict__ demb, __nv_bfloat16* __restrict__ dskip,
+                   long long R, int H, int W, int Cs, int Cp, const Dec3 dec) {
+  const int G = Cs / 8;
+  const uint32_t total = (uint32_t)(R * (H + 2) * (long long)(W + 2) * G);
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    int g, xx, yy, ri;
+    dec3(i, dec, g, xx, yy, ri);
+    const long long r = ri;
+    const long long p = (r * (H + 2) + yy) * (long long)(W + 2) + xx;
     const bool inner = xx >= 1 && xx <= W && yy >= 1 && yy <= H;
-    const float g = inner ? bf2f(dcat[p * Cp + c]) : 0.f;
-    if (c < 4) {
-      if (inner) {
-        const long long e = (r * 4 + c) * (long long)(H * W) + (yy - 1) * W + xx - 1;
-        demb[e] = emb[e] > 0.f ? g : 0.f;
+    BF8 o;
+    o.u = make_uint4(0, 0, 0, 0);
+    if (inner) {
+      BF8 sk;
+      sk.u = __ldg(reinterpret_cast<const uint4*>(skip + p * Cs + g * 8));
+      const uint2 d0 = __ldg(reinterpret_cast<const uint2*>(dcat + p * Cp + 4 + g * 8));
+      const uint2 d1 = __ldg(reinterpret_cast<const uint2*>(dcat + p * Cp + 8 + g * 8));
+      const __nv_bfloat16* dh0 = reinterpret_cast<const __nv_bfloat16*>(&d0);
+      const __nv_bfloat16* dh1 = reinterpret_cast<const __nv_bfloat16*>(&d1);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        o.h[j] = bf2f(sk.h[j]) > 0.f ? dh0[j] : f2bf(0.f);
+        o.h[4 + j] = bf2f(sk.h[4 + j]) > 0.f ? dh1[j] : f2bf(0.f);
       }
-    } else {
-      const long long s = p * Cs + c - 4;
-      dskip[s] = (inner && bf2f(skip[s]) > 0.f) ? f2bf(g) : f2bf(0.f);
+      if (g == 0) {
+        const uint2 de = __ldg(reinterpret_cast<const uint2*>(dcat + p * Cp));
+        const __nv_bfloat16* eh = reinterpret_cast<const __nv_bfloat16*>(&de);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const long long e = (r * 4 + j) * (long long)(H * W) + (yy - 1) * W + xx - 1;
+          demb[e] = __ldg(emb + e) > 0.f ? bf2f(eh[j]) : 0.f;
+        }
+      }
     }
+    *reinterpret_cast<uint4*>(dskip + p * Cs + g * 8) = o.u;
   }
 }
 
 int loc_cat_fwd(const float* emb, const void* skip, void* out, long long R, int H, int W, int Cs, int Cp, cudaStream_t st) {
   if (R <= 0) return AS_OK;
-  if (Cp < 4 + Cs) return AS_ESIZE;
+  if (Cp < 4 + Cs || (Cp % 8) || (Cs % 8)) return AS_ESIZE;
   if (!emb || !skip || !out) return AS_EINVAL;
-  const long long total = R * (H + 2) * (long long)(W + 2) * Cp;
-  loc_cat_fwd_kernel<<<ew_grid(total, 1), 256, 0, st>>>(emb, (const __nv_bfloat16*)skip, (__nv_bfloat16*)out, R, H, W, Cs, Cp);
+  const long long total = R * (H + 2) * (long long)(W + 2) * (Cp / 8);
+  if (total >= (1LL << 31)) return AS_ESIZE;
+  loc_cat_fwd_kernel<<<ew_grid(total, 1), 256, 0, st>>>(emb, (const __nv_bfloat16*)skip, (__nv_bfloat16*)out, R, H, W, Cs, Cp,
+                                                        make_dec3(Cp / 8, W + 2, H + 2));
   AS_LAUNCH_CHECK();
   return AS_OK;
 }
@@ -460,9 +500,11 @@ int loc_cat_bwd(const void* dcat, const float* emb, const void* skip, float* dem
                 int Cs, int Cp, cudaStream_t st) {
   if (R <= 0) return AS_OK;
   if (!dcat || !emb || !skip || !demb || !dskip) return AS_EINVAL;
-  const long long total = R * (H + 2) * (long long)(W + 2) * (4 + Cs);
+  if (Cp < 4 + Cs || (Cp % 8) || (Cs % 8)) return AS_ESIZE;
+  const long long total = R * (H + 2) * (long long)(W + 2) * (Cs / 8);
+  if (total >= (1LL << 31)) return AS_ESIZE;
   loc_cat_bwd_kernel<<<ew_grid(total, 1), 256, 0, st>>>((const __nv_bfloat16*)dcat, emb, (const __nv_bfloat16*)skip, demb,
-                                                       (__nv_bfloat16*)dskip, R, H, W, Cs, Cp);
+                                                        (__nv_bfloat16*)dskip, R, H, W, Cs, Cp, make_dec3(Cs / 8, W + 2, H + 2));
   AS_LAUNCH_CHECK();
   return AS_OK;
 }
@@ -885,59 +927,82 @@ spatial_features_kernel(const SpatialPlanes sp, const float* __restrict__ scatte
   }
   __syncthreads();
   const int Cp = 64;
-  for (int i = threadIdx.x; i < kFeatBand * (W + 2); i += blockDim.x) {
+  // every lane builds the 128 bytes of its pixel (zeros for the border ring and for lanes past the band); the warp's 32
+  // pixels are contiguous in the output, so they are staged in a swizzled 4 KB tile and written as 512-byte rows
+  __shared__ __align__(16) uint4 stile[8][32 * 8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int n_band = kFeatBand * (W + 2);
+  for (int i0 = 0; i0 < n_band; i0 += blockDim.x) {
+    const int i = i0 + threadIdx.x;
     const int yy = band * kFeatBand + i / (W + 2);
     const int xx = i % (W + 2);
-    if (yy >= H + 2) continue;
-    uint4* dst = reinterpret_cast<uint4*>(out + (((long long)r * (H + 2) + yy) * (W + 2) + xx) * Cp);
-    if (yy == 0 || yy == H + 1 || xx == 0 || xx == W + 1) {
+    const bool valid = i < n_band && yy < H + 2;
+    uint4 u[8];
 #pragma unroll
-      for (int q = 0; q < 8; ++q) dst[q] = make_uint4(0, 0, 0, 0);
-      continue;
+    for (int q = 0; q < 8; ++q) u[q] = make_uint4(0, 0, 0, 0);
+    if (valid && !(yy == 0 || yy == H + 1 || xx == 0 || xx == W + 1)) {
+      const int y = yy - 1, x = xx - 1;
+      const long long pix = ((long long)r * H + y) * W + x;
+      float f[64];
+#pragma unroll
+      for (int c = 0; c < 64; ++c) f[c] = 0.f;
+      f[0] = (float)sp.plane[0][pix] * (1.f / 256.f);
+      {
+        int v;
+        v = sp.plane[1][pix]; v = v > 3 ? 3 : v;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) f[1 + k] = (v == k) ? 1.f : 0.f;
+        v = sp.plane[2][pix]; v = v > 1 ? 1 : v;
+        f[5] = (v == 0) ? 1.f : 0.f; f[6] = (v == 1) ? 1.f : 0.f;
+        v = sp.plane[3][pix]; v = v > 4 ? 4 : v;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) f[7 + k] = (v == k) ? 1.f : 0.f;
+        v = sp.plane[4][pix]; v = v > 1 ? 1 : v;
+        f[12] = (v == 0) ? 1.f : 0.f; f[13] = (v == 1) ? 1.f : 0.f;
+        v = sp.plane[5][pix]; v = v > 1 ? 1 : v;
+        f[14] = (v == 0) ? 1.f : 0.f; f[15] = (v == 1) ? 1.f : 0.f;
+        v = sp.plane[6][pix]; v = v > 1 ? 1 : v;
+        f[16] = (v == 0) ? 1.f : 0.f; f[17] = (v == 1) ? 1.f : 0.f;
+      }
+      {
+        const int local = (y - y_lo) * W + x;
+        const unsigned int bits = (effbits[local >> 2] >> ((local & 3) * 8)) & 0xFFu;
+#pragma unroll
+        for (int e = 0; e < 6; ++e) f[18 + e] = ((bits >> e) & 1u) ? 1.f : 0.f;
+      }
+      const float* sm = scatter_map + (long long)r * Cs * HW + (long long)y * W + x;
+#pragma unroll
+      for (int k = 0; k < 32; ++k) f[24 + k] = (k < Cs) ? __ldg(sm + (long long)k * HW) : 0.f;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        __nv_bfloat162 h0 = __floats2bfloat162_rn(f[8 * q], f[8 * q + 1]), h1 = __floats2bfloat162_rn(f[8 * q + 2], f[8 * q + 3]);
+        __nv_bfloat162 h2 = __floats2bfloat162_rn(f[8 * q + 4], f[8 * q + 5]), h3 = __floats2bfloat162_rn(f[8 * q + 6], f[8 * q + 7]);
+        u[q].x = *reinterpret_cast<uint32_t*>(&h0); u[q].y = *reinterpret_cast<uint32_t*>(&h1);
+        u[q].z = *reinterpret_cast<uint32_t*>(&h2); u[q].w = *reinterpret_cast<uint32_t*>(&h3);
+      }
     }
-    const int y = yy - 1, x = xx - 1;
-    const long long pix = ((long long)r * H + y) * W + x;
-    float f[64];
 #pragma unroll
-    for (int c = 0; c < 64; ++c) f[c] = 0.f;
-    f[0] = (float)sp.plane[0][pix] * (1.f / 256.f);
-    {
-      int v;
-      v = sp.plane[1][pix]; v = v > 3 ? 3 : v;
+    for (int q = 0; q < 8; ++q) stile[warp][lane * 8 + (q ^ (lane & 7))] = u[q];
+    __syncwarp();
+    // first pixel of this warp in the band, and how many of its 32 pixels exist
+    const int iw = i0 + warp * 32;
+    int nvalid = n_band - iw;
+    const int rows_left = (H + 2 - band * kFeatBand) * (W + 2) - iw;         // pixels of the image below this point
+    nvalid = nvalid < rows_left ? nvalid : rows_left;
+    nvalid = nvalid > 32 ? 32 : nvalid;
+    if (nvalid > 0) {
+      uint4* gbase = reinterpret_cast<uint4*>(out + (((long long)r * (H + 2) + band * kFeatBand) * (W + 2) + iw) * Cp);
 #pragma unroll
-      for (int k = 0; k < 4; ++k) f[1 + k] = (v == k) ? 1.f : 0.f;
-      v = sp.plane[2][pix]; v = v > 1 ? 1 : v;
-      f[5] = (v == 0) ? 1.f : 0.f; f[6] = (v == 1) ? 1.f : 0.f;
-      v = sp.plane[3][pix]; v = v > 4 ? 4 : v;
-#pragma unroll
-      for (int k = 0; k < 5; ++k) f[7 + k] = (v == k) ? 1.f : 0.f;
-      v = sp.plane[4][pix]; v = v > 1 ? 1 : v;
-      f[12] = (v == 0) ? 1.f : 0.f; f[13] = (v == 1) ? 1.f : 0.f;
-      v = sp.plane[5][pix]; v = v > 1 ? 1 : v;
-      f[14] = (v == 0) ? 1.f : 0.f; f[15] = (v == 1) ? 1.f : 0.f;
-      v = sp.plane[6][pix]; v = v > 1 ? 1 : v;
-      f[16] = (v == 0) ? 1.f : 0.f; f[17] = (v == 1) ? 1.f : 0.f;
+      for (int k = 0; k < 8; ++k) {
+        const int idx = k * 32 + lane;
+        const int px = idx >> 3, ch = idx & 7;
+        if (px < nvalid) gbase[idx] = stile[warp][px * 8 + (ch ^ (px & 7))];
+      }
     }
-    {
-      const int local = (y - y_lo) * W + x;
-      const unsigned int bits = (effbits[local >> 2] >> ((local & 3) * 8)) & 0xFFu;
-#pragma unroll
-      for (int e = 0; e < 6; ++e) f[18 + e] = ((bits >> e) & 1u) ? 1.f : 0.f;
-    }
-    const float* sm = scatter_map + (long long)r * Cs * HW + (long long)y * W + x;
-#pragma unroll
-    for (int k = 0; k < 32; ++k) f[24 + k] = (k < Cs) ? __ldg(sm + (long long)k * HW) : 0.f;
-#pragma unroll
-    for (int q = 0; q < 8; ++q) {
-      __nv_bfloat162 h0 = __floats2bfloat162_rn(f[8 * q], f[8 * q + 1]), h1 = __floats2bfloat162_rn(f[8 * q + 2], f[8 * q + 3]);
-      __nv_bfloat162 h2 = __floats2bfloat162_rn(f[8 * q + 4], f[8 * q + 5]), h3 = __floats2bfloat162_rn(f[8 * q + 6], f[8 * q + 7]);
-      uint4 u;
-      u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
-      u.z = *reinterpret_cast<uint32_t*>(&h2); u.w = *reinterpret_cast<uint32_t*>(&h3);
-      dst[q] = u;
-    }
+    __syncwarp();
   }
 }
+
 
 int spatial_features(const void* const* planes, const void* const* effects, int n_eff, const float* scatter_map,
                      void* out, long long R, int H, int W, int Cs, cudaStream_t st) {
