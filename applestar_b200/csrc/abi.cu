@@ -49,6 +49,11 @@ long long colsum_scratch_floats(int);
 int colsum_bf16(const void*, float*, float*, long long, int, cudaStream_t);
 int colsum_bf16_static(const void*, float*, long long, int, cudaStream_t);
 int relu_bwd_colsum(const void*, const void*, void*, float*, float*, long long, int, cudaStream_t);
+int su_prefix_fwd(const float*, const long long*, const long long*, const long long*, float*, float*, unsigned char*, long long,
+                  int, int, int, int, cudaStream_t);
+int su_prefix_bwd(const float*, const long long*, const long long*, const float*, const unsigned char*, float*, long long, int, int,
+                  int, int, cudaStream_t);
+int su_mask_logits(const float*, const long long*, const long long*, float*, long long, int, int, int, float, float, cudaStream_t);
 int linear_bwd_prep(const float*, const float*, const void*, void*, float*, float*, long long, int, cudaStream_t);
 int colsum_f32(const float*, float*, float*, long long, int, cudaStream_t);
 int lnlstm_fwd(const float*, const float*, const float*, const void*, const float*, const float*, const float*,
@@ -250,6 +255,21 @@ int as_colsum_f32(const float* x, float* out, float* scratch, int64_t rows, int 
 int as_relu_bwd_colsum_bf16(const void* dy, const void* y, void* dz, float* colsum, float* scratch, int64_t rows, int C,
                             void* stream) {
   return as::relu_bwd_colsum(dy, y, dz, colsum, scratch, rows, C, ST(stream));
+}
+int as_su_prefix_fwd(const float* key, const int64_t* selected_units, const int64_t* entity_num, const int64_t* su_num, float* emb,
+                     float* cnt, uint8_t* isnew, int64_t R, int N1, int D, int Smax, int S, void* stream) {
+  return as::su_prefix_fwd(key, reinterpret_cast<const long long*>(selected_units), reinterpret_cast<const long long*>(entity_num),
+                           reinterpret_cast<const long long*>(su_num), emb, cnt, isnew, R, N1, D, Smax, S, ST(stream));
+}
+int as_su_prefix_bwd(const float* demb, const int64_t* selected_units, const int64_t* su_num, const float* cnt, const uint8_t* isnew,
+                     float* dkey, int64_t R, int N1, int D, int Smax, int S, void* stream) {
+  return as::su_prefix_bwd(demb, reinterpret_cast<const long long*>(selected_units), reinterpret_cast<const long long*>(su_num), cnt,
+                           isnew, dkey, R, N1, D, Smax, S, ST(stream));
+}
+int as_su_mask_logits(const float* x, const int64_t* selected_units, const int64_t* entity_num, float* out, int64_t R, int N1,
+                      int Smax, int S, float scale, float fill, void* stream) {
+  return as::su_mask_logits(x, reinterpret_cast<const long long*>(selected_units), reinterpret_cast<const long long*>(entity_num), out,
+                            R, N1, Smax, S, scale, fill, ST(stream));
 }
 int as_linear_bwd_prep(const float* dy, const float* y32, const void* y16, void* dz16, float* colsum, float* scratch,
                        int64_t rows, int C, void* stream) {

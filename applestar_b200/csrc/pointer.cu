@@ -1,0 +1,127 @@
+// Teacher-forced SelectedUnits pointer loop without the loop (reference: head/action_arg_head.py:168-216).
+//
+// In the learner the picks of every step are given (teacher forcing), so everything that the reference recomputes
+// step by step from one-hot tensors is a function of `selected_units` alone:
+//   * the autoregressive embedding of step i is the mean of the key rows of the distinct units picked up to step i
+//     (before the end token)                                   -> su_prefix_fwd / bwd: one warp per row, running sum;
+//   * the logits mask of step i removes padding, the end token at step 0 and every unit picked before step i
+//                                                              -> su_mask_logits: first-pick step per entity in
+//                                                                 shared memory, then one pass over [S, N+1].
+// With these two kernels the S steps of query MLP, LayerNorm-LSTM, key dot products and embedding MLP run as a few
+// batched launches over all steps instead of ~65 small launches per step.
+#include "common.cuh"
+
+namespace as {
+
+// emb[r,i,:] = (sum over distinct live picks j <= i of key[r, sel[r,j], :]) / (has_units ? count : 1)
+// cnt[r,i] = count, isnew[r,i] = 1 when step i added a unit.  D must be 32 (one lane per channel).
+__global__ void __launch_bounds__(256)
+su_prefix_fwd_kernel(const float* __restrict__ key, const long long* __restrict__ sel, const long long* __restrict__ entity_num,
+                     const long long* __restrict__ su_num, float* __restrict__ emb, float* __restrict__ cnt,
+                     unsigned char* __restrict__ isnew, long long R, int N1, int Smax, int S) {
+  const int lane = threadIdx.x & 31;
+  const long long r = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (r >= R) return;
+  const long long en = entity_num[r];
+  const bool has_units = su_num[r] != 0;
+  const long long s_lo = lane < S ? sel[r * Smax + lane] : -1, s_hi = lane + 32 < S ? sel[r * Smax + lane + 32] : -1;
+  unsigned long long newmask = 0ull;
+  float acc = 0.f, count = 0.f;
+  bool ended = false;
+  for (int i = 0; i < S; ++i) {
+    const long long s = __shfl_sync(0xffffffffu, i < 32 ? s_lo : s_hi, i & 31);
+    ended = ended || (s == en);
+    bool add = !ended;
+    if (add) {   // a unit already in the set is not counted twice (the reference takes the maximum of one-hots)
+      const bool dup = (((newmask >> lane) & 1ull) && s_lo == s) || (((newmask >> (lane + 32)) & 1ull) && s_hi == s);
+      if (__any_sync(0xffffffffu, dup)) add = false;
+    }
+    if (add) {
+      const long long sc = s < 0 ? 0 : (s > N1 - 1 ? N1 - 1 : s);
+      acc += __ldg(key + (r * N1 + sc) * 32 + lane);
+      count += 1.f;
+      newmask |= 1ull << i;
+    }
+    emb[(r * S + i) * 32 + lane] = has_units ? acc / count : acc;
+    if (lane == 0) { cnt[r * S + i] = count; isnew[r * S + i] = add ? 1 : 0; }
+  }
+}
+
+// dkey[r, sel[r,j], :] += sum_{i >= j} demb[r,i,:] / count_i for every step j that added a unit (dkey zeroed by the caller)
+__global__ void __launch_bounds__(256)
+su_prefix_bwd_kernel(const float* __restrict__ demb, const long long* __restrict__ sel, const long long* __restrict__ su_num,
+                     const float* __restrict__ cnt, const unsigned char* __restrict__ isnew, float* __restrict__ dkey,
+                     long long R, int N1, int Smax, int S) {
+  const int lane = threadIdx.x & 31;
+  const long long r = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (r >= R) return;
+  const bool has_units = su_num[r] != 0;
+  float suffix = 0.f;
+  for (int i = S - 1; i >= 0; --i) {
+    float g = demb[(r * S + i) * 32 + lane];
+    if (has_units) {
+      const float c = cnt[r * S + i];
+      g = c > 0.f ? g / c : 0.f;
+    }
+    suffix += g;
+    if (isnew[r * S + i]) {
+      long long s = sel[r * Smax + i];
+      s = s < 0 ? 0 : (s > N1 - 1 ? N1 - 1 : s);
+      dkey[(r * N1 + s) * 32 + lane] += suffix;
+    }
+  }
+}
+
+// out[r,i,n] = valid(r,i,n) ? x[r,i,n] * scale : fill, valid = n <= entity_num[r] and not (i == 0 and n == entity_num[r])
+// and n not picked at any step before i (action_arg_head.py:179-187).  fill = -1e9 * scale forward, 0 backward.
+__global__ void __launch_bounds__(256)
+su_mask_logits_kernel(const float* __restrict__ x, const long long* __restrict__ sel, const long long* __restrict__ entity_num,
+                      float* __restrict__ out, int N1, int Smax, int S, float scale, float fill) {
+  extern __shared__ int first_sel[];                 // [N1] first step at which entity n was picked (S = never)
+  const long long r = blockIdx.x;
+  for (int n = threadIdx.x; n < N1; n += blockDim.x) first_sel[n] = S;
+  __syncthreads();
+  for (int j = threadIdx.x; j < S; j += blockDim.x) {
+    const long long s = sel[r * Smax + j];
+    if (s >= 0 && s < N1) atomicMin(&first_sel[(int)s], j);
+  }
+  __syncthreads();
+  const long long en = entity_num[r];
+  const int total = S * N1;
+  for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+    const int i = idx / N1, n = idx - i * N1;
+    const bool valid = (long long)n <= en && !(i == 0 && (long long)n == en) && first_sel[n] >= i;
+    const long long o = r * total + idx;
+    out[o] = valid ? x[o] * scale : fill;
+  }
+}
+
+int su_prefix_fwd(const float* key, const long long* sel, const long long* entity_num, const long long* su_num, float* emb,
+                  float* cnt, unsigned char* isnew, long long R, int N1, int D, int Smax, int S, cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (D != 32 || S <= 0 || S > 64 || S > Smax) return AS_ESIZE;
+  if (!key || !sel || !entity_num || !su_num || !emb || !cnt || !isnew) return AS_EINVAL;
+  su_prefix_fwd_kernel<<<(unsigned)((R * 32 + 255) / 256), 256, 0, st>>>(key, sel, entity_num, su_num, emb, cnt, isnew, R, N1, Smax, S);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+int su_prefix_bwd(const float* demb, const long long* sel, const long long* su_num, const float* cnt,
+                  const unsigned char* isnew, float* dkey, long long R, int N1, int D, int Smax, int S, cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (D != 32 || S <= 0 || S > 64 || S > Smax) return AS_ESIZE;
+  if (!demb || !sel || !su_num || !cnt || !isnew || !dkey) return AS_EINVAL;
+  su_prefix_bwd_kernel<<<(unsigned)((R * 32 + 255) / 256), 256, 0, st>>>(demb, sel, su_num, cnt, isnew, dkey, R, N1, Smax, S);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+int su_mask_logits(const float* x, const long long* sel, const long long* entity_num, float* out, long long R, int N1,
+                   int Smax, int S, float scale, float fill, cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (S <= 0 || S > Smax || N1 <= 0 || N1 > 8192) return AS_ESIZE;
+  if (!x || !sel || !entity_num || !out) return AS_EINVAL;
+  su_mask_logits_kernel<<<(unsigned)R, 256, N1 * sizeof(int), st>>>(x, sel, entity_num, out, N1, Smax, S, scale, fill);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+}  // namespace as

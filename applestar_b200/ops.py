@@ -248,8 +248,85 @@ SU_STEPS_HINT = None     # host-side max(selected_units_num) supplied by the cal
                          # on the CPU for free); lets the learner step run without any device->host sync
 
 
+class _SUPrefix(torch.autograd.Function):
+    """[kernel] embedding of the units picked so far, for all S steps at once (as_su_prefix_fwd/bwd)."""
+
+    @staticmethod
+    def forward(ctx, key, sel, entity_num, su_num, S):
+        R, N1, D = key.shape
+        key = key.contiguous()
+        sel = sel.contiguous()
+        emb = torch.empty((R, S, D), dtype=torch.float32, device=key.device)
+        cnt = torch.empty((R, S), dtype=torch.float32, device=key.device)
+        isnew = torch.empty((R, S), dtype=torch.uint8, device=key.device)
+        _lib.call('as_su_prefix_fwd', key.data_ptr(), sel.data_ptr(), entity_num.data_ptr(), su_num.data_ptr(),
+                  emb.data_ptr(), cnt.data_ptr(), isnew.data_ptr(), R, N1, D, sel.shape[1], S, _lib.stream_ptr())
+        ctx.dims = (R, N1, D, S)
+        ctx.save_for_backward(sel, su_num, cnt, isnew)
+        return emb
+
+    @staticmethod
+    def backward(ctx, demb):
+        sel, su_num, cnt, isnew = ctx.saved_tensors
+        R, N1, D, S = ctx.dims
+        demb = demb.contiguous()
+        dkey = torch.zeros((R, N1, D), dtype=torch.float32, device=demb.device)
+        _lib.call('as_su_prefix_bwd', demb.data_ptr(), sel.data_ptr(), su_num.data_ptr(), cnt.data_ptr(),
+                  isnew.data_ptr(), dkey.data_ptr(), R, N1, D, sel.shape[1], S, _lib.stream_ptr())
+        return dkey, None, None, None, None
+
+
+class _SUMask(torch.autograd.Function):
+    """[kernel] logits mask of every step + 1/temperature (as_su_mask_logits); masked entries are -1e9/temperature."""
+
+    @staticmethod
+    def forward(ctx, x, sel, entity_num, S, scale):
+        R, _, N1 = x.shape
+        x = x.contiguous()
+        sel = sel.contiguous()
+        out = torch.empty_like(x)
+        _lib.call('as_su_mask_logits', x.data_ptr(), sel.data_ptr(), entity_num.data_ptr(), out.data_ptr(), R, N1,
+                  sel.shape[1], S, float(scale), float(-1e9 * scale), _lib.stream_ptr())
+        ctx.args = (R, N1, S, float(scale))
+        ctx.save_for_backward(sel, entity_num)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        sel, entity_num = ctx.saved_tensors
+        R, N1, S, scale = ctx.args
+        dy = dy.contiguous()
+        dx = torch.empty_like(dy)
+        _lib.call('as_su_mask_logits', dy.data_ptr(), sel.data_ptr(), entity_num.data_ptr(), dx.data_ptr(), R, N1,
+                  sel.shape[1], S, scale, 0.0, _lib.stream_ptr())
+        return dx, None, None, None, None
+
+
 def selected_units_train(head, key, ae0, entity_num, selected_units, selected_units_num, temperature):
-    """Teacher-forced pointer loop (action_arg_head.py:168-216).  The loop length is the maximum needed by the
+    """Teacher-forced pointer loop (action_arg_head.py:168-216) WITHOUT the loop: the picks are given, so the embedding
+    after every step (as_su_prefix_fwd) and the logits mask of every step (as_su_mask_logits) depend on
+    `selected_units` only; the embedding MLP, the query MLP, the LayerNorm-LSTM and the key dot products then run once
+    over all S steps.  Same results as selected_units_train_loop (tests/test_model_gpu.py)."""
+    R, N1, D = key.shape
+    S = int(SU_STEPS_HINT) if SU_STEPS_HINT is not None else max(int(selected_units_num.max()), 1)
+    S = max(1, min(S, selected_units.shape[1]))
+    entity_num = entity_num.contiguous()
+    su_num = selected_units_num.contiguous()
+    emb = _SUPrefix.apply(key, selected_units, entity_num, su_num, S)                    # [R,S,32] after each step
+    delta = head.embed_fc2(head.embed_fc1(emb.reshape(R * S, D))).view(R, S, -1)
+    ae_seq = ae0.unsqueeze(1) + delta                                                    # embedding after step i
+    x = torch.cat([ae0.unsqueeze(1), ae_seq[:, :S - 1]], dim=1)                          # embedding fed to step i
+    x = x.transpose(0, 1).contiguous()                                                   # time-major [S,R,1024]
+    q = head.query_fc2(head.query_fc1(x.view(S * R, -1))).view(S, R, -1)
+    zeros = key.new_zeros(R, q.shape[-1])
+    out, _, _ = K.lnlstm_layer(q, zeros, zeros, head.lstm.layers[0].cell)               # [S,R,32]
+    logits = torch.bmm(out.transpose(0, 1), key.transpose(1, 2))                         # [library] [R,S,N1]
+    logits = _SUMask.apply(logits, selected_units, entity_num, S, 1.0 / temperature)
+    return logits, selected_units, ae_seq[:, S - 1], selected_units_num, None
+
+
+def selected_units_train_loop(head, key, ae0, entity_num, selected_units, selected_units_num, temperature):
+    """Step-by-step version of selected_units_train (kept as the readable restatement and test reference).  The loop length is the maximum needed by the
     batch: taken from SU_STEPS_HINT when the caller knows it on the host, else read once from the device (one
     sync per call instead of the reference's 2-4 per step).  Any length >= max(selected_units_num) gives identical
     valid logits and embedding (ended rows keep a frozen selection)."""

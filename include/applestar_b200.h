@@ -198,6 +198,21 @@ int as_softmax_fwd(const void* scores, const int64_t* key_len, void* probs, int6
 int as_softmax_bwd(const void* probs, const void* dprobs, void* dscores, int64_t rows, int Nk, int dprobs_bf16,
                    void* stream);
 
+/* Teacher-forced SelectedUnits pointer loop (head/action_arg_head.py:168-216) without the per-step one-hot tensors.
+ * as_su_prefix_fwd: emb[r,i,:] = mean (sum when selected_units_num[r] == 0) of the key rows of the distinct units picked
+ * at steps <= i before the end token (= entity_num[r]) -- the `one_hot`/`einsum`/division of :198-206 for all S steps;
+ * cnt [R,S] and isnew [R,S] are saved for as_su_prefix_bwd, which accumulates d key (caller zeroes dkey first).
+ * key [R,N1,32] fp32, selected_units [R,Smax] int64, S <= min(Smax, 64).
+ * as_su_mask_logits: out = valid ? x * scale : fill over x [R,S,N1], valid = the logits mask of step i (:179-187):
+ * n <= entity_num, not the end token at step 0, not picked before step i.  Forward: fill = -1e9 * scale; backward:
+ * the same call on the gradient with fill = 0. */
+int as_su_prefix_fwd(const float* key, const int64_t* selected_units, const int64_t* entity_num, const int64_t* su_num, float* emb,
+                     float* cnt, uint8_t* isnew, int64_t R, int N1, int D, int Smax, int S, void* stream);
+int as_su_prefix_bwd(const float* demb, const int64_t* selected_units, const int64_t* su_num, const float* cnt, const uint8_t* isnew,
+                     float* dkey, int64_t R, int N1, int D, int Smax, int S, void* stream);
+int as_su_mask_logits(const float* x, const int64_t* selected_units, const int64_t* entity_num, float* out, int64_t R, int N1,
+                      int Smax, int S, float scale, float fill, void* stream);
+
 /* bf16 feature rows for the entity embedding GEMM -- replaces the 28 embedding lookups + torch.cat at
  * obs_encoder/entity_encoder.py:60-78.  Per field f: data[f] = device array [rows] of element type dtype[f]
  * (0 u8, 1 i8, 2 i16, 3 f16, 4 i64, 5 f32), kind[f] (0 one-hot clamped to num-1, 1 num-bit binary MSB first,

@@ -136,3 +136,50 @@ def test_cuda_graph_learner_step_matches_eager():
     assert abs(l_e - l_g) <= 1e-3 * max(1.0, abs(l_e)), (l_e, l_g)
     info = graph_step(data)
     assert 'winloss/td' in info and isinstance(info['kl/total'], float)
+
+
+@gpu
+def test_selected_units_batched_matches_step_loop():
+    """ops.selected_units_train (all steps at once) vs the step-by-step loop: logits, final embedding, gradients."""
+    from applestar_b200 import ops
+    from applestar_b200.model import SelectedUnitsHead
+    torch.manual_seed(5)
+    R, N, S = 6, 40, 7
+    head = SelectedUnitsHead(False).cuda()
+    key0 = torch.randn(R, N + 1, 32, device='cuda')
+    ae0 = torch.randn(R, 1024, device='cuda') * 0.1
+    en = torch.tensor([40, 12, 30, 5, 40, 22], device='cuda')
+    sel = torch.zeros(R, 64, dtype=torch.long, device='cuda')
+    num = torch.tensor([7, 3, 0, 2, 5, 1], device='cuda')
+    for r in range(R):
+        k = int(num[r])
+        perm = torch.randperm(int(en[r]))[:max(k - 1, 0)]
+        sel[r, :len(perm)] = perm.cuda()
+        sel[r, len(perm):] = en[r]                    # end token, repeated
+    sel[4, 1] = sel[4, 0]                              # a duplicate pick (one-hot maximum counts it once)
+    outs = []
+    for fn in (ops.selected_units_train, ops.selected_units_train_loop):
+        ops.SU_STEPS_HINT = S
+        key = key0.clone().requires_grad_(True)
+        ae = ae0.clone().requires_grad_(True)
+        for p in head.parameters():
+            p.grad = None
+        logits, _, ae_out, _, _ = fn(head, key, ae, en, sel, num, 0.8)
+        valid = logits > -1e8
+        g1 = torch.randn(logits.shape, device='cuda', generator=torch.Generator('cuda').manual_seed(1))
+        g2 = torch.randn(ae_out.shape, device='cuda', generator=torch.Generator('cuda').manual_seed(2))
+        ((logits * g1 * valid).sum() + (ae_out * g2).sum()).backward()
+        outs.append((logits.detach(), ae_out.detach(), key.grad.clone(), ae.grad.clone(),
+                     head.query_fc1[0].weight.grad.clone()))
+    ops.SU_STEPS_HINT = None
+    a, b = outs
+    assert torch.equal(a[0] > -1e8, b[0] > -1e8)                       # masks bit-exact
+    v = a[0] > -1e8
+    assert (a[0][v] - b[0][v]).abs().max().item() < 0.05               # bf16 GEMMs batched differently
+    nan_ok = torch.isnan(b[1]) == torch.isnan(a[1])
+    assert bool(nan_ok.all())
+    fin = ~torch.isnan(b[1])
+    assert (a[1][fin] - b[1][fin]).abs().max().item() < 0.05
+    for x, y in zip(a[2:], b[2:]):
+        fin = ~(torch.isnan(x) | torch.isnan(y))
+        assert (x[fin] - y[fin]).abs().max().item() < 0.08 * y[fin].abs().max().item() + 1e-3
