@@ -54,6 +54,8 @@ int su_prefix_fwd(const float*, const long long*, const long long*, const long l
 int su_prefix_bwd(const float*, const long long*, const long long*, const float*, const unsigned char*, float*, long long, int, int,
                   int, int, cudaStream_t);
 int su_mask_logits(const float*, const long long*, const long long*, float*, long long, int, int, int, float, float, cudaStream_t);
+int masked_mean_fwd(const float*, const long long*, float*, long long, int, int, cudaStream_t);
+int masked_mean_bwd(const float*, const long long*, float*, long long, int, int, cudaStream_t);
 int linear_bwd_prep(const float*, const float*, const void*, void*, float*, float*, long long, int, cudaStream_t);
 int colsum_f32(const float*, float*, float*, long long, int, cudaStream_t);
 int lnlstm_fwd(const float*, const float*, const float*, const void*, const float*, const float*, const float*,
@@ -270,6 +272,12 @@ int as_su_mask_logits(const float* x, const int64_t* selected_units, const int64
                       int Smax, int S, float scale, float fill, void* stream) {
   return as::su_mask_logits(x, reinterpret_cast<const long long*>(selected_units), reinterpret_cast<const long long*>(entity_num), out,
                             R, N1, Smax, S, scale, fill, ST(stream));
+}
+int as_masked_mean_fwd(const float* x, const int64_t* len, float* out, int64_t R, int N, int C, void* stream) {
+  return as::masked_mean_fwd(x, reinterpret_cast<const long long*>(len), out, R, N, C, ST(stream));
+}
+int as_masked_mean_bwd(const float* dout, const int64_t* len, float* dx, int64_t R, int N, int C, void* stream) {
+  return as::masked_mean_bwd(dout, reinterpret_cast<const long long*>(len), dx, R, N, C, ST(stream));
 }
 int as_linear_bwd_prep(const float* dy, const float* y32, const void* y16, void* dz16, float* colsum, float* scratch,
                        int64_t rows, int C, void* stream) {

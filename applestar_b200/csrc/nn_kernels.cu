@@ -570,4 +570,74 @@ int entity_features(const void* const* data, const int* kind, const int* num, co
   return AS_OK;
 }
 
+// ------------------------------------------------------------------------------------------ masked mean over entities
+// out[r,c] = sum_{n < len[r]} x[r,n,c] / len[r]   (entity_encoder.py:83-85).  Block = (row r, 32-entity slab) partial
+// sums would need a second pass; rows are short (<= 512 x 1 KB), so one block per row with 4 entity lanes per channel
+// quad keeps every load a coalesced float4 and finishes in shared memory.
+__global__ void __launch_bounds__(256)
+masked_mean_fwd_kernel(const float* __restrict__ x, const long long* __restrict__ len, float* __restrict__ out, int N, int C) {
+  const long long r = blockIdx.x;
+  const int c4n = C >> 2;                              // float4 columns
+  const int cq = threadIdx.x % c4n, lane_n = threadIdx.x / c4n, n_lanes = blockDim.x / c4n;
+  long long l = len[r];
+  l = l < 0 ? 0 : (l > N ? N : l);
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (lane_n < n_lanes) {
+    const float4* xr = reinterpret_cast<const float4*>(x + r * (long long)N * C);
+    for (int n = lane_n; n < (int)l; n += n_lanes) {
+      const float4 v = __ldg(xr + (long long)n * c4n + cq);
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+  }
+  extern __shared__ float4 s_mm[];                     // [n_lanes][c4n]
+  if (lane_n < n_lanes) s_mm[lane_n * c4n + cq] = acc;
+  __syncthreads();
+  if (threadIdx.x < c4n) {
+    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int k = 0; k < n_lanes; ++k) { const float4 v = s_mm[k * c4n + threadIdx.x]; t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w; }
+    const float inv = 1.f / (float)len[r];             // the reference divides by entity_num as given
+    reinterpret_cast<float4*>(out + r * C)[threadIdx.x] = make_float4(t.x * inv, t.y * inv, t.z * inv, t.w * inv);
+  }
+}
+// dx[r,n,c] = n < len[r] ? dout[r,c] / len[r] : 0
+__global__ void __launch_bounds__(256)
+masked_mean_bwd_kernel(const float* __restrict__ dout, const long long* __restrict__ len, float* __restrict__ dx, long long R,
+                       int N, int C) {
+  const int c4n = C >> 2;
+  const long long total = R * (long long)N * c4n;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long per_row = (long long)N * c4n;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const long long r = i / per_row;
+    const int rem = (int)(i - r * per_row);
+    const int n = rem / c4n, cq = rem - n * c4n;
+    const long long l = len[r];
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if ((long long)n < l) {
+      const float inv = 1.f / (float)l;
+      const float4 g = __ldg(reinterpret_cast<const float4*>(dout + r * C) + cq);
+      v = make_float4(g.x * inv, g.y * inv, g.z * inv, g.w * inv);
+    }
+    reinterpret_cast<float4*>(dx)[i] = v;
+  }
+}
+int masked_mean_fwd(const float* x, const long long* len, float* out, long long R, int N, int C, cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (C <= 0 || (C % 4) != 0 || C / 4 > 256 || N <= 0) return AS_ESIZE;
+  if (!x || !len || !out) return AS_EINVAL;
+  const int c4n = C / 4, n_lanes = 256 / c4n;
+  masked_mean_fwd_kernel<<<(unsigned)R, 256, n_lanes * c4n * 16, st>>>(x, len, out, N, C);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+int masked_mean_bwd(const float* dout, const long long* len, float* dx, long long R, int N, int C, cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (C <= 0 || (C % 4) != 0 || N <= 0) return AS_ESIZE;
+  if (!dout || !len || !dx) return AS_EINVAL;
+  long long blocks = (R * (long long)N * (C / 4) + 255) / 256;
+  masked_mean_bwd_kernel<<<(unsigned)(blocks < 148 * 16 ? blocks : 148 * 16), 256, 0, st>>>(dout, len, dx, R, N, C);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
 }  // namespace as

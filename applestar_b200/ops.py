@@ -121,11 +121,34 @@ def raise_if_negative_index():
             raise RuntimeError('negative one-hot index in entity_info')
 
 
+class _MaskedMean(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, entity_num):
+        R, N, Cc = x.shape
+        x = x.contiguous()
+        entity_num = entity_num.contiguous()
+        out = torch.empty((R, Cc), dtype=torch.float32, device=x.device)
+        _lib.call('as_masked_mean_fwd', x.data_ptr(), entity_num.data_ptr(), out.data_ptr(), R, N, Cc, _lib.stream_ptr())
+        ctx.dims = (R, N, Cc)
+        ctx.save_for_backward(entity_num)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (entity_num,) = ctx.saved_tensors
+        R, N, Cc = ctx.dims
+        dout = dout.contiguous()
+        dx = torch.empty((R, N, Cc), dtype=torch.float32, device=dout.device)
+        _lib.call('as_masked_mean_bwd', dout.data_ptr(), entity_num.data_ptr(), dx.data_ptr(), R, N, Cc, _lib.stream_ptr())
+        return dx, None
+
+
 def masked_mean(x, entity_num):
-    """sum over valid entities / entity_num (entity_encoder.py:83-85)."""
-    N = x.shape[1]
-    mask = torch.arange(N, device=x.device).unsqueeze(0) < entity_num.unsqueeze(1)
-    return (x * mask.unsqueeze(2)).sum(dim=1) / entity_num.unsqueeze(-1)
+    """[kernel] sum over valid entities / entity_num (entity_encoder.py:83-85)."""
+    require_cuda(x)
+    if x.dtype != torch.float32 or x.shape[-1] % 4 or x.shape[-1] > 1024:
+        raise RuntimeError('masked_mean: fp32 rows with C % 4 == 0 expected')
+    return _MaskedMean.apply(x, entity_num.long())
 
 
 def attention(qkv, key_len, heads, head_dim):

@@ -198,6 +198,12 @@ int as_softmax_fwd(const void* scores, const int64_t* key_len, void* probs, int6
 int as_softmax_bwd(const void* probs, const void* dprobs, void* dscores, int64_t rows, int Nk, int dprobs_bf16,
                    void* stream);
 
+/* Mean of the valid entity rows: out[r,c] = sum_{n < len[r]} x[r,n,c] / len[r] over x [R,N,C] fp32 (C % 4 == 0,
+ * C <= 1024) -- the mask multiply + sum + divide of entity_encoder.py:83-85; backward writes
+ * dx[r,n,c] = n < len[r] ? dout[r,c] / len[r] : 0. */
+int as_masked_mean_fwd(const float* x, const int64_t* len, float* out, int64_t R, int N, int C, void* stream);
+int as_masked_mean_bwd(const float* dout, const int64_t* len, float* dx, int64_t R, int N, int C, void* stream);
+
 /* Teacher-forced SelectedUnits pointer loop (head/action_arg_head.py:168-216) without the per-step one-hot tensors.
  * as_su_prefix_fwd: emb[r,i,:] = mean (sum when selected_units_num[r] == 0) of the key rows of the distinct units picked
  * at steps <= i before the end token (= entity_num[r]) -- the `one_hot`/`einsum`/division of :198-206 for all S steps;
