@@ -11,6 +11,7 @@ Module tree (names are the state_dict contract; do not rename):
   value_networks.<field>, core_lstm
 """
 import math
+import os
 
 import torch
 import torch.nn as nn
@@ -258,6 +259,43 @@ class ScalarEncoder(nn.Module):
         return torch.cat(emb, 1), torch.cat(ctx, 1), torch.cat(base, 1)
 
 
+_SIDE_STREAMS = {}
+
+
+class side_stream:
+    """Runs the enclosed (small-kernel) branch on a second CUDA stream, forked from and later joined to the current
+    one: the value towers and the scalar encoder are chains of ~100 launches that each fill a few SMs, and they do
+    not depend on the big kernels issued next to them.  Autograd replays the backward of the branch on the same
+    stream, so the overlap holds in both directions; CUDA-graph capture records the fork / join as graph edges."""
+
+    def __init__(self, device, enabled=True):
+        self.enabled = enabled and device.type == 'cuda' and os.environ.get('APPLESTAR_SIDE_STREAM', '1') == '1'
+        if self.enabled:
+            if device.index not in _SIDE_STREAMS:
+                _SIDE_STREAMS[device.index] = torch.cuda.Stream(device=device)
+            self.side = _SIDE_STREAMS[device.index]
+            self.main = torch.cuda.current_stream(device)
+
+    def __enter__(self):
+        if self.enabled:
+            self.side.wait_stream(self.main)
+            self.ctx = torch.cuda.stream(self.side)
+            self.ctx.__enter__()
+        return self
+
+    def __exit__(self, *exc):
+        if self.enabled:
+            self.ctx.__exit__(*exc)
+        return False
+
+    def join(self, tensors):
+        """Call on the main stream before the branch's results are consumed."""
+        if self.enabled:
+            self.main.wait_stream(self.side)
+            for t in tensors:
+                t.record_stream(self.main)
+
+
 class Encoder(nn.Module):
     """model/encoder.py:15-45."""
 
@@ -270,7 +308,9 @@ class Encoder(nn.Module):
         self.scatter_project = FC(256, 32, relu=True)
 
     def forward(self, spatial_info, entity_info, scalar_info, entity_num):
-        embedded_scalar, scalar_context, baseline_feature = self.scalar_encoder(scalar_info)
+        br = side_stream(entity_num.device)
+        with br:
+            embedded_scalar, scalar_context, baseline_feature = self.scalar_encoder(scalar_info)
         entity_embeddings, embedded_entity = self.entity_encoder(entity_info, entity_num)
         proj = self.scatter_project(entity_embeddings)
         # ScatterConnection ('add') + one-hot / effect planes + 1x1 project conv + ReLU in padded NHWC bf16
@@ -278,6 +318,7 @@ class Encoder(nn.Module):
         projected = spatial.spatial_project(proj, entity_info['x'], entity_info['y'], entity_num, spatial_info,
                                             pw.weight, pw.bias)
         embedded_spatial, map_skip = self.spatial_encoder(spatial_info, projected)
+        br.join([embedded_scalar, scalar_context, baseline_feature])
         lstm_input = torch.cat([embedded_scalar, embedded_entity, embedded_spatial], dim=-1)
         return lstm_input, scalar_context, baseline_feature, entity_embeddings, map_skip
 
@@ -615,6 +656,10 @@ class Model(nn.Module):
         state0 = [tuple(s.view(-1, B, hs)[0] for s in layer) for layer in hidden_state]     # t=0 state only (A12)
         out, _ = self.core_lstm(lstm_input.view(-1, B, lstm_input.shape[-1]), state0)
         out = out.reshape(-1, out.shape[-1])
+        critic_input = out.detach() if self.only_update_baseline else out
+        br = side_stream(out.device)
+        with br:                                                       # value towers next to the policy heads
+            values = {k: v(critic_input).view(T + 1, B) for k, v in self.value_networks.items()}
         ops.SU_STEPS_HINT = kwargs.get('selected_units_max')       # optional host-side int: avoids a device sync
         try:
             _, _, logits = self.policy.train_forward(out[:-B], ent[:-B], [None if m is None else m[:-B] for m in skip],
@@ -622,8 +667,7 @@ class Model(nn.Module):
                                                      selected_units_num.flatten(0, 1), self.cfg.temperature)
         finally:
             ops.SU_STEPS_HINT = None
-        critic_input = out.detach() if self.only_update_baseline else out
-        values = {k: v(critic_input).view(T + 1, B) for k, v in self.value_networks.items()}
+        br.join(list(values.values()))
         logits = {k: v.view(T, B, *v.shape[1:]) for k, v in logits.items()}
         su = logits['selected_units']
         if su.shape[2] < C.MAX_SELECTED_UNITS_NUM:                                           # model.py:156-158
