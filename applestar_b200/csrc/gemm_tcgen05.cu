@@ -885,12 +885,12 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ ws, float* __rest
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
     float4 s = accumulate ? reinterpret_cast<const float4*>(out)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
     int k = 0;
-    for (; k + 4 <= splits; k += 4) {
-      float4 v[4];
+    for (; k + 8 <= splits; k += 8) {
+      float4 v[8];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) v[u] = __ldg(reinterpret_cast<const float4*>(ws + (long long)(k + u) * n) + i);
+      for (int u = 0; u < 8; ++u) v[u] = __ldg(reinterpret_cast<const float4*>(ws + (long long)(k + u) * n) + i);
 #pragma unroll
-      for (int u = 0; u < 4; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
+      for (int u = 0; u < 8; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
     }
     for (; k < splits; ++k) {
       const float4 v = __ldg(reinterpret_cast<const float4*>(ws + (long long)k * n) + i);
@@ -918,10 +918,10 @@ __global__ void splitk_reduce_scalar_kernel(const float* __restrict__ ws, float*
 int splitk_reduce(const float* ws, float* out, long long n, int splits, int accumulate, cudaStream_t st) {
   if (n <= 0) return AS_OK;
   const bool vec = (n % 4 == 0) && ((reinterpret_cast<uintptr_t>(ws) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
-  long long blocks = ((vec ? n / 4 : n) + 127) / 128;
-  int grid = (int)(blocks < 148 * 8 ? (blocks > 0 ? blocks : 1) : 148 * 8);
-  if (vec) splitk_reduce_kernel<<<grid, 128, 0, st>>>(ws, out, n, splits, accumulate);
-  else splitk_reduce_scalar_kernel<<<grid, 128, 0, st>>>(ws, out, n, splits, accumulate);
+  long long blocks = ((vec ? n / 4 : n) + 63) / 64;
+  int grid = (int)(blocks < 148 * 16 ? (blocks > 0 ? blocks : 1) : 148 * 16);
+  if (vec) splitk_reduce_kernel<<<grid, 64, 0, st>>>(ws, out, n, splits, accumulate);
+  else splitk_reduce_scalar_kernel<<<grid, 64, 0, st>>>(ws, out, n, splits, accumulate);
   AS_LAUNCH_CHECK();
   return AS_OK;
 }

@@ -445,6 +445,94 @@ softmax_bwd_kernel(const __nv_bfloat16* __restrict__ p, const ST* __restrict__ d
   }
 }
 
+// bf16 scores, Nk a multiple of 256: a lane owns chunks of 8 consecutive keys (16-byte loads / stores); the scalar
+// kernels above move 2 bytes per lane per instruction and reach only half of the HBM rate on [*, 512] rows
+template <int CH>      // chunks of 8 keys per lane: Nk = 256 * CH
+__global__ void __launch_bounds__(256)
+softmax_fwd_v8_kernel(const __nv_bfloat16* __restrict__ s, const long long* __restrict__ key_len,
+                      __nv_bfloat16* __restrict__ p, long long rows, int Nq, int groups_per_len) {
+  constexpr int Nk = 256 * CH;
+  const int lane = threadIdx.x & 31;
+  const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long row = warp_global; row < rows; row += warps_total) {
+    int len = Nk;
+    if (key_len) {
+      const long long l = key_len[(row / Nq) / groups_per_len];
+      len = l < Nk ? (int)l : Nk;
+    }
+    float v[CH][8];
+    float m = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < CH; ++j) {
+      const int c0 = (lane + 32 * j) * 8;
+      uint4 q = make_uint4(0, 0, 0, 0);
+      if (c0 < len) q = __ldg(reinterpret_cast<const uint4*>(s + row * Nk + c0));
+      const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(&q);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        v[j][e] = (c0 + e < len) ? __bfloat162float(h[e]) : -INFINITY;
+        m = fmaxf(m, v[j][e]);
+      }
+    }
+    m = warp_max(m);
+    float sum = 0.f;
+#pragma unroll
+    for (int j = 0; j < CH; ++j)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int c = (lane + 32 * j) * 8 + e;
+        v[j][e] = (c < len) ? expf(v[j][e] - m) : 0.f;
+        sum += v[j][e];
+      }
+    const float inv = 1.f / warp_sum(sum);
+#pragma unroll
+    for (int j = 0; j < CH; ++j) {
+      uint4 q;
+      __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&q);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) h2[e] = __floats2bfloat162_rn(v[j][2 * e] * inv, v[j][2 * e + 1] * inv);
+      *reinterpret_cast<uint4*>(p + row * Nk + (lane + 32 * j) * 8) = q;
+    }
+  }
+}
+template <int CH>
+__global__ void __launch_bounds__(256)
+softmax_bwd_v8_kernel(const __nv_bfloat16* __restrict__ p, const __nv_bfloat16* __restrict__ dp,
+                      __nv_bfloat16* __restrict__ ds, long long rows) {
+  constexpr int Nk = 256 * CH;
+  const int lane = threadIdx.x & 31;
+  const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long row = warp_global; row < rows; row += warps_total) {
+    float pv[CH][8], dv[CH][8];
+    float dot = 0.f;
+#pragma unroll
+    for (int j = 0; j < CH; ++j) {
+      const uint4 qp = __ldg(reinterpret_cast<const uint4*>(p + row * Nk + (lane + 32 * j) * 8));
+      const uint4 qd = __ldg(reinterpret_cast<const uint4*>(dp + row * Nk + (lane + 32 * j) * 8));
+      const __nv_bfloat16* hp = reinterpret_cast<const __nv_bfloat16*>(&qp);
+      const __nv_bfloat16* hd = reinterpret_cast<const __nv_bfloat16*>(&qd);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        pv[j][e] = __bfloat162float(hp[e]);
+        dv[j][e] = __bfloat162float(hd[e]);
+        dot += pv[j][e] * dv[j][e];
+      }
+    }
+    dot = warp_sum(dot);
+#pragma unroll
+    for (int j = 0; j < CH; ++j) {
+      uint4 q;
+      __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&q);
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        h2[e] = __floats2bfloat162_rn(pv[j][2 * e] * (dv[j][2 * e] - dot), pv[j][2 * e + 1] * (dv[j][2 * e + 1] - dot));
+      *reinterpret_cast<uint4*>(ds + row * Nk + (lane + 32 * j) * 8) = q;
+    }
+  }
+}
+
 #define SM_DISPATCH(KERNEL, ST, ...)                                        \
   do {                                                                      \
     const int per = (Nk + 31) / 32;                                         \
@@ -462,7 +550,10 @@ int softmax_fwd(const void* s, const long long* key_len, void* p, long long grou
   if (Nk <= 0 || Nk > 1024 || groups_per_len <= 0) return AS_ESIZE;
   if (!s || !p) return AS_EINVAL;
   const int grid = ln_grid(rows);
-  if (scores_bf16) SM_DISPATCH(softmax_fwd_kernel, __nv_bfloat16, reinterpret_cast<const __nv_bfloat16*>(s), key_len, reinterpret_cast<__nv_bfloat16*>(p), rows, Nq, Nk, groups_per_len);
+  const bool al16 = ((reinterpret_cast<uintptr_t>(s) | reinterpret_cast<uintptr_t>(p)) & 15) == 0;
+  if (scores_bf16 && al16 && Nk == 512) softmax_fwd_v8_kernel<2><<<grid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(s), key_len, reinterpret_cast<__nv_bfloat16*>(p), rows, Nq, groups_per_len);
+  else if (scores_bf16 && al16 && Nk == 256) softmax_fwd_v8_kernel<1><<<grid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(s), key_len, reinterpret_cast<__nv_bfloat16*>(p), rows, Nq, groups_per_len);
+  else if (scores_bf16) SM_DISPATCH(softmax_fwd_kernel, __nv_bfloat16, reinterpret_cast<const __nv_bfloat16*>(s), key_len, reinterpret_cast<__nv_bfloat16*>(p), rows, Nq, Nk, groups_per_len);
   else SM_DISPATCH(softmax_fwd_kernel, float, reinterpret_cast<const float*>(s), key_len, reinterpret_cast<__nv_bfloat16*>(p), rows, Nq, Nk, groups_per_len);
   AS_LAUNCH_CHECK();
   return AS_OK;
@@ -473,7 +564,10 @@ int softmax_bwd(const void* p, const void* dp, void* ds, long long rows, int Nk,
   if (Nk <= 0 || Nk > 1024) return AS_ESIZE;
   if (!p || !dp || !ds) return AS_EINVAL;
   const int grid = ln_grid(rows);
-  if (dprobs_bf16) SM_DISPATCH(softmax_bwd_kernel, __nv_bfloat16, reinterpret_cast<const __nv_bfloat16*>(p), reinterpret_cast<const __nv_bfloat16*>(dp), reinterpret_cast<__nv_bfloat16*>(ds), rows, Nk);
+  const bool al16 = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(dp) | reinterpret_cast<uintptr_t>(ds)) & 15) == 0;
+  if (dprobs_bf16 && al16 && Nk == 512) softmax_bwd_v8_kernel<2><<<grid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(p), reinterpret_cast<const __nv_bfloat16*>(dp), reinterpret_cast<__nv_bfloat16*>(ds), rows);
+  else if (dprobs_bf16 && al16 && Nk == 256) softmax_bwd_v8_kernel<1><<<grid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(p), reinterpret_cast<const __nv_bfloat16*>(dp), reinterpret_cast<__nv_bfloat16*>(ds), rows);
+  else if (dprobs_bf16) SM_DISPATCH(softmax_bwd_kernel, __nv_bfloat16, reinterpret_cast<const __nv_bfloat16*>(p), reinterpret_cast<const __nv_bfloat16*>(dp), reinterpret_cast<__nv_bfloat16*>(ds), rows, Nk);
   else SM_DISPATCH(softmax_bwd_kernel, float, reinterpret_cast<const __nv_bfloat16*>(p), reinterpret_cast<const float*>(dp), reinterpret_cast<__nv_bfloat16*>(ds), rows, Nk);
   AS_LAUNCH_CHECK();
   return AS_OK;
