@@ -81,7 +81,7 @@ def _wgrad(dy16, x16, n_out, k_in):
     """dW[n_out, k_in] = dY^T X with both operands read MN-major (no transposes); split-K over the rows."""
     M = dy16.shape[0]
     tiles = ((n_out + 127) // 128) * ((k_in + 255) // 256 if k_in > 128 else 1)
-    want = max(1, min((M + 63) // 64, (2 * NUM_SMS) // max(tiles, 1)))
+    want = max(1, min((M + 63) // 64, NUM_SMS // max(tiles, 1)))
     splits = _lib.lib().as_gemm_splits(M, want)
     dw = torch.empty((n_out, k_in), dtype=torch.float32, device=dy16.device)
     if splits > 1:

@@ -82,7 +82,7 @@ class ConvNHWC(torch.autograd.Function):
         if ctx.needs_input_grad[1]:
             P = R * (H + 2) * (W + 2)
             tiles = taps * ((cout + 127) // 128) * max(1, (cin_p + 255) // 256)
-            want = max(1, min((P + 63) // 64, (2 * K.NUM_SMS) // tiles))
+            want = max(1, min((P + 63) // 64, K.NUM_SMS // tiles))
             splits = _lib.lib().as_gemm_splits(P, want)
             dw9 = torch.empty((taps, cout, cin_p), dtype=torch.float32, device=x.device)
             ws = torch.empty((splits, taps, cout, cin_p), dtype=torch.float32, device=x.device) if splits > 1 else None
@@ -375,7 +375,7 @@ class SpatialProject(torch.autograd.Function):
         scratch = torch.empty(_lib.lib().as_colsum_scratch_floats(cout), dtype=torch.float32, device=dy.device)
         _lib.call('as_relu_bwd_colsum_bf16', dy.data_ptr(), out.data_ptr(), dz.data_ptr(), db.data_ptr(),
                   scratch.data_ptr(), P, cout, st)
-        splits = _lib.lib().as_gemm_splits(P, 2 * K.NUM_SMS)
+        splits = _lib.lib().as_gemm_splits(P, K.NUM_SMS)
         dw1 = torch.empty((1, cout, 64), dtype=torch.float32, device=dy.device)
         ws = torch.empty((splits, 1, cout, 64), dtype=torch.float32, device=dy.device) if splits > 1 else None
         _lib.call('as_conv_wgrad_nhwc_bf16', dz.data_ptr(), feats.data_ptr(), dw1.data_ptr(), _ptr(ws), R, H, W, 64, cout,
