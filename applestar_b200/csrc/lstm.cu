@@ -279,6 +279,11 @@ __global__ void __launch_bounds__(kLstmThreads) lnlstm_bwd_kernel(const LstmBwd 
 }
 
 bool lnlstm_cluster_ok(int H);
+int lnlstm_small_fwd(const float*, const float*, const float*, const void*, const float*, const float*, const float*,
+                     const float*, float*, float*, float*, float*, float*, int, int, cudaStream_t);
+int lnlstm_small_bwd(const float*, const float*, const float*, const float*, const float*, const float*, const void*,
+                     const float*, const float*, const float*, const float*, const float*, const float*, const float*,
+                     float*, float*, float*, float*, float*, int, int, cudaStream_t);
 int lnlstm_fwd_cluster(const float*, const float*, const float*, const void*, const float*, const float*, const float*,
                        const float*, float*, float*, float*, float*, float*, int, int, int, cudaStream_t);
 int lnlstm_bwd_cluster(const float*, const float*, const float*, const float*, const float*, const float*, const void*,
@@ -291,6 +296,8 @@ int lnlstm_fwd(const float* gi, const float* h0, const float* c0, const void* wh
   if (T <= 0 || B <= 0) return AS_OK;
   if (H <= 0 || (H % 8) != 0 || H > 2 * kLstmThreads) return AS_ESIZE;
   if (!gi || !h0 || !c0 || !whh || !gh_w || !gh_b || !gc_w || !gc_b || !y || !c_all) return AS_EINVAL;
+  if (H == 32)                   // warp per trajectory (lstm_small.cu)
+    return lnlstm_small_fwd(gi, h0, c0, whh, gh_w, gh_b, gc_w, gc_b, y, c_all, u_all, z_all, stats, T, B, st);
   if (lnlstm_cluster_ok(H))      // W_hh slices resident in shared memory, 8 CTAs per trajectory (lstm_cluster.cu)
     return lnlstm_fwd_cluster(gi, h0, c0, whh, gh_w, gh_b, gc_w, gc_b, y, c_all, u_all, z_all, stats, T, B, H, st);
   LstmFwd p{gi, h0, c0, reinterpret_cast<const __nv_bfloat16*>(whh), gh_w, gh_b, gc_w, gc_b, y, c_all, u_all, z_all, stats, T, B, H};
@@ -307,6 +314,9 @@ int lnlstm_bwd(const float* gi, const float* h0, const float* c0, const float* y
   if (T <= 0 || B <= 0) return AS_OK;
   if (H <= 0 || (H % 8) != 0 || H > 2 * kLstmThreads) return AS_ESIZE;
   if (!gi || !c0 || !c_all || !u_all || !z_all || !stats || !whh_t || !dgi || !du || !dparam) return AS_EINVAL;
+  if (H == 32)
+    return lnlstm_small_bwd(gi, c0, c_all, u_all, z_all, stats, whh_t, gh_w, gh_b, gc_w, gc_b, dy, dhT, dcT, dgi, du, dh0,
+                            dc0, dparam, T, B, st);
   if (lnlstm_cluster_ok(H))
     return lnlstm_bwd_cluster(gi, c0, c_all, u_all, z_all, stats, whh_t, gh_w, gh_b, gc_w, gc_b, dy, dhT, dcT, dgi, du,
                               dh0, dc0, dparam, T, B, H, st);
