@@ -482,7 +482,7 @@ softmax_fwd_v8_kernel(const __nv_bfloat16* __restrict__ s, const long long* __re
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
         const int c = (lane + 32 * j) * 8 + e;
-        v[j][e] = (c < len) ? expf(v[j][e] - m) : 0.f;
+        v[j][e] = (c < len) ? __expf(v[j][e] - m) : 0.f;
         sum += v[j][e];
       }
     const float inv = 1.f / warp_sum(sum);

@@ -146,6 +146,16 @@ class LinearFn(torch.autograd.Function):
             _lib.call('as_linear_bwd_prep', dy2.data_ptr(), _ptr(y32), _ptr(y16), dy16b.data_ptr(), _ptr(db),
                       _ptr(scratch) if want_db else 0, M, N, _lib.stream_ptr())
             want_db = False
+        elif (ctx.relu and want_db and dy2.dtype == torch.bfloat16 and y is not None and y.dtype == torch.bfloat16
+              and N % 8 == 0 and dy2.is_contiguous() and y.is_contiguous()):
+            # bf16 gradient of a ReLU layer with bias (FFN hidden): mask and bias gradient in one pass
+            dy16b = torch.empty((M, N), dtype=torch.bfloat16, device=dy.device)
+            db = torch.empty(N, dtype=torch.float32, device=dy.device)
+            scratch = torch.empty(_lib.lib().as_colsum_scratch_floats(N), dtype=torch.float32, device=dy.device)
+            _lib.call('as_relu_bwd_colsum_bf16', dy2.data_ptr(), y.data_ptr(), dy16b.data_ptr(), db.data_ptr(),
+                      scratch.data_ptr(), M, N, _lib.stream_ptr())
+            dy2 = dy16b
+            want_db = False
         else:
             if ctx.relu:
                 dy2 = relu_backward(dy2, y)
