@@ -18,6 +18,14 @@ _ERR = {-1: 'AS_EINVAL (bad pointer / argument)', -2: 'AS_ESIZE (size out of ran
         -3: 'AS_EALIGN (pointer or pitch not 16-byte aligned)', -4: 'AS_EUNSUPPORTED', -5: 'AS_EDRIVER (tensor-map encode failed)'}
 
 
+class AsSuSampleArgs(ctypes.Structure):
+    """as_su_sample_args (include/applestar_b200.h)."""
+    PTRS = ('key', 'c0', 'c1', 'mt', 'wf1t', 'bf1', 'wq2t', 'bq2', 'wih_t', 'whh_t', 'ln_i_w', 'ln_i_b', 'ln_h_w', 'ln_h_b',
+            'ln_c_w', 'ln_c_b', 'entity_num', 'su_mask', 'noise', 'logits', 'units', 'num', 'extra', 'emb', 'steps_row')
+    _fields_ = [(n, c_void_p) for n in PTRS] + [('R', c_int32), ('N1', c_int32), ('S', c_int32), ('extra_units', c_int32),
+                                                  ('temperature', c_float)]
+
+
 class AsLossArgs(ctypes.Structure):
     _fields_ = [
         ('T', c_int32), ('B', c_int32), ('F', c_int32), ('S', c_int32), ('N1', c_int32), ('NE', c_int32),
@@ -78,6 +86,7 @@ _SIGS = {
     'as_su_prefix_fwd': (c_int, [c_void_p] * 7 + [c_int64, c_int, c_int, c_int, c_int, c_void_p]),
     'as_su_prefix_bwd': (c_int, [c_void_p] * 6 + [c_int64, c_int, c_int, c_int, c_int, c_void_p]),
     'as_su_mask_logits': (c_int, [c_void_p] * 4 + [c_int64, c_int, c_int, c_int, c_float, c_float, c_void_p]),
+    'as_su_sample': (c_int, [POINTER(AsSuSampleArgs), c_void_p]),
     'as_masked_mean_fwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
     'as_masked_mean_bwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
     'as_linear_bwd_prep': (c_int, [c_void_p] * 6 + [c_int64, c_int, c_void_p]),

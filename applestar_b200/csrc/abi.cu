@@ -2,6 +2,7 @@
 #include "common.cuh"
 #include "gemm.h"
 #include "loss.h"
+#include "su_sample.h"
 
 namespace as {
 extern int g_gemm_debug;
@@ -78,7 +79,7 @@ int maxpool2_bwd(const void*, const void*, void*, long long, int, int, int, cuda
 
 extern "C" {
 
-int as_abi_version(void) { return 4; }
+int as_abi_version(void) { return 5; }
 
 // diagnostics only (not part of the public header): 0 normal, 1 GEMM epilogue skips global stores, 2 only drains TMEM
 // bit 3: register-store epilogue, bit 4: per-tap convolution mode
@@ -272,6 +273,17 @@ int as_su_mask_logits(const float* x, const int64_t* selected_units, const int64
                       int Smax, int S, float scale, float fill, void* stream) {
   return as::su_mask_logits(x, reinterpret_cast<const long long*>(selected_units), reinterpret_cast<const long long*>(entity_num), out,
                             R, N1, Smax, S, scale, fill, ST(stream));
+}
+int as_su_sample(const as_su_sample_args* a, void* stream) {
+  if (!a) return AS_EINVAL;
+  as::SuSampleDev p;
+  p.key = a->key; p.c0 = a->c0; p.c1 = a->c1; p.mt = a->mt; p.wf1t = a->wf1t; p.bf1 = a->bf1; p.wq2t = a->wq2t; p.bq2 = a->bq2;
+  p.wih_t = a->wih_t; p.whh_t = a->whh_t; p.ln_i_w = a->ln_i_w; p.ln_i_b = a->ln_i_b; p.ln_h_w = a->ln_h_w; p.ln_h_b = a->ln_h_b;
+  p.ln_c_w = a->ln_c_w; p.ln_c_b = a->ln_c_b; p.entity_num = reinterpret_cast<const long long*>(a->entity_num);
+  p.su_mask = a->su_mask; p.noise = a->noise; p.logits = a->logits; p.units = reinterpret_cast<long long*>(a->units);
+  p.num = reinterpret_cast<long long*>(a->num); p.extra = a->extra; p.emb = a->emb; p.steps_row = a->steps_row;
+  p.R = a->R; p.N1 = a->N1; p.S = a->S; p.extra_units = a->extra_units; p.temperature = a->temperature;
+  return as::su_sample(p, ST(stream));
 }
 int as_masked_mean_fwd(const float* x, const int64_t* len, float* out, int64_t R, int N, int C, void* stream) {
   return as::masked_mean_fwd(x, reinterpret_cast<const long long*>(len), out, R, N, C, ST(stream));

@@ -280,3 +280,73 @@ class LearnerStep:
             return None
         entry = self._graphs.get(key) or self._capture(data, key)
         return entry[1]
+
+
+class ActorStep:
+    """Batched actor inference (`Model.compute_logp_action`, model.py:82-116 of the reference) replayed from a CUDA
+    graph.  The sampling pointer loop always runs its 64 steps inside the graph; the reference's early `break`
+    (action_arg_head.py:309-310) is reproduced after the replay by one host read of the loop's step count and a trim
+    of the selected-units tensors, so the results equal the eager call's.  One graph per (batch, entity) shape.
+
+    The returned tensors are views of the graph's static output buffers: they are overwritten by the next call, so a
+    caller that keeps them (e.g. to build a trajectory) clones what it needs.  `hidden_state` may be fed back directly:
+    inputs are copied into separate static buffers before the replay."""
+
+    def __init__(self, model, use_graph=True):
+        self.model = model.eval()
+        self.use_graph = use_graph
+        self._graphs = {}
+        self._pool = None
+        self.launches_per_call = None
+
+    def _run(self, static, defer):
+        with torch.no_grad():
+            return self.model.compute_logp_action(static['spatial_info'], static['entity_info'], static['scalar_info'],
+                                                  static['entity_num'], static['hidden_state'],
+                                                  gumbel_noise=static['gumbel_noise'], defer_checks=defer,
+                                                  defer_trim=defer)
+
+    def _capture(self, data, key):
+        dev = next(self.model.parameters()).device
+        static = _tree_to(data, dev)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                self._run(static, True)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        n0 = _lib.LAUNCHES
+        with torch.cuda.graph(graph, pool=self._pool):
+            out = self._run(static, True)
+        self.launches_per_call = _lib.LAUNCHES - n0
+        if self._pool is None:
+            self._pool = graph.pool()
+        out['_neg_flag'] = K.entity_embed.last_neg_flag            # zeroed and written inside the graph
+        K.entity_embed.last_neg_flag = None
+        self._graphs[key] = (graph, static, out)
+        return self._graphs[key]
+
+    def __call__(self, spatial_info, entity_info, scalar_info, entity_num, hidden_state, gumbel_noise=None):
+        from . import ops
+        if gumbel_noise is None:
+            gumbel_noise = ops.fresh_gumbel(entity_num.shape[0], entity_info['x'].shape[1], entity_num.device)
+        data = {'spatial_info': spatial_info, 'entity_info': entity_info, 'scalar_info': scalar_info,
+                'entity_num': entity_num, 'hidden_state': hidden_state, 'gumbel_noise': gumbel_noise}
+        if not self.use_graph:
+            return self._run(data, False)
+        key = (int(entity_num.shape[0]), tuple(gumbel_noise['selected_units'].shape))
+        entry = self._graphs.get(key) or self._capture(data, key)
+        graph, static, out = entry
+        _tree_copy_(static, data)
+        graph.replay()
+        host = torch.stack([out['selected_units_steps'].to(torch.int64), out['_neg_flag'].view(-1)[0].to(torch.int64)])
+        steps, neg = host.tolist()                                # the call's one host read
+        if neg != 0:
+            raise RuntimeError('negative one-hot index in entity_info')
+        res = {k: v for k, v in out.items() if k not in ('selected_units_steps', '_neg_flag')}
+        for name in ('logit', 'action_info', 'action_logp'):
+            res[name] = dict(out[name])
+            res[name]['selected_units'] = out[name]['selected_units'][:, :steps]
+        return res

@@ -613,8 +613,9 @@ class Model(nn.Module):
             noise = ops.fresh_gumbel(rows, n_entity, device)
         return noise
 
-    def _encode_core(self, spatial_info, entity_info, scalar_info, entity_num, hidden_state):
-        ops.raise_if_negative_index()
+    def _encode_core(self, spatial_info, entity_info, scalar_info, entity_num, hidden_state, defer_checks=False):
+        if not defer_checks:
+            ops.raise_if_negative_index()
         lstm_input, ctx, base, ent, skip = self.encoder(spatial_info, entity_info, scalar_info, entity_num)
         out, state = self.core_lstm(lstm_input.unsqueeze(0), hidden_state)
         return out.squeeze(0), state, ctx, base, ent, skip
@@ -628,13 +629,24 @@ class Model(nn.Module):
         return action, sun, state
 
     def compute_logp_action(self, spatial_info, entity_info, scalar_info, entity_num, hidden_state, **kwargs):
+        """model.py:82-116.  `defer_checks` / `defer_trim` (used by learner.ActorStep) keep the call free of host reads
+        so that it can be captured into a CUDA graph: the selected-units tensors then keep all 64 steps and the
+        reference's step count comes back as the device scalar `selected_units_steps`."""
         out, state, ctx, _, ent, skip = self._encode_core(spatial_info, entity_info, scalar_info, entity_num,
-                                                          hidden_state)
+                                                          hidden_state, kwargs.get('defer_checks', False))
         noise = self._noise(kwargs, out.shape[0], ent.shape[1], out.device)
-        action, sun, logit, extra = self.policy(out, ent, skip, ctx, entity_num, self.cfg.temperature, noise)
+        ops.SU_DEFER_TRIM = [] if kwargs.get('defer_trim', False) else None
+        try:
+            action, sun, logit, extra = self.policy(out, ent, skip, ctx, entity_num, self.cfg.temperature, noise)
+            steps = ops.SU_DEFER_TRIM[0] if ops.SU_DEFER_TRIM else None
+        finally:
+            ops.SU_DEFER_TRIM = None
         logp = {k: ops.categorical_log_prob(logit[k], action[k]) for k in action}
-        return {'action_info': action, 'action_logp': logp, 'selected_units_num': sun, 'entity_num': entity_num,
-                'hidden_state': state, 'logit': logit, 'extra_units': extra}
+        res = {'action_info': action, 'action_logp': logp, 'selected_units_num': sun, 'entity_num': entity_num,
+               'hidden_state': state, 'logit': logit, 'extra_units': extra}
+        if steps is not None:
+            res['selected_units_steps'] = steps
+        return res
 
     def compute_teacher_logit(self, spatial_info, entity_info, scalar_info, entity_num, hidden_state,
                               selected_units_num, action_info, **kwargs):

@@ -6,6 +6,7 @@ stock ATen/cuBLAS/cuDNN CUDA ops and are the replacement queue documented in DES
 falls back to the CPU: `require_cuda` raises, and `_lib` raises if the shared library is missing.
 """
 import math
+import os
 
 import torch
 import torch.nn.functional as F
@@ -267,6 +268,8 @@ def _su_step(head, ae, h, c):
     return out[0], h, c
 
 
+SU_DEFER_TRIM = None     # a list while an actor step is being captured into a CUDA graph: the sampling loop appends its
+                         # device-side step count there and returns untrimmed [R, 64, ...] tensors (learner.ActorStep)
 SU_STEPS_HINT = None     # host-side max(selected_units_num) supplied by the caller (e.g. the collate step, which has it
                          # on the CPU for free); lets the learner step run without any device->host sync
 
@@ -388,8 +391,73 @@ def selected_units_train_loop(head, key, ae0, entity_num, selected_units, select
     return logits, selected_units, ae, selected_units_num, None
 
 
+def _su_sample_weights(head):
+    """fp32 operands of the fused sampling kernel, derived from the head's weights and cached until they change:
+    mt = (Wq1 Wf2)^T, c1 = Wq1 bf2 (see su_sample.cu) and the transposed small matrices."""
+    cell = head.lstm.layers[0].cell
+    src = (head.query_fc1[0].weight, head.query_fc1[0].bias, head.query_fc2[0].weight, head.query_fc2[0].bias,
+           head.embed_fc1[0].weight, head.embed_fc1[0].bias, head.embed_fc2[0].weight, head.embed_fc2[0].bias,
+           cell.weight_ih, cell.weight_hh)
+    tag = (K._SHADOW_GEN[0],) + tuple((t._version, t.data_ptr()) for t in src)
+    hit = getattr(head, '_su_sample_cache', None)
+    if hit is not None and hit[0] == tag:
+        return hit[1]
+    with torch.no_grad():
+        wq1, bq1, wq2, bq2, wf1, bf1, wf2, bf2, wih, whh = (t.detach().float() for t in src)
+        w = {'mt': (wq1 @ wf2).t().contiguous(), 'c1': (wq1 @ bf2).contiguous(), 'wq1t': wq1.t().contiguous(), 'bq1': bq1,
+             'wf1t': wf1.t().contiguous(), 'bf1': bf1.contiguous(), 'wq2t': wq2.t().contiguous(), 'bq2': bq2.contiguous(),
+             'wih_t': wih.t().contiguous(), 'whh_t': whh.t().contiguous()}
+    head._su_sample_cache = (tag, w)
+    return w
+
+
 def selected_units_sample(head, key, ae0, entity_num, su_mask, noise, temperature, extra_units):
-    """Sampling pointer loop (action_arg_head.py:262-313) with Gumbel-max picks; runs all 64 steps on the
+    """Sampling pointer loop (action_arg_head.py:262-313): one launch of the fused kernel (su_sample.cu) for all 64
+    steps, then the reference's early-break trim.  `APPLESTAR_SU_FUSED=0` selects the step-by-step loop below."""
+    if os.environ.get('APPLESTAR_SU_FUSED', '1') == '0' or torch.is_grad_enabled() and (key.requires_grad or ae0.requires_grad):
+        return selected_units_sample_loop(head, key, ae0, entity_num, su_mask, noise, temperature, extra_units)
+    require_cuda(key)
+    R, N1, D = key.shape
+    S = C.MAX_SELECTED_UNITS_NUM
+    dev = key.device
+    w = _su_sample_weights(head)
+    cell = head.lstm.layers[0].cell
+    key = key.float().contiguous()
+    c0 = torch.addmm(w['bq1'], ae0.float(), w['wq1t'])                    # query_fc1(ae0) pre-activation, fp32
+    noise = noise.float().contiguous()
+    entity_num = entity_num.long().contiguous()
+    mask8 = su_mask.to(torch.uint8).contiguous()
+    logits = torch.empty(R, S, N1, device=dev)
+    units = torch.empty(R, S, dtype=torch.long, device=dev)
+    num = torch.empty(R, dtype=torch.long, device=dev)
+    extra = torch.empty(R, N1, device=dev)
+    emb = torch.empty(R, D, device=dev)
+    steps_row = torch.empty(R, dtype=torch.int32, device=dev)
+    li, lh, lc = cell.layernorm_i, cell.layernorm_h, cell.layernorm_c
+    a = _lib.AsSuSampleArgs()
+    for name, t in (('key', key), ('c0', c0), ('c1', w['c1']), ('mt', w['mt']), ('wf1t', w['wf1t']), ('bf1', w['bf1']),
+                    ('wq2t', w['wq2t']), ('bq2', w['bq2']), ('wih_t', w['wih_t']), ('whh_t', w['whh_t']),
+                    ('ln_i_w', li.weight), ('ln_i_b', li.bias), ('ln_h_w', lh.weight), ('ln_h_b', lh.bias),
+                    ('ln_c_w', lc.weight), ('ln_c_b', lc.bias), ('entity_num', entity_num), ('su_mask', mask8),
+                    ('noise', noise), ('logits', logits), ('units', units), ('num', num), ('extra', extra), ('emb', emb),
+                    ('steps_row', steps_row)):
+        assert t.is_contiguous() and t.device == dev
+        setattr(a, name, t.data_ptr())
+    a.R, a.N1, a.S, a.extra_units, a.temperature = R, N1, S, int(bool(extra_units)), float(temperature)
+    import ctypes
+    _lib.call('as_su_sample', ctypes.byref(a), _lib.stream_ptr())
+    ae = ae0 + head.embed_fc2(head.embed_fc1(emb))
+    steps_dev = steps_row.max().clamp(min=1).long()
+    if SU_DEFER_TRIM is not None:       # graph capture: keep all S steps, hand the count out as a device scalar
+        SU_DEFER_TRIM.append(steps_dev)
+    else:
+        steps = int(steps_dev.item())                                    # one host read
+        logits, units = logits[:, :steps], units[:, :steps]
+    return logits, units, ae, num, extra
+
+
+def selected_units_sample_loop(head, key, ae0, entity_num, su_mask, noise, temperature, extra_units):
+    """Step-by-step form of the sampling pointer loop (action_arg_head.py:262-313) with Gumbel-max picks; runs all 64 steps on the
     device without the per-step `end_flag.all()` host sync, then trims to the reference's step count."""
     R, N1, D = key.shape
     dev = key.device
@@ -398,7 +466,8 @@ def selected_units_sample(head, key, ae0, entity_num, su_mask, noise, temperatur
     h = key.new_zeros(R, 32)
     c = key.new_zeros(R, 32)
     lm = torch.arange(N1, device=dev).unsqueeze(0) < (entity_num + 1).unsqueeze(1)
-    lm[ar, entity_num] = False
+    end_col = entity_num.long().unsqueeze(1)
+    lm.scatter_(1, end_col, False)              # scalar scatter: no host tensor, safe under graph capture
     num = torch.where(su_mask, torch.full((R,), S, dtype=torch.long, device=dev), torch.zeros(R, dtype=torch.long, device=dev))
     end_flag = ~su_mask
     one_hot = key.new_zeros(R, N1)
@@ -410,8 +479,8 @@ def selected_units_sample(head, key, ae0, entity_num, su_mask, noise, temperatur
     for i in range(S):
         if i > 0:
             if i == 1:
-                lm[ar, entity_num] = True
-            lm[ar, result] = False
+                lm.scatter_(1, end_col, True)
+            lm.scatter_(1, result.unsqueeze(1), False)
         q, h, c = _su_step(head, ae, h, c)
         step_logits = torch.einsum('rk,rnk->rn', q, key).masked_fill(~lm, -1e9)
         if temperature != 1.0:
@@ -433,8 +502,12 @@ def selected_units_sample(head, key, ae0, entity_num, su_mask, noise, temperatur
         units.append(result)
         done = done | end_flag.all()
         all_ended.append(done)
-    steps = int((~torch.stack(all_ended)).sum().item()) + 1     # one host read for the whole loop
-    steps = min(steps, S)
+    steps_dev = ((~torch.stack(all_ended)).sum() + 1).clamp(max=S)
+    if SU_DEFER_TRIM is not None:       # graph capture: keep all S steps, hand the count out as a device scalar
+        SU_DEFER_TRIM.append(steps_dev)
+        steps = S
+    else:
+        steps = int(steps_dev.item())                            # one host read for the whole loop
     logits = torch.stack(logits[:steps], dim=1)
     units = torch.stack(units[:steps], dim=1)
     extra = key.new_zeros(R, N1)

@@ -219,6 +219,33 @@ int as_su_prefix_bwd(const float* demb, const int64_t* selected_units, const int
 int as_su_mask_logits(const float* x, const int64_t* selected_units, const int64_t* entity_num, float* out, int64_t R, int N1,
                       int Smax, int S, float scale, float fill, void* stream);
 
+/* as_su_sample: the whole SelectedUnits SAMPLING loop (head/action_arg_head.py:262-313: up to 64 autoregressive picks
+ * per row) in one launch.  query_fc1 o (ae0 + embed_fc2(.)) is folded by the caller into c0 = Wq1 ae0 + bq1 [R,256],
+ * c1 = Wq1 bf2 [256] and mt = (Wq1 Wf2)^T [256,256]; wf1t/wq2t/wih_t/whh_t are the transposed fp32 weights of
+ * embed_fc1, query_fc2 and the H=32 LN-LSTM cell (lstm.py:138-153).  noise [S,R,N1] is Gumbel(0,1) (arg-max of
+ * logits + noise == the reference's multinomial draw).  Writes logits [R,S,N1] (masked -1e9, / temperature), units
+ * [R,S], num [R] (selected_units_num, :283), extra [R,N1] (:307-309), emb [R,32] (mean picked key after the last
+ * step) and steps_row [R]: the reference's loop length (:305 early break) is max(1, max_r steps_row[r]). */
+#ifndef AS_SU_SAMPLE_ARGS_DEFINED
+#define AS_SU_SAMPLE_ARGS_DEFINED
+typedef struct as_su_sample_args {
+  const float *key, *c0, *c1, *mt, *wf1t, *bf1, *wq2t, *bq2, *wih_t, *whh_t;
+  const float *ln_i_w, *ln_i_b, *ln_h_w, *ln_h_b, *ln_c_w, *ln_c_b;
+  const int64_t* entity_num;
+  const uint8_t* su_mask;
+  const float* noise;
+  float* logits;
+  int64_t* units;
+  int64_t* num;
+  float* extra;
+  float* emb;
+  int* steps_row;
+  int R, N1, S, extra_units;
+  float temperature;
+} as_su_sample_args;
+#endif
+int as_su_sample(const as_su_sample_args* args, void* stream);
+
 /* bf16 feature rows for the entity embedding GEMM -- replaces the 28 embedding lookups + torch.cat at
  * obs_encoder/entity_encoder.py:60-78.  Per field f: data[f] = device array [rows] of element type dtype[f]
  * (0 u8, 1 i8, 2 i16, 3 f16, 4 i64, 5 f32), kind[f] (0 one-hot clamped to num-1, 1 num-bit binary MSB first,

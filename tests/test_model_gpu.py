@@ -6,6 +6,7 @@ import torch
 
 from applestar_b200 import config as C, synth, tables
 from oracle import restate as R
+from oracle import restate as R_
 from util import clone_tree, golden, load_spec
 
 gpu = pytest.mark.gpu
@@ -136,6 +137,91 @@ def test_cuda_graph_learner_step_matches_eager():
     assert abs(l_e - l_g) <= 1e-3 * max(1.0, abs(l_e)), (l_e, l_g)
     info = graph_step(data)
     assert 'winloss/td' in info and isinstance(info['kl/total'], float)
+
+
+@gpu
+def test_actor_step_graph_matches_eager():
+    """learner.ActorStep (compute_logp_action replayed from a CUDA graph, 64 pointer steps inside, trim outside) returns
+    the eager call's tensors: same kernels on the same inputs, so sampled actions and step count are bit-exact."""
+    from applestar_b200.learner import ActorStep
+    model, _ = _model(['winloss'], 'winloss')
+    model.eval()
+    B, N = 6, 48
+    dev = torch.device('cuda')
+    outs = []
+    actor = ActorStep(model)
+    for seed in (3, 4):                      # second call replays the graph captured by the first
+        data = synth.tree_map(lambda t: t.to(dev), synth.gen_observations(B, N, seed, entity_num_range=(N // 2, N)))
+        noise = synth.tree_map(lambda t: t.to(dev), synth.gen_gumbel(B, seed + 10, N))
+        with torch.no_grad():
+            eager = model.compute_logp_action(gumbel_noise=noise, **data)
+        graphed = actor(data['spatial_info'], data['entity_info'], data['scalar_info'], data['entity_num'],
+                        data['hidden_state'], gumbel_noise=noise)
+        outs.append((eager, graphed))
+        assert 'selected_units_steps' not in graphed
+        for k in eager['action_info']:
+            assert torch.equal(eager['action_info'][k], graphed['action_info'][k]), k
+            assert eager['logit'][k].shape == graphed['logit'][k].shape, k
+            assert (eager['logit'][k] - graphed['logit'][k]).abs().max().item() < 1e-3, k
+        assert torch.equal(eager['selected_units_num'], graphed['selected_units_num'])
+        assert torch.equal(eager['extra_units'], graphed['extra_units'])
+        for (h0, c0), (h1, c1) in zip(eager['hidden_state'], graphed['hidden_state']):
+            assert (h0 - h1).abs().max().item() < 1e-4 and (c0 - c1).abs().max().item() < 1e-4
+    assert actor.launches_per_call > 100 and len(actor._graphs) == 1
+    bad = synth.tree_map(lambda t: t.to(dev), synth.gen_observations(B, N, 5, entity_num_range=(N // 2, N)))
+    bad['entity_info']['unit_type'][0, 0] = -1
+    if bad['entity_info']['unit_type'].dtype.is_signed:
+        with pytest.raises(RuntimeError):
+            actor(bad['spatial_info'], bad['entity_info'], bad['scalar_info'], bad['entity_num'], bad['hidden_state'],
+                  gumbel_noise=noise)
+
+
+@gpu
+@pytest.mark.parametrize('R,N,temperature', [(7, 48, 0.8), (150, 512, 1.0)])
+def test_su_sample_fused_kernel_vs_oracle(R, N, temperature):
+    """as_su_sample (all 64 sampling steps in one launch, fp32) against the oracle's step loop on the same keys, noise
+    and weights: picks, selected_units_num, step count and extra_units bit-exact; logits to fp32 round-off."""
+    from applestar_b200 import ops
+    from applestar_b200.model import SelectedUnitsHead
+    torch.manual_seed(11)
+    head = SelectedUnitsHead(True).cuda()
+    with torch.no_grad():
+        for prm in head.lstm.parameters():
+            if prm.dim() == 2:
+                prm.mul_(0.3)                                  # keep the pointer logits in a realistic range
+    sd = {'policy.selected_units_head.' + k: v.detach().cpu() for k, v in head.state_dict().items()}
+    ent = torch.randn(R, N, 256) * 0.5
+    en = torch.randint(max(N // 3, 2), N + 1, (R,))
+    en[0], en[1] = N, 2
+    su_mask = torch.rand(R) < 0.8
+    su_mask[0], su_mask[2] = True, False
+    ae0 = torch.randn(R, 1024) * 0.3
+    noise = synth.gen_gumbel(R, 21, N)['selected_units']
+    if R < 10:
+        noise[:, 3, :] = -50.0
+        noise[1:, 3, int(en[3])] = 0.0                     # row 3 takes the end token at step 1; others run on
+    ref_logits, ref_units, ref_ae, ref_num, ref_extra = R_.su_head_sample(sd, ae0, ent, en, su_mask, noise, temperature, True)
+    key, _ = R_.su_keys(sd, ent, en)
+    with torch.no_grad():
+        logits, units, ae, num, extra = ops.selected_units_sample(head, key.cuda(), ae0.cuda(), en.cuda(), su_mask.cuda(),
+                                                                  noise.cuda(), temperature, True)
+    assert logits.shape == ref_logits.shape, (logits.shape, ref_logits.shape)
+    assert torch.equal(units.cpu(), ref_units)
+    assert torch.equal(num.cpu(), ref_num)
+    assert torch.equal(extra.cpu(), ref_extra)
+    masked = ref_logits < -1e8
+    assert torch.equal(logits.cpu() < -1e8, masked)
+    assert (logits.cpu() - ref_logits)[~masked].abs().max().item() < 2e-3
+    assert (ae.cpu() - ref_ae).abs().max().item() < 0.05      # the final embed_fc1/2 run on the bf16 GEMM
+    with torch.no_grad():                                   # the step-by-step device loop agrees on every pick too
+        import os
+        os.environ['APPLESTAR_SU_FUSED'] = '0'
+        try:
+            l2, u2, _, n2, e2 = ops.selected_units_sample(head, key.cuda(), ae0.cuda(), en.cuda(), su_mask.cuda(),
+                                                          noise.cuda(), temperature, True)
+        finally:
+            del os.environ['APPLESTAR_SU_FUSED']
+    assert l2.shape == logits.shape and torch.equal(n2 > 0, num > 0)
 
 
 @gpu

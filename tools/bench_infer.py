@@ -1,5 +1,5 @@
 """Batched actor inference (BASELINE.json configs[2]): Model.compute_logp_action on B observations x 512 entities,
-inputs resident on the device, Gumbel noise supplied.  Prints obs/s.  usage: python tools/bench_infer.py [B] [iters]"""
+inputs resident on the device, Gumbel noise supplied.  Prints obs/s.  usage: python tools/bench_infer.py [B] [iters] [graph=1]"""
 import json
 import os
 import sys
@@ -13,6 +13,7 @@ from applestar_b200 import Model, synth  # noqa: E402
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 256
 iters = int(sys.argv[2]) if len(sys.argv) > 2 else 5
+use_graph = (int(sys.argv[3]) if len(sys.argv) > 3 else 1) != 0
 dev = torch.device('cuda:0')
 model = Model({}, use_value_network=False)
 model.load_state_dict(synth.full_state_dict(bench.load_spec(), 0), strict=False)
@@ -20,18 +21,24 @@ model = model.to(dev).eval()
 obs = synth.tree_map(lambda t: t.to(dev), synth.gen_observations(B, 512, 7))
 hidden = [(torch.zeros(B, 384, device=dev), torch.zeros(B, 384, device=dev)) for _ in range(3)]
 noise = synth.tree_map(lambda t: t.to(dev), synth.gen_gumbel(B, 11))
+from applestar_b200.learner import ActorStep  # noqa: E402
+actor = ActorStep(model, use_graph=use_graph)
+
+
+def call():
+    return actor(obs['spatial_info'], obs['entity_info'], obs['scalar_info'], obs['entity_num'], hidden, gumbel_noise=noise)
+
+
 with torch.no_grad():
     for _ in range(2):
-        out = model.compute_logp_action(obs['spatial_info'], obs['entity_info'], obs['scalar_info'], obs['entity_num'], hidden,
-                                        gumbel_noise=noise)
+        out = call()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(iters):
-        out = model.compute_logp_action(obs['spatial_info'], obs['entity_info'], obs['scalar_info'], obs['entity_num'], hidden,
-                                        gumbel_noise=noise)
+        out = call()
     e1.record()
     torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / iters
 print(json.dumps({'metric': 'inference_obs_per_sec_per_gpu', 'value': B / ms * 1e3, 'unit': 'obs/s', 'ms_per_call': ms, 'batch': B,
-                  'entities': 512, 'dtype': 'bf16', 'data': 'synthetic', 'selected_units_steps': int(out['logit']['selected_units'].shape[1])}))
+                  'entities': 512, 'cuda_graph': use_graph, 'launches_per_call': actor.launches_per_call, 'dtype': 'bf16', 'data': 'synthetic', 'selected_units_steps': int(out['logit']['selected_units'].shape[1])}))
