@@ -9,6 +9,8 @@ extern int g_gemm_debug;
 extern int g_gemm_no_tma_store;
 extern int g_gemm_no_slab;
 int gemm_set_profile(long long*);
+int attn_fwd_ok(int, int);
+int attn_fwd(const void*, const long long*, void*, void*, long long, int, int, int, float, cudaStream_t);
 int scatter_fwd(const float*, const void*, const void*, int, const long long*, float*, long long, int, int, int, int,
                 int, cudaStream_t);
 int scatter_bwd(const float*, const void*, const void*, int, const long long*, float*, long long, int, int, int, int,
@@ -273,6 +275,11 @@ int as_su_mask_logits(const float* x, const int64_t* selected_units, const int64
                       int Smax, int S, float scale, float fill, void* stream) {
   return as::su_mask_logits(x, reinterpret_cast<const long long*>(selected_units), reinterpret_cast<const long long*>(entity_num), out,
                             R, N1, Smax, S, scale, fill, ST(stream));
+}
+int as_attn_fwd_ok(int N, int D) { return as::attn_fwd_ok(N, D); }
+int as_attn_fwd(const void* qkv, const int64_t* key_len, void* out, void* probs, int64_t R, int N, int H, int D, float scale,
+                void* stream) {
+  return as::attn_fwd(qkv, reinterpret_cast<const long long*>(key_len), out, probs, R, N, H, D, scale, ST(stream));
 }
 int as_su_sample(const as_su_sample_args* a, void* stream) {
   if (!a) return AS_EINVAL;

@@ -1,0 +1,311 @@
+// Fused attention forward for the entity Transformer (module_utils.py:71-111 of the reference: softmax(Q K^T / sqrt(d),
+// padded keys filled with -1e9) V, 2 heads x 128, up to 512 keys): scores never leave the SM.
+//
+// One work item = 128 queries of one (observation, head).  All keys of the row fit the tensor memory at once
+// (4 blocks x 128 fp32 columns = the full 512 TMEM columns), so the softmax is EXACT two-pass rather than the online
+// form with accumulator rescaling:
+//   TMA   : Q tile + the K blocks -> shared memory (128-byte swizzle), V blocks behind them
+//   MMA   : S_kb = Q K_kb^T                  tcgen05.mma 128x128x16, accumulators in TMEM columns [128 kb, 128 kb+128)
+//   pass 1: 8 warps read S from TMEM (thread = query row, two threads share a row), scale, mask, running max / sum
+//   pass 2: read S again, P = exp2(s - m) / l as bf16 into the shared-memory tiles that held K (K is dead by then),
+//           laid out as the K-major A operand of the second product; the same tiles are sent to global memory by TMA
+//           when the backward pass needs P
+//   MMA   : O += P_kb V_kb                   V straight from the packed qkv buffer as an MN-major B operand; O reuses
+//           the TMEM columns of S_0
+//   out   : O from TMEM -> bf16 -> global
+// The CTA is persistent over work items; every mbarrier completes exactly once per item, so one parity bit tracks them.
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "gemm.h"
+
+namespace as {
+
+constexpr int kAtThreads = 384;            // warp 0: TMA, warp 1: MMA, warps 4-11: softmax / epilogue
+constexpr int kAtSub = 128 * 64 * 2;       // one [128 rows][64 bf16] swizzled sub-tile: 16 KB
+constexpr int kAtKP = 0;                   // 4 key blocks x 2 sub-tiles (K by d-half, later P by key-half)
+constexpr int kAtQ = 8 * kAtSub;           // 2 sub-tiles (d halves); V block 2 lands here once Q is dead
+constexpr int kAtV = 10 * kAtSub;          // 2 stages x 2 sub-tiles (d chunks)
+constexpr int kAtBars = 14 * kAtSub;       // 229376
+constexpr int kAtRed = kAtBars + 256;      // float2 [2][128]
+constexpr int kAtTotal = kAtRed + 2 * 128 * 8;
+constexpr int kAtSmemMax = 232448;
+constexpr float kLog2e = 1.4426950408889634f;
+
+struct AttnDev {
+  const long long* key_len;
+  __nv_bfloat16* O;
+  int R, N, H, NB, NQ, store_p;
+  float scale_log2;
+  long long tiles;
+};
+
+// barrier indices
+enum { kBarK = 0, kBarS = 4, kBarP = 8, kBarV = 12, kBarPv0 = 16, kBarO = 17, kBarDone = 18, kBarCount = 19 };
+
+// V block -> buffer: 0 and 3 share stage 0 (3 is loaded once P_0 V_0 has retired), 1 -> stage 1, 2 -> the dead Q tile
+__device__ __forceinline__ int at_v_offset(int kb) { return kb == 2 ? kAtQ : kAtV + (kb == 1 ? 2 * kAtSub : 0); }
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+__global__ void __launch_bounds__(kAtThreads, 1)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmP, const AttnDev p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t pad = (1024u - (raw & 1023u)) & 1023u;
+  if (pad + kAtTotal > kAtSmemMax) __trap();
+  uint8_t* smem = smem_raw + pad;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kAtBars);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + kAtBars + kBarCount * 8);
+  float2* red = reinterpret_cast<float2*>(smem + kAtRed);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int NB = p.NB, HD = p.H * 128;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kBarCount; ++i) mbar_init(&bars[i], (i >= kBarP && i < kBarP + 4) ? 256u : (i == kBarDone ? 257u : 1u));
+    mbar_fence_init();
+    tma_prefetch_desc(&tmQKV);
+    if (p.store_p) tma_prefetch_desc(&tmP);
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (long long tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+        const uint32_t ph = it & 1u;
+        const int qt = (int)(tile % p.NQ);
+        const int bh = (int)(tile / p.NQ);
+        const int h = bh % p.H, b = bh / p.H;
+        if (it > 0) mbar_wait(&bars[kBarDone], ph ^ 1u);           // previous item: K/P, Q and V buffers are free
+        for (int kb = 0; kb < NB; ++kb) {
+          mbar_expect_tx(&bars[kBarK + kb], (kb == 0 ? 4u : 2u) * kAtSub);
+          if (kb == 0) {
+            tma_load_4d(smem + kAtQ, &tmQKV, &bars[kBarK], h * 128, qt * 128, b, 0);
+            tma_load_4d(smem + kAtQ + kAtSub, &tmQKV, &bars[kBarK], h * 128 + 64, qt * 128, b, 0);
+          }
+          tma_load_4d(smem + kAtKP + (2 * kb) * kAtSub, &tmQKV, &bars[kBarK + kb], HD + h * 128, kb * 128, b, 0);
+          tma_load_4d(smem + kAtKP + (2 * kb + 1) * kAtSub, &tmQKV, &bars[kBarK + kb], HD + h * 128 + 64, kb * 128, b, 0);
+        }
+        for (int kb = 0; kb < NB; ++kb) {
+          uint8_t* dst = smem + at_v_offset(kb);
+          if (kb == 2) mbar_wait(&bars[kBarS + NB - 1], ph);       // every Q K^T product has retired: Q is dead
+          if (kb == 3) mbar_wait(&bars[kBarPv0], ph);             // P_0 V_0 has retired: V stage 0 is free
+          mbar_expect_tx(&bars[kBarV + kb], 2u * kAtSub);
+          tma_load_4d(dst, &tmQKV, &bars[kBarV + kb], 2 * HD + h * 128, kb * 128, b, 0);
+          tma_load_4d(dst + kAtSub, &tmQKV, &bars[kBarV + kb], 2 * HD + h * 128 + 64, kb * 128, b, 0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer (warp-uniform, one lane issues)
+    constexpr uint32_t kDescHi = (1024u >> 4) | (1u << 14) | (2u << 29);
+    constexpr uint32_t idesc_qk = (1u << 4) | (1u << 7) | (1u << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
+    constexpr uint32_t idesc_pv = idesc_qk | (1u << 16);           // B (= V) is MN-major
+    const uint32_t sbase = smem_u32(smem);
+    uint32_t it = 0;
+    for (long long tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+      const uint32_t ph = it & 1u;
+      const int qt = (int)(tile % p.NQ);
+      const int bh = (int)(tile / p.NQ);
+      if (it > 0) mbar_wait(&bars[kBarDone], ph ^ 1u);             // TMEM drained by the epilogue of the previous item
+      tc_fence_after();
+      for (int kb = 0; kb < NB; ++kb) {
+        mbar_wait(&bars[kBarK + kb], ph);
+        tc_fence_after();
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const uint32_t a_lo = (1u << 16) | ((sbase + kAtQ + j * kAtSub) >> 4);
+          const uint32_t b_lo = (1u << 16) | ((sbase + kAtKP + (2 * kb + j) * kAtSub) >> 4);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint64_t da = ((uint64_t)kDescHi << 32) | (a_lo + 2u * k);
+            const uint64_t db = ((uint64_t)kDescHi << 32) | (b_lo + 2u * k);
+            umma_bf16_lead(0, tmem_base + (uint32_t)(kb * 128), da, db, idesc_qk, (j | k) ? 1u : 0u);
+          }
+        }
+        umma_commit_lead(0, &bars[kBarS + kb]);
+      }
+      for (int kb = 0; kb < NB; ++kb) {
+        mbar_wait(&bars[kBarP + kb], ph);
+        mbar_wait(&bars[kBarV + kb], ph);
+        tc_fence_after();
+        const uint32_t vaddr = sbase + (uint32_t)at_v_offset(kb);
+        const uint32_t b_lo = ((uint32_t)(kAtSub >> 4) << 16) | (vaddr >> 4);
+#pragma unroll
+        for (int s = 0; s < 8; ++s) {
+          const uint32_t a_lo = (1u << 16) | ((sbase + kAtKP + (2 * kb + (s >> 2)) * kAtSub) >> 4);
+          const uint64_t da = ((uint64_t)kDescHi << 32) | (a_lo + 2u * (s & 3));
+          const uint64_t db = ((uint64_t)kDescHi << 32) | (b_lo + (uint32_t)(s * (16 * 128 / 16)));
+          umma_bf16_lead(0, tmem_base, da, db, idesc_pv, (kb | s) ? 1u : 0u);
+        }
+        if (kb == 0) umma_commit_lead(0, &bars[kBarPv0]);
+        if (p.store_p && lane == 0) {                              // probabilities for the backward pass
+          tma_store_4d(&tmP, smem + kAtKP + (2 * kb) * kAtSub, kb * 128, qt * 128, bh, 0);
+          tma_store_4d(&tmP, smem + kAtKP + (2 * kb + 1) * kAtSub, kb * 128 + 64, qt * 128, bh, 0);
+          tma_store_commit();
+        }
+        __syncwarp();
+      }
+      umma_commit_lead(0, &bars[kBarO]);
+      if (lane == 0) {
+        if (p.store_p) tma_store_wait_read();
+        mbar_arrive(&bars[kBarDone]);
+      }
+      __syncwarp();
+    }
+  } else if (warp >= 4) {
+    // ------------------------------------------------------------------ softmax + output (8 warps, 256 threads)
+    const int e = warp - 4;
+    const int quarter = warp & 3;                                  // TMEM lane quarter this warp may read
+    const int half = e >> 2;                                       // which 64 of a block's 128 columns
+    const int row = quarter * 32 + lane;
+    const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * 64);
+    uint32_t it = 0;
+    for (long long tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+      const uint32_t ph = it & 1u;
+      const int qt = (int)(tile % p.NQ);
+      const int bh = (int)(tile / p.NQ);
+      const int h = bh % p.H, b = bh / p.H;
+      long long kl = p.key_len ? p.key_len[b] : (long long)p.N;
+      if (kl > p.N) kl = p.N;
+      float m = -INFINITY, l = 0.f;
+      uint32_t v[64];
+      // pass 1: running max / sum over this thread's 64 columns of every key block
+      for (int kb = 0; kb < NB; ++kb) {
+        mbar_wait(&bars[kBarS + kb], ph);
+        tc_fence_after();
+        tmem_ld32(t_row + kb * 128, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+        tmem_ld32(t_row + kb * 128 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+        tmem_ld_wait();
+        const int lim = (int)kl - (kb * 128 + half * 64);
+        float cm = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < 64; ++i) {
+          const float t = i < lim ? __uint_as_float(v[i]) * p.scale_log2 : -1e9f * kLog2e;
+          v[i] = __float_as_uint(t);
+          cm = fmaxf(cm, t);
+        }
+        if (cm > m) { l *= fast_exp2(m - cm); m = cm; }
+        float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+        for (int i = 0; i < 64; i += 2) {
+          s0 += fast_exp2(__uint_as_float(v[i]) - m);
+          s1 += fast_exp2(__uint_as_float(v[i + 1]) - m);
+        }
+        l += s0 + s1;
+      }
+      red[half * 128 + row] = make_float2(m, l);
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      {
+        const float2 o = red[(half ^ 1) * 128 + row];
+        const float mm = fmaxf(m, o.x);
+        l = l * fast_exp2(m - mm) + o.y * fast_exp2(o.x - mm);
+        m = mm;
+      }
+      const float rinv = 1.f / l;
+      // pass 2: normalised probabilities -> bf16 -> the A-operand tiles (128-byte swizzle: chunk c of row r at c ^ (r & 7))
+      for (int kb = 0; kb < NB; ++kb) {
+        tmem_ld32(t_row + kb * 128, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+        tmem_ld32(t_row + kb * 128 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+        tmem_ld_wait();
+        const int lim = (int)kl - (kb * 128 + half * 64);
+        uint8_t* dst = smem + kAtKP + (2 * kb + half) * kAtSub + row * 128;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          uint32_t w[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int i = c * 8 + 2 * j;
+            const float t0 = i < lim ? __uint_as_float(v[i]) * p.scale_log2 : -1e9f * kLog2e;
+            const float t1 = i + 1 < lim ? __uint_as_float(v[i + 1]) * p.scale_log2 : -1e9f * kLog2e;
+            w[j] = pack_bf16(fast_exp2(t0 - m) * rinv, fast_exp2(t1 - m) * rinv);
+          }
+          *reinterpret_cast<uint4*>(dst + ((c ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+        tc_fence_before();
+        fence_proxy_async_smem();
+        mbar_arrive(&bars[kBarP + kb]);
+      }
+      // output: O (fp32, TMEM columns [0,128)) -> bf16 rows of the [R, N, H*128] buffer
+      mbar_wait(&bars[kBarO], ph);
+      tc_fence_after();
+      tmem_ld32(t_row, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+      tmem_ld32(t_row + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+      tmem_ld_wait();
+      {
+        uint4* out = reinterpret_cast<uint4*>(p.O + ((long long)b * p.N + qt * 128 + row) * HD + h * 128 + half * 64);
+#pragma unroll
+        for (int c = 0; c < 8; ++c)
+          out[c] = make_uint4(pack_bf16(__uint_as_float(v[8 * c]), __uint_as_float(v[8 * c + 1])),
+                              pack_bf16(__uint_as_float(v[8 * c + 2]), __uint_as_float(v[8 * c + 3])),
+                              pack_bf16(__uint_as_float(v[8 * c + 4]), __uint_as_float(v[8 * c + 5])),
+                              pack_bf16(__uint_as_float(v[8 * c + 6]), __uint_as_float(v[8 * c + 7])));
+      }
+      tc_fence_before();
+      fence_proxy_async_smem();
+      mbar_arrive(&bars[kBarDone]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+int make_map_bf16(CUtensorMap* tm, const void* ptr, long long inner, long long rows, long long ld, int nb0, long long sb0,
+                  int nb1, long long sb1, int box_inner, int box_rows);
+int gemm_num_sms();
+
+int attn_fwd_ok(int N, int D) { return D == 128 && N >= 128 && N <= 512 && N % 128 == 0; }
+
+int attn_fwd(const void* qkv, const long long* key_len, void* O, void* P, long long R, int N, int H, int D, float scale,
+             cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (!attn_fwd_ok(N, D) || H <= 0) return AS_EUNSUPPORTED;
+  if (!qkv || !O) return AS_EINVAL;
+  CUtensorMap tq, tp;
+  int rc = make_map_bf16(&tq, qkv, 3LL * H * D, N, 3LL * H * D, (int)R, (long long)N * 3 * H * D, 1, 0, 64, 128);
+  if (rc != AS_OK) return rc;
+  if (P) {
+    rc = make_map_bf16(&tp, P, N, N, N, (int)(R * H), (long long)N * N, 1, 0, 64, 128);
+    if (rc != AS_OK) return rc;
+  } else {
+    tp = tq;
+  }
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAtSmemMax);
+    if (e != cudaSuccess) return (int)e;
+    attr_done = true;
+  }
+  AttnDev p;
+  p.key_len = key_len;
+  p.O = reinterpret_cast<__nv_bfloat16*>(O);
+  p.R = (int)R; p.N = N; p.H = H; p.NB = N / 128; p.NQ = N / 128; p.store_p = P ? 1 : 0;
+  p.scale_log2 = scale * kLog2e;
+  p.tiles = R * H * p.NQ;
+  const int sms = gemm_num_sms();
+  const int grid = (int)(p.tiles < sms ? p.tiles : sms);
+  attn_fwd_kernel<<<grid, kAtThreads, kAtSmemMax, st>>>(tq, tp, p);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+}  // namespace as

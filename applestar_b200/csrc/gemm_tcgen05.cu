@@ -14,6 +14,7 @@
 // mode re-reads A for every tap and is L2-bandwidth bound (measured 190-730 TFLOP/s).
 //
 // Warp roles (12 warps): w0 TMA producer, w1 MMA issuer, w2 TMEM allocator, w4-11 epilogue.
+#include <cstdio>
 #include <cstdlib>
 
 #include "common.cuh"
@@ -682,6 +683,10 @@ static int make_map(CUtensorMap* tm, const void* ptr, long long inner, long long
                     long long sb0, int nb1, long long sb1, int box_inner, int box_rows, int es = 2) {
   EncodeTiledFn enc = get_encode();
   if (!enc) return AS_EDRIVER;
+  // the encode is a driver-API call: a thread that has not touched the runtime yet (e.g. autograd's backward thread
+  // when its first kernel is one of ours) has no current context and gets CUDA_ERROR_INVALID_CONTEXT
+  static thread_local bool ctx_ready = false;
+  if (!ctx_ready) { cudaFree(nullptr); ctx_ready = true; }
   if ((reinterpret_cast<uintptr_t>(ptr) & 15) || ((ld * es) & 15)) return AS_EALIGN;
   cuuint64_t dims[4] = {(cuuint64_t)inner, (cuuint64_t)rows, (cuuint64_t)nb0, (cuuint64_t)nb1};
   long long s0 = nb0 > 1 ? sb0 : ld * rows, s1 = nb1 > 1 ? sb1 : s0 * nb0;
@@ -693,6 +698,11 @@ static int make_map(CUtensorMap* tm, const void* ptr, long long inner, long long
                    const_cast<void*>(ptr), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS && getenv("AS_DEBUG_TMAP"))
+    fprintf(stderr, "tensor map encode failed: CUresult %d ptr %p dims %llu %llu %llu %llu strides %llu %llu %llu box %u %u es %d\n",
+            (int)r, ptr, (unsigned long long)dims[0], (unsigned long long)dims[1], (unsigned long long)dims[2],
+            (unsigned long long)dims[3], (unsigned long long)strides[0], (unsigned long long)strides[1],
+            (unsigned long long)strides[2], box[0], box[1], es);
   return r == CUDA_SUCCESS ? AS_OK : AS_EDRIVER;
 }
 
@@ -706,6 +716,13 @@ static int num_sms() {
   }
   return g_num_sms;
 }
+
+// used by attn.cu
+int make_map_bf16(CUtensorMap* tm, const void* ptr, long long inner, long long rows, long long ld, int nb0, long long sb0,
+                  int nb1, long long sb1, int box_inner, int box_rows) {
+  return make_map(tm, ptr, inner, rows, ld, nb0, sb0, nb1, sb1, box_inner, box_rows);
+}
+int gemm_num_sms() { return num_sms(); }
 
 template <int BN, bool A_MN, bool B_MN>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const CUtensorMap& tc2,

@@ -314,6 +314,9 @@ def layer_norm_dual(x, weight, bias, residual=None, relu=False):
 SCORE_DTYPE = torch.bfloat16 if os.environ.get('APPLESTAR_ATTN_BF16_SCORES', '1') == '1' else torch.float32
 
 
+ATTN_FUSED = os.environ.get('APPLESTAR_ATTN_FUSED', '1') != '0'
+
+
 class AttentionFn(torch.autograd.Function):
     """softmax(Q K^T / sqrt(d), keys >= key_len masked) V over a packed bf16 qkv buffer [R, N, 3*H*D].
     Q K^T, P V and the four backward products are batched tcgen05 GEMMs reading Q/K/V (and dO) in place through
@@ -327,6 +330,17 @@ class AttentionFn(torch.autograd.Function):
         qkv = qkv.contiguous()
         q, k, v = qkv[:, :, :H * D], qkv[:, :, H * D:2 * H * D], qkv[:, :, 2 * H * D:]
         scale = 1.0 / math.sqrt(D)
+        kl = None if key_len is None else key_len.contiguous().long()
+        if ATTN_FUSED and _lib.lib().as_attn_fwd_ok(N, D):
+            # scores stay in tensor memory (attn.cu); P is written only when a backward pass will read it
+            need_p = ctx.needs_input_grad[0]
+            P = torch.empty((R, H, N, N), dtype=torch.bfloat16, device=qkv.device) if need_p else None
+            O = torch.empty((R, N, H * D), dtype=torch.bfloat16, device=qkv.device)
+            _lib.call('as_attn_fwd', qkv.data_ptr(), _ptr(kl), O.data_ptr(), _ptr(P), R, N, H, D, scale, _lib.stream_ptr())
+            ctx.dims = (R, N, N, H, D)
+            if need_p:
+                ctx.save_for_backward(qkv, P)
+            return O
         Np = (N + 7) // 8 * 8                       # pitch of the score rows (bf16 P must be 16-byte pitched)
         S = torch.empty((R, H, N, Np), dtype=SCORE_DTYPE, device=qkv.device)
         gemm(q, k, S, N, N, D, lda=ld, ldb=ld, ldc=Np, batch=(H, R), a_strides=(D, N * ld), b_strides=(D, N * ld),
@@ -334,7 +348,6 @@ class AttentionFn(torch.autograd.Function):
         P = torch.empty((R, H, N, Np), dtype=torch.bfloat16, device=qkv.device)
         if Np != N:
             P.zero_()
-        kl = None if key_len is None else key_len.contiguous().long()
         _softmax_rows(S, kl, P, R * H, N, N, Np, H)
         O = torch.empty((R, N, H * D), dtype=torch.bfloat16, device=qkv.device)
         gemm(P, v, O, N, D, N, lda=Np, b_mn=True, ldb=ld, ldc=H * D, batch=(H, R),

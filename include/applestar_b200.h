@@ -219,6 +219,15 @@ int as_su_prefix_bwd(const float* demb, const int64_t* selected_units, const int
 int as_su_mask_logits(const float* x, const int64_t* selected_units, const int64_t* entity_num, float* out, int64_t R, int N1,
                       int Smax, int S, float scale, float fill, void* stream);
 
+/* as_attn_fwd: fused attention forward of the entity Transformer (module_utils.py:71-111): out[r,n,h*D:(h+1)*D] =
+ * softmax_j(q.k_j * scale, keys j >= key_len[r] filled with -1e9) V over the packed bf16 qkv [R, N, 3*H*D] (q | k | v
+ * column blocks).  Scores stay in tensor memory; probs [R,H,N,N] bf16 (optional, NULL at inference) receives the
+ * normalised probabilities the backward products read.  Supported when as_attn_fwd_ok(N, D) != 0 (D == 128, N a
+ * multiple of 128 up to 512); otherwise AS_EUNSUPPORTED and the caller composes as_gemm_bf16 + as_softmax_fwd. */
+int as_attn_fwd_ok(int N, int D);
+int as_attn_fwd(const void* qkv, const int64_t* key_len, void* out, void* probs, int64_t R, int N, int H, int D, float scale,
+                void* stream);
+
 /* as_su_sample: the whole SelectedUnits SAMPLING loop (head/action_arg_head.py:262-313: up to 64 autoregressive picks
  * per row) in one launch.  query_fc1 o (ae0 + embed_fc2(.)) is folded by the caller into c0 = Wq1 ae0 + bq1 [R,256],
  * c1 = Wq1 bf2 [256] and mt = (Wq1 Wf2)^T [256,256]; wf1t/wq2t/wih_t/whh_t are the transposed fp32 weights of

@@ -62,6 +62,41 @@ def test_attention_fwd_bwd(N, H, D, masked):
     assert (qkv.grad.float() - qr.grad).abs().max().item() < 0.06 * qr.grad.abs().max().item() + 1e-3
 
 
+@pytest.mark.parametrize('Rr,N', [(40, 512), (5, 384), (3, 128)])
+def test_attention_fused_forward(Rr, N):
+    """as_attn_fwd (scores in tensor memory) vs fp32 torch: outputs, stored probabilities, persistent loop over > 148
+    work items, inference call without a probability buffer."""
+    from applestar_b200 import _lib, kernels as K
+    H, D = 2, 128
+    assert _lib.lib().as_attn_fwd_ok(N, D) == 1 and _lib.lib().as_attn_fwd_ok(N + 8, D) == 0
+    g = torch.Generator().manual_seed(N + Rr)
+    qkv = (torch.randn(Rr, N, 3 * H * D, generator=g) * 0.7).cuda().to(torch.bfloat16)
+    key_len = torch.randint(1, N + 1, (Rr,), generator=g).cuda()
+    key_len[0] = N
+    key_len[1] = 1
+    scale = 1.0 / math.sqrt(D)
+    O = torch.empty(Rr, N, H * D, dtype=torch.bfloat16, device='cuda')
+    P = torch.empty(Rr, H, N, N, dtype=torch.bfloat16, device='cuda')
+    _lib.call('as_attn_fwd', qkv.data_ptr(), key_len.data_ptr(), O.data_ptr(), P.data_ptr(), Rr, N, H, D, scale, _lib.stream_ptr())
+    O2 = torch.empty_like(O)
+    _lib.call('as_attn_fwd', qkv.data_ptr(), key_len.data_ptr(), O2.data_ptr(), 0, Rr, N, H, D, scale, _lib.stream_ptr())
+    q, k, v = qkv.float().chunk(3, dim=2)
+    q = q.view(Rr, N, H, D).permute(0, 2, 1, 3)
+    k = k.view(Rr, N, H, D).permute(0, 2, 3, 1)
+    v = v.view(Rr, N, H, D).permute(0, 2, 1, 3)
+    s = torch.matmul(q, k) * scale
+    m = torch.arange(N, device='cuda').view(1, 1, 1, N) < key_len.view(Rr, 1, 1, 1)
+    pr = torch.softmax(s.masked_fill(~m, -1e9), -1)
+    orf = torch.matmul(pr, v).permute(0, 2, 1, 3).reshape(Rr, N, H * D)
+    assert torch.equal(O, O2)
+    assert (P.float() - pr).abs().max().item() < 6e-3               # bf16 rounding of probabilities <= 1
+    assert bool((P.float()[~m.expand_as(pr)] == 0).all())           # padded keys get exactly zero weight
+    assert (O.float() - orf).abs().max().item() < 0.03
+    with torch.no_grad():
+        o3 = K.attention(qkv, key_len, H, D)
+    assert torch.equal(o3, O)
+
+
 def test_entity_features_match_oracle_concat():
     from applestar_b200 import kernels as K
     obs = synth.gen_observations(4, 96, 3, special=True)

@@ -34,11 +34,13 @@ with torch.no_grad():
         out = call()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.profiler.start()                       # `ncu --profile-from-start off` captures only the timed calls
     e0.record()
     for _ in range(iters):
         out = call()
     e1.record()
     torch.cuda.synchronize()
+    torch.cuda.profiler.stop()
 ms = e0.elapsed_time(e1) / iters
 print(json.dumps({'metric': 'inference_obs_per_sec_per_gpu', 'value': B / ms * 1e3, 'unit': 'obs/s', 'ms_per_call': ms, 'batch': B,
                   'entities': 512, 'cuda_graph': use_graph, 'launches_per_call': actor.launches_per_call, 'dtype': 'bf16', 'data': 'synthetic', 'selected_units_steps': int(out['logit']['selected_units'].shape[1])}))
