@@ -10,7 +10,9 @@ extern int g_gemm_no_tma_store;
 extern int g_gemm_no_slab;
 int gemm_set_profile(long long*);
 int attn_fwd_ok(int, int);
+int attn_set_profile(long long*);
 int attn_fwd(const void*, const long long*, void*, void*, long long, int, int, int, float, cudaStream_t);
+int attn_bwd_dq(const void*, const void*, const void*, const void*, void*, void*, long long, int, int, int, float, cudaStream_t);
 int scatter_fwd(const float*, const void*, const void*, int, const long long*, float*, long long, int, int, int, int,
                 int, cudaStream_t);
 int scatter_bwd(const float*, const void*, const void*, int, const long long*, float*, long long, int, int, int, int,
@@ -281,6 +283,10 @@ int as_attn_fwd(const void* qkv, const int64_t* key_len, void* out, void* probs,
                 void* stream) {
   return as::attn_fwd(qkv, reinterpret_cast<const long long*>(key_len), out, probs, R, N, H, D, scale, ST(stream));
 }
+int as_attn_bwd_dq(const void* qkv, const void* out, const void* dout, const void* probs, void* dscores, void* dqkv, int64_t R, int N,
+                   int H, int D, float scale, void* stream) {
+  return as::attn_bwd_dq(qkv, out, dout, probs, dscores, dqkv, R, N, H, D, scale, ST(stream));
+}
 int as_su_sample(const as_su_sample_args* a, void* stream) {
   if (!a) return AS_EINVAL;
   as::SuSampleDev p;
@@ -338,6 +344,7 @@ int as_lnlstm_cluster_ok(int H) { return as::lnlstm_cluster_ok(H) ? 1 : 0; }
 // diagnostics only (not part of the public header)
 int as_debug_gemm_profile(void* buf) { return as::gemm_set_profile(reinterpret_cast<long long*>(buf)); }
 int as_debug_lstm_max_clusters(int H) { return as::lnlstm_cluster_max_active(H); }
+int as_debug_attn_profile(void* buf) { return as::attn_set_profile(reinterpret_cast<long long*>(buf)); }
 int as_debug_lstm_profile(void* buf) { return as::lnlstm_set_profile(reinterpret_cast<long long*>(buf)); }
 
 int as_softmax_fwd(const void* scores, const int64_t* key_len, void* probs, int64_t groups, int Nq, int Nk,

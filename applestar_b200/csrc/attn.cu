@@ -35,11 +35,20 @@ constexpr float kLog2e = 1.4426950408889634f;
 
 struct AttnDev {
   const long long* key_len;
-  __nv_bfloat16* O;
+  __nv_bfloat16* out;                 // forward: O [R,N,H*128]; backward: the dq column block of dqkv [R,N,3*H*128]
+  const __nv_bfloat16* O;             // backward only: forward output, dO, stored probabilities
+  const __nv_bfloat16* dO;
+  const __nv_bfloat16* P;
   int R, N, H, NB, NQ, store_p;
-  float scale_log2;
+  int out_ld;                         // row pitch of `out` in elements
+  int b1_col, b2_col;                 // qkv column of the first / second B operand (forward: K, V; backward: V, K)
+  float scale_log2, out_scale;
   long long tiles;
+  long long* prof;                    // diagnostics: cycle sums of the softmax warps' phases (CTA 0)
 };
+
+static long long* g_attn_prof = nullptr;
+int attn_set_profile(long long* buf) { g_attn_prof = buf; return AS_OK; }
 
 // barrier indices
 enum { kBarK = 0, kBarS = 4, kBarP = 8, kBarV = 12, kBarPv0 = 16, kBarO = 17, kBarDone = 18, kBarCount = 19 };
@@ -56,8 +65,14 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
+// BWD = false: forward as described above (A = Q, first B = K, second B = V).
+// BWD = true : the query-side half of the backward pass with the same pipeline: dP = dO V^T into TMEM (A = dO tile,
+//              first B = V), dS = P o (dP - delta) with delta = rowsum(dO o O) and P read from global memory, dS -> bf16
+//              -> shared-memory A tiles (and by TMA to global for the dK product), dQ = scale dS K (second B = K).
+template <bool BWD>
 __global__ void __launch_bounds__(kAtThreads, 1)
-attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmP, const AttnDev p) {
+attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmQKV,
+            const __grid_constant__ CUtensorMap tmP, const AttnDev p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t pad = (1024u - (raw & 1023u)) & 1023u;
@@ -74,6 +89,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     for (int i = 0; i < kBarCount; ++i) mbar_init(&bars[i], (i >= kBarP && i < kBarP + 4) ? 256u : (i == kBarDone ? 257u : 1u));
     mbar_fence_init();
     tma_prefetch_desc(&tmQKV);
+    tma_prefetch_desc(&tmA);
     if (p.store_p) tma_prefetch_desc(&tmP);
   }
   if (warp == 1) tmem_alloc(tmem_slot, 512);
@@ -95,19 +111,19 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         for (int kb = 0; kb < NB; ++kb) {
           mbar_expect_tx(&bars[kBarK + kb], (kb == 0 ? 4u : 2u) * kAtSub);
           if (kb == 0) {
-            tma_load_4d(smem + kAtQ, &tmQKV, &bars[kBarK], h * 128, qt * 128, b, 0);
-            tma_load_4d(smem + kAtQ + kAtSub, &tmQKV, &bars[kBarK], h * 128 + 64, qt * 128, b, 0);
+            tma_load_4d(smem + kAtQ, &tmA, &bars[kBarK], h * 128, qt * 128, b, 0);
+            tma_load_4d(smem + kAtQ + kAtSub, &tmA, &bars[kBarK], h * 128 + 64, qt * 128, b, 0);
           }
-          tma_load_4d(smem + kAtKP + (2 * kb) * kAtSub, &tmQKV, &bars[kBarK + kb], HD + h * 128, kb * 128, b, 0);
-          tma_load_4d(smem + kAtKP + (2 * kb + 1) * kAtSub, &tmQKV, &bars[kBarK + kb], HD + h * 128 + 64, kb * 128, b, 0);
+          tma_load_4d(smem + kAtKP + (2 * kb) * kAtSub, &tmQKV, &bars[kBarK + kb], p.b1_col + h * 128, kb * 128, b, 0);
+          tma_load_4d(smem + kAtKP + (2 * kb + 1) * kAtSub, &tmQKV, &bars[kBarK + kb], p.b1_col + h * 128 + 64, kb * 128, b, 0);
         }
         for (int kb = 0; kb < NB; ++kb) {
           uint8_t* dst = smem + at_v_offset(kb);
           if (kb == 2) mbar_wait(&bars[kBarS + NB - 1], ph);       // every Q K^T product has retired: Q is dead
           if (kb == 3) mbar_wait(&bars[kBarPv0], ph);             // P_0 V_0 has retired: V stage 0 is free
           mbar_expect_tx(&bars[kBarV + kb], 2u * kAtSub);
-          tma_load_4d(dst, &tmQKV, &bars[kBarV + kb], 2 * HD + h * 128, kb * 128, b, 0);
-          tma_load_4d(dst + kAtSub, &tmQKV, &bars[kBarV + kb], 2 * HD + h * 128 + 64, kb * 128, b, 0);
+          tma_load_4d(dst, &tmQKV, &bars[kBarV + kb], p.b2_col + h * 128, kb * 128, b, 0);
+          tma_load_4d(dst + kAtSub, &tmQKV, &bars[kBarV + kb], p.b2_col + h * 128 + 64, kb * 128, b, 0);
         }
       }
     }
@@ -181,10 +197,15 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       const int qt = (int)(tile % p.NQ);
       const int bh = (int)(tile / p.NQ);
       const int h = bh % p.H, b = bh / p.H;
-      long long kl = p.key_len ? p.key_len[b] : (long long)p.N;
+      long long kl = (!BWD && p.key_len) ? p.key_len[b] : (long long)p.N;
       if (kl > p.N) kl = p.N;
-      float m = -INFINITY, l = 0.f;
       uint32_t v[64];
+      float out_scale = 1.f;
+      const bool prof = p.prof && blockIdx.x == 0 && threadIdx.x == 128;
+      long long tp0 = 0, tp1 = 0, tp2 = 0, tp3 = 0;
+      if (prof) tp0 = clock64();
+      if constexpr (!BWD) {
+      float m = -INFINITY, l = 0.f;
       // pass 1: running max / sum over this thread's 64 columns of every key block
       for (int kb = 0; kb < NB; ++kb) {
         mbar_wait(&bars[kBarS + kb], ph);
@@ -209,6 +230,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         }
         l += s0 + s1;
       }
+      if (prof) tp1 = clock64();
       red[half * 128 + row] = make_float2(m, l);
       asm volatile("bar.sync 1, 256;" ::: "memory");
       {
@@ -241,24 +263,80 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         fence_proxy_async_smem();
         mbar_arrive(&bars[kBarP + kb]);
       }
-      // output: O (fp32, TMEM columns [0,128)) -> bf16 rows of the [R, N, H*128] buffer
+      } else {
+        // delta = rowsum(dO o O): each of the row's two threads sums its 64 columns
+        const long long orow = ((long long)b * p.N + qt * 128 + row) * HD + h * 128 + half * 64;
+        const uint4* o4 = reinterpret_cast<const uint4*>(p.O + orow);
+        const uint4* g4 = reinterpret_cast<const uint4*>(p.dO + orow);
+        float d = 0.f;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          const uint4 ov = __ldg(o4 + c), gv = __ldg(g4 + c);
+          const uint32_t ow[4] = {ov.x, ov.y, ov.z, ov.w}, gw[4] = {gv.x, gv.y, gv.z, gv.w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            d = fmaf(__uint_as_float(ow[j] << 16), __uint_as_float(gw[j] << 16), d);
+            d = fmaf(__uint_as_float(ow[j] & 0xffff0000u), __uint_as_float(gw[j] & 0xffff0000u), d);
+          }
+        }
+        red[half * 128 + row] = make_float2(d, 0.f);
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        const float delta = d + red[(half ^ 1) * 128 + row].x;
+        out_scale = p.out_scale;
+        const __nv_bfloat16* prow = p.P + ((long long)bh * p.N + qt * 128 + row) * p.N + half * 64;
+        for (int kb = 0; kb < NB; ++kb) {
+          uint4 pv[8];
+#pragma unroll
+          for (int c = 0; c < 8; ++c) pv[c] = __ldg(reinterpret_cast<const uint4*>(prow + kb * 128) + c);
+          mbar_wait(&bars[kBarS + kb], ph);
+          tc_fence_after();
+          tmem_ld32(t_row + kb * 128, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+          tmem_ld32(t_row + kb * 128 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+          tmem_ld_wait();
+          uint8_t* dst = smem + kAtKP + (2 * kb + half) * kAtSub + row * 128;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            const uint32_t pw[4] = {pv[c].x, pv[c].y, pv[c].z, pv[c].w};
+            uint32_t w[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const int i = c * 8 + 2 * j;
+              const float p0 = __uint_as_float(pw[j] << 16), p1 = __uint_as_float(pw[j] & 0xffff0000u);
+              w[j] = pack_bf16(p0 * (__uint_as_float(v[i]) - delta), p1 * (__uint_as_float(v[i + 1]) - delta));
+            }
+            *reinterpret_cast<uint4*>(dst + ((c ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+          }
+          tc_fence_before();
+          fence_proxy_async_smem();
+          mbar_arrive(&bars[kBarP + kb]);
+        }
+      }
+      // output: accumulator (fp32, TMEM columns [0,128)) -> bf16 rows of O / dq
+      if (prof) tp2 = clock64();
       mbar_wait(&bars[kBarO], ph);
+      if (prof) tp3 = clock64();
       tc_fence_after();
       tmem_ld32(t_row, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
       tmem_ld32(t_row + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
       tmem_ld_wait();
       {
-        uint4* out = reinterpret_cast<uint4*>(p.O + ((long long)b * p.N + qt * 128 + row) * HD + h * 128 + half * 64);
+        uint4* out = reinterpret_cast<uint4*>(p.out + ((long long)b * p.N + qt * 128 + row) * p.out_ld + h * 128 + half * 64);
 #pragma unroll
         for (int c = 0; c < 8; ++c)
-          out[c] = make_uint4(pack_bf16(__uint_as_float(v[8 * c]), __uint_as_float(v[8 * c + 1])),
-                              pack_bf16(__uint_as_float(v[8 * c + 2]), __uint_as_float(v[8 * c + 3])),
-                              pack_bf16(__uint_as_float(v[8 * c + 4]), __uint_as_float(v[8 * c + 5])),
-                              pack_bf16(__uint_as_float(v[8 * c + 6]), __uint_as_float(v[8 * c + 7])));
+          out[c] = make_uint4(pack_bf16(__uint_as_float(v[8 * c]) * out_scale, __uint_as_float(v[8 * c + 1]) * out_scale),
+                              pack_bf16(__uint_as_float(v[8 * c + 2]) * out_scale, __uint_as_float(v[8 * c + 3]) * out_scale),
+                              pack_bf16(__uint_as_float(v[8 * c + 4]) * out_scale, __uint_as_float(v[8 * c + 5]) * out_scale),
+                              pack_bf16(__uint_as_float(v[8 * c + 6]) * out_scale, __uint_as_float(v[8 * c + 7]) * out_scale));
       }
       tc_fence_before();
       fence_proxy_async_smem();
       mbar_arrive(&bars[kBarDone]);
+      if (prof) {
+        const long long tp4 = clock64();
+        p.prof[0] += 1; p.prof[1] += tp1 - tp0; p.prof[2] += tp2 - tp1; p.prof[3] += tp3 - tp2; p.prof[4] += tp4 - tp3;
+        if (it > 0) p.prof[5] += tp0 - p.prof[7];
+        p.prof[7] = tp4;
+      }
     }
   }
   tc_fence_before();
@@ -275,6 +353,21 @@ int gemm_num_sms();
 
 int attn_fwd_ok(int N, int D) { return D == 128 && N >= 128 && N <= 512 && N % 128 == 0; }
 
+template <bool BWD>
+static int attn_launch(const CUtensorMap& ta, const CUtensorMap& tq, const CUtensorMap& tp, const AttnDev& p, cudaStream_t st) {
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(attn_kernel<BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAtSmemMax);
+    if (e != cudaSuccess) return (int)e;
+    attr_done = true;
+  }
+  const int sms = gemm_num_sms();
+  const int grid = (int)(p.tiles < sms ? p.tiles : sms);
+  attn_kernel<BWD><<<grid, kAtThreads, kAtSmemMax, st>>>(ta, tq, tp, p);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
 int attn_fwd(const void* qkv, const long long* key_len, void* O, void* P, long long R, int N, int H, int D, float scale,
              cudaStream_t st) {
   if (R <= 0) return AS_OK;
@@ -289,23 +382,42 @@ int attn_fwd(const void* qkv, const long long* key_len, void* O, void* P, long l
   } else {
     tp = tq;
   }
-  static bool attr_done = false;
-  if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAtSmemMax);
-    if (e != cudaSuccess) return (int)e;
-    attr_done = true;
-  }
-  AttnDev p;
+  AttnDev p = {};
   p.key_len = key_len;
-  p.O = reinterpret_cast<__nv_bfloat16*>(O);
+  p.out = reinterpret_cast<__nv_bfloat16*>(O);
   p.R = (int)R; p.N = N; p.H = H; p.NB = N / 128; p.NQ = N / 128; p.store_p = P ? 1 : 0;
-  p.scale_log2 = scale * kLog2e;
+  p.out_ld = H * D; p.b1_col = H * D; p.b2_col = 2 * H * D;
+  p.scale_log2 = scale * kLog2e; p.out_scale = 1.f;
   p.tiles = R * H * p.NQ;
-  const int sms = gemm_num_sms();
-  const int grid = (int)(p.tiles < sms ? p.tiles : sms);
-  attn_fwd_kernel<<<grid, kAtThreads, kAtSmemMax, st>>>(tq, tp, p);
-  AS_LAUNCH_CHECK();
-  return AS_OK;
+  p.prof = g_attn_prof;
+  return attn_launch<false>(tq, tq, tp, p, st);
+}
+
+// dS [R,H,N,N] and dq (column block 0 of dqkv [R,N,3*H*D]) from P, O, dO, qkv; dK and dV remain GEMMs over dS / P.
+int attn_bwd_dq(const void* qkv, const void* O, const void* dO, const void* P, void* dS, void* dqkv, long long R, int N, int H,
+                int D, float scale, cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (!attn_fwd_ok(N, D) || H <= 0) return AS_EUNSUPPORTED;
+  if (!qkv || !O || !dO || !P || !dS || !dqkv) return AS_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(O) | reinterpret_cast<uintptr_t>(P)) & 15) return AS_EALIGN;
+  CUtensorMap tq, ta, tp;
+  int rc = make_map_bf16(&tq, qkv, 3LL * H * D, N, 3LL * H * D, (int)R, (long long)N * 3 * H * D, 1, 0, 64, 128);
+  if (rc != AS_OK) return rc;
+  rc = make_map_bf16(&ta, dO, (long long)H * D, N, (long long)H * D, (int)R, (long long)N * H * D, 1, 0, 64, 128);
+  if (rc != AS_OK) return rc;
+  rc = make_map_bf16(&tp, dS, N, N, N, (int)(R * H), (long long)N * N, 1, 0, 64, 128);
+  if (rc != AS_OK) return rc;
+  AttnDev p = {};
+  p.out = reinterpret_cast<__nv_bfloat16*>(dqkv);
+  p.O = reinterpret_cast<const __nv_bfloat16*>(O);
+  p.dO = reinterpret_cast<const __nv_bfloat16*>(dO);
+  p.P = reinterpret_cast<const __nv_bfloat16*>(P);
+  p.R = (int)R; p.N = N; p.H = H; p.NB = N / 128; p.NQ = N / 128; p.store_p = 1;
+  p.out_ld = 3 * H * D; p.b1_col = 2 * H * D; p.b2_col = H * D;
+  p.scale_log2 = 0.f; p.out_scale = scale;
+  p.tiles = R * H * p.NQ;
+  p.prof = g_attn_prof;
+  return attn_launch<true>(ta, tq, tp, p, st);
 }
 
 }  // namespace as

@@ -338,8 +338,9 @@ class AttentionFn(torch.autograd.Function):
             O = torch.empty((R, N, H * D), dtype=torch.bfloat16, device=qkv.device)
             _lib.call('as_attn_fwd', qkv.data_ptr(), _ptr(kl), O.data_ptr(), _ptr(P), R, N, H, D, scale, _lib.stream_ptr())
             ctx.dims = (R, N, N, H, D)
+            ctx.fused = True
             if need_p:
-                ctx.save_for_backward(qkv, P)
+                ctx.save_for_backward(qkv, P, O)
             return O
         Np = (N + 7) // 8 * 8                       # pitch of the score rows (bf16 P must be 16-byte pitched)
         S = torch.empty((R, H, N, Np), dtype=SCORE_DTYPE, device=qkv.device)
@@ -353,12 +354,13 @@ class AttentionFn(torch.autograd.Function):
         gemm(P, v, O, N, D, N, lda=Np, b_mn=True, ldb=ld, ldc=H * D, batch=(H, R),
              a_strides=(N * Np, H * N * Np), b_strides=(D, N * ld), c_strides=(D, N * H * D))
         ctx.dims = (R, N, Np, H, D)
+        ctx.fused = False
         ctx.save_for_backward(qkv, P)
         return O
 
     @staticmethod
     def backward(ctx, dO):
-        qkv, P = ctx.saved_tensors
+        qkv, P = ctx.saved_tensors[:2]
         R, N, Np, H, D = ctx.dims
         ld = 3 * H * D
         scale = 1.0 / math.sqrt(D)
@@ -368,6 +370,17 @@ class AttentionFn(torch.autograd.Function):
         dq, dk, dv = dqkv[:, :, :H * D], dqkv[:, :, H * D:2 * H * D], dqkv[:, :, 2 * H * D:]
         sP, sO = (N * Np, H * N * Np), (D, N * H * D)
         sQ = (D, N * ld)
+        if ctx.fused:
+            # dP stays in tensor memory: one launch gives dS and dQ; dV and dK are the two query-summed products
+            O = ctx.saved_tensors[2]
+            dS = torch.empty((R, H, N, N), dtype=torch.bfloat16, device=qkv.device)
+            _lib.call('as_attn_bwd_dq', qkv.data_ptr(), O.data_ptr(), dO.data_ptr(), P.data_ptr(), dS.data_ptr(),
+                      dqkv.data_ptr(), R, N, H, D, scale, _lib.stream_ptr())
+            gemm(P, dO, dv, N, D, N, a_mn=True, lda=Np, b_mn=True, ldb=H * D, ldc=ld, batch=(H, R), a_strides=sP,
+                 b_strides=sO, c_strides=sQ)
+            gemm(dS, q, dk, N, D, N, a_mn=True, lda=Np, b_mn=True, ldb=ld, ldc=ld, batch=(H, R), a_strides=sP,
+                 b_strides=sQ, c_strides=sQ, alpha=scale)
+            return dqkv, None, None, None
         # dP = dO V^T
         dP = torch.empty((R, H, N, Np), dtype=SCORE_DTYPE, device=qkv.device)
         gemm(dO, v, dP, N, N, D, lda=H * D, ldb=ld, ldc=Np, batch=(H, R), a_strides=sO, b_strides=sQ, c_strides=sP)

@@ -227,6 +227,12 @@ int as_su_mask_logits(const float* x, const int64_t* selected_units, const int64
 int as_attn_fwd_ok(int N, int D);
 int as_attn_fwd(const void* qkv, const int64_t* key_len, void* out, void* probs, int64_t R, int N, int H, int D, float scale,
                 void* stream);
+/* as_attn_bwd_dq: query side of the attention backward in one launch with the same pipeline: dP = dout V^T stays in
+ * tensor memory, dscores = probs o (dP - rowsum(dout o out)) is written once as bf16 [R,H,N,N] (for the dK product)
+ * and dq = scale * dscores K goes to the q column block of dqkv [R,N,3*H*D].  dK = scale dscores^T Q and
+ * dV = probs^T dout remain as_gemm_bf16 calls. */
+int as_attn_bwd_dq(const void* qkv, const void* out, const void* dout, const void* probs, void* dscores, void* dqkv, int64_t R, int N,
+                   int H, int D, float scale, void* stream);
 
 /* as_su_sample: the whole SelectedUnits SAMPLING loop (head/action_arg_head.py:262-313: up to 64 autoregressive picks
  * per row) in one launch.  query_fc1 o (ae0 + embed_fc2(.)) is folded by the caller into c0 = Wq1 ae0 + bq1 [R,256],

@@ -57,3 +57,14 @@ with torch.no_grad():
     t_old = timeit(lambda: K.attention(qkv, key_len, H, D))
 flops = 4.0 * R * H * N * N * D
 print('fused+P %.3f ms (%.0f TF/s)  fused %.3f ms (%.0f TF/s)  composed %.3f ms' % (t_p, flops / t_p / 1e9, t_np, flops / t_np / 1e9, t_old))
+
+prof = torch.zeros(8, dtype=torch.int64, device='cuda')
+_lib.lib().as_debug_attn_profile.argtypes = [__import__('ctypes').c_void_p]
+_lib.lib().as_debug_attn_profile(prof.data_ptr())
+_lib.call('as_attn_fwd', qkv.data_ptr(), key_len.data_ptr(), O.data_ptr(), P.data_ptr(), R, N, H, D, scale, _lib.stream_ptr())
+torch.cuda.synchronize()
+_lib.lib().as_debug_attn_profile(0)
+pr = prof.tolist()
+n = max(pr[0], 1)
+print('fwd CTA0 items %d: pass1(incl. wait S0) %.0f  exchange+pass2 %.0f  wait O %.0f  store %.0f  gap to next item %.0f clk'
+      % (pr[0], pr[1] / n, pr[2] / n, pr[3] / n, pr[4] / n, pr[5] / max(n - 1, 1)))
