@@ -51,10 +51,11 @@ static long long* g_attn_prof = nullptr;
 int attn_set_profile(long long* buf) { g_attn_prof = buf; return AS_OK; }
 
 // barrier indices
-enum { kBarK = 0, kBarS = 4, kBarP = 8, kBarV = 12, kBarPv0 = 16, kBarO = 17, kBarDone = 18, kBarCount = 19 };
+enum { kBarK = 0, kBarS = 4, kBarP = 8, kBarV = 12, kBarPv = 16, kBarO = 20, kBarDone = 21, kBarCount = 22 };
 
-// V block -> buffer: 0 and 3 share stage 0 (3 is loaded once P_0 V_0 has retired), 1 -> stage 1, 2 -> the dead Q tile
-__device__ __forceinline__ int at_v_offset(int kb) { return kb == 2 ? kAtQ : kAtV + (kb == 1 ? 2 * kAtSub : 0); }
+// second-operand block at position o of the item's block order -> buffer: 0 and 3 share stage 0, 1 -> stage 1,
+// 2 -> the dead Q tile
+__device__ __forceinline__ int at_v_offset(int o) { return o == 2 ? kAtQ : kAtV + (o == 1 ? 2 * kAtSub : 0); }
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
@@ -86,7 +87,7 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const int NB = p.NB, HD = p.H * 128;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < kBarCount; ++i) mbar_init(&bars[i], (i >= kBarP && i < kBarP + 4) ? 256u : (i == kBarDone ? 257u : 1u));
+    for (int i = 0; i < kBarCount; ++i) mbar_init(&bars[i], (i >= kBarP && i < kBarP + 4) ? 256u : (i == kBarDone ? 256u : 1u));
     mbar_fence_init();
     tma_prefetch_desc(&tmQKV);
     tma_prefetch_desc(&tmA);
@@ -99,7 +100,9 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ------------------------------------------------------------------ TMA producer
+    // ------------------------------------------------------------------ TMA producer (+ TMA stores of P / dS)
+    // Buffers are handed back block by block: K/P tile kb of the next item is loaded as soon as P_kb V_kb of this item
+    // has retired (kBarPv + kb), so the next item's first products run under this item's epilogue.
     if (lane == 0) {
       uint32_t it = 0;
       for (long long tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
@@ -107,40 +110,71 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         const int qt = (int)(tile % p.NQ);
         const int bh = (int)(tile / p.NQ);
         const int h = bh % p.H, b = bh / p.H;
-        if (it > 0) mbar_wait(&bars[kBarDone], ph ^ 1u);           // previous item: K/P, Q and V buffers are free
-        for (int kb = 0; kb < NB; ++kb) {
-          mbar_expect_tx(&bars[kBarK + kb], (kb == 0 ? 4u : 2u) * kAtSub);
-          if (kb == 0) {
-            tma_load_4d(smem + kAtQ, &tmA, &bars[kBarK], h * 128, qt * 128, b, 0);
-            tma_load_4d(smem + kAtQ + kAtSub, &tmA, &bars[kBarK], h * 128 + 64, qt * 128, b, 0);
+        if (it > 0) {
+          if (p.store_p) tma_store_wait_read();                    // the stores of the previous item have read their tiles
+          for (int kb = 0; kb < NB; ++kb) mbar_wait(&bars[kBarPv + kb], ph ^ 1u);
+        }
+        const int rot = (int)(it % (uint32_t)NB);                  // block order of this item: rot, rot+1, .. (MMA warp)
+        for (int o = 0; o < NB; ++o) {
+          const int kb = rot + o < NB ? rot + o : rot + o - NB;
+          mbar_expect_tx(&bars[kBarK + kb], (o == 0 ? 4u : 2u) * kAtSub);
+          if (o == 0) {
+            tma_load_4d(smem + kAtQ, &tmA, &bars[kBarK + kb], h * 128, qt * 128, b, 0);
+            tma_load_4d(smem + kAtQ + kAtSub, &tmA, &bars[kBarK + kb], h * 128 + 64, qt * 128, b, 0);
           }
           tma_load_4d(smem + kAtKP + (2 * kb) * kAtSub, &tmQKV, &bars[kBarK + kb], p.b1_col + h * 128, kb * 128, b, 0);
           tma_load_4d(smem + kAtKP + (2 * kb + 1) * kAtSub, &tmQKV, &bars[kBarK + kb], p.b1_col + h * 128 + 64, kb * 128, b, 0);
         }
-        for (int kb = 0; kb < NB; ++kb) {
-          uint8_t* dst = smem + at_v_offset(kb);
-          if (kb == 2) mbar_wait(&bars[kBarS + NB - 1], ph);       // every Q K^T product has retired: Q is dead
-          if (kb == 3) mbar_wait(&bars[kBarPv0], ph);             // P_0 V_0 has retired: V stage 0 is free
-          mbar_expect_tx(&bars[kBarV + kb], 2u * kAtSub);
-          tma_load_4d(dst, &tmQKV, &bars[kBarV + kb], p.b2_col + h * 128, kb * 128, b, 0);
-          tma_load_4d(dst + kAtSub, &tmQKV, &bars[kBarV + kb], p.b2_col + h * 128 + 64, kb * 128, b, 0);
+        // second-operand blocks by POSITION o in the order: 0 -> stage 0, 1 -> stage 1, 2 -> the Q tile (once every
+        // first product has retired), 3 -> stage 0 again (once the position-0 second product has retired)
+        auto load_v = [&](int o) {
+          const int kb = rot + o < NB ? rot + o : rot + o - NB;
+          uint8_t* dst = smem + at_v_offset(o);
+          mbar_expect_tx(&bars[kBarV + o], 2u * kAtSub);
+          tma_load_4d(dst, &tmQKV, &bars[kBarV + o], p.b2_col + h * 128, kb * 128, b, 0);
+          tma_load_4d(dst + kAtSub, &tmQKV, &bars[kBarV + o], p.b2_col + h * 128 + 64, kb * 128, b, 0);
+        };
+        load_v(0);
+        if (NB > 1) load_v(1);
+        if (NB > 2) {
+          const int last = rot + NB - 1 < NB ? rot + NB - 1 : rot - 1;
+          mbar_wait(&bars[kBarS + last], ph);
+          load_v(2);
+        }
+        for (int o = 0; o < NB; ++o) {
+          const int kb = rot + o < NB ? rot + o : rot + o - NB;
+          if (p.store_p) {
+            mbar_wait(&bars[kBarP + kb], ph);                      // tile kb written (and proxy-fenced) by all 256 threads
+            tma_store_4d(&tmP, smem + kAtKP + (2 * kb) * kAtSub, kb * 128, qt * 128, bh, 0);
+            tma_store_4d(&tmP, smem + kAtKP + (2 * kb + 1) * kAtSub, kb * 128 + 64, qt * 128, bh, 0);
+            tma_store_commit();
+          }
+          if (o == 0 && NB > 3) {
+            mbar_wait(&bars[kBarPv + kb], ph);
+            load_v(3);
+          }
         }
       }
+      if (p.store_p) tma_store_wait_all();
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (warp-uniform, one lane issues)
+    // Item `it` walks its key blocks in the order rot, rot+1, .. (rot = it mod NB) and accumulates the second product
+    // in the TMEM columns of block rot, the first one the softmax warps consume.  The next item starts at rot+1: the
+    // columns of all its blocks but the last are free once this item's softmax has consumed them (this warp has waited
+    // for that before issuing this item's second products), and its last block -- this item's accumulator -- waits for
+    // the epilogue.  So the next item's first products run under this item's epilogue.
     constexpr uint32_t kDescHi = (1024u >> 4) | (1u << 14) | (2u << 29);
     constexpr uint32_t idesc_qk = (1u << 4) | (1u << 7) | (1u << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
-    constexpr uint32_t idesc_pv = idesc_qk | (1u << 16);           // B (= V) is MN-major
+    constexpr uint32_t idesc_pv = idesc_qk | (1u << 16);           // second B operand is MN-major
     const uint32_t sbase = smem_u32(smem);
     uint32_t it = 0;
     for (long long tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
       const uint32_t ph = it & 1u;
-      const int qt = (int)(tile % p.NQ);
-      const int bh = (int)(tile / p.NQ);
-      if (it > 0) mbar_wait(&bars[kBarDone], ph ^ 1u);             // TMEM drained by the epilogue of the previous item
-      tc_fence_after();
-      for (int kb = 0; kb < NB; ++kb) {
+      const int rot = (int)(it % (uint32_t)NB);
+      for (int o = 0; o < NB; ++o) {
+        const int kb = rot + o < NB ? rot + o : rot + o - NB;
+        if (o == NB - 1 && it > 0) mbar_wait(&bars[kBarDone], ph ^ 1u);  // accumulator drained by the previous epilogue
         mbar_wait(&bars[kBarK + kb], ph);
         tc_fence_after();
 #pragma unroll
@@ -156,33 +190,23 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
         umma_commit_lead(0, &bars[kBarS + kb]);
       }
-      for (int kb = 0; kb < NB; ++kb) {
+      for (int o = 0; o < NB; ++o) {
+        const int kb = rot + o < NB ? rot + o : rot + o - NB;
         mbar_wait(&bars[kBarP + kb], ph);
-        mbar_wait(&bars[kBarV + kb], ph);
+        mbar_wait(&bars[kBarV + o], ph);
         tc_fence_after();
-        const uint32_t vaddr = sbase + (uint32_t)at_v_offset(kb);
+        const uint32_t vaddr = sbase + (uint32_t)at_v_offset(o);
         const uint32_t b_lo = ((uint32_t)(kAtSub >> 4) << 16) | (vaddr >> 4);
 #pragma unroll
         for (int s = 0; s < 8; ++s) {
           const uint32_t a_lo = (1u << 16) | ((sbase + kAtKP + (2 * kb + (s >> 2)) * kAtSub) >> 4);
           const uint64_t da = ((uint64_t)kDescHi << 32) | (a_lo + 2u * (s & 3));
           const uint64_t db = ((uint64_t)kDescHi << 32) | (b_lo + (uint32_t)(s * (16 * 128 / 16)));
-          umma_bf16_lead(0, tmem_base, da, db, idesc_pv, (kb | s) ? 1u : 0u);
+          umma_bf16_lead(0, tmem_base + (uint32_t)(rot * 128), da, db, idesc_pv, (o | s) ? 1u : 0u);
         }
-        if (kb == 0) umma_commit_lead(0, &bars[kBarPv0]);
-        if (p.store_p && lane == 0) {                              // probabilities for the backward pass
-          tma_store_4d(&tmP, smem + kAtKP + (2 * kb) * kAtSub, kb * 128, qt * 128, bh, 0);
-          tma_store_4d(&tmP, smem + kAtKP + (2 * kb + 1) * kAtSub, kb * 128 + 64, qt * 128, bh, 0);
-          tma_store_commit();
-        }
-        __syncwarp();
+        umma_commit_lead(0, &bars[kBarPv + kb]);
       }
       umma_commit_lead(0, &bars[kBarO]);
-      if (lane == 0) {
-        if (p.store_p) tma_store_wait_read();
-        mbar_arrive(&bars[kBarDone]);
-      }
-      __syncwarp();
     }
   } else if (warp >= 4) {
     // ------------------------------------------------------------------ softmax + output (8 warps, 256 threads)
@@ -201,13 +225,15 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       if (kl > p.N) kl = p.N;
       uint32_t v[64];
       float out_scale = 1.f;
+      const int rot = (int)(it % (uint32_t)NB);                    // block order rot, rot+1, ..; accumulator in block rot
       const bool prof = p.prof && blockIdx.x == 0 && threadIdx.x == 128;
       long long tp0 = 0, tp1 = 0, tp2 = 0, tp3 = 0;
       if (prof) tp0 = clock64();
       if constexpr (!BWD) {
       float m = -INFINITY, l = 0.f;
       // pass 1: running max / sum over this thread's 64 columns of every key block
-      for (int kb = 0; kb < NB; ++kb) {
+      for (int o = 0; o < NB; ++o) {
+        const int kb = rot + o < NB ? rot + o : rot + o - NB;
         mbar_wait(&bars[kBarS + kb], ph);
         tc_fence_after();
         tmem_ld32(t_row + kb * 128, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
@@ -241,7 +267,8 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       }
       const float rinv = 1.f / l;
       // pass 2: normalised probabilities -> bf16 -> the A-operand tiles (128-byte swizzle: chunk c of row r at c ^ (r & 7))
-      for (int kb = 0; kb < NB; ++kb) {
+      for (int o = 0; o < NB; ++o) {
+        const int kb = rot + o < NB ? rot + o : rot + o - NB;
         tmem_ld32(t_row + kb * 128, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
         tmem_ld32(t_row + kb * 128 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
         tmem_ld_wait();
@@ -284,7 +311,8 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         const float delta = d + red[(half ^ 1) * 128 + row].x;
         out_scale = p.out_scale;
         const __nv_bfloat16* prow = p.P + ((long long)bh * p.N + qt * 128 + row) * p.N + half * 64;
-        for (int kb = 0; kb < NB; ++kb) {
+        for (int o = 0; o < NB; ++o) {
+          const int kb = rot + o < NB ? rot + o : rot + o - NB;
           uint4 pv[8];
 #pragma unroll
           for (int c = 0; c < 8; ++c) pv[c] = __ldg(reinterpret_cast<const uint4*>(prow + kb * 128) + c);
@@ -316,8 +344,8 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       mbar_wait(&bars[kBarO], ph);
       if (prof) tp3 = clock64();
       tc_fence_after();
-      tmem_ld32(t_row, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
-      tmem_ld32(t_row + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+      tmem_ld32(t_row + rot * 128, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+      tmem_ld32(t_row + rot * 128 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
       tmem_ld_wait();
       {
         uint4* out = reinterpret_cast<uint4*>(p.out + ((long long)b * p.N + qt * 128 + row) * p.out_ld + h * 128 + half * 64);
@@ -329,7 +357,6 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                               pack_bf16(__uint_as_float(v[8 * c + 6]) * out_scale, __uint_as_float(v[8 * c + 7]) * out_scale));
       }
       tc_fence_before();
-      fence_proxy_async_smem();
       mbar_arrive(&bars[kBarDone]);
       if (prof) {
         const long long tp4 = clock64();

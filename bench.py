@@ -152,13 +152,13 @@ class ClockSampler:
 
 
 def gemm_flops_hook(records):
-    """Wrap _lib.call so every as_gemm_bf16 / as_conv_nhwc_bf16 / as_attn_fwd launch is bracketed by CUDA events (used for ONE
+    """Wrap _lib.call so every as_gemm_bf16 / as_conv_nhwc_bf16 / as_attn_* launch is bracketed by CUDA events (used for ONE
     extra instrumented step after the timed region; the timed steps run unhooked)."""
     from applestar_b200 import _lib
     orig = _lib.call
 
     def hooked(name, *a):
-        if name not in ('as_gemm_bf16', 'as_conv_nhwc_bf16', 'as_attn_fwd'):
+        if name not in ('as_gemm_bf16', 'as_conv_nhwc_bf16', 'as_attn_fwd', 'as_attn_bwd_dq'):
             return orig(name, *a)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -169,6 +169,9 @@ def gemm_flops_hook(records):
             fl = 2.0 * M * N * K * nb
         elif name == 'as_attn_fwd':                       # Q K^T and P V: 2 x (2 N N D) per (row, head)
             R, N, H, D = a[4], a[5], a[6], a[7]
+            fl = 4.0 * R * H * N * N * D
+        elif name == 'as_attn_bwd_dq':                    # dO V^T and dS K
+            R, N, H, D = a[6], a[7], a[8], a[9]
             fl = 4.0 * R * H * N * N * D
         else:
             R, H, W, Cin, Cout, taps = a[4], a[5], a[6], a[7], a[8], a[9]
@@ -311,7 +314,7 @@ def run_ours(args):
                     'd2h_bytes_per_step': 4 * _lib.AS_LOSS_MAX_STATS},
             'gpu_launches': int(launches),
             'clocks': clocks,
-            'roofline': {'bound': 'tensor', 'kernel': 'tcgen05 kernels as::gemm_kernel + as::attn_fwd_kernel (all %d launches of one step)' % len(records),
+            'roofline': {'bound': 'tensor', 'kernel': 'tcgen05 kernels as::gemm_kernel + as::attn_kernel (all %d launches of one step)' % len(records),
                          'achieved': achieved, 'peak': tf_sus, 'unit': 'TFLOP/s', 'frac': achieved / tf_sus,
                          'peak_source': which + ' bf16_tflops_sustained', 'gemm_ms_per_step': g_ms,
                          'gemm_share_of_step': g_ms / (ms / args.steps), 'traffic': None},
