@@ -11,6 +11,9 @@ extern int g_gemm_no_slab;
 int gemm_set_profile(long long*);
 int attn_fwd_ok(int, int);
 int attn_set_profile(long long*);
+int attn_small_ok(int, int);
+int attn_small_fwd(const void*, const long long*, void*, long long, int, int, int, float, cudaStream_t);
+int attn_small_bwd(const void*, const long long*, const void*, void*, long long, int, int, int, float, cudaStream_t);
 int attn_fwd(const void*, const long long*, void*, void*, long long, int, int, int, float, cudaStream_t);
 int attn_bwd_dq(const void*, const void*, const void*, const void*, void*, void*, long long, int, int, int, float, cudaStream_t);
 int scatter_fwd(const float*, const void*, const void*, int, const long long*, float*, long long, int, int, int, int,
@@ -286,6 +289,14 @@ int as_attn_fwd(const void* qkv, const int64_t* key_len, void* out, void* probs,
 int as_attn_bwd_dq(const void* qkv, const void* out, const void* dout, const void* probs, void* dscores, void* dqkv, int64_t R, int N,
                    int H, int D, float scale, void* stream) {
   return as::attn_bwd_dq(qkv, out, dout, probs, dscores, dqkv, R, N, H, D, scale, ST(stream));
+}
+int as_attn_small_ok(int N, int D) { return as::attn_small_ok(N, D); }
+int as_attn_small_fwd(const void* qkv, const int64_t* key_len, void* out, int64_t R, int N, int H, int D, float scale, void* stream) {
+  return as::attn_small_fwd(qkv, reinterpret_cast<const long long*>(key_len), out, R, N, H, D, scale, ST(stream));
+}
+int as_attn_small_bwd(const void* qkv, const int64_t* key_len, const void* dout, void* dqkv, int64_t R, int N, int H, int D,
+                      float scale, void* stream) {
+  return as::attn_small_bwd(qkv, reinterpret_cast<const long long*>(key_len), dout, dqkv, R, N, H, D, scale, ST(stream));
 }
 int as_su_sample(const as_su_sample_args* a, void* stream) {
   if (!a) return AS_EINVAL;

@@ -331,6 +331,15 @@ class AttentionFn(torch.autograd.Function):
         q, k, v = qkv[:, :, :H * D], qkv[:, :, H * D:2 * H * D], qkv[:, :, 2 * H * D:]
         scale = 1.0 / math.sqrt(D)
         kl = None if key_len is None else key_len.contiguous().long()
+        if ATTN_FUSED and _lib.lib().as_attn_small_ok(N, D):
+            # short sequence / narrow heads: one warp per (row, head), nothing saved but the inputs (attn_small.cu)
+            O = torch.empty((R, N, H * D), dtype=torch.bfloat16, device=qkv.device)
+            _lib.call('as_attn_small_fwd', qkv.data_ptr(), _ptr(kl), O.data_ptr(), R, N, H, D, scale, _lib.stream_ptr())
+            ctx.dims = (R, N, N, H, D)
+            ctx.fused = 'small'
+            ctx.kl = kl
+            ctx.save_for_backward(qkv)
+            return O
         if ATTN_FUSED and _lib.lib().as_attn_fwd_ok(N, D):
             # scores stay in tensor memory (attn.cu); P is written only when a backward pass will read it
             need_p = ctx.needs_input_grad[0]
@@ -360,8 +369,15 @@ class AttentionFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dO):
-        qkv, P = ctx.saved_tensors[:2]
         R, N, Np, H, D = ctx.dims
+        if ctx.fused == 'small':
+            qkv, = ctx.saved_tensors
+            dO = to_bf16(dO.contiguous().reshape(R * N, H * D))
+            dqkv = torch.empty_like(qkv)
+            _lib.call('as_attn_small_bwd', qkv.data_ptr(), _ptr(ctx.kl), dO.data_ptr(), dqkv.data_ptr(), R, N, H, D,
+                      1.0 / math.sqrt(D), _lib.stream_ptr())
+            return dqkv, None, None, None
+        qkv, P = ctx.saved_tensors[:2]
         ld = 3 * H * D
         scale = 1.0 / math.sqrt(D)
         dO = to_bf16(dO.contiguous().reshape(R * N, H * D)).view(R, N, H * D)

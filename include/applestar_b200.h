@@ -234,6 +234,14 @@ int as_attn_fwd(const void* qkv, const int64_t* key_len, void* out, void* probs,
 int as_attn_bwd_dq(const void* qkv, const void* out, const void* dout, const void* probs, void* dscores, void* dqkv, int64_t R, int N,
                    int H, int D, float scale, void* stream);
 
+/* as_attn_small_fwd / _bwd: the same attention for short sequences and narrow heads (N <= 32, D in {8, 16}: the
+ * build-order Transformer, obs_encoder/scalar_encoder.py:19-53) -- one warp per (row, head), fp32 in registers,
+ * probabilities recomputed in the backward pass.  dqkv receives dq | dk | dv in the layout of qkv. */
+int as_attn_small_ok(int N, int D);
+int as_attn_small_fwd(const void* qkv, const int64_t* key_len, void* out, int64_t R, int N, int H, int D, float scale, void* stream);
+int as_attn_small_bwd(const void* qkv, const int64_t* key_len, const void* dout, void* dqkv, int64_t R, int N, int H, int D,
+                      float scale, void* stream);
+
 /* as_su_sample: the whole SelectedUnits SAMPLING loop (head/action_arg_head.py:262-313: up to 64 autoregressive picks
  * per row) in one launch.  query_fc1 o (ae0 + embed_fc2(.)) is folded by the caller into c0 = Wq1 ae0 + bq1 [R,256],
  * c1 = Wq1 bf2 [256] and mt = (Wq1 Wf2)^T [256,256]; wf1t/wq2t/wih_t/whh_t are the transposed fp32 weights of

@@ -37,7 +37,8 @@ def test_layer_norm_fwd_bwd(C_, relu):
     assert (b.grad - br.grad).abs().max().item() < 1e-4
 
 
-@pytest.mark.parametrize('N,H,D,masked', [(512, 2, 128, True), (256, 2, 128, True), (20, 2, 8, False)])
+@pytest.mark.parametrize('N,H,D,masked', [(512, 2, 128, True), (256, 2, 128, True), (20, 2, 8, False), (20, 2, 8, True),
+                                           (32, 3, 16, True), (40, 2, 8, True)])
 def test_attention_fwd_bwd(N, H, D, masked):
     from applestar_b200 import kernels as K
     g = torch.Generator().manual_seed(N)
