@@ -21,6 +21,7 @@ int scatter_fwd(const float*, const void*, const void*, int, const long long*, f
 int scatter_bwd(const float*, const void*, const void*, int, const long long*, float*, long long, int, int, int, int,
                 cudaStream_t);
 int cast_f32_bf16(const float*, void*, long long, cudaStream_t);
+int pack_f32(const long long*, int, float*, cudaStream_t);
 int relu_bwd_f32(const float*, const float*, float*, long long, cudaStream_t);
 int gumbel_argmax(const float*, const float*, long long*, long long, int, cudaStream_t);
 int loss_forward(const AsLossArgs&, cudaStream_t);
@@ -375,6 +376,9 @@ int as_entity_features(const void* const* data, const int* kind, const int* num,
   return as::entity_features(data, kind, num, col, dtype, n_fields, out, rows, pitch, neg_flag, ST(stream));
 }
 
+int as_pack_f32(const int64_t* table, int chunks, float* dst, void* stream) {
+  return as::pack_f32(reinterpret_cast<const long long*>(table), chunks, dst, ST(stream));
+}
 int as_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream) {
   return as::cast_f32_bf16(src, dst, n, ST(stream));
 }

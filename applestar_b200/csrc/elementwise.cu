@@ -21,6 +21,31 @@ __global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat1
     dst[i] = __float2bfloat16_rn(src[i]);
 }
 
+// ------------------------------------------------------------------ gradient packing
+// table[c] = {source pointer (0: fill with zeros), destination offset, element count}: one CTA per chunk copies a piece of
+// a parameter's gradient tensor into the flat gradient buffer.  Replaces one `grad += g` launch per parameter.
+__global__ void __launch_bounds__(256) pack_f32_kernel(const long long* __restrict__ table, float* __restrict__ dst) {
+  const long long* e = table + 3LL * blockIdx.x;
+  const float* src = reinterpret_cast<const float*>(e[0]);
+  float* d = dst + e[1];
+  const int n = (int)e[2];
+  if (src && ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(d)) & 15) == 0) {
+    const int n4 = n >> 2;
+    for (int i = threadIdx.x; i < n4; i += 256) reinterpret_cast<float4*>(d)[i] = __ldg(reinterpret_cast<const float4*>(src) + i);
+    for (int i = n4 * 4 + threadIdx.x; i < n; i += 256) d[i] = src[i];
+  } else {
+    for (int i = threadIdx.x; i < n; i += 256) d[i] = src ? src[i] : 0.f;
+  }
+}
+
+int pack_f32(const long long* table, int chunks, float* dst, cudaStream_t st) {
+  if (chunks <= 0) return AS_OK;
+  if (!table || !dst) return AS_EINVAL;
+  pack_f32_kernel<<<chunks, 256, 0, st>>>(table, dst);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
 int cast_f32_bf16(const float* src, void* dst, long long n, cudaStream_t st) {
   if (n <= 0) return AS_OK;
   if (!src || !dst) return AS_EINVAL;

@@ -315,6 +315,7 @@ SCORE_DTYPE = torch.bfloat16 if os.environ.get('APPLESTAR_ATTN_BF16_SCORES', '1'
 
 
 ATTN_FUSED = os.environ.get('APPLESTAR_ATTN_FUSED', '1') != '0'
+ATTN_SMALL = os.environ.get('APPLESTAR_ATTN_SMALL', '1') != '0'
 
 
 class AttentionFn(torch.autograd.Function):
@@ -331,7 +332,7 @@ class AttentionFn(torch.autograd.Function):
         q, k, v = qkv[:, :, :H * D], qkv[:, :, H * D:2 * H * D], qkv[:, :, 2 * H * D:]
         scale = 1.0 / math.sqrt(D)
         kl = None if key_len is None else key_len.contiguous().long()
-        if ATTN_FUSED and _lib.lib().as_attn_small_ok(N, D):
+        if ATTN_FUSED and ATTN_SMALL and _lib.lib().as_attn_small_ok(N, D):
             # short sequence / narrow heads: one warp per (row, head), nothing saved but the inputs (attn_small.cu)
             O = torch.empty((R, N, H * D), dtype=torch.bfloat16, device=qkv.device)
             _lib.call('as_attn_small_fwd', qkv.data_ptr(), _ptr(kl), O.data_ptr(), R, N, H, D, scale, _lib.stream_ptr())

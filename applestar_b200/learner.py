@@ -10,6 +10,8 @@ forward -> loss -> zero_grad -> backward -> sync_gradients -> grad clip -> Adam 
   stream, while the rest of backward is still running (the reference issues 394 blocking per-tensor all_reduces
   after backward, dist_helper.py:421-431).  Trajectories are independent, so there is no other collective.
 """
+import os
+
 import torch
 import torch.distributed as dist
 import torch.nn as nn
@@ -22,6 +24,7 @@ class FlatParams:
     """Re-homes every trainable parameter of `module` into flat buffers (views keep the nn.Parameter objects)."""
 
     ALIGN = 8          # elements: keeps every tensor 32-byte (fp32) / 16-byte (bf16 shadow) aligned for TMA
+    CHUNK = 1 << 16    # elements per CTA of the gradient packing kernel
 
     def __init__(self, module, order=('encoder', 'core_lstm', 'policy', 'value_networks'), with_shadow=True):
         named = [(k, p) for k, p in module.named_parameters() if p.requires_grad]
@@ -45,7 +48,42 @@ class FlatParams:
             p.grad = self.grad[o:o + n].view(p.shape)
             if self.shadow is not None:
                 p._as_shadow = self.shadow[o:o + n].view(p.shape[0], -1) if p.dim() >= 2 else None
+        # CUDA: autograd hands every parameter its gradient as a fresh tensor (p.grad = None before backward, so
+        # AccumulateGrad keeps the incoming tensor instead of launching `grad += g` per parameter) and ONE kernel per
+        # all-reduce bucket gathers them into the flat buffer (`pack`); CPU (gloo tests): gradients accumulate into views
+        self.pack_mode = dev.type == 'cuda' and os.environ.get('APPLESTAR_GRAD_PACK', '1') != '0'
+        self._pack_keep = []
         self.refresh_shadow()
+
+    def pack(self, idx=None):
+        """Copy the .grad tensors of the parameters `idx` (default: all) into their slots of the flat gradient buffer;
+        a parameter that received no gradient gets zeros."""
+        rows, keep = [], []
+        for i in (range(len(self.params)) if idx is None else idx):
+            p, o, n = self.params[i], self.offsets[i], self.params[i].numel()
+            g = p.grad
+            if g is not None and (g.dtype != torch.float32 or not g.is_contiguous()):
+                g = g.float().contiguous()
+            if g is not None and g.data_ptr() == self.grad.data_ptr() + 4 * o:
+                continue                                            # already a view of its slot
+            keep.append(g)
+            src = 0 if g is None else g.data_ptr()
+            for c in range(0, n, self.CHUNK):
+                rows.append((src + 4 * c if src else 0, o + c, min(self.CHUNK, n - c)))
+        if not rows:
+            return
+        host = torch.tensor(rows, dtype=torch.int64).pin_memory()
+        table = host.to(self.grad.device, non_blocking=True)
+        if torch.cuda.is_current_stream_capturing():                # the captured copy re-reads `host` at every replay
+            self._pack_keep.append((host, table, keep))
+        _lib.call('as_pack_f32', table.data_ptr(), len(rows), self.grad.data_ptr(), _lib.stream_ptr())
+
+    def attach_views(self):
+        """Point every p.grad at its slot of the flat buffer (what callers of the reference API read after
+        `sync_gradients`)."""
+        for p, o in zip(self.params, self.offsets):
+            if p.grad is None or p.grad.data_ptr() != self.grad.data_ptr() + 4 * o:
+                p.grad = self.grad[o:o + p.numel()].view(p.shape)
 
     def refresh_shadow(self):
         if self.shadow is not None:
@@ -53,10 +91,12 @@ class FlatParams:
         K.weights_changed()
 
     def zero_grad(self):
+        if self.pack_mode:
+            for p in self.params:
+                p.grad = None
+            return
         self.grad.zero_()
-        for p, o in zip(self.params, self.offsets):          # autograd may have replaced .grad; re-attach the views
-            if p.grad is None or p.grad.data_ptr() != self.grad.data_ptr() + 4 * o:
-                p.grad = self.grad[o:o + p.numel()].view(p.shape)
+        self.attach_views()                                    # autograd may have replaced .grad
 
     def buckets(self, bucket_elems):
         """Contiguous [start, end) ranges of the flat grad buffer, filled from the END (grads of the heads / value
@@ -118,7 +158,9 @@ class DistModule(nn.Module):
         return hook
 
     def _launch(self, b):
-        start, end, _ = self._buckets[b]
+        start, end, idx = self._buckets[b]
+        if self.flat.pack_mode:
+            self.flat.pack(idx)
         chunk = self.flat.grad[start:end]
         if self._comm_stream is not None:
             ev = torch.cuda.Event()
@@ -133,6 +175,9 @@ class DistModule(nn.Module):
     def sync_gradients(self):
         """Average gradients across ranks.  With hooks active this only waits for the in-flight bucket reductions."""
         if self.world <= 1:
+            if self.flat.pack_mode:
+                self.flat.pack()
+                self.flat.attach_views()
             return
         for b, n in enumerate(self._pending):
             if n > 0:                       # parameters that received no gradient this step: reduce what is there
@@ -143,6 +188,8 @@ class DistModule(nn.Module):
             if self._avg is None:
                 chunk.div_(self.world)
         self._works = []
+        if self.flat.pack_mode:
+            self.flat.attach_views()
 
 
 class FusedAdam:

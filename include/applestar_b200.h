@@ -277,6 +277,12 @@ int as_su_sample(const as_su_sample_args* args, void* stream);
 int as_entity_features(const void* const* data, const int* kind, const int* num, const int* col, const int* dtype,
                        int n_fields, void* out, int64_t rows, int pitch, int* neg_flag, void* stream);
 
+/* Gather scattered fp32 tensors into one flat buffer: table (device, 3 x int64 per chunk) = {source pointer or 0 for
+ * zero fill, destination offset in elements, element count}.  Used once per all-reduce bucket to move the parameter
+ * gradients autograd produced into the flat gradient buffer (instead of one accumulate launch per parameter,
+ * rl_learner.py:118-125 / dist_helper.py:421-431 work per parameter tensor). */
+int as_pack_f32(const int64_t* table, int chunks, float* dst, void* stream);
+
 /* fp32 -> bf16 cast (operand staging for the GEMMs). */
 int as_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream);
 

@@ -225,6 +225,34 @@ def test_su_sample_fused_kernel_vs_oracle(R, N, temperature):
 
 
 @gpu
+def test_grad_pack_matches_accumulate(monkeypatch):
+    """FlatParams pack mode (p.grad = None, one as_pack_f32 launch per bucket) fills the flat gradient buffer exactly like
+    accumulation into views does, over two steps, including a parameter that gets no gradient (zeros, not stale data)."""
+    import torch.nn as nn
+    from applestar_b200.learner import DistModule, FlatParams
+    flats = []
+    for mode in ('1', '0'):
+        monkeypatch.setenv('APPLESTAR_GRAD_PACK', mode)
+        torch.manual_seed(3)
+        m = nn.ModuleDict({'a': nn.Linear(70001, 3), 'b': nn.Linear(3, 5), 'unused': nn.Linear(4, 4)}).cuda()
+        dm = DistModule(m, flat=FlatParams(m))
+        assert dm.flat.pack_mode == (mode == '1')
+        for step in range(2):
+            dm.flat.zero_grad()
+            x = torch.randn(6, 70001, device='cuda', generator=torch.Generator('cuda').manual_seed(step))
+            y = m['b'](m['a'](x))
+            if step == 0:
+                y = y.sum() + m['unused'](torch.ones(2, 4, device='cuda')).sum()
+            y.sum().backward()
+            dm.sync_gradients()
+            for p, o in zip(dm.flat.params, dm.flat.offsets):
+                assert p.grad.data_ptr() == dm.flat.grad.data_ptr() + 4 * o       # views again after the sync
+        flats.append(dm.flat.grad.clone())
+    assert torch.equal(flats[0], flats[1])
+    assert float(flats[0].abs().sum()) > 0
+
+
+@gpu
 def test_selected_units_batched_matches_step_loop():
     """ops.selected_units_train (all steps at once) vs the step-by-step loop: logits, final embedding, gradients."""
     from applestar_b200 import ops
