@@ -100,6 +100,8 @@ _SIGS = {
     'as_relu_bwd_colsum_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     'as_spatial_features': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
                                     c_void_p]),
+    'as_spatial_features_scatter': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int,
+                                            c_void_p, c_int64, c_int, c_int, c_void_p]),
     'as_scatter_connection_bwd_pnhwc': (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int64,
                                                 c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     'as_maxpool2_fwd_bf16': (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p]),

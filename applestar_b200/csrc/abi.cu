@@ -75,8 +75,8 @@ int lnlstm_set_profile(long long*);
 int lnlstm_bwd(const float*, const float*, const float*, const float*, const float*, const float*, const float*,
                const float*, const void*, const float*, const float*, const float*, const float*, const float*,
                const float*, const float*, float*, float*, float*, float*, float*, int, int, int, cudaStream_t);
-int spatial_features(const void* const*, const void* const*, int, const float*, void*, long long, int, int, int,
-                     cudaStream_t);
+int spatial_features(const void* const*, const void* const*, int, const float*, const float*, const void*, const void*, int,
+                     const long long*, int, void*, long long, int, int, int, cudaStream_t);
 int scatter_bwd_pnhwc(const void*, const void*, const void*, int, const long long*, float*, long long, int, int, int,
                       int, int, int, cudaStream_t);
 int maxpool2_fwd(const void*, void*, long long, int, int, int, cudaStream_t);
@@ -245,7 +245,14 @@ int as_colsum_bf16(const void* x, float* out, float* scratch, int64_t rows, int 
 
 int as_spatial_features(const void* const* planes, const void* const* effects, int n_eff, const float* scatter_map,
                         void* out, int64_t R, int H, int W, int Cs, void* stream) {
-  return as::spatial_features(planes, effects, n_eff, scatter_map, out, R, H, W, Cs, ST(stream));
+  return as::spatial_features(planes, effects, n_eff, scatter_map, nullptr, nullptr, nullptr, 0, nullptr, 0, out, R, H, W, Cs,
+                              ST(stream));
+}
+int as_spatial_features_scatter(const void* const* planes, const void* const* effects, int n_eff, const float* emb, const void* xs,
+                                const void* ys, int idx_bytes, const int64_t* entity_num, int N, void* out, int64_t R, int H,
+                                int W, void* stream) {
+  return as::spatial_features(planes, effects, n_eff, nullptr, emb, xs, ys, idx_bytes,
+                              reinterpret_cast<const long long*>(entity_num), N, out, R, H, W, 32, ST(stream));
 }
 int as_scatter_connection_bwd_pnhwc(const void* d_feat, const void* xs, const void* ys, int idx_bytes,
                                     const int64_t* entity_num, float* d_emb, int64_t R, int N, int D, int H, int W,

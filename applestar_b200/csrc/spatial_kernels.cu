@@ -902,10 +902,26 @@ struct SpatialPlanes {
 
 constexpr int kFeatBand = 8;   // rows per CTA
 
+// ScatterConnection operands for the fused mode (scatter_map == nullptr): the 32 scatter channels of a pixel are summed
+// straight from the entity embeddings, in ascending entity order like as_scatter_connection_fwd (bit-identical fp32
+// sums), so the dense fp32 map [R,32,H,W] (3.2 GB written and read back at the benchmark size) never exists.
+struct ScatterSrc {
+  const float* emb;            // [R, N, 32]
+  const void* xs;              // [R, N] uint8 or int64
+  const void* ys;
+  const long long* entity_num; // [R] or nullptr
+  int idx_bytes, N;
+};
+
 __global__ void __launch_bounds__(256)
-spatial_features_kernel(const SpatialPlanes sp, const float* __restrict__ scatter_map, __nv_bfloat16* __restrict__ out,
-                        int H, int W, int Cs) {
+spatial_features_kernel(const SpatialPlanes sp, const float* __restrict__ scatter_map, const ScatterSrc sc,
+                        __nv_bfloat16* __restrict__ out, int H, int W, int Cs) {
   __shared__ unsigned int effbits[kFeatBand * 256];      // one byte-sized bit set per pixel, W <= 1024/… (W*band <= 1024*… checked on host)
+  __shared__ __align__(16) uint4 stile[8][32 * 8];       // per-warp output staging (below); before that: unsorted keys
+  __shared__ uint32_t sorted[512];                       // fused scatter: (band-local cell << 9 | entity) of the band's entities
+  uint32_t* skeys = reinterpret_cast<uint32_t*>(&stile[0][0]);
+  __shared__ uint16_t cmap[kFeatBand * 256];             // band-local cell -> 1 + index of its first sorted key
+  __shared__ int s_count;
   const int r = blockIdx.x;
   const int band = blockIdx.y;                            // padded row band: rows [band*kFeatBand, +kFeatBand) of H+2
   const int HW = H * W;
@@ -926,10 +942,46 @@ spatial_features_kernel(const SpatialPlanes sp, const float* __restrict__ scatte
     }
   }
   __syncthreads();
+  int n_b = 0;
+  long long en_r = 0;
+  if (!scatter_map) {
+    en_r = sc.entity_num ? sc.entity_num[r] : (long long)sc.N;
+    if (threadIdx.x == 0) s_count = 0;
+    for (int i = threadIdx.x; i < n_pix; i += blockDim.x) cmap[i] = 0;
+    __syncthreads();
+    for (int e = threadIdx.x; e < sc.N; e += blockDim.x) {
+      if ((long long)e >= en_r) continue;                                   // encoder.py:38 mask: contributes 0
+      long long x, y;
+      if (sc.idx_bytes == 1) {
+        x = reinterpret_cast<const uint8_t*>(sc.xs)[(long long)r * sc.N + e];
+        y = reinterpret_cast<const uint8_t*>(sc.ys)[(long long)r * sc.N + e];
+      } else {
+        x = reinterpret_cast<const long long*>(sc.xs)[(long long)r * sc.N + e];
+        y = reinterpret_cast<const long long*>(sc.ys)[(long long)r * sc.N + e];
+      }
+      x = x < 0 ? 0 : (x > W - 1 ? W - 1 : x);                              // module_utils.py:18-19
+      y = y < 0 ? 0 : (y > H - 1 ? H - 1 : y);
+      const int yl = (int)y - y_lo;
+      if (yl >= 0 && yl < kFeatBand) skeys[atomicAdd(&s_count, 1)] = ((uint32_t)(yl * W + (int)x) << 9) | (uint32_t)e;
+    }
+    __syncthreads();
+    n_b = s_count;
+    for (int i = threadIdx.x; i < n_b; i += blockDim.x) {                    // rank sort (keys are unique)
+      const uint32_t k = skeys[i];
+      int rank = 0;
+      for (int j = 0; j < n_b; ++j) rank += skeys[j] < k ? 1 : 0;
+      sorted[rank] = k;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < n_b; i += blockDim.x) {
+      const uint32_t cell = sorted[i] >> 9;
+      if (i == 0 || (sorted[i - 1] >> 9) != cell) cmap[cell] = (uint16_t)(i + 1);
+    }
+    __syncthreads();
+  }
   const int Cp = 64;
   // every lane builds the 128 bytes of its pixel (zeros for the border ring and for lanes past the band); the warp's 32
   // pixels are contiguous in the output, so they are staged in a swizzled 4 KB tile and written as 512-byte rows
-  __shared__ __align__(16) uint4 stile[8][32 * 8];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int n_band = kFeatBand * (W + 2);
   for (int i0 = 0; i0 < n_band; i0 += blockDim.x) {
@@ -970,9 +1022,24 @@ spatial_features_kernel(const SpatialPlanes sp, const float* __restrict__ scatte
 #pragma unroll
         for (int e = 0; e < 6; ++e) f[18 + e] = ((bits >> e) & 1u) ? 1.f : 0.f;
       }
-      const float* sm = scatter_map + (long long)r * Cs * HW + (long long)y * W + x;
+      if (scatter_map) {
+        const float* sm = scatter_map + (long long)r * Cs * HW + (long long)y * W + x;
 #pragma unroll
-      for (int k = 0; k < 32; ++k) f[24 + k] = (k < Cs) ? __ldg(sm + (long long)k * HW) : 0.f;
+        for (int k = 0; k < 32; ++k) f[24 + k] = (k < Cs) ? __ldg(sm + (long long)k * HW) : 0.f;
+      } else {
+        const uint32_t cell = (uint32_t)((y - y_lo) * W + x);
+        const int m = cmap[cell];
+        if (m) {
+          for (int j = m - 1; j < n_b && (sorted[j] >> 9) == cell; ++j) {
+            const float4* src = reinterpret_cast<const float4*>(sc.emb + ((long long)r * sc.N + (sorted[j] & 511u)) * 32);
+#pragma unroll
+            for (int k4 = 0; k4 < 8; ++k4) {
+              const float4 v = __ldg(src + k4);
+              f[24 + 4 * k4] += v.x; f[24 + 4 * k4 + 1] += v.y; f[24 + 4 * k4 + 2] += v.z; f[24 + 4 * k4 + 3] += v.w;
+            }
+          }
+        }
+      }
 #pragma unroll
       for (int q = 0; q < 8; ++q) {
         __nv_bfloat162 h0 = __floats2bfloat162_rn(f[8 * q], f[8 * q + 1]), h1 = __floats2bfloat162_rn(f[8 * q + 2], f[8 * q + 3]);
@@ -1005,16 +1072,24 @@ spatial_features_kernel(const SpatialPlanes sp, const float* __restrict__ scatte
 
 
 int spatial_features(const void* const* planes, const void* const* effects, int n_eff, const float* scatter_map,
+                     const float* emb, const void* xs, const void* ys, int idx_bytes, const long long* entity_num, int N,
                      void* out, long long R, int H, int W, int Cs, cudaStream_t st) {
   if (R <= 0) return AS_OK;
   if (H <= 0 || W <= 0 || W > 256 || Cs != 32 || n_eff <= 0) return AS_ESIZE;
-  if (!planes || !effects || !scatter_map || !out) return AS_EINVAL;
+  if (!planes || !effects || !out) return AS_EINVAL;
+  ScatterSrc sc = {emb, xs, ys, entity_num, idx_bytes, N};
+  if (!scatter_map) {
+    if (!emb || !xs || !ys) return AS_EINVAL;
+    if (N <= 0 || N > 512) return AS_ESIZE;
+    if (idx_bytes != 1 && idx_bytes != 8) return AS_EUNSUPPORTED;
+    if (reinterpret_cast<uintptr_t>(emb) & 15) return AS_EALIGN;
+  }
   SpatialPlanes sp;
   for (int i = 0; i < 7; ++i) { sp.plane[i] = reinterpret_cast<const uint8_t*>(planes[i]); if (!planes[i]) return AS_EINVAL; }
   for (int i = 0; i < 6; ++i) { sp.effect[i] = reinterpret_cast<const int16_t*>(effects[i]); if (!effects[i]) return AS_EINVAL; }
   sp.n_eff = n_eff;
   dim3 grid((unsigned)R, (unsigned)((H + 2 + kFeatBand - 1) / kFeatBand));
-  spatial_features_kernel<<<grid, 256, 0, st>>>(sp, scatter_map, reinterpret_cast<__nv_bfloat16*>(out), H, W, Cs);
+  spatial_features_kernel<<<grid, 256, 0, st>>>(sp, scatter_map, sc, reinterpret_cast<__nv_bfloat16*>(out), H, W, Cs);
   AS_LAUNCH_CHECK();
   return AS_OK;
 }

@@ -6,6 +6,8 @@ kernel (forward, data-gradient and weight-gradient); the tails (residual ReLU, g
 Reference modules: ResBlock (ctools/torch_utils/network/res_block.py:13-65), GatedResBlock
 (model/module_utils.py:204-231), LocationHead (model/head/action_arg_head.py:366-450).
 """
+import os
+
 import torch
 import torch.nn.functional as F
 
@@ -317,7 +319,9 @@ def _build_features(proj, x, y, entity_num, spatial_info):
     R, N, D = proj.shape
     hm = spatial_info['height_map']
     H, W = hm.shape[1], hm.shape[2]
-    smap = K.ScatterConnection.apply(proj.detach(), x, y, entity_num, H, W, 'add')     # dense map: temporary
+    fused = os.environ.get('APPLESTAR_SCATTER_FUSED', '1') != '0' and D == 32 and N <= 512
+    if not fused:
+        smap = K.ScatterConnection.apply(proj.detach(), x, y, entity_num, H, W, 'add')     # dense map: temporary
     planes = (ctypes.c_void_p * 7)()
     effects = (ctypes.c_void_p * 6)()
     keep = []
@@ -335,8 +339,17 @@ def _build_features(proj, x, y, entity_num, spatial_info):
         keep.append(t)
         effects[i] = t.data_ptr()
     out = torch.empty((R, H + 2, W + 2, 64), dtype=torch.bfloat16, device=proj.device)
-    _lib.call('as_spatial_features', planes, effects, n_eff, smap.data_ptr(), out.data_ptr(), R, H, W, D,
-              _lib.stream_ptr())
+    if fused:      # scatter channels summed inside the feature kernel: the dense fp32 map is never written
+        xs, ys = x.contiguous(), y.contiguous()
+        if xs.dtype not in (torch.uint8, torch.int64):
+            xs, ys = xs.long(), ys.long()
+        en = None if entity_num is None else entity_num.contiguous().long()
+        emb = proj.detach().float().contiguous()
+        _lib.call('as_spatial_features_scatter', planes, effects, n_eff, emb.data_ptr(), xs.data_ptr(), ys.data_ptr(),
+                  xs.element_size(), 0 if en is None else en.data_ptr(), N, out.data_ptr(), R, H, W, _lib.stream_ptr())
+    else:
+        _lib.call('as_spatial_features', planes, effects, n_eff, smap.data_ptr(), out.data_ptr(), R, H, W, D,
+                  _lib.stream_ptr())
     return out, H, W
 
 

@@ -143,6 +143,13 @@ int as_colsum_bf16_static(const void* x, float* out, int64_t rows, int C, void* 
  * [R,H+2,W+2,64] (56 real channels in the reference order, 8 zero), the A operand of the 1x1 project GEMM. */
 int as_spatial_features(const void* const* planes, const void* const* effects, int n_eff, const float* scatter_map,
                         void* out, int64_t R, int H, int W, int Cs, void* stream);
+/* The same with ScatterConnection ('add', module_utils.py:11-34 via encoder.py:37-42) fused in: the 32 scatter
+ * channels of a pixel are summed straight from emb [R,N,32] fp32 at the clamped (xs, ys) of the entities below
+ * entity_num, in ascending entity order (bit-identical to as_scatter_connection_fwd), so the dense fp32 map is never
+ * written.  idx_bytes 1 (uint8) or 8 (int64); N <= 512. */
+int as_spatial_features_scatter(const void* const* planes, const void* const* effects, int n_eff, const float* emb, const void* xs,
+                                const void* ys, int idx_bytes, const int64_t* entity_num, int N, void* out, int64_t R, int H,
+                                int W, void* stream);
 /* ScatterConnection backward reading the gradient of that feature map directly (channels ch0 .. ch0+D-1). */
 int as_scatter_connection_bwd_pnhwc(const void* d_feat, const void* xs, const void* ys, int idx_bytes,
                                     const int64_t* entity_num, float* d_emb, int64_t R, int N, int D, int H, int W,

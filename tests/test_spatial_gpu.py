@@ -166,6 +166,33 @@ def test_maxpool_fwd_bwd():
     assert torch.equal(x.grad, xr.grad)                                   # first-max routing == torch
 
 
+def test_fused_scatter_features_bit_exact(monkeypatch):
+    """as_spatial_features_scatter (scatter sums inside the feature kernel) == as_scatter_connection_fwd +
+    as_spatial_features, bit for bit: heavy collisions (512 entities on one cell), entity_num = 1, uint8 and int64
+    coordinates, and the oracle's scatter channels."""
+    from applestar_b200 import spatial, synth
+    from oracle import restate as R
+    obs = synth.gen_observations(5, 512, 77, special=True)
+    g = torch.Generator().manual_seed(5)
+    proj = torch.relu(torch.randn(5, 512, 32, generator=g)).cuda()
+    sp = {k: v.cuda() for k, v in obs['spatial_info'].items()}
+    en = obs['entity_num'].cuda()
+    outs = {}
+    for idx_dtype in (torch.uint8, torch.int64):
+        x = obs['entity_info']['x'].to(idx_dtype).cuda()
+        y = obs['entity_info']['y'].to(idx_dtype).cuda()
+        for mode in ('1', '0'):
+            monkeypatch.setenv('APPLESTAR_SCATTER_FUSED', mode)
+            feats, H, W = spatial._build_features(proj, x, y, en, sp)
+            outs[(idx_dtype, mode)] = feats
+        assert torch.equal(outs[(idx_dtype, '1')], outs[(idx_dtype, '0')])
+    assert torch.equal(outs[(torch.uint8, '1')], outs[(torch.int64, '1')])
+    mask = (torch.arange(512).unsqueeze(0) < obs['entity_num'].unsqueeze(1)).unsqueeze(2)
+    smap = R.scatter_connection(proj.cpu() * mask, obs['entity_info']['x'], obs['entity_info']['y'], 'add')
+    got = outs[(torch.uint8, '1')][:, 1:-1, 1:-1, 24:56].permute(0, 3, 1, 2).float().cpu()
+    assert torch.equal(got, smap.to(torch.bfloat16).float())
+
+
 def test_spatial_project_matches_reference_front():
     """scatter + 56-channel input + 1x1 project conv + ReLU (+ its backward) vs the oracle's fp32 front end."""
     from applestar_b200 import spatial, synth
