@@ -51,7 +51,7 @@ static long long* g_attn_prof = nullptr;
 int attn_set_profile(long long* buf) { g_attn_prof = buf; return AS_OK; }
 
 // barrier indices
-enum { kBarK = 0, kBarS = 4, kBarP = 8, kBarV = 12, kBarPv = 16, kBarO = 20, kBarDone = 21, kBarCount = 22 };
+enum { kBarK = 0, kBarS = 4, kBarP = 8, kBarV = 12, kBarPv = 16, kBarO = 20, kBarDone = 21, kBarPf = 22, kBarCount = 26 };
 
 // second-operand block at position o of the item's block order -> buffer: 0 and 3 share stage 0, 1 -> stage 1,
 // 2 -> the dead Q tile
@@ -73,7 +73,7 @@ __device__ __forceinline__ float fast_exp2(float x) {
 template <bool BWD>
 __global__ void __launch_bounds__(kAtThreads, 1)
 attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmQKV,
-            const __grid_constant__ CUtensorMap tmP, const AttnDev p) {
+            const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmPin, const AttnDev p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t pad = (1024u - (raw & 1023u)) & 1023u;
@@ -92,6 +92,7 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     tma_prefetch_desc(&tmQKV);
     tma_prefetch_desc(&tmA);
     if (p.store_p) tma_prefetch_desc(&tmP);
+    if (BWD) tma_prefetch_desc(&tmPin);
   }
   if (warp == 1) tmem_alloc(tmem_slot, 512);
   tc_fence_before();
@@ -136,6 +137,17 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         };
         load_v(0);
         if (NB > 1) load_v(1);
+        if constexpr (BWD) {
+          // stored probabilities: block kb lands in the tile that held the first-product operand of block kb as soon as
+          // that product has retired; the softmax warps turn it into dS in place
+          for (int o = 0; o < NB; ++o) {
+            const int kb = rot + o < NB ? rot + o : rot + o - NB;
+            mbar_wait(&bars[kBarS + kb], ph);
+            mbar_expect_tx(&bars[kBarPf + kb], 2u * kAtSub);
+            tma_load_4d(smem + kAtKP + (2 * kb) * kAtSub, &tmPin, &bars[kBarPf + kb], kb * 128, qt * 128, bh, 0);
+            tma_load_4d(smem + kAtKP + (2 * kb + 1) * kAtSub, &tmPin, &bars[kBarPf + kb], kb * 128 + 64, qt * 128, bh, 0);
+          }
+        }
         if (NB > 2) {
           const int last = rot + NB - 1 < NB ? rot + NB - 1 : rot - 1;
           mbar_wait(&bars[kBarS + last], ph);
@@ -310,21 +322,19 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         asm volatile("bar.sync 1, 256;" ::: "memory");
         const float delta = d + red[(half ^ 1) * 128 + row].x;
         out_scale = p.out_scale;
-        const __nv_bfloat16* prow = p.P + ((long long)bh * p.N + qt * 128 + row) * p.N + half * 64;
         for (int o = 0; o < NB; ++o) {
           const int kb = rot + o < NB ? rot + o : rot + o - NB;
-          uint4 pv[8];
-#pragma unroll
-          for (int c = 0; c < 8; ++c) pv[c] = __ldg(reinterpret_cast<const uint4*>(prow + kb * 128) + c);
           mbar_wait(&bars[kBarS + kb], ph);
           tc_fence_after();
           tmem_ld32(t_row + kb * 128, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
           tmem_ld32(t_row + kb * 128 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
           tmem_ld_wait();
           uint8_t* dst = smem + kAtKP + (2 * kb + half) * kAtSub + row * 128;
+          mbar_wait(&bars[kBarPf + kb], ph);                       // P block in place (TMA, same swizzle as the dS tile)
 #pragma unroll
           for (int c = 0; c < 8; ++c) {
-            const uint32_t pw[4] = {pv[c].x, pv[c].y, pv[c].z, pv[c].w};
+            const uint4 pvc = *reinterpret_cast<const uint4*>(dst + ((c ^ (row & 7)) << 4));
+            const uint32_t pw[4] = {pvc.x, pvc.y, pvc.z, pvc.w};
             uint32_t w[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
@@ -381,7 +391,8 @@ int gemm_num_sms();
 int attn_fwd_ok(int N, int D) { return D == 128 && N >= 128 && N <= 512 && N % 128 == 0; }
 
 template <bool BWD>
-static int attn_launch(const CUtensorMap& ta, const CUtensorMap& tq, const CUtensorMap& tp, const AttnDev& p, cudaStream_t st) {
+static int attn_launch(const CUtensorMap& ta, const CUtensorMap& tq, const CUtensorMap& tp, const CUtensorMap& tpin,
+                       const AttnDev& p, cudaStream_t st) {
   static bool attr_done = false;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(attn_kernel<BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAtSmemMax);
@@ -390,7 +401,7 @@ static int attn_launch(const CUtensorMap& ta, const CUtensorMap& tq, const CUten
   }
   const int sms = gemm_num_sms();
   const int grid = (int)(p.tiles < sms ? p.tiles : sms);
-  attn_kernel<BWD><<<grid, kAtThreads, kAtSmemMax, st>>>(ta, tq, tp, p);
+  attn_kernel<BWD><<<grid, kAtThreads, kAtSmemMax, st>>>(ta, tq, tp, tpin, p);
   AS_LAUNCH_CHECK();
   return AS_OK;
 }
@@ -417,7 +428,7 @@ int attn_fwd(const void* qkv, const long long* key_len, void* O, void* P, long l
   p.scale_log2 = scale * kLog2e; p.out_scale = 1.f;
   p.tiles = R * H * p.NQ;
   p.prof = g_attn_prof;
-  return attn_launch<false>(tq, tq, tp, p, st);
+  return attn_launch<false>(tq, tq, tp, tp, p, st);
 }
 
 // dS [R,H,N,N] and dq (column block 0 of dqkv [R,N,3*H*D]) from P, O, dO, qkv; dK and dV remain GEMMs over dS / P.
@@ -427,8 +438,10 @@ int attn_bwd_dq(const void* qkv, const void* O, const void* dO, const void* P, v
   if (!attn_fwd_ok(N, D) || H <= 0) return AS_EUNSUPPORTED;
   if (!qkv || !O || !dO || !P || !dS || !dqkv) return AS_EINVAL;
   if ((reinterpret_cast<uintptr_t>(O) | reinterpret_cast<uintptr_t>(P)) & 15) return AS_EALIGN;
-  CUtensorMap tq, ta, tp;
-  int rc = make_map_bf16(&tq, qkv, 3LL * H * D, N, 3LL * H * D, (int)R, (long long)N * 3 * H * D, 1, 0, 64, 128);
+  CUtensorMap tq, ta, tp, tpin;
+  int rc = make_map_bf16(&tpin, P, N, N, N, (int)(R * H), (long long)N * N, 1, 0, 64, 128);
+  if (rc != AS_OK) return rc;
+  rc = make_map_bf16(&tq, qkv, 3LL * H * D, N, 3LL * H * D, (int)R, (long long)N * 3 * H * D, 1, 0, 64, 128);
   if (rc != AS_OK) return rc;
   rc = make_map_bf16(&ta, dO, (long long)H * D, N, (long long)H * D, (int)R, (long long)N * H * D, 1, 0, 64, 128);
   if (rc != AS_OK) return rc;
@@ -444,7 +457,7 @@ int attn_bwd_dq(const void* qkv, const void* O, const void* dO, const void* P, v
   p.scale_log2 = 0.f; p.out_scale = scale;
   p.tiles = R * H * p.NQ;
   p.prof = g_attn_prof;
-  return attn_launch<true>(ta, tq, tp, p, st);
+  return attn_launch<true>(ta, tq, tp, tpin, p, st);
 }
 
 }  // namespace as

@@ -100,6 +100,7 @@ class LinearFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, weight, bias, relu, want32, want16):
+        ctx.set_materialize_grads(False)        # an unused output copy must not cost a zero fill + an add in backward
         K = x.shape[-1]
         N = weight.shape[0]
         x2 = x.reshape(-1, K)
@@ -127,6 +128,8 @@ class LinearFn(torch.autograd.Function):
         x16, w16, y = ctx.saved_tensors
         N = w16.shape[0]
         K8 = w16.shape[1]
+        if dy32 is None and dy16 is None:
+            return None, None, None, None, None, None
         if dy32 is not None and dy16 is not None:
             dy = dy32 + dy16
         else:
@@ -268,6 +271,7 @@ class LayerNormFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, residual, weight, bias, relu, want32, want16):
+        ctx.set_materialize_grads(False)
         C = x.shape[-1]
         x = x.contiguous().float()
         res = None if residual is None else residual.contiguous().float()
@@ -286,6 +290,8 @@ class LayerNormFn(torch.autograd.Function):
     def backward(ctx, dy32, dy16):
         x, res, weight, bias, stats = ctx.saved_tensors
         C, rows = ctx.C, ctx.rows
+        if dy32 is None and dy16 is None:
+            return None, None, None, None, None, None, None
         dy32 = None if dy32 is None else dy32.contiguous()
         dy16 = None if dy16 is None else dy16.contiguous()
         dx = torch.empty_like(x) if (ctx.needs_input_grad[0] or ctx.needs_input_grad[1]) else None
@@ -481,6 +487,7 @@ class LNLSTMLayerFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, gi, h0, c0, whh, gh_w, gh_b, gc_w, gc_b):
+        ctx.set_materialize_grads(False)
         T, B, G = gi.shape
         H = G // 4
         gi, h0, c0 = gi.contiguous(), h0.contiguous().float(), c0.contiguous().float()

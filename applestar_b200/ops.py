@@ -234,10 +234,35 @@ def fresh_gumbel(rows, n_entity, device):
             'target_unit': gum(rows, n_entity), 'target_location': gum(rows, C.SPATIAL_Y * C.SPATIAL_X)}
 
 
+class _OneHotLinear(torch.autograd.Function):
+    """fc over a one-hot input == gather of one weight column (+bias, ReLU).  Backward: dW = dy^T one_hot as one small
+    dense product (deterministic; the index_put backward of `weight.t()[idx]` sorts and serialises, ~130 us per call)."""
+
+    @staticmethod
+    def forward(ctx, idx, weight, bias, relu):
+        idx = idx.long()
+        y = weight.t()[idx] + bias
+        if relu:
+            y = F.relu(y)
+        ctx.relu, ctx.k = relu, weight.shape[1]
+        ctx.save_for_backward(idx, y if relu else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        idx, y = ctx.saved_tensors
+        if ctx.relu:
+            dy = dy * (y > 0)
+        dy = dy.reshape(-1, dy.shape[-1]).float()
+        one_hot = F.one_hot(idx.reshape(-1), ctx.k).to(dy.dtype)
+        dw = dy.t() @ one_hot if ctx.needs_input_grad[1] else None
+        db = dy.sum(dim=0) if ctx.needs_input_grad[2] else None
+        return None, dw, db, None
+
+
 def one_hot_linear(idx, weight, bias, relu=False):
     """fc over a one-hot input == gather of one weight column (+bias)."""
-    y = weight.t()[idx.long()] + bias
-    return F.relu(y) if relu else y
+    return _OneHotLinear.apply(idx, weight, bias, relu)
 
 
 def categorical_log_prob(logits, action):

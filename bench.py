@@ -297,6 +297,14 @@ def run_ours(args):
             print('GEMM %-22s args=%s n=%d ms=%.3f TF/s=%.0f' % (k[0], k[1:], t[0], t[1], t[2] / t[1] / 1e9), file=sys.stderr)
     hbm, tf_burst, tf_sus, which = peaks()
     achieved = g_fl / (g_ms * 1e-3) / 1e12 if g_ms > 0 else 0.0
+    traffic = traffic_note = None             # DRAM bytes of the same kernel family from the committed ncu capture
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'profiles', 'r01_tensor_family_traffic.json')) as f:
+            tj = json.load(f)
+        traffic, traffic_note = tj['dram_bytes_per_launch_mean'], '%s: %.1f GB per step over %d launches' % (
+            tj['source'], tj['dram_bytes_per_step'] / 1e9, tj['launches'])
+    except (OSError, KeyError, ValueError):
+        pass
 
     if rank == 0:
         total_steps = T * B * world
@@ -318,7 +326,7 @@ def run_ours(args):
             'roofline': {'bound': 'tensor', 'kernel': 'tcgen05 kernels as::gemm_kernel + as::attn_kernel (all %d launches of one step)' % len(records),
                          'achieved': achieved, 'peak': tf_sus, 'unit': 'TFLOP/s', 'frac': achieved / tf_sus,
                          'peak_source': which + ' bf16_tflops_sustained', 'gemm_ms_per_step': g_ms,
-                         'gemm_share_of_step': g_ms / (ms / args.steps), 'traffic': None},
+                         'gemm_share_of_step': g_ms / (ms / args.steps), 'traffic': traffic, 'traffic_source': traffic_note},
         }
         if not args.no_cpu_baseline and world == 1:      # the CPU baseline is an N = 1 figure
             Tc, Bc = (int(x) for x in args.cpu_sample.split('x'))
