@@ -166,6 +166,19 @@ int as_conv_nhwc_bf16(const void* x, const void* w, void* y, const float* bias, 
   return as::gemm_run(g, ST(stream));
 }
 
+// 0: one tap per tile; 1 / 2: tap pairs on a 64-channel M side (dy / swapped x), needs split-K partials
+int as_conv_wgrad_pair_mode(int Cin, int Cout, int taps, int splits) {
+  if (taps != 9 || splits <= 1 || getenv("AS_WGRAD_NO_PAIR")) return 0;
+  if (Cout == 64) return 1;
+  if (Cin == 64 && Cout < 64) return 2;
+  return 0;
+}
+int64_t as_conv_wgrad_ws_floats(int Cin, int Cout, int taps, int splits) {
+  if (splits <= 1) return 0;
+  const int pair = as_conv_wgrad_pair_mode(Cin, Cout, taps, splits);
+  if (pair) return (int64_t)splits * 5 * 128 * (pair == 1 ? Cin : Cout);
+  return (int64_t)splits * taps * Cout * Cin;
+}
 int as_conv_wgrad_nhwc_bf16(const void* dy, const void* x, float* dw, float* ws, int64_t R, int H, int W, int Cin,
                             int Cout, int taps, int splits, void* stream) {
   if (taps != 1 && taps != 9) return AS_EUNSUPPORTED;
@@ -174,6 +187,30 @@ int as_conv_wgrad_nhwc_bf16(const void* dy, const void* x, float* dw, float* ws,
   const int pw = W + 2, ph = H + 2;
   const int64_t P = R * (int64_t)ph * pw;
   if (P > 2147483647LL) return AS_ESIZE;
+  const int pair = as_conv_wgrad_pair_mode(Cin, Cout, taps, splits);
+  if (pair) {
+    // two taps per 128-row MMA (gemm_tcgen05.cu, wg_pair).  mode 1: M = Cout = 64, the second tap's dy rows are read
+    // shift[b] - shift[a] earlier; mode 2 (Cout < 64 = Cin): operands swapped, M = Cin = 64, both x chunks shifted
+    int shift[10];
+    for (int ky = 0; ky < 3; ++ky)
+      for (int kx = 0; kx < 3; ++kx) shift[ky * 3 + kx] = (ky - 1) * pw + (kx - 1);
+    shift[9] = shift[8];
+    as::GemmCall g;
+    g.K = (int)P; g.a_mn = true; g.b_mn = true; g.nb0 = 5; g.nb1 = 1; g.wgrad_taps = 5; g.wg_pair = 1;
+    g.M = 64;
+    if (pair == 1) {
+      g.A = dy; g.B = x; g.N = Cin; g.lda = Cout; g.ldb = Cin;
+      for (int b = 0; b < 5; ++b) { g.pair_a[b][0] = 0; g.pair_a[b][1] = -(shift[2 * b + 1] - shift[2 * b]); g.pair_b[b] = shift[2 * b]; }
+    } else {
+      g.A = x; g.B = dy; g.N = Cout; g.lda = Cin; g.ldb = Cout;
+      for (int b = 0; b < 5; ++b) { g.pair_a[b][0] = shift[2 * b]; g.pair_a[b][1] = shift[2 * b + 1]; g.pair_b[b] = 0; }
+    }
+    g.C = dw; g.ldc = g.N; g.c_sb0 = 128LL * g.N; g.c_bf16 = 0;
+    g.splits = splits; g.ws = ws;
+    int rc = as::gemm_run(g, ST(stream));
+    if (rc) return rc;
+    return as::wgrad_pair_reduce(ws, dw, splits, 5LL * 128 * g.N, taps, Cout, Cin, pair == 2, ST(stream));
+  }
   as::GemmCall g;
   g.A = dy; g.B = x;
   g.M = Cout; g.N = Cin; g.K = (int)P;

@@ -30,9 +30,15 @@ struct GemmCall {
   int b_k_shift = 0;         // MN-major B: offset (rows) added to the contraction coordinate
   int wgrad_taps = 0;        // >0: conv weight-gradient mode, batch dim 0 = tap (see gemm_tcgen05.cu)
   int bn_override = 0;
+  // conv weight gradients with a 64-channel M side: two taps share one 128-row MMA (see gemm_tcgen05.cu, wg_pair)
+  int wg_pair = 0;
+  int pair_a[5][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}};   // contraction-row offset of A's two 64-column chunks
+  int pair_b[5] = {0, 0, 0, 0, 0};                                 // contraction-row offset of B
 };
 
 int gemm_run(const GemmCall& g, cudaStream_t st);
 int splitk_reduce(const float* ws, float* out, long long n, int splits, int accumulate, cudaStream_t st);
+int wgrad_pair_reduce(const float* ws, float* out, int splits, long long stride, int taps, int cout, int cin, int transposed,
+                      cudaStream_t st);
 
 }  // namespace as

@@ -39,6 +39,10 @@ struct GemmDev {
   int img_w, img_h;  // padded image dims for border masking (0 = off)
   int b_k_shift;     // MN-major B only: row offset added to the contraction coordinate
   int wgrad_taps;    // >0: batch index b0 = conv tap; A and B are shared by all taps, B rows shifted by shift[b0]
+  // wg_pair: batch index b0 = PAIR of taps.  The M side has only 64 channels, so the two 64-column chunks of the A tile
+  // are loaded at different contraction rows (pair_a[b0][j]) and one 128-row MMA produces both taps: accumulator rows
+  // 0-63 = first tap, 64-127 = second tap.  B rows are shifted by pair_b[b0].
+  int wg_pair, pair_a[5][2], pair_b[5];
   // slab mode (multi-tap conv): 256-row steps, A slab = 2 TMA boxes of slab_box rows starting at row m0 - halo
   int slab, halo, slab_box, slab_bytes, slab_slots, b_slots, tpb, b_resident;
   int mc;            // slab ring mode on CTA pairs: each CTA loads half of every weight tile and multicasts it to both
@@ -296,11 +300,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             ka = kbcol = kb * BK;
           }
           const int ob0 = p.wgrad_taps > 0 ? 0 : b0;                       // operands shared by all taps
-          const int kshift = p.wgrad_taps > 0 ? p.shift[b0] : p.b_k_shift;
+          const int kshift = p.wg_pair ? p.pair_b[b0] : (p.wgrad_taps > 0 ? p.shift[b0] : p.b_k_shift);
           if (A_MN) {
 #pragma unroll
             for (int j = 0; j < BM / 64; ++j)
-              tma_load_4d(sa + j * (BK * 128), &tmA, &full_bar[stage], m0 + j * 64, ka, ob0, b1);
+              tma_load_4d(sa + j * (BK * 128), &tmA, &full_bar[stage], p.wg_pair ? 0 : m0 + j * 64,
+                          p.wg_pair ? ka + p.pair_a[b0][j] : ka, ob0, b1);
           } else {
             tma_load_4d(sa, &tmA, &full_bar[stage], ka, m0 + mshift, ob0, b1);
           }
@@ -791,7 +796,12 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
   int BN = g.bn_override ? g.bn_override : pick_bn(g.N, g.b_mn);
   if (g.b_mn && BN < 64) return AS_EUNSUPPORTED;
   GemmDev p{};
-  p.M = g.M; p.N = g.N; p.K = g.K; p.nb0 = g.nb0; p.nb1 = g.nb1;
+  p.M = g.wg_pair ? 128 : g.M; p.N = g.N; p.K = g.K; p.nb0 = g.nb0; p.nb1 = g.nb1;
+  p.wg_pair = g.wg_pair;
+  if (g.wg_pair) {
+    if (g.M != 64 || !g.a_mn || !g.b_mn || g.wgrad_taps != 5 || g.nb0 != 5 || g.splits <= 1) return AS_EUNSUPPORTED;
+    for (int i = 0; i < 5; ++i) { p.pair_a[i][0] = g.pair_a[i][0]; p.pair_a[i][1] = g.pair_a[i][1]; p.pair_b[i] = g.pair_b[i]; }
+  }
   p.m_blocks = (g.M + BM - 1) / BM;
   p.n_blocks = (g.N + BN - 1) / BN;
   p.taps = g.taps; p.cin = g.K;
@@ -930,6 +940,30 @@ __global__ void splitk_reduce_scalar_kernel(const float* __restrict__ ws, float*
     for (int k = 0; k < splits; ++k) s += ws[(long long)k * n + i];
     out[i] = s;
   }
+}
+
+// out[t][co][ci] (t < taps) from the tap-pair partials ws[split][5][128][N]: row t * 64 + m of a split's [640][N] matrix;
+// plain (m = co, N = cin) or transposed (m = ci, N = cout: the operands were swapped to get a 64-channel M side)
+__global__ void wgrad_pair_reduce_kernel(const float* __restrict__ ws, float* __restrict__ out, int splits, long long stride,
+                                         int total, int cout, int cin, int transposed) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  long long src = i;
+  if (transposed) {
+    const int ci = i % cin, co = (i / cin) % cout, t = i / (cin * cout);
+    src = ((long long)t * 64 + ci) * cout + co;
+  }
+  float a = 0.f;
+  for (int s = 0; s < splits; ++s) a += ws[(long long)s * stride + src];
+  out[i] = a;
+}
+
+int wgrad_pair_reduce(const float* ws, float* out, int splits, long long stride, int taps, int cout, int cin, int transposed,
+                      cudaStream_t st) {
+  const int total = taps * cout * cin;
+  wgrad_pair_reduce_kernel<<<(total + 127) / 128, 128, 0, st>>>(ws, out, splits, stride, total, cout, cin, transposed);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
 }
 
 int splitk_reduce(const float* ws, float* out, long long n, int splits, int accumulate, cudaStream_t st) {

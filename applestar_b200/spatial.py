@@ -84,10 +84,13 @@ class ConvNHWC(torch.autograd.Function):
         if ctx.needs_input_grad[1]:
             P = R * (H + 2) * (W + 2)
             tiles = taps * ((cout + 127) // 128) * max(1, (cin_p + 255) // 256)
+            if _lib.lib().as_conv_wgrad_pair_mode(cin_p, cout, taps, 2):
+                tiles = 5                       # two taps per 128-row tile (64-channel M side)
             want = max(1, min((P + 63) // 64, K.NUM_SMS // tiles))
             splits = _lib.lib().as_gemm_splits(P, want)
             dw9 = torch.empty((taps, cout, cin_p), dtype=torch.float32, device=x.device)
-            ws = torch.empty((splits, taps, cout, cin_p), dtype=torch.float32, device=x.device) if splits > 1 else None
+            ws_n = _lib.lib().as_conv_wgrad_ws_floats(cin_p, cout, taps, splits)
+            ws = torch.empty(ws_n, dtype=torch.float32, device=x.device) if splits > 1 else None
             _lib.call('as_conv_wgrad_nhwc_bf16', dy.data_ptr(), x.data_ptr(), dw9.data_ptr(), _ptr(ws), R, H, W, cin_p,
                       cout, taps, splits, st)
             dw = dw9[:, :, :cin].permute(1, 2, 0).reshape(cout, cin, kh, kh)

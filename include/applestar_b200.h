@@ -70,6 +70,12 @@ int as_conv_nhwc_bf16(const void* x, const void* w, void* y, const float* bias, 
  * (splits must equal as_gemm_splits(R*(H+2)*(W+2), want)).  Replaces autograd of nn.Conv2d (nn_module.py:166-168). */
 int as_conv_wgrad_nhwc_bf16(const void* dy, const void* x, float* dw, float* ws, int64_t R, int H, int W, int Cin,
                             int Cout, int taps, int splits, void* stream);
+/* Tap pairing of the 3x3 weight gradient: when the M side of dW = dy^T x has 64 channels (Cout == 64, or Cin == 64 with
+ * the operands swapped), two taps share one 128-row tcgen05.mma.  as_conv_wgrad_pair_mode tells which form
+ * as_conv_wgrad_nhwc_bf16 will use (0 none, 1 dy side, 2 swapped) and as_conv_wgrad_ws_floats the split-K workspace
+ * size it then needs. */
+int as_conv_wgrad_pair_mode(int Cin, int Cout, int taps, int splits);
+int64_t as_conv_wgrad_ws_floats(int Cin, int Cout, int taps, int splits);
 
 /* Layout conversion between the reference's NCHW fp32 maps and the padded NHWC bf16 maps the convolutions use:
  * dst [R,H+2,W+2,Cp] (border and channels >= C zero; relu != 0 applies ReLU on the way) / its inverse (interior,
