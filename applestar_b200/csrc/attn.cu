@@ -22,13 +22,16 @@
 
 namespace as {
 
-constexpr int kAtThreads = 384;            // warp 0: TMA, warp 1: MMA, warps 4-11: softmax / epilogue
+constexpr int kAtParts = 4;                // softmax threads per query row (each owns 128 / kAtParts columns of a block)
+constexpr int kAtCols = 128 / kAtParts;
+constexpr int kAtSoft = 128 * kAtParts;    // softmax / epilogue threads
+constexpr int kAtThreads = 128 + kAtSoft;  // warp 0: TMA, warp 1: MMA, warps 4..: softmax / epilogue
 constexpr int kAtSub = 128 * 64 * 2;       // one [128 rows][64 bf16] swizzled sub-tile: 16 KB
 constexpr int kAtKP = 0;                   // 4 key blocks x 2 sub-tiles (K by d-half, later P by key-half)
 constexpr int kAtQ = 8 * kAtSub;           // 2 sub-tiles (d halves); V block 2 lands here once Q is dead
 constexpr int kAtV = 10 * kAtSub;          // 2 stages x 2 sub-tiles (d chunks)
 constexpr int kAtBars = 14 * kAtSub;       // 229376
-constexpr int kAtRed = kAtBars + 256;      // float2 [2][128]
+constexpr int kAtRed = kAtBars + 256;      // exchange slots of the backward (float [kAtParts][128]); the forward uses a dead K tile
 constexpr int kAtTotal = kAtRed + 2 * 128 * 8;
 constexpr int kAtSmemMax = 232448;
 constexpr float kLog2e = 1.4426950408889634f;
@@ -87,7 +90,7 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const int NB = p.NB, HD = p.H * 128;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < kBarCount; ++i) mbar_init(&bars[i], (i >= kBarP && i < kBarP + 4) ? 256u : (i == kBarDone ? 256u : 1u));
+    for (int i = 0; i < kBarCount; ++i) mbar_init(&bars[i], (i >= kBarP && i < kBarP + 4) ? (uint32_t)kAtSoft : (i == kBarDone ? (uint32_t)kAtSoft : 1u));
     mbar_fence_init();
     tma_prefetch_desc(&tmQKV);
     tma_prefetch_desc(&tmA);
@@ -156,7 +159,7 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         for (int o = 0; o < NB; ++o) {
           const int kb = rot + o < NB ? rot + o : rot + o - NB;
           if (p.store_p) {
-            mbar_wait(&bars[kBarP + kb], ph);                      // tile kb written (and proxy-fenced) by all 256 threads
+            mbar_wait(&bars[kBarP + kb], ph);                      // tile kb written (and proxy-fenced) by all softmax threads
             tma_store_4d(&tmP, smem + kAtKP + (2 * kb) * kAtSub, kb * 128, qt * 128, bh, 0);
             tma_store_4d(&tmP, smem + kAtKP + (2 * kb + 1) * kAtSub, kb * 128 + 64, qt * 128, bh, 0);
             tma_store_commit();
@@ -221,12 +224,12 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       umma_commit_lead(0, &bars[kBarO]);
     }
   } else if (warp >= 4) {
-    // ------------------------------------------------------------------ softmax + output (8 warps, 256 threads)
+    // ------------------------------------------------------------------ softmax + output (4 * kAtParts warps)
     const int e = warp - 4;
     const int quarter = warp & 3;                                  // TMEM lane quarter this warp may read
-    const int half = e >> 2;                                       // which 64 of a block's 128 columns
+    const int half = e >> 2;                                       // which kAtCols of a block's 128 columns
     const int row = quarter * 32 + lane;
-    const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * 64);
+    const uint32_t t_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * kAtCols);
     uint32_t it = 0;
     for (long long tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
       const uint32_t ph = it & 1u;
@@ -235,7 +238,7 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const int h = bh % p.H, b = bh / p.H;
       long long kl = (!BWD && p.key_len) ? p.key_len[b] : (long long)p.N;
       if (kl > p.N) kl = p.N;
-      uint32_t v[64];
+      uint32_t v[kAtCols];
       float out_scale = 1.f;
       const int rot = (int)(it % (uint32_t)NB);                    // block order rot, rot+1, ..; accumulator in block rot
       const bool prof = p.prof && blockIdx.x == 0 && threadIdx.x == 128;
@@ -249,12 +252,12 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         mbar_wait(&bars[kBarS + kb], ph);
         tc_fence_after();
         tmem_ld32(t_row + kb * 128, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
-        tmem_ld32(t_row + kb * 128 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+        if constexpr (kAtCols > 32) tmem_ld32(t_row + kb * 128 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[kAtCols - 32]));
         tmem_ld_wait();
-        const int lim = (int)kl - (kb * 128 + half * 64);
+        const int lim = (int)kl - (kb * 128 + half * kAtCols);
         float cm = -INFINITY;
 #pragma unroll
-        for (int i = 0; i < 64; ++i) {
+        for (int i = 0; i < kAtCols; ++i) {
           const float t = i < lim ? __uint_as_float(v[i]) * p.scale_log2 : -1e9f * kLog2e;
           v[i] = __float_as_uint(t);
           cm = fmaxf(cm, t);
@@ -262,32 +265,40 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         if (cm > m) { l *= fast_exp2(m - cm); m = cm; }
         float s0 = 0.f, s1 = 0.f;
 #pragma unroll
-        for (int i = 0; i < 64; i += 2) {
+        for (int i = 0; i < kAtCols; i += 2) {
           s0 += fast_exp2(__uint_as_float(v[i]) - m);
           s1 += fast_exp2(__uint_as_float(v[i + 1]) - m);
         }
         l += s0 + s1;
       }
       if (prof) tp1 = clock64();
-      red[half * 128 + row] = make_float2(m, l);
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      // the row's kAtParts threads combine (max, sum) through the first K tile: every thread has waited for all first
+      // products, so K is dead; the second barrier keeps pass 2 from overwriting the slots while they are still read
       {
-        const float2 o = red[(half ^ 1) * 128 + row];
-        const float mm = fmaxf(m, o.x);
-        l = l * fast_exp2(m - mm) + o.y * fast_exp2(o.x - mm);
-        m = mm;
+        float2* xch = reinterpret_cast<float2*>(smem + kAtKP);
+        xch[half * 128 + row] = make_float2(m, l);
+        asm volatile("bar.sync 1, %0;" ::"n"(kAtSoft) : "memory");
+        float mm = m;
+#pragma unroll
+        for (int q = 0; q < kAtParts; ++q) mm = fmaxf(mm, xch[q * 128 + row].x);
+        float ll = 0.f;
+#pragma unroll
+        for (int q = 0; q < kAtParts; ++q) { const float2 o = xch[q * 128 + row]; ll += o.y * fast_exp2(o.x - mm); }
+        m = mm; l = ll;
+        asm volatile("bar.sync 1, %0;" ::"n"(kAtSoft) : "memory");
       }
       const float rinv = 1.f / l;
       // pass 2: normalised probabilities -> bf16 -> the A-operand tiles (128-byte swizzle: chunk c of row r at c ^ (r & 7))
       for (int o = 0; o < NB; ++o) {
         const int kb = rot + o < NB ? rot + o : rot + o - NB;
         tmem_ld32(t_row + kb * 128, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
-        tmem_ld32(t_row + kb * 128 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+        if constexpr (kAtCols > 32) tmem_ld32(t_row + kb * 128 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[kAtCols - 32]));
         tmem_ld_wait();
-        const int lim = (int)kl - (kb * 128 + half * 64);
-        uint8_t* dst = smem + kAtKP + (2 * kb + half) * kAtSub + row * 128;
+        const int lim = (int)kl - (kb * 128 + half * kAtCols);
+        uint8_t* dst = smem + kAtKP + (2 * kb + (half * kAtCols) / 64) * kAtSub + row * 128;
+        const int c0 = ((half * kAtCols) % 64) / 8;              // first 16-byte chunk of this thread in the 128-byte row
 #pragma unroll
-        for (int c = 0; c < 8; ++c) {
+        for (int c = 0; c < kAtCols / 8; ++c) {
           uint32_t w[4];
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
@@ -296,20 +307,20 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             const float t1 = i + 1 < lim ? __uint_as_float(v[i + 1]) * p.scale_log2 : -1e9f * kLog2e;
             w[j] = pack_bf16(fast_exp2(t0 - m) * rinv, fast_exp2(t1 - m) * rinv);
           }
-          *reinterpret_cast<uint4*>(dst + ((c ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+          *reinterpret_cast<uint4*>(dst + (((c0 + c) ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
         }
         tc_fence_before();
         fence_proxy_async_smem();
         mbar_arrive(&bars[kBarP + kb]);
       }
       } else {
-        // delta = rowsum(dO o O): each of the row's two threads sums its 64 columns
-        const long long orow = ((long long)b * p.N + qt * 128 + row) * HD + h * 128 + half * 64;
+        // delta = rowsum(dO o O): each of the row's kAtParts threads sums its kAtCols columns
+        const long long orow = ((long long)b * p.N + qt * 128 + row) * HD + h * 128 + half * kAtCols;
         const uint4* o4 = reinterpret_cast<const uint4*>(p.O + orow);
         const uint4* g4 = reinterpret_cast<const uint4*>(p.dO + orow);
         float d = 0.f;
 #pragma unroll
-        for (int c = 0; c < 8; ++c) {
+        for (int c = 0; c < kAtCols / 8; ++c) {
           const uint4 ov = __ldg(o4 + c), gv = __ldg(g4 + c);
           const uint32_t ow[4] = {ov.x, ov.y, ov.z, ov.w}, gw[4] = {gv.x, gv.y, gv.z, gv.w};
 #pragma unroll
@@ -318,22 +329,27 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             d = fmaf(__uint_as_float(ow[j] & 0xffff0000u), __uint_as_float(gw[j] & 0xffff0000u), d);
           }
         }
-        red[half * 128 + row] = make_float2(d, 0.f);
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        const float delta = d + red[(half ^ 1) * 128 + row].x;
+        float* xch = reinterpret_cast<float*>(red);                // [kAtParts][128] floats: 2 KB
+        if (it > 0) asm volatile("bar.sync 1, %0;" ::"n"(kAtSoft) : "memory");   // previous item's reads are done
+        xch[half * 128 + row] = d;
+        asm volatile("bar.sync 1, %0;" ::"n"(kAtSoft) : "memory");
+        float delta = 0.f;
+#pragma unroll
+        for (int q = 0; q < kAtParts; ++q) delta += xch[q * 128 + row];
         out_scale = p.out_scale;
         for (int o = 0; o < NB; ++o) {
           const int kb = rot + o < NB ? rot + o : rot + o - NB;
           mbar_wait(&bars[kBarS + kb], ph);
           tc_fence_after();
           tmem_ld32(t_row + kb * 128, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
-          tmem_ld32(t_row + kb * 128 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+          if constexpr (kAtCols > 32) tmem_ld32(t_row + kb * 128 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[kAtCols - 32]));
           tmem_ld_wait();
-          uint8_t* dst = smem + kAtKP + (2 * kb + half) * kAtSub + row * 128;
+          uint8_t* dst = smem + kAtKP + (2 * kb + (half * kAtCols) / 64) * kAtSub + row * 128;
+          const int c0 = ((half * kAtCols) % 64) / 8;               // first 16-byte chunk of this thread in the 128-byte row
           mbar_wait(&bars[kBarPf + kb], ph);                       // P block in place (TMA, same swizzle as the dS tile)
 #pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            const uint4 pvc = *reinterpret_cast<const uint4*>(dst + ((c ^ (row & 7)) << 4));
+          for (int c = 0; c < kAtCols / 8; ++c) {
+            const uint4 pvc = *reinterpret_cast<const uint4*>(dst + (((c0 + c) ^ (row & 7)) << 4));
             const uint32_t pw[4] = {pvc.x, pvc.y, pvc.z, pvc.w};
             uint32_t w[4];
 #pragma unroll
@@ -342,7 +358,7 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               const float p0 = __uint_as_float(pw[j] << 16), p1 = __uint_as_float(pw[j] & 0xffff0000u);
               w[j] = pack_bf16(p0 * (__uint_as_float(v[i]) - delta), p1 * (__uint_as_float(v[i + 1]) - delta));
             }
-            *reinterpret_cast<uint4*>(dst + ((c ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+            *reinterpret_cast<uint4*>(dst + (((c0 + c) ^ (row & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
           }
           tc_fence_before();
           fence_proxy_async_smem();
@@ -355,12 +371,12 @@ attn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       if (prof) tp3 = clock64();
       tc_fence_after();
       tmem_ld32(t_row + rot * 128, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
-      tmem_ld32(t_row + rot * 128 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+      if constexpr (kAtCols > 32) tmem_ld32(t_row + rot * 128 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[kAtCols - 32]));
       tmem_ld_wait();
       {
-        uint4* out = reinterpret_cast<uint4*>(p.out + ((long long)b * p.N + qt * 128 + row) * p.out_ld + h * 128 + half * 64);
+        uint4* out = reinterpret_cast<uint4*>(p.out + ((long long)b * p.N + qt * 128 + row) * p.out_ld + h * 128 + half * kAtCols);
 #pragma unroll
-        for (int c = 0; c < 8; ++c)
+        for (int c = 0; c < kAtCols / 8; ++c)
           out[c] = make_uint4(pack_bf16(__uint_as_float(v[8 * c]) * out_scale, __uint_as_float(v[8 * c + 1]) * out_scale),
                               pack_bf16(__uint_as_float(v[8 * c + 2]) * out_scale, __uint_as_float(v[8 * c + 3]) * out_scale),
                               pack_bf16(__uint_as_float(v[8 * c + 4]) * out_scale, __uint_as_float(v[8 * c + 5]) * out_scale),
