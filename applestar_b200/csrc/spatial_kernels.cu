@@ -555,29 +555,43 @@ conv_c32_1_fwd_kernel(const __nv_bfloat16* __restrict__ in, const float* __restr
     const int y0 = seg * kC32Seg, y1 = min(H, y0 + kC32Seg);
     const long long pitch = (long long)(W + 2) * 32;
     const __nv_bfloat16* p = in + ((r * (H + 2) + y0) * (long long)(W + 2) + x) * 32 + cg * 8;
-    uint4 r0[3], r1[3], r2[3];
+    // Every padded input row is loaded and unpacked ONCE and feeds the three output rows it belongs to (as tap row 0 of
+    // output j, 1 of j - 1, 2 of j - 2): the bf16 -> fp32 unpacking runs on the half-rate ALU pipe, which was the limit
+    // (73 % busy) when each row was unpacked again in each of the three iterations that used it.
+    const int nrow = y1 - y0 + 2;
+    uint4 rn[3];
 #pragma unroll
-    for (int kx = 0; kx < 3; ++kx) {
-      r0[kx] = __ldg(reinterpret_cast<const uint4*>(p + kx * 32));
-      r1[kx] = __ldg(reinterpret_cast<const uint4*>(p + pitch + kx * 32));
-    }
-    for (int y = y0; y < y1; ++y) {
-      const __nv_bfloat16* pr = p + (long long)(y - y0 + 2) * pitch;
+    for (int kx = 0; kx < 3; ++kx) rn[kx] = __ldg(reinterpret_cast<const uint4*>(p + kx * 32));
+    float o1 = 0.f, o2 = 0.f;                          // partial sums of output rows j - 1 and j - 2
+    for (int j = 0; j < nrow; ++j) {
+      uint4 rr[3];
 #pragma unroll
-      for (int kx = 0; kx < 3; ++kx) r2[kx] = __ldg(reinterpret_cast<const uint4*>(pr + kx * 32));
-      float a0 = 0.f, a1 = 0.f, a2 = 0.f;             // three independent chains
+      for (int kx = 0; kx < 3; ++kx) rr[kx] = rn[kx];
+      if (j + 1 < nrow) {
+        const __nv_bfloat16* pr = p + (long long)(j + 1) * pitch;
+#pragma unroll
+        for (int kx = 0; kx < 3; ++kx) rn[kx] = __ldg(reinterpret_cast<const uint4*>(pr + kx * 32));
+      }
+      float d0 = 0.f, d1 = 0.f, d2 = 0.f;
 #pragma unroll
       for (int kx = 0; kx < 3; ++kx) {
-        a0 += dot8w(r0[kx], sw[0 * 3 + kx]);
-        a1 += dot8w(r1[kx], sw[1 * 3 + kx]);
-        a2 += dot8w(r2[kx], sw[2 * 3 + kx]);
-      }
-      float acc = a0 + a1 + a2;
-      acc += __shfl_xor_sync(0xffffffffu, acc, 1);
-      acc += __shfl_xor_sync(0xffffffffu, acc, 2);
-      if (ok && cg == 0) out[(r * H + y) * (long long)W + x] = (acc + b) * inv_temp;
+        float f[8];
+        unpack8(rr[kx], f);
 #pragma unroll
-      for (int kx = 0; kx < 3; ++kx) { r0[kx] = r1[kx]; r1[kx] = r2[kx]; }
+        for (int c = 0; c < 8; ++c) {
+          d0 = fmaf(f[c], sw[0 * 3 + kx][c], d0);
+          d1 = fmaf(f[c], sw[1 * 3 + kx][c], d1);
+          d2 = fmaf(f[c], sw[2 * 3 + kx][c], d2);
+        }
+      }
+      if (j >= 2) {
+        float acc = o2 + d2;
+        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+        if (ok && cg == 0) out[(r * H + (y0 + j - 2)) * (long long)W + x] = (acc + b) * inv_temp;
+      }
+      o2 = o1 + d1;
+      o1 = d0;
     }
   }
 }
@@ -651,33 +665,39 @@ conv_c32_1_wgrad_kernel(const float* __restrict__ dy, const __nv_bfloat16* __res
     const int y0 = seg * kC32Seg, y1 = min(H, y0 + kC32Seg);
     const long long pitch = (long long)(W + 2) * 32;
     const __nv_bfloat16* p = in + ((r * (H + 2) + y0) * (long long)(W + 2) + x) * 32 + cg * 8;
-    uint4 r0[3], r1[3], r2[3];
+    // each padded row is loaded and unpacked once and multiplied by the gradients of the three output rows it belongs
+    // to (tap row 0 of output j, 1 of j - 1, 2 of j - 2)
+    const int nout = y1 - y0, nrow = nout + 2;
+    uint4 rn[3];
 #pragma unroll
-    for (int kx = 0; kx < 3; ++kx) {
-      r0[kx] = __ldg(reinterpret_cast<const uint4*>(p + kx * 32));
-      r1[kx] = __ldg(reinterpret_cast<const uint4*>(p + pitch + kx * 32));
-    }
-    for (int y = y0; y < y1; ++y) {
-      const __nv_bfloat16* pr = p + (long long)(y - y0 + 2) * pitch;
+    for (int kx = 0; kx < 3; ++kx) rn[kx] = __ldg(reinterpret_cast<const uint4*>(p + kx * 32));
+    float gn = __ldg(dy + (r * H + y0) * (long long)W + x);
+    float g1 = 0.f, g2 = 0.f;
+    for (int j = 0; j < nrow; ++j) {
+      uint4 rr[3];
 #pragma unroll
-      for (int kx = 0; kx < 3; ++kx) r2[kx] = __ldg(reinterpret_cast<const uint4*>(pr + kx * 32));
-      const float g = __ldg(dy + (r * H + y) * (long long)W + x) * inv_temp;
-      accb += g;
+      for (int kx = 0; kx < 3; ++kx) rr[kx] = rn[kx];
+      const float g0 = j < nout ? gn * inv_temp : 0.f;
+      if (j + 1 < nrow) {
+        const __nv_bfloat16* pr = p + (long long)(j + 1) * pitch;
+#pragma unroll
+        for (int kx = 0; kx < 3; ++kx) rn[kx] = __ldg(reinterpret_cast<const uint4*>(pr + kx * 32));
+        if (j + 1 < nout) gn = __ldg(dy + (r * H + y0 + j + 1) * (long long)W + x);
+      }
+      accb += g0;
 #pragma unroll
       for (int kx = 0; kx < 3; ++kx) {
         float f[8];
-        unpack8(r0[kx], f);
+        unpack8(rr[kx], f);
 #pragma unroll
-        for (int c = 0; c < 8; ++c) acc[kx][c] += g * f[c];
-        unpack8(r1[kx], f);
-#pragma unroll
-        for (int c = 0; c < 8; ++c) acc[3 + kx][c] += g * f[c];
-        unpack8(r2[kx], f);
-#pragma unroll
-        for (int c = 0; c < 8; ++c) acc[6 + kx][c] += g * f[c];
+        for (int c = 0; c < 8; ++c) {
+          acc[kx][c] = fmaf(g0, f[c], acc[kx][c]);
+          acc[3 + kx][c] = fmaf(g1, f[c], acc[3 + kx][c]);
+          acc[6 + kx][c] = fmaf(g2, f[c], acc[6 + kx][c]);
+        }
       }
-#pragma unroll
-      for (int kx = 0; kx < 3; ++kx) { r0[kx] = r1[kx]; r1[kx] = r2[kx]; }
+      g2 = g1;
+      g1 = g0;
     }
   }
   __shared__ float red[8][9 * 32 + 1];
