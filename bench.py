@@ -34,6 +34,7 @@ def parse():
     ap.add_argument('--entities', type=int, default=512)
     ap.add_argument('--cpu-sample', default='8x2', help='unroll x trajectories of the bounded CPU sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-inference', action='store_true', help='skip the batched actor-inference figure (N = 1 only)')
     return ap.parse_args()
 
 
@@ -180,6 +181,34 @@ def gemm_flops_hook(records):
         records.append((e0, e1, fl, (name,) + tuple(a[4:16])))
     _lib.call = hooked
     return orig
+
+
+def actor_inference(model, dev, batch=256, iters=8):
+    """BASELINE.json's second metric (reported per GPU): `compute_logp_action` on `batch` observations x 512 entities
+    through learner.ActorStep (CUDA graph, all 64 sampling steps inside), observations resident on the device."""
+    from applestar_b200 import synth
+    from applestar_b200.learner import ActorStep
+    actor = ActorStep(model)
+    obs = synth.tree_map(lambda t: t.to(dev), synth.gen_observations(batch, 512, 7))
+    hidden = [(torch.zeros(batch, 384, device=dev), torch.zeros(batch, 384, device=dev)) for _ in range(3)]
+    noise = synth.tree_map(lambda t: t.to(dev), synth.gen_gumbel(batch, 11))
+
+    def call():
+        return actor(obs['spatial_info'], obs['entity_info'], obs['scalar_info'], obs['entity_num'], hidden, gumbel_noise=noise)
+
+    for _ in range(3):
+        call()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        call()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    return {'metric': 'inference_obs_per_sec_per_gpu', 'value': batch / ms * 1e3, 'unit': 'obs/s', 'ms_per_call': ms,
+            'config': {'workload': 'compute_logp_action_B%d_N512' % batch, 'cuda_graph': True,
+                       'launches_per_call': actor.launches_per_call}}
 
 
 def run_ours(args):
@@ -334,6 +363,8 @@ def run_ours(args):
             v, dt = cpu_learner_throughput(Tc, Bc, N, 2, 1, threads)
             line['cpu_baseline'] = {'value': v, 'unit': 'traj-steps/s', 'cores': threads, 'kind': 'port',
                                     'sample': 'oracle/restate.py forward+loss+backward, T=%d B=%d N=%d, 2 steps' % (Tc, Bc, N)}
+        if not args.no_inference and world == 1:
+            line['inference'] = actor_inference(model, dev)
         print(json.dumps(line))
     if world > 1:
         # tear-down: captured NCCL kernels inside CUDA graphs can stall destroy_process_group(); the numbers are out,
