@@ -99,6 +99,7 @@ _SIGS = {
     'as_masked_mean_fwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
     'as_masked_mean_bwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
     'as_linear_bwd_prep': (c_int, [c_void_p] * 6 + [c_int64, c_int, c_void_p]),
+    'as_linear_bwd_prep2': (c_int, [c_void_p] * 7 + [c_int64, c_int, c_void_p]),
     'as_relu_bwd_colsum_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     'as_spatial_features': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
                                     c_void_p]),

@@ -65,7 +65,7 @@ int su_prefix_bwd(const float*, const long long*, const long long*, const float*
 int su_mask_logits(const float*, const long long*, const long long*, float*, long long, int, int, int, float, float, cudaStream_t);
 int masked_mean_fwd(const float*, const long long*, float*, long long, int, int, cudaStream_t);
 int masked_mean_bwd(const float*, const long long*, float*, long long, int, int, cudaStream_t);
-int linear_bwd_prep(const float*, const float*, const void*, void*, float*, float*, long long, int, cudaStream_t);
+int linear_bwd_prep(const float*, const void*, const float*, const void*, void*, float*, float*, long long, int, cudaStream_t);
 int colsum_f32(const float*, float*, float*, long long, int, cudaStream_t);
 int lnlstm_fwd(const float*, const float*, const float*, const void*, const float*, const float*, const float*,
                const float*, float*, float*, float*, float*, float*, int, int, int, cudaStream_t);
@@ -362,7 +362,11 @@ int as_masked_mean_bwd(const float* dout, const int64_t* len, float* dx, int64_t
 }
 int as_linear_bwd_prep(const float* dy, const float* y32, const void* y16, void* dz16, float* colsum, float* scratch,
                        int64_t rows, int C, void* stream) {
-  return as::linear_bwd_prep(dy, y32, y16, dz16, colsum, scratch, rows, C, ST(stream));
+  return as::linear_bwd_prep(dy, nullptr, y32, y16, dz16, colsum, scratch, rows, C, ST(stream));
+}
+int as_linear_bwd_prep2(const float* dy32, const void* dy16, const float* y32, const void* y16, void* dz16, float* colsum,
+                        float* scratch, int64_t rows, int C, void* stream) {
+  return as::linear_bwd_prep(dy32, dy16, y32, y16, dz16, colsum, scratch, rows, C, ST(stream));
 }
 int as_colsum_bf16_static(const void* x, float* out, int64_t rows, int C, void* stream) {
   return as::colsum_bf16_static(x, out, rows, C, ST(stream));

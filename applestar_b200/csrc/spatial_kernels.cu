@@ -1358,7 +1358,8 @@ int relu_bwd_colsum(const void* dy, const void* y, void* dz, float* out, float* 
 //   colsum[c] = sum_r dz[r][c]                         ->  bias gradient (optional)
 // replaces three passes (ReLU mask, fp32 -> bf16 cast, column sum).  Same thread mapping as colsum_partial_v8_kernel.
 __global__ void __launch_bounds__(256)
-linear_bwd_prep_kernel(const float* __restrict__ dy, const float* __restrict__ y32, const __nv_bfloat16* __restrict__ y16,
+linear_bwd_prep_kernel(const float* __restrict__ dy, const __nv_bfloat16* __restrict__ dy_extra, const float* __restrict__ y32,
+                       const __nv_bfloat16* __restrict__ y16,
                        __nv_bfloat16* __restrict__ dz, float* __restrict__ partial, long long rows, int C, int chunks,
                        int txn) {
   const int tx = threadIdx.x & (txn - 1), ty = threadIdx.x / txn, tyn = 256 / txn;
@@ -1377,6 +1378,12 @@ linear_bwd_prep_kernel(const float* __restrict__ dy, const float* __restrict__ y
         const float4 a = __ldg(reinterpret_cast<const float4*>(dy + rr * C + c));
         const float4 b = __ldg(reinterpret_cast<const float4*>(dy + rr * C + c) + 1);
         float f[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        if (dy_extra) {                                  // second gradient of the same output (its bf16 copy had a consumer too)
+          BF8 ev;
+          ev.u = __ldg(reinterpret_cast<const uint4*>(dy_extra + rr * C + c));
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] += bf2f(ev.h[j]);
+        }
         if (y32) {
           const float4 ya = __ldg(reinterpret_cast<const float4*>(y32 + rr * C + c));
           const float4 yb = __ldg(reinterpret_cast<const float4*>(y32 + rr * C + c) + 1);
@@ -1412,17 +1419,18 @@ linear_bwd_prep_kernel(const float* __restrict__ dy, const float* __restrict__ y
   }
 }
 
-int linear_bwd_prep(const float* dy, const float* y32, const void* y16, void* dz, float* colsum, float* scratch,
-                    long long rows, int C, cudaStream_t st) {
+int linear_bwd_prep(const float* dy, const void* dy_extra, const float* y32, const void* y16, void* dz, float* colsum,
+                    float* scratch, long long rows, int C, cudaStream_t st) {
   if (rows <= 0 || C <= 0 || (C % 8) != 0) return AS_ESIZE;
   if (!dy || !dz || (colsum && !scratch)) return AS_EINVAL;
-  if ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(y32) | reinterpret_cast<uintptr_t>(y16) |
+  if ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(dy_extra) | reinterpret_cast<uintptr_t>(y32) |
+       reinterpret_cast<uintptr_t>(y16) |
        reinterpret_cast<uintptr_t>(dz)) & 15) return AS_EALIGN;
   long long want = (rows + 63) / 64;
   const int chunks = (int)(want < 1 ? 1 : (want > 1024 ? 1024 : want));   // scratch: as_colsum_scratch_floats(C) = 1024 * C floats
   const int txn = C >= 128 ? 16 : (C >= 64 ? 8 : 4);
   dim3 g((C + txn * 8 - 1) / (txn * 8), chunks);
-  linear_bwd_prep_kernel<<<g, 256, 0, st>>>(dy, y32, (const __nv_bfloat16*)y16, (__nv_bfloat16*)dz, colsum ? scratch : nullptr,
+  linear_bwd_prep_kernel<<<g, 256, 0, st>>>(dy, (const __nv_bfloat16*)dy_extra, y32, (const __nv_bfloat16*)y16, (__nv_bfloat16*)dz, colsum ? scratch : nullptr,
                                             rows, C, chunks, txn);
   AS_LAUNCH_CHECK();
   if (colsum) {

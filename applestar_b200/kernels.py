@@ -130,8 +130,13 @@ class LinearFn(torch.autograd.Function):
         K8 = w16.shape[1]
         if dy32 is None and dy16 is None:
             return None, None, None, None, None, None
+        extra = None
         if dy32 is not None and dy16 is not None:
-            dy = dy32 + dy16
+            if (dy32.dtype == torch.float32 and dy16.dtype == torch.bfloat16 and N % 8 == 0 and dy32.is_contiguous()
+                    and dy16.is_contiguous() and (y is None or y.is_contiguous())):
+                dy, extra = dy32, dy16.reshape(-1, N)         # summed inside as_linear_bwd_prep2
+            else:
+                dy = dy32 + dy16
         else:
             dy = dy32 if dy32 is not None else dy16
         dy2 = dy.reshape(-1, N)
@@ -146,7 +151,7 @@ class LinearFn(torch.autograd.Function):
             if want_db:
                 db = torch.empty(N, dtype=torch.float32, device=dy.device)
                 scratch = torch.empty(_lib.lib().as_colsum_scratch_floats(N), dtype=torch.float32, device=dy.device)
-            _lib.call('as_linear_bwd_prep', dy2.data_ptr(), _ptr(y32), _ptr(y16), dy16b.data_ptr(), _ptr(db),
+            _lib.call('as_linear_bwd_prep2', dy2.data_ptr(), _ptr(extra), _ptr(y32), _ptr(y16), dy16b.data_ptr(), _ptr(db),
                       _ptr(scratch) if want_db else 0, M, N, _lib.stream_ptr())
             want_db = False
         elif (ctx.relu and want_db and dy2.dtype == torch.bfloat16 and y is not None and y.dtype == torch.bfloat16

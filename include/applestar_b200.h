@@ -131,7 +131,11 @@ int as_relu_bwd_colsum_bf16(const void* dy, const void* y, void* dz, float* cols
  * no activation) and colsum[c] = sum_r dy*(y>0) = the bias gradient (colsum NULL = no bias).  Replaces autograd's
  * threshold_backward, the dtype cast and the `.sum(0)`.  scratch: as_colsum_scratch_floats(C) floats. */
 int as_linear_bwd_prep(const float* dy, const float* y32, const void* y16, void* dz16, float* colsum, float* scratch,
-                       int64_t rows, int C, void* stream);   /* fp32 rows, same scratch size */
+                       int64_t rows, int C, void* stream);
+/* The same when the layer's output existed as an fp32 and a bf16 copy and BOTH received a gradient (dy = dy32 + dy16):
+ * the sum is formed inside the pass instead of by a separate add over the two tensors. */
+int as_linear_bwd_prep2(const float* dy32, const void* dy16, const float* y32, const void* y16, void* dz16, float* colsum,
+                        float* scratch, int64_t rows, int C, void* stream);   /* fp32 rows, same scratch size */
 /* Same column sums for hosts that may not allocate device memory at all (a process that gave its whole device
  * budget to an arena at start-up, or a step loop that cannot afford the device-wide synchronisation cudaMalloc /
  * cudaFree bring).  This entry point has no counterpart in the reference.  It allocates nothing: the partial sums
