@@ -5,6 +5,8 @@ The fixtures pin oracle/restate.py (and through it the CUDA path) to the execute
   state_dict_spec.json   keys / shapes / trainable flags of the reference Model (1 and 4 baselines)
   learner_small.pt       rl_learner_forward + compute_loss + backward, T=2 B=2 N=64, fp32 (+fp64 truth)
   infer_small.pt         compute_logp_action under fixed Gumbel noise, B=3 N=512 (incl. collision / 1-entity obs)
+  learner_n128.pt        the learner case at N=128 entities, one baseline (the size from which the fused tcgen05 attention
+                         forward / backward kernels run); written by `python oracle/make_golden.py n128` alone
   scatter_small.pt       scatter_connection on a heavy-collision case
 Inputs and weights are NOT stored: tests regenerate them from the same seeds (applestar_b200/synth.py).
 """
@@ -168,6 +170,10 @@ def main():
     os.makedirs(GOLD, exist_ok=True)
     torch.manual_seed(0)
     torch.set_num_threads(8)
+    if len(sys.argv) > 1 and sys.argv[1] == 'n128':     # additional fixture only; the others stay byte-identical
+        torch.save(learner_case(2, 2, 128, ['winloss'], 4242), os.path.join(GOLD, 'learner_n128.pt'))
+        print('learner_n128.pt', os.path.getsize(os.path.join(GOLD, 'learner_n128.pt')))
+        return
     specs = {}
     for name, bl in (('winloss', ['winloss']), ('four', ['winloss', 'build_order', 'built_unit', 'battle'])):
         _, _, spec = build_ref_model(bl)

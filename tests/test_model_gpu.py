@@ -35,10 +35,13 @@ def test_state_dict_contract():
 
 
 @gpu
-def test_learner_forward_loss_backward_vs_golden():
+@pytest.mark.parametrize('fixture,spec', [('learner_small.pt', 'four'), ('learner_n128.pt', 'winloss')])
+def test_learner_forward_loss_backward_vs_golden(fixture, spec):
+    """learner_small: N = 64 (composed attention path); learner_n128: N = 128, where the fused tcgen05 attention forward
+    and backward kernels, the scatter-fused feature kernel and the tap-pair weight gradients all run."""
     from applestar_b200 import ReinforcementLoss
-    g = golden('learner_small.pt')
-    model, sd = _model(g['baselines'], 'four')
+    g = golden(fixture)
+    model, sd = _model(g['baselines'], spec)
     data = synth.gen_trajectories(g['T'], g['B'], g['N'], g['seed'])
     out = model.rl_learner_forward(**synth.tree_map(lambda t: t.cuda(), data))
     for k in C.HEADS:

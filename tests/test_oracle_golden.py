@@ -120,3 +120,20 @@ def test_scan_matches_python_loops():
             else:
                 g_next = r[t, b].item() + 0.997 * 0.8 * g_next + 0.997 * 0.2 * v[t + 1, b].item()
             assert abs(g_next - ret[t, b].item()) < 1e-5
+
+
+def test_learner_n128_fixture():
+    """The N = 128 fixture (fused-attention size) pins the restatement the same way: logits, values, total loss."""
+    g = golden('learner_n128.pt')
+    sd = synth.full_state_dict(load_spec('winloss'), 0)
+    data = synth.gen_trajectories(g['T'], g['B'], g['N'], g['seed'])
+    with torch.no_grad():
+        out = R.rl_learner_forward(sd, g['baselines'], **clone_tree(data))
+        info = R.compute_loss(C.DEFAULT_LOSS_CONFIG, out)
+    for k in C.HEADS:
+        a, b = valid_logits(out['target_logit'][k], g['logit'][k])
+        assert max_abs(a, b) < 1e-5, k
+    for k, v in out['value'].items():
+        assert max_abs(v, g['value'][k]) < 1e-5, k
+    v = g['loss_info']['total_loss']
+    assert abs(float(info['total_loss']) - v) <= 1e-5 * max(1.0, abs(v))
