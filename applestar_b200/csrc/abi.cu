@@ -141,8 +141,8 @@ int as_splitk_reduce(const float* ws, float* out, int64_t n, int splits, int acc
   return as::splitk_reduce(ws, out, n, splits, accumulate, ST(stream));
 }
 
-int as_conv_nhwc_bf16(const void* x, const void* w, void* y, const float* bias, int64_t R, int H, int W, int Cin,
-                      int Cout, int taps, int w_mn, int y_bf16, int relu, void* stream) {
+static int conv_nhwc_impl(const void* x, const void* w, void* y, const float* bias, const void* resid, int64_t R, int H, int W,
+                          int Cin, int Cout, int taps, int w_mn, int y_bf16, int relu, void* stream) {
   if (taps != 1 && taps != 9) return AS_EUNSUPPORTED;
   if (R <= 0 || H <= 0 || W <= 0 || Cin <= 0 || Cout <= 0) return AS_ESIZE;
   if (Cin % 8 != 0) return AS_EUNSUPPORTED;
@@ -150,7 +150,7 @@ int as_conv_nhwc_bf16(const void* x, const void* w, void* y, const float* bias, 
   const int64_t P = R * (int64_t)ph * pw;
   if (P > 2147483647LL) return AS_ESIZE;
   as::GemmCall g;
-  g.A = x; g.B = w; g.C = y; g.bias = bias;
+  g.A = x; g.B = w; g.C = y; g.bias = bias; g.resid = resid;
   g.M = (int)P; g.N = Cout; g.K = Cin;
   g.a_mn = false; g.b_mn = w_mn != 0;
   g.lda = Cin; g.ldb = g.b_mn ? Cout : (int64_t)taps * Cin; g.ldc = Cout;
@@ -164,6 +164,15 @@ int as_conv_nhwc_bf16(const void* x, const void* w, void* y, const float* bias, 
   }
   g.img_w = pw; g.img_h = ph;
   return as::gemm_run(g, ST(stream));
+}
+int as_conv_nhwc_bf16(const void* x, const void* w, void* y, const float* bias, int64_t R, int H, int W, int Cin,
+                      int Cout, int taps, int w_mn, int y_bf16, int relu, void* stream) {
+  return conv_nhwc_impl(x, w, y, bias, nullptr, R, H, W, Cin, Cout, taps, w_mn, y_bf16, relu, stream);
+}
+int as_conv_nhwc_bf16_add(const void* x, const void* w, void* y, const float* bias, const void* addend, int64_t R, int H,
+                          int W, int Cin, int Cout, int taps, int relu, void* stream) {
+  if (!addend) return AS_EINVAL;
+  return conv_nhwc_impl(x, w, y, bias, addend, R, H, W, Cin, Cout, taps, 0, 1, relu, stream);
 }
 
 // 0: one tap per tile; 1 / 2: tap pairs on a 64-channel M side (dy / swapped x), needs split-K partials

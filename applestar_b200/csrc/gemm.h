@@ -20,6 +20,7 @@ struct GemmCall {
   int c_bf16 = 0;
   long long ldc = 0, c_sb0 = 0, c_sb1 = 0;
   const float* bias = nullptr;
+  const void* resid = nullptr;   // optional bf16 tensor with C's layout (ldc, batch strides), added before ReLU (TMA-store path)
   int relu = 0;
   float alpha = 1.f;
   int splits = 1;            // >1: fp32 partials to ws[splits][batch][M][N]

@@ -52,6 +52,7 @@ struct GemmDev {
   int c_bf16;
   long long ldc, c_sb0, c_sb1;
   const float* bias;
+  const __nv_bfloat16* resid;   // bf16 [.., M, ldc]: added to the accumulator row before ReLU / border masking (or nullptr)
   int relu;
   float alpha;
   float* ws;  // split-K partials
@@ -444,6 +445,21 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = fmaf(__uint_as_float(v[j]), p.alpha, __shfl_sync(0xffffffffu, bl, j));
           }
+          if (p.resid != nullptr && grow < p.M && gc + 32 <= p.N) {
+            // residual / second gradient contribution with C's layout: this lane's 32 columns are 64 contiguous bytes
+            const uint4* r4 = reinterpret_cast<const uint4*>(p.resid + (long long)b0 * p.c_sb0 + (long long)b1 * p.c_sb1 +
+                                                             (long long)grow * p.ldc + gc);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const uint4 rv = __ldg(r4 + q);
+              const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
+#pragma unroll
+              for (int t = 0; t < 4; ++t) {
+                f[8 * q + 2 * t] += __uint_as_float(rw[t] << 16);
+                f[8 * q + 2 * t + 1] += __uint_as_float(rw[t] & 0xffff0000u);
+              }
+            }
+          }
           if (p.relu) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
@@ -828,6 +844,7 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
   p.splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;   // drop empty splits
   if (g.splits > 1 && p.splits != g.splits) return AS_ESIZE;     // caller sizes ws from as_gemm_splits()
   p.C = g.C; p.C2 = g.C2; p.c_bf16 = g.c_bf16; p.ldc = g.ldc; p.c_sb0 = g.c_sb0; p.c_sb1 = g.c_sb1;
+  p.resid = reinterpret_cast<const __nv_bfloat16*>(g.resid);
   p.bias = g.bias; p.relu = g.relu; p.alpha = g.alpha; p.ws = g.ws;
   p.debug = g_gemm_debug;
   // slab mode for multi-tap convolutions (see the header comment): needs the halo'd slab of a 256-row step to fit two
@@ -894,6 +911,10 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
     if ((g.c_bf16 || g.C2 != nullptr) && BN < 64 && p.n_blocks > 1) ok = 0;
     p.tma_store = ok;
   }
+  // the residual add lives in the TMA-store epilogue only; whole 32-column chunks, 16-byte aligned rows
+  if (g.resid != nullptr && (!p.tma_store || (g.N % 32) != 0 || (g.ldc % 8) != 0 ||
+                             (reinterpret_cast<uintptr_t>(g.resid) & 15) != 0))
+    return AS_EUNSUPPORTED;
   switch (BN) {
     case 32: return dispatch_major<32>(g.a_mn, g.b_mn, ta, tb, tc, tc2, tb2, p, st);
     case 64: return dispatch_major<64>(g.a_mn, g.b_mn, ta, tb, tc, tc2, tb2, p, st);

@@ -65,6 +65,11 @@ class Conv(nn.Sequential):
             return spatial.conv(x, self[0].weight, self[0].bias, self.relu)
         return ops.conv2d(x, self[0].weight, self[0].bias, self.pad, self.relu)
 
+    def fork(self, x):
+        """-> (self(x), x'): x' aliases x and must replace it in x's OTHER consumers, so that their gradient is added to
+        this convolution's data gradient in its GEMM epilogue (spatial.ConvNHWC)."""
+        return spatial.conv_fork(x, self[0].weight, self[0].bias, self.relu)
+
 
 def _eye_table(n):
     return nn.Embedding.from_pretrained(torch.eye(n), freeze=True, padding_idx=None)
@@ -172,7 +177,8 @@ class ResBlock(nn.Module):
         self.conv2 = Conv(ch, ch, 3, 1, nhwc=True)
 
     def forward(self, x):
-        return spatial.add_relu(self.conv2(self.conv1(x)), x)
+        h, x = self.conv1.fork(x)
+        return spatial.add_relu(self.conv2(h), x)
 
 
 class SpatialEncoder(nn.Module):
@@ -478,7 +484,11 @@ class GatedResBlock(nn.Module):
         self.UpdateSP = nn.Parameter(torch.full((1,), 0.1))
 
     def forward(self, x):
-        return spatial.gated_residual(self.conv2(self.conv1(x)), self.GateWeightG(x), self.UpdateSP, x)
+        h, x = self.conv1.fork(x)
+        g, x = self.GateWeightG[0].fork(x)
+        for layer in list(self.GateWeightG)[1:]:
+            g = layer(g)
+        return spatial.gated_residual(self.conv2(h), g, self.UpdateSP, x)
 
 
 class LocationHead(nn.Module):

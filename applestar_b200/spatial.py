@@ -42,9 +42,18 @@ def _conv_call(x, w2, y, bias, R, H, W, cin, cout, taps, relu):
               1, int(relu), _lib.stream_ptr())
 
 
+FORK_CONV = os.environ.get('APPLESTAR_CONV_FORK', '1') != '0'
+
+
 class ConvNHWC(torch.autograd.Function):
+    """3x3 / 1x1 convolution on a padded NHWC bf16 map.  With `fork` the input is handed back as a second output (an
+    alias): the caller gives THAT tensor to the input's other consumers (residual add, gate branch), so in backward their
+    gradient arrives here as `dxa` and is added to this convolution's data gradient inside the GEMM epilogue
+    (as_conv_nhwc_bf16_add) instead of by autograd's separate add over the two maps."""
+
     @staticmethod
-    def forward(ctx, x, weight, bias, relu):
+    def forward(ctx, x, weight, bias, relu, fork=False):
+        ctx.set_materialize_grads(False)
         R, ph, pw, cin_p = x.shape
         H, W = ph - 2, pw - 2
         cout, cin, kh, _ = weight.shape
@@ -57,10 +66,14 @@ class ConvNHWC(torch.autograd.Function):
         ctx.relu = relu
         ctx.has_bias = bias is not None
         ctx.save_for_backward(x, w_dg, y if relu else None)
+        if fork:
+            return y, x.view_as(x)
         return y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, dxa=None):
+        if dy is None:                                   # only the pass-through alias was used downstream
+            return dxa, None, None, None, None
         x, w_dg, y = ctx.saved_tensors
         R, H, W, cin, cin_p, cout, taps, kh = ctx.dims
         dy = dy.contiguous()
@@ -80,7 +93,14 @@ class ConvNHWC(torch.autograd.Function):
             dy = dz
         if ctx.needs_input_grad[0]:
             dx = torch.empty_like(x)
-            _conv_call(dy, w_dg, dx, None, R, H, W, cout, cin_p, taps, False)
+            if dxa is not None and cin_p % 32 == 0 and dxa.dtype == torch.bfloat16 and dxa.shape == x.shape:
+                dxa = dxa.contiguous()
+                _lib.call('as_conv_nhwc_bf16_add', dy.data_ptr(), w_dg.data_ptr(), dx.data_ptr(), 0, dxa.data_ptr(), R, H, W,
+                          cout, cin_p, taps, 0, st)
+            else:
+                _conv_call(dy, w_dg, dx, None, R, H, W, cout, cin_p, taps, False)
+                if dxa is not None:
+                    dx = dx + dxa
         if ctx.needs_input_grad[1]:
             P = R * (H + 2) * (W + 2)
             tiles = taps * ((cout + 127) // 128) * max(1, (cin_p + 255) // 256)
@@ -98,11 +118,18 @@ class ConvNHWC(torch.autograd.Function):
             db = torch.empty(cout, dtype=torch.float32, device=x.device)
             scratch = torch.empty(_lib.lib().as_colsum_scratch_floats(cout), dtype=torch.float32, device=x.device)
             _lib.call('as_colsum_bf16', dy.data_ptr(), db.data_ptr(), scratch.data_ptr(), R * (H + 2) * (W + 2), cout, st)
-        return dx, dw, db, None
+        return dx, dw, db, None, None
 
 
 def conv(x, weight, bias, relu=False):
     return ConvNHWC.apply(x, weight, bias, relu)
+
+
+def conv_fork(x, weight, bias, relu=False):
+    """-> (conv(x), alias of x for x's other consumers); see ConvNHWC."""
+    if not FORK_CONV or not (torch.is_grad_enabled() and x.requires_grad):
+        return ConvNHWC.apply(x, weight, bias, relu), x
+    return ConvNHWC.apply(x, weight, bias, relu, True)
 
 
 class AddAct(torch.autograd.Function):

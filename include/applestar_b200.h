@@ -63,6 +63,12 @@ int as_splitk_reduce(const float* ws, float* out, int64_t n, int splits, int acc
  * (border written as zero).  taps = 9 (3x3, pad 1) or 1.  Cin % 8 == 0. */
 int as_conv_nhwc_bf16(const void* x, const void* w, void* y, const float* bias, int64_t R, int H, int W, int Cin,
                       int Cout, int taps, int w_mn, int y_bf16, int relu, void* stream);
+/* y = act(conv(x) + bias + addend): the same convolution with a bf16 map of y's shape added in the epilogue.  Used in the
+ * backward pass where an activation feeds a convolution AND a residual / gate branch (res_block.py:60-64,
+ * module_utils.py:222-231): the data gradient of the convolution is accumulated onto the branch's gradient in the GEMM
+ * epilogue instead of by a separate add over the two maps.  Cout % 32 == 0. */
+int as_conv_nhwc_bf16_add(const void* x, const void* w, void* y, const float* bias, const void* addend, int64_t R, int H,
+                          int W, int Cin, int Cout, int taps, int relu, void* stream);
 
 /* Weight gradient of the NHWC convolution above: dw[tap][co][ci] = sum_p dy[p][co] * x[p + shift(tap)][ci] as one
  * tap-batched, split-K tcgen05 GEMM with both operands read MN-major.  dy [R,(H+2),(W+2),Cout] bf16 (zero border),
