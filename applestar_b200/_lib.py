@@ -93,8 +93,8 @@ _SIGS = {
     'as_attn_small_fwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_float, c_void_p]),
     'as_attn_small_bwd': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_float, c_void_p]),
     'as_pack_f32': (c_int, [c_void_p, c_int, c_void_p, c_void_p]),
-    'as_conv_wgrad_pair_mode': (c_int, [c_int, c_int, c_int, c_int]),
-    'as_conv_wgrad_ws_floats': (c_int64, [c_int, c_int, c_int, c_int]),
+    'as_conv_wgrad_pair_mode': (c_int, [c_int, c_int, c_int, c_int, c_int]),
+    'as_conv_wgrad_ws_floats': (c_int64, [c_int, c_int, c_int, c_int, c_int]),
     'as_conv_nhwc_bf16_add': (c_int, [c_void_p] * 5 + [c_int64, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     'as_su_sample': (c_int, [POINTER(AsSuSampleArgs), c_void_p]),
     'as_masked_mean_fwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),

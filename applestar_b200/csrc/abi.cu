@@ -176,15 +176,18 @@ int as_conv_nhwc_bf16_add(const void* x, const void* w, void* y, const float* bi
 }
 
 // 0: one tap per tile; 1 / 2: tap pairs on a 64-channel M side (dy / swapped x), needs split-K partials
-int as_conv_wgrad_pair_mode(int Cin, int Cout, int taps, int splits) {
+// 11 / 12: the same pairing with all nine taps walked from one shared-memory slab per pixel block (wgrad_slab.cu)
+int as_conv_wgrad_pair_mode(int Cin, int Cout, int taps, int splits, int W) {
   if (taps != 9 || splits <= 1 || getenv("AS_WGRAD_NO_PAIR")) return 0;
-  if (Cout == 64) return 1;
-  if (Cin == 64 && Cout < 64) return 2;
-  return 0;
+  int mode = 0;
+  if (Cout == 64) mode = 1;
+  else if (Cin == 64 && Cout < 64) mode = 2;
+  if (mode && !getenv("AS_WGRAD_NO_SLAB") && as::wgrad_slab_ok(mode, Cin, Cout, W + 2)) mode += 10;
+  return mode;
 }
-int64_t as_conv_wgrad_ws_floats(int Cin, int Cout, int taps, int splits) {
+int64_t as_conv_wgrad_ws_floats(int Cin, int Cout, int taps, int splits, int W) {
   if (splits <= 1) return 0;
-  const int pair = as_conv_wgrad_pair_mode(Cin, Cout, taps, splits);
+  const int pair = as_conv_wgrad_pair_mode(Cin, Cout, taps, splits, W) % 10;
   if (pair) return (int64_t)splits * 5 * 128 * (pair == 1 ? Cin : Cout);
   return (int64_t)splits * taps * Cout * Cin;
 }
@@ -196,7 +199,14 @@ int as_conv_wgrad_nhwc_bf16(const void* dy, const void* x, float* dw, float* ws,
   const int pw = W + 2, ph = H + 2;
   const int64_t P = R * (int64_t)ph * pw;
   if (P > 2147483647LL) return AS_ESIZE;
-  const int pair = as_conv_wgrad_pair_mode(Cin, Cout, taps, splits);
+  const int pmode = as_conv_wgrad_pair_mode(Cin, Cout, taps, splits, W);
+  const int pair = pmode % 10;
+  if (pmode >= 10) {
+    const int n = pair == 1 ? Cin : Cout;
+    int rc = as::wgrad_slab(pair, dy, x, ws, P, pw, Cin, Cout, splits, ST(stream));
+    if (rc) return rc;
+    return as::wgrad_pair_reduce(ws, dw, splits, 5LL * 128 * n, taps, Cout, Cin, pair == 2, pair == 1, ST(stream));
+  }
   if (pair) {
     // two taps per 128-row MMA (gemm_tcgen05.cu, wg_pair).  mode 1: M = Cout = 64, the second tap's dy rows are read
     // shift[b] - shift[a] earlier; mode 2 (Cout < 64 = Cin): operands swapped, M = Cin = 64, both x chunks shifted
@@ -218,7 +228,7 @@ int as_conv_wgrad_nhwc_bf16(const void* dy, const void* x, float* dw, float* ws,
     g.splits = splits; g.ws = ws;
     int rc = as::gemm_run(g, ST(stream));
     if (rc) return rc;
-    return as::wgrad_pair_reduce(ws, dw, splits, 5LL * 128 * g.N, taps, Cout, Cin, pair == 2, ST(stream));
+    return as::wgrad_pair_reduce(ws, dw, splits, 5LL * 128 * g.N, taps, Cout, Cin, pair == 2, 0, ST(stream));
   }
   as::GemmCall g;
   g.A = dy; g.B = x;

@@ -40,6 +40,9 @@ struct GemmCall {
 int gemm_run(const GemmCall& g, cudaStream_t st);
 int splitk_reduce(const float* ws, float* out, long long n, int splits, int accumulate, cudaStream_t st);
 int wgrad_pair_reduce(const float* ws, float* out, int splits, long long stride, int taps, int cout, int cin, int transposed,
-                      cudaStream_t st);
+                      int swap_halves, cudaStream_t st);
+int wgrad_slab_ok(int mode, int Cin, int Cout, int pw);
+int wgrad_slab(int mode, const void* dy, const void* x, float* ws, long long P, int pw, int Cin, int Cout, int splits,
+               cudaStream_t st);
 
 }  // namespace as

@@ -966,23 +966,24 @@ __global__ void splitk_reduce_scalar_kernel(const float* __restrict__ ws, float*
 // out[t][co][ci] (t < taps) from the tap-pair partials ws[split][5][128][N]: row t * 64 + m of a split's [640][N] matrix;
 // plain (m = co, N = cin) or transposed (m = ci, N = cout: the operands were swapped to get a 64-channel M side)
 __global__ void wgrad_pair_reduce_kernel(const float* __restrict__ ws, float* __restrict__ out, int splits, long long stride,
-                                         int total, int cout, int cin, int transposed) {
+                                         int total, int cout, int cin, int transposed, int swap_halves) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total) return;
-  long long src = i;
-  if (transposed) {
-    const int ci = i % cin, co = (i / cin) % cout, t = i / (cin * cout);
-    src = ((long long)t * 64 + ci) * cout + co;
-  }
+  const int ci = i % cin, co = (i / cin) % cout, t = i / (cin * cout);
+  // row of tap t inside a split's [5 pairs][128][N] block; swap_halves: the later tap of a pair sits in rows 0-63
+  const int half = swap_halves ? ((t & 1) ^ 1) : (t & 1);
+  const long long row0 = (long long)(t >> 1) * 128 + half * 64;
+  const long long src = transposed ? (row0 + ci) * cout + co : (row0 + co) * cin + ci;
   float a = 0.f;
   for (int s = 0; s < splits; ++s) a += ws[(long long)s * stride + src];
   out[i] = a;
 }
 
 int wgrad_pair_reduce(const float* ws, float* out, int splits, long long stride, int taps, int cout, int cin, int transposed,
-                      cudaStream_t st) {
+                      int swap_halves, cudaStream_t st) {
   const int total = taps * cout * cin;
-  wgrad_pair_reduce_kernel<<<(total + 127) / 128, 128, 0, st>>>(ws, out, splits, stride, total, cout, cin, transposed);
+  wgrad_pair_reduce_kernel<<<(total + 127) / 128, 128, 0, st>>>(ws, out, splits, stride, total, cout, cin, transposed,
+                                                                swap_halves);
   AS_LAUNCH_CHECK();
   return AS_OK;
 }

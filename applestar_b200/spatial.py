@@ -104,12 +104,15 @@ class ConvNHWC(torch.autograd.Function):
         if ctx.needs_input_grad[1]:
             P = R * (H + 2) * (W + 2)
             tiles = taps * ((cout + 127) // 128) * max(1, (cin_p + 255) // 256)
-            if _lib.lib().as_conv_wgrad_pair_mode(cin_p, cout, taps, 2):
+            pmode = _lib.lib().as_conv_wgrad_pair_mode(cin_p, cout, taps, 2, W)
+            if pmode >= 10:
+                tiles = 1                       # one CTA per split walks all nine taps from a shared-memory slab
+            elif pmode:
                 tiles = 5                       # two taps per 128-row tile (64-channel M side)
             want = max(1, min((P + 63) // 64, K.NUM_SMS // tiles))
             splits = _lib.lib().as_gemm_splits(P, want)
             dw9 = torch.empty((taps, cout, cin_p), dtype=torch.float32, device=x.device)
-            ws_n = _lib.lib().as_conv_wgrad_ws_floats(cin_p, cout, taps, splits)
+            ws_n = _lib.lib().as_conv_wgrad_ws_floats(cin_p, cout, taps, splits, W)
             ws = torch.empty(ws_n, dtype=torch.float32, device=x.device) if splits > 1 else None
             _lib.call('as_conv_wgrad_nhwc_bf16', dy.data_ptr(), x.data_ptr(), dw9.data_ptr(), _ptr(ws), R, H, W, cin_p,
                       cout, taps, splits, st)

@@ -78,10 +78,11 @@ int as_conv_wgrad_nhwc_bf16(const void* dy, const void* x, float* dw, float* ws,
                             int Cout, int taps, int splits, void* stream);
 /* Tap pairing of the 3x3 weight gradient: when the M side of dW = dy^T x has 64 channels (Cout == 64, or Cin == 64 with
  * the operands swapped), two taps share one 128-row tcgen05.mma.  as_conv_wgrad_pair_mode tells which form
- * as_conv_wgrad_nhwc_bf16 will use (0 none, 1 dy side, 2 swapped) and as_conv_wgrad_ws_floats the split-K workspace
- * size it then needs. */
-int as_conv_wgrad_pair_mode(int Cin, int Cout, int taps, int splits);
-int64_t as_conv_wgrad_ws_floats(int Cin, int Cout, int taps, int splits);
+ * as_conv_wgrad_nhwc_bf16 will use (0 none, 1 dy side, 2 swapped; 11 / 12: the same with all nine taps taken from one
+ * shared-memory slab per 64-pixel block, one CTA per split -- maps up to 125 pixels wide) and as_conv_wgrad_ws_floats the
+ * split-K workspace size it then needs. */
+int as_conv_wgrad_pair_mode(int Cin, int Cout, int taps, int splits, int W);
+int64_t as_conv_wgrad_ws_floats(int Cin, int Cout, int taps, int splits, int W);
 
 /* Layout conversion between the reference's NCHW fp32 maps and the padded NHWC bf16 maps the convolutions use:
  * dst [R,H+2,W+2,Cp] (border and channels >= C zero; relu != 0 applies ReLU on the way) / its inverse (interior,
