@@ -183,6 +183,9 @@ int as_conv_wgrad_pair_mode(int Cin, int Cout, int taps, int splits, int W) {
   if (Cout == 64) mode = 1;
   else if (Cin == 64 && Cout < 64) mode = 2;
   if (mode && !getenv("AS_WGRAD_NO_SLAB") && as::wgrad_slab_ok(mode, Cin, Cout, W + 2)) mode += 10;
+  // 64 -> 128 channels: the plain form has a full M = 128; the slab form (operands swapped, two column halves) still wins by
+  // reading the pixels once
+  if (!mode && Cin == 64 && Cout == 128 && !getenv("AS_WGRAD_NO_SLAB") && as::wgrad_slab_ok(2, Cin, Cout, W + 2)) mode = 12;
   return mode;
 }
 int64_t as_conv_wgrad_ws_floats(int Cin, int Cout, int taps, int splits, int W) {

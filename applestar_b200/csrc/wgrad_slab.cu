@@ -33,7 +33,7 @@ struct WgradSlabDev {
   int halo_a, halo_b;                     // slab row 0 = pixel k0 - halo
   int bytes_a, bytes_b;                   // slab sizes rounded up to 1024
   int a_row[5], a_lbo[5], b_row[5];       // per tap pair: chunk-0 row of A, chunk distance in bytes, row of B
-  int N;                                  // real columns of B (<= 64)
+  int N;                                  // real columns of B (<= 128: blockIdx.y selects a 64-column half)
   float* ws;                              // [gridDim][5][128][N]
 };
 
@@ -47,6 +47,7 @@ wgrad_slab_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint64_t* done_bar = empty_bar + kWsStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done_bar + 1);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = blockIdx.y * 64;
   const int kb_begin = blockIdx.x * p.kb_per_split;
   const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
 
@@ -72,7 +73,7 @@ wgrad_slab_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         uint8_t* sa = smem + stage * stage_bytes;
         mbar_expect_tx(&full_bar[stage], (uint32_t)((p.rows_a + p.rows_b) * 128));
         tma_load_4d(sa, &tmA, &full_bar[stage], 0, kb * kWsBK - p.halo_a, 0, 0);
-        tma_load_4d(sa + p.bytes_a, &tmB, &full_bar[stage], 0, kb * kWsBK - p.halo_b, 0, 0);
+        tma_load_4d(sa + p.bytes_a, &tmB, &full_bar[stage], n0, kb * kWsBK - p.halo_b, 0, 0);
         if (++stage == kWsStages) { stage = 0; phase ^= 1; }
       }
     }
@@ -111,8 +112,9 @@ wgrad_slab_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       tc_fence_after();
     }
     for (int b = 0; b < 5; ++b) {
-      float* dst = p.ws + (((long long)blockIdx.x * 5 + b) * 128 + row) * p.N;
-      for (int c0 = 0; c0 < p.N; c0 += 32) {
+      float* dst = p.ws + (((long long)blockIdx.x * 5 + b) * 128 + row) * p.N + n0;
+      const int ncols = min(64, p.N - n0);
+      for (int c0 = 0; c0 < ncols; c0 += 32) {
         uint32_t v[32];
         if (kb_end > kb_begin) {
           tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(b * 64 + c0), v);
@@ -123,7 +125,7 @@ wgrad_slab_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         }
 #pragma unroll
         for (int j = 0; j < 32; j += 4)
-          if (c0 + j < p.N)
+          if (c0 + j < ncols)
             *reinterpret_cast<float4*>(dst + c0 + j) = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]),
                                                                    __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
       }
@@ -143,8 +145,8 @@ int make_map_bf16(CUtensorMap* tm, const void* ptr, long long inner, long long r
 // mode 1: A = dy [P][64], B = x [P][Cin <= 64]     accumulator rows 0-63 = tap 2b+1, 64-127 = tap 2b
 // mode 2: A = x  [P][64], B = dy [P][Cout <= 64]   accumulator rows 0-63 = tap 2b,   64-127 = tap 2b+1 (transposed dW)
 int wgrad_slab_ok(int mode, int Cin, int Cout, int pw) {
-  if (mode == 1 && !(Cout == 64 && Cin <= 64 && Cin % 8 == 0)) return 0;
-  if (mode == 2 && !(Cin == 64 && Cout <= 64 && Cout % 8 == 0)) return 0;
+  if (mode == 1 && !(Cout == 64 && Cin <= 128 && Cin % 8 == 0)) return 0;
+  if (mode == 2 && !(Cin == 64 && Cout <= 128 && Cout % 8 == 0)) return 0;
   if (mode != 1 && mode != 2) return 0;
   return kWsBK + 2 * (pw + 1) <= 256;           // slab box height limit
 }
@@ -206,7 +208,7 @@ int wgrad_slab(int mode, const void* dy, const void* x, float* ws, long long P, 
     if (e != cudaSuccess) return (int)e;
     attr_smem = smem;
   }
-  wgrad_slab_kernel<<<splits, kWsThreads, smem, st>>>(ta, tb, p);
+  wgrad_slab_kernel<<<dim3((unsigned)splits, (unsigned)((cb + 63) / 64)), kWsThreads, smem, st>>>(ta, tb, p);
   AS_LAUNCH_CHECK();
   return AS_OK;
 }

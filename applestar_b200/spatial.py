@@ -105,8 +105,8 @@ class ConvNHWC(torch.autograd.Function):
             P = R * (H + 2) * (W + 2)
             tiles = taps * ((cout + 127) // 128) * max(1, (cin_p + 255) // 256)
             pmode = _lib.lib().as_conv_wgrad_pair_mode(cin_p, cout, taps, 2, W)
-            if pmode >= 10:
-                tiles = 1                       # one CTA per split walks all nine taps from a shared-memory slab
+            if pmode >= 10:                     # one CTA per split (and 64-column half) walks all nine taps from a slab
+                tiles = ((cin_p if pmode == 11 else cout) + 63) // 64
             elif pmode:
                 tiles = 5                       # two taps per 128-row tile (64-channel M side)
             want = max(1, min((P + 63) // 64, K.NUM_SMS // tiles))
