@@ -159,7 +159,8 @@ def gemm_flops_hook(records):
     orig = _lib.call
 
     def hooked(name, *a):
-        if name not in ('as_gemm_bf16', 'as_conv_nhwc_bf16', 'as_attn_fwd', 'as_attn_bwd_dq'):
+        if name not in ('as_gemm_bf16', 'as_conv_nhwc_bf16', 'as_conv_nhwc_bf16_add', 'as_conv_wgrad_nhwc_bf16', 'as_attn_fwd',
+                        'as_attn_bwd_dq'):
             return orig(name, *a)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda._sleep(120000)         # keep the stream busy while the host enqueues, so that e0 -> e1 is the kernel's
@@ -169,6 +170,12 @@ def gemm_flops_hook(records):
         if name == 'as_gemm_bf16':
             M, N, K, nb = a[5], a[6], a[7], a[13] * a[14]
             fl = 2.0 * M * N * K * nb
+        elif name == 'as_conv_nhwc_bf16_add':             # (x, w, y, bias, addend, R, H, W, Cin, Cout, taps, ...)
+            R, H, W, Cin, Cout, taps = a[5], a[6], a[7], a[8], a[9], a[10]
+            fl = 2.0 * R * (H + 2) * (W + 2) * Cin * Cout * taps
+        elif name == 'as_conv_wgrad_nhwc_bf16':           # (dy, x, dw, ws, R, H, W, Cin, Cout, taps, ...)
+            R, H, W, Cin, Cout, taps = a[4], a[5], a[6], a[7], a[8], a[9]
+            fl = 2.0 * R * (H + 2) * (W + 2) * Cin * Cout * taps
         elif name == 'as_attn_fwd':                       # Q K^T and P V: 2 x (2 N N D) per (row, head)
             R, N, H, D = a[4], a[5], a[6], a[7]
             fl = 4.0 * R * H * N * N * D
@@ -352,7 +359,7 @@ def run_ours(args):
                     'd2h_bytes_per_step': 4 * _lib.AS_LOSS_MAX_STATS},
             'gpu_launches': int(launches),
             'clocks': clocks,
-            'roofline': {'bound': 'tensor', 'kernel': 'tcgen05 kernels as::gemm_kernel + as::attn_kernel (all %d launches of one step)' % len(records),
+            'roofline': {'bound': 'tensor', 'kernel': 'tcgen05 kernels as::gemm_kernel + as::attn_kernel + as::wgrad_slab_kernel (all %d launches of one step)' % len(records),
                          'achieved': achieved, 'peak': tf_sus, 'unit': 'TFLOP/s', 'frac': achieved / tf_sus,
                          'peak_source': which + ' bf16_tflops_sustained', 'gemm_ms_per_step': g_ms,
                          'gemm_share_of_step': g_ms / (ms / args.steps), 'traffic': traffic, 'traffic_source': traffic_note},
