@@ -45,6 +45,7 @@ struct GemmDev {
   int wg_pair, pair_a[5][2], pair_b[5];
   // slab mode (multi-tap conv): 256-row steps, A slab = 2 TMA boxes of slab_box rows starting at row m0 - halo
   int slab, halo, slab_box, slab_bytes, slab_slots, b_slots, tpb, b_resident;
+  int half_k;        // slab mode: only K steps 0-1 of a block hold real input channels (Cin <= 32)
   int mc;            // slab ring mode on CTA pairs: each CTA loads half of every weight tile and multicasts it to both
   // epilogue
   void* C;
@@ -204,6 +205,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       constexpr uint32_t kDescHi = (1024u >> 4) | (1u << 14) | (2u << 29);
       constexpr uint32_t kDescLbo = (16u >> 4) << 16;
       const int nsl = p.slab_slots;
+      const bool half_k = p.half_k != 0;
       int bslot = 0; uint32_t bphase = 0;
       long long ci = 0;
       uint32_t it2 = 0;
@@ -245,14 +247,21 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               const uint32_t bj_lo = __shfl_sync(0xffffffffu, b_lo + (uint32_t)(j * (L::kBBytes >> 4)), 0);
               const uint32_t first = (cb > 0 || tap + j > 0) ? 1u : 0u;
               // consecutive MMAs alternate between the two accumulators (no back-to-back dependent accumulation)
-#pragma unroll
-              for (int k = 0; k < BK / 16; ++k) {
+              auto mma_k = [&](int k) {
 #pragma unroll
                 for (int sub = 0; sub < 2; ++sub) {
                   const uint64_t da = ((uint64_t)kDescHi << 32) | (a_lo + (uint32_t)(sub * (BM * 128 / 16) + k * 2));
                   const uint64_t db = ((uint64_t)kDescHi << 32) | (bj_lo + (uint32_t)(k * 2));
                   umma_bf16_lead(leader, d0 + (uint32_t)(sub * BN), da, db, idesc, k > 0 ? 1u : first);
                 }
+              };
+              // a layer with <= 32 input channels fills only half of the 64-wide K block (the rest is TMA zero fill):
+              // two fully unrolled variants, chosen by a warp-uniform flag, instead of a data-dependent trip count
+              if (half_k) {
+                mma_k(0); mma_k(1);
+              } else {
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k) mma_k(k);
               }
             }
             if (!p.b_resident) {
@@ -880,6 +889,7 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
         if (p.slab && p.n_blocks == 1 && BN >= 64 && (p.m_blocks + 1) / 2 >= 2 && getenv("AS_SLAB_MC")) p.mc = 1;
       }
       if (p.slab) { p.halo = halo; p.slab_box = box; p.slab_bytes = slab_bytes; a_box_rows = box; }
+      if (p.slab && g.K <= 32 && !getenv("AS_SLAB_NO_HALFK")) p.half_k = 1;
     }
   }
 
