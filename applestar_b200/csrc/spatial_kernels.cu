@@ -933,7 +933,7 @@ struct ScatterSrc {
   int idx_bytes, N;
 };
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 spatial_features_kernel(const SpatialPlanes sp, const float* __restrict__ scatter_map, const ScatterSrc sc,
                         __nv_bfloat16* __restrict__ out, int H, int W, int Cs) {
   __shared__ unsigned int effbits[kFeatBand * 256];      // one byte-sized bit set per pixel, W <= 1024/… (W*band <= 1024*… checked on host)
@@ -1009,67 +1009,60 @@ spatial_features_kernel(const SpatialPlanes sp, const float* __restrict__ scatte
     const int yy = band * kFeatBand + i / (W + 2);
     const int xx = i % (W + 2);
     const bool valid = i < n_band && yy < H + 2;
-    uint4 u[8];
+    // the pixel's eight 16-byte chunks are packed as bf16 bit patterns directly (one-hot = 0x3F80 or 0) and stored into
+    // the staging tile one by one: no 64-float image of the pixel is ever live (it cost 128 registers = 2 CTAs per SM)
+    uint4* srow = &stile[warp][lane * 8];
+    const int sw = lane & 7;
+    const bool inside = valid && !(yy == 0 || yy == H + 1 || xx == 0 || xx == W + 1);
+    if (!inside) {
 #pragma unroll
-    for (int q = 0; q < 8; ++q) u[q] = make_uint4(0, 0, 0, 0);
-    if (valid && !(yy == 0 || yy == H + 1 || xx == 0 || xx == W + 1)) {
+      for (int q = 0; q < 8; ++q) srow[q ^ sw] = make_uint4(0, 0, 0, 0);
+    } else {
       const int y = yy - 1, x = xx - 1;
       const long long pix = ((long long)r * H + y) * W + x;
-      float f[64];
+      const uint32_t kOne = 0x3F80u;
+      auto oh = [&](int v, int k) -> uint32_t { return v == k ? kOne : 0u; };
+      const int hgt = sp.plane[0][pix];
+      int vis = sp.plane[1][pix], crp = sp.plane[2][pix], pr = sp.plane[3][pix], alr = sp.plane[4][pix];
+      int pth = sp.plane[5][pix], bld = sp.plane[6][pix];
+      vis = vis > 3 ? 3 : vis; crp = crp > 1 ? 1 : crp; pr = pr > 4 ? 4 : pr; alr = alr > 1 ? 1 : alr;
+      pth = pth > 1 ? 1 : pth; bld = bld > 1 ? 1 : bld;
+      const int local = (y - y_lo) * W + x;
+      const unsigned int bits = (effbits[local >> 2] >> ((local & 3) * 8)) & 0xFFu;
+      const uint32_t hb = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn((float)hgt * (1.f / 256.f)));
+      srow[0 ^ sw] = make_uint4(hb | (oh(vis, 0) << 16), oh(vis, 1) | (oh(vis, 2) << 16), oh(vis, 3) | (oh(crp, 0) << 16),
+                                oh(crp, 1) | (oh(pr, 0) << 16));
+      srow[1 ^ sw] = make_uint4(oh(pr, 1) | (oh(pr, 2) << 16), oh(pr, 3) | (oh(pr, 4) << 16), oh(alr, 0) | (oh(alr, 1) << 16),
+                                oh(pth, 0) | (oh(pth, 1) << 16));
+      auto eb = [&](int e) -> uint32_t { return ((bits >> e) & 1u) ? kOne : 0u; };
+      srow[2 ^ sw] = make_uint4(oh(bld, 0) | (oh(bld, 1) << 16), eb(0) | (eb(1) << 16), eb(2) | (eb(3) << 16), eb(4) | (eb(5) << 16));
+      int m = 0;
+      uint32_t cell = 0;
+      if (!scatter_map) { cell = (uint32_t)local; m = cmap[cell]; }
 #pragma unroll
-      for (int c = 0; c < 64; ++c) f[c] = 0.f;
-      f[0] = (float)sp.plane[0][pix] * (1.f / 256.f);
-      {
-        int v;
-        v = sp.plane[1][pix]; v = v > 3 ? 3 : v;
+      for (int q = 0; q < 4; ++q) {                                // scatter channels 8 q .. 8 q + 7 -> chunk 3 + q
+        float f[8];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) f[1 + k] = (v == k) ? 1.f : 0.f;
-        v = sp.plane[2][pix]; v = v > 1 ? 1 : v;
-        f[5] = (v == 0) ? 1.f : 0.f; f[6] = (v == 1) ? 1.f : 0.f;
-        v = sp.plane[3][pix]; v = v > 4 ? 4 : v;
+        for (int c = 0; c < 8; ++c) f[c] = 0.f;
+        if (scatter_map) {
+          const float* smp = scatter_map + (long long)r * Cs * HW + (long long)y * W + x;
 #pragma unroll
-        for (int k = 0; k < 5; ++k) f[7 + k] = (v == k) ? 1.f : 0.f;
-        v = sp.plane[4][pix]; v = v > 1 ? 1 : v;
-        f[12] = (v == 0) ? 1.f : 0.f; f[13] = (v == 1) ? 1.f : 0.f;
-        v = sp.plane[5][pix]; v = v > 1 ? 1 : v;
-        f[14] = (v == 0) ? 1.f : 0.f; f[15] = (v == 1) ? 1.f : 0.f;
-        v = sp.plane[6][pix]; v = v > 1 ? 1 : v;
-        f[16] = (v == 0) ? 1.f : 0.f; f[17] = (v == 1) ? 1.f : 0.f;
-      }
-      {
-        const int local = (y - y_lo) * W + x;
-        const unsigned int bits = (effbits[local >> 2] >> ((local & 3) * 8)) & 0xFFu;
-#pragma unroll
-        for (int e = 0; e < 6; ++e) f[18 + e] = ((bits >> e) & 1u) ? 1.f : 0.f;
-      }
-      if (scatter_map) {
-        const float* sm = scatter_map + (long long)r * Cs * HW + (long long)y * W + x;
-#pragma unroll
-        for (int k = 0; k < 32; ++k) f[24 + k] = (k < Cs) ? __ldg(sm + (long long)k * HW) : 0.f;
-      } else {
-        const uint32_t cell = (uint32_t)((y - y_lo) * W + x);
-        const int m = cmap[cell];
-        if (m) {
-          for (int j = m - 1; j < n_b && (sorted[j] >> 9) == cell; ++j) {
-            const float4* src = reinterpret_cast<const float4*>(sc.emb + ((long long)r * sc.N + (sorted[j] & 511u)) * 32);
-#pragma unroll
-            for (int k4 = 0; k4 < 8; ++k4) {
-              const float4 v = __ldg(src + k4);
-              f[24 + 4 * k4] += v.x; f[24 + 4 * k4 + 1] += v.y; f[24 + 4 * k4 + 2] += v.z; f[24 + 4 * k4 + 3] += v.w;
-            }
+          for (int c = 0; c < 8; ++c) f[c] = (8 * q + c < Cs) ? __ldg(smp + (long long)(8 * q + c) * HW) : 0.f;
+        } else if (m) {
+          for (int j = m - 1; j < n_b && (sorted[j] >> 9) == cell; ++j) {       // ascending entity index: exact sum order
+            const float4* src = reinterpret_cast<const float4*>(sc.emb + ((long long)r * sc.N + (sorted[j] & 511u)) * 32) + 2 * q;
+            const float4 v0 = __ldg(src), v1 = __ldg(src + 1);
+            f[0] += v0.x; f[1] += v0.y; f[2] += v0.z; f[3] += v0.w;
+            f[4] += v1.x; f[5] += v1.y; f[6] += v1.z; f[7] += v1.w;
           }
         }
+        __nv_bfloat162 h0 = __floats2bfloat162_rn(f[0], f[1]), h1 = __floats2bfloat162_rn(f[2], f[3]);
+        __nv_bfloat162 h2 = __floats2bfloat162_rn(f[4], f[5]), h3 = __floats2bfloat162_rn(f[6], f[7]);
+        srow[(3 + q) ^ sw] = make_uint4(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1),
+                                        *reinterpret_cast<uint32_t*>(&h2), *reinterpret_cast<uint32_t*>(&h3));
       }
-#pragma unroll
-      for (int q = 0; q < 8; ++q) {
-        __nv_bfloat162 h0 = __floats2bfloat162_rn(f[8 * q], f[8 * q + 1]), h1 = __floats2bfloat162_rn(f[8 * q + 2], f[8 * q + 3]);
-        __nv_bfloat162 h2 = __floats2bfloat162_rn(f[8 * q + 4], f[8 * q + 5]), h3 = __floats2bfloat162_rn(f[8 * q + 6], f[8 * q + 7]);
-        u[q].x = *reinterpret_cast<uint32_t*>(&h0); u[q].y = *reinterpret_cast<uint32_t*>(&h1);
-        u[q].z = *reinterpret_cast<uint32_t*>(&h2); u[q].w = *reinterpret_cast<uint32_t*>(&h3);
-      }
+      srow[7 ^ sw] = make_uint4(0, 0, 0, 0);
     }
-#pragma unroll
-    for (int q = 0; q < 8; ++q) stile[warp][lane * 8 + (q ^ (lane & 7))] = u[q];
     __syncwarp();
     // first pixel of this warp in the band, and how many of its 32 pixels exist
     const int iw = i0 + warp * 32;
