@@ -288,7 +288,7 @@ constexpr int kUp2Ty = 4;     // input rows per CTA in the backward
 // touch each input row (vertical taps) for every OUTPUT column into fp32 V[ty][ox][c]; phase 2 combines four columns
 // of V per input pixel.  Each output gradient is read ~1.25 times (rows shared by neighbouring tiles) instead of
 // nine times from L1/L2 in a per-pixel gather.
-__global__ void __launch_bounds__(512)
+__global__ void __launch_bounds__(512, 2)
 up2_bwd_kernel(const __nv_bfloat16* __restrict__ dout, __nv_bfloat16* __restrict__ din, int H, int W, int C, int nty,
                const Dec3 d1, const Dec3 d2) {
   extern __shared__ __align__(16) float sV[];        // [kUp2Ty][2W][C + 4]  (+4: column stride off the bank period)
@@ -300,7 +300,7 @@ up2_bwd_kernel(const __nv_bfloat16* __restrict__ dout, __nv_bfloat16* __restrict
   const int n1 = kUp2Ty * W2 * C8;
   // phase 1 in batches of kB items per thread: all 4 * kB loads are issued before any is consumed (the kernel is
   // bound by the number of bytes in flight, not by arithmetic)
-  constexpr int kB = 5;
+  constexpr int kB = 2;
   for (int i0 = threadIdx.x; i0 < n1; i0 += kB * blockDim.x) {
     uint4 v[kB][4];
     float wy[kB][4];
@@ -317,7 +317,7 @@ up2_bwd_kernel(const __nv_bfloat16* __restrict__ dout, __nv_bfloat16* __restrict
         const int y = y0 + ty;
         if (y < H) {
           up2_tw(y, H, wy[u]);
-          so[u] = (ty * W2 + ox) * Cp + c8 * 8;
+          so[u] = (ty * W2 + ox) * Cp + c8 * 4;
 #pragma unroll
           for (int k = 0; k < 4; ++k)
             if (wy[u][k] != 0.f)                     // also excludes the rows outside the image
@@ -338,9 +338,10 @@ up2_bwd_kernel(const __nv_bfloat16* __restrict__ dout, __nv_bfloat16* __restrict
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[j] += wy[u][k] * bf2f(t.h[j]);
       }
-      float4* dst = reinterpret_cast<float4*>(sV + so[u]);
-      dst[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
-      dst[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+      // channels 8 c8 .. +3 at column 4 c8, channels +4 .. +7 at column C / 2 + 4 c8: consecutive threads are 16 bytes
+      // apart in both stores (a 32-byte stride made every float4 store a 2-way bank conflict)
+      *reinterpret_cast<float4*>(sV + so[u]) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+      *reinterpret_cast<float4*>(sV + so[u] + C / 2) = make_float4(acc[4], acc[5], acc[6], acc[7]);
     }
   }
   __syncthreads();
@@ -358,8 +359,8 @@ up2_bwd_kernel(const __nv_bfloat16* __restrict__ dout, __nv_bfloat16* __restrict
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       if (wx[k] == 0.f) continue;
-      const float4* src = reinterpret_cast<const float4*>(sV + ((long long)ty * W2 + 2 * x - 1 + k) * Cp + c8 * 8);
-      const float4 a = src[0], b = src[1];
+      const float* src = sV + ((long long)ty * W2 + 2 * x - 1 + k) * Cp + c8 * 4;
+      const float4 a = *reinterpret_cast<const float4*>(src), b = *reinterpret_cast<const float4*>(src + C / 2);
       acc[0] += wx[k] * a.x; acc[1] += wx[k] * a.y; acc[2] += wx[k] * a.z; acc[3] += wx[k] * a.w;
       acc[4] += wx[k] * b.x; acc[5] += wx[k] * b.y; acc[6] += wx[k] * b.z; acc[7] += wx[k] * b.w;
     }
