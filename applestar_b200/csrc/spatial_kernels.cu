@@ -605,43 +605,67 @@ conv_c32_1_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ 
   __shared__ __align__(16) float sw[288];
   for (int i = threadIdx.x; i < 288; i += blockDim.x) sw[i] = w[i] * inv_temp;
   __syncthreads();
+  // Two pixels per thread (p and p + 256 of a 512-pixel group): every 16-byte weight read from shared memory feeds
+  // both, which halves the traffic of the L1 / shared-memory pipe (82 % busy with one pixel per thread).
   const long long total = R * (long long)(H + 2) * (W + 2);
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += stride) {
-    int xx, yy, ri, unused;
-    dec3((uint32_t)p, dec, xx, yy, ri, unused);
-    const long long r = ri;
-    float acc[32];
+  const long long stride = (long long)gridDim.x * 512;
+  for (long long base = (long long)blockIdx.x * 512 + threadIdx.x; base < total; base += stride) {
+    float acc[2][32];
+    float g[2][9];
+    long long pp[2];
 #pragma unroll
-    for (int c = 0; c < 32; ++c) acc[c] = 0.f;
-    if (xx >= 1 && xx <= W && yy >= 1 && yy <= H) {
+    for (int u = 0; u < 2; ++u) {
+      const long long p = base + u * 256;
+      pp[u] = p;
 #pragma unroll
-      for (int ky = 0; ky < 3; ++ky) {
-        const int oy = yy - ky;
+      for (int c = 0; c < 32; ++c) acc[u][c] = 0.f;
 #pragma unroll
-        for (int kx = 0; kx < 3; ++kx) {
-          const int ox = xx - kx;
-          if (oy >= 0 && oy < H && ox >= 0 && ox < W) {
-            const float g = __ldg(dy + (r * H + oy) * (long long)W + ox);
-            const float* wt = sw + (ky * 3 + kx) * 32;
+      for (int t = 0; t < 9; ++t) g[u][t] = 0.f;
+      if (p < total) {
+        int xx, yy, ri, unused;
+        dec3((uint32_t)p, dec, xx, yy, ri, unused);
+        const long long r = ri;
+        if (xx >= 1 && xx <= W && yy >= 1 && yy <= H) {
 #pragma unroll
-            for (int c4 = 0; c4 < 8; ++c4) {
-              const float4 wv = *reinterpret_cast<const float4*>(wt + c4 * 4);
-              acc[c4 * 4] += g * wv.x; acc[c4 * 4 + 1] += g * wv.y; acc[c4 * 4 + 2] += g * wv.z; acc[c4 * 4 + 3] += g * wv.w;
+          for (int ky = 0; ky < 3; ++ky) {
+            const int oy = yy - ky;
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) {
+              const int ox = xx - kx;
+              if (oy >= 0 && oy < H && ox >= 0 && ox < W) g[u][ky * 3 + kx] = __ldg(dy + (r * H + oy) * (long long)W + ox);
             }
           }
         }
       }
     }
-    uint4* dst = reinterpret_cast<uint4*>(din + p * 32);
 #pragma unroll
-    for (int c4 = 0; c4 < 4; ++c4) {
-      __nv_bfloat162 h0 = __floats2bfloat162_rn(acc[c4 * 8], acc[c4 * 8 + 1]), h1 = __floats2bfloat162_rn(acc[c4 * 8 + 2], acc[c4 * 8 + 3]);
-      __nv_bfloat162 h2 = __floats2bfloat162_rn(acc[c4 * 8 + 4], acc[c4 * 8 + 5]), h3 = __floats2bfloat162_rn(acc[c4 * 8 + 6], acc[c4 * 8 + 7]);
-      uint4 u;
-      u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
-      u.z = *reinterpret_cast<uint32_t*>(&h2); u.w = *reinterpret_cast<uint32_t*>(&h3);
-      dst[c4] = u;
+    for (int t = 0; t < 9; ++t) {
+      const float* wt = sw + t * 32;
+#pragma unroll
+      for (int c4 = 0; c4 < 8; ++c4) {
+        const float4 wv = *reinterpret_cast<const float4*>(wt + c4 * 4);
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          acc[u][c4 * 4] = fmaf(g[u][t], wv.x, acc[u][c4 * 4]);
+          acc[u][c4 * 4 + 1] = fmaf(g[u][t], wv.y, acc[u][c4 * 4 + 1]);
+          acc[u][c4 * 4 + 2] = fmaf(g[u][t], wv.z, acc[u][c4 * 4 + 2]);
+          acc[u][c4 * 4 + 3] = fmaf(g[u][t], wv.w, acc[u][c4 * 4 + 3]);
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (pp[u] >= total) continue;
+      uint4* dst = reinterpret_cast<uint4*>(din + pp[u] * 32);
+#pragma unroll
+      for (int c4 = 0; c4 < 4; ++c4) {
+        __nv_bfloat162 h0 = __floats2bfloat162_rn(acc[u][c4 * 8], acc[u][c4 * 8 + 1]), h1 = __floats2bfloat162_rn(acc[u][c4 * 8 + 2], acc[u][c4 * 8 + 3]);
+        __nv_bfloat162 h2 = __floats2bfloat162_rn(acc[u][c4 * 8 + 4], acc[u][c4 * 8 + 5]), h3 = __floats2bfloat162_rn(acc[u][c4 * 8 + 6], acc[u][c4 * 8 + 7]);
+        uint4 q;
+        q.x = *reinterpret_cast<uint32_t*>(&h0); q.y = *reinterpret_cast<uint32_t*>(&h1);
+        q.z = *reinterpret_cast<uint32_t*>(&h2); q.w = *reinterpret_cast<uint32_t*>(&h3);
+        dst[c4] = q;
+      }
     }
   }
 }
@@ -752,7 +776,7 @@ int conv_c32_1_bwd(const float* dy, const void* in, const float* w, void* din, f
   if (R <= 0) return AS_OK;
   if (!dy || !in || !w || !din || !dw || !scratch) return AS_EINVAL;
   if (R * (long long)(H + 2) * (W + 2) >= (1LL << 31)) return AS_ESIZE;
-  conv_c32_1_dgrad_kernel<<<ew_grid(R * (long long)(H + 2) * (W + 2), 1), 256, 0, st>>>(dy, w, (__nv_bfloat16*)din, R, H, W, inv_temp,
+  conv_c32_1_dgrad_kernel<<<ew_grid((R * (long long)(H + 2) * (W + 2) + 1) / 2, 1), 256, 0, st>>>(dy, w, (__nv_bfloat16*)din, R, H, W, inv_temp,
                                                                                             make_dec3(W + 2, H + 2, 1u << 30));
   AS_LAUNCH_CHECK();
   const int nseg = (H + kC32Seg - 1) / kC32Seg;
