@@ -46,10 +46,15 @@ def weights_changed():
 
 def weight_bf16(w):
     """bf16 copy of a weight matrix [N, K] (K padded to 8).  Parameters that live in a FlatParams buffer carry a
-    view of the flat bf16 shadow the fused Adam kernel keeps fresh; otherwise the copy is cached on the Parameter
-    object itself (never keyed by address: freed addresses get reused by other models)."""
+    view of the flat bf16 shadow the fused Adam kernel keeps fresh; the view is re-cast here whenever the parameter
+    was changed behind its back (torch optimizers, `load_state_dict`, `copy_`: anything that bumps `_version`).
+    Otherwise the copy is cached on the Parameter object itself (never keyed by address: freed addresses get reused
+    by other models)."""
     sh = getattr(w, '_as_shadow', None)
     if sh is not None and w.shape[-1] % 8 == 0 and w.dim() == 2:
+        if w._version != getattr(w, '_as_shadow_ver', None):
+            _lib.call('as_cast_f32_bf16', w.data_ptr(), sh.data_ptr(), w.numel(), _lib.stream_ptr())
+            w._as_shadow_ver = w._version
         return sh
     tag = (_SHADOW_GEN[0], w._version, w.data_ptr())
     hit = getattr(w, '_as_w16', None)

@@ -72,6 +72,19 @@ class FlatParams:
                 rows.append((src + 4 * c if src else 0, o + c, min(self.CHUNK, n - c)))
         if not rows:
             return
+        if not self.grad.is_cuda:                                   # host tensors (gloo tests): plain copies
+            pos = 0
+            for i in (range(len(self.params)) if idx is None else idx):
+                p, o, n = self.params[i], self.offsets[i], self.params[i].numel()
+                if p.grad is not None and p.grad.data_ptr() == self.grad.data_ptr() + 4 * o:
+                    continue
+                g = keep[pos]
+                pos += 1
+                if g is None:
+                    self.grad[o:o + n].zero_()
+                else:
+                    self.grad[o:o + n].copy_(g.reshape(-1))
+            return
         host = torch.tensor(rows, dtype=torch.int64).pin_memory()
         table = host.to(self.grad.device, non_blocking=True)
         if torch.cuda.is_current_stream_capturing():                # the captured copy re-reads `host` at every replay
@@ -86,8 +99,13 @@ class FlatParams:
                 p.grad = self.grad[o:o + p.numel()].view(p.shape)
 
     def refresh_shadow(self):
+        """Re-cast the whole bf16 shadow from the fp32 master buffer and tag every parameter as in sync
+        (kernels.weight_bf16 re-casts a single parameter whose `_version` moved since: torch optimizers,
+        `load_state_dict`)."""
         if self.shadow is not None:
             _lib.call('as_cast_f32_bf16', self.flat.data_ptr(), self.shadow.data_ptr(), self.numel, _lib.stream_ptr())
+        for p in self.params:
+            p._as_shadow_ver = p._version
         K.weights_changed()
 
     def zero_grad(self):
@@ -131,11 +149,21 @@ class DistModule(nn.Module):
             for i in idx:
                 self._bucket_of[i] = b
         self._comm_stream = torch.cuda.Stream() if self.flat.flat.is_cuda else None
+        self._grad_events = {}          # parameter index -> event recorded on the stream that produced its gradient
+        self.local_only = False         # True: skip the collectives (graph warm-up of one rank, see LearnerStep._capture)
         self._avg = dist.ReduceOp.AVG if (self.world > 1 and dist.get_backend() == 'nccl') else None
         self.broadcast_params()
         if self.world > 1:
             for i, p in enumerate(self.flat.params):
                 p.register_post_accumulate_grad_hook(self._make_hook(i))
+            if self._comm_stream is not None:
+                # one eager all-reduce per bucket shape (the gradient buffer is still zero): NCCL sets up the channels
+                # of every algorithm / protocol it will use, so that a later CUDA-graph capture only records kernels
+                self._comm_stream.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(self._comm_stream):
+                    for start, end, _ in self._buckets:
+                        dist.all_reduce(self.flat.grad[start:end], op=self._avg or dist.ReduceOp.SUM)
+                torch.cuda.current_stream().wait_stream(self._comm_stream)
         self.prepare_backward()
 
     # -- collectives ------------------------------------------------------------------------------
@@ -146,11 +174,22 @@ class DistModule(nn.Module):
             self.flat.refresh_shadow()
 
     def prepare_backward(self):
+        """Arm the per-bucket counters for the next backward pass.  `sync_gradients` re-arms them itself, so callers
+        that follow the reference's `zero_grad / backward / sync_gradients` sequence never need to call this."""
         self._pending = [len(idx) for _, _, idx in self._buckets]
         self._works = []
+        self._grad_events = {}
 
     def _make_hook(self, i):
         def hook(_param):
+            if self.local_only:
+                return
+            if self._comm_stream is not None:
+                # gradients of one bucket are produced on different streams (value towers / scalar encoder run on the
+                # side stream): remember where this one was written so that the bucket launch can wait for it
+                ev = torch.cuda.Event()
+                ev.record()
+                self._grad_events[i] = ev
             b = self._bucket_of[i]
             self._pending[b] -= 1
             if self._pending[b] == 0:
@@ -159,8 +198,13 @@ class DistModule(nn.Module):
 
     def _launch(self, b):
         start, end, idx = self._buckets[b]
-        if self.flat.pack_mode:
-            self.flat.pack(idx)
+        if self._comm_stream is not None:
+            cur = torch.cuda.current_stream()
+            for i in idx:
+                ev = self._grad_events.get(i)
+                if ev is not None:
+                    cur.wait_event(ev)
+        self.flat.pack(idx)                 # gathers whatever is not already a view of its slot (p.grad = None -> zeros)
         chunk = self.flat.grad[start:end]
         if self._comm_stream is not None:
             ev = torch.cuda.Event()
@@ -174,10 +218,9 @@ class DistModule(nn.Module):
 
     def sync_gradients(self):
         """Average gradients across ranks.  With hooks active this only waits for the in-flight bucket reductions."""
-        if self.world <= 1:
-            if self.flat.pack_mode:
-                self.flat.pack()
-                self.flat.attach_views()
+        if self.world <= 1 or self.local_only:
+            self.flat.pack()
+            self.flat.attach_views()
             return
         for b, n in enumerate(self._pending):
             if n > 0:                       # parameters that received no gradient this step: reduce what is there
@@ -187,9 +230,8 @@ class DistModule(nn.Module):
             work.wait()
             if self._avg is None:
                 chunk.div_(self.world)
-        self._works = []
-        if self.flat.pack_mode:
-            self.flat.attach_views()
+        self.flat.attach_views()            # callers of the reference API read p.grad after sync_gradients
+        self.prepare_backward()             # re-arm for the next zero_grad / backward / sync_gradients round
 
 
 class FusedAdam:
@@ -216,6 +258,24 @@ class FusedAdam:
                   self.grad_norm.data_ptr(), _lib.stream_ptr())
         _lib.LAUNCHES += 1
         K.weights_changed()
+
+    def state_dict(self):
+        """Adam moments and the device-side step counter (the reference checkpoints `optimizer.state_dict()`,
+        ctools/torch_utils/checkpoint_helper.py:85-141).  Note: a parameter that received no gradient in a step is
+        treated as having a zero gradient (its second moment decays), unlike torch.optim.Adam, which skips it."""
+        return {'m': self.m.clone(), 'v': self.v.clone(), 't': int(self.t_dev.item()), 'names': list(self.flat.names),
+                'offsets': list(self.flat.offsets), 'lr': self.lr, 'betas': tuple(self.betas), 'eps': self.eps,
+                'weight_decay': self.wd, 'max_norm': self.max_norm}
+
+    def load_state_dict(self, state):
+        if list(state['names']) != list(self.flat.names) or list(state['offsets']) != list(self.flat.offsets):
+            raise ValueError('optimizer state belongs to a different parameter layout')
+        self.m.copy_(state['m'])
+        self.v.copy_(state['v'])
+        self.t = int(state['t'])
+        self.t_dev.fill_(self.t)
+        self.lr, self.betas, self.eps = state['lr'], tuple(state['betas']), state['eps']
+        self.wd, self.max_norm = state['weight_decay'], state['max_norm']
 
 
 def _tree_copy_(dst, src):
@@ -269,26 +329,54 @@ class LearnerStep:
         return info
 
     # -- graph ----------------------------------------------------------------------------------------
-    @staticmethod
-    def _key(data):
+    SU_STEPS = (1, 2, 4, 6, 8, 12, 16, 24, 32, 48, 64)    # captured loop lengths of the selected-units head
+
+    def _key(self, data):
+        """Graph key of a batch, or None (eager).  The selected-units loop length is rounded up to one of SU_STEPS
+        (any length >= the batch maximum gives the same valid logits) and, when several ranks train together, the
+        (any length >= the batch maximum gives the same valid logits).  Ranks may pick different graphs for the same
+        step: every graph holds the same sequence of bucket all-reduces, and a rank that has to capture first
+        issues no collective while doing so (`_capture`), so the ranks' collectives always pair up.
+        Loss settings that are baked into captured launch arguments are part of the key."""
         su = data.get('selected_units_max')
-        return None if su is None else (int(su), int(data['batch_size']), int(data['unroll_len']),
-                                        tuple(data['entity_info']['x'].shape))
+        if su is None:
+            return None
+        su = int(su)
+        su = next((s for s in self.SU_STEPS if s >= su), self.SU_STEPS[-1])
+        loss = self.loss
+        loss_tag = (bool(getattr(loss, 'only_update_value', False)), bool(getattr(self.model, 'only_update_baseline', False)),
+                    repr(sorted((k, repr(v)) for k, v in getattr(loss, 'cfg', {}).items())))
+        return (su, int(data['batch_size']), int(data['unroll_len']), tuple(data['entity_info']['x'].shape), loss_tag)
 
     def _capture(self, data, key):
         dev = self.flat.flat.device
         static = _tree_to(data, dev)
+        static['selected_units_max'] = key[0]
+        # warm-up (allocator, lazy initialisation) must leave no trace: the weights, the Adam moments and the step
+        # counter are put back afterwards, so that the batch that triggers a capture gets exactly one optimizer
+        # update like every other batch; and it runs without collectives (a peer may be replaying an existing graph
+        # at the same time; NCCL's channels were set up by DistModule.__init__)
+        opt = self.optimizer
+        self.dist_model.local_only = True
+        keep = [t.clone() for t in (self.flat.flat, opt.m, opt.v, opt.t_dev)]
+        keep_t = opt.t
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(side):                        # warm-up on a side stream (allocator, lazy inits)
+        with torch.cuda.stream(side):                        # warm-up on a side stream
             for _ in range(2):
                 self._run(static, defer_checks=True)
         torch.cuda.current_stream().wait_stream(side)
+        self.dist_model.local_only = False
+        for dst, src in zip((self.flat.flat, opt.m, opt.v, opt.t_dev), keep):
+            dst.copy_(src)
+        opt.t = keep_t
+        self.flat.refresh_shadow()
         torch.cuda.synchronize()
         graph = torch.cuda.CUDAGraph()
         n0 = _lib.LAUNCHES
         with torch.cuda.graph(graph, pool=self._pool):
             info = self._run(static, defer_checks=True)
+        opt.t = keep_t                                       # capturing does not execute: nothing was stepped
         self.launches_per_step = _lib.LAUNCHES - n0
         if self._pool is None:
             self._pool = graph.pool()
@@ -302,28 +390,21 @@ class LearnerStep:
             return self._run(data)
         entry = self._graphs.get(key)
         if entry is None:
-            try:
-                entry = self._capture(data, key)
-            except Exception as exc:                          # e.g. a collective that cannot be captured
-                import traceback
-                import warnings
-                warnings.warn('CUDA-graph capture of the learner step failed (%r); running eagerly\n%s'
-                              % (exc, ''.join(traceback.format_exc().splitlines(True)[-14:])))
-                torch.cuda.synchronize()
-                self.use_graph = False
-                return self._run(data)
+            entry = self._capture(data, key)
         graph, static, info = entry
         if data is not static:
             _tree_copy_(static, data)
         graph.replay()
+        self.optimizer.t += 1
+        K.weights_changed()                                  # the replay moved the weights behind Python's back
         from .rl_loss import LossInfo
         return LossInfo(self.loss, list(self.model.value_networks.keys()), info['total_loss'], info.stats_tensor())
 
     def static_inputs(self, data):
         """The graph's own input buffers for `data`'s shape (captures on first use): callers that fill them in place
         (e.g. with H2D copies from pinned memory) skip one device-to-device copy per step."""
-        key = self._key(data)
-        if key is None or not self.use_graph:
+        key = self._key(data) if self.use_graph else None
+        if key is None:
             return None
         entry = self._graphs.get(key) or self._capture(data, key)
         return entry[1]

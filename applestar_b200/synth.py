@@ -95,12 +95,13 @@ def gen_observations(rows, n_entity=C.MAX_ENTITY_NUM, seed=1234, entity_num_rang
 
 
 def gen_trajectories(unroll_len, batch_size, n_entity=C.MAX_ENTITY_NUM, seed=1234,
-                     fields=('winloss', 'build_order', 'built_unit', 'battle')):
+                     fields=('winloss', 'build_order', 'built_unit', 'battle'), special=False):
     """Learner batch: `(T+1)*B` flattened observations (row = t*B + b) + the `[T,B,...]` learner-only
-    tensors, as `rl_dataloader.collate_fn` would deliver them (padded to `n_entity`)."""
+    tensors, as `rl_dataloader.collate_fn` would deliver them (padded to `n_entity`).  `special` puts the
+    all-entities-on-one-cell observation in row 0 and the `entity_num == 1` observation in row 1."""
     T, B, N = unroll_len, batch_size, n_entity
     S = C.MAX_SELECTED_UNITS_NUM
-    data = gen_observations((T + 1) * B, N, seed, hidden=True)
+    data = gen_observations((T + 1) * B, N, seed, hidden=True, special=special)
     g = _gen(seed + 7919)
     entity_num = data['entity_num'][:T * B].view(T, B)
 
@@ -109,6 +110,7 @@ def gen_trajectories(unroll_len, batch_size, n_entity=C.MAX_ENTITY_NUM, seed=123
            for k in ('queued', 'selected_units', 'target_unit', 'target_location')}
     actions_mask = {k: has[k][action_type].long() for k in has}
     sun = _randint(g, 2, 13, (T, B)) * actions_mask['selected_units']         # {0} U [2,12]
+    sun = torch.minimum(sun, entity_num + 1)                                  # distinct valid units + the end flag
     # distinct random unit ids < entity_num, last valid slot = entity_num (the end flag)
     selected_units = torch.zeros((T, B, S), dtype=torch.int64)
     scores = torch.rand((T, B, N), generator=g)

@@ -7,6 +7,8 @@ The fixtures pin oracle/restate.py (and through it the CUDA path) to the execute
   infer_small.pt         compute_logp_action under fixed Gumbel noise, B=3 N=512 (incl. collision / 1-entity obs)
   learner_n128.pt        the learner case at N=128 entities, one baseline (the size from which the fused tcgen05 attention
                          forward / backward kernels run); written by `python oracle/make_golden.py n128` alone
+  learner_n512.pt        the learner case at the benchmarked N=512 (T=4, B=2, special observations) with ~300 reference
+                         gradient tensors and the reference's own bf16-autocast gradient error; `... make_golden.py n512`
   scatter_small.pt       scatter_connection on a heavy-collision case
 Inputs and weights are NOT stored: tests regenerate them from the same seeds (applestar_b200/synth.py).
 """
@@ -113,6 +115,133 @@ def learner_case(T, B, N, baselines, seed):
     return res
 
 
+BIG_GRADS = [   # tensors above FULL_GRAD_NUMEL whose reference gradient is kept (strided sample when above BIG_GRAD_CAP)
+    'encoder.entity_encoder.transformer.embedding.0.weight',
+    'encoder.entity_encoder.transformer.layers.0.attention.attention_pre.0.weight',
+    'encoder.entity_encoder.transformer.layers.1.attention.project.0.weight',
+    'encoder.entity_encoder.transformer.layers.2.mlp.0.0.weight',
+    'encoder.entity_encoder.transformer.layers.2.mlp.1.0.weight',
+    'encoder.entity_encoder.entity_fc.0.weight', 'encoder.entity_encoder.embed_fc.0.weight',
+    'encoder.spatial_encoder.downsample.0.0.weight', 'encoder.spatial_encoder.downsample.1.0.weight',
+    'encoder.spatial_encoder.downsample.2.0.weight', 'encoder.spatial_encoder.res.0.conv1.0.weight',
+    'encoder.spatial_encoder.res.3.conv2.0.weight', 'encoder.spatial_encoder.fc.0.weight',
+    'encoder.scalar_encoder.encode_modules.unit_counts_bow.0.weight',
+    'encoder.scalar_encoder.encode_modules.beginning_order.transformer.embedding.0.weight',
+    'core_lstm.layers.0.cell.weight_ih', 'core_lstm.layers.0.cell.weight_hh', 'core_lstm.layers.1.cell.weight_ih',
+    'core_lstm.layers.2.cell.weight_hh',
+    'policy.action_type_head.project.0.weight', 'policy.action_type_head.action_fc.layer2.0.weight',
+    'policy.action_type_head.action_map_fc1.0.weight', 'policy.action_type_head.glu1.layer2.0.weight',
+    'policy.action_type_head.glu2.layer1.0.weight',
+    'policy.delay_head.fc1.0.weight', 'policy.delay_head.fc3.0.weight', 'policy.delay_head.embed_fc2.0.weight',
+    'policy.queued_head.fc1.0.weight', 'policy.queued_head.embed_fc2.0.weight',
+    'policy.selected_units_head.query_fc1.0.weight', 'policy.selected_units_head.embed_fc2.0.weight',
+    'policy.target_unit_head.query_fc1.0.weight',
+    'policy.location_head.project_embed.0.weight', 'policy.location_head.conv1.0.weight',
+    'policy.location_head.res.0.conv1.0.weight', 'policy.location_head.res.1.GateWeightG.0.0.weight',
+    'policy.location_head.res.3.conv2.0.weight', 'policy.location_head.res.3.GateWeightG.3.0.weight',
+    'policy.location_head.upsample.0.0.weight', 'policy.location_head.upsample.1.0.weight',
+    'value_networks.winloss.project.0.weight', 'value_networks.winloss.res.0.fc1.0.weight',
+    'value_networks.winloss.res.15.fc2.0.weight']
+FULL_GRAD_NUMEL = 8192      # every trainable tensor up to this size keeps its full reference gradient
+BIG_GRAD_CAP = 65536
+
+
+def grad_sample_index(numel):
+    """Flat indices of the stored gradient sample: everything up to BIG_GRAD_CAP elements, else a fixed odd stride."""
+    if numel <= BIG_GRAD_CAP:
+        return None
+    stride = (numel // BIG_GRAD_CAP) | 1
+    return torch.arange(0, numel, stride)[:BIG_GRAD_CAP]
+
+
+def _kept_grads(model, everything=False):
+    out = {}
+    for k, p in model.named_parameters():
+        if not p.requires_grad or (not everything and p.numel() > FULL_GRAD_NUMEL and k not in BIG_GRADS):
+            continue
+        if everything:
+            out[k] = (p.grad if p.grad is not None else torch.zeros_like(p)).detach().float().reshape(-1).clone()
+            continue
+        g = (p.grad if p.grad is not None else torch.zeros_like(p)).detach().float().reshape(-1)
+        idx = grad_sample_index(g.numel())
+        out[k] = (g if idx is None else g[idx]).clone()
+    return out
+
+
+def learner_n512_case(T=4, B=2, N=512, seed=5120):
+    """The benchmarked entity count (N = 512: four key blocks in the fused attention, 512-key scatter sort, cluster LSTM)
+    with the all-on-one-cell and entity_num == 1 observations: reference fp32 logits / values / 63 loss scalars /
+    gradients of ~300 tensors (every tensor <= 8192 elements in full + BIG_GRADS), the fp64 forward, and the
+    reference's OWN bf16-autocast error for every logit head (max-abs, RMS) and every kept gradient (relative L2,
+    cosine) as the tolerance budget of a bf16 implementation."""
+    from distar.agent.default.rl_training.rl_loss import ReinforcementLoss
+    baselines = ['winloss']
+    model, cfg, _ = build_ref_model(baselines)
+    data = synth.gen_trajectories(T, B, N, seed, special=True)
+    loss_fn = ReinforcementLoss(cfg.learner, 'MP0')
+    out = model.rl_learner_forward(**synth.tree_map(lambda t: t.clone(), data))
+    logits = {k: v.detach().clone() for k, v in out['target_logit'].items()}
+    values = {k: v.detach().clone() for k, v in out['value'].items()}
+    info = loss_fn.compute_loss(out)
+    model.zero_grad()
+    info['total_loss'].backward()
+    grads = _kept_grads(model)
+    all_grads = _kept_grads(model, everything=True)
+    res = {'T': T, 'B': B, 'N': N, 'seed': seed, 'baselines': baselines, 'special': True,
+           'logit': logits, 'value': values,
+           'loss_info': {k: (float(v) if not isinstance(v, torch.Tensor) else float(v.detach())) for k, v in info.items()},
+           'grad_summary': grad_summary(model), 'grads': grads,
+           'grad_rule': {'full_numel': FULL_GRAD_NUMEL, 'cap': BIG_GRAD_CAP, 'big': list(BIG_GRADS)}}
+    old_float = torch.Tensor.float
+    torch.set_default_dtype(torch.float64)
+    torch.Tensor.float = lambda self, *a, **k: self.double()
+    try:
+        m64 = model.double()
+        d64 = synth.tree_map(lambda t: t.double() if t.dtype == torch.float32 else t.clone(), data)
+        with torch.no_grad():
+            o64 = m64.rl_learner_forward(**d64)
+        res['logit64'] = {k: v.clone() for k, v in o64['target_logit'].items()}
+        res['value64'] = {k: v.clone() for k, v in o64['value'].items()}
+    finally:
+        torch.Tensor.float = old_float
+        torch.set_default_dtype(torch.float32)
+    model = model.float()
+    import distar.agent.default.model.encoder as enc_mod
+    orig_sc = enc_mod.scatter_connection
+    enc_mod.scatter_connection = lambda shape, pe, loc, dim, typ='add': orig_sc(shape, pe.float(), loc, dim, typ)
+    try:
+        model.zero_grad()
+        with torch.autocast('cpu', dtype=torch.bfloat16):
+            ob = model.rl_learner_forward(**synth.tree_map(lambda t: t.clone(), data))
+            ob = dict(ob)
+            ob['target_logit'] = {k: v.float() for k, v in ob['target_logit'].items()}
+            ob['value'] = {k: v.float() for k, v in ob['value'].items()}
+        ib = loss_fn.compute_loss(ob)
+        ib['total_loss'].backward()
+        err = {}
+        for k in logits:
+            valid = res['logit64'][k] > -1e8
+            d = (ob['target_logit'][k].detach().double() - res['logit64'][k])[valid]
+            err[k] = torch.tensor([d.abs().max().item(), d.pow(2).mean().sqrt().item()])
+        for k in values:
+            d = ob['value'][k].detach().double() - res['value64'][k]
+            err['value/' + k] = torch.tensor([d.abs().max().item(), d.pow(2).mean().sqrt().item()])
+        res['bf16_autocast_err'] = err
+        gb = _kept_grads(model, everything=True)
+        gerr = {}                           # every trainable tensor: [relative L2, cosine] of autocast-bf16 vs fp32
+        for k, g in all_grads.items():
+            a, b = gb[k].double(), g.double()
+            rel = ((a - b).norm() / b.norm().clamp(min=1e-30)).item()
+            cos = (torch.dot(a, b) / (a.norm() * b.norm()).clamp(min=1e-30)).item()
+            gerr[k] = torch.tensor([rel, cos])
+        res['bf16_autocast_grad_err'] = gerr
+        res['bf16_autocast_loss_info'] = {k: (float(v) if not isinstance(v, torch.Tensor) else float(v.detach()))
+                                          for k, v in ib.items()}
+    finally:
+        enc_mod.scatter_connection = orig_sc
+    return res
+
+
 def infer_case(B, N, seed):
     model, cfg, _ = build_ref_model(['winloss'])
     model.eval()
@@ -173,6 +302,10 @@ def main():
     if len(sys.argv) > 1 and sys.argv[1] == 'n128':     # additional fixture only; the others stay byte-identical
         torch.save(learner_case(2, 2, 128, ['winloss'], 4242), os.path.join(GOLD, 'learner_n128.pt'))
         print('learner_n128.pt', os.path.getsize(os.path.join(GOLD, 'learner_n128.pt')))
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == 'n512':     # the benchmarked entity count; written alone like n128
+        torch.save(learner_n512_case(), os.path.join(GOLD, 'learner_n512.pt'))
+        print('learner_n512.pt', os.path.getsize(os.path.join(GOLD, 'learner_n512.pt')))
         return
     specs = {}
     for name, bl in (('winloss', ['winloss']), ('four', ['winloss', 'build_order', 'built_unit', 'battle'])):

@@ -6,7 +6,7 @@ shipped or measured as product. It is a functional re-derivation (weights come i
 `state_dict` with the reference's key names); every function cites the
 reference lines it follows. Pinned against the executed reference by oracle/make_golden.py
 -> tests/golden/*.pt and tests/test_oracle_golden.py (and, in the build container, directly
-against the imported reference by tests/test_oracle_vs_reference.py).
+against the imported reference by tests/test_oracle_vs_reference.py, marker `reference`).
 
 Floating point only: plain torch ops with autograd, so gradients of the oracle come for free.
 """

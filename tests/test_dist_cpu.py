@@ -45,21 +45,31 @@ def _worker(rank, world, port, q):
     assert torch.equal(gathered[0], gathered[1])
     # each rank gets its own shard of a global batch of 8 "trajectories"
     g = torch.Generator().manual_seed(7)
-    full = torch.randn(8, 12, generator=g)
-    shard = full[rank * 4:(rank + 1) * 4]
-    dm.flat.zero_grad()
-    dm.prepare_backward()
-    model(shard).backward()
-    dm.sync_gradients()
-    # reference: single-process gradient of the mean over both shards
+    # the reference learner's sequence, nothing else (rl_learner.py:114-132): zero_grad / backward / sync_gradients
+    # / optimizer.step, for THREE steps with a plain torch optimizer -- from the second step on the buckets must
+    # have re-armed themselves
+    opt = torch.optim.SGD(model.parameters(), lr=0.1)
     ref = Tiny()
     ref.load_state_dict(model.state_dict())
-    (0.5 * (ref(full[:4]) + ref(full[4:]))).backward()
+    ref_opt = torch.optim.SGD(ref.parameters(), lr=0.1)
     worst = 0.0
-    for (k, p), (_, pr) in zip(model.named_parameters(), ref.named_parameters()):
-        gr = pr.grad if pr.grad is not None else torch.zeros_like(pr)
-        worst = max(worst, (p.grad - gr).abs().max().item())
-        assert p.grad.data_ptr() >= dm.flat.grad.data_ptr()          # grads live in the flat buffer
+    for step in range(3):
+        full = torch.randn(8, 12, generator=g)
+        shard = full[rank * 4:(rank + 1) * 4]
+        opt.zero_grad()
+        model(shard).backward()
+        dm.sync_gradients()
+        # single-process gradient of the mean over both shards
+        ref_opt.zero_grad()
+        (0.5 * (ref(full[:4]) + ref(full[4:]))).backward()
+        for (k, p), (_, pr) in zip(model.named_parameters(), ref.named_parameters()):
+            gr = pr.grad if pr.grad is not None else torch.zeros_like(pr)
+            mine = p.grad if p.grad is not None else torch.zeros_like(p)
+            worst = max(worst, (mine - gr).abs().max().item())
+        opt.step()
+        ref_opt.step()
+    for p, pr in zip(model.parameters(), ref.parameters()):
+        worst = max(worst, (p - pr).abs().max().item())
     q.put((rank, worst))
     dist.destroy_process_group()
 

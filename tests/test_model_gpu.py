@@ -127,7 +127,7 @@ def test_cuda_graph_learner_step_matches_eager():
         m.load_state_dict(sd, strict=False)
         m = m.cuda()
         step = LearnerStep(m, ReinforcementLoss({}, 'MP0'), lr=1e-4, use_graph=use_graph)
-        for _ in range(3 if not use_graph else 1):     # graph: 2 warm-up steps + capture + 1 replay = 3 steps too
+        for _ in range(3):        # the capture's warm-up leaves no trace: 3 calls = 3 optimizer updates either way
             step(data)
         steps[use_graph] = step
     eager_step, graph_step = steps[False], steps[True]
@@ -140,6 +140,45 @@ def test_cuda_graph_learner_step_matches_eager():
     assert abs(l_e - l_g) <= 1e-3 * max(1.0, abs(l_e)), (l_e, l_g)
     info = graph_step(data)
     assert 'winloss/td' in info and isinstance(info['kl/total'], float)
+
+
+@gpu
+def test_shadow_follows_load_state_dict_and_torch_optimizer():
+    """The bf16 weight shadow of a DistModule-wrapped model must follow every way the reference changes weights:
+    `load_state_dict` after wrapping (checkpoint hook, value reset: rl_learner.py:228) and an in-place torch
+    optimizer step (the documented drop-in mode keeps the reference's own Adam)."""
+    from applestar_b200 import Model
+    from applestar_b200.learner import DistModule
+    spec = load_spec('winloss')
+    data = synth.tree_map(lambda t: t.cuda(), synth.gen_trajectories(2, 2, 48, 9))
+
+    def values_of(model):
+        with torch.no_grad():
+            return model.rl_learner_forward(**data)['value']['winloss'].clone()
+
+    sd0, sd1 = synth.full_state_dict(spec, 0), synth.full_state_dict(spec, 1)
+    fresh = Model({'model': {'enable_baselines': ['winloss']}}, use_value_network=True)
+    fresh.load_state_dict(sd1, strict=False)
+    want = values_of(fresh.cuda())
+    m = Model({'model': {'enable_baselines': ['winloss']}}, use_value_network=True)
+    m.load_state_dict(sd0, strict=False)
+    dm = DistModule(m.cuda())
+    before = values_of(m)
+    dm.load_state_dict(sd1, strict=False)                     # after wrapping, as the reference does
+    after = values_of(m)
+    assert (before - want).abs().max().item() > 1e-3
+    assert torch.equal(after, want)
+    opt = torch.optim.SGD(m.parameters(), lr=0.05)
+    opt.zero_grad()
+    out = m.rl_learner_forward(**data)
+    out['value']['winloss'].sum().backward()
+    dm.sync_gradients()
+    opt.step()
+    moved = values_of(m)
+    ref = Model({'model': {'enable_baselines': ['winloss']}}, use_value_network=True)
+    ref.load_state_dict({k: v.detach().cpu() for k, v in m.state_dict().items()}, strict=False)
+    assert (moved - after).abs().max().item() > 1e-4          # the step is visible in the forward pass ...
+    assert torch.equal(moved, values_of(ref.cuda()))          # ... and equals a freshly built model with those weights
 
 
 @gpu

@@ -115,7 +115,8 @@ def test_entity_features_match_oracle_concat():
     assert int(neg.item()) == 1                                           # the reference raises here
 
 
-@pytest.mark.parametrize('T,B,I,H', [(5, 3, 64, 384), (1, 4, 32, 32), (9, 2, 384, 384), (4, 17, 64, 384), (7, 40, 32, 32)])
+@pytest.mark.parametrize('T,B,I,H', [(5, 3, 64, 384), (1, 4, 32, 32), (9, 2, 384, 384), (4, 17, 64, 384), (7, 40, 32, 32),
+                                     (65, 16, 1536, 384)])
 def test_lnlstm_layer_fwd_bwd_vs_oracle_cell(T, B, I, H):
     """Persistent LN-LSTM kernel vs the oracle's per-step cell (lstm.py:138-153 restated).  W_hh and the input GEMM
     run in bf16 -> tolerance 3e-2 abs on O(1) outputs, 8% of max on gradients."""

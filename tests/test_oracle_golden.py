@@ -137,3 +137,31 @@ def test_learner_n128_fixture():
         assert max_abs(v, g['value'][k]) < 1e-5, k
     v = g['loss_info']['total_loss']
     assert abs(float(info['total_loss']) - v) <= 1e-5 * max(1.0, abs(v))
+
+
+def test_learner_n512_fixture():
+    """The benchmarked entity count (N = 512, special observations): restatement vs executed reference -- logits, values,
+    every loss scalar, all 394 gradient norms and the ~300 stored gradient tensors."""
+    from util import grad_sample
+    g = golden('learner_n512.pt')
+    sd = synth.full_state_dict(load_spec('winloss'), 0)
+    sd = {k: v.requires_grad_(True) for k, v in sd.items()}
+    data = synth.gen_trajectories(g['T'], g['B'], g['N'], g['seed'], special=True)
+    out = R.rl_learner_forward(sd, g['baselines'], **clone_tree(data))
+    for k in C.HEADS:
+        a, b = valid_logits(out['target_logit'][k].detach(), g['logit'][k])
+        assert max_abs(a, b) < 2e-5, k
+    for k, v in out['value'].items():
+        assert max_abs(v.detach(), g['value'][k]) < 1e-5, k
+    info = R.compute_loss(C.DEFAULT_LOSS_CONFIG, out)
+    assert set(info) == set(g['loss_info'])
+    for k, v in g['loss_info'].items():
+        assert abs(float(info[k]) - v) <= 2e-5 * max(1.0, abs(v)), k
+    info['total_loss'].backward()
+    for k, (norm, _) in g['grad_summary'].items():
+        mn = 0.0 if sd[k].grad is None else sd[k].grad.double().norm().item()
+        assert abs(mn - float(norm)) <= 2e-3 * float(norm) + 1e-7, k
+    assert len(g['grads']) >= 300
+    for k, v in g['grads'].items():
+        mine = grad_sample(sd[k].grad)
+        assert max_abs(mine, v) <= 2e-3 * v.abs().max().item() + 1e-7, k
