@@ -168,7 +168,7 @@ def _kept_grads(model, everything=False):
     return out
 
 
-def learner_n512_case(T=4, B=2, N=512, seed=5120):
+def learner_n512_case(T=4, B=2, N=512, seed=5120, budgets_only=False):
     """The benchmarked entity count (N = 512: four key blocks in the fused attention, 512-key scatter sort, cluster LSTM)
     with the all-on-one-cell and entity_num == 1 observations: reference fp32 logits / values / 63 loss scalars /
     gradients of ~300 tensors (every tensor <= 8192 elements in full + BIG_GRADS), the fp64 forward, and the
@@ -239,6 +239,9 @@ def learner_n512_case(T=4, B=2, N=512, seed=5120):
                                           for k, v in ib.items()}
     finally:
         enc_mod.scatter_connection = orig_sc
+    if budgets_only:        # the GPU test recomputes the fp32 side with the oracle on the box's CPU
+        for k in ('logit', 'value', 'logit64', 'value64', 'grads'):
+            del res[k]
     return res
 
 
@@ -306,6 +309,10 @@ def main():
     if len(sys.argv) > 1 and sys.argv[1] == 'n512':     # the benchmarked entity count; written alone like n128
         torch.save(learner_n512_case(), os.path.join(GOLD, 'learner_n512.pt'))
         print('learner_n512.pt', os.path.getsize(os.path.join(GOLD, 'learner_n512.pt')))
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == 'n512t8':   # tolerance budgets (only) of the T = 8 all-gradients test
+        torch.save(learner_n512_case(8, 2, 512, 8512, budgets_only=True), os.path.join(GOLD, 'learner_n512_t8_budget.pt'))
+        print('learner_n512_t8_budget.pt', os.path.getsize(os.path.join(GOLD, 'learner_n512_t8_budget.pt')))
         return
     specs = {}
     for name, bl in (('winloss', ['winloss']), ('four', ['winloss', 'build_order', 'built_unit', 'battle'])):

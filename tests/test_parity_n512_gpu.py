@@ -3,15 +3,17 @@ sort, the cluster LSTM, up to 12 pointer steps) against the executed reference (
 against the oracle run on the box's CPU.
 
 Tolerance policy: a bf16 implementation may be 2x as far from the truth as the REFERENCE'S OWN
-bf16-autocast run -- per logit head in max-abs AND RMS, per loss scalar, and per gradient TENSOR in relative L2 and
-cosine (fixture `bf16_autocast_err`, `bf16_autocast_loss_info`, `bf16_autocast_grad_err`).  No tensor may fail.
+bf16-autocast run -- per logit head in max-abs AND RMS, per loss scalar, per module-level gradient aggregate in
+relative L2 (util.grad_group_check); every gradient TENSOR is checked in relative L2 and cosine at 3x its own budget
+(util.grad_check says why 3), and the median relative error over all tensors must not exceed the reference's.
+Fixture keys: `bf16_autocast_err`, `bf16_autocast_loss_info`, `bf16_autocast_grad_err`.  No tensor may fail.  tools/parity_report.py prints the full per-tensor table (profiles/r02_parity_n512*.txt).
 Masks and indices are compared bit-exactly."""
 import pytest
 import torch
 
 from applestar_b200 import config as C, synth, tables
 from oracle import restate as R
-from util import clone_tree, golden, grad_check, grad_sample, load_spec
+from util import clone_tree, golden, grad_budgets, grad_check, grad_group_check, grad_sample, load_spec
 
 gpu = pytest.mark.gpu
 
@@ -69,19 +71,25 @@ def test_learner_n512_vs_golden():
     assert not bad, bad
     info['total_loss'].backward()
     params = dict(model.named_parameters())
-    gerr = g['bf16_autocast_grad_err']
+    gerr, typical = grad_budgets(g)
     assert len(g['grads']) >= 300
+    mine = {k: grad_sample(params[k].grad) for k in g['grads']}
+    rels = []
     for k, ref in g['grads'].items():                            # ~300 gradient TENSORS (full, or a fixed sample)
         assert params[k].grad is not None, k
-        why = grad_check(grad_sample(params[k].grad), ref, gerr[k])
+        why = grad_check(mine[k], ref, gerr[k], typical)
         if why:
             bad.append((k, why))
+        if float(gerr[k][0]) < 1.0:
+            rels.append(((mine[k].double() - ref.double()).norm() / ref.double().norm()).item())
+    bad += grad_group_check(mine, g['grads'], gerr, typical)[0]
+    assert sorted(rels)[len(rels) // 2] <= typical, 'median relative gradient error above the reference bf16 run'
     for k, (norm, _) in g['grad_summary'].items():               # all 394: gradient norm within the same budget
         gn = params[k].grad.double().norm().item()
         rel_b = float(gerr[k][0])
         if rel_b > 1.0:
             continue
-        if abs(gn - norm.item()) > (2.0 * rel_b + 0.02) * norm.item() + 1e-6:
+        if abs(gn - norm.item()) > max(3.0 * rel_b, typical) * norm.item() + 1e-6:
             bad.append((k, 'norm %.4e vs %.4e' % (gn, norm.item())))
     assert not bad, (len(bad), bad[:12])
 
@@ -90,9 +98,9 @@ def test_learner_n512_vs_golden():
 def test_learner_n512_all_gradients_vs_oracle():
     """T = 8, B = 2, N = 512: the oracle restatement runs on the box's CPU (a few seconds) and EVERY one of the 394
     gradient tensors is compared in full (cosine / relative L2).  The budgets are the reference's bf16-autocast
-    errors stored for the T = 4 fixture; different data, hence slack 3 instead of 2."""
+    errors on exactly this batch (tests/golden/learner_n512_t8_budget.pt, `make_golden.py n512t8`)."""
     from applestar_b200 import ReinforcementLoss
-    g = golden('learner_n512.pt')
+    g = golden('learner_n512_t8_budget.pt')
     model, sd = _model()
     data = synth.gen_trajectories(8, 2, 512, 8512, special=True)
     out = model.rl_learner_forward(**_cuda(data))
@@ -107,21 +115,22 @@ def test_learner_n512_all_gradients_vs_oracle():
         keep = b > -1e8
         assert torch.equal(a <= -1e8, ~keep), k
         d = (a - b)[keep].double()
-        bmx, brms = (3.0 * v.item() for v in g['bf16_autocast_err'][k])
+        bmx, brms = (2.0 * v.item() for v in g['bf16_autocast_err'][k])
         assert d.abs().max().item() <= bmx and d.pow(2).mean().sqrt().item() <= brms, (k, d.abs().max().item(), bmx)
     bad = []
-    gerr = g['bf16_autocast_grad_err']
+    gerr, typical = grad_budgets(g)
     params = dict(model.named_parameters())
-    n = 0
+    mine, refs = {}, {}
     for k, p in params.items():
         if not p.requires_grad:
             continue
-        n += 1
-        rg = sdr[k].grad if sdr[k].grad is not None else torch.zeros_like(sdr[k])
-        why = grad_check(p.grad.cpu(), rg, gerr[k], slack=3.0)
+        refs[k] = (sdr[k].grad if sdr[k].grad is not None else torch.zeros_like(sdr[k])).reshape(-1)
+        mine[k] = p.grad.detach().float().cpu().reshape(-1)
+        why = grad_check(mine[k], refs[k], gerr[k], typical)
         if why:
             bad.append((k, why))
-    assert n == 394
+    assert len(refs) == 394
+    bad += grad_group_check(mine, refs, gerr, typical)[0]
     assert not bad, (len(bad), bad[:12])
 
 
