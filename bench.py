@@ -35,6 +35,11 @@ def parse():
     ap.add_argument('--cpu-sample', default='8x2', help='unroll x trajectories of the bounded CPU sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-inference', action='store_true', help='skip the batched actor-inference figure (N = 1 only)')
+    ap.add_argument('--no-extras', action='store_true',
+                    help='skip the secondary measurements of the JSON line (library baseline, encoder microbench, HBM rooflines)')
+    ap.add_argument('--workload', default='learner', choices=['learner', 'encoder_microbench'],
+                    help='encoder_microbench: BASELINE.json configs[1] alone (entity Transformer + ScatterConnection + '
+                         'spatial encoder, batch 1024) as its own JSON line')
     return ap.parse_args()
 
 
@@ -190,32 +195,278 @@ def gemm_flops_hook(records):
     return orig
 
 
-def actor_inference(model, dev, batch=256, iters=8):
+def actor_inference(model, dev, batch=256, iters=8, cpu_baseline=True):
     """BASELINE.json's second metric (reported per GPU): `compute_logp_action` on `batch` observations x 512 entities
-    through learner.ActorStep (CUDA graph, all 64 sampling steps inside), observations resident on the device."""
+    through learner.ActorStep (CUDA graph, all 64 sampling steps inside).  `value`: observations resident on the
+    device; `e2e`: every call copies its observations (and the Gumbel noise it samples with) from pinned host memory
+    and reads the sampled actions + log-probs back to the host, inside the timed region."""
     from applestar_b200 import synth
     from applestar_b200.learner import ActorStep
+    _, _, tf_sus, which = peaks()
     actor = ActorStep(model)
-    obs = synth.tree_map(lambda t: t.to(dev), synth.gen_observations(batch, 512, 7))
+    host_obs = synth.tree_map(lambda t: t.pin_memory(), synth.gen_observations(batch, 512, 7))
+    host_noise = synth.tree_map(lambda t: t.pin_memory(), synth.gen_gumbel(batch, 11))
+    obs = synth.tree_map(lambda t: t.to(dev), host_obs)
+    noise = synth.tree_map(lambda t: t.to(dev), host_noise)
     hidden = [(torch.zeros(batch, 384, device=dev), torch.zeros(batch, 384, device=dev)) for _ in range(3)]
-    noise = synth.tree_map(lambda t: t.to(dev), synth.gen_gumbel(batch, 11))
+    nbytes = [0, 0]
 
-    def call():
-        return actor(obs['spatial_info'], obs['entity_info'], obs['scalar_info'], obs['entity_num'], hidden, gumbel_noise=noise)
+    def call(o=obs, n=noise):
+        return actor(o['spatial_info'], o['entity_info'], o['scalar_info'], o['entity_num'], hidden, gumbel_noise=n)
+
+    def call_e2e(count=False):
+        o = synth.tree_map(lambda t: t.to(dev, non_blocking=True), {k: host_obs[k] for k in ('spatial_info', 'entity_info', 'scalar_info', 'entity_num')})
+        n = synth.tree_map(lambda t: t.to(dev, non_blocking=True), host_noise)
+        res = call(o, n)
+        back = [res['selected_units_num']] + list(res['action_info'].values()) + list(res['action_logp'].values())
+        back = [t.cpu() for t in back]
+        if count:
+            tot = [0]
+            synth.tree_map(lambda t: tot.__setitem__(0, tot[0] + t.numel() * t.element_size()),
+                           [{k: host_obs[k] for k in ('spatial_info', 'entity_info', 'scalar_info', 'entity_num')}, host_noise])
+            nbytes[0], nbytes[1] = tot[0], sum(t.numel() * t.element_size() for t in back)
 
     for _ in range(3):
         call()
     torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0, e1 = _events()
     e0.record()
     for _ in range(iters):
         call()
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / iters
-    return {'metric': 'inference_obs_per_sec_per_gpu', 'value': batch / ms * 1e3, 'unit': 'obs/s', 'ms_per_call': ms,
+    call_e2e(count=True)
+    torch.cuda.synchronize()
+    e0, e1 = _events()
+    e0.record()
+    for _ in range(iters):
+        call_e2e()
+    e1.record()
+    torch.cuda.synchronize()
+    ms_e2e = e0.elapsed_time(e1) / iters
+    obs_s = batch / ms * 1e3
+    line = {'metric': 'inference_obs_per_sec_per_gpu', 'value': obs_s, 'unit': 'obs/s', 'ms_per_call': ms,
             'config': {'workload': 'compute_logp_action_B%d_N512' % batch, 'cuda_graph': True,
-                       'launches_per_call': actor.launches_per_call}}
+                       'launches_per_call': actor.launches_per_call},
+            'e2e': {'value': batch / ms_e2e * 1e3, 'unit': 'obs/s', 'ms_per_call': ms_e2e,
+                    'h2d_bytes_per_step': nbytes[0], 'd2h_bytes_per_step': nbytes[1]},
+            'roofline': {'bound': 'tensor', 'achieved': obs_s * 6.81e9 / 1e12, 'peak': tf_sus, 'unit': 'TFLOP/s',
+                         'frac': obs_s * 6.81e9 / 1e12 / tf_sus, 'flop_per_obs': 6.81e9,
+                         'peak_source': which + ' bf16_tflops_sustained',
+                         'note': 'whole call incl. the 64 sequential pointer steps and the small-M heads (latency-bound)'}}
+    if cpu_baseline:
+        line['cpu_baseline'] = cpu_inference_throughput(16, os.cpu_count() or 1)
+    return line
+
+
+def cpu_inference_throughput(batch, threads):
+    """Oracle port of `compute_logp_action` (oracle/restate.py) on the host cores: bounded sample of `batch` observations."""
+    from applestar_b200 import synth, tables
+    from oracle import restate as R
+    torch.set_num_threads(threads)
+    sd = synth.full_state_dict(load_spec(), 0)
+    data = synth.gen_observations(batch, 512, 7)
+    noise = synth.gen_gumbel(batch, 11)
+    su_table = torch.tensor(tables.flags(tables.ACTION_HAS_SELECTED_UNITS))
+    times = []
+    for i in range(3):
+        t0 = time.perf_counter()
+        with torch.no_grad():
+            R.compute_logp_action(sd, noise=noise, su_table=su_table, **synth.tree_map(lambda t: t.clone(), data))
+        times.append(time.perf_counter() - t0)
+    dt = min(times[1:])
+    return {'value': batch / dt, 'unit': 'obs/s', 'cores': threads, 'kind': 'port',
+            'sample': 'oracle/restate.py compute_logp_action, B=%d N=512, best of 2 calls' % batch}
+
+
+def algorithmic_flops(T, B, su_steps_mean, fields=1):
+    """dense algorithmic FLOPs of one learner step (forward x 3 for forward + backward)."""
+    fwd = (T + 1) * B * 5.138e9 + T * B * (1.574e9 + 0.024e9 + su_steps_mean * 0.00116e9) + (T + 1) * B * fields * 0.0044e9
+    return 3.0 * fwd
+
+
+def _events():
+    return torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+
+def gpu_library_baseline(T, B, N, dev, hbm_guard_gb=150.0):
+    """SURVEY §8(d) 'GPU reference baseline': the SAME algorithm through stock ATen / cuBLAS / cuDNN kernels on the same
+    B200 -- the oracle restatement of the reference (plain torch ops, its autograd) moved to the GPU, fp32 with TF32
+    off and under autocast(bfloat16): forward + loss + backward.  This is the 'existing GPU path' every kernel of this
+    repo has to beat; it is a reported baseline, never part of the product path.  The largest trajectory count that
+    fits is used (and named)."""
+    from applestar_b200 import synth, config as C
+    from oracle import restate as R
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    sd = {k: v.to(dev).requires_grad_(True) for k, v in synth.full_state_dict(load_spec(), 0).items()}
+    res = {}
+    for mode in ('fp32', 'autocast_bf16'):
+        b = B
+        while b >= 1:
+            try:
+                data = synth.tree_map(lambda t: t.to(dev), synth.gen_trajectories(T, b, N, 1234))
+                times = []
+                for i in range(3):
+                    torch.cuda.synchronize()
+                    e0, e1 = _events()
+                    e0.record()
+                    with torch.autocast('cuda', dtype=torch.bfloat16, enabled=(mode != 'fp32')):
+                        out = R.rl_learner_forward(sd, ['winloss'], **synth.tree_map(lambda t: t.clone(), data))
+                        out['target_logit'] = {k: v.float() for k, v in out['target_logit'].items()}
+                        out['value'] = {k: v.float() for k, v in out['value'].items()}
+                    info = R.compute_loss(C.DEFAULT_LOSS_CONFIG, out)
+                    for v in sd.values():
+                        v.grad = None
+                    info['total_loss'].backward()
+                    e1.record()
+                    torch.cuda.synchronize()
+                    times.append(e0.elapsed_time(e1))
+                    del out, info
+                ms = min(times[1:])
+                res[mode] = {'value': T * b / ms * 1e3, 'unit': 'traj-steps/s', 'ms_per_step': ms, 'trajectories': b,
+                             'unroll_len': T, 'peak_mem_gb': torch.cuda.max_memory_allocated(dev) / 1e9}
+                break
+            except torch.OutOfMemoryError:
+                b //= 2
+            finally:
+                data = None
+                for v in sd.values():
+                    v.grad = None
+                torch.cuda.empty_cache()
+        if mode not in res:
+            res[mode] = {'unavailable': 'out of memory down to 1 trajectory'}
+    res['what'] = ('oracle/restate.py (plain torch restatement of the reference) on this GPU: ATen/cuBLAS/cuDNN kernels, '
+                   'forward + loss + backward, TF32 off; best of 2 steps after 1 warm-up')
+    return res
+
+
+def encoder_microbench(model, dev, batch=1024, chunk=256, iters=3):
+    """BASELINE.json configs[1]: entity Transformer + ScatterConnection + spatial encoder, batch 1024 observations x 512
+    entities, 152x160 map, forward, observations resident on the device (processed in chunks of `chunk`).  The
+    stand-alone ScatterConnection kernel (as_scatter_connection_fwd: [R,512,32] fp32 -> [R,32,152,160] fp32) is timed
+    on its own against its algorithmic bytes, 3.179 MB per observation; inside the model the scatter is
+    fused into the kernel that builds the spatial encoder's input."""
+    from applestar_b200 import synth, ops, spatial, config as C
+    hbm, _, tf_sus, which = peaks()
+    enc = model.encoder
+    obs = synth.tree_map(lambda t: t.to(dev), synth.gen_observations(chunk, 512, 77, entity_num_range=(512, 512), hidden=False))
+    n_chunks = batch // chunk
+    stages = {'entity_encoder': 0.0, 'scatter_project': 0.0, 'scatter_connection': 0.0, 'spatial_encoder': 0.0}
+
+    def run(record):
+        for _ in range(n_chunks):
+            marks = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+            with torch.no_grad():
+                marks[0].record()
+                ent, _pooled = enc.entity_encoder(obs['entity_info'], obs['entity_num'])
+                marks[1].record()
+                proj = enc.scatter_project(ent)
+                marks[2].record()
+                smap = ops.scatter_connection(proj.float(), obs['entity_info']['x'], obs['entity_info']['y'],
+                                              obs['entity_num'], C.SPATIAL_Y, C.SPATIAL_X)
+                marks[3].record()
+                pw = enc.spatial_encoder.project[0]
+                x = spatial.spatial_project(proj, obs['entity_info']['x'], obs['entity_info']['y'], obs['entity_num'],
+                                            obs['spatial_info'], pw.weight, pw.bias)
+                enc.spatial_encoder(obs['spatial_info'], x)
+                marks[4].record()
+            del smap
+            if record:
+                torch.cuda.synchronize()
+                for name, a, b in zip(stages, marks[:-1], marks[1:]):
+                    stages[name] += a.elapsed_time(b)
+    run(False)
+    for _ in range(iters):
+        run(True)
+    stages = {k: v / iters for k, v in stages.items()}
+    total = sum(stages.values())
+    model_ms = total - stages['scatter_connection']          # the model path (scatter fused into the feature kernel)
+    sc_bytes = batch * (512 * 32 * 4 + 512 * 2 + 32 * C.SPATIAL_Y * C.SPATIAL_X * 4)
+    sc_gbs = sc_bytes / (stages['scatter_connection'] * 1e-3) / 1e9
+    flops = batch * 5.127e9
+    return {'metric': 'encoder_microbench_obs_per_sec', 'value': batch / model_ms * 1e3, 'unit': 'obs/s',
+            'config': {'workload': 'entity_transformer+scatter_connection+spatial_encoder_B%d_N512_152x160' % batch,
+                       'chunk': chunk, 'direction': 'forward', 'data': 'synthetic, resident'},
+            'ms_per_stage': stages, 'ms_model_path': model_ms,
+            'roofline': {'bound': 'tensor', 'achieved': flops / (model_ms * 1e-3) / 1e12, 'peak': tf_sus, 'unit': 'TFLOP/s',
+                         'frac': flops / (model_ms * 1e-3) / 1e12 / tf_sus, 'flop_per_obs': 5.127e9,
+                         'peak_source': which + ' bf16_tflops_sustained'},
+            'scatter_connection': {'bound': 'hbm', 'kernel': 'as::scatter_fwd_kernel (stand-alone op)', 'achieved': sc_gbs,
+                                   'peak': hbm, 'unit': 'GB/s', 'frac': sc_gbs / hbm, 'bytes_per_obs': sc_bytes / batch,
+                                   'ms': stages['scatter_connection'], 'peak_source': which + ' hbm_gbs'}}
+
+
+def hbm_rooflines(model, loss_fn, resident, dev):
+    """CUDA-event time of the two HBM-bound kernel families the north star names, against their ALGORITHMIC bytes
+    (SURVEY §8d): the ScatterConnection kernel at the learner's row count, and the fused loss (forward statistics pass
+    + scan + gradient pass) on the step's own logits: 3 x 4 B per VALID logit (target + teacher read, gradient
+    written; the -1e9 padding is not counted)."""
+    from applestar_b200 import ops, config as C
+    hbm, _, _, which = peaks()
+    out = {}
+    R = resident['entity_num'].shape[0]
+    proj = torch.randn(R, 512, 32, device=dev)
+    x, y, en = resident['entity_info']['x'], resident['entity_info']['y'], resident['entity_num']
+    with torch.no_grad():
+        for _ in range(2):
+            ops.scatter_connection(proj, x, y, en, C.SPATIAL_Y, C.SPATIAL_X)
+        e0, e1 = _events()
+        e0.record()
+        for _ in range(5):
+            ops.scatter_connection(proj, x, y, en, C.SPATIAL_Y, C.SPATIAL_X)
+        e1.record()
+        torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 5
+    nbytes = R * (512 * 32 * 4 + 512 * 2 + 32 * C.SPATIAL_Y * C.SPATIAL_X * 4)
+    out['scatter_connection'] = {'kernel': 'as::scatter_fwd_kernel', 'rows': R, 'ms': ms, 'bytes': nbytes,
+                                 'achieved': nbytes / (ms * 1e-3) / 1e9, 'peak': hbm, 'unit': 'GB/s',
+                                 'frac': nbytes / (ms * 1e-3) / 1e9 / hbm}
+    del proj
+    with torch.no_grad():
+        fwd = model.rl_learner_forward(**resident, defer_checks=True)
+    T, B = fwd['unroll_len'], fwd['batch_size']
+    en_tb = resident['entity_num'][:T * B].view(T, B)
+    sun = resident['selected_units_num']
+    valid = T * B * (327 + 128 + 2 + C.SPATIAL_Y * C.SPATIAL_X) + int(en_tb.sum()) + int((torch.clamp(sun, min=1) * (en_tb + 1)).sum())
+    leaf = dict(fwd)
+    leaf['target_logit'] = {k: v.detach().clone().requires_grad_(True) for k, v in fwd['target_logit'].items()}
+    leaf['value'] = {k: v.detach().clone().requires_grad_(True) for k, v in fwd['value'].items()}
+
+    def once():
+        info = loss_fn.compute_loss(leaf)
+        info['total_loss'].backward()
+        for d in (leaf['target_logit'], leaf['value']):
+            for v in d.values():
+                v.grad = None
+
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        once()
+        once()
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()                   # as in the learner step: the 12 launches replay from a CUDA graph
+    with torch.cuda.graph(graph):
+        once()
+    graph.replay()
+    torch.cuda.synchronize()
+    e0, e1 = _events()
+    e0.record()
+    for _ in range(5):
+        graph.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 5
+    nbytes = 12.0 * valid
+    out['rl_loss'] = {'kernel': 'as::loss_row_stats + loss_scan + loss_finalize + loss_row_grad (forward + backward)',
+                      'valid_logits': valid, 'ms': ms, 'bytes': nbytes, 'achieved': nbytes / (ms * 1e-3) / 1e9,
+                      'peak': hbm, 'unit': 'GB/s', 'frac': nbytes / (ms * 1e-3) / 1e9 / hbm,
+                      'note': 'compute_loss + backward (12 launches) replayed from a CUDA graph, CUDA events around 5 replays'}
+    out['peak_source'] = which + ' hbm_gbs'
+    return out
 
 
 def run_ours(args):
@@ -237,6 +488,13 @@ def run_ours(args):
     model = Model({'model': {'enable_baselines': ['winloss']}}, use_value_network=True)
     model.load_state_dict(synth.full_state_dict(load_spec(), 0), strict=False)
     model = model.to(dev)
+    if args.workload == 'encoder_microbench':
+        if rank == 0:
+            mb = encoder_microbench(model, dev)
+            mb.update({'n_gpus': 1, 'steps': 3, 'warmup': 1, 'ms_per_step': mb['ms_model_path'], 'higher_is_better': True,
+                       'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic', 'gpu_launches': None})
+            print(json.dumps(mb))
+        return
     step_fn = LearnerStep(model, ReinforcementLoss({}, 'MP0'))
     host = synth.gen_trajectories(T, B, N, 1234 + rank)
     host = synth.tree_map(lambda t: t.pin_memory(), host)
@@ -318,11 +576,23 @@ def run_ours(args):
     # dominant kernel family = the tcgen05 GEMM: one instrumented step (outside the timed region)
     records = []
     orig = gemm_flops_hook(records)
-    step_fn._run(resident)                                # eager (un-captured) so that every launch can be bracketed
+    # eager (un-captured) so that every launch can be bracketed, and on ONE stream: a launch of the side-stream
+    # branches (value towers, scalar encoder) would otherwise be timed while it waits for SMs held by the main stream.
+    # The optimizer state is put back afterwards (this extra step is not part of the run).
+    os.environ['APPLESTAR_SIDE_STREAM'] = '0'
+    keep = [t.clone() for t in (step_fn.flat.flat, step_fn.optimizer.m, step_fn.optimizer.v, step_fn.optimizer.t_dev)]
+    step_fn._run(resident)
     torch.cuda.synchronize()
+    for dst, src in zip((step_fn.flat.flat, step_fn.optimizer.m, step_fn.optimizer.v, step_fn.optimizer.t_dev), keep):
+        dst.copy_(src)
+    step_fn.flat.refresh_shadow()
+    del keep
+    os.environ['APPLESTAR_SIDE_STREAM'] = '1'
     _lib.call = orig
     g_ms = sum(r[0].elapsed_time(r[1]) for r in records)
     g_fl = sum(r[2] for r in records)
+    su_mean = float(torch.clamp(host['selected_units_num'], min=1).float().mean())
+    alg_fl = algorithmic_flops(T, B, su_mean)
     if os.environ.get('APPLESTAR_GEMM_DUMP') and rank == 0:
         agg = {}
         for r in records:
@@ -332,10 +602,11 @@ def run_ours(args):
         for k, t in sorted(agg.items(), key=lambda kv: -kv[1][1])[:45]:
             print('GEMM %-22s args=%s n=%d ms=%.3f TF/s=%.0f' % (k[0], k[1:], t[0], t[1], t[2] / t[1] / 1e9), file=sys.stderr)
     hbm, tf_burst, tf_sus, which = peaks()
-    achieved = g_fl / (g_ms * 1e-3) / 1e12 if g_ms > 0 else 0.0
+    achieved = alg_fl / (g_ms * 1e-3) / 1e12 if g_ms > 0 else 0.0            # ALGORITHMIC flops
+    executed = g_fl / (g_ms * 1e-3) / 1e12 if g_ms > 0 else 0.0              # incl. zero borders / padded channels
     traffic = traffic_note = None             # DRAM bytes of the same kernel family from the committed ncu capture
     try:
-        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'profiles', 'r01_tensor_family_traffic.json')) as f:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'profiles', 'tensor_family_traffic.json')) as f:
             tj = json.load(f)
         traffic, traffic_note = tj['dram_bytes_per_launch_mean'], '%s: %.1f GB per step over %d launches' % (
             tj['source'], tj['dram_bytes_per_step'] / 1e9, tj['launches'])
@@ -361,6 +632,9 @@ def run_ours(args):
             'clocks': clocks,
             'roofline': {'bound': 'tensor', 'kernel': 'tcgen05 kernels as::gemm_kernel + as::attn_kernel + as::wgrad_slab_kernel (all %d launches of one step)' % len(records),
                          'achieved': achieved, 'peak': tf_sus, 'unit': 'TFLOP/s', 'frac': achieved / tf_sus,
+                         'flops': 'algorithmic: %.2f TFLOP per step (SURVEY 8d: dense forward x 3, H x W pixels, real K)' % (alg_fl / 1e12),
+                         'achieved_executed': executed, 'frac_executed': executed / tf_sus,
+                         'frac_of_whole_step': alg_fl / (ms / args.steps * 1e-3) / 1e12 / tf_sus,
                          'peak_source': which + ' bf16_tflops_sustained', 'gemm_ms_per_step': g_ms,
                          'gemm_share_of_step': g_ms / (ms / args.steps), 'traffic': traffic, 'traffic_source': traffic_note},
         }
@@ -371,17 +645,33 @@ def run_ours(args):
             line['cpu_baseline'] = {'value': v, 'unit': 'traj-steps/s', 'cores': threads, 'kind': 'port',
                                     'sample': 'oracle/restate.py forward+loss+backward, T=%d B=%d N=%d, 2 steps' % (Tc, Bc, N)}
         if not args.no_inference and world == 1:
-            line['inference'] = actor_inference(model, dev)
+            line['inference'] = actor_inference(model, dev, cpu_baseline=not args.no_cpu_baseline)
+        if not args.no_extras and world == 1:
+            line['roofline_hbm'] = hbm_rooflines(model, step_fn.loss, resident, dev)
+            line['encoder_microbench'] = encoder_microbench(model, dev)
+            step_fn._graphs.clear()                       # free the graph pool before the library path needs its memory
+            torch.cuda.empty_cache()
+            line['gpu_library_baseline'] = gpu_library_baseline(T, B, N, dev)
         print(json.dumps(line))
     if world > 1:
-        # tear-down: captured NCCL kernels inside CUDA graphs can stall destroy_process_group(); the numbers are out,
-        # so synchronise, drop the graphs and leave without the collective tear-down
+        # tear-down: the graphs hold captured NCCL kernels, so they go first (all ranks, after a common barrier),
+        # then the process group
         dist.barrier()
         torch.cuda.synchronize()
         step_fn._graphs.clear()
+        step_fn._pool = None
+        import gc
+        gc.collect()
+        torch.cuda.synchronize()
         sys.stdout.flush()
         sys.stderr.flush()
-        os._exit(0)
+        # a tear-down that does not finish within a minute (a peer that already left) must not hang the job: the
+        # numbers are out, so the watchdog ends the process
+        guard = threading.Timer(60.0, lambda: os._exit(0))
+        guard.daemon = True
+        guard.start()
+        dist.destroy_process_group()
+        guard.cancel()
 
 
 def main():
