@@ -29,8 +29,8 @@ class AsSuSampleArgs(ctypes.Structure):
 class AsLossArgs(ctypes.Structure):
     _fields_ = [
         ('T', c_int32), ('B', c_int32), ('F', c_int32), ('S', c_int32), ('N1', c_int32), ('NE', c_int32),
-        ('head_k', c_int32 * 6), ('upgo_field', c_int32), ('at_kl_steps', c_float),
-        ('logit', c_void_p * 6), ('teacher', c_void_p * 6), ('dlogit', c_void_p * 6), ('action', c_void_p * 6),
+        ('head_k', c_int32 * 6), ('upgo_field', c_int32), ('at_kl_steps', c_float), ('dapo_steps', c_float),
+        ('logit', c_void_p * 6), ('teacher', c_void_p * 6), ('successive', c_void_p * 6), ('dlogit', c_void_p * 6), ('action', c_void_p * 6),
         ('mu_logp', c_void_p * 6), ('actions_mask', c_void_p * 6),
         ('su_mask', c_void_p), ('su_logits_mask', c_void_p), ('tu_logits_mask', c_void_p),
         ('cum_action_mask', c_void_p), ('step', c_void_p),
@@ -40,8 +40,9 @@ class AsLossArgs(ctypes.Structure):
         ('gamma_td', c_float * AS_LOSS_MAX_FIELDS), ('w_pg', c_float * AS_LOSS_MAX_FIELDS),
         ('w_td', c_float * AS_LOSS_MAX_FIELDS),
         ('hw_pg', c_float * 6), ('hw_upgo', c_float * 6), ('hw_ent', c_float * 6), ('hw_kl', c_float * 6),
-        ('w_upgo', c_float), ('w_ent', c_float), ('w_kl', c_float), ('w_atkl', c_float),
-        ('stat_weight', c_void_p),
+        ('hw_dapo', c_float * 6),
+        ('w_upgo', c_float), ('w_ent', c_float), ('w_kl', c_float), ('w_atkl', c_float), ('w_dapo', c_float),
+        ('stat_weight', c_void_p), ('grad_scale', c_void_p),
         ('row_stats', c_void_p * 6), ('coef', c_void_p * 6), ('partial', c_void_p), ('out', c_void_p),
     ]
 
@@ -86,6 +87,8 @@ _SIGS = {
     'as_su_prefix_fwd': (c_int, [c_void_p] * 7 + [c_int64, c_int, c_int, c_int, c_int, c_void_p]),
     'as_su_prefix_bwd': (c_int, [c_void_p] * 6 + [c_int64, c_int, c_int, c_int, c_int, c_void_p]),
     'as_su_mask_logits': (c_int, [c_void_p] * 4 + [c_int64, c_int, c_int, c_int, c_float, c_float, c_void_p]),
+    'as_pointer_logits_fwd': (c_int, [c_void_p] * 4 + [c_int64, c_int, c_int, c_int, c_float, c_float, c_void_p]),
+    'as_pointer_logits_bwd': (c_int, [c_void_p] * 6 + [c_int64, c_int, c_int, c_int, c_float, c_void_p]),
     'as_attn_fwd_ok': (c_int, [c_int, c_int]),
     'as_attn_fwd': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_float, c_void_p]),
     'as_attn_bwd_dq': (c_int, [c_void_p] * 6 + [c_int64, c_int, c_int, c_int, c_float, c_void_p]),

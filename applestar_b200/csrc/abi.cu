@@ -63,6 +63,9 @@ int su_prefix_fwd(const float*, const long long*, const long long*, const long l
 int su_prefix_bwd(const float*, const long long*, const long long*, const float*, const unsigned char*, float*, long long, int, int,
                   int, int, cudaStream_t);
 int su_mask_logits(const float*, const long long*, const long long*, float*, long long, int, int, int, float, float, cudaStream_t);
+int pointer_logits_fwd(const float*, const float*, const long long*, float*, long long, int, int, int, float, float, cudaStream_t);
+int pointer_logits_bwd(const float*, const float*, const float*, const long long*, float*, float*, long long, int, int, int, float,
+                       cudaStream_t);
 int masked_mean_fwd(const float*, const long long*, float*, long long, int, int, cudaStream_t);
 int masked_mean_bwd(const float*, const long long*, float*, long long, int, int, cudaStream_t);
 int linear_bwd_prep(const float*, const void*, const float*, const void*, void*, float*, float*, long long, int, cudaStream_t);
@@ -347,6 +350,15 @@ int as_su_mask_logits(const float* x, const int64_t* selected_units, const int64
                       int Smax, int S, float scale, float fill, void* stream) {
   return as::su_mask_logits(x, reinterpret_cast<const long long*>(selected_units), reinterpret_cast<const long long*>(entity_num), out,
                             R, N1, Smax, S, scale, fill, ST(stream));
+}
+int as_pointer_logits_fwd(const float* query, const float* key, const int64_t* key_len, float* out, int64_t R, int S, int N, int D,
+                          float scale, float fill, void* stream) {
+  return as::pointer_logits_fwd(query, key, reinterpret_cast<const long long*>(key_len), out, R, S, N, D, scale, fill, ST(stream));
+}
+int as_pointer_logits_bwd(const float* dout, const float* query, const float* key, const int64_t* key_len, float* dquery, float* dkey,
+                          int64_t R, int S, int N, int D, float scale, void* stream) {
+  return as::pointer_logits_bwd(dout, query, key, reinterpret_cast<const long long*>(key_len), dquery, dkey, R, S, N, D, scale,
+                                ST(stream));
 }
 int as_attn_fwd_ok(int N, int D) { return as::attn_fwd_ok(N, D); }
 int as_attn_fwd(const void* qkv, const int64_t* key_len, void* out, void* probs, int64_t R, int N, int H, int D, float scale,

@@ -17,8 +17,8 @@
 
 namespace as {
 
-constexpr int kStatStride = 8;   // lse, logp_a, ent, lse_t, kl, (pad)
-constexpr int kCoefStride = 4;   // c_a, c_e, c_k, (pad)
+constexpr int kStatStride = 8;   // lse, logp_a, ent, lse_t, kl, lse_successive, kl_successive, (pad)
+constexpr int kCoefStride = 4;   // c_a, c_e, c_k, c_dapo
 
 struct Triple { float m, s, w; };
 
@@ -53,20 +53,24 @@ __global__ void loss_row_stats_kernel(const AsLossArgs a, int h, long long rows,
     const bool full = row_active(a, h, row, &step);   // false: only lse / log pi(a) are needed
     const float* x = a.logit[h] + row * (long long)K;
     const float* t = a.teacher[h] + row * (long long)K;
-    float mx = -INFINITY, mt = -INFINITY;
+    const float* sc = (full && a.successive[h] != nullptr) ? a.successive[h] + row * (long long)K : nullptr;   // DAPO
+    float mx = -INFINITY, mt = -INFINITY, ms = -INFINITY;
     for (int k = tr; k < K; k += THREADS_PER_ROW) {
       mx = fmaxf(mx, __ldg(x + k));
       if (full) mt = fmaxf(mt, __ldg(t + k));
+      if (sc) ms = fmaxf(ms, __ldg(sc + k));
     }
     mx = warp_max(mx);
     mt = warp_max(mt);
+    ms = warp_max(ms);
     if (THREADS_PER_ROW > 32) {
       const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-      if (l == 0) { red[0][w] = mx; red[1][w] = mt; }
+      if (l == 0) { red[0][w] = mx; red[1][w] = mt; red[7][w] = ms; }
       __syncthreads();
-      mx = red[0][0]; mt = red[1][0];
+      mx = red[0][0]; mt = red[1][0]; ms = red[7][0];
 #pragma unroll
-      for (int i = 1; i < 8; ++i) { mx = fmaxf(mx, red[0][i]); mt = fmaxf(mt, red[1][i]); }
+      for (int i = 1; i < 8; ++i) { mx = fmaxf(mx, red[0][i]); mt = fmaxf(mt, red[1][i]); ms = fmaxf(ms, red[7][i]); }
+      __syncthreads();                                  // red[7] is reused below
     }
     // pass 2 (rows come back from L1/L2): s = sum e^(x-mx), w = sum e^(x-mx) x, s2, w2 (teacher), u = sum e^(t-mt) x
     float s = 0.f, w = 0.f, s2 = 0.f, w2 = 0.f, u = 0.f;
@@ -89,6 +93,25 @@ __global__ void loss_row_stats_kernel(const AsLossArgs a, int h, long long rows,
 #pragma unroll
       for (int i = 0; i < 8; ++i) { s += red[2][i]; w += red[3][i]; s2 += red[4][i]; w2 += red[5][i]; u += red[6][i]; }
     }
+    // DAPO (as_rl_utils.py:105-127): KL(successive || pi) needs s3 = sum e^(c-ms), w3 = sum e^(c-ms) c, u3 = sum e^(c-ms) x
+    float s3 = 0.f, w3 = 0.f, u3 = 0.f;
+    if (sc) {
+      for (int k = tr; k < K; k += THREADS_PER_ROW) {
+        const float cv = __ldg(sc + k);
+        const float ec = expf(cv - ms);
+        s3 += ec; w3 += ec * cv; u3 += ec * __ldg(x + k);
+      }
+      s3 = warp_sum(s3); w3 = warp_sum(w3); u3 = warp_sum(u3);
+      if (THREADS_PER_ROW > 32) {
+        const int wi = threadIdx.x >> 5, l = threadIdx.x & 31;
+        __syncthreads();
+        if (l == 0) { red[2][wi] = s3; red[3][wi] = w3; red[4][wi] = u3; }
+        __syncthreads();
+        s3 = w3 = u3 = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { s3 += red[2][i]; w3 += red[3][i]; u3 += red[4][i]; }
+      }
+    }
     if (tr == 0) {
       const float lse = mx + logf(s);
       const long long act_idx = a.action[h][row];
@@ -102,7 +125,14 @@ __global__ void loss_row_stats_kernel(const AsLossArgs a, int h, long long rows,
       } else {
         st[2] = 0.f; st[3] = 0.f; st[4] = 0.f;
       }
-      st[5] = 0.f; st[6] = 0.f; st[7] = 0.f;
+      if (sc) {
+        const float lse_s = ms + logf(s3);
+        st[5] = lse_s;
+        st[6] = (w3 / s3 - lse_s) - (u3 / s3 - lse);            // KL  sum p_s (log p_s - log p)
+      } else {
+        st[5] = 0.f; st[6] = 0.f;
+      }
+      st[7] = 0.f;
     }
   }
 }
@@ -111,7 +141,7 @@ __global__ void loss_row_stats_kernel(const AsLossArgs a, int h, long long rows,
 // Stat slots (per-b partial sums, later divided by T*B):
 //   [f*10 + h]      pg loss of field f, head h (h<6);  [f*10+6] td;  [f*10+7] reward;  [f*10+8] value (mean over T+1)
 //   base = F*10:    [base + h] upgo h;  [base+6+h] entropy h;  [base+12+h] kl h;  [base+18] kl extra_at;
-//                   [base+19] battle reward
+//                   [base+19] battle reward;  [base+20+h] DAPO kl h
 __device__ __forceinline__ float head_mask_at(const AsLossArgs& a, int h, long long step) {
   return a.actions_mask[h] ? (float)a.actions_mask[h][step] : 1.f;
 }
@@ -147,6 +177,10 @@ __global__ void __launch_bounds__(kScanThreads) loss_scan_kernel(const AsLossArg
   float* s_nltu = s_nlsu + T;             // [T] valid target-unit logits
   float* s_atm = s_nltu + T;              // [T] action-type extra-KL mask
   float* s_br = s_atm + T;                // [T] battle reward
+  float* s_st6 = s_br + T;                // [6][T]  DAPO KL statistic
+  float* s_c3 = s_st6 + 6 * T;            // [6][T]  out: DAPO KL coefficient
+  float* s_dpm = s_c3 + 6 * T;            // [T] DAPO step flag
+  const bool dapo = a.successive[0] != nullptr;
   const float inv_tb = 1.f / (float)(T * B);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = kScanThreads / 32;
 
@@ -162,7 +196,9 @@ __global__ void __launch_bounds__(kScanThreads) loss_scan_kernel(const AsLossArg
       s_rho[i] = fminf(expf(lp - a.mu_logp[h][step]), 1.f);
       s_st2[i] = a.row_stats[h][step * kStatStride + 2];
       s_st4[i] = a.row_stats[h][step * kStatStride + 4];
+      s_st6[i] = a.row_stats[h][step * kStatStride + 6];
     }
+    s_c3[i] = 0.f;
   }
   for (int i = tid; i < T * F; i += kScanThreads) {
     const int f = i / T, t = i - f * T;
@@ -180,11 +216,12 @@ __global__ void __launch_bounds__(kScanThreads) loss_scan_kernel(const AsLossArg
     const long long step = (long long)t * B + b;
     s_atm[t] = ((a.step[step] < a.at_kl_steps) ? 1.f : 0.f) * a.cum_action_mask[step];
     s_br[t] = a.battle_reward[step];
+    s_dpm[t] = (a.step[step] < a.dapo_steps) ? 1.f : 0.f;
   }
   // ---- A2: warp per step: sums over the selected-units rows and the pointer-head logit masks
   for (int t = warp; t < T; t += nwarp) {
     const long long step = (long long)t * B + b;
-    float lp = 0.f, lr = 0.f, e2 = 0.f, k4 = 0.f, cnt = 0.f, nsu = 0.f, ntu = 0.f;
+    float lp = 0.f, lr = 0.f, e2 = 0.f, k4 = 0.f, k6 = 0.f, cnt = 0.f, nsu = 0.f, ntu = 0.f;
     for (int j = lane; j < S; j += 32) {
       const long long row = step * S + j;
       if (a.su_mask[row]) {
@@ -193,18 +230,20 @@ __global__ void __launch_bounds__(kScanThreads) loss_scan_kernel(const AsLossArg
         lr += l - a.mu_logp[3][row];
         e2 += a.row_stats[3][row * kStatStride + 2];
         k4 += a.row_stats[3][row * kStatStride + 4];
+        k6 += a.row_stats[3][row * kStatStride + 6];
         cnt += 1.f;
       }
     }
     for (int j = lane; j < a.N1; j += 32) nsu += a.su_logits_mask[step * a.N1 + j] ? 1.f : 0.f;
     for (int j = lane; j < a.NE; j += 32) ntu += a.tu_logits_mask[step * a.NE + j] ? 1.f : 0.f;
-    lp = warp_sum(lp); lr = warp_sum(lr); e2 = warp_sum(e2); k4 = warp_sum(k4);
+    lp = warp_sum(lp); lr = warp_sum(lr); e2 = warp_sum(e2); k4 = warp_sum(k4); k6 = warp_sum(k6);
     cnt = warp_sum(cnt); nsu = warp_sum(nsu); ntu = warp_sum(ntu);
     if (lane == 0) {
       s_lp[3 * T + t] = lp;
       s_rho[3 * T + t] = fminf(expf(lr), 1.f);
       s_st2[3 * T + t] = e2;
       s_st4[3 * T + t] = k4;
+      s_st6[3 * T + t] = k6;
       s_cnt[t] = cnt; s_nlsu[t] = nsu; s_nltu[t] = ntu;
     }
   }
@@ -327,6 +366,18 @@ __global__ void __launch_bounds__(kScanThreads) loss_scan_kernel(const AsLossArg
     float acc = 0.f;
     for (int t = 0; t < T; ++t) acc += s_br[t];
     part[base + 19] = acc;
+  } else if (tid >= 160 && tid < 166) {
+    // DAPO: KL(successive || pi) per head while step < dapo_steps (as_rl_utils.py:105-127)
+    const int h = tid - 160;
+    float acc = 0.f;
+    if (dapo) {
+      for (int t = 0; t < T; ++t) {
+        const float m = s_hm[h * T + t] * s_dpm[t];
+        s_c3[h * T + t] = a.w_dapo * a.hw_dapo[h] * m * inv_tb;
+        acc += s_st6[h * T + t] * m;
+      }
+    }
+    part[base + 20 + h] = acc;
   }
   __syncthreads();
 
@@ -338,6 +389,7 @@ __global__ void __launch_bounds__(kScanThreads) loss_scan_kernel(const AsLossArg
     if (h != 3) {
       a.coef[h][step * kCoefStride + 1] = s_c1[i];
       a.coef[h][step * kCoefStride + 2] = s_c2[i];
+      a.coef[h][step * kCoefStride + 3] = s_c3[i];
     }
   }
   for (int i = tid; i < T * S; i += kScanThreads) {
@@ -346,6 +398,7 @@ __global__ void __launch_bounds__(kScanThreads) loss_scan_kernel(const AsLossArg
     const bool on = a.su_mask[row];
     a.coef[3][row * kCoefStride + 1] = on ? s_c1[3 * T + t] : 0.f;
     a.coef[3][row * kCoefStride + 2] = on ? s_c2[3 * T + t] : 0.f;
+    a.coef[3][row * kCoefStride + 3] = on ? s_c3[3 * T + t] : 0.f;
   }
   for (int i = tid; i < T * F; i += kScanThreads) {
     const int f = i / T, t = i - f * T;
@@ -356,7 +409,7 @@ __global__ void __launch_bounds__(kScanThreads) loss_scan_kernel(const AsLossArg
 
 // ---------------------------------------------------------------------------------------------- K3
 __global__ void loss_finalize_kernel(const AsLossArgs a) {
-  const int n = a.F * 10 + 20;
+  const int n = a.F * 10 + 26;
   __shared__ float tot[64];
   const float inv_tb = 1.f / (float)(a.T * a.B);
   float contrib = 0.f;
@@ -381,6 +434,7 @@ __global__ void loss_finalize_kernel(const AsLossArgs a) {
 template <int THREADS_PER_ROW>
 __global__ void loss_row_grad_kernel(const AsLossArgs a, int h, long long rows, int K, float gscale) {
   constexpr int RPB = 256 / THREADS_PER_ROW;
+  if (a.grad_scale != nullptr) gscale *= __ldg(a.grad_scale);
   const int sub = threadIdx.x / THREADS_PER_ROW;
   const int tr = threadIdx.x % THREADS_PER_ROW;
   for (long long row0 = (long long)blockIdx.x * RPB; row0 < rows; row0 += (long long)gridDim.x * RPB) {
@@ -394,18 +448,20 @@ __global__ void loss_row_grad_kernel(const AsLossArgs a, int h, long long rows, 
       continue;
     }
     const float* st = a.row_stats[h] + row * kStatStride;
-    const float lse = st[0], ent = st[2], lse_t = st[3];
+    const float lse = st[0], ent = st[2], lse_t = st[3], lse_s = st[5];
     const float c_a = a.coef[h][step * kCoefStride + 0] * gscale;
     const float* cf = a.coef[h] + row * kCoefStride;
-    const float c_e = cf[1] * gscale, c_k = cf[2] * gscale;
+    const float c_e = cf[1] * gscale, c_k = cf[2] * gscale, c_d = cf[3] * gscale;
     const float* x = a.logit[h] + row * (long long)K;
     const float* t = a.teacher[h] + row * (long long)K;
+    const float* sc = (a.successive[h] != nullptr && c_d != 0.f) ? a.successive[h] + row * (long long)K : nullptr;
     const int act_idx = (int)a.action[h][row];
     for (int k = tr; k < K; k += THREADS_PER_ROW) {
       const float lp = __ldg(x + k) - lse;
       const float p = expf(lp);
       const float pt = expf(__ldg(t + k) - lse_t);
       float g = -c_a * p - c_e * p * (lp + ent) + c_k * (p - pt);
+      if (sc) g += c_d * (p - expf(__ldg(sc + k) - lse_s));
       if (k == act_idx) g += c_a;
       dx[k] = g;
     }
@@ -421,7 +477,9 @@ static int stats_grid(long long rows, int rpb) {
 
 int loss_forward(const AsLossArgs& a, cudaStream_t st) {
   if (a.T <= 0 || a.B <= 0 || a.F <= 0 || a.F > AS_LOSS_MAX_FIELDS || a.S <= 0) return AS_ESIZE;
-  if (a.F * 10 + 20 >= AS_LOSS_MAX_STATS) return AS_ESIZE;
+  if (a.F * 10 + 26 >= AS_LOSS_MAX_STATS) return AS_ESIZE;
+  for (int h = 1; h < 6; ++h)
+    if ((a.successive[h] != nullptr) != (a.successive[0] != nullptr)) return AS_EINVAL;   // DAPO: all heads or none
   if (a.upgo_field < 0 || a.upgo_field >= a.F) return AS_EINVAL;
   const long long TB = (long long)a.T * a.B;
   for (int h = 0; h < 6; ++h) {
@@ -432,7 +490,7 @@ int loss_forward(const AsLossArgs& a, cudaStream_t st) {
     else loss_row_stats_kernel<32><<<stats_grid(rows, 8), 256, 0, st>>>(a, h, rows, K);
     AS_LAUNCH_CHECK();
   }
-  const int smem = (48 * a.T + a.F * (4 * a.T + 1) + 5 * a.T) * 4;
+  const int smem = (60 * a.T + a.F * (4 * a.T + 1) + 6 * a.T) * 4;
   if (smem > 48 * 1024) return AS_ESIZE;
   loss_scan_kernel<<<a.B, kScanThreads, smem, st>>>(a);
   AS_LAUNCH_CHECK();

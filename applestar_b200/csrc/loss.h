@@ -6,7 +6,7 @@
 #include <stdint.h>
 
 #define AS_LOSS_MAX_FIELDS 6
-#define AS_LOSS_MAX_STATS 96   /* out[0 .. F*10+20) = means, out[AS_LOSS_MAX_STATS-1] = total_loss */
+#define AS_LOSS_MAX_STATS 96   /* out[0 .. F*10+26) = means, out[AS_LOSS_MAX_STATS-1] = total_loss */
 
 typedef struct AsLossArgs {
   int32_t T, B, F, S;            /* unroll length, trajectories, enabled value fields, selected-units rows (64) */
@@ -14,8 +14,10 @@ typedef struct AsLossArgs {
   int32_t head_k[6];             /* logits per row of each head */
   int32_t upgo_field;            /* index of 'winloss' among the F fields */
   float at_kl_steps;             /* extra action-type KL while step < at_kl_steps */
+  float dapo_steps;              /* DAPO KL while step < dapo_steps */
   const float* logit[6];         /* target policy logits  [rows, K] fp32 */
   const float* teacher[6];       /* teacher logits        [rows, K] fp32 */
+  const float* successive[6];    /* DAPO: logits of the successive policy [rows, K] fp32, or all NULL (use_dapo off) */
   float* dlogit[6];              /* out: d total_loss / d logit */
   const int64_t* action[6];      /* taken action per row */
   const float* mu_logp[6];       /* behaviour log-prob per row */
@@ -33,9 +35,10 @@ typedef struct AsLossArgs {
   const float* battle_reward;    /* [T, B] (logged only) */
   float gamma_td[AS_LOSS_MAX_FIELDS];
   float w_pg[AS_LOSS_MAX_FIELDS], w_td[AS_LOSS_MAX_FIELDS];
-  float hw_pg[6], hw_upgo[6], hw_ent[6], hw_kl[6];
-  float w_upgo, w_ent, w_kl, w_atkl;
+  float hw_pg[6], hw_upgo[6], hw_ent[6], hw_kl[6], hw_dapo[6];
+  float w_upgo, w_ent, w_kl, w_atkl, w_dapo;
   const float* stat_weight;      /* [AS_LOSS_MAX_STATS]: total_loss = sum_i stat_weight[i] * means[i] */
+  const float* grad_scale;       /* backward only: device scalar d(objective)/d(total_loss) multiplied into dlogit, or NULL (= 1) */
   /* scratch (caller-provided device memory) */
   float* row_stats[6];           /* [rows, 8] */
   float* coef[6];                /* [rows, 4] */

@@ -96,6 +96,127 @@ su_mask_logits_kernel(const float* __restrict__ x, const long long* __restrict__
   }
 }
 
+// Pointer logits (action_arg_head.py:343-363 target unit, :190-196 selected units): one CTA per row r keeps the row's
+// keys [N, 32] in shared memory; thread n forms <query[r,s,:], key[r,n,:]> for every query step s (queries broadcast
+// from shared memory), applies the key-length mask and the 1/temperature scale, and stores coalesced along n.
+//   out[r,s,n] = n < len[r] ? scale * sum_k q[r,s,k] key[r,n,k] : fill          (len == nullptr: no mask)
+constexpr int kPtrThreads = 256;
+__global__ void __launch_bounds__(kPtrThreads)
+pointer_logits_fwd_kernel(const float* __restrict__ query, const float* __restrict__ key, const long long* __restrict__ len,
+                          float* __restrict__ out, int S, int N, float scale, float fill) {
+  extern __shared__ float psm[];
+  float* s_key = psm;                     // [N][33] (padded: thread n reads row n, conflict-free)
+  float* s_q = psm + (size_t)N * 33;      // [S][32]
+  const long long r = blockIdx.x;
+  const float4* k4 = reinterpret_cast<const float4*>(key + r * (long long)N * 32);
+  for (int i = threadIdx.x; i < N * 8; i += kPtrThreads) {
+    const float4 v = __ldg(k4 + i);
+    float* d = s_key + (i >> 3) * 33 + (i & 7) * 4;
+    d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+  }
+  for (int i = threadIdx.x; i < S * 32; i += kPtrThreads) s_q[i] = __ldg(query + r * (long long)S * 32 + i);
+  __syncthreads();
+  const long long L = len ? len[r] : (long long)N;
+  for (int n = threadIdx.x; n < N; n += kPtrThreads) {
+    float kr[32];
+#pragma unroll
+    for (int k = 0; k < 32; ++k) kr[k] = s_key[n * 33 + k];
+    const bool valid = (long long)n < L;
+    for (int s = 0; s < S; ++s) {
+      float acc = 0.f;
+#pragma unroll
+      for (int k = 0; k < 32; ++k) acc = fmaf(s_q[s * 32 + k], kr[k], acc);
+      out[(r * S + s) * (long long)N + n] = valid ? acc * scale : fill;
+    }
+  }
+}
+
+// dquery[r,s,k] = scale * sum_{n < len} dout[r,s,n] key[r,n,k];   dkey[r,n,k] = scale * sum_s dout[r,s,n] query[r,s,k]
+// (n >= len: zero).  Phase 1: thread n accumulates its dkey row over s; phase 2: warp w owns the steps s = w, w + 8, ...,
+// lane = k, and walks n (keys from shared memory, dout broadcast).  Fixed summation order: deterministic.
+__global__ void __launch_bounds__(kPtrThreads)
+pointer_logits_bwd_kernel(const float* __restrict__ dout, const float* __restrict__ query, const float* __restrict__ key,
+                          const long long* __restrict__ len, float* __restrict__ dquery, float* __restrict__ dkey, int S, int N,
+                          float scale) {
+  extern __shared__ float psm[];
+  float* s_key = psm;
+  float* s_q = psm + (size_t)N * 33;
+  const long long r = blockIdx.x;
+  const float4* k4 = reinterpret_cast<const float4*>(key + r * (long long)N * 32);
+  for (int i = threadIdx.x; i < N * 8; i += kPtrThreads) {
+    const float4 v = __ldg(k4 + i);
+    float* d = s_key + (i >> 3) * 33 + (i & 7) * 4;
+    d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+  }
+  for (int i = threadIdx.x; i < S * 32; i += kPtrThreads) s_q[i] = __ldg(query + r * (long long)S * 32 + i);
+  __syncthreads();
+  const long long Lr = len ? len[r] : (long long)N;
+  const int L = (int)(Lr < 0 ? 0 : (Lr > N ? N : Lr));
+  const float* dro = dout + r * (long long)S * N;
+  if (dkey) {
+    for (int n = threadIdx.x; n < N; n += kPtrThreads) {
+      float acc[32];
+#pragma unroll
+      for (int k = 0; k < 32; ++k) acc[k] = 0.f;
+      if (n < L) {
+        for (int s = 0; s < S; ++s) {
+          const float g = __ldg(dro + (long long)s * N + n) * scale;
+#pragma unroll
+          for (int k = 0; k < 32; ++k) acc[k] = fmaf(g, s_q[s * 32 + k], acc[k]);
+        }
+      }
+      float4* d4 = reinterpret_cast<float4*>(dkey + (r * (long long)N + n) * 32);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) d4[q] = make_float4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]);
+    }
+  }
+  if (dquery) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int s = warp; s < S; s += kPtrThreads / 32) {
+      float acc = 0.f;
+      for (int n0 = 0; n0 < L; n0 += 32) {
+        const float gl = (n0 + lane < L) ? __ldg(dro + (long long)s * N + n0 + lane) : 0.f;   // coalesced, then broadcast
+        const int m = min(32, L - n0);
+        for (int j = 0; j < m; ++j) acc = fmaf(__shfl_sync(0xffffffffu, gl, j), s_key[(n0 + j) * 33 + lane], acc);
+      }
+      dquery[(r * S + s) * 32 + lane] = acc * scale;
+    }
+  }
+}
+
+int pointer_logits_fwd(const float* query, const float* key, const long long* len, float* out, long long R, int S, int N,
+                       int D, float scale, float fill, cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (D != 32 || S <= 0 || S > 64 || N <= 0 || N > 1024) return AS_ESIZE;
+  if (!query || !key || !out) return AS_EINVAL;
+  const size_t smem = ((size_t)N * 33 + (size_t)S * 32) * sizeof(float);
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(pointer_logits_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    cudaFuncSetAttribute(pointer_logits_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    attr = true;
+  }
+  pointer_logits_fwd_kernel<<<(unsigned)R, kPtrThreads, smem, st>>>(query, key, len, out, S, N, scale, fill);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+int pointer_logits_bwd(const float* dout, const float* query, const float* key, const long long* len, float* dquery, float* dkey,
+                       long long R, int S, int N, int D, float scale, cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (D != 32 || S <= 0 || S > 64 || N <= 0 || N > 1024) return AS_ESIZE;
+  if (!dout || !query || !key || (!dquery && !dkey)) return AS_EINVAL;
+  const size_t smem = ((size_t)N * 33 + (size_t)S * 32) * sizeof(float);
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(pointer_logits_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    cudaFuncSetAttribute(pointer_logits_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    attr = true;
+  }
+  pointer_logits_bwd_kernel<<<(unsigned)R, kPtrThreads, smem, st>>>(dout, query, key, len, dquery, dkey, S, N, scale);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
 int su_prefix_fwd(const float* key, const long long* sel, const long long* entity_num, const long long* su_num, float* emb,
                   float* cnt, unsigned char* isnew, long long R, int N1, int D, int Smax, int S, cudaStream_t st) {
   if (R <= 0) return AS_OK;

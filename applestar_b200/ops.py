@@ -277,14 +277,41 @@ def pointer_keys(key, end_embedding, entity_num):
     return torch.where(is_end.unsqueeze(2), end_embedding.view(1, 1, D), key)
 
 
-def pointer_logits(query, key, entity_num, temperature=1.0, extra_mask=None):
-    """logits[r,n] = <query[r], key[r,n]>, keys n >= entity_num masked to -1e9."""
-    logits = torch.einsum('rk,rnk->rn', query, key)
-    mask = torch.arange(key.shape[1], device=key.device).unsqueeze(0) < entity_num.unsqueeze(1)
-    if extra_mask is not None:
-        mask = mask & extra_mask
-    logits = logits.masked_fill(~mask, -1e9)
-    return logits / temperature if temperature != 1.0 else logits
+class _PointerLogits(torch.autograd.Function):
+    """[kernel] out[r,s,n] = n < key_len[r] ? scale * <query[r,s], key[r,n]> : fill (as_pointer_logits_fwd / _bwd)."""
+
+    @staticmethod
+    def forward(ctx, query, key, key_len, scale, fill):
+        R, S, D = query.shape
+        N = key.shape[1]
+        query, key = query.contiguous().float(), key.contiguous().float()
+        kl = None if key_len is None else key_len.contiguous().long()
+        out = torch.empty((R, S, N), dtype=torch.float32, device=query.device)
+        _lib.call('as_pointer_logits_fwd', query.data_ptr(), key.data_ptr(), K._ptr(kl), out.data_ptr(), R, S, N, D,
+                  float(scale), float(fill), _lib.stream_ptr())
+        ctx.dims = (R, S, N, D, float(scale))
+        ctx.save_for_backward(query, key, kl)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        query, key, kl = ctx.saved_tensors
+        R, S, N, D, scale = ctx.dims
+        dout = dout.contiguous().float()
+        dq = torch.empty_like(query) if ctx.needs_input_grad[0] else None
+        dk = torch.empty_like(key) if ctx.needs_input_grad[1] else None
+        if dq is not None or dk is not None:
+            _lib.call('as_pointer_logits_bwd', dout.data_ptr(), query.data_ptr(), key.data_ptr(), K._ptr(kl), K._ptr(dq),
+                      K._ptr(dk), R, S, N, D, scale, _lib.stream_ptr())
+        return dq, dk, None, None, None
+
+
+def pointer_logits(query, key, entity_num, temperature=1.0):
+    """[kernel] logits[r,n] = <query[r], key[r,n]> / temperature, keys n >= entity_num masked to -1e9 / temperature
+    (head/action_arg_head.py:343-363)."""
+    require_cuda(query)
+    inv_t = 1.0 / temperature
+    return _PointerLogits.apply(query.unsqueeze(1), key, entity_num, inv_t, -1e9 * inv_t).squeeze(1)
 
 
 def _su_step(head, ae, h, c):
@@ -371,7 +398,7 @@ def selected_units_train(head, key, ae0, entity_num, selected_units, selected_un
     q = head.query_fc2(head.query_fc1(x.view(S * R, -1))).view(S, R, -1)
     zeros = key.new_zeros(R, q.shape[-1])
     out, _, _ = K.lnlstm_layer(q, zeros, zeros, head.lstm.layers[0].cell)               # [S,R,32]
-    logits = torch.bmm(out.transpose(0, 1), key.transpose(1, 2))                         # [library] [R,S,N1]
+    logits = _PointerLogits.apply(out.transpose(0, 1), key, None, 1.0, 0.0)              # [kernel] [R,S,N1]
     logits = _SUMask.apply(logits, selected_units, entity_num, S, 1.0 / temperature)
     return logits, selected_units, ae_seq[:, S - 1], selected_units_num, None
 

@@ -45,6 +45,7 @@ class _FusedLoss(torch.autograd.Function):
             a.head_k[h] = lg.shape[-1]
             a.logit[h] = lg.data_ptr()
             a.teacher[h] = dptr(inputs['teacher_logit'][name], torch.float32)
+            a.successive[h] = dptr(inputs['successive_logit'][name], torch.float32) if owner.use_dapo else None
             a.action[h] = dptr(inputs['action'][name], torch.int64)
             a.mu_logp[h] = dptr(inputs['action_log_prob'][name], torch.float32)
             a.actions_mask[h] = dptr(mask['actions_mask'][name], torch.int64) if name in _MASKED_HEADS else None
@@ -59,6 +60,7 @@ class _FusedLoss(torch.autograd.Function):
         a.cum_action_mask = dptr(mask['cum_action_mask'], torch.float32)
         a.step = dptr(inputs['step'], torch.float32)
         a.at_kl_steps = float(owner.action_type_kl_steps)
+        a.dapo_steps = float(owner.dapo_steps)
         dvalues = []
         lw = owner.loss_weights
         for f, name in enumerate(fields):
@@ -79,11 +81,13 @@ class _FusedLoss(torch.autograd.Function):
             a.hw_upgo[h] = float(owner.upgo_head_weights[name])
             a.hw_ent[h] = float(owner.entropy_head_weights[name])
             a.hw_kl[h] = float(owner.kl_head_weights[name])
+            a.hw_dapo[h] = float(owner.dapo_head_weights[name])
         only_value = bool(owner.only_update_value)
         a.w_upgo = float(lw['upgo']['winloss'])
         a.w_ent = float(lw['entropy'])
         a.w_kl = float(lw['kl'])
         a.w_atkl = float(lw['action_type_kl'])
+        a.w_dapo = float(lw['dapo']) if owner.use_dapo else 0.0
         F_ = len(fields)
         sw = torch.zeros(_lib.AS_LOSS_MAX_STATS, dtype=torch.float32)
         base = F_ * 10
@@ -92,7 +96,7 @@ class _FusedLoss(torch.autograd.Function):
         if only_value:                      # rl_loss.py:170-171: critic loss only -> policy coefficients vanish
             for f in range(F_):
                 a.w_pg[f] = 0.0
-            a.w_upgo = a.w_ent = a.w_kl = a.w_atkl = 0.0
+            a.w_upgo = a.w_ent = a.w_kl = a.w_atkl = a.w_dapo = 0.0
         else:
             for f in range(F_):
                 for h in range(6):
@@ -102,6 +106,8 @@ class _FusedLoss(torch.autograd.Function):
                 sw[base + 6 + h] = -a.w_ent * a.hw_ent[h]
                 sw[base + 12 + h] = a.w_kl * a.hw_kl[h]
             sw[base + 18] = a.w_atkl
+            for h in range(6):
+                sw[base + 20 + h] = a.w_dapo * a.hw_dapo[h]
         key = (str(dev), tuple(sw.tolist()))
         cache = owner._sw_cache
         if key not in cache:                       # uploaded once: no H2D copy inside a captured step
@@ -110,6 +116,7 @@ class _FusedLoss(torch.autograd.Function):
         sw = cache[key]
         keep.append(sw)
         a.stat_weight = sw.data_ptr()
+        a.grad_scale = None
         partial = torch.empty((B, _lib.AS_LOSS_MAX_STATS), dtype=torch.float32, device=dev)
         out = torch.zeros(_lib.AS_LOSS_MAX_STATS, dtype=torch.float32, device=dev)
         a.partial, a.out = partial.data_ptr(), out.data_ptr()
@@ -125,11 +132,14 @@ class _FusedLoss(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, gtotal, _gout):
-        # grad_scale is applied on the device side of dvalue; dlogit kernels take it as a launch argument.
-        # The usual call is loss.backward() => gtotal == 1 (read lazily: no host sync, use as tensor multiplier).
+        # d(objective)/d(total_loss) (1 for loss.backward()) stays on the device: the gradient kernels read it
+        # through a pointer, so there is neither a host sync nor a separate multiply pass over the 240 MB of dlogits
+        gs = gtotal.detach().reshape(1).float().contiguous()
+        ctx.args.grad_scale = gs.data_ptr()
         _lib.call('as_rl_loss_backward', ctypes.byref(ctx.args), 1.0, _lib.stream_ptr())
         _lib.LAUNCHES += 5
-        grads = [g * gtotal for g in ctx.dlogits] + [g * gtotal for g in ctx.dvalues]
+        ctx.keep.append(gs)
+        grads = list(ctx.dlogits) + [g * gs for g in ctx.dvalues]          # the [T+1, B] value gradients are tiny
         return (None, None, None) + tuple(grads)
 
 
@@ -222,13 +232,17 @@ class ReinforcementLoss:
         self.use_total_rhos = cfg.get('use_total_rhos', False)
 
     def reset(self, learner_cfg):
+        """rl_loss.py:187-199: re-reads the weights; `use_dapo`, `dapo_steps` and the DAPO head weights keep their
+        constructor values there, so they do here."""
+        keep = (self.use_dapo, self.dapo_steps, self.dapo_head_weights, float(self.loss_weights.get('dapo', 0.0)))
         self.cfg = C.AttrDict(C.deep_merge(self.cfg, dict(learner_cfg or {})))
         self._bind()
+        self.use_dapo, self.dapo_steps, self.dapo_head_weights = keep[:3]
         self.only_update_value = False
 
     def compute_loss(self, inputs):
-        if self.use_dapo:
-            raise NotImplementedError('DAPO KL (successive_logit) is not part of the B200 path yet')
+        if self.use_dapo and 'successive_logit' not in inputs:
+            raise KeyError("use_dapo needs inputs['successive_logit'] (rl_loss.py:40)")
         fields = list(inputs['value'].keys())
         if 'winloss' not in fields:
             raise KeyError("the UPGO term needs the 'winloss' baseline (rl_loss.py:112-114)")
@@ -261,5 +275,11 @@ class ReinforcementLoss:
                 tot += sign * s[base + off + h] * float(hw[head])
             info[key + '/total'] = tot
         info['kl/extra_at'] = s[base + 18]
+        if self.use_dapo:                        # as_rl_utils.py:105-127 logs the DAPO terms under 'battle/<head>'
+            tot = 0.0
+            for h, head in enumerate(HEADS):
+                info['battle/%s' % head] = s[base + 20 + h]
+                tot += s[base + 20 + h] * float(self.dapo_head_weights[head])
+            info['battle/total'] = tot
         info['total_loss'] = total
         return info

@@ -243,6 +243,16 @@ int as_su_prefix_bwd(const float* demb, const int64_t* selected_units, const int
 int as_su_mask_logits(const float* x, const int64_t* selected_units, const int64_t* entity_num, float* out, int64_t R, int N1,
                       int Smax, int S, float scale, float fill, void* stream);
 
+/* Pointer logits of the TargetUnit head (head/action_arg_head.py:343-363: `query . key^T`, entity mask, 1/temperature)
+ * and the key product of the SelectedUnits head (:190-196):
+ *   out[r,s,n] = n < key_len[r] ? scale * sum_k query[r,s,k] key[r,n,k] : fill      (key_len NULL: no mask)
+ * query [R,S,32], key [R,N,32], out [R,S,N] fp32, S <= 64, N <= 1024.  The backward gives dquery and / or dkey (either
+ * may be NULL) from dout; masked positions carry no gradient. */
+int as_pointer_logits_fwd(const float* query, const float* key, const int64_t* key_len, float* out, int64_t R, int S, int N, int D,
+                          float scale, float fill, void* stream);
+int as_pointer_logits_bwd(const float* dout, const float* query, const float* key, const int64_t* key_len, float* dquery, float* dkey,
+                          int64_t R, int S, int N, int D, float scale, void* stream);
+
 /* as_attn_fwd: fused attention forward of the entity Transformer (module_utils.py:71-111): out[r,n,h*D:(h+1)*D] =
  * softmax_j(q.k_j * scale, keys j >= key_len[r] filled with -1e9) V over the packed bf16 qkv [R, N, 3*H*D] (q | k | v
  * column blocks).  Scores stay in tensor memory; probs [R,H,N,N] bf16 (optional, NULL at inference) receives the

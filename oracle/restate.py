@@ -538,9 +538,10 @@ def upgo_ret(rewards, values):
     return lambda_returns(rewards, 1.0, values, lam)
 
 
-def compute_loss(cfg, inputs, only_update_value=False):
+def compute_loss(cfg, inputs, only_update_value=False, use_dapo=False):
     """rl_loss.py:33-185. `cfg` = merged learner loss config (dict). Returns the reference's info dict
-    (python floats) with 'total_loss' as an autograd tensor. Mutates value[-1] in place like the reference."""
+    (python floats) with 'total_loss' as an autograd tensor. Mutates value[-1] in place like the reference.
+    `use_dapo`: adds the DAPO term KL(successive || pi) of as_rl_utils.py:105-127 (inputs['successive_logit'])."""
     logits, values = inputs['target_logit'], inputs['value']
     mu_logp, teacher = inputs['action_log_prob'], inputs['teacher_logit']
     mask, action, reward, step = inputs['mask'], inputs['action'], inputs['reward'], inputs['step']
@@ -634,8 +635,23 @@ def compute_loss(cfg, inputs, only_update_value=False):
     info['kl/total'] = float(total_kl.detach())
     total_kl = total_kl * lw['kl']
     at_kl = at_kl * lw['action_type_kl']
+    total_dapo = 0.
+    if use_dapo:
+        flag = (step < cfg['dapo']['dapo_steps'])
+        for h in HEADS:
+            sl = F.log_softmax(inputs['successive_logit'][h], dim=-1)
+            kl = (sl.exp() * (sl - logp_all[h])).sum(-1)
+            if h == 'selected_units':
+                kl = (kl * su_mask).sum(-1)
+            if h not in ('action_type', 'delay'):
+                kl = kl * mask['actions_mask'][h]
+            l = (kl * flag).mean()
+            total_dapo = total_dapo + l * cfg['dapo_head_weights'][h]
+            info['battle/' + h] = l.item()
+        info['battle/total'] = float(total_dapo.detach())
+        total_dapo = total_dapo * lw['dapo']
     if only_update_value:
         info['total_loss'] = total_critic
     else:
-        info['total_loss'] = total_pg + total_upgo + total_critic + total_ent + total_kl + at_kl
+        info['total_loss'] = total_pg + total_upgo + total_critic + total_ent + total_kl + at_kl + total_dapo
     return info

@@ -122,18 +122,27 @@ def _loss_inputs(T, B, N, seed, fields):
     return inputs
 
 
-@pytest.mark.parametrize('fields', [['winloss'], ['winloss', 'build_order', 'built_unit', 'battle']])
-def test_fused_rl_loss_matches_oracle(fields):
-    """fp32 vs fp32: atol 2e-5 on every logged scalar, 1e-3 relative (of the tensor max) on gradients."""
+@pytest.mark.parametrize('fields,dapo', [(['winloss'], False), (['winloss', 'build_order', 'built_unit', 'battle'], False),
+                                         (['winloss'], True), (['winloss', 'build_order', 'built_unit', 'battle'], True)])
+def test_fused_rl_loss_matches_oracle(fields, dapo):
+    """fp32 vs fp32: atol 2e-5 on every logged scalar, 1e-3 relative (of the tensor max) on gradients.  `dapo`: with the
+    DAPO term KL(successive || pi) (as_rl_utils.py:105-127, `use_dapo`), half of the steps below `dapo_steps`."""
     from applestar_b200 import ReinforcementLoss
     T, B, N = 6, 3, 40
     inputs = _loss_inputs(T, B, N, 21, fields)
+    cfg = C.DEFAULT_LOSS_CONFIG
+    if dapo:
+        gen = torch.Generator().manual_seed(5)
+        inputs['successive_logit'] = {k: torch.where(t > -1e8, torch.randn(t.shape, generator=gen), t)
+                                      for k, t in inputs['teacher_logit'].items()}
+        cfg = C.deep_merge(C.DEFAULT_LOSS_CONFIG, {'use_dapo': True, 'dapo': {'dapo_steps': 5000},
+                                                   'dapo_head_weights': {'selected_units': 0.5, 'target_location': 2.0}})
     ref_in = synth.tree_map(lambda t: t.clone(), inputs)
     for k in C.HEADS:
         ref_in['target_logit'][k].requires_grad_(True)
     for f in fields:
         ref_in['value'][f].requires_grad_(True)
-    ref = R.compute_loss(C.DEFAULT_LOSS_CONFIG, ref_in)
+    ref = R.compute_loss(cfg, ref_in, use_dapo=dapo)
     ref['total_loss'].backward()
 
     dev_in = synth.tree_map(lambda t: t.cuda(), inputs)
@@ -141,7 +150,10 @@ def test_fused_rl_loss_matches_oracle(fields):
         dev_in['target_logit'][k].requires_grad_(True)
     for f in fields:
         dev_in['value'][f].requires_grad_(True)
-    info = ReinforcementLoss({}, 'MP0').compute_loss(dev_in)
+    info = ReinforcementLoss(cfg if dapo else {}, 'MP0').compute_loss(dev_in)
+    if dapo:
+        assert abs(float(ref['battle/total'])) > 1e-3 and 'battle/target_location' in info
+        assert not ReinforcementLoss(cfg, 'SP0').use_dapo            # rl_loss.py:22-24: main players only
     info['total_loss'].backward()
     assert set(info) == set(ref)
     for k, v in ref.items():
@@ -152,3 +164,31 @@ def test_fused_rl_loss_matches_oracle(fields):
     for f in fields:
         gr, gd = ref_in['value'][f].grad, dev_in['value'][f].grad.cpu()
         assert (gd - gr).abs().max().item() <= 1e-3 * gr.abs().max().item() + 1e-9, f
+
+
+@pytest.mark.parametrize('R,S,N,masked', [(5, 1, 512, True), (7, 12, 513, False), (3, 64, 40, True)])
+def test_pointer_logits_fwd_bwd(R, S, N, masked):
+    """as_pointer_logits_fwd/_bwd (TargetUnit logits, head/action_arg_head.py:343-363, and the SelectedUnits key product)
+    against fp32 torch: logits and both gradients to fp32 round-off, mask predicate bit-exact."""
+    from applestar_b200 import ops
+    g = torch.Generator().manual_seed(R * 100 + S)
+    q = torch.randn(R, S, 32, generator=g).cuda().requires_grad_(True)
+    k = torch.randn(R, N, 32, generator=g).cuda().requires_grad_(True)
+    ln = torch.randint(1, N + 1, (R,), generator=g).cuda()
+    ln[0] = N
+    scale = 1.0 / 0.8
+    out = ops._PointerLogits.apply(q, k, ln if masked else None, scale, -1e9 * scale)
+    go = torch.randn(R, S, N, generator=g).cuda()
+    out.backward(go)
+    qr, kr = q.detach().clone().requires_grad_(True), k.detach().clone().requires_grad_(True)
+    ref = torch.einsum('rsk,rnk->rsn', qr, kr)
+    if masked:
+        m = torch.arange(N, device='cuda').view(1, 1, N) < ln.view(R, 1, 1)
+        ref = ref.masked_fill(~m, -1e9)
+    ref = ref * scale
+    ref.backward(go)
+    assert torch.equal(out <= -1e8, ref <= -1e8)
+    v = ref > -1e8
+    assert (out[v] - ref[v]).abs().max().item() < 1e-4
+    assert (q.grad - qr.grad).abs().max().item() < 1e-3 * qr.grad.abs().max().item() + 1e-5
+    assert (k.grad - kr.grad).abs().max().item() < 1e-3 * kr.grad.abs().max().item() + 1e-5

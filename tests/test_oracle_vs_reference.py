@@ -85,6 +85,32 @@ def test_only_update_value_matches_reference(ref_model):
 
 
 @reference
+def test_dapo_loss_matches_reference(ref_model):
+    """`use_dapo` (rl_loss.py:40,165-170; as_rl_utils.py:105-127): the oracle's DAPO term against the executed reference."""
+    from easydict import EasyDict
+    from distar.agent.default.rl_training.rl_loss import ReinforcementLoss
+    model, cfg, sd = ref_model
+    data = synth.gen_trajectories(3, 2, 48, 4)
+    lc = C.deep_merge(dict(cfg.learner), {'use_dapo': True, 'dapo': {'dapo_steps': 9000},
+                                          'dapo_head_weights': {'selected_units': 0.5, 'target_location': 2.0}})
+    loss_fn = ReinforcementLoss(EasyDict(lc), 'MP0')
+    assert loss_fn.use_dapo
+    gen = torch.Generator().manual_seed(9)
+    with torch.no_grad():
+        out = model.rl_learner_forward(**clone_tree(data))
+        out['successive_logit'] = {k: torch.where(t > -1e8, torch.randn(t.shape, generator=gen), t)
+                                   for k, t in out['teacher_logit'].items()}
+        mine = R.rl_learner_forward(sd, ['winloss'], **clone_tree(data))
+        mine['successive_logit'] = clone_tree(out['successive_logit'])
+        want = loss_fn.compute_loss(out)
+        got = R.compute_loss(lc, mine, use_dapo=True)
+    assert set(got) == set(want)
+    for k, v in want.items():
+        assert abs(float(got[k]) - float(v)) <= 1e-5 * max(1.0, abs(float(v))), k
+    assert abs(float(want['battle/total'])) > 1e-4
+
+
+@reference
 def test_drop_in_signatures(ref_model):
     """Parameter names and order of the five Model entry methods, the loss and the DistModule surface."""
     from distar.agent.default.model.model import Model as RefModel
