@@ -56,6 +56,8 @@ _SIGS = {
     'as_gemm_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
                              c_int64, c_int64, c_int64, c_int, c_int, c_int64, c_int64, c_int64, c_int64, c_int64,
                              c_int64, c_int, c_int, c_float, c_int, c_void_p, c_int, c_void_p]),
+    'as_gemm_bf16_masked': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int64, c_int64,
+                                    c_int64, c_int, c_float, c_void_p]),
     'as_gemm_splits': (c_int, [c_int, c_int]),
     'as_splitk_reduce': (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
     'as_conv_nhwc_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int,
@@ -87,6 +89,9 @@ _SIGS = {
     'as_su_prefix_fwd': (c_int, [c_void_p] * 7 + [c_int64, c_int, c_int, c_int, c_int, c_void_p]),
     'as_su_prefix_bwd': (c_int, [c_void_p] * 6 + [c_int64, c_int, c_int, c_int, c_int, c_void_p]),
     'as_su_mask_logits': (c_int, [c_void_p] * 4 + [c_int64, c_int, c_int, c_int, c_float, c_float, c_void_p]),
+    'as_conv_weight_layouts': (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    'as_spatial_fc_weight_fwd': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    'as_spatial_fc_weight_bwd': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     'as_pointer_logits_fwd': (c_int, [c_void_p] * 4 + [c_int64, c_int, c_int, c_int, c_float, c_float, c_void_p]),
     'as_pointer_logits_bwd': (c_int, [c_void_p] * 6 + [c_int64, c_int, c_int, c_int, c_float, c_void_p]),
     'as_attn_fwd_ok': (c_int, [c_int, c_int]),
@@ -118,6 +123,8 @@ _SIGS = {
     'as_layer_norm_bwd_scratch_floats': (c_int64, [c_int]),
     'as_layer_norm_bwd': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
+    'as_layer_norm_bwd_fused_scratch_floats': (c_int64, [c_int]),
+    'as_layer_norm_bwd_fused': (c_int, [c_void_p] * 9 + [c_int] + [c_void_p] * 4 + [c_int64, c_int, c_int, c_void_p]),
     'as_lnlstm_fwd': (c_int, [c_void_p] * 13 + [c_int, c_int, c_int, c_void_p]),
     'as_lnlstm_bwd': (c_int, [c_void_p] * 21 + [c_int, c_int, c_int, c_void_p]),
     'as_lnlstm_cluster_ok': (c_int, [c_int]),

@@ -32,6 +32,9 @@ int clip_adam(float*, const float*, float*, float*, void*, long long, float, flo
 int layer_norm_fwd(const float*, const float*, const float*, const float*, float*, void*, float*, long long, int, int,
                    cudaStream_t);
 long long layer_norm_bwd_scratch_floats(int);
+long long layer_norm_bwd_fused_scratch_floats(int);
+int layer_norm_bwd_fused(const float*, const void*, const float*, const float*, const float*, const float*, const float*, float*,
+                         void*, int, float*, float*, float*, float*, long long, int, int, cudaStream_t);
 int layer_norm_bwd(const float*, const void*, const float*, const float*, const float*, const float*, const float*,
                    float*, float*, float*, float*, long long, int, int, cudaStream_t);
 int softmax_fwd(const void*, const long long*, void*, long long, int, int, int, int, cudaStream_t);
@@ -63,6 +66,9 @@ int su_prefix_fwd(const float*, const long long*, const long long*, const long l
 int su_prefix_bwd(const float*, const long long*, const long long*, const float*, const unsigned char*, float*, long long, int, int,
                   int, int, cudaStream_t);
 int su_mask_logits(const float*, const long long*, const long long*, float*, long long, int, int, int, float, float, cudaStream_t);
+int conv_weight_layouts(const float*, void*, void*, int, int, int, int, cudaStream_t);
+int spatial_fc_weight_fwd(const float*, void*, int, int, int, int, cudaStream_t);
+int spatial_fc_weight_bwd(const float*, float*, int, int, int, int, cudaStream_t);
 int pointer_logits_fwd(const float*, const float*, const long long*, float*, long long, int, int, int, float, float, cudaStream_t);
 int pointer_logits_bwd(const float*, const float*, const float*, const long long*, float*, float*, long long, int, int, int, float,
                        cudaStream_t);
@@ -136,6 +142,17 @@ int as_gemm_bf16(const void* A, const void* B, void* C, void* C2, const float* b
   g.a_sb0 = a_sb0; g.a_sb1 = a_sb1; g.b_sb0 = b_sb0; g.b_sb1 = b_sb1; g.c_sb0 = c_sb0; g.c_sb1 = c_sb1;
   g.c_bf16 = c_bf16; g.relu = relu; g.alpha = alpha;
   g.splits = splits; g.ws = ws;
+  return as::gemm_run(g, ST(stream));
+}
+
+int as_gemm_bf16_masked(const void* A, const void* B, void* C, const void* mask, int M, int N, int K, int a_mn, int b_mn, int64_t lda,
+                        int64_t ldb, int64_t ldc, int c_bf16, float alpha, void* stream) {
+  as::GemmCall g;
+  g.A = A; g.B = B; g.C = C; g.mask = mask;
+  g.M = M; g.N = N; g.K = K;
+  g.a_mn = a_mn != 0; g.b_mn = b_mn != 0;
+  g.lda = lda; g.ldb = ldb; g.ldc = ldc;
+  g.c_bf16 = c_bf16; g.alpha = alpha;
   return as::gemm_run(g, ST(stream));
 }
 
@@ -360,6 +377,15 @@ int as_pointer_logits_bwd(const float* dout, const float* query, const float* ke
   return as::pointer_logits_bwd(dout, query, key, reinterpret_cast<const long long*>(key_len), dquery, dkey, R, S, N, D, scale,
                                 ST(stream));
 }
+int as_conv_weight_layouts(const float* weight, void* w_fwd, void* w_dgrad, int cout, int cin, int cin_pad, int taps, void* stream) {
+  return as::conv_weight_layouts(weight, w_fwd, w_dgrad, cout, cin, cin_pad, taps, ST(stream));
+}
+int as_spatial_fc_weight_fwd(const float* weight, void* w16, int out_features, int C, int H, int W, void* stream) {
+  return as::spatial_fc_weight_fwd(weight, w16, out_features, C, H, W, ST(stream));
+}
+int as_spatial_fc_weight_bwd(const float* dw_padded, float* dweight, int out_features, int C, int H, int W, void* stream) {
+  return as::spatial_fc_weight_bwd(dw_padded, dweight, out_features, C, H, W, ST(stream));
+}
 int as_attn_fwd_ok(int N, int D) { return as::attn_fwd_ok(N, D); }
 int as_attn_fwd(const void* qkv, const int64_t* key_len, void* out, void* probs, int64_t R, int N, int H, int D, float scale,
                 void* stream) {
@@ -413,6 +439,13 @@ int as_layer_norm_fwd(const float* x, const float* res, const float* gamma, cons
 
 int64_t as_layer_norm_bwd_scratch_floats(int C) { return as::layer_norm_bwd_scratch_floats(C); }
 
+int64_t as_layer_norm_bwd_fused_scratch_floats(int C) { return as::layer_norm_bwd_fused_scratch_floats(C); }
+int as_layer_norm_bwd_fused(const float* dy32, const void* dy16, const float* x, const float* res, const float* gamma,
+                            const float* beta, const float* stats, float* dx, void* dz16, int mask_x, float* dgamma, float* dbeta,
+                            float* dbias, float* scratch, int64_t rows, int C, int relu, void* stream) {
+  return as::layer_norm_bwd_fused(dy32, dy16, x, res, gamma, beta, stats, dx, dz16, mask_x, dgamma, dbeta, dbias, scratch, rows, C,
+                                  relu, ST(stream));
+}
 int as_layer_norm_bwd(const float* dy32, const void* dy16, const float* x, const float* res, const float* gamma,
                       const float* beta, const float* stats, float* dx, float* dgamma, float* dbeta, float* scratch,
                       int64_t rows, int C, int relu, void* stream) {

@@ -21,6 +21,8 @@ struct GemmCall {
   long long ldc = 0, c_sb0 = 0, c_sb1 = 0;
   const float* bias = nullptr;
   const void* resid = nullptr;   // optional bf16 tensor with C's layout (ldc, batch strides), added before ReLU (TMA-store path)
+  const void* mask = nullptr;    // optional bf16 tensor with C's layout: the output is zeroed where mask <= 0 (the ReLU
+                                 // backward of the layer that produced `mask`, applied to the gradient this GEMM computes)
   int relu = 0;
   float alpha = 1.f;
   int splits = 1;            // >1: fp32 partials to ws[splits][batch][M][N]

@@ -54,6 +54,7 @@ struct GemmDev {
   long long ldc, c_sb0, c_sb1;
   const float* bias;
   const __nv_bfloat16* resid;   // bf16 [.., M, ldc]: added to the accumulator row before ReLU / border masking (or nullptr)
+  const __nv_bfloat16* mask;    // bf16 [.., M, ldc]: output zeroed where mask <= 0 (ReLU backward of the producing layer)
   int relu;
   float alpha;
   float* ws;  // split-K partials
@@ -469,6 +470,22 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               }
             }
           }
+          if (p.mask != nullptr && grow < p.M && gc + 32 <= p.N) {
+            // ReLU backward of the layer whose output `mask` is: keep the gradient where that output was positive
+            const uint4* m4 = reinterpret_cast<const uint4*>(p.mask + (long long)b0 * p.c_sb0 + (long long)b1 * p.c_sb1 +
+                                                             (long long)grow * p.ldc + gc);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const uint4 mv = __ldg(m4 + q);
+              const uint32_t mw[4] = {mv.x, mv.y, mv.z, mv.w};
+#pragma unroll
+              for (int t = 0; t < 4; ++t) {
+                // bf16 > 0  <=>  sign bit clear and magnitude non-zero
+                if (!((mw[t] & 0x7fffu) != 0u && (mw[t] & 0x8000u) == 0u)) f[8 * q + 2 * t] = 0.f;
+                if (!((mw[t] & 0x7fff0000u) != 0u && (mw[t] & 0x80000000u) == 0u)) f[8 * q + 2 * t + 1] = 0.f;
+              }
+            }
+          }
           if (p.relu) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
@@ -854,6 +871,7 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
   if (g.splits > 1 && p.splits != g.splits) return AS_ESIZE;     // caller sizes ws from as_gemm_splits()
   p.C = g.C; p.C2 = g.C2; p.c_bf16 = g.c_bf16; p.ldc = g.ldc; p.c_sb0 = g.c_sb0; p.c_sb1 = g.c_sb1;
   p.resid = reinterpret_cast<const __nv_bfloat16*>(g.resid);
+  p.mask = reinterpret_cast<const __nv_bfloat16*>(g.mask);
   p.bias = g.bias; p.relu = g.relu; p.alpha = g.alpha; p.ws = g.ws;
   p.debug = g_gemm_debug;
   // slab mode for multi-tap convolutions (see the header comment): needs the halo'd slab of a 256-row step to fit two
@@ -924,6 +942,9 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
   // the residual add lives in the TMA-store epilogue only; whole 32-column chunks, 16-byte aligned rows
   if (g.resid != nullptr && (!p.tma_store || (g.N % 32) != 0 || (g.ldc % 8) != 0 ||
                              (reinterpret_cast<uintptr_t>(g.resid) & 15) != 0))
+    return AS_EUNSUPPORTED;
+  if (g.mask != nullptr && (!p.tma_store || (g.N % 32) != 0 || (g.ldc % 8) != 0 ||
+                            (reinterpret_cast<uintptr_t>(g.mask) & 15) != 0))
     return AS_EUNSUPPORTED;
   switch (BN) {
     case 32: return dispatch_major<32>(g.a_mn, g.b_mn, ta, tb, tc, tc2, tb2, p, st);

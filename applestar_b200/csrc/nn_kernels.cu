@@ -142,23 +142,33 @@ layer_norm_fwd_v4_kernel(const float* __restrict__ x, const float* __restrict__ 
   }
 }
 
-template <int V, bool PG>
+template <int V, bool PG, bool DZ = false>
 __global__ void __launch_bounds__(256)
 layer_norm_bwd_v4_kernel(const float* __restrict__ dy32, const __nv_bfloat16* __restrict__ dy16,
                          const float* __restrict__ x, const float* __restrict__ res, const float* __restrict__ gamma,
                          const float* __restrict__ beta, const float* __restrict__ stats, float* __restrict__ dx,
-                         long long rows, int C, int relu, float* __restrict__ pgrad) {
+                         long long rows, int C, int relu, float* __restrict__ pgrad,
+                         __nv_bfloat16* __restrict__ dz16 = nullptr, int mask_x = 0) {
+  // DZ: `x` is the output of a linear layer (bias, optional ReLU) whose backward follows: the kernel also writes that
+  // layer's pre-activation gradient dz16 = bf16(dx (* (x > 0) when mask_x)) -- the operand of its dgrad / wgrad GEMMs --
+  // and accumulates its column sums (the bias gradient) as a third partial row, so no separate pass reads dx again.
   // pgrad != NULL (PG): the parameter gradients are accumulated in the same pass -- every lane owns 4V fixed columns,
   // sums g*xhat and g over the rows of its warp, the block's 8 warps are combined in shared memory and one partial
   // row [2][C] per block goes to pgrad (reduced in fixed order by layer_norm_param_reduce_kernel).
   const int lane = threadIdx.x & 31;
   const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
-  float4 pg[PG ? V : 1], pb[PG ? V : 1];
+  constexpr int NP = DZ ? 3 : 2;
+  float4 pg[PG ? V : 1], pb[PG ? V : 1], pz[DZ ? V : 1];
   if (PG) {
 #pragma unroll
     for (int i = 0; i < V; ++i) { pg[i] = make_float4(0.f, 0.f, 0.f, 0.f); pb[i] = make_float4(0.f, 0.f, 0.f, 0.f); }
   }
+  if (DZ) {
+#pragma unroll
+    for (int i = 0; i < V; ++i) pz[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  bool xpos[DZ ? 4 * V : 1];
   for (long long row = warp_global; row < rows; row += warps_total) {
     const float mean = stats[row * 2], rstd = stats[row * 2 + 1];
     float4 xh[V], dg[V];
@@ -167,6 +177,7 @@ layer_norm_bwd_v4_kernel(const float* __restrict__ dy32, const __nv_bfloat16* __
     for (int i = 0; i < V; ++i) {
       const int idx = lane + i * 32;
       float4 t = __ldg(reinterpret_cast<const float4*>(x + row * C) + idx);
+      if (DZ) { xpos[4 * i] = t.x > 0.f; xpos[4 * i + 1] = t.y > 0.f; xpos[4 * i + 2] = t.z > 0.f; xpos[4 * i + 3] = t.w > 0.f; }
       if (res) { const float4 u = __ldg(reinterpret_cast<const float4*>(res + row * C) + idx); t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w; }
       float4 a = make_float4((t.x - mean) * rstd, (t.y - mean) * rstd, (t.z - mean) * rstd, (t.w - mean) * rstd);
       float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -200,28 +211,66 @@ layer_norm_bwd_v4_kernel(const float* __restrict__ dy32, const __nv_bfloat16* __
       float4 o;
       o.x = rstd * (dg[i].x - m1 - xh[i].x * m2); o.y = rstd * (dg[i].y - m1 - xh[i].y * m2);
       o.z = rstd * (dg[i].z - m1 - xh[i].z * m2); o.w = rstd * (dg[i].w - m1 - xh[i].w * m2);
-      reinterpret_cast<float4*>(dx + row * C)[lane + i * 32] = o;
+      if (dx) reinterpret_cast<float4*>(dx + row * C)[lane + i * 32] = o;
+      if (DZ) {
+        if (mask_x) {
+          o.x = xpos[4 * i] ? o.x : 0.f; o.y = xpos[4 * i + 1] ? o.y : 0.f;
+          o.z = xpos[4 * i + 2] ? o.z : 0.f; o.w = xpos[4 * i + 3] ? o.w : 0.f;
+        }
+        pz[i].x += o.x; pz[i].y += o.y; pz[i].z += o.z; pz[i].w += o.w;
+        __nv_bfloat162 h0 = __floats2bfloat162_rn(o.x, o.y), h1 = __floats2bfloat162_rn(o.z, o.w);
+        uint2 u;
+        u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
+        reinterpret_cast<uint2*>(dz16 + row * C)[lane + i * 32] = u;
+      }
     }
   }
   if (PG) {
-    extern __shared__ float4 s_pg[];                     // [8 warps][2][V*32] float4
+    extern __shared__ float4 s_pg[];                     // [8 warps][NP][V*32] float4
     const int w = threadIdx.x >> 5;
 #pragma unroll
     for (int i = 0; i < V; ++i) {
-      s_pg[(w * 2 + 0) * (V * 32) + lane + i * 32] = pg[i];
-      s_pg[(w * 2 + 1) * (V * 32) + lane + i * 32] = pb[i];
+      s_pg[(w * NP + 0) * (V * 32) + lane + i * 32] = pg[i];
+      s_pg[(w * NP + 1) * (V * 32) + lane + i * 32] = pb[i];
+      if (DZ) s_pg[(w * NP + 2) * (V * 32) + lane + i * 32] = pz[i];
     }
     __syncthreads();
-    for (int j = threadIdx.x; j < 2 * V * 32; j += blockDim.x) {
+    for (int j = threadIdx.x; j < NP * V * 32; j += blockDim.x) {
       const int which = j / (V * 32), col4 = j - which * (V * 32);
       float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
-        const float4 u = s_pg[(k * 2 + which) * (V * 32) + col4];
+        const float4 u = s_pg[(k * NP + which) * (V * 32) + col4];
         t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
       }
-      reinterpret_cast<float4*>(pgrad + ((long long)blockIdx.x * 2 + which) * C)[col4] = t;
+      reinterpret_cast<float4*>(pgrad + ((long long)blockIdx.x * NP + which) * C)[col4] = t;
     }
+  }
+}
+
+// fixed-order reduction of [chunks][3][C] partials -> dgamma, dbeta, dbias
+__global__ void __launch_bounds__(256)
+layer_norm_param_reduce3_kernel(const float* __restrict__ partial, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                float* __restrict__ dbias, int C, int chunks) {
+  const int cx = threadIdx.x & 31, ky = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + cx;
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+  if (c < C)
+    for (int k = ky; k < chunks; k += 8) {
+      a0 += partial[((long long)k * 3 + 0) * C + c];
+      a1 += partial[((long long)k * 3 + 1) * C + c];
+      a2 += partial[((long long)k * 3 + 2) * C + c];
+    }
+  __shared__ float s0[8][33], s1[8][33], s2[8][33];
+  s0[ky][cx] = a0; s1[ky][cx] = a1; s2[ky][cx] = a2;
+  __syncthreads();
+  if (ky == 0 && c < C) {
+    float t0 = 0.f, t1 = 0.f, t2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { t0 += s0[i][cx]; t1 += s1[i][cx]; t2 += s2[i][cx]; }
+    dgamma[c] = t0;
+    dbeta[c] = t1;
+    if (dbias) dbias[c] = t2;
   }
 }
 
@@ -371,6 +420,36 @@ int layer_norm_bwd(const float* dy32, const void* dy16, const float* x, const fl
     layer_norm_param_reduce_kernel<<<(C + 31) / 32, 256, 0, st>>>(scratch, dgamma, dbeta, C, chunks);
     AS_LAUNCH_CHECK();
   }
+  return AS_OK;
+}
+
+// LayerNorm backward of y = LN(res + x) where x = act(linear(...)) is followed directly by that linear layer's backward:
+// one pass gives dx (fp32, the residual-path gradient; may be NULL), dz16 = bf16(dx * (x > 0 if mask_x)), dgamma, dbeta
+// and dbias = column sums of dz.  C = 256 or 384; scratch = as_layer_norm_bwd_fused_scratch_floats(C) floats.
+long long layer_norm_bwd_fused_scratch_floats(int C) { return (long long)kLnChunks * 3 * C; }
+
+int layer_norm_bwd_fused(const float* dy32, const void* dy16, const float* x, const float* res, const float* gamma,
+                         const float* beta, const float* stats, float* dx, void* dz16, int mask_x, float* dgamma,
+                         float* dbeta, float* dbias, float* scratch, long long rows, int C, int relu, cudaStream_t st) {
+  if (rows <= 0) return AS_OK;
+  if (C != 256 && C != 384) return AS_EUNSUPPORTED;
+  if (!x || !gamma || !beta || !stats || (!dy32 && !dy16) || !dz16 || !dgamma || !dbeta || !scratch) return AS_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(res) | reinterpret_cast<uintptr_t>(dy32) |
+       reinterpret_cast<uintptr_t>(gamma) | reinterpret_cast<uintptr_t>(beta) | reinterpret_cast<uintptr_t>(dx) |
+       reinterpret_cast<uintptr_t>(scratch)) & 15) return AS_EALIGN;
+  if ((reinterpret_cast<uintptr_t>(dy16) | reinterpret_cast<uintptr_t>(dz16)) & 7) return AS_EALIGN;
+  const __nv_bfloat16* d16 = reinterpret_cast<const __nv_bfloat16*>(dy16);
+  __nv_bfloat16* z16 = reinterpret_cast<__nv_bfloat16*>(dz16);
+  const int grid = ln_grid(rows);
+  if (C == 256)
+    layer_norm_bwd_v4_kernel<2, true, true><<<grid, 256, 8 * 3 * 64 * 16, st>>>(dy32, d16, x, res, gamma, beta, stats, dx, rows, C,
+                                                                                  relu, scratch, z16, mask_x);
+  else
+    layer_norm_bwd_v4_kernel<3, true, true><<<grid, 256, 8 * 3 * 96 * 16, st>>>(dy32, d16, x, res, gamma, beta, stats, dx, rows, C,
+                                                                                  relu, scratch, z16, mask_x);
+  AS_LAUNCH_CHECK();
+  layer_norm_param_reduce3_kernel<<<(C + 31) / 32, 256, 0, st>>>(scratch, dgamma, dbeta, dbias, C, grid);
+  AS_LAUNCH_CHECK();
   return AS_OK;
 }
 

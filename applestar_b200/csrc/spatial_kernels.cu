@@ -1510,4 +1510,90 @@ int colsum_bf16_static(const void* x, float* out, long long rows, int C, cudaStr
   return colsum_bf16(x, out, g_colsum_static_ptr[dev], rows, C, st);
 }
 
+// bf16 operand layouts of a Conv2d weight [Cout, Cin, k, k] fp32 for the implicit-GEMM kernels, one launch:
+//   w_fwd[co][tap][ci]          (ci < cin_pad, zero beyond Cin)            forward:  A = pixels x (tap, ci)
+//   w_dg [ci][flipped tap][co]  (ci < cin_pad, rows beyond Cin zero)       data gradient: contraction over (tap, co)
+__global__ void conv_weight_layouts_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ w_fwd,
+                                           __nv_bfloat16* __restrict__ w_dg, int cout, int cin, int cin_pad, int taps) {
+  const long long total = (long long)cout * taps * cin_pad;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    {   // forward layout: i = (co * taps + tap) * cin_pad + ci
+      const int ci = (int)(i % cin_pad);
+      const int tap = (int)((i / cin_pad) % taps);
+      const int co = (int)(i / ((long long)cin_pad * taps));
+      const float v = ci < cin ? __ldg(w + ((long long)co * cin + ci) * taps + tap) : 0.f;
+      w_fwd[i] = f2bf(v);
+    }
+    {   // data-gradient layout: i = (ci * taps + tf) * cout + co, tf = flipped tap
+      const int co = (int)(i % cout);
+      const int tf = (int)((i / cout) % taps);
+      const int ci = (int)(i / ((long long)cout * taps));
+      const float v = ci < cin ? __ldg(w + ((long long)co * cin + ci) * taps + (taps - 1 - tf)) : 0.f;
+      w_dg[i] = f2bf(v);
+    }
+  }
+}
+int conv_weight_layouts(const float* w, void* w_fwd, void* w_dg, int cout, int cin, int cin_pad, int taps, cudaStream_t st) {
+  if (cout <= 0 || cin <= 0 || cin_pad < cin || taps <= 0) return AS_ESIZE;
+  if (!w || !w_fwd || !w_dg) return AS_EINVAL;
+  const long long total = (long long)cout * taps * cin_pad;
+  const int grid = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
+  conv_weight_layouts_kernel<<<grid, 256, 0, st>>>(w, (__nv_bfloat16*)w_fwd, (__nv_bfloat16*)w_dg, cout, cin, cin_pad, taps);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+// Spatial-encoder FC weight (spatial_encoder.py:88-89): the reference flattens NCHW (column c*H*W + y*W + x); the
+// activations here are padded NHWC, column ((y+1)*(W+2) + (x+1))*C + c, border columns zero.
+//   fwd: w16[o][padded column] = bf16(w[o][nchw column])            bwd: dw[o][nchw column] = dwp[o][padded column]
+__global__ void spatial_fc_weight_fwd_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ w16, int O, int C, int H,
+                                             int W) {
+  const int pw = W + 2, ph = H + 2;
+  const long long total = (long long)O * ph * pw * C;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int c = (int)(i % C);
+    long long t = i / C;
+    const int px = (int)(t % pw); t /= pw;
+    const int py = (int)(t % ph);
+    const long long o = t / ph;
+    float v = 0.f;
+    if (px >= 1 && px <= W && py >= 1 && py <= H) v = __ldg(w + o * ((long long)C * H * W) + ((long long)c * H + (py - 1)) * W + (px - 1));
+    w16[i] = f2bf(v);
+  }
+}
+__global__ void spatial_fc_weight_bwd_kernel(const float* __restrict__ dwp, float* __restrict__ dw, int O, int C, int H, int W) {
+  const int pw = W + 2, ph = H + 2;
+  const long long total = (long long)O * C * H * W;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  // thread index follows the PADDED (source) layout so that the big read is coalesced; the scattered 4-byte writes of one
+  // warp land in C different 128-byte lines that neighbouring warps complete
+  const long long total_p = (long long)O * ph * pw * C;
+  (void)total;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total_p; i += stride) {
+    const int c = (int)(i % C);
+    long long t = i / C;
+    const int px = (int)(t % pw); t /= pw;
+    const int py = (int)(t % ph);
+    const long long o = t / ph;
+    if (px >= 1 && px <= W && py >= 1 && py <= H)
+      dw[o * ((long long)C * H * W) + ((long long)c * H + (py - 1)) * W + (px - 1)] = __ldg(dwp + i);
+  }
+}
+int spatial_fc_weight_fwd(const float* w, void* w16, int O, int C, int H, int W, cudaStream_t st) {
+  if (O <= 0 || C <= 0 || H <= 0 || W <= 0) return AS_ESIZE;
+  if (!w || !w16) return AS_EINVAL;
+  spatial_fc_weight_fwd_kernel<<<148 * 16, 256, 0, st>>>(w, (__nv_bfloat16*)w16, O, C, H, W);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+int spatial_fc_weight_bwd(const float* dwp, float* dw, int O, int C, int H, int W, cudaStream_t st) {
+  if (O <= 0 || C <= 0 || H <= 0 || W <= 0) return AS_ESIZE;
+  if (!dwp || !dw) return AS_EINVAL;
+  spatial_fc_weight_bwd_kernel<<<148 * 16, 256, 0, st>>>(dwp, dw, O, C, H, W);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
 }  // namespace as

@@ -104,14 +104,17 @@ class LinearFn(torch.autograd.Function):
     (y fp32 | None, y bf16 | None): the bf16 copy (written by the same epilogue) feeds a following GEMM directly."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, relu, want32, want16):
+    def forward(ctx, x, weight, bias, relu, want32, want16, relayout=None):
+        """`relayout` = (w16, unmap): the GEMM reads `w16` (a bf16 re-layout of `weight` for x's column order) and the
+        weight gradient of that layout goes through `unmap` to become d `weight`."""
         ctx.set_materialize_grads(False)        # an unused output copy must not cost a zero fill + an add in backward
         K = x.shape[-1]
         N = weight.shape[0]
         x2 = x.reshape(-1, K)
         M = x2.shape[0]
         x16 = to_bf16(x2)
-        w16 = weight_bf16(weight)
+        w16 = weight_bf16(weight) if relayout is None else relayout[0]
+        ctx.unmap = None if relayout is None else relayout[1]
         y32 = torch.empty((M, N), dtype=torch.float32, device=x.device) if want32 else None
         y16 = torch.empty((M, N), dtype=torch.bfloat16, device=x.device) if want16 else None
         if want32:
@@ -134,7 +137,7 @@ class LinearFn(torch.autograd.Function):
         N = w16.shape[0]
         K8 = w16.shape[1]
         if dy32 is None and dy16 is None:
-            return None, None, None, None, None, None
+            return None, None, None, None, None, None, None
         extra = None
         if dy32 is not None and dy16 is not None:
             if (dy32.dtype == torch.float32 and dy16.dtype == torch.bfloat16 and N % 8 == 0 and dy32.is_contiguous()
@@ -182,11 +185,13 @@ class LinearFn(torch.autograd.Function):
             dx = dx.reshape(ctx.xshape)
         if ctx.needs_input_grad[1]:
             dw = _wgrad(dy16b, x16, N, K8)
-            if K8 != ctx.wk:
+            if ctx.unmap is not None:
+                dw = ctx.unmap(dw)
+            elif K8 != ctx.wk:
                 dw = dw[:, :ctx.wk]
         if want_db:
             db = column_sum(dy2)
-        return dx, dw, db, None, None, None
+        return dx, dw, db, None, None, None, None
 
 
 def column_sum(x):
@@ -221,14 +226,14 @@ def relu_backward(dy, y):
     return dz
 
 
-def linear(x, weight, bias, relu=False, out_bf16=False):
-    y32, y16 = LinearFn.apply(x, weight, bias, relu, not out_bf16, out_bf16)
+def linear(x, weight, bias, relu=False, out_bf16=False, relayout=None):
+    y32, y16 = LinearFn.apply(x, weight, bias, relu, not out_bf16, out_bf16, relayout)
     return y16 if out_bf16 else y32
 
 
 def linear_dual(x, weight, bias, relu=False):
     """-> (fp32, bf16) copies of the same output."""
-    return LinearFn.apply(x, weight, bias, relu, True, True)
+    return LinearFn.apply(x, weight, bias, relu, True, True, None)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -323,6 +328,126 @@ def layer_norm(x, weight, bias, residual=None, relu=False):
 def layer_norm_dual(x, weight, bias, residual=None, relu=False):
     """-> (fp32, bf16) copies of the same normalised rows."""
     return LayerNormFn.apply(x, residual, weight, bias, relu, True, True)
+
+
+def _ln_fwd(z32, res, gamma, beta, relu):
+    rows, C = z32.shape
+    y32 = torch.empty_like(z32)
+    y16 = torch.empty(z32.shape, dtype=torch.bfloat16, device=z32.device)
+    stats = torch.empty((rows, 2), dtype=torch.float32, device=z32.device)
+    _lib.call('as_layer_norm_fwd', z32.data_ptr(), _ptr(res), gamma.data_ptr(), beta.data_ptr(), y32.data_ptr(),
+              y16.data_ptr(), stats.data_ptr(), rows, C, int(relu), _lib.stream_ptr())
+    return y32, y16, stats
+
+
+def _ln_bwd_fused(dy32, dy16, z32, res, gamma, beta, stats, relu_ln, mask_z, want_dres):
+    """-> (dres fp32 | None, dz16, dgamma, dbeta, dbias): as_layer_norm_bwd_fused."""
+    rows, C = z32.shape
+    dev = z32.device
+    dres = torch.empty_like(z32) if want_dres else None
+    dz16 = torch.empty(z32.shape, dtype=torch.bfloat16, device=dev)
+    dgamma, dbeta, dbias = (torch.empty(C, dtype=torch.float32, device=dev) for _ in range(3))
+    scratch = torch.empty(_lib.lib().as_layer_norm_bwd_fused_scratch_floats(C), dtype=torch.float32, device=dev)
+    dy32 = None if dy32 is None else dy32.contiguous().reshape(rows, C)
+    dy16 = None if dy16 is None else dy16.contiguous().reshape(rows, C)
+    _lib.call('as_layer_norm_bwd_fused', _ptr(dy32), _ptr(dy16), z32.data_ptr(), _ptr(res), gamma.data_ptr(), beta.data_ptr(),
+              stats.data_ptr(), _ptr(dres), dz16.data_ptr(), int(mask_z), dgamma.data_ptr(), dbeta.data_ptr(),
+              dbias.data_ptr(), scratch.data_ptr(), rows, C, int(relu_ln), _lib.stream_ptr())
+    return dres, dz16, dgamma, dbeta, dbias
+
+
+class LinearLNFn(torch.autograd.Function):
+    """(y fp32, y bf16) = LN(res + x W^T + b) (+ReLU) -- attention projection + layernorm1 of the post-LN Transformer
+    layer (module_utils.py:133-135) as one autograd node: the LayerNorm backward kernel hands the projection's backward
+    its bf16 operand and bias gradient directly (as_layer_norm_bwd_fused)."""
+
+    @staticmethod
+    def forward(ctx, x, res, weight, bias, gamma, beta, relu_ln):
+        ctx.set_materialize_grads(False)
+        Kd, N = x.shape[-1], weight.shape[0]
+        x16 = to_bf16(x.reshape(-1, Kd))
+        M = x16.shape[0]
+        w16 = weight_bf16(weight)
+        z32 = torch.empty((M, N), dtype=torch.float32, device=x.device)
+        gemm(x16, w16, z32, M, N, x16.shape[1], lda=x16.shape[1], ldb=w16.shape[1], bias=bias)
+        res2 = res.reshape(M, N).contiguous().float()
+        y32, y16, stats = _ln_fwd(z32, res2, gamma, beta, relu_ln)
+        ctx.relu_ln, ctx.xshape, ctx.x_bf16 = relu_ln, x.shape, x.dtype == torch.bfloat16
+        ctx.save_for_backward(x16, w16, z32, res2, gamma, beta, stats)
+        shp = (*x.shape[:-1], N)
+        return y32.view(shp), y16.view(shp)
+
+    @staticmethod
+    def backward(ctx, dy32, dy16):
+        x16, w16, z32, res2, gamma, beta, stats = ctx.saved_tensors
+        if dy32 is None and dy16 is None:
+            return (None,) * 7
+        M, N = z32.shape
+        K8 = w16.shape[1]
+        dres, dz16, dgamma, dbeta, dbias = _ln_bwd_fused(dy32, dy16, z32, res2, gamma, beta, stats, ctx.relu_ln, False,
+                                                         ctx.needs_input_grad[1])
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty((M, K8), dtype=torch.bfloat16 if ctx.x_bf16 else torch.float32, device=z32.device)
+            gemm(dz16, w16, dx, M, K8, N, lda=N, b_mn=True, ldb=K8)
+            dx = dx.reshape(ctx.xshape)
+        if ctx.needs_input_grad[2]:
+            dw = _wgrad(dz16, x16, N, K8)
+        return dx, (None if dres is None else dres.view(*ctx.xshape[:-1], N)), dw, dbias, dgamma, dbeta, None
+
+
+class MLPLNFn(torch.autograd.Function):
+    """(y fp32, y bf16) = LN(res + ReLU(ReLU(x W1^T + b1) W2^T + b2)) (+ReLU) -- the FFN (ReLU on BOTH layers,
+    module_utils.py:121-123) + layernorm2 of the post-LN Transformer layer (:136-139) as one autograd node.  Backward:
+    the LayerNorm kernel emits the masked bf16 gradient and bias gradient of the second layer; the data-gradient GEMM of
+    the second layer applies the first layer's ReLU mask in its epilogue (as_gemm_bf16_masked), so the [rows, hidden]
+    gradient is written once and never re-read by an element-wise pass."""
+
+    @staticmethod
+    def forward(ctx, x, res, w1, b1, w2, b2, gamma, beta, relu_ln):
+        ctx.set_materialize_grads(False)
+        Kd, Hd, N = x.shape[-1], w1.shape[0], w2.shape[0]
+        x16 = to_bf16(x.reshape(-1, Kd))
+        M = x16.shape[0]
+        w1_16, w2_16 = weight_bf16(w1), weight_bf16(w2)
+        h16 = torch.empty((M, Hd), dtype=torch.bfloat16, device=x.device)
+        gemm(x16, w1_16, h16, M, Hd, Kd, lda=Kd, ldb=Kd, bias=b1, relu=True)
+        z32 = torch.empty((M, N), dtype=torch.float32, device=x.device)
+        gemm(h16, w2_16, z32, M, N, Hd, lda=Hd, ldb=Hd, bias=b2, relu=True)
+        res2 = res.reshape(M, N).contiguous().float()
+        y32, y16, stats = _ln_fwd(z32, res2, gamma, beta, relu_ln)
+        ctx.relu_ln, ctx.xshape, ctx.x_bf16 = relu_ln, x.shape, x.dtype == torch.bfloat16
+        ctx.save_for_backward(x16, w1_16, w2_16, h16, z32, res2, gamma, beta, stats)
+        shp = (*x.shape[:-1], N)
+        return y32.view(shp), y16.view(shp)
+
+    @staticmethod
+    def backward(ctx, dy32, dy16):
+        x16, w1_16, w2_16, h16, z32, res2, gamma, beta, stats = ctx.saved_tensors
+        if dy32 is None and dy16 is None:
+            return (None,) * 9
+        M, N = z32.shape
+        Hd, Kd = w1_16.shape
+        dev = z32.device
+        dres, dz2, dgamma, dbeta, db2 = _ln_bwd_fused(dy32, dy16, z32, res2, gamma, beta, stats, ctx.relu_ln, True,
+                                                      ctx.needs_input_grad[1])
+        # d hidden = (dz2 W2) * (h > 0): mask applied in the GEMM epilogue
+        dz1 = torch.empty((M, Hd), dtype=torch.bfloat16, device=dev)
+        _lib.call('as_gemm_bf16_masked', dz2.data_ptr(), w2_16.data_ptr(), dz1.data_ptr(), h16.data_ptr(), M, Hd, N, 0, 1,
+                  N, Hd, Hd, 1, 1.0, _lib.stream_ptr())
+        db1 = column_sum(dz1) if ctx.needs_input_grad[3] else None
+        dw2 = _wgrad(dz2, h16, N, Hd) if ctx.needs_input_grad[4] else None
+        dw1 = _wgrad(dz1, x16, Hd, Kd) if ctx.needs_input_grad[2] else None
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty((M, Kd), dtype=torch.bfloat16 if ctx.x_bf16 else torch.float32, device=dev)
+            gemm(dz1, w1_16, dx, M, Kd, Hd, lda=Hd, b_mn=True, ldb=Kd)
+            dx = dx.reshape(ctx.xshape)
+        return (dx, (None if dres is None else dres.view(*ctx.xshape[:-1], N)), dw1, db1, dw2, db2, dgamma, dbeta, None)
+
+
+def fused_ln_ok(dim, *weights):
+    return dim in (256, 384) and all(w.dim() == 2 and w.shape[1] % 8 == 0 and w.shape[0] % 32 == 0 for w in weights)
 
 
 # dtype of the materialised attention scores S = QK^T/sqrt(d) and of dP = dO V^T.  fp32 keeps the reference's fp32

@@ -52,8 +52,9 @@ class FCLN(nn.Sequential):
 
 
 class Conv(nn.Sequential):
-    """conv2d_block (no norm): `.0` = Conv2d.  `nhwc=True`: implicit GEMM on the tcgen05 kernel over a zero-padded
-    NHWC bf16 map (spatial.py); otherwise the [library] NCHW path."""
+    """conv2d_block (no norm): `.0` = Conv2d, run as an implicit GEMM on the tcgen05 kernel over a zero-padded NHWC bf16
+    map (spatial.py).  The one convolution built with `nhwc=False` (the location head's final 32 -> 1 layer) only holds
+    the parameters: its arithmetic is spatial.conv_c32_to_1."""
 
     def __init__(self, cin, cout, k, pad, relu=False, nhwc=False):
         super().__init__(nn.Conv2d(cin, cout, k, 1, pad))
@@ -61,9 +62,9 @@ class Conv(nn.Sequential):
         self.relu, self.pad, self.nhwc = relu, pad, nhwc
 
     def forward(self, x):
-        if self.nhwc:
-            return spatial.conv(x, self[0].weight, self[0].bias, self.relu)
-        return ops.conv2d(x, self[0].weight, self[0].bias, self.pad, self.relu)
+        if not self.nhwc:
+            raise RuntimeError('this convolution is evaluated by its owner (no library convolution path exists)')
+        return spatial.conv(x, self[0].weight, self[0].bias, self.relu)
 
     def fork(self, x):
         """-> (self(x), x'): x' aliases x and must replace it in x's OTHER consumers, so that their gradient is added to
@@ -118,7 +119,13 @@ class TransformerLayer(nn.Module):
     def forward(self, x32, x16, key_len, final_relu=False):
         """(fp32 residual stream, bf16 GEMM operand) in and out."""
         l1, l2 = self.layernorm1, self.layernorm2
-        if self.post_ln:     # module_utils.py:133-139
+        if self.post_ln and ops.transformer_layer_fused_ok(self):     # module_utils.py:133-139, two fused autograd nodes
+            att = self.attention
+            a = ops.attention(att.attention_pre(x16), key_len, att.head_num, att.head_dim)
+            pj, f1, f2 = att.project[0], self.mlp[0][0], self.mlp[1][0]
+            x32, x16 = ops.linear_ln(a, x32, pj.weight, pj.bias, l1.weight, l1.bias)
+            x32, x16 = ops.mlp_ln(x16, x32, f1.weight, f1.bias, f2.weight, f2.bias, l2.weight, l2.bias, final_relu)
+        elif self.post_ln:
             x32, x16 = ops.layer_norm_dual(self.attention(x16, key_len), l1.weight, l1.bias, residual=x32)
             x32, x16 = ops.layer_norm_dual(self.mlp(x16), l2.weight, l2.bias, residual=x32, relu=final_relu)
         else:                # :140-148
@@ -206,8 +213,7 @@ class SpatialEncoder(nn.Module):
             skip.append(x)
             x = block(x)
         H8, W8 = C.SPATIAL_Y // 8, C.SPATIAL_X // 8
-        w = spatial.spatial_fc_weight(self.fc[0].weight, 128, H8, W8)
-        return ops.linear(x.reshape(x.shape[0], -1), w, self.fc[0].bias, True), skip
+        return spatial.spatial_fc(x, self.fc[0].weight, self.fc[0].bias, 128, H8, W8), skip
 
 
 class BeginningBuildOrderEncoder(nn.Module):

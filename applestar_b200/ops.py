@@ -1,8 +1,8 @@
 """Operator layer of the hot path.
 
 Every function here runs on the GPU only.  Ops marked [kernel] launch this repo's sm_100a kernels
-through the C-ABI (applestar_b200/_lib.py -> libapplestar_b200.so); ops marked [library] still call
-stock ATen/cuBLAS/cuDNN CUDA ops and are the replacement queue documented in DESIGN.md.  Nothing
+through the C-ABI (applestar_b200/_lib.py -> libapplestar_b200.so); the few small element-wise / gather
+ops that still go through ATen (scalar-encoder embeddings, gates, glue) are listed in DESIGN.md §7.  Nothing
 falls back to the CPU: `require_cuda` raises, and `_lib` raises if the shared library is missing.
 """
 import math
@@ -40,14 +40,22 @@ def layer_norm_dual(x, weight, bias, residual=None, relu=False):
     return K.layer_norm_dual(x, weight, bias, residual, relu)
 
 
-def conv2d(x, weight, bias, pad, relu=False):
-    """[library] cuDNN conv (+ReLU)."""
-    y = F.conv2d(x, weight, bias, padding=pad)
-    return F.relu(y) if relu else y
+def transformer_layer_fused_ok(layer):
+    pj, f1, f2 = layer.attention.project[0], layer.mlp[0][0], layer.mlp[1][0]
+    return (os.environ.get('APPLESTAR_FUSED_LAYER', '1') != '0'
+            and K.fused_ln_ok(pj.weight.shape[0], pj.weight, f1.weight, f2.weight))
 
 
-def relu(x):
-    return F.relu(x)
+def linear_ln(x, res, weight, bias, gamma, beta, relu_ln=False):
+    """[kernel] (fp32, bf16) = LN(res + x W^T + b) as one autograd node (kernels.LinearLNFn)."""
+    require_cuda(x)
+    return K.LinearLNFn.apply(x, res, weight, bias, gamma, beta, relu_ln)
+
+
+def mlp_ln(x, res, w1, b1, w2, b2, gamma, beta, relu_ln=False):
+    """[kernel] (fp32, bf16) = LN(res + ReLU(ReLU(x W1^T + b1) W2^T + b2)) as one autograd node (kernels.MLPLNFn)."""
+    require_cuda(x)
+    return K.MLPLNFn.apply(x, res, w1, b1, w2, b2, gamma, beta, relu_ln)
 
 
 def add_relu(a, b):
@@ -60,19 +68,6 @@ def sigmoid_gate(gate_pre, x):
 
 def atan_squash(v):
     return (2.0 / math.pi) * torch.atan((math.pi / 2.0) * v)
-
-
-def max_pool2(x):
-    return F.max_pool2d(x, 2, 2)
-
-
-def upsample_bilinear2(x):
-    return F.interpolate(x, scale_factor=2., mode='bilinear')
-
-
-def gated_residual(r, g, update_sp, x):
-    """GatedResBlock tail: ReLU(tanh(r * sigmoid(g)) * UpdateSP + x)."""
-    return F.relu(torch.tanh(r * torch.sigmoid(g)) * update_sp + x)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -162,27 +157,6 @@ def scatter_connection(proj, x, y, entity_num, H, W, scatter_type='add'):
     entity order per cell.  proj [R,N,D] fp32, x/y [R,N] integer -> [R,D,H,W] fp32."""
     require_cuda(proj)
     return K.ScatterConnection.apply(proj, x, y, entity_num, H, W, scatter_type)
-
-
-# ---------------------------------------------------------------------------------------------
-# spatial path
-_EFFECTS = [n for n, arc, _ in C.SPATIAL_FIELDS if arc == 'scatter']
-_ONE_HOT_PLANES = [(n, k) for n, arc, k in C.SPATIAL_FIELDS if arc == 'one_hot']
-
-
-def spatial_project(spatial_info, scatter_map, weight, bias):
-    """1x1 conv 56->32 + ReLU over the on-the-fly 56-channel input (spatial_encoder.py:52-72)."""
-    hm = spatial_info['height_map']
-    R, H, W = hm.shape
-    planes = [hm.float().unsqueeze(1) / 256]
-    for name, num in _ONE_HOT_PLANES:
-        planes.append(F.one_hot(spatial_info[name].long(), num).permute(0, 3, 1, 2).float())
-    for name in _EFFECTS:
-        e = torch.zeros(R, H * W, device=hm.device)
-        e.scatter_(1, spatial_info[name].long(), 1.0)          # zero padding => pixel (0,0) set (App. A7)
-        planes.append(e.view(R, 1, H, W))
-    planes.append(scatter_map)
-    return F.relu(F.conv2d(torch.cat(planes, dim=1), weight, bias))
 
 
 # ---------------------------------------------------------------------------------------------

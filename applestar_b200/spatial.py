@@ -24,12 +24,12 @@ def _conv_weights(weight, cin_pad):
     hit = getattr(weight, '_as_conv16', None)
     if hit is not None and hit[0] == tag:
         return hit[1], hit[2]
-    w = weight.detach()
+    w = weight.detach().contiguous()
     cout, cin, kh, kw = w.shape
-    if cin_pad > cin:
-        w = F.pad(w, (0, 0, 0, 0, 0, cin_pad - cin))
-    w_fwd = w.permute(0, 2, 3, 1).reshape(cout, kh * kw * cin_pad).contiguous().to(torch.bfloat16)
-    w_dg = w.flip(2, 3).permute(1, 2, 3, 0).reshape(cin_pad, kh * kw * cout).contiguous().to(torch.bfloat16)
+    w_fwd = torch.empty((cout, kh * kw * cin_pad), dtype=torch.bfloat16, device=w.device)
+    w_dg = torch.empty((cin_pad, kh * kw * cout), dtype=torch.bfloat16, device=w.device)
+    _lib.call('as_conv_weight_layouts', w.data_ptr(), w_fwd.data_ptr(), w_dg.data_ptr(), cout, cin, cin_pad, kh * kw,
+              _lib.stream_ptr())
     try:
         weight._as_conv16 = (tag, w_fwd, w_dg)
     except AttributeError:
@@ -307,13 +307,31 @@ def conv_c32_to_1(x, weight, bias, inv_temp=1.0):
     return ConvC32To1.apply(x, weight, bias, inv_temp)
 
 
-def spatial_fc_weight(weight, ch, H, W):
-    """Linear weight over the NCHW flatten (index c*H*W + y*W + x, spatial_encoder.py:88) re-indexed for the padded
-    NHWC flatten ((y+1)*(W+2) + (x+1))*ch + c with zero columns on the border.  Differentiable torch view ops."""
+def spatial_fc(x, weight, bias, ch, H, W):
+    """ReLU(fc) of the spatial encoder (spatial_encoder.py:88-89) over a padded NHWC bf16 map x [R, H+2, W+2, ch].  The
+    reference's weight is laid out for the NCHW flatten (column c*H*W + y*W + x); the GEMM reads a bf16 re-layout for
+    the padded NHWC flatten, column ((y+1)*(W+2) + (x+1))*ch + c, border columns zero (as_spatial_fc_weight_fwd, cached
+    until the weight changes), and the weight gradient of that layout is mapped back by as_spatial_fc_weight_bwd."""
     out = weight.shape[0]
-    w = weight.view(out, ch, H, W).permute(0, 2, 3, 1)
-    w = F.pad(w, (0, 0, 1, 1, 1, 1))
-    return w.reshape(out, (H + 2) * (W + 2) * ch)
+    tag = (K._SHADOW_GEN[0], weight._version, weight.data_ptr())
+    hit = getattr(weight, '_as_fc16', None)
+    if hit is None or hit[0] != tag:
+        w = weight.detach().contiguous()
+        w16 = torch.empty((out, (H + 2) * (W + 2) * ch), dtype=torch.bfloat16, device=w.device)
+        _lib.call('as_spatial_fc_weight_fwd', w.data_ptr(), w16.data_ptr(), out, ch, H, W, _lib.stream_ptr())
+        hit = (tag, w16)
+        try:
+            weight._as_fc16 = hit
+        except AttributeError:
+            pass
+
+    def unmap(dwp):
+        dwp = dwp.contiguous()
+        dw = torch.empty((out, ch * H * W), dtype=torch.float32, device=dwp.device)
+        _lib.call('as_spatial_fc_weight_bwd', dwp.data_ptr(), dw.data_ptr(), out, ch, H, W, _lib.stream_ptr())
+        return dw
+
+    return K.linear(x.reshape(x.shape[0], -1), weight, bias, True, relayout=(hit[1], unmap))
 
 
 class MaxPool2(torch.autograd.Function):

@@ -54,6 +54,14 @@ int as_gemm_bf16(const void* A, const void* B, void* C, void* C2, const float* b
                  int b_k_shift, void* stream);
 /* Number of non-empty K splits the kernel will produce when `want` are requested. */
 int as_gemm_splits(int K, int want);
+/* as_gemm_bf16_masked: C = alpha * A B^T (same operand conventions as as_gemm_bf16, no batch / bias) with the ReLU
+ * backward of the layer that feeds on C folded into the epilogue: C[m][n] is written as zero where mask[m][n] <= 0
+ * (mask = that layer's bf16 output, C's layout).  Used for d hidden of the Transformer FFN (module_utils.py:121-123:
+ * ReLU on both layers): autograd's threshold_backward pass over the [rows, 1024] gradient disappears.
+ * Needs N % 32 == 0, ldc % 8 == 0 and 16-byte aligned C / mask. */
+int as_gemm_bf16_masked(const void* A, const void* B, void* C, const void* mask, int M, int N, int K, int a_mn, int b_mn, int64_t lda,
+                        int64_t ldb, int64_t ldc, int c_bf16, float alpha, void* stream);
+
 /* out[i] = (accumulate ? out[i] : 0) + sum_s ws[s][i], s ascending (deterministic). */
 int as_splitk_reduce(const float* ws, float* out, int64_t n, int splits, int accumulate, void* stream);
 
@@ -190,6 +198,16 @@ int as_layer_norm_bwd(const float* dy32, const void* dy16, const float* x, const
                       const float* beta, const float* stats, float* dx, float* dgamma, float* dbeta, float* scratch,
                       int64_t rows, int C, int relu, void* stream);
 
+/* as_layer_norm_bwd_fused: backward of y = LN(res + x) where x is the output of a linear layer (post-LN Transformer:
+ * module_utils.py:133-139, x = attention projection or FFN output) whose own backward follows.  One pass yields the
+ * residual-path gradient dx (fp32, may be NULL), the linear layer's pre-activation gradient dz16 = bf16(dx * (x > 0))
+ * (mask_x != 0 when that layer has a ReLU), dgamma / dbeta and dbias = column sums of dz, replacing autograd's
+ * threshold_backward + cast + bias `.sum(0)` passes.  C = 256 or 384. */
+int64_t as_layer_norm_bwd_fused_scratch_floats(int C);
+int as_layer_norm_bwd_fused(const float* dy32, const void* dy16, const float* x, const float* res, const float* gamma,
+                            const float* beta, const float* stats, float* dx, void* dz16, int mask_x, float* dgamma, float* dbeta,
+                            float* dbias, float* scratch, int64_t rows, int C, int relu, void* stream);
+
 /* LayerNorm-LSTM recurrence over a whole unroll, one CTA per trajectory -- replaces the Python time loop of
  * LSTMLayer / LayerNormLSTMCell (model/lstm.py:138-167; 65 x 3 cell calls per learner step).
  * gi [T,B,4H] = LN_i(x W_ih^T) for all t (computed by as_gemm_bf16 + as_layer_norm_fwd), h0/c0 [B,H],
@@ -242,6 +260,17 @@ int as_su_prefix_bwd(const float* demb, const int64_t* selected_units, const int
                      float* dkey, int64_t R, int N1, int D, int Smax, int S, void* stream);
 int as_su_mask_logits(const float* x, const int64_t* selected_units, const int64_t* entity_num, float* out, int64_t R, int N1,
                       int Smax, int S, float scale, float fill, void* stream);
+
+/* bf16 GEMM-operand layouts of a Conv2d weight [Cout, Cin, k, k] fp32 (ctools/torch_utils/network/nn_module.py:119-174
+ * holds it in that layout) for as_conv_nhwc_bf16: w_fwd [Cout][tap][cin_pad] (forward) and w_dgrad
+ * [cin_pad][flipped tap][Cout] (data gradient), channels beyond Cin zero.  taps = k * k. */
+int as_conv_weight_layouts(const float* weight, void* w_fwd, void* w_dgrad, int cout, int cin, int cin_pad, int taps, void* stream);
+
+/* Spatial-encoder FC weight (obs_encoder/spatial_encoder.py:88-89, [out, C*H*W] over the NCHW flatten) re-indexed for
+ * the zero-padded NHWC activation layout: w16 [out, (H+2)*(W+2)*C] bf16 (border columns zero); the backward maps the
+ * weight gradient of that layout back to [out, C*H*W] fp32. */
+int as_spatial_fc_weight_fwd(const float* weight, void* w16, int out_features, int C, int H, int W, void* stream);
+int as_spatial_fc_weight_bwd(const float* dw_padded, float* dweight, int out_features, int C, int H, int W, void* stream);
 
 /* Pointer logits of the TargetUnit head (head/action_arg_head.py:343-363: `query . key^T`, entity mask, 1/temperature)
  * and the key product of the SelectedUnits head (:190-196):

@@ -220,3 +220,47 @@ def test_lnlstm_layer_fwd_bwd_vs_oracle_cell(T, B, I, H):
                             (cell.layernorm_i.weight.grad, sd['c.layernorm_i.weight'].grad, 'lni.w')):
         err = (got.cpu() - want).abs().max().item()
         assert err < 0.08 * want.abs().max().item() + 2e-3, (name, err, want.abs().max().item())
+
+
+@pytest.mark.parametrize('relu_ln', [False, True])
+def test_fused_transformer_layer_nodes_vs_torch(relu_ln):
+    """ops.linear_ln / ops.mlp_ln (attention projection + LN1, FFN + LN2 of the post-LN layer, module_utils.py:121-139,
+    each ONE autograd node whose LayerNorm backward feeds the linear backward, hidden ReLU mask in the GEMM epilogue)
+    against plain fp32 torch: outputs and every gradient (bf16 GEMMs -> 2% of the tensor's max)."""
+    import torch.nn.functional as F
+    from applestar_b200 import ops
+    g = torch.Generator().manual_seed(3)
+    M, D, Hd = 1500, 256, 1024
+    def rnd(*s, scale=1.0):
+        return (torch.randn(*s, generator=g) * scale).cuda()
+    a16 = rnd(M, D).to(torch.bfloat16).requires_grad_(True)
+    res = rnd(M, D).requires_grad_(True)
+    wp, bp = rnd(D, D, scale=0.06).requires_grad_(True), rnd(D, scale=0.1).requires_grad_(True)
+    w1, b1 = rnd(Hd, D, scale=0.06).requires_grad_(True), rnd(Hd, scale=0.1).requires_grad_(True)
+    w2, b2 = rnd(D, Hd, scale=0.03).requires_grad_(True), rnd(D, scale=0.1).requires_grad_(True)
+    g1, be1 = (1 + rnd(D, scale=0.1)).requires_grad_(True), rnd(D, scale=0.1).requires_grad_(True)
+    g2, be2 = (1 + rnd(D, scale=0.1)).requires_grad_(True), rnd(D, scale=0.1).requires_grad_(True)
+    leaves = [a16, res, wp, bp, w1, b1, w2, b2, g1, be1, g2, be2]
+    x32, x16 = ops.linear_ln(a16, res, wp, bp, g1, be1)
+    y32, y16 = ops.mlp_ln(x16, x32, w1, b1, w2, b2, g2, be2, relu_ln)
+    go32, go16 = rnd(M, D), rnd(M, D).to(torch.bfloat16)
+    torch.autograd.backward([y32, y16], [go32, go16])
+    mine = [t.grad.float().clone() for t in leaves]
+    for t in leaves:
+        t.grad = None
+    # fp32 torch restatement (bf16 rounding only where the kernels round: GEMM operands)
+    def q(t):
+        return t.to(torch.bfloat16).float()
+    xr = F.layer_norm(res + F.linear(a16.float(), q(wp), bp), (D,), g1, be1)
+    h = F.relu(F.linear(q(xr), q(w1), b1))
+    z = F.relu(F.linear(q(h), q(w2), b2))
+    yr = F.layer_norm(xr + z, (D,), g2, be2)
+    if relu_ln:
+        yr = F.relu(yr)
+    assert (y32 - yr).abs().max().item() < 0.03 and (y16.float() - yr).abs().max().item() < 0.06
+    torch.autograd.backward([yr], [go32 + go16.float()])
+    names = ['a16', 'res', 'wp', 'bp', 'w1', 'b1', 'w2', 'b2', 'g1', 'be1', 'g2', 'be2']
+    for nm, t, m in zip(names, leaves, mine):
+        r = t.grad.float()
+        rel = ((m - r).norm() / r.norm()).item()
+        assert rel < 0.02, (nm, rel)
