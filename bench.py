@@ -599,7 +599,7 @@ def run_ours(args):
             k = r[3]
             t = agg.setdefault(k, [0, 0.0, 0.0])
             t[0] += 1; t[1] += r[0].elapsed_time(r[1]); t[2] += r[2]
-        for k, t in sorted(agg.items(), key=lambda kv: -kv[1][1])[:45]:
+        for k, t in sorted(agg.items(), key=lambda kv: -kv[1][1])[:120]:
             print('GEMM %-22s args=%s n=%d ms=%.3f TF/s=%.0f' % (k[0], k[1:], t[0], t[1], t[2] / t[1] / 1e9), file=sys.stderr)
     hbm, tf_burst, tf_sus, which = peaks()
     achieved = alg_fl / (g_ms * 1e-3) / 1e12 if g_ms > 0 else 0.0            # ALGORITHMIC flops

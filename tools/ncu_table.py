@@ -5,7 +5,9 @@ import re
 import sys
 from collections import OrderedDict
 
-rows = list(csv.reader(open(sys.argv[1])))
+import gzip
+opener = gzip.open if sys.argv[1].endswith('.gz') else open
+rows = [r for r in csv.reader(l for l in opener(sys.argv[1], 'rt') if not l.startswith('==') and l.strip() != 'ok')]
 peak = float(sys.argv[2]) if len(sys.argv) > 2 else 6548.8
 hdr = rows[0]
 col = {h: i for i, h in enumerate(hdr)}
