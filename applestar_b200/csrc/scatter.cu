@@ -87,26 +87,27 @@ scatter_fwd_kernel(const float* __restrict__ emb, const IdxT* __restrict__ xs, c
     }
   }
   __syncthreads();
-  // 4. stream the planes: one cell-map read per group of 4 cells serves all DG channels (no index division in the
-  //    loop, one shared-memory read per 16 * DG bytes written); each channel's store is 512 contiguous bytes per warp
+  // 4. stream the planes, ONE CHANNEL AT A TIME: the CTA writes a plane (H*W*4 bytes, contiguous) front to back with
+  //    16-byte stores before it starts the next one, so that the few hundred CTAs in flight are a few hundred linear
+  //    write streams (DRAM page locality) instead of DG interleaved streams each.  The cell map (shared memory) is
+  //    re-read per channel; zeros are written by the same pass.
   const int q4 = HW / 4;                                                     // HW % 4 == 0 checked on host
   float* obase = out + ((long long)r * D + d0) * HW;
-  for (int p4 = tid; p4 < q4; p4 += kScatterThreads) {
-    const uint2 m = *reinterpret_cast<const uint2*>(cellmap + p4 * 4);
-    if ((m.x | m.y) == 0u) {
-#pragma unroll
-      for (int c = 0; c < DG; ++c) __stcs(reinterpret_cast<float4*>(obase + (long long)c * HW) + p4, make_float4(0.f, 0.f, 0.f, 0.f));
-    } else {
-      const uint32_t m0 = m.x & 0xFFFFu, m1 = m.x >> 16, m2 = m.y & 0xFFFFu, m3 = m.y >> 16;
-#pragma unroll
-      for (int c = 0; c < DG; ++c) {
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+  for (int c = 0; c < DG; ++c) {
+    float4* plane = reinterpret_cast<float4*>(obase + (long long)c * HW);
+#pragma unroll 4
+    for (int p4 = tid; p4 < q4; p4 += kScatterThreads) {
+      const uint2 m = *reinterpret_cast<const uint2*>(cellmap + p4 * 4);
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if ((m.x | m.y) != 0u) {
+        const uint32_t m0 = m.x & 0xFFFFu, m1 = m.x >> 16, m2 = m.y & 0xFFFFu, m3 = m.y >> 16;
         if (m0) v.x = segsum[(m0 - 1) * DG + c];
         if (m1) v.y = segsum[(m1 - 1) * DG + c];
         if (m2) v.z = segsum[(m2 - 1) * DG + c];
         if (m3) v.w = segsum[(m3 - 1) * DG + c];
-        __stcs(reinterpret_cast<float4*>(obase + (long long)c * HW) + p4, v);
       }
+      plane[p4] = v;
     }
   }
 }
