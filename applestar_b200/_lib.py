@@ -89,6 +89,13 @@ _SIGS = {
     'as_su_prefix_fwd': (c_int, [c_void_p] * 7 + [c_int64, c_int, c_int, c_int, c_int, c_void_p]),
     'as_su_prefix_bwd': (c_int, [c_void_p] * 6 + [c_int64, c_int, c_int, c_int, c_int, c_void_p]),
     'as_su_mask_logits': (c_int, [c_void_p] * 4 + [c_int64, c_int, c_int, c_int, c_float, c_float, c_void_p]),
+    'as_spatial_front_fwd': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p,
+                                     c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
+    'as_spatial_front_cells_bytes': (c_int64, [c_int64]),
+    'as_spatial_front_bwd_scratch_floats': (c_int64, [c_int64, c_int]),
+    'as_spatial_front_bwd': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p,
+                                     c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int,
+                                     c_int, c_void_p]),
     'as_conv_weight_layouts': (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     'as_spatial_fc_weight_fwd': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     'as_spatial_fc_weight_bwd': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
@@ -104,6 +111,7 @@ _SIGS = {
     'as_conv_wgrad_pair_mode': (c_int, [c_int, c_int, c_int, c_int, c_int]),
     'as_conv_wgrad_ws_floats': (c_int64, [c_int, c_int, c_int, c_int, c_int]),
     'as_conv_nhwc_bf16_add': (c_int, [c_void_p] * 5 + [c_int64, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    'as_conv_nhwc_bf16_masked': (c_int, [c_void_p] * 5 + [c_int64, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     'as_su_sample': (c_int, [POINTER(AsSuSampleArgs), c_void_p]),
     'as_masked_mean_fwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
     'as_masked_mean_bwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
@@ -117,7 +125,7 @@ _SIGS = {
     'as_scatter_connection_bwd_pnhwc': (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int64,
                                                 c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     'as_maxpool2_fwd_bf16': (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p]),
-    'as_maxpool2_bwd_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p]),
+    'as_maxpool2_bwd_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p]),
     'as_layer_norm_fwd': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int,
                                   c_int, c_void_p]),
     'as_layer_norm_bwd_scratch_floats': (c_int64, [c_int]),

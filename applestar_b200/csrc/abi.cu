@@ -67,6 +67,13 @@ int su_prefix_bwd(const float*, const long long*, const long long*, const float*
                   int, int, cudaStream_t);
 int su_mask_logits(const float*, const long long*, const long long*, float*, long long, int, int, int, float, float, cudaStream_t);
 int conv_weight_layouts(const float*, void*, void*, int, int, int, int, cudaStream_t);
+int spatial_front_fwd(const void* const*, const void* const*, int, const float*, const void*, const void*, int, const long long*, int,
+                      const float*, const float*, void*, void*, void*, long long, int, int, cudaStream_t);
+long long spatial_front_cells_bytes(long long);
+long long spatial_front_bwd_scratch_floats(long long, int);
+int spatial_front_bwd(const void* const*, const void* const*, int, const float*, const void*, const void*, int, const long long*, int,
+                      const float*, const float*, const void*, const void*, const void*, float*, float*, float*, float*, long long, int,
+                      int, cudaStream_t);
 int spatial_fc_weight_fwd(const float*, void*, int, int, int, int, cudaStream_t);
 int spatial_fc_weight_bwd(const float*, float*, int, int, int, int, cudaStream_t);
 int pointer_logits_fwd(const float*, const float*, const long long*, float*, long long, int, int, int, float, float, cudaStream_t);
@@ -89,7 +96,7 @@ int spatial_features(const void* const*, const void* const*, int, const float*, 
 int scatter_bwd_pnhwc(const void*, const void*, const void*, int, const long long*, float*, long long, int, int, int,
                       int, int, int, cudaStream_t);
 int maxpool2_fwd(const void*, void*, long long, int, int, int, cudaStream_t);
-int maxpool2_bwd(const void*, const void*, void*, long long, int, int, int, cudaStream_t);
+int maxpool2_bwd(const void*, const void*, void*, long long, int, int, int, int, cudaStream_t);
 }  // namespace as
 
 #define ST(s) reinterpret_cast<cudaStream_t>(s)
@@ -162,7 +169,7 @@ int as_splitk_reduce(const float* ws, float* out, int64_t n, int splits, int acc
 }
 
 static int conv_nhwc_impl(const void* x, const void* w, void* y, const float* bias, const void* resid, int64_t R, int H, int W,
-                          int Cin, int Cout, int taps, int w_mn, int y_bf16, int relu, void* stream) {
+                          int Cin, int Cout, int taps, int w_mn, int y_bf16, int relu, void* stream, const void* mask = nullptr) {
   if (taps != 1 && taps != 9) return AS_EUNSUPPORTED;
   if (R <= 0 || H <= 0 || W <= 0 || Cin <= 0 || Cout <= 0) return AS_ESIZE;
   if (Cin % 8 != 0) return AS_EUNSUPPORTED;
@@ -170,7 +177,7 @@ static int conv_nhwc_impl(const void* x, const void* w, void* y, const float* bi
   const int64_t P = R * (int64_t)ph * pw;
   if (P > 2147483647LL) return AS_ESIZE;
   as::GemmCall g;
-  g.A = x; g.B = w; g.C = y; g.bias = bias; g.resid = resid;
+  g.A = x; g.B = w; g.C = y; g.bias = bias; g.resid = resid; g.mask = mask;
   g.M = (int)P; g.N = Cout; g.K = Cin;
   g.a_mn = false; g.b_mn = w_mn != 0;
   g.lda = Cin; g.ldb = g.b_mn ? Cout : (int64_t)taps * Cin; g.ldc = Cout;
@@ -193,6 +200,12 @@ int as_conv_nhwc_bf16_add(const void* x, const void* w, void* y, const float* bi
                           int W, int Cin, int Cout, int taps, int relu, void* stream) {
   if (!addend) return AS_EINVAL;
   return conv_nhwc_impl(x, w, y, bias, addend, R, H, W, Cin, Cout, taps, 0, 1, relu, stream);
+}
+
+int as_conv_nhwc_bf16_masked(const void* x, const void* w, void* y, const void* addend, const void* mask, int64_t R, int H, int W,
+                             int Cin, int Cout, int taps, void* stream) {
+  if (!mask) return AS_EINVAL;
+  return conv_nhwc_impl(x, w, y, nullptr, addend, R, H, W, Cin, Cout, taps, 0, 1, 0, stream, mask);
 }
 
 // 0: one tap per tile; 1 / 2: tap pairs on a 64-channel M side (dy / swapped x), needs split-K partials
@@ -342,8 +355,8 @@ int as_scatter_connection_bwd_pnhwc(const void* d_feat, const void* xs, const vo
 int as_maxpool2_fwd_bf16(const void* in, void* out, int64_t R, int H, int W, int C, void* stream) {
   return as::maxpool2_fwd(in, out, R, H, W, C, ST(stream));
 }
-int as_maxpool2_bwd_bf16(const void* in, const void* dout, void* din, int64_t R, int H, int W, int C, void* stream) {
-  return as::maxpool2_bwd(in, dout, din, R, H, W, C, ST(stream));
+int as_maxpool2_bwd_bf16(const void* in, const void* dout, void* din, int64_t R, int H, int W, int C, int relu_input, void* stream) {
+  return as::maxpool2_bwd(in, dout, din, R, H, W, C, relu_input, ST(stream));
 }
 
 int as_colsum_f32(const float* x, float* out, float* scratch, int64_t rows, int C, void* stream) {
@@ -385,6 +398,21 @@ int as_spatial_fc_weight_fwd(const float* weight, void* w16, int out_features, i
 }
 int as_spatial_fc_weight_bwd(const float* dw_padded, float* dweight, int out_features, int C, int H, int W, void* stream) {
   return as::spatial_fc_weight_bwd(dw_padded, dweight, out_features, C, H, W, ST(stream));
+}
+int as_spatial_front_fwd(const void* const* planes, const void* const* effects, int n_eff, const float* emb, const void* xs,
+                         const void* ys, int idx_bytes, const int64_t* entity_num, int N, const float* weight, const float* bias,
+                         void* cells, void* out, void* codes, int64_t R, int H, int W, void* stream) {
+  return as::spatial_front_fwd(planes, effects, n_eff, emb, xs, ys, idx_bytes, reinterpret_cast<const long long*>(entity_num), N,
+                               weight, bias, cells, out, codes, R, H, W, ST(stream));
+}
+int64_t as_spatial_front_cells_bytes(int64_t R) { return as::spatial_front_cells_bytes(R); }
+int64_t as_spatial_front_bwd_scratch_floats(int64_t R, int H) { return as::spatial_front_bwd_scratch_floats(R, H); }
+int as_spatial_front_bwd(const void* const* planes, const void* const* effects, int n_eff, const float* emb, const void* xs,
+                         const void* ys, int idx_bytes, const int64_t* entity_num, int N, const float* weight, const float* bias,
+                         const void* cells, const void* codes, const void* dpool, float* dweight, float* dbias, float* g_entity,
+                         float* scratch, int64_t R, int H, int W, void* stream) {
+  return as::spatial_front_bwd(planes, effects, n_eff, emb, xs, ys, idx_bytes, reinterpret_cast<const long long*>(entity_num), N,
+                               weight, bias, cells, codes, dpool, dweight, dbias, g_entity, scratch, R, H, W, ST(stream));
 }
 int as_attn_fwd_ok(int N, int D) { return as::attn_fwd_ok(N, D); }
 int as_attn_fwd(const void* qkv, const int64_t* key_len, void* out, void* probs, int64_t R, int N, int H, int D, float scale,

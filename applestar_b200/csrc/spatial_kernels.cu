@@ -1205,8 +1205,11 @@ __global__ void maxpool2_fwd_kernel(const __nv_bfloat16* __restrict__ in, __nv_b
 }
 
 __global__ void maxpool2_bwd_kernel(const __nv_bfloat16* __restrict__ in, const __nv_bfloat16* __restrict__ dout,
-                                    __nv_bfloat16* __restrict__ din, long long R, int H, int W, int C, const Dec3 dec) {
-  // thread per (pooled pixel incl. border ring handled separately, 8 channels): writes the four input pixels
+                                    __nv_bfloat16* __restrict__ din, long long R, int H, int W, int C, const Dec3 dec,
+                                    int relu_input) {
+  // thread per (pooled pixel incl. border ring handled separately, 8 channels): writes the four input pixels.
+  // relu_input: `in` is the output of a ReLU layer -- a window whose maximum is 0 routes nothing, which IS that layer's
+  // ReLU backward mask (every routed element is positive), so its backward can skip the mask pass
   const int Ho = H / 2, Wo = W / 2, C8 = C / 8;
   const uint32_t total = (uint32_t)(R * (long long)Ho * Wo * C8);
   const uint32_t stride = gridDim.x * blockDim.x;
@@ -1228,6 +1231,7 @@ __global__ void maxpool2_bwd_kernel(const __nv_bfloat16* __restrict__ in, const 
       if (vb > m) { m = vb; best = 1; }
       if (vc > m) { m = vc; best = 2; }
       if (vd > m) { m = vd; best = 3; }
+      if (relu_input && !(m > 0.f)) best = -1;
       const __nv_bfloat16 z = f2bf(0.f);
       oa.h[j] = best == 0 ? g.h[j] : z; ob.h[j] = best == 1 ? g.h[j] : z;
       oc.h[j] = best == 2 ? g.h[j] : z; od.h[j] = best == 3 ? g.h[j] : z;
@@ -1276,14 +1280,14 @@ int maxpool2_fwd(const void* in, void* out, long long R, int H, int W, int C, cu
   return AS_OK;
 }
 
-int maxpool2_bwd(const void* in, const void* dout, void* din, long long R, int H, int W, int C, cudaStream_t st) {
+int maxpool2_bwd(const void* in, const void* dout, void* din, long long R, int H, int W, int C, int relu_input, cudaStream_t st) {
   if (R <= 0) return AS_OK;
   if ((C % 8) || (H % 2) || (W % 2) || H <= 0 || W <= 0) return AS_ESIZE;
   if (!in || !dout || !din) return AS_EINVAL;
   const long long total = R * (long long)(H / 2) * (W / 2) * (C / 8);
   if (total >= (1LL << 31)) return AS_ESIZE;
   maxpool2_bwd_kernel<<<ew_grid(total, 1), 256, 0, st>>>((const __nv_bfloat16*)in, (const __nv_bfloat16*)dout, (__nv_bfloat16*)din, R, H, W, C,
-                                                         make_dec3(C / 8, W / 2, H / 2));
+                                                         make_dec3(C / 8, W / 2, H / 2), relu_input);
   AS_LAUNCH_CHECK();
   const long long ring = R * (long long)(2 * (W + 2) + 2 * H) * (C / 8);
   zero_border_kernel<<<ew_grid(ring, 1), 256, 0, st>>>((__nv_bfloat16*)din, R, H, W, C);

@@ -61,15 +61,17 @@ class Conv(nn.Sequential):
         _xavier_normal(self[0].weight)
         self.relu, self.pad, self.nhwc = relu, pad, nhwc
 
-    def forward(self, x):
+    def forward(self, x, grad_premasked=False, mask_input_grad=False):
+        """grad_premasked / mask_input_grad: see spatial.ConvNHWC (who applies the ReLU backward mask of a conv -> ReLU ->
+        single consumer chain: the consumer's data-gradient epilogue instead of a separate pass)."""
         if not self.nhwc:
             raise RuntimeError('this convolution is evaluated by its owner (no library convolution path exists)')
-        return spatial.conv(x, self[0].weight, self[0].bias, self.relu)
+        return spatial.conv(x, self[0].weight, self[0].bias, self.relu, grad_premasked, mask_input_grad)
 
-    def fork(self, x):
+    def fork(self, x, grad_premasked=False):
         """-> (self(x), x'): x' aliases x and must replace it in x's OTHER consumers, so that their gradient is added to
         this convolution's data gradient in its GEMM epilogue (spatial.ConvNHWC)."""
-        return spatial.conv_fork(x, self[0].weight, self[0].bias, self.relu)
+        return spatial.conv_fork(x, self[0].weight, self[0].bias, self.relu, grad_premasked)
 
 
 def _eye_table(n):
@@ -184,8 +186,8 @@ class ResBlock(nn.Module):
         self.conv2 = Conv(ch, ch, 3, 1, nhwc=True)
 
     def forward(self, x):
-        h, x = self.conv1.fork(x)
-        return spatial.add_relu(self.conv2(h), x)
+        h, x = self.conv1.fork(x, grad_premasked=True)           # h feeds conv2 only: conv2's dgrad applies h's ReLU mask
+        return spatial.add_relu(self.conv2(h, mask_input_grad=True), x)
 
 
 class SpatialEncoder(nn.Module):
@@ -201,14 +203,16 @@ class SpatialEncoder(nn.Module):
         self.fc = FC(128 * (C.SPATIAL_Y // 8) * (C.SPATIAL_X // 8), 256, relu=True)
 
     def forward(self, spatial_info, x):
-        """`x` = output of the 1x1 project conv + ReLU as a padded NHWC bf16 map (spatial.spatial_project, which also
-        holds the ScatterConnection and the 56-channel input build).
+        """`x` = the 2x2 max-pooled output of the 1x1 project conv + ReLU as a padded NHWC bf16 map (spatial.spatial_front,
+        which also holds the ScatterConnection and the 56-channel input).
         -> (embedded_spatial [R,256], map_skip).  map_skip[0..2] (pre-pool maps, only read by the U-Net variant of
         the location head, which the default config disables) are not kept; map_skip[3..6] are the 19x20x128 maps
         as zero-padded NHWC bf16.  Every convolution is an implicit GEMM on the tcgen05 kernel."""
         skip = [None, None, None]
-        for conv in self.downsample:                              # 3 x (2x2 max-pool, 3x3 conv + ReLU)
-            x = conv(spatial.max_pool2(x))
+        for i, conv in enumerate(self.downsample):                # 3 x (2x2 max-pool, 3x3 conv + ReLU); the first pool is
+            if i > 0:                                             # part of the fused front kernel
+                x = spatial.max_pool2(x, relu_input=True)         # the pool's backward applies the conv's ReLU mask
+            x = conv(x, grad_premasked=(i < 2))                   # outputs 0 and 1 feed only the next pool
         for block in self.res:
             skip.append(x)
             x = block(x)
@@ -327,8 +331,8 @@ class Encoder(nn.Module):
         proj = self.scatter_project(entity_embeddings)
         # ScatterConnection ('add') + one-hot / effect planes + 1x1 project conv + ReLU in padded NHWC bf16
         pw = self.spatial_encoder.project[0]
-        projected = spatial.spatial_project(proj, entity_info['x'], entity_info['y'], entity_num, spatial_info,
-                                            pw.weight, pw.bias)
+        projected = spatial.spatial_front(proj, entity_info['x'], entity_info['y'], entity_num, spatial_info,
+                                          pw.weight, pw.bias)
         embedded_spatial, map_skip = self.spatial_encoder(spatial_info, projected)
         br.join([embedded_scalar, scalar_context, baseline_feature])
         lstm_input = torch.cat([embedded_scalar, embedded_entity, embedded_spatial], dim=-1)
@@ -490,11 +494,12 @@ class GatedResBlock(nn.Module):
         self.UpdateSP = nn.Parameter(torch.full((1,), 0.1))
 
     def forward(self, x):
-        h, x = self.conv1.fork(x)
-        g, x = self.GateWeightG[0].fork(x)
-        for layer in list(self.GateWeightG)[1:]:
-            g = layer(g)
-        return spatial.gated_residual(self.conv2(h), g, self.UpdateSP, x)
+        h, x = self.conv1.fork(x, grad_premasked=True)           # single-consumer ReLU chains: the consumer's data-gradient
+        g, x = self.GateWeightG[0].fork(x, grad_premasked=True)  # epilogue applies the producer's ReLU mask
+        gates = list(self.GateWeightG)
+        for j, layer in enumerate(gates[1:], 1):
+            g = layer(g, grad_premasked=(j < len(gates) - 1), mask_input_grad=True)
+        return spatial.gated_residual(self.conv2(h, mask_input_grad=True), g, self.UpdateSP, x)
 
 
 class LocationHead(nn.Module):

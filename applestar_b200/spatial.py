@@ -6,6 +6,7 @@ kernel (forward, data-gradient and weight-gradient); the tails (residual ReLU, g
 Reference modules: ResBlock (ctools/torch_utils/network/res_block.py:13-65), GatedResBlock
 (model/module_utils.py:204-231), LocationHead (model/head/action_arg_head.py:366-450).
 """
+import ctypes
 import os
 
 import torch
@@ -52,8 +53,13 @@ class ConvNHWC(torch.autograd.Function):
     (as_conv_nhwc_bf16_add) instead of by autograd's separate add over the two maps."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, relu, fork=False):
+    def forward(ctx, x, weight, bias, relu, fork=False, grad_premasked=False, mask_input_grad=False):
+        """grad_premasked: every consumer of this (ReLU) layer's output already applies the ReLU backward mask to the
+        gradient it sends back (a following convolution called with mask_input_grad, a max-pool with relu_input), so
+        the backward skips its own mask pass.  mask_input_grad: the input is the ReLU output of the previous layer and
+        this convolution is its only consumer: the data-gradient GEMM zeroes the gradient where the input is <= 0."""
         ctx.set_materialize_grads(False)
+        ctx.grad_premasked, ctx.mask_input_grad = bool(grad_premasked and relu), bool(mask_input_grad)
         R, ph, pw, cin_p = x.shape
         H, W = ph - 2, pw - 2
         cout, cin, kh, _ = weight.shape
@@ -73,14 +79,14 @@ class ConvNHWC(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy, dxa=None):
         if dy is None:                                   # only the pass-through alias was used downstream
-            return dxa, None, None, None, None
+            return dxa, None, None, None, None, None, None
         x, w_dg, y = ctx.saved_tensors
         R, H, W, cin, cin_p, cout, taps, kh = ctx.dims
         dy = dy.contiguous()
         st = _lib.stream_ptr()
         dx = dw = db = None
         want_db = ctx.has_bias and ctx.needs_input_grad[2]
-        if ctx.relu:
+        if ctx.relu and not ctx.grad_premasked:
             dz = torch.empty_like(dy)
             if want_db and cout % 8 == 0:       # ReLU mask and bias gradient in one pass
                 db = torch.empty(cout, dtype=torch.float32, device=x.device)
@@ -93,7 +99,13 @@ class ConvNHWC(torch.autograd.Function):
             dy = dz
         if ctx.needs_input_grad[0]:
             dx = torch.empty_like(x)
-            if dxa is not None and cin_p % 32 == 0 and dxa.dtype == torch.bfloat16 and dxa.shape == x.shape:
+            if ctx.mask_input_grad and cin_p % 32 == 0 and (dxa is None or (dxa.dtype == torch.bfloat16 and dxa.shape == x.shape)):
+                dxa = None if dxa is None else dxa.contiguous()
+                _lib.call('as_conv_nhwc_bf16_masked', dy.data_ptr(), w_dg.data_ptr(), dx.data_ptr(), _ptr(dxa), x.data_ptr(),
+                          R, H, W, cout, cin_p, taps, st)
+            elif ctx.mask_input_grad:
+                raise RuntimeError('mask_input_grad needs a channel count that is a multiple of 32')
+            elif dxa is not None and cin_p % 32 == 0 and dxa.dtype == torch.bfloat16 and dxa.shape == x.shape:
                 dxa = dxa.contiguous()
                 _lib.call('as_conv_nhwc_bf16_add', dy.data_ptr(), w_dg.data_ptr(), dx.data_ptr(), 0, dxa.data_ptr(), R, H, W,
                           cout, cin_p, taps, 0, st)
@@ -121,18 +133,18 @@ class ConvNHWC(torch.autograd.Function):
             db = torch.empty(cout, dtype=torch.float32, device=x.device)
             scratch = torch.empty(_lib.lib().as_colsum_scratch_floats(cout), dtype=torch.float32, device=x.device)
             _lib.call('as_colsum_bf16', dy.data_ptr(), db.data_ptr(), scratch.data_ptr(), R * (H + 2) * (W + 2), cout, st)
-        return dx, dw, db, None, None
+        return dx, dw, db, None, None, None, None
 
 
-def conv(x, weight, bias, relu=False):
-    return ConvNHWC.apply(x, weight, bias, relu)
+def conv(x, weight, bias, relu=False, grad_premasked=False, mask_input_grad=False):
+    return ConvNHWC.apply(x, weight, bias, relu, False, grad_premasked, mask_input_grad)
 
 
-def conv_fork(x, weight, bias, relu=False):
+def conv_fork(x, weight, bias, relu=False, grad_premasked=False):
     """-> (conv(x), alias of x for x's other consumers); see ConvNHWC."""
     if not FORK_CONV or not (torch.is_grad_enabled() and x.requires_grad):
-        return ConvNHWC.apply(x, weight, bias, relu), x
-    return ConvNHWC.apply(x, weight, bias, relu, True)
+        return ConvNHWC.apply(x, weight, bias, relu, False, grad_premasked, False), x
+    return ConvNHWC.apply(x, weight, bias, relu, True, grad_premasked, False)
 
 
 class AddAct(torch.autograd.Function):
@@ -335,8 +347,12 @@ def spatial_fc(x, weight, bias, ch, H, W):
 
 
 class MaxPool2(torch.autograd.Function):
+    """2x2 max-pool.  relu_input: x is a ReLU layer's output and this pool is its only consumer -- the backward then routes
+    nothing through windows whose maximum is 0, i.e. the gradient it returns already carries that layer's ReLU mask."""
+
     @staticmethod
-    def forward(ctx, x):
+    def forward(ctx, x, relu_input=False):
+        ctx.relu_input = bool(relu_input)
         R, ph, pw, Cc = x.shape
         H, W = ph - 2, pw - 2
         x = x.contiguous()
@@ -352,12 +368,13 @@ class MaxPool2(torch.autograd.Function):
         R, H, W, Cc = ctx.dims
         dy = dy.contiguous()
         dx = torch.empty_like(x)
-        _lib.call('as_maxpool2_bwd_bf16', x.data_ptr(), dy.data_ptr(), dx.data_ptr(), R, H, W, Cc, _lib.stream_ptr())
-        return dx
+        _lib.call('as_maxpool2_bwd_bf16', x.data_ptr(), dy.data_ptr(), dx.data_ptr(), R, H, W, Cc, int(ctx.relu_input),
+                  _lib.stream_ptr())
+        return dx, None
 
 
-def max_pool2(x):
-    return MaxPool2.apply(x)
+def max_pool2(x, relu_input=False):
+    return MaxPool2.apply(x, relu_input)
 
 
 _PLANES = ('height_map', 'visibility_map', 'creep', 'player_relative', 'alerts', 'pathable', 'buildable')
@@ -455,3 +472,87 @@ class SpatialProject(torch.autograd.Function):
 
 def spatial_project(proj, x, y, entity_num, spatial_info, weight, bias):
     return SpatialProject.apply(proj, x, y, entity_num, spatial_info, weight, bias)
+
+
+def _plane_ptrs(spatial_info):
+    planes = (ctypes.c_void_p * 7)()
+    effects = (ctypes.c_void_p * 6)()
+    keep = []
+    for i, k in enumerate(_PLANES):
+        t = spatial_info[k].contiguous()
+        if t.dtype != torch.uint8:
+            t = t.to(torch.uint8)
+        keep.append(t)
+        planes[i] = t.data_ptr()
+    for i, k in enumerate(_EFFECTS):
+        t = spatial_info[k].contiguous()
+        if t.dtype != torch.int16:
+            t = t.to(torch.int16)
+        keep.append(t)
+        effects[i] = t.data_ptr()
+    return planes, effects, keep, spatial_info[_EFFECTS[0]].shape[1]
+
+
+class SpatialFront(torch.autograd.Function):
+    """ScatterConnection ('add') + 56-channel spatial input + 1x1 project conv (56 -> 32) + ReLU + the first 2x2 max-pool
+    (encoder.py:37-42, spatial_encoder.py:52-72,79) as ONE kernel per direction (csrc/spatial_front.cu): the one-hot
+    input makes the convolution two table look-ups per pixel, evaluated exactly in fp32; only the pooled map
+    [R, H/2+2, W/2+2, 32] (zero-padded NHWC bf16) touches HBM.  Backward: the kernel recomputes the windows, routes the
+    pooled gradient, and returns the weight / bias gradients and the per-entity gradient rows; d proj and the scatter
+    block of d weight are two small GEMMs on them."""
+
+    @staticmethod
+    def forward(ctx, proj, x, y, entity_num, spatial_info, weight, bias):
+        R, N, D = proj.shape
+        planes, effects, keep, n_eff = _plane_ptrs(spatial_info)
+        H, W = keep[0].shape[1], keep[0].shape[2]
+        xs, ys = x.contiguous(), y.contiguous()
+        if xs.dtype not in (torch.uint8, torch.int64):
+            xs, ys = xs.long(), ys.long()
+        en = None if entity_num is None else entity_num.contiguous().long()
+        emb = proj.detach().float().contiguous()
+        w2 = weight.detach().reshape(weight.shape[0], -1).float().contiguous()
+        b1 = bias.detach().float().contiguous()
+        out = torch.empty((R, H // 2 + 2, W // 2 + 2, 32), dtype=torch.bfloat16, device=proj.device)
+        cells = torch.empty(_lib.lib().as_spatial_front_cells_bytes(R), dtype=torch.uint8, device=proj.device)
+        need_bwd = any(ctx.needs_input_grad)
+        codes = torch.empty((R, H // 2, W // 2, 4), dtype=torch.int32, device=proj.device) if need_bwd else None
+        _lib.call('as_spatial_front_fwd', planes, effects, n_eff, emb.data_ptr(), xs.data_ptr(), ys.data_ptr(),
+                  xs.element_size(), _ptr(en), N, w2.data_ptr(), b1.data_ptr(), cells.data_ptr(), out.data_ptr(), _ptr(codes),
+                  R, H, W, _lib.stream_ptr())
+        _lib.LAUNCHES += 2
+        ctx.dims = (R, N, D, H, W, n_eff)
+        ctx.wshape = weight.shape
+        ctx.save_for_backward(emb, xs, ys, en, w2, b1, cells, codes, *keep)
+        return out
+
+    @staticmethod
+    def backward(ctx, dpool):
+        emb, xs, ys, en, w2, b1, cells, codes = ctx.saved_tensors[:8]
+        keep = ctx.saved_tensors[8:]
+        R, N, D, H, W, n_eff = ctx.dims
+        dev = dpool.device
+        planes = (ctypes.c_void_p * 7)(*[t.data_ptr() for t in keep[:7]])
+        effects = (ctypes.c_void_p * 6)(*[t.data_ptr() for t in keep[7:13]])
+        dpool = dpool.contiguous()
+        dw = torch.empty((32, 56), dtype=torch.float32, device=dev)
+        db = torch.empty(32, dtype=torch.float32, device=dev)
+        g = torch.empty((R, N, 32), dtype=torch.float32, device=dev)
+        scratch = torch.empty(_lib.lib().as_spatial_front_bwd_scratch_floats(R, H), dtype=torch.float32, device=dev)
+        _lib.call('as_spatial_front_bwd', planes, effects, n_eff, emb.data_ptr(), xs.data_ptr(), ys.data_ptr(),
+                  xs.element_size(), _ptr(en), N, w2.data_ptr(), b1.data_ptr(), cells.data_ptr(), codes.data_ptr(), dpool.data_ptr(),
+                  dw.data_ptr(), db.data_ptr(), g.data_ptr(), scratch.data_ptr(), R, H, W, _lib.stream_ptr())
+        _lib.LAUNCHES += 2
+        g16 = K.to_bf16(g.view(R * N, 32))                                   # exact: the rows are bf16 gradients
+        dproj = None
+        if ctx.needs_input_grad[0]:
+            ws16 = K.to_bf16(w2[:, 24:56].contiguous())                      # [o, c]
+            dproj = torch.empty((R * N, 32), dtype=torch.float32, device=dev)
+            K.gemm(g16, ws16, dproj, R * N, 32, 32, lda=32, b_mn=True, ldb=32)
+            dproj = dproj.view(R, N, D)
+        dw[:, 24:56] = K._wgrad(g16, K.to_bf16(emb.view(R * N, 32)), 32, 32)
+        return dproj, None, None, None, None, dw.view(ctx.wshape), db
+
+
+def spatial_front(proj, x, y, entity_num, spatial_info, weight, bias):
+    return SpatialFront.apply(proj, x, y, entity_num, spatial_info, weight, bias)

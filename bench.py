@@ -368,8 +368,8 @@ def encoder_microbench(model, dev, batch=1024, chunk=256, iters=3):
                                               obs['entity_num'], C.SPATIAL_Y, C.SPATIAL_X)
                 marks[3].record()
                 pw = enc.spatial_encoder.project[0]
-                x = spatial.spatial_project(proj, obs['entity_info']['x'], obs['entity_info']['y'], obs['entity_num'],
-                                            obs['spatial_info'], pw.weight, pw.bias)
+                x = spatial.spatial_front(proj, obs['entity_info']['x'], obs['entity_info']['y'], obs['entity_num'],
+                                          obs['spatial_info'], pw.weight, pw.bias)
                 enc.spatial_encoder(obs['spatial_info'], x)
                 marks[4].record()
             del smap

@@ -77,6 +77,12 @@ int as_conv_nhwc_bf16(const void* x, const void* w, void* y, const float* bias, 
  * epilogue instead of by a separate add over the two maps.  Cout % 32 == 0. */
 int as_conv_nhwc_bf16_add(const void* x, const void* w, void* y, const float* bias, const void* addend, int64_t R, int H,
                           int W, int Cin, int Cout, int taps, int relu, void* stream);
+/* as_conv_nhwc_bf16_masked: data gradient of a convolution whose INPUT is the ReLU output `mask` of the previous layer
+ * (conv1 -> ReLU -> conv2 in ResBlock / GatedResBlock / the gate chain, res_block.py:61-65, module_utils.py:221-230):
+ * y = (conv(x, w) + addend) * (mask > 0), i.e. the previous layer's threshold_backward is applied in the GEMM epilogue
+ * and that layer's backward starts from an already masked gradient.  addend may be NULL; mask has y's layout. */
+int as_conv_nhwc_bf16_masked(const void* x, const void* w, void* y, const void* addend, const void* mask, int64_t R, int H, int W,
+                             int Cin, int Cout, int taps, void* stream);
 
 /* Weight gradient of the NHWC convolution above: dw[tap][co][ci] = sum_p dy[p][co] * x[p + shift(tap)][ci] as one
  * tap-batched, split-K tcgen05 GEMM with both operands read MN-major.  dy [R,(H+2),(W+2),Cout] bf16 (zero border),
@@ -183,7 +189,9 @@ int as_scatter_connection_bwd_pnhwc(const void* d_feat, const void* xs, const vo
 /* 2x2 max-pool on padded NHWC bf16 maps -- replaces F.max_pool2d (spatial_encoder.py:79).  in [R,H+2,W+2,C] ->
  * out [R,H/2+2,W/2+2,C]; backward routes to the first maximum of the window (torch semantics), border zero. */
 int as_maxpool2_fwd_bf16(const void* in, void* out, int64_t R, int H, int W, int C, void* stream);
-int as_maxpool2_bwd_bf16(const void* in, const void* dout, void* din, int64_t R, int H, int W, int C, void* stream);
+int as_maxpool2_bwd_bf16(const void* in, const void* dout, void* din, int64_t R, int H, int W, int C, int relu_input, void* stream);
+/* relu_input != 0: `in` is a ReLU layer's output; windows whose maximum is 0 route nothing, so din already carries that
+ * layer's ReLU backward mask. */
 
 /* LayerNorm(x (+ residual)) * gamma + beta, eps 1e-5, optional fused ReLU -- replaces nn.LayerNorm at
  * module_utils.py:135,139 (Transformer), lstm.py:140-151 (LN-LSTM), res_block.py:68-141 (ResFCBlock/ResFCBlock2).
@@ -260,6 +268,29 @@ int as_su_prefix_bwd(const float* demb, const int64_t* selected_units, const int
                      float* dkey, int64_t R, int N1, int D, int Smax, int S, void* stream);
 int as_su_mask_logits(const float* x, const int64_t* selected_units, const int64_t* entity_num, float* out, int64_t R, int N1,
                       int Smax, int S, float scale, float fill, void* stream);
+
+/* Front of the spatial encoder in one kernel per direction: ScatterConnection 'add' (model/encoder.py:37-42,
+ * module_utils.py:11-34) + the 56-channel input (one-hot planes, height / 256, effect planes with the pixel-0 padding
+ * quirk, scatter channels: obs_encoder/spatial_encoder.py:52-71) + 1x1 project conv 56 -> 32 + ReLU (:72) + the first
+ * 2x2 max-pool (:79), evaluated sparsely and exactly in fp32 (two table rows per pixel).
+ * planes[7] uint8 [R,H,W] (height, visibility, creep, player_relative, alerts, pathable, buildable), effects[6] int16
+ * [R,n_eff], emb [R,N,32] fp32 projected entity embeddings, xs / ys [R,N] (idx_bytes 1 or 8), weight [32,56] fp32, bias
+ * [32] -> out [R, H/2+2, W/2+2, 32] bf16, zero border.  H % 38 == 0, W even and <= 160, N <= 512.  `cells` =
+ * as_spatial_front_cells_bytes(R) bytes (256-byte aligned) that receive the weight tables and the per-observation sorted
+ * cell list; `codes` (may be NULL at inference) = R * (H/2) * (W/2) * 16 bytes: per pooled pixel and channel the 4-bit
+ * index of the window pixel that won the max (15: none survived the ReLU).  The backward reads both buffers.
+ * Backward: dpool (layout of out) -> dweight [32,56] columns 0..23 (columns 24..55 = g_entity^T emb, left to the caller),
+ * dbias [32], g_entity [R,N,32] = gradient of the pre-activation at each entity's cell (rows >= entity_num zero), from
+ * which d emb = g_entity W[:,24:56]; scratch = as_spatial_front_bwd_scratch_floats(R, H) floats. */
+int as_spatial_front_fwd(const void* const* planes, const void* const* effects, int n_eff, const float* emb, const void* xs,
+                         const void* ys, int idx_bytes, const int64_t* entity_num, int N, const float* weight, const float* bias,
+                         void* cells, void* out, void* codes, int64_t R, int H, int W, void* stream);
+int64_t as_spatial_front_cells_bytes(int64_t R);
+int64_t as_spatial_front_bwd_scratch_floats(int64_t R, int H);
+int as_spatial_front_bwd(const void* const* planes, const void* const* effects, int n_eff, const float* emb, const void* xs,
+                         const void* ys, int idx_bytes, const int64_t* entity_num, int N, const float* weight, const float* bias,
+                         const void* cells, const void* codes, const void* dpool, float* dweight, float* dbias, float* g_entity,
+                         float* scratch, int64_t R, int H, int W, void* stream);
 
 /* bf16 GEMM-operand layouts of a Conv2d weight [Cout, Cin, k, k] fp32 (ctools/torch_utils/network/nn_module.py:119-174
  * holds it in that layout) for as_conv_nhwc_bf16: w_fwd [Cout][tap][cin_pad] (forward) and w_dgrad

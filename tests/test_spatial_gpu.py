@@ -227,6 +227,49 @@ def test_spatial_project_matches_reference_front():
     assert ((bd.grad.cpu() - br.grad).norm() / br.grad.norm()).item() < 0.05
 
 
+def test_spatial_front_fused_vs_oracle():
+    """csrc/spatial_front.cu: scatter + 56-channel input + 1x1 project + ReLU + first 2x2 max-pool in one kernel, evaluated
+    in fp32 from the one-hot planes -> the pooled map equals the fp32 oracle up to the bf16 store (and the bf16 copy of
+    the per-cell contribution); pool routing / ReLU masks / effect-plane pixel-0 quirk / clamped coordinates are index
+    work and agree exactly wherever the window maximum is unambiguous.  Gradients (weight incl. the scatter block, bias,
+    entity projections) against the oracle's autograd."""
+    from applestar_b200 import spatial, synth
+    from oracle import restate as R
+    Rn = 4
+    obs = synth.gen_observations(Rn, 512, 31, special=True)
+    obs['entity_info']['x'][2, :40] = 250                       # out of range: clamps to 159 / 151
+    obs['entity_info']['y'][2, :40] = 200
+    g = torch.Generator().manual_seed(32)
+    proj = torch.relu(torch.randn(Rn, 512, 32, generator=g)) * 0.5
+    w = torch.randn(32, 56, 1, 1, generator=g) * 0.3
+    b = torch.randn(32, generator=g) * 0.1
+    en = obs['entity_num']
+    mask = (torch.arange(512).unsqueeze(0) < en.unsqueeze(1)).unsqueeze(2)
+    pr = proj.clone().requires_grad_(True)
+    wr, br = w.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    smap = R.scatter_connection(pr * mask, obs['entity_info']['x'], obs['entity_info']['y'], 'add')
+    ref = F.max_pool2d(torch.relu(F.conv2d(R.spatial_input(obs['spatial_info'], smap), wr, br)), 2, 2)
+    gout = torch.randn(ref.shape, generator=g).to(torch.bfloat16).float()
+    ref.backward(gout)
+
+    pd = proj.cuda().requires_grad_(True)
+    wd, bd = w.cuda().requires_grad_(True), b.cuda().requires_grad_(True)
+    sp = {k: v.cuda() for k, v in obs['spatial_info'].items()}
+    out = spatial.spatial_front(pd, obs['entity_info']['x'].cuda(), obs['entity_info']['y'].cuda(), en.cuda(), sp, wd, bd)
+    assert out.shape == (Rn, 78, 82, 32) and _border_zero(out)
+    got = _from_p(out).cpu()
+    refd = ref.detach()
+    assert torch.equal(got > 0, refd.to(torch.bfloat16).float() > 0) or ((got > 0) != (refd > 0)).float().mean().item() < 1e-4
+    assert (got - refd).abs().max().item() < 0.01 * refd.abs().max().item() + 1e-2
+    gy = torch.zeros_like(out)
+    gy[:, 1:-1, 1:-1] = gout.permute(0, 2, 3, 1).cuda().to(torch.bfloat16)
+    out.backward(gy)
+    for name, mine, want, tol in (('proj', pd.grad, pr.grad, 0.05), ('weight', wd.grad, wr.grad, 0.01), ('bias', bd.grad, br.grad, 0.01)):
+        rel = ((mine.cpu() - want).norm() / want.norm()).item()
+        assert rel < tol, (name, rel)
+    assert float(pd.grad[1, 1:].abs().sum()) == 0.0              # entity_num == 1: masked entities get exactly zero
+
+
 @pytest.mark.parametrize('rows,C', [(1000, 256), (4097, 40), (77, 128), (25000, 32)])
 @pytest.mark.parametrize('ykind', ['none', 'f32', 'bf16'])
 def test_linear_bwd_prep(rows, C, ykind):
