@@ -96,6 +96,9 @@ _SIGS = {
     'as_spatial_front_bwd': (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p,
                                      c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int,
                                      c_int, c_void_p]),
+    'as_upconv_c32_1_fwd': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_float, c_void_p]),
+    'as_upconv_c32_1_scratch_floats': (c_int64, [c_int64, c_int]),
+    'as_upconv_c32_1_bwd': (c_int, [c_void_p] * 7 + [c_int64, c_int, c_int, c_float, c_int, c_void_p]),
     'as_conv_weight_layouts': (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     'as_spatial_fc_weight_fwd': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     'as_spatial_fc_weight_bwd': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),

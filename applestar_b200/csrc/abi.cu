@@ -67,6 +67,9 @@ int su_prefix_bwd(const float*, const long long*, const long long*, const float*
                   int, int, cudaStream_t);
 int su_mask_logits(const float*, const long long*, const long long*, float*, long long, int, int, int, float, float, cudaStream_t);
 int conv_weight_layouts(const float*, void*, void*, int, int, int, int, cudaStream_t);
+int upconv_fwd(const void*, const float*, const float*, float*, long long, int, int, float, cudaStream_t);
+long long upconv_scratch_floats(long long, int);
+int upconv_bwd(const float*, const void*, const float*, void*, float*, float*, float*, long long, int, int, float, int, cudaStream_t);
 int spatial_front_fwd(const void* const*, const void* const*, int, const float*, const void*, const void*, int, const long long*, int,
                       const float*, const float*, void*, void*, void*, long long, int, int, cudaStream_t);
 long long spatial_front_cells_bytes(long long);
@@ -413,6 +416,15 @@ int as_spatial_front_bwd(const void* const* planes, const void* const* effects, 
                          float* scratch, int64_t R, int H, int W, void* stream) {
   return as::spatial_front_bwd(planes, effects, n_eff, emb, xs, ys, idx_bytes, reinterpret_cast<const long long*>(entity_num), N,
                                weight, bias, cells, codes, dpool, dweight, dbias, g_entity, scratch, R, H, W, ST(stream));
+}
+int as_upconv_c32_1_fwd(const void* x, const float* w9, const float* bias, float* out, int64_t R, int h, int w, float inv_temp,
+                        void* stream) {
+  return as::upconv_fwd(x, w9, bias, out, R, h, w, inv_temp, ST(stream));
+}
+int64_t as_upconv_c32_1_scratch_floats(int64_t R, int h) { return as::upconv_scratch_floats(R, h); }
+int as_upconv_c32_1_bwd(const float* dout, const void* x, const float* w9, void* dx, float* dw9, float* dbias, float* scratch,
+                        int64_t R, int h, int w, float inv_temp, int relu_input, void* stream) {
+  return as::upconv_bwd(dout, x, w9, dx, dw9, dbias, scratch, R, h, w, inv_temp, relu_input, ST(stream));
 }
 int as_attn_fwd_ok(int N, int D) { return as::attn_fwd_ok(N, D); }
 int as_attn_fwd(const void* qkv, const int64_t* key_len, void* out, void* probs, int64_t R, int N, int H, int D, float scale,

@@ -520,9 +520,9 @@ class LocationHead(nn.Module):
         for i, block in enumerate(self.res):
             x = block(spatial.add(x, map_skip[len(map_skip) - i - 1]))
         x = self.upsample[0](spatial.upsample2(x))
-        x = self.upsample[1](spatial.upsample2(x))
-        last = self.upsample[2][0]                                # 3x3, 32 -> 1, flatten, 1/temperature: one kernel
-        logits = spatial.conv_c32_to_1(spatial.upsample2(x), last.weight, last.bias, 1.0 / temperature)
+        x = self.upsample[1](spatial.upsample2(x), grad_premasked=True)     # only consumer: the fused tail, which masks
+        last = self.upsample[2][0]      # bilinear x2 + 3x3 conv 32 -> 1 + flatten + 1/temperature: one kernel, no 152x160x32 map
+        logits = spatial.upconv_c32_to_1(x, last.weight, last.bias, 1.0 / temperature, relu_input=True)
         if location is None:
             location = ops.gumbel_argmax(logits, noise)
         return logits, location

@@ -319,6 +319,44 @@ def conv_c32_to_1(x, weight, bias, inv_temp=1.0):
     return ConvC32To1.apply(x, weight, bias, inv_temp)
 
 
+class UpConvC32To1(torch.autograd.Function):
+    """bilinear x2 + 3x3 conv 32 -> 1 + flatten + 1/temperature (action_arg_head.py:440-446) as one kernel per
+    direction that never forms the upsampled map (csrc/upconv.cu).  relu_input: x is a ReLU output consumed only here,
+    so the returned gradient already carries x's ReLU mask."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, inv_temp, relu_input):
+        R, ph, pw, Cc = x.shape
+        h, w = ph - 2, pw - 2
+        assert Cc == 32 and tuple(weight.shape) == (1, 32, 3, 3)
+        x = x.contiguous()
+        w9 = weight.detach().permute(0, 2, 3, 1).reshape(9, 32).contiguous().float()
+        out = torch.empty((R, 4 * h * w), dtype=torch.float32, device=x.device)
+        _lib.call('as_upconv_c32_1_fwd', x.data_ptr(), w9.data_ptr(), _ptr(bias), out.data_ptr(), R, h, w, float(inv_temp),
+                  _lib.stream_ptr())
+        ctx.dims = (R, h, w)
+        ctx.inv_temp, ctx.relu_input = float(inv_temp), bool(relu_input)
+        ctx.save_for_backward(x, w9)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w9 = ctx.saved_tensors
+        R, h, w = ctx.dims
+        dy = dy.contiguous().float()
+        dx = torch.empty_like(x)
+        dw = torch.empty((9, 32), dtype=torch.float32, device=x.device)
+        db = torch.empty(1, dtype=torch.float32, device=x.device)
+        scratch = torch.empty(_lib.lib().as_upconv_c32_1_scratch_floats(R, h), dtype=torch.float32, device=x.device)
+        _lib.call('as_upconv_c32_1_bwd', dy.data_ptr(), x.data_ptr(), w9.data_ptr(), dx.data_ptr(), dw.data_ptr(),
+                  db.data_ptr(), scratch.data_ptr(), R, h, w, ctx.inv_temp, int(ctx.relu_input), _lib.stream_ptr())
+        return dx, dw.view(3, 3, 32).permute(2, 0, 1).reshape(1, 32, 3, 3), db, None, None
+
+
+def upconv_c32_to_1(x, weight, bias, inv_temp=1.0, relu_input=False):
+    return UpConvC32To1.apply(x, weight, bias, inv_temp, relu_input)
+
+
 def spatial_fc(x, weight, bias, ch, H, W):
     """ReLU(fc) of the spatial encoder (spatial_encoder.py:88-89) over a padded NHWC bf16 map x [R, H+2, W+2, ch].  The
     reference's weight is laid out for the NCHW flatten (column c*H*W + y*W + x); the GEMM reads a bf16 re-layout for

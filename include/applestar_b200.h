@@ -292,6 +292,18 @@ int as_spatial_front_bwd(const void* const* planes, const void* const* effects, 
                          const void* cells, const void* codes, const void* dpool, float* dweight, float* dbias, float* g_entity,
                          float* scratch, int64_t R, int H, int W, void* stream);
 
+/* Tail of the location head (head/action_arg_head.py:440-446): bilinear x2 upsampling (F.interpolate, align_corners
+ * False) of x [R,h+2,w+2,32] (padded NHWC bf16) + 3x3 convolution 32 -> 1 (zero padding) + flatten + 1/temperature ->
+ * out [R, 2h * 2w] fp32, WITHOUT forming the upsampled map: the two linear steps commute into nine numbers per
+ * low-resolution pixel (csrc/upconv.cu).  w9 [9][32] fp32 (tap-major), bias [1] or NULL, w <= 80.
+ * Backward: dout [R, 2h * 2w] -> dx (x's layout, zero border; multiplied by (x > 0) when relu_input: x is a ReLU output
+ * with no other consumer), dw9 [9][32], dbias [1]; scratch = as_upconv_c32_1_scratch_floats(R, h) floats. */
+int as_upconv_c32_1_fwd(const void* x, const float* w9, const float* bias, float* out, int64_t R, int h, int w, float inv_temp,
+                        void* stream);
+int64_t as_upconv_c32_1_scratch_floats(int64_t R, int h);
+int as_upconv_c32_1_bwd(const float* dout, const void* x, const float* w9, void* dx, float* dw9, float* dbias, float* scratch,
+                        int64_t R, int h, int w, float inv_temp, int relu_input, void* stream);
+
 /* bf16 GEMM-operand layouts of a Conv2d weight [Cout, Cin, k, k] fp32 (ctools/torch_utils/network/nn_module.py:119-174
  * holds it in that layout) for as_conv_nhwc_bf16: w_fwd [Cout][tap][cin_pad] (forward) and w_dgrad
  * [cin_pad][flipped tap][Cout] (data gradient), channels beyond Cin zero.  taps = k * k. */

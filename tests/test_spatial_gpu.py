@@ -305,3 +305,32 @@ def test_relu_bwd_colsum_bf16(rows, C):
     assert torch.equal(dz, want)
     ref = want.double().sum(0)
     assert (db.double() - ref).abs().max().item() <= 1e-5 * want.float().abs().sum(0).max().item() + 1e-5
+
+
+@pytest.mark.parametrize('relu_input', [False, True])
+def test_upconv_fused_tail_vs_torch(relu_input):
+    """csrc/upconv.cu: bilinear x2 + 3x3 conv 32 -> 1 + flatten + 1/temperature without the upsampled map, against
+    F.interpolate + F.conv2d in fp32 (forward 1e-4 relative; dx rounds to bf16; weight / bias gradients fp32)."""
+    from applestar_b200 import spatial
+    g = torch.Generator().manual_seed(5)
+    R, h, w = 3, 76, 80
+    x = torch.relu(torch.randn(R, 32, h, w, generator=g)).to(torch.bfloat16).float()
+    wt = torch.randn(1, 32, 3, 3, generator=g) * 0.2
+    b = torch.randn(1, generator=g)
+    inv_t = 1.0 / 0.8
+    xr, wr, br = x.clone().requires_grad_(True), wt.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    ref = F.conv2d(F.interpolate(torch.relu(xr) if relu_input else xr, scale_factor=2., mode='bilinear'), wr, br, padding=1)
+    ref = ref.reshape(R, -1) * inv_t
+    go = torch.randn(ref.shape, generator=g)
+    ref.backward(go)
+    xp = spatial.to_pnhwc(x.cuda()).detach().requires_grad_(True)
+    wd, bd = wt.cuda().requires_grad_(True), b.cuda().requires_grad_(True)
+    out = spatial.upconv_c32_to_1(xp, wd, bd, inv_t, relu_input=relu_input)
+    assert out.shape == (R, 4 * h * w)
+    assert (out.cpu() - ref.detach()).abs().max().item() < 1e-4 * ref.abs().max().item() + 1e-4
+    out.backward(go.cuda())
+    assert _border_zero(xp.grad)
+    gx = _from_p(xp.grad).cpu()
+    assert (gx - xr.grad).abs().max().item() < 0.01 * xr.grad.abs().max().item() + 1e-3
+    assert (wd.grad.cpu() - wr.grad).abs().max().item() < 1e-4 * wr.grad.abs().max().item() + 1e-3
+    assert abs(float(bd.grad) - float(br.grad)) < 1e-3 * abs(float(br.grad)) + 1e-3
