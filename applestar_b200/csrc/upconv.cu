@@ -13,7 +13,7 @@
 namespace as {
 
 constexpr int kUcC = 32;
-constexpr int kUcThreads = 256;
+constexpr int kUcThreads = 320;                // forward: two row groups x 160 output columns
 constexpr int kUcBandHi = 8;                 // output rows per forward CTA
 constexpr int kUcBandLo = 4;                 // low-res rows per backward CTA
 constexpr int kUcMaxWlo = 80;                // low-res width limit (shared-memory tiles)
@@ -41,63 +41,99 @@ upconv_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__
                   float* __restrict__ out, int h, int w, float inv_temp) {
   constexpr int kRows = kUcBandHi / 2 + 3;                                   // low rows needed by a band (incl. halo)
   __shared__ float sY[kRows][kUcMaxWlo][9];
-  __shared__ float sW[9 * kUcC];
+  __shared__ __align__(16) float sW[9 * kUcC];
   const int r = blockIdx.x, band = blockIdx.y;
   const int H = 2 * h, W = 2 * w;
   const int y0 = band * kUcBandHi;
   const int lo0 = max(0, (y0 - 1) / 2 - 1);                                  // first low row that can be a neighbour
   for (int i = threadIdx.x; i < 9 * kUcC; i += kUcThreads) sW[i] = w9[i];
   __syncthreads();
-  for (int i = threadIdx.x; i < kRows * w; i += kUcThreads) {
-    const int lr = i / w, lx = i - lr * w;
-    const int ly = lo0 + lr;
-    float acc[9];
+  // two low-res pixels per thread-iteration: every 16-byte weight load serves eight multiply-adds
+  const int n_lo = kRows * w;
+  for (int i = threadIdx.x; i < (n_lo + 1) / 2; i += kUcThreads) {
+    float acc[2][9];
+    uint4 xv[2][4];
 #pragma unroll
-    for (int t = 0; t < 9; ++t) acc[t] = 0.f;
-    if (ly < h) {
-      const uint4* px = reinterpret_cast<const uint4*>(x + (((long long)r * (h + 2) + ly + 1) * (w + 2) + lx + 1) * kUcC);
+    for (int u = 0; u < 2; ++u) {
+      const int ii = 2 * i + u;
+      const int lr = ii / w, lx = ii - lr * w;
+      const int ly = lo0 + lr;
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const uint4 v = __ldg(px + q);
-        const uint32_t vw[4] = {v.x, v.y, v.z, v.w};
+      for (int t = 0; t < 9; ++t) acc[u][t] = 0.f;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const float a = __uint_as_float(vw[k] << 16), b = __uint_as_float(vw[k] & 0xffff0000u);
-          const int c = q * 8 + 2 * k;
+      for (int q = 0; q < 4; ++q) xv[u][q] = make_uint4(0, 0, 0, 0);
+      if (ii < n_lo && ly < h) {
+        const uint4* px = reinterpret_cast<const uint4*>(x + (((long long)r * (h + 2) + ly + 1) * (w + 2) + lx + 1) * kUcC);
 #pragma unroll
-          for (int t = 0; t < 9; ++t) acc[t] = fmaf(a, sW[t * kUcC + c], fmaf(b, sW[t * kUcC + c + 1], acc[t]));
+        for (int q = 0; q < 4; ++q) xv[u][q] = __ldg(px + q);
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+#pragma unroll
+      for (int hq = 0; hq < 2; ++hq) {                                         // channels 8 q + 4 hq .. + 3
+        float xa[2][4];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const uint32_t w0 = hq ? xv[u][q].z : xv[u][q].x, w1 = hq ? xv[u][q].w : xv[u][q].y;
+          xa[u][0] = __uint_as_float(w0 << 16); xa[u][1] = __uint_as_float(w0 & 0xffff0000u);
+          xa[u][2] = __uint_as_float(w1 << 16); xa[u][3] = __uint_as_float(w1 & 0xffff0000u);
+        }
+#pragma unroll
+        for (int t = 0; t < 9; ++t) {
+          const float4 wv = *reinterpret_cast<const float4*>(&sW[t * kUcC + q * 8 + hq * 4]);
+#pragma unroll
+          for (int u = 0; u < 2; ++u)
+            acc[u][t] = fmaf(xa[u][0], wv.x, fmaf(xa[u][1], wv.y, fmaf(xa[u][2], wv.z, fmaf(xa[u][3], wv.w, acc[u][t]))));
         }
       }
     }
 #pragma unroll
-    for (int t = 0; t < 9; ++t) sY[lr][lx][t] = acc[t];
+    for (int u = 0; u < 2; ++u) {
+      const int ii = 2 * i + u;
+      if (ii < n_lo) {
+        const int lr = ii / w, lx = ii - lr * w;
+#pragma unroll
+        for (int t = 0; t < 9; ++t) sY[lr][lx][t] = acc[u][t];
+      }
+    }
   }
   __syncthreads();
   const float b0 = bias ? bias[0] : 0.f;
-  for (int i = threadIdx.x; i < kUcBandHi * W; i += kUcThreads) {
-    const int yy = i / W, xx = i - yy * W;
-    const int y = y0 + yy;
-    if (y >= H) break;
-    float acc = b0;
+  // thread = output column (and a group of rows): the three column taps' neighbours / weights are computed once
+  const int ncol_groups = kUcThreads / W > 0 ? kUcThreads / W : 1;             // threads beyond ncol_groups * W idle here
+  const int xx = threadIdx.x % W, rg = threadIdx.x / W;
+  if (rg < ncol_groups) {
+    int j0[3], j1[3]; float wx[3]; bool okx[3];
 #pragma unroll
-    for (int ty = 0; ty < 3; ++ty) {
-      const int qy = y + ty - 1;
-      if (qy < 0 || qy >= H) continue;
-      int i0, i1; float wy;
-      uc_src(qy, h, &i0, &i1, &wy);
-#pragma unroll
-      for (int tx = 0; tx < 3; ++tx) {
-        const int qx = xx + tx - 1;
-        if (qx < 0 || qx >= W) continue;
-        int j0, j1; float wx;
-        uc_src(qx, w, &j0, &j1, &wx);
-        const int t = ty * 3 + tx;
-        const float top = (1.f - wx) * sY[i0 - lo0][j0][t] + wx * sY[i0 - lo0][j1][t];
-        const float bot = (1.f - wx) * sY[i1 - lo0][j0][t] + wx * sY[i1 - lo0][j1][t];
-        acc += (1.f - wy) * top + wy * bot;
-      }
+    for (int tx = 0; tx < 3; ++tx) {
+      const int qx = xx + tx - 1;
+      okx[tx] = qx >= 0 && qx < W;
+      uc_src(okx[tx] ? qx : 0, w, &j0[tx], &j1[tx], &wx[tx]);
     }
-    out[(long long)r * H * W + (long long)y * W + xx] = acc * inv_temp;
+    for (int yy = rg; yy < kUcBandHi; yy += ncol_groups) {
+      const int y = y0 + yy;
+      if (y >= H) break;
+      float acc = b0;
+#pragma unroll
+      for (int ty = 0; ty < 3; ++ty) {
+        const int qy = y + ty - 1;
+        if (qy < 0 || qy >= H) continue;
+        int i0, i1; float wy;
+        uc_src(qy, h, &i0, &i1, &wy);
+        const float (*r0)[9] = sY[i0 - lo0];
+        const float (*r1)[9] = sY[i1 - lo0];
+#pragma unroll
+        for (int tx = 0; tx < 3; ++tx) {
+          if (!okx[tx]) continue;
+          const int t = ty * 3 + tx;
+          const float top = (1.f - wx[tx]) * r0[j0[tx]][t] + wx[tx] * r0[j1[tx]][t];
+          const float bot = (1.f - wx[tx]) * r1[j0[tx]][t] + wx[tx] * r1[j1[tx]][t];
+          acc += (1.f - wy) * top + wy * bot;
+        }
+      }
+      out[(long long)r * H * W + (long long)y * W + xx] = acc * inv_temp;
+    }
   }
 }
 
@@ -106,24 +142,25 @@ upconv_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__
 // 1/temperature, zero outside the image) -> shared memory; B: dY_t[n] = sum over the 4x4 outputs q around n of
 // bilinear weight x dlogit[q - t]; C: thread = (low pixel, 8 channels): dX = sum_t w[t][c] dY_t (masked by X > 0 when
 // relu_input), dW partials in registers (fixed channel group per thread), reduced over the CTA in fixed order.
+constexpr int kUcBwdThreads = 256;
 constexpr int kUcDRows = 2 * kUcBandLo + 5;                                  // output rows 2 n0 - 2 .. 2 n0 + 2 * band + 2
 
-__global__ void __launch_bounds__(kUcThreads)
+__global__ void __launch_bounds__(kUcBwdThreads)
 upconv_bwd_kernel(const float* __restrict__ dout, const __nv_bfloat16* __restrict__ x, const float* __restrict__ w9,
                   __nv_bfloat16* __restrict__ dx, float* __restrict__ partial, int h, int w, float inv_temp, int relu_input) {
   __shared__ float sD[kUcDRows][2 * kUcMaxWlo + 4];                          // column index = output column + 2
   __shared__ float sdY[kUcBandLo * kUcMaxWlo][9];
-  __shared__ float sW[9 * kUcC];
-  __shared__ float sRed[kUcThreads / 32][4][72];
-  __shared__ float sDb[kUcThreads / 32];
+  __shared__ __align__(16) float sW[9 * kUcC];
+  __shared__ float sRed[kUcBwdThreads / 32][4][72];
+  __shared__ float sDb[kUcBwdThreads / 32];
   const int r = blockIdx.x, band = blockIdx.y;
   const int H = 2 * h, W = 2 * w;
   const int n0 = band * kUcBandLo;
   const int prow0 = 2 * n0 - 2;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (int i = tid; i < 9 * kUcC; i += kUcThreads) sW[i] = w9[i];
+  for (int i = tid; i < 9 * kUcC; i += kUcBwdThreads) sW[i] = w9[i];
   float dbl = 0.f;
-  for (int i = tid; i < kUcDRows * (W + 4); i += kUcThreads) {
+  for (int i = tid; i < kUcDRows * (W + 4); i += kUcBwdThreads) {
     const int rr = i / (W + 4), cc = i - rr * (W + 4);
     const int py = prow0 + rr, px = cc - 2;
     float v = 0.f;
@@ -137,7 +174,7 @@ upconv_bwd_kernel(const float* __restrict__ dout, const __nv_bfloat16* __restric
   if (lane == 0) sDb[warp] = dbl;
   __syncthreads();
   // B
-  for (int i = tid; i < kUcBandLo * w * 9; i += kUcThreads) {
+  for (int i = tid; i < kUcBandLo * w * 9; i += kUcBwdThreads) {
     const int t = i % 9, n = i / 9;
     const int ny = n / w, nx = n - ny * w;
     const int gy = n0 + ny;
@@ -170,7 +207,7 @@ upconv_bwd_kernel(const float* __restrict__ dout, const __nv_bfloat16* __restric
   float dw[72];
 #pragma unroll
   for (int j = 0; j < 72; ++j) dw[j] = 0.f;
-  for (int i = tid; i < kUcBandLo * w * 4; i += kUcThreads) {
+  for (int i = tid; i < kUcBandLo * w * 4; i += kUcBwdThreads) {
     const int n = i >> 2;
     const int ny = n / w, nx = n - ny * w;
     const int gy = n0 + ny;
@@ -186,9 +223,12 @@ upconv_bwd_kernel(const float* __restrict__ dout, const __nv_bfloat16* __restric
 #pragma unroll
     for (int t = 0; t < 9; ++t) {
       const float dy = sdY[n][t];
+      const float4 wa = *reinterpret_cast<const float4*>(&sW[t * kUcC + cg * 8]);
+      const float4 wb = *reinterpret_cast<const float4*>(&sW[t * kUcC + cg * 8 + 4]);
+      const float wv[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        g[j] = fmaf(dy, sW[t * kUcC + cg * 8 + j], g[j]);
+        g[j] = fmaf(dy, wv[j], g[j]);
         dw[t * 8 + j] = fmaf(dy, xf[j], dw[t * 8 + j]);
       }
     }
@@ -206,15 +246,15 @@ upconv_bwd_kernel(const float* __restrict__ dout, const __nv_bfloat16* __restric
   }
   // zero border of dx: left / right pixel of the band's rows, top / bottom row from the first / last band
   const uint4 z = make_uint4(0, 0, 0, 0);
-  for (int i = tid; i < kUcBandLo * 2 * 4; i += kUcThreads) {
+  for (int i = tid; i < kUcBandLo * 2 * 4; i += kUcBwdThreads) {
     const int q = i & 3, side = (i >> 2) & 1, ny = i >> 3;
     if (n0 + ny < h)
       reinterpret_cast<uint4*>(dx + (((long long)r * (h + 2) + n0 + ny + 1) * (w + 2) + (side ? w + 1 : 0)) * kUcC)[q] = z;
   }
   if (band == 0)
-    for (int i = tid; i < (w + 2) * 4; i += kUcThreads) reinterpret_cast<uint4*>(dx + ((long long)r * (h + 2)) * (w + 2) * kUcC)[i] = z;
+    for (int i = tid; i < (w + 2) * 4; i += kUcBwdThreads) reinterpret_cast<uint4*>(dx + ((long long)r * (h + 2)) * (w + 2) * kUcC)[i] = z;
   if (band == (int)gridDim.y - 1)
-    for (int i = tid; i < (w + 2) * 4; i += kUcThreads)
+    for (int i = tid; i < (w + 2) * 4; i += kUcBwdThreads)
       reinterpret_cast<uint4*>(dx + (((long long)r * (h + 2)) + h + 1) * (w + 2) * kUcC)[i] = z;
   // dW: lanes with the same channel group (lane & 3) -> butterfly over lane bits 2..4, then the 8 warps in fixed order
 #pragma unroll
@@ -227,27 +267,30 @@ upconv_bwd_kernel(const float* __restrict__ dout, const __nv_bfloat16* __restric
   }
   __syncthreads();
   float* dst = partial + ((long long)blockIdx.x * gridDim.y + blockIdx.y) * 289;
-  for (int i = tid; i < 288; i += kUcThreads) {                              // i = t * 32 + c
+  for (int i = tid; i < 288; i += kUcBwdThreads) {                              // i = t * 32 + c
     const int t = i >> 5, c = i & 31;
     float s = 0.f;
 #pragma unroll
-    for (int wq = 0; wq < kUcThreads / 32; ++wq) s += sRed[wq][c >> 3][t * 8 + (c & 7)];
+    for (int wq = 0; wq < kUcBwdThreads / 32; ++wq) s += sRed[wq][c >> 3][t * 8 + (c & 7)];
     dst[i] = s;
   }
   if (tid == 0) {
     float s = 0.f;
-    for (int wq = 0; wq < kUcThreads / 32; ++wq) s += sDb[wq];
+    for (int wq = 0; wq < kUcBwdThreads / 32; ++wq) s += sDb[wq];
     dst[288] = s;
   }
 }
 
-// fixed-order sum of the per-CTA partials [n][289] -> dw9 [9][32], db [1]
+// fixed-order sum of the per-CTA partials [n][289] -> dw9 [9][32], db [1], in two levels (kUcChunks partial sums first)
+constexpr int kUcChunks = 64;
 __global__ void __launch_bounds__(256)
-upconv_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw9, float* __restrict__ db, int n) {
+upconv_reduce1_kernel(const float* __restrict__ partial, float* __restrict__ part2, int n) {
   const int col = blockIdx.x * 32 + (threadIdx.x & 31), grp = threadIdx.x >> 5;
+  const int per = (n + kUcChunks - 1) / kUcChunks;
+  const int i0 = blockIdx.y * per, i1 = min(n, i0 + per);
   float acc = 0.f;
   if (col < 289)
-    for (int i = grp; i < n; i += 8) acc += partial[(long long)i * 289 + col];
+    for (int i = i0 + grp; i < i1; i += 8) acc += partial[(long long)i * 289 + col];
   __shared__ float sm[8][33];
   sm[grp][threadIdx.x & 31] = acc;
   __syncthreads();
@@ -255,8 +298,15 @@ upconv_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw9,
     float t = 0.f;
 #pragma unroll
     for (int k = 0; k < 8; ++k) t += sm[k][threadIdx.x & 31];
-    if (col < 288) dw9[col] = t; else db[0] = t;
+    part2[blockIdx.y * 289 + col] = t;
   }
+}
+__global__ void upconv_reduce2_kernel(const float* __restrict__ part2, float* __restrict__ dw9, float* __restrict__ db) {
+  const int col = blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= 289) return;
+  float t = 0.f;
+  for (int k = 0; k < kUcChunks; ++k) t += part2[k * 289 + col];
+  if (col < 288) dw9[col] = t; else db[0] = t;
 }
 
 static int uc_check(long long R, int h, int w) {
@@ -277,7 +327,7 @@ int upconv_fwd(const void* x, const float* w9, const float* bias, float* out, lo
   return AS_OK;
 }
 
-long long upconv_scratch_floats(long long R, int h) { return R * ((h + kUcBandLo - 1) / kUcBandLo) * 289LL; }
+long long upconv_scratch_floats(long long R, int h) { return (R * ((h + kUcBandLo - 1) / kUcBandLo) + kUcChunks) * 289LL; }
 
 int upconv_bwd(const float* dout, const void* x, const float* w9, void* dx, float* dw9, float* db, float* scratch, long long R,
                int h, int w, float inv_temp, int relu_input, cudaStream_t st) {
@@ -287,10 +337,13 @@ int upconv_bwd(const float* dout, const void* x, const float* w9, void* dx, floa
   if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dx)) & 15) return AS_EALIGN;
   const int bands = (h + kUcBandLo - 1) / kUcBandLo;
   dim3 grid((unsigned)R, (unsigned)bands);
-  upconv_bwd_kernel<<<grid, kUcThreads, 0, st>>>(dout, reinterpret_cast<const __nv_bfloat16*>(x), w9,
+  upconv_bwd_kernel<<<grid, kUcBwdThreads, 0, st>>>(dout, reinterpret_cast<const __nv_bfloat16*>(x), w9,
                                                  reinterpret_cast<__nv_bfloat16*>(dx), scratch, h, w, inv_temp, relu_input);
   AS_LAUNCH_CHECK();
-  upconv_reduce_kernel<<<(289 + 31) / 32, 256, 0, st>>>(scratch, dw9, db, (int)(R * bands));
+  float* part2 = scratch + R * bands * 289LL;
+  upconv_reduce1_kernel<<<dim3((289 + 31) / 32, kUcChunks), 256, 0, st>>>(scratch, part2, (int)(R * bands));
+  AS_LAUNCH_CHECK();
+  upconv_reduce2_kernel<<<3, 128, 0, st>>>(part2, dw9, db);
   AS_LAUNCH_CHECK();
   return AS_OK;
 }
