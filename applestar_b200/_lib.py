@@ -99,6 +99,11 @@ _SIGS = {
     'as_upconv_c32_1_fwd': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_float, c_void_p]),
     'as_upconv_c32_1_scratch_floats': (c_int64, [c_int64, c_int]),
     'as_upconv_c32_1_bwd': (c_int, [c_void_p] * 7 + [c_int64, c_int, c_int, c_float, c_int, c_void_p]),
+    'as_ln256_bf16_fwd': (c_int, [c_void_p] * 6 + [c_int64, c_int, c_void_p]),
+    'as_ln256_bf16_bwd_scratch_floats': (c_int64, []),
+    'as_ln256_bf16_bwd': (c_int, [c_void_p] * 9 + [c_int] + [c_void_p] * 4 + [c_int64, c_int, c_void_p]),
+    'as_masked_mean256_bf16_fwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
+    'as_masked_mean256_bf16_bwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     'as_conv_weight_layouts': (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     'as_spatial_fc_weight_fwd': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     'as_spatial_fc_weight_bwd': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),

@@ -67,6 +67,12 @@ int su_prefix_bwd(const float*, const long long*, const long long*, const float*
                   int, int, cudaStream_t);
 int su_mask_logits(const float*, const long long*, const long long*, float*, long long, int, int, int, float, float, cudaStream_t);
 int conv_weight_layouts(const float*, void*, void*, int, int, int, int, cudaStream_t);
+int ln256_bf16_fwd(const void*, const void*, const float*, const float*, void*, float*, long long, int, cudaStream_t);
+long long ln256_bf16_bwd_scratch_floats();
+int ln256_bf16_bwd(const void*, const void*, const void*, const void*, const float*, const float*, const float*, void*, void*, int,
+                   float*, float*, float*, float*, long long, int, cudaStream_t);
+int masked_mean256_bf16_fwd(const void*, const long long*, float*, long long, int, cudaStream_t);
+int masked_mean256_bf16_bwd(const float*, const long long*, void*, long long, int, cudaStream_t);
 int upconv_fwd(const void*, const float*, const float*, float*, long long, int, int, float, cudaStream_t);
 long long upconv_scratch_floats(long long, int);
 int upconv_bwd(const float*, const void*, const float*, void*, float*, float*, float*, long long, int, int, float, int, cudaStream_t);
@@ -425,6 +431,23 @@ int64_t as_upconv_c32_1_scratch_floats(int64_t R, int h) { return as::upconv_scr
 int as_upconv_c32_1_bwd(const float* dout, const void* x, const float* w9, void* dx, float* dw9, float* dbias, float* scratch,
                         int64_t R, int h, int w, float inv_temp, int relu_input, void* stream) {
   return as::upconv_bwd(dout, x, w9, dx, dw9, dbias, scratch, R, h, w, inv_temp, relu_input, ST(stream));
+}
+int as_ln256_bf16_fwd(const void* z, const void* res, const float* gamma, const float* beta, void* y, float* stats, int64_t rows,
+                      int relu, void* stream) {
+  return as::ln256_bf16_fwd(z, res, gamma, beta, y, stats, rows, relu, ST(stream));
+}
+int64_t as_ln256_bf16_bwd_scratch_floats(void) { return as::ln256_bf16_bwd_scratch_floats(); }
+int as_ln256_bf16_bwd(const void* dy_a, const void* dy_b, const void* z, const void* res, const float* gamma, const float* beta,
+                      const float* stats, void* dres, void* dz, int mask_z, float* dgamma, float* dbeta, float* dbias,
+                      float* scratch, int64_t rows, int relu, void* stream) {
+  return as::ln256_bf16_bwd(dy_a, dy_b, z, res, gamma, beta, stats, dres, dz, mask_z, dgamma, dbeta, dbias, scratch, rows, relu,
+                            ST(stream));
+}
+int as_masked_mean256_bf16_fwd(const void* x, const int64_t* len, float* out, int64_t R, int N, void* stream) {
+  return as::masked_mean256_bf16_fwd(x, reinterpret_cast<const long long*>(len), out, R, N, ST(stream));
+}
+int as_masked_mean256_bf16_bwd(const float* dout, const int64_t* len, void* dx, int64_t R, int N, void* stream) {
+  return as::masked_mean256_bf16_bwd(dout, reinterpret_cast<const long long*>(len), dx, R, N, ST(stream));
 }
 int as_attn_fwd_ok(int N, int D) { return as::attn_fwd_ok(N, D); }
 int as_attn_fwd(const void* qkv, const int64_t* key_len, void* out, void* probs, int64_t R, int N, int H, int D, float scale,

@@ -423,6 +423,12 @@ int layer_norm_bwd(const float* dy32, const void* dy16, const float* x, const fl
   return AS_OK;
 }
 
+int layer_norm_param_reduce3(const float* partial, float* dgamma, float* dbeta, float* dbias, int C, int chunks, cudaStream_t st) {
+  layer_norm_param_reduce3_kernel<<<(C + 31) / 32, 256, 0, st>>>(partial, dgamma, dbeta, dbias, C, chunks);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
 // LayerNorm backward of y = LN(res + x) where x = act(linear(...)) is followed directly by that linear layer's backward:
 // one pass gives dx (fp32, the residual-path gradient; may be NULL), dz16 = bf16(dx * (x > 0 if mask_x)), dgamma, dbeta
 // and dbias = column sums of dz.  C = 256 or 384; scratch = as_layer_norm_bwd_fused_scratch_floats(C) floats.

@@ -446,6 +446,145 @@ class MLPLNFn(torch.autograd.Function):
         return (dx, (None if dres is None else dres.view(*ctx.xshape[:-1], N)), dw1, db1, dw2, db2, dgamma, dbeta, None)
 
 
+def _ln16_fwd(z16, res16, gamma, beta, relu):
+    rows = z16.shape[0]
+    y16 = torch.empty_like(z16)
+    stats = torch.empty((rows, 2), dtype=torch.float32, device=z16.device)
+    _lib.call('as_ln256_bf16_fwd', z16.data_ptr(), _ptr(res16), gamma.data_ptr(), beta.data_ptr(), y16.data_ptr(),
+              stats.data_ptr(), rows, int(relu), _lib.stream_ptr())
+    return y16, stats
+
+
+def _ln16_bwd(dya, dyb, z16, res16, gamma, beta, stats, relu_ln, mask_z, want_dres):
+    rows, C = z16.shape
+    dev = z16.device
+    if dya is None:
+        dya, dyb = dyb, None
+    dya = dya.contiguous().reshape(rows, C)
+    dyb = None if dyb is None else dyb.contiguous().reshape(rows, C)
+    if dya.dtype != torch.bfloat16:
+        dya = dya.to(torch.bfloat16)
+    if dyb is not None and dyb.dtype != torch.bfloat16:
+        dyb = dyb.to(torch.bfloat16)
+    dres = torch.empty_like(z16) if want_dres else None
+    dz16 = torch.empty_like(z16)
+    dgamma, dbeta, dbias = (torch.empty(C, dtype=torch.float32, device=dev) for _ in range(3))
+    scratch = torch.empty(_lib.lib().as_ln256_bf16_bwd_scratch_floats(), dtype=torch.float32, device=dev)
+    _lib.call('as_ln256_bf16_bwd', dya.data_ptr(), _ptr(dyb), z16.data_ptr(), _ptr(res16), gamma.data_ptr(), beta.data_ptr(),
+              stats.data_ptr(), _ptr(dres), dz16.data_ptr(), int(mask_z), dgamma.data_ptr(), dbeta.data_ptr(),
+              dbias.data_ptr(), scratch.data_ptr(), rows, int(relu_ln), _lib.stream_ptr())
+    return dres, dz16, dgamma, dbeta, dbias
+
+
+class LinearLN16Fn(torch.autograd.Function):
+    """bf16-stream form of LinearLNFn: (y, y') = LN(res + x W^T + b) with x, res, the GEMM output and y in bf16.  The two
+    returned tensors are the same data: the caller hands one to the residual path and one to the next GEMM, so that their
+    gradients come back separately and are summed inside the LayerNorm backward kernel."""
+
+    @staticmethod
+    def forward(ctx, x, res, weight, bias, gamma, beta, relu_ln):
+        ctx.set_materialize_grads(False)
+        Kd, N = x.shape[-1], weight.shape[0]
+        x16 = to_bf16(x.reshape(-1, Kd))
+        M = x16.shape[0]
+        w16 = weight_bf16(weight)
+        z16 = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
+        gemm(x16, w16, z16, M, N, x16.shape[1], lda=x16.shape[1], ldb=w16.shape[1], bias=bias)
+        res16 = to_bf16(res.reshape(M, N))
+        y16, stats = _ln16_fwd(z16, res16, gamma, beta, relu_ln)
+        ctx.relu_ln, ctx.xshape = relu_ln, x.shape
+        ctx.save_for_backward(x16, w16, z16, res16, gamma, beta, stats)
+        shp = (*x.shape[:-1], N)
+        return y16.view(shp), y16.view(shp)
+
+    @staticmethod
+    def backward(ctx, dya, dyb):
+        x16, w16, z16, res16, gamma, beta, stats = ctx.saved_tensors
+        if dya is None and dyb is None:
+            return (None,) * 7
+        M, N = z16.shape
+        K8 = w16.shape[1]
+        dres, dz16, dgamma, dbeta, dbias = _ln16_bwd(dya, dyb, z16, res16, gamma, beta, stats, ctx.relu_ln, False,
+                                                     ctx.needs_input_grad[1])
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty((M, K8), dtype=torch.bfloat16, device=z16.device)
+            gemm(dz16, w16, dx, M, K8, N, lda=N, b_mn=True, ldb=K8)
+            dx = dx.reshape(ctx.xshape)
+        if ctx.needs_input_grad[2]:
+            dw = _wgrad(dz16, x16, N, K8)
+        return dx, (None if dres is None else dres.view(*ctx.xshape[:-1], N)), dw, dbias, dgamma, dbeta, None
+
+
+class MLPLN16Fn(torch.autograd.Function):
+    """bf16-stream form of MLPLNFn (FFN with ReLU on both layers + layernorm2, module_utils.py:121-123,136-139)."""
+
+    @staticmethod
+    def forward(ctx, x, res, w1, b1, w2, b2, gamma, beta, relu_ln):
+        ctx.set_materialize_grads(False)
+        Kd, Hd, N = x.shape[-1], w1.shape[0], w2.shape[0]
+        x16 = to_bf16(x.reshape(-1, Kd))
+        M = x16.shape[0]
+        w1_16, w2_16 = weight_bf16(w1), weight_bf16(w2)
+        h16 = torch.empty((M, Hd), dtype=torch.bfloat16, device=x.device)
+        gemm(x16, w1_16, h16, M, Hd, Kd, lda=Kd, ldb=Kd, bias=b1, relu=True)
+        z16 = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
+        gemm(h16, w2_16, z16, M, N, Hd, lda=Hd, ldb=Hd, bias=b2, relu=True)
+        res16 = to_bf16(res.reshape(M, N))
+        y16, stats = _ln16_fwd(z16, res16, gamma, beta, relu_ln)
+        ctx.relu_ln, ctx.xshape = relu_ln, x.shape
+        ctx.save_for_backward(x16, w1_16, w2_16, h16, z16, res16, gamma, beta, stats)
+        shp = (*x.shape[:-1], N)
+        return y16.view(shp), y16.view(shp)
+
+    @staticmethod
+    def backward(ctx, dya, dyb):
+        x16, w1_16, w2_16, h16, z16, res16, gamma, beta, stats = ctx.saved_tensors
+        if dya is None and dyb is None:
+            return (None,) * 9
+        M, N = z16.shape
+        Hd, Kd = w1_16.shape
+        dev = z16.device
+        dres, dz2, dgamma, dbeta, db2 = _ln16_bwd(dya, dyb, z16, res16, gamma, beta, stats, ctx.relu_ln, True,
+                                                  ctx.needs_input_grad[1])
+        dz1 = torch.empty((M, Hd), dtype=torch.bfloat16, device=dev)
+        _lib.call('as_gemm_bf16_masked', dz2.data_ptr(), w2_16.data_ptr(), dz1.data_ptr(), h16.data_ptr(), M, Hd, N, 0, 1,
+                  N, Hd, Hd, 1, 1.0, _lib.stream_ptr())
+        db1 = column_sum(dz1) if ctx.needs_input_grad[3] else None
+        dw2 = _wgrad(dz2, h16, N, Hd) if ctx.needs_input_grad[4] else None
+        dw1 = _wgrad(dz1, x16, Hd, Kd) if ctx.needs_input_grad[2] else None
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty((M, Kd), dtype=torch.bfloat16, device=dev)
+            gemm(dz1, w1_16, dx, M, Kd, Hd, lda=Hd, b_mn=True, ldb=Kd)
+            dx = dx.reshape(ctx.xshape)
+        return (dx, (None if dres is None else dres.view(*ctx.xshape[:-1], N)), dw1, db1, dw2, db2, dgamma, dbeta, None)
+
+
+class MaskedMean16Fn(torch.autograd.Function):
+    """sum over valid entities / entity_num of a bf16 stream [R, N, 256] -> fp32 [R, 256]; bf16 gradient."""
+
+    @staticmethod
+    def forward(ctx, x, entity_num):
+        R, N, Cc = x.shape
+        x = x.contiguous()
+        entity_num = entity_num.contiguous()
+        out = torch.empty((R, Cc), dtype=torch.float32, device=x.device)
+        _lib.call('as_masked_mean256_bf16_fwd', x.data_ptr(), entity_num.data_ptr(), out.data_ptr(), R, N, _lib.stream_ptr())
+        ctx.dims = (R, N, Cc)
+        ctx.save_for_backward(entity_num)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (entity_num,) = ctx.saved_tensors
+        R, N, Cc = ctx.dims
+        dout = dout.contiguous().float()
+        dx = torch.empty((R, N, Cc), dtype=torch.bfloat16, device=dout.device)
+        _lib.call('as_masked_mean256_bf16_bwd', dout.data_ptr(), entity_num.data_ptr(), dx.data_ptr(), R, N, _lib.stream_ptr())
+        return dx, None
+
+
 def fused_ln_ok(dim, *weights):
     return dim in (256, 384) and all(w.dim() == 2 and w.shape[1] % 8 == 0 and w.shape[0] % 32 == 0 for w in weights)
 
@@ -606,13 +745,15 @@ def entity_features(entity_info, fields, pitch):
     return out, neg
 
 
-def entity_embed(entity_info, weight, bias, layout):
+def entity_embed(entity_info, weight, bias, layout, bf16_only=False):
     """ReLU(features @ W^T + b) -> (fp32, bf16) [R, N, 256].  The one-hot concat exists only as a bf16 GEMM operand."""
     from . import config as C
     first = entity_info['x']
     R, N = first.shape
     feats, neg = entity_features(entity_info, C.ENTITY_FIELDS, 1000)
     entity_embed.last_neg_flag = neg          # checked lazily by the caller (no host sync on the hot path)
+    if bf16_only:
+        return linear(feats, weight, bias, relu=True, out_bf16=True).view(R, N, -1)
     y32, y16 = linear_dual(feats, weight, bias, relu=True)
     return y32.view(R, N, -1), y16.view(R, N, -1)
 

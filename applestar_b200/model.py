@@ -121,6 +121,14 @@ class TransformerLayer(nn.Module):
     def forward(self, x32, x16, key_len, final_relu=False):
         """(fp32 residual stream, bf16 GEMM operand) in and out."""
         l1, l2 = self.layernorm1, self.layernorm2
+        if self.post_ln and x32 is None:            # bf16 stream: x16 = (residual handle, GEMM-operand handle) of one tensor
+            xa, xb = x16
+            att = self.attention
+            a = ops.attention(att.attention_pre(xb), key_len, att.head_num, att.head_dim)
+            pj, f1, f2 = att.project[0], self.mlp[0][0], self.mlp[1][0]
+            xa, xb = ops.linear_ln16(a, xa, pj.weight, pj.bias, l1.weight, l1.bias)
+            xa, xb = ops.mlp_ln16(xb, xa, f1.weight, f1.bias, f2.weight, f2.bias, l2.weight, l2.bias, final_relu)
+            return None, (xa, xb)
         if self.post_ln and ops.transformer_layer_fused_ok(self):     # module_utils.py:133-139, two fused autograd nodes
             att = self.attention
             a = ops.attention(att.attention_pre(x16), key_len, att.head_num, att.head_dim)
@@ -170,6 +178,12 @@ class EntityEncoder(nn.Module):
 
     def forward(self, entity_info, entity_num):
         emb = self.transformer.embedding[0]
+        layer0 = self.transformer.layers[0]
+        if ops.ENTITY_BF16 and ops.transformer_layer_fused_ok(layer0) and emb.weight.shape[0] == 256:
+            # bf16 residual stream (what the reference's autocast path holds): LayerNorm traffic 0.4 - 0.6x
+            x16 = ops.entity_embed(entity_info, emb.weight, emb.bias, bf16_only=True)
+            _, (xa, xb) = self.transformer.run_layers(None, (x16, x16), entity_num, final_relu=True)
+            return self.entity_fc(xb), self.embed_fc(ops.masked_mean16(xa, entity_num))
         x32, x16 = ops.entity_embed(entity_info, emb.weight, emb.bias)    # [R,N,256], ReLU applied
         # the reference's in-place ReLU after the transformer feeds both entity_fc and the mean (A1): fused
         # into the last LayerNorm

@@ -58,6 +58,30 @@ def mlp_ln(x, res, w1, b1, w2, b2, gamma, beta, relu_ln=False):
     return K.MLPLNFn.apply(x, res, w1, b1, w2, b2, gamma, beta, relu_ln)
 
 
+# Residual stream of the entity Transformer in bf16 (LayerNorm traffic 0.4 - 0.6x, measured -1.07 ms of 60.2 ms per learner
+# step).  OFF by default: at N = 512 the target-unit head's gradient aggregate rose from 0.087 to 0.169 relative L2 against
+# the reference (budget 0.128 = 2 x the reference's own bf16-autocast error), so the fp32 stream stays the product path.
+ENTITY_BF16 = os.environ.get('APPLESTAR_ENTITY_BF16', '0') == '1'
+
+
+def linear_ln16(x, res, weight, bias, gamma, beta, relu_ln=False):
+    """[kernel] bf16-stream LN(res + x W^T + b) -> two handles of the same bf16 tensor (kernels.LinearLN16Fn)."""
+    require_cuda(x)
+    return K.LinearLN16Fn.apply(x, res, weight, bias, gamma, beta, relu_ln)
+
+
+def mlp_ln16(x, res, w1, b1, w2, b2, gamma, beta, relu_ln=False):
+    """[kernel] bf16-stream LN(res + FFN(x)) -> two handles of the same bf16 tensor (kernels.MLPLN16Fn)."""
+    require_cuda(x)
+    return K.MLPLN16Fn.apply(x, res, w1, b1, w2, b2, gamma, beta, relu_ln)
+
+
+def masked_mean16(x, entity_num):
+    """[kernel] masked mean of a bf16 [R, N, 256] stream (entity_encoder.py:83-85)."""
+    require_cuda(x)
+    return K.MaskedMean16Fn.apply(x, entity_num.long())
+
+
 def add_relu(a, b):
     return F.relu(a + b)
 
@@ -99,12 +123,12 @@ def _entity_layout(device):
     return _ENTITY_LAYOUT
 
 
-def entity_embed(entity_info, weight, bias):
-    """[kernel] ReLU(onehot_concat(entity_info) @ W^T + b) -> (fp32, bf16).  The 997-wide concat exists only as a
-    bf16 GEMM operand written by one kernel from the narrow per-field arrays (never as 2 MB/obs of fp32)."""
+def entity_embed(entity_info, weight, bias, bf16_only=False):
+    """[kernel] ReLU(onehot_concat(entity_info) @ W^T + b) -> (fp32, bf16), or the bf16 copy alone.  The 997-wide concat
+    exists only as a bf16 GEMM operand written by one kernel from the narrow per-field arrays (never as 2 MB/obs of fp32)."""
     x0 = entity_info['x']
     require_cuda(x0)
-    return K.entity_embed(entity_info, weight, bias, _entity_layout(x0.device))
+    return K.entity_embed(entity_info, weight, bias, _entity_layout(x0.device), bf16_only)
 
 
 def raise_if_negative_index():

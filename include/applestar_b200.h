@@ -292,6 +292,21 @@ int as_spatial_front_bwd(const void* const* planes, const void* const* effects, 
                          const void* cells, const void* codes, const void* dpool, float* dweight, float* dbias, float* g_entity,
                          float* scratch, int64_t R, int H, int W, void* stream);
 
+/* bf16 entity stream of the post-LN Transformer (module_utils.py:133-139): LayerNorm over 256 channels with the linear
+ * output z, the residual, the result and every gradient in bf16 (statistics and reductions fp32).
+ * as_ln256_bf16_fwd: y = LN(z + res) * gamma + beta (+ReLU), stats [rows,2] = (mean, rstd); res may be NULL.
+ * as_ln256_bf16_bwd: g = dy_a + dy_b (dy_b may be NULL: the gradients of y's two consumers arrive separately) ->
+ * dres (residual path, may be NULL), dz = dx * (z > 0 when mask_z), dgamma, dbeta, dbias = column sums of dz;
+ * scratch = as_ln256_bf16_bwd_scratch_floats() floats.  as_masked_mean256_bf16_*: entity_encoder.py:83-85 on that stream. */
+int as_ln256_bf16_fwd(const void* z, const void* res, const float* gamma, const float* beta, void* y, float* stats, int64_t rows,
+                      int relu, void* stream);
+int64_t as_ln256_bf16_bwd_scratch_floats(void);
+int as_ln256_bf16_bwd(const void* dy_a, const void* dy_b, const void* z, const void* res, const float* gamma, const float* beta,
+                      const float* stats, void* dres, void* dz, int mask_z, float* dgamma, float* dbeta, float* dbias,
+                      float* scratch, int64_t rows, int relu, void* stream);
+int as_masked_mean256_bf16_fwd(const void* x, const int64_t* len, float* out, int64_t R, int N, void* stream);
+int as_masked_mean256_bf16_bwd(const float* dout, const int64_t* len, void* dx, int64_t R, int N, void* stream);
+
 /* Tail of the location head (head/action_arg_head.py:440-446): bilinear x2 upsampling (F.interpolate, align_corners
  * False) of x [R,h+2,w+2,32] (padded NHWC bf16) + 3x3 convolution 32 -> 1 (zero padding) + flatten + 1/temperature ->
  * out [R, 2h * 2w] fp32, WITHOUT forming the upsampled map: the two linear steps commute into nine numbers per

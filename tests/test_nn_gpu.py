@@ -222,8 +222,8 @@ def test_lnlstm_layer_fwd_bwd_vs_oracle_cell(T, B, I, H):
         assert err < 0.08 * want.abs().max().item() + 2e-3, (name, err, want.abs().max().item())
 
 
-@pytest.mark.parametrize('relu_ln', [False, True])
-def test_fused_transformer_layer_nodes_vs_torch(relu_ln):
+@pytest.mark.parametrize('relu_ln,bf16_stream', [(False, False), (True, False), (True, True)])
+def test_fused_transformer_layer_nodes_vs_torch(relu_ln, bf16_stream):
     """ops.linear_ln / ops.mlp_ln (attention projection + LN1, FFN + LN2 of the post-LN layer, module_utils.py:121-139,
     each ONE autograd node whose LayerNorm backward feeds the linear backward, hidden ReLU mask in the GEMM epilogue)
     against plain fp32 torch: outputs and every gradient (bf16 GEMMs -> 2% of the tensor's max)."""
@@ -241,10 +241,17 @@ def test_fused_transformer_layer_nodes_vs_torch(relu_ln):
     g1, be1 = (1 + rnd(D, scale=0.1)).requires_grad_(True), rnd(D, scale=0.1).requires_grad_(True)
     g2, be2 = (1 + rnd(D, scale=0.1)).requires_grad_(True), rnd(D, scale=0.1).requires_grad_(True)
     leaves = [a16, res, wp, bp, w1, b1, w2, b2, g1, be1, g2, be2]
-    x32, x16 = ops.linear_ln(a16, res, wp, bp, g1, be1)
-    y32, y16 = ops.mlp_ln(x16, x32, w1, b1, w2, b2, g2, be2, relu_ln)
     go32, go16 = rnd(M, D), rnd(M, D).to(torch.bfloat16)
-    torch.autograd.backward([y32, y16], [go32, go16])
+    if bf16_stream:          # optional all-bf16 stream (ops.ENTITY_BF16): same nodes, residual / outputs / gradients in bf16
+        xa, xb = ops.linear_ln16(a16, res, wp, bp, g1, be1)
+        ya, yb = ops.mlp_ln16(xb, xa, w1, b1, w2, b2, g2, be2, relu_ln)
+        y32, y16 = ya.float(), yb
+        torch.autograd.backward([ya, yb], [go32.to(torch.bfloat16), go16])
+        go32 = go32.to(torch.bfloat16).float()
+    else:
+        x32, x16 = ops.linear_ln(a16, res, wp, bp, g1, be1)
+        y32, y16 = ops.mlp_ln(x16, x32, w1, b1, w2, b2, g2, be2, relu_ln)
+        torch.autograd.backward([y32, y16], [go32, go16])
     mine = [t.grad.float().clone() for t in leaves]
     for t in leaves:
         t.grad = None
@@ -257,10 +264,10 @@ def test_fused_transformer_layer_nodes_vs_torch(relu_ln):
     yr = F.layer_norm(xr + z, (D,), g2, be2)
     if relu_ln:
         yr = F.relu(yr)
-    assert (y32 - yr).abs().max().item() < 0.03 and (y16.float() - yr).abs().max().item() < 0.06
+    assert (y32 - yr).abs().max().item() < (0.08 if bf16_stream else 0.03) and (y16.float() - yr).abs().max().item() < 0.08
     torch.autograd.backward([yr], [go32 + go16.float()])
     names = ['a16', 'res', 'wp', 'bp', 'w1', 'b1', 'w2', 'b2', 'g1', 'be1', 'g2', 'be2']
     for nm, t, m in zip(names, leaves, mine):
         r = t.grad.float()
         rel = ((m - r).norm() / r.norm()).item()
-        assert rel < 0.02, (nm, rel)
+        assert rel < (0.06 if bf16_stream else 0.02), (nm, rel)
