@@ -152,6 +152,11 @@ _SIGS = {
     'as_gumbel_argmax': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     'as_rl_loss_forward': (c_int, [POINTER(AsLossArgs), c_void_p]),
     'as_rl_loss_backward': (c_int, [POINTER(AsLossArgs), c_float, c_void_p]),
+    'as_debug_gemm_mode': (c_int, [c_int]),
+    'as_debug_gemm_profile': (c_int, [c_void_p]),
+    'as_debug_attn_profile': (c_int, [c_void_p]),
+    'as_debug_lstm_profile': (c_int, [c_void_p]),
+    'as_debug_lstm_max_clusters': (c_int, [c_int]),
     'as_clip_adam_scratch_bytes': (c_int64, []),
     'as_clip_adam': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_float, c_float,
                              c_float, c_float, c_float, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -110,6 +110,24 @@ int maxpool2_bwd(const void*, const void*, void*, long long, int, int, int, int,
 
 #define ST(s) reinterpret_cast<cudaStream_t>(s)
 
+namespace as {
+const Knobs& knobs() {
+  static const Knobs k = [] {
+    Knobs v{};
+    v.wgrad_no_pair = getenv("AS_WGRAD_NO_PAIR") != nullptr;
+    v.wgrad_no_slab = getenv("AS_WGRAD_NO_SLAB") != nullptr;
+    v.slab_no_resident = getenv("AS_SLAB_NO_RESIDENT") != nullptr;
+    v.slab_mc = getenv("AS_SLAB_MC") != nullptr;       // CTA-pair weight multicast (this GPU's own weight buffer only); slower, off
+    v.slab_no_halfk = getenv("AS_SLAB_NO_HALFK") != nullptr;
+    v.debug_tmap = getenv("AS_DEBUG_TMAP") != nullptr;
+    const char* e = getenv("AS_SLAB_BSLOTS");
+    v.slab_bslots = e ? atoi(e) : 0;
+    return v;
+  }();
+  return k;
+}
+}  // namespace as
+
 extern "C" {
 
 int as_abi_version(void) { return 5; }
@@ -220,14 +238,14 @@ int as_conv_nhwc_bf16_masked(const void* x, const void* w, void* y, const void* 
 // 0: one tap per tile; 1 / 2: tap pairs on a 64-channel M side (dy / swapped x), needs split-K partials
 // 11 / 12: the same pairing with all nine taps walked from one shared-memory slab per pixel block (wgrad_slab.cu)
 int as_conv_wgrad_pair_mode(int Cin, int Cout, int taps, int splits, int W) {
-  if (taps != 9 || splits <= 1 || getenv("AS_WGRAD_NO_PAIR")) return 0;
+  if (taps != 9 || splits <= 1 || as::knobs().wgrad_no_pair) return 0;
   int mode = 0;
   if (Cout == 64) mode = 1;
   else if (Cin == 64 && Cout < 64) mode = 2;
-  if (mode && !getenv("AS_WGRAD_NO_SLAB") && as::wgrad_slab_ok(mode, Cin, Cout, W + 2)) mode += 10;
+  if (mode && !as::knobs().wgrad_no_slab && as::wgrad_slab_ok(mode, Cin, Cout, W + 2)) mode += 10;
   // 64 -> 128 channels: the plain form has a full M = 128; the slab form (operands swapped, two column halves) still wins by
   // reading the pixels once
-  if (!mode && Cin == 64 && Cout == 128 && !getenv("AS_WGRAD_NO_SLAB") && as::wgrad_slab_ok(2, Cin, Cout, W + 2)) mode = 12;
+  if (!mode && Cin == 64 && Cout == 128 && !as::knobs().wgrad_no_slab && as::wgrad_slab_ok(2, Cin, Cout, W + 2)) mode = 12;
   return mode;
 }
 int64_t as_conv_wgrad_ws_floats(int Cin, int Cout, int taps, int splits, int W) {

@@ -745,7 +745,7 @@ static int make_map(CUtensorMap* tm, const void* ptr, long long inner, long long
                    const_cast<void*>(ptr), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS && getenv("AS_DEBUG_TMAP"))
+  if (r != CUDA_SUCCESS && knobs().debug_tmap)
     fprintf(stderr, "tensor map encode failed: CUresult %d ptr %p dims %llu %llu %llu %llu strides %llu %llu %llu box %u %u es %d\n",
             (int)r, ptr, (unsigned long long)dims[0], (unsigned long long)dims[1], (unsigned long long)dims[2],
             (unsigned long long)dims[3], (unsigned long long)strides[0], (unsigned long long)strides[1],
@@ -890,7 +890,7 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
     const int cin_blocks = (g.K + BK - 1) / BK;
     const long long all_b = (long long)cin_blocks * g.taps * b_bytes;
     if (box <= 256) {
-      if (p.n_blocks == 1 && 2 * slab_bytes + all_b <= ring && !getenv("AS_SLAB_NO_RESIDENT")) {
+      if (p.n_blocks == 1 && 2 * slab_bytes + all_b <= ring && !knobs().slab_no_resident) {
         // every weight tile stays in shared memory for the whole kernel; two slabs double-buffer the pixels
         p.slab = 1; p.slab_slots = 2; p.b_resident = 1; p.tpb = 1; p.b_slots = 1;
       } else {
@@ -900,14 +900,14 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
         int slots = (ring - 3 * slab_bytes) / (tpb * b_bytes);
         if (slots < 3 && tpb > 1) { tpb = 1; slots = (ring - 3 * slab_bytes) / b_bytes; }
         if (slots > max_slots) slots = max_slots;
-        if (const char* e = getenv("AS_SLAB_BSLOTS")) { const int v = atoi(e); if (v >= 2 && v < slots) slots = v; }
+        if (knobs().slab_bslots >= 2 && knobs().slab_bslots < slots) slots = knobs().slab_bslots;
         if (slots >= 2) { p.slab = 1; p.slab_slots = 3; p.b_resident = 0; p.tpb = tpb; p.b_slots = slots; }
         // weight multicast across a CTA pair halves the L2 -> SM weight stream, but measured 4 % SLOWER than independent
         // CTAs on the 128-channel convs (the issuer, not the weight stream, is the limit there): opt-in only
-        if (p.slab && p.n_blocks == 1 && BN >= 64 && (p.m_blocks + 1) / 2 >= 2 && getenv("AS_SLAB_MC")) p.mc = 1;
+        if (p.slab && p.n_blocks == 1 && BN >= 64 && (p.m_blocks + 1) / 2 >= 2 && knobs().slab_mc) p.mc = 1;
       }
       if (p.slab) { p.halo = halo; p.slab_box = box; p.slab_bytes = slab_bytes; a_box_rows = box; }
-      if (p.slab && g.K <= 32 && !getenv("AS_SLAB_NO_HALFK")) p.half_k = 1;
+      if (p.slab && g.K <= 32 && !knobs().slab_no_halfk) p.half_k = 1;
     }
   }
 

@@ -429,6 +429,17 @@ int as_clip_adam(float* p, const float* g, float* m, float* v, void* shadow, int
                  float beta1, float beta2, float eps, float weight_decay, int step, int* step_dev, float* scratch,
                  float* norm_out, void* stream);
 
+/* ---- Diagnostics (tools/ only; no counterpart in the reference).  They set or read PROCESS-GLOBAL state and are not for
+ * production callers: as_debug_gemm_mode changes how every later GEMM / convolution launch behaves (bits 0-2: epilogue
+ * stages skipped for profiling, bit 3: register-store epilogue, bit 4: per-tap convolution mode); the *_profile entry
+ * points install a device buffer that the issuing warps fill with cycle counters (NULL uninstalls it);
+ * as_debug_lstm_max_clusters reports how many 8-CTA clusters of the recurrent kernel fit the device. */
+int as_debug_gemm_mode(int mode);
+int as_debug_gemm_profile(void* buf);
+int as_debug_attn_profile(void* buf);
+int as_debug_lstm_profile(void* buf);
+int as_debug_lstm_max_clusters(int H);
+
 #ifdef __cplusplus
 }
 #endif

@@ -17,6 +17,10 @@ def test_library_exports_every_declared_symbol():
     for name in declared:
         assert hasattr(lib, name), name
     assert declared == set(_lib.EXPORTS)
+    import subprocess
+    nm = subprocess.run(['nm', '-D', '--defined-only', _lib.LIB_PATH], capture_output=True, text=True).stdout
+    exported = {ln.split()[-1] for ln in nm.splitlines() if ln.split() and ln.split()[-1].startswith('as_')}
+    assert exported == declared, sorted(exported ^ declared)        # nothing undeclared is exported either
     assert lib.as_abi_version() >= 1
     assert lib.as_gemm_splits(64 * 10, 4) == 4
     assert lib.as_gemm_splits(64 * 10, 7) == 5     # ceil(10/7)=2 k-blocks per split -> 5 non-empty splits

@@ -58,7 +58,10 @@ def _worker(rank, world, port, q):
         shard = full[rank * 4:(rank + 1) * 4]
         opt.zero_grad()
         model(shard).backward()
+        stats = torch.full((6,), float(rank + 1 + step))          # the step's packed log scalars: one collective, rank mean
+        dm.reduce_stats(stats)
         dm.sync_gradients()
+        assert torch.allclose(stats, torch.full((6,), 1.5 + step)), stats
         # single-process gradient of the mean over both shards
         ref_opt.zero_grad()
         (0.5 * (ref(full[:4]) + ref(full[4:]))).backward()
