@@ -104,6 +104,11 @@ _SIGS = {
     'as_ln256_bf16_bwd': (c_int, [c_void_p] * 9 + [c_int] + [c_void_p] * 4 + [c_int64, c_int, c_void_p]),
     'as_masked_mean256_bf16_fwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     'as_masked_mean256_bf16_bwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
+    'as_embed_relu_fwd': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
+    'as_one_hot_bf16': (c_int, [c_void_p, c_int, c_void_p, c_int64, c_int, c_int, c_void_p]),
+    'as_time_encode': (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
+    'as_bo_features': (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    'as_cast_any_bf16': (c_int, [c_void_p, c_int, c_void_p, c_int64, c_int, c_int, c_void_p]),
     'as_conv_weight_layouts': (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     'as_spatial_fc_weight_fwd': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     'as_spatial_fc_weight_bwd': (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),

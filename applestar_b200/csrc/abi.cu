@@ -67,6 +67,11 @@ int su_prefix_bwd(const float*, const long long*, const long long*, const float*
                   int, int, cudaStream_t);
 int su_mask_logits(const float*, const long long*, const long long*, float*, long long, int, int, int, float, float, cudaStream_t);
 int conv_weight_layouts(const float*, void*, void*, int, int, int, int, cudaStream_t);
+int embed_relu_fwd(const void*, int, const float*, float*, long long, int, int, cudaStream_t);
+int one_hot_bf16(const void*, int, void*, long long, int, int, cudaStream_t);
+int time_encode(const void*, int, const float*, float*, long long, int, cudaStream_t);
+int bo_features(const void*, int, const void*, int, void*, long long, int, int, int, int, int, cudaStream_t);
+int cast_any_bf16(const void*, int, void*, long long, int, int, cudaStream_t);
 int ln256_bf16_fwd(const void*, const void*, const float*, const float*, void*, float*, long long, int, cudaStream_t);
 long long ln256_bf16_bwd_scratch_floats();
 int ln256_bf16_bwd(const void*, const void*, const void*, const void*, const float*, const float*, const float*, void*, void*, int,
@@ -466,6 +471,22 @@ int as_masked_mean256_bf16_fwd(const void* x, const int64_t* len, float* out, in
 }
 int as_masked_mean256_bf16_bwd(const float* dout, const int64_t* len, void* dx, int64_t R, int N, void* stream) {
   return as::masked_mean256_bf16_bwd(dout, reinterpret_cast<const long long*>(len), dx, R, N, ST(stream));
+}
+int as_embed_relu_fwd(const void* idx, int dtype, const float* table, float* out, int64_t R, int V, int D, void* stream) {
+  return as::embed_relu_fwd(idx, dtype, table, out, R, V, D, ST(stream));
+}
+int as_one_hot_bf16(const void* idx, int dtype, void* out, int64_t R, int V, int Vpad, void* stream) {
+  return as::one_hot_bf16(idx, dtype, out, R, V, Vpad, ST(stream));
+}
+int as_time_encode(const void* t, int dtype, const float* position_array, float* out, int64_t R, int D, void* stream) {
+  return as::time_encode(t, dtype, position_array, out, R, D, ST(stream));
+}
+int as_bo_features(const void* order, int order_dtype, const void* location, int location_dtype, void* out, int64_t tokens, int L,
+                   int A, int NB, int map_w, int Kpad, void* stream) {
+  return as::bo_features(order, order_dtype, location, location_dtype, out, tokens, L, A, NB, map_w, Kpad, ST(stream));
+}
+int as_cast_any_bf16(const void* src, int dtype, void* dst, int64_t rows, int K, int Kpad, void* stream) {
+  return as::cast_any_bf16(src, dtype, dst, rows, K, Kpad, ST(stream));
 }
 int as_attn_fwd_ok(int N, int D) { return as::attn_fwd_ok(N, D); }
 int as_attn_fwd(const void* qkv, const int64_t* key_len, void* out, void* probs, int64_t R, int N, int H, int D, float scale,

@@ -12,6 +12,7 @@ import torch.nn.functional as F
 from . import _lib
 
 NUM_SMS = 148
+_DT_CODE = {torch.uint8: 0, torch.int8: 1, torch.int16: 2, torch.float16: 3, torch.int64: 4, torch.float32: 5}
 
 
 def _ptr(t):
@@ -21,7 +22,15 @@ def _ptr(t):
 # ---------------------------------------------------------------------------------------------
 # bf16 staging
 def to_bf16(x):
-    """fp32 [rows, K] -> bf16 [rows, K8] (K padded to a multiple of 8 with zeros so TMA pitches are 16-byte)."""
+    """fp32 (or any narrow storage dtype) [rows, K] -> bf16 [rows, K8] (K padded to a multiple of 8 with zeros so TMA
+    pitches are 16-byte)."""
+    if x.dtype in _DT_CODE and x.dtype != torch.float32 and x.dim() == 2:      # uint8 / int16 / ... straight to the operand
+        x = x.contiguous()
+        k8 = (x.shape[1] + 7) // 8 * 8
+        out = torch.empty((x.shape[0], k8), dtype=torch.bfloat16, device=x.device)
+        _lib.call('as_cast_any_bf16', x.data_ptr(), _DT_CODE[x.dtype], out.data_ptr(), x.shape[0], x.shape[1], k8,
+                  _lib.stream_ptr())
+        return out
     if x.dtype == torch.bfloat16:
         return x if x.shape[-1] % 8 == 0 and x.is_contiguous() else _pad8(x.contiguous())
     x = x.contiguous()
@@ -718,7 +727,6 @@ def attention(qkv, key_len, heads, head_dim):
     return AttentionFn.apply(qkv, key_len, heads, head_dim)
 
 
-_DT_CODE = {torch.uint8: 0, torch.int8: 1, torch.int16: 2, torch.float16: 3, torch.int64: 4, torch.float32: 5}
 _KIND = {'one_hot': 0, 'binary': 1, 'unsqueeze': 2}
 
 

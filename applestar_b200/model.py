@@ -279,7 +279,7 @@ class ScalarEncoder(nn.Module):
             elif arc == 'transformer':
                 e = self.encode_modules[name](s[name], s['bo_location'])
             else:
-                e = self.encode_modules[name](s[name].float())
+                e = self.encode_modules[name](s[name])            # narrow storage dtypes go straight to the bf16 operand
             emb.append(e)
             if is_ctx:
                 ctx.append(e)

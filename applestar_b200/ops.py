@@ -185,28 +185,81 @@ def scatter_connection(proj, x, y, entity_num, H, W, scatter_type='add'):
 
 # ---------------------------------------------------------------------------------------------
 # scalar path
+def _index_tensor(t):
+    t = t.contiguous()
+    if t.dtype not in K._DT_CODE:
+        t = t.long()
+    return t
+
+
+def one_hot_bf16(idx, V):
+    """[kernel] bf16 one-hot rows [R, V8] (index clamped to V - 1): a GEMM operand."""
+    idx = _index_tensor(idx).reshape(-1)
+    v8 = (V + 7) // 8 * 8
+    out = torch.empty((idx.numel(), v8), dtype=torch.bfloat16, device=idx.device)
+    _lib.call('as_one_hot_bf16', idx.data_ptr(), K._DT_CODE[idx.dtype], out.data_ptr(), idx.numel(), V, v8, _lib.stream_ptr())
+    return out
+
+
+class _EmbedRelu(torch.autograd.Function):
+    """[kernel] relu(table[min(idx, V-1)]) (scalar_encoder.py:112-116): exact fp32 gather forward; the table gradient is the
+    tensor-core product (masked dy)^T . one_hot (split-K, deterministic) instead of an index_put."""
+
+    @staticmethod
+    def forward(ctx, idx, table):
+        idx = _index_tensor(idx)
+        table = table.contiguous()
+        R = idx.numel()
+        V, D = table.shape
+        out = torch.empty((R, D), dtype=torch.float32, device=table.device)
+        _lib.call('as_embed_relu_fwd', idx.data_ptr(), K._DT_CODE[idx.dtype], table.data_ptr(), out.data_ptr(), R, V, D,
+                  _lib.stream_ptr())
+        ctx.save_for_backward(idx, out)
+        ctx.vd = (V, D)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        idx, out = ctx.saved_tensors
+        V, D = ctx.vd
+        dy = dy.contiguous().float()
+        R = idx.numel()
+        dz16 = torch.empty((R, D), dtype=torch.bfloat16, device=dy.device)
+        _lib.call('as_linear_bwd_prep2', dy.data_ptr(), 0, out.data_ptr(), 0, dz16.data_ptr(), 0, 0, R, D, _lib.stream_ptr())
+        dt = K._wgrad(dz16, one_hot_bf16(idx, V), D, (V + 7) // 8 * 8)           # [D, V8]
+        return None, dt.t()[:V].contiguous()
+
+
 def embedding_relu(idx, table):
-    return F.relu(F.embedding(idx.long().clamp(max=table.shape[0] - 1), table))
+    require_cuda(table)
+    return _EmbedRelu.apply(idx, table)
 
 
 def time_encode(t, position_array):
-    t = t.float().unsqueeze(1)
-    v = torch.empty(t.shape[0], position_array.shape[0], device=t.device)
-    v[:, 0::2] = torch.sin(t * position_array[0::2])
-    v[:, 1::2] = torch.cos(t * position_array[1::2])
-    return v
+    """[kernel] sinusoidal time code (scalar_encoder.py:91-97)."""
+    require_cuda(position_array)
+    t = _index_tensor(t) if t.dtype != torch.float32 else t.contiguous()
+    out = torch.empty((t.numel(), position_array.shape[0]), dtype=torch.float32, device=position_array.device)
+    _lib.call('as_time_encode', t.data_ptr(), K._DT_CODE[t.dtype], position_array.detach().contiguous().data_ptr(),
+              out.data_ptr(), t.numel(), position_array.shape[0], _lib.stream_ptr())
+    return out
 
 
 def build_order_embed(order, location, weight, bias):
-    """ReLU(W . [one_hot(order,174) | eye(20) | bits10(x) | bits10(y)] + b) as column gathers."""
+    """[kernel] ReLU(W . [one_hot(order,174) | eye(20) | bits10(x) | bits10(y)] + b) (scalar_encoder.py:41-50 + the
+    transformer's embedding layer): the token features are written once as a bf16 operand (as_bo_features) and the
+    product, its ReLU and both gradients run on the tcgen05 GEMM like every other linear layer."""
+    require_cuda(weight)
     R, L = order.shape
-    Wt = weight.t()                                             # [214, 64]
-    loc = location.long()
-    shifts = torch.arange(9, -1, -1, device=order.device)
-    bx = ((loc % C.SPATIAL_X).unsqueeze(-1) >> shifts & 1).float()
-    by = ((loc // C.SPATIAL_X).unsqueeze(-1) >> shifts & 1).float()
-    y = Wt[order.long()] + Wt[174:194].unsqueeze(0) + bx @ Wt[194:204] + by @ Wt[204:214] + bias
-    return F.relu(y)
+    order, location = _index_tensor(order), _index_tensor(location)
+    Kin = weight.shape[1]
+    A = C.NUM_BEGINNING_ORDER_ACTIONS
+    NB = (Kin - A - L) // 2
+    k8 = (Kin + 7) // 8 * 8
+    feats = torch.empty((R * L, k8), dtype=torch.bfloat16, device=weight.device)
+    _lib.call('as_bo_features', order.data_ptr(), K._DT_CODE[order.dtype], location.data_ptr(), K._DT_CODE[location.dtype],
+              feats.data_ptr(), R * L, L, A, NB, C.SPATIAL_X, k8, _lib.stream_ptr())
+    return K.linear(feats, weight, bias, relu=True).view(R, L, -1)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -232,35 +285,13 @@ def fresh_gumbel(rows, n_entity, device):
             'target_unit': gum(rows, n_entity), 'target_location': gum(rows, C.SPATIAL_Y * C.SPATIAL_X)}
 
 
-class _OneHotLinear(torch.autograd.Function):
-    """fc over a one-hot input == gather of one weight column (+bias, ReLU).  Backward: dW = dy^T one_hot as one small
-    dense product (deterministic; the index_put backward of `weight.t()[idx]` sorts and serialises, ~130 us per call)."""
-
-    @staticmethod
-    def forward(ctx, idx, weight, bias, relu):
-        idx = idx.long()
-        y = weight.t()[idx] + bias
-        if relu:
-            y = F.relu(y)
-        ctx.relu, ctx.k = relu, weight.shape[1]
-        ctx.save_for_backward(idx, y if relu else None)
-        return y
-
-    @staticmethod
-    def backward(ctx, dy):
-        idx, y = ctx.saved_tensors
-        if ctx.relu:
-            dy = dy * (y > 0)
-        dy = dy.reshape(-1, dy.shape[-1]).float()
-        one_hot = F.one_hot(idx.reshape(-1), ctx.k).to(dy.dtype)
-        dw = dy.t() @ one_hot if ctx.needs_input_grad[1] else None
-        db = dy.sum(dim=0) if ctx.needs_input_grad[2] else None
-        return None, dw, db, None
-
-
 def one_hot_linear(idx, weight, bias, relu=False):
-    """fc over a one-hot input == gather of one weight column (+bias)."""
-    return _OneHotLinear.apply(idx, weight, bias, relu)
+    """[kernel] fc over a one-hot input (head/action_type_head.py:60-61, action_arg_head.py:48-50, 81-83): the one-hot rows
+    are written as a bf16 operand and the layer is an ordinary tcgen05 linear (forward, data-free backward: dW, db)."""
+    require_cuda(weight)
+    shape = idx.shape
+    y = K.linear(one_hot_bf16(idx, weight.shape[1]), weight, bias, relu)
+    return y.view(*shape, -1)
 
 
 def categorical_log_prob(logits, action):

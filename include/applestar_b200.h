@@ -292,6 +292,22 @@ int as_spatial_front_bwd(const void* const* planes, const void* const* effects, 
                          const void* cells, const void* codes, const void* dpool, float* dweight, float* dbias, float* g_entity,
                          float* scratch, int64_t R, int H, int W, void* stream);
 
+/* Scalar encoder front (obs_encoder/scalar_encoder.py:91-132, :41-53).  dtype codes: 0 uint8, 1 int8, 2 int16, 3 float16,
+ * 4 int64, 5 float32 (the narrow storage types of lib/features.py:44-54 are read directly).
+ * as_embed_relu_fwd: out[r,:] = relu(table[min(idx[r], V-1), :]) (clamp + nn.Embedding + ReLU, :112-116).
+ * as_one_hot_bf16: out[r,:] = e_{min(idx[r], V-1)} as bf16 [R, Vpad]: operand of the GEMMs that replace an embedding's
+ *   index_put backward and the fc over a one-hot action (head/action_type_head.py:60-61, action_arg_head.py:48-50).
+ * as_time_encode: out[r,2k] = sin(t[r] pos[2k]), out[r,2k+1] = cos(t[r] pos[2k+1]) (:91-97).
+ * as_bo_features: build-order token features [one_hot(order, A) | eye(L)[position] | bits_NB(x) | bits_NB(y) | 0] as
+ *   bf16 [tokens, Kpad] (x = location % map_w, y = location / map_w, bits MSB first): operand of the embedding GEMM.
+ * as_cast_any_bf16: [rows, K] of any of the dtypes above -> bf16 [rows, Kpad] zero padded (GEMM operand of an fc field). */
+int as_embed_relu_fwd(const void* idx, int dtype, const float* table, float* out, int64_t R, int V, int D, void* stream);
+int as_one_hot_bf16(const void* idx, int dtype, void* out, int64_t R, int V, int Vpad, void* stream);
+int as_time_encode(const void* t, int dtype, const float* position_array, float* out, int64_t R, int D, void* stream);
+int as_bo_features(const void* order, int order_dtype, const void* location, int location_dtype, void* out, int64_t tokens, int L,
+                   int A, int NB, int map_w, int Kpad, void* stream);
+int as_cast_any_bf16(const void* src, int dtype, void* dst, int64_t rows, int K, int Kpad, void* stream);
+
 /* bf16 entity stream of the post-LN Transformer (module_utils.py:133-139): LayerNorm over 256 channels with the linear
  * output z, the residual, the result and every gradient in bf16 (statistics and reductions fp32).
  * as_ln256_bf16_fwd: y = LN(z + res) * gamma + beta (+ReLU), stats [rows,2] = (mean, rstd); res may be NULL.

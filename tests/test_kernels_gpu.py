@@ -192,3 +192,50 @@ def test_pointer_logits_fwd_bwd(R, S, N, masked):
     assert (out[v] - ref[v]).abs().max().item() < 1e-4
     assert (q.grad - qr.grad).abs().max().item() < 1e-3 * qr.grad.abs().max().item() + 1e-5
     assert (k.grad - kr.grad).abs().max().item() < 1e-3 * kr.grad.abs().max().item() + 1e-5
+
+
+def test_scalar_encoder_front_kernels_vs_torch():
+    """as_embed_relu_fwd / as_one_hot_bf16 / as_time_encode / as_bo_features / as_cast_any_bf16 (scalar_encoder.py:91-132,
+    :41-53) against plain torch on the narrow storage dtypes: the embedding gather is exact, the operand builders are
+    bit-exact, products and weight gradients carry the bf16 rounding of every other linear layer."""
+    import torch.nn.functional as F
+    from applestar_b200 import ops
+    g = torch.Generator().manual_seed(8)
+    Rn = 300
+    idx = torch.randint(0, 140, (Rn,), generator=g).to(torch.int16)            # values above V - 1 are clamped
+    table = torch.randn(128, 64, generator=g)
+    td = table.cuda().requires_grad_(True)
+    out = ops.embedding_relu(idx.cuda(), td)
+    tr = table.clone().requires_grad_(True)
+    ref = F.relu(F.embedding(idx.long().clamp(max=127), tr))
+    assert torch.equal(out.cpu(), ref.detach())
+    go = torch.randn(Rn, 64, generator=g)
+    out.backward(go.cuda()); ref.backward(go)
+    assert (td.grad.cpu() - tr.grad).abs().max().item() < 1e-2 * tr.grad.abs().max().item()
+    assert torch.equal(ops.one_hot_bf16(idx.cuda(), 128)[:, :128].float().cpu(), F.one_hot(idx.long().clamp(max=127), 128).float())
+    t = torch.rand(Rn, generator=g) * 30000
+    pos = synth.time_position_array(32)
+    v = ops.time_encode(t.cuda(), pos.cuda()).cpu()
+    want = torch.empty(Rn, 32)
+    want[:, 0::2] = torch.sin(t.unsqueeze(1) * pos[0::2]); want[:, 1::2] = torch.cos(t.unsqueeze(1) * pos[1::2])
+    assert (v - want).abs().max().item() < 2e-3                                # fp32 sin / cos of arguments up to 3e4
+    order = torch.randint(0, 174, (Rn, 20), generator=g).to(torch.int16)
+    loc = torch.randint(0, 152 * 160, (Rn, 20), generator=g).to(torch.int16)
+    W = torch.randn(64, 214, generator=g) * 0.2
+    b = torch.randn(64, generator=g) * 0.1
+    Wd, bd = W.cuda().requires_grad_(True), b.cuda().requires_grad_(True)
+    y = ops.build_order_embed(order.cuda(), loc.cuda(), Wd, bd)
+    Wr, br = W.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    l = loc.long()
+    feats = torch.cat([F.one_hot(order.long(), 174).float(), torch.eye(20).unsqueeze(0).expand(Rn, 20, 20),
+                       R.bits_msb_first(l % 160, 10), R.bits_msb_first(l // 160, 10)], dim=2)
+    yr = F.relu(F.linear(feats, Wr, br))
+    assert (y.cpu() - yr.detach()).abs().max().item() < 2e-2
+    gy = torch.randn(Rn, 20, 64, generator=g)
+    y.backward(gy.cuda()); yr.backward(gy)
+    assert ((Wd.grad.cpu() - Wr.grad).norm() / Wr.grad.norm()).item() < 5e-2
+    assert ((bd.grad.cpu() - br.grad).norm() / br.grad.norm()).item() < 5e-2
+    x8 = torch.randint(0, 6, (Rn, 261), generator=g).to(torch.uint8)
+    from applestar_b200 import kernels as K
+    x16 = K.to_bf16(x8.cuda())
+    assert x16.shape == (Rn, 264) and torch.equal(x16[:, :261].float().cpu(), x8.float()) and float(x16[:, 261:].abs().sum()) == 0

@@ -270,4 +270,4 @@ def test_fused_transformer_layer_nodes_vs_torch(relu_ln, bf16_stream):
     for nm, t, m in zip(names, leaves, mine):
         r = t.grad.float()
         rel = ((m - r).norm() / r.norm()).item()
-        assert rel < (0.06 if bf16_stream else 0.02), (nm, rel)
+        assert rel < (0.1 if bf16_stream else 0.02), (nm, rel)
