@@ -600,11 +600,63 @@ class ResFCBlock2(nn.Module):
         return ops.layer_norm(self.fc2(self.fc1(x)), self.norm.weight, self.norm.bias, residual=x)
 
 
+class ValueEncoder(nn.Module):
+    """obs_encoder/value_encoder.py:12-74 (`learner.use_value_feature`, self-play critics): opponent statistics through
+    small fc layers, a second ScatterConnection (own + enemy units, 8 channels, 'add') feeding a 10-channel spatial tower
+    (1x1 project, 3 x (max-pool, 3x3 conv), 4 ResBlocks at 32 channels, fc) and the build-order Transformer ->
+    [rows, 544].  Same kernels as the observation encoder: tcgen05 GEMM / implicit-GEMM convolutions, as_scatter_connection."""
+
+    FC_FIELDS = (('enemy_unit_counts_bow', 260, 64), ('enemy_unit_type_bool', 260, 64), ('enemy_agent_statistics', 10, 64),
+                 ('enemy_upgrades', 90, 32), ('cumulative_stat', 167, 128))
+    ONE_HOT_FIELDS = (('unit_alliance', 2, 16), ('unit_type', 260, 48))
+
+    def __init__(self):
+        super().__init__()
+        self.encode_modules = nn.ModuleDict()
+        order = ('enemy_unit_counts_bow', 'enemy_unit_type_bool', 'enemy_agent_statistics', 'enemy_upgrades', 'unit_alliance',
+                 'unit_type', 'cumulative_stat')                       # yaml order (registration order = state_dict order)
+        fc = {n: (i, o) for n, i, o in self.FC_FIELDS}
+        oh = {n: (v, d) for n, v, d in self.ONE_HOT_FIELDS}
+        for name in order:
+            if name in fc:
+                self.encode_modules[name] = FC(fc[name][0], fc[name][1], relu=True)
+            else:
+                self.encode_modules[name] = nn.Embedding(oh[name][0], oh[name][1])
+        self.encode_modules['beginning_order'] = BeginningBuildOrderEncoder()
+        self.scatter_project = FC(64, 8, relu=True)
+        self.project = Conv(10, 16, 1, 0, relu=True, nhwc=True)
+        self.downsample = nn.Sequential(nn.Identity(), Conv(16, 16, 3, 1, True, nhwc=True), nn.Identity(),
+                                        Conv(16, 32, 3, 1, True, nhwc=True), nn.Identity(), Conv(32, 32, 3, 1, True, nhwc=True))
+        self.res = nn.ModuleList([ResBlock(32) for _ in range(4)])
+        self.spatial_fc = FC(32 * (C.SPATIAL_Y // 8) * (C.SPATIAL_X // 8), 128, relu=True)
+
+    def forward(self, x):
+        fc_emb = [self.encode_modules[n](x[n]) for n, _, _ in self.FC_FIELDS]
+        unit = [ops.embedding(x[n], self.encode_modules[n].weight) for n, _, _ in self.ONE_HOT_FIELDS]   # [R*U, d]
+        R, U = x['unit_type'].shape
+        proj = self.scatter_project(torch.cat(unit, dim=-1)).view(R, U, -1)
+        H, W = C.SPATIAL_Y, C.SPATIAL_X
+        smap = ops.scatter_connection(proj, x['unit_x'], x['unit_y'], x['total_unit_count'], H, W, 'add')
+        planes = torch.cat([smap, x['own_units_spatial'].reshape(R, 1, H, W).float(),
+                            x['enemy_units_spatial'].reshape(R, 1, H, W).float()], dim=1)
+        m = self.project(spatial.to_pnhwc(planes, 16))
+        for i in (1, 3, 5):
+            m = self.downsample[i](spatial.max_pool2(m))
+        for block in self.res:
+            m = block(m)
+        sp = spatial.spatial_fc(m, self.spatial_fc[0].weight, self.spatial_fc[0].bias, 32, H // 8, W // 8)
+        bo = self.encode_modules['beginning_order'](x['beginning_order'], x['bo_location'])
+        return torch.cat(fc_emb + [sp, bo], dim=-1)
+
+
 class ValueBaseline(nn.Module):
     """model/value.py:9-39."""
 
-    def __init__(self, param):
+    def __init__(self, param, use_value_feature=False):
         super().__init__()
+        param = dict(param)
+        if use_value_feature:                    # value.py:20-21: + value-encoder output (544) + baseline feature (512)
+            param['input_dim'] = param['input_dim'] + 1056
         self.project = FC(param['input_dim'], param['res_dim'], relu=True)
         self.res = nn.Sequential(*[ResFCBlock2(param['res_dim']) for _ in range(param['res_num'])])
         self.value_fc = FC(param['res_dim'], 1)
@@ -627,16 +679,17 @@ class Model(nn.Module):
         if temperature is not None:
             self.whole_cfg.model.temperature = temperature
         self.cfg = self.whole_cfg.model
-        if self.whole_cfg.get('learner', {}).get('use_value_feature', False):
-            raise NotImplementedError('ValueEncoder (use_value_feature=True) is outside this round (SURVEY §8f-3)')
+        self._use_value_feature = bool(self.whole_cfg.get('learner', {}).get('use_value_feature', False))
         self.encoder = Encoder()
         extra_units = bool(self.whole_cfg.get('agent', {}).get('extra_units', False))
         self.policy = Policy(self.whole_cfg.common.type, extra_units)
         if use_value_network:
+            if self._use_value_feature:                      # model.py:33-34
+                self.value_encoder = ValueEncoder()
             self.value_networks = nn.ModuleDict()
             for k, v in self.cfg.value.items():
                 if k in self.cfg.enable_baselines:
-                    self.value_networks[v['name']] = ValueBaseline(v['param'])
+                    self.value_networks[v['name']] = ValueBaseline(v['param'], self._use_value_feature)
         self.only_update_baseline = self.cfg.get('only_update_baseline', False)
         lc = self.cfg.encoder.core_lstm
         self.core_lstm = StackedLNLSTM(lc.input_size, lc.hidden_size, lc.num_layers)
@@ -706,6 +759,9 @@ class Model(nn.Module):
         critic_input = out.detach() if self.only_update_baseline else out
         br = side_stream(out.device)
         with br:                                                       # value towers next to the policy heads
+            if self._use_value_feature:                                # model.py:138-144
+                bf = base.detach() if self.only_update_baseline else base
+                critic_input = torch.cat([critic_input, self.value_encoder(kwargs['value_feature']), bf], dim=1)
             values = {k: v(critic_input).view(T + 1, B) for k, v in self.value_networks.items()}
         ops.SU_STEPS_HINT = kwargs.get('selected_units_max')       # optional host-side int: avoids a device sync
         try:

@@ -235,6 +235,13 @@ def embedding_relu(idx, table):
     return _EmbedRelu.apply(idx, table)
 
 
+def embedding(idx, table):
+    """[kernel] plain nn.Embedding(idx) (value_encoder.py:53-55) as a tensor-core product one_hot . table, so that the
+    forward and the table gradient are ordinary GEMMs -> [idx.numel(), D]."""
+    require_cuda(table)
+    return K.linear(one_hot_bf16(idx, table.shape[0]), table.t(), None, False)
+
+
 def time_encode(t, position_array):
     """[kernel] sinusoidal time code (scalar_encoder.py:91-97)."""
     require_cuda(position_array)

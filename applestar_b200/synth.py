@@ -196,6 +196,34 @@ def gen_trajectories(unroll_len, batch_size, n_entity=C.MAX_ENTITY_NUM, seed=123
     return data
 
 
+def gen_value_feature(rows, seed=77, n_units=C.MAX_ENTITY_NUM):
+    """`value_feature` of the self-play learner (lib/features.py:690-765 + behaviour Z, agent.py:628-630): opponent
+    statistics, own + enemy unit lists padded to `n_units`, two unit-presence planes, build order / cumulative stat."""
+    g = _gen(seed)
+    H, W = C.SPATIAL_Y, C.SPATIAL_X
+    total = _randint(g, max(2, n_units // 4), n_units + 1, (rows,))
+    valid = torch.arange(n_units).unsqueeze(0) < total.unsqueeze(1)
+
+    def bern(shape, p=0.1):
+        return (torch.rand(shape, generator=g) < p).to(torch.uint8)
+    return {
+        'unit_type': _randint(g, 0, C.NUM_UNIT_TYPES, (rows, n_units), torch.int16) * valid.to(torch.int16),
+        'unit_alliance': _randint(g, 0, 2, (rows, n_units), torch.uint8) * valid.to(torch.uint8),
+        'unit_x': _randint(g, 0, W, (rows, n_units), torch.uint8) * valid.to(torch.uint8),
+        'unit_y': _randint(g, 0, H, (rows, n_units), torch.uint8) * valid.to(torch.uint8),
+        'total_unit_count': total,
+        'enemy_unit_counts_bow': bern((rows, C.NUM_UNIT_TYPES)) * _randint(g, 1, 6, (rows, C.NUM_UNIT_TYPES), torch.uint8),
+        'enemy_unit_type_bool': bern((rows, C.NUM_UNIT_TYPES)),
+        'enemy_agent_statistics': torch.rand((rows, 10), generator=g) * 8.0,
+        'enemy_upgrades': bern((rows, C.NUM_UPGRADES)),
+        'own_units_spatial': torch.rand((rows, 1, H, W), generator=g) < 0.02,
+        'enemy_units_spatial': torch.rand((rows, 1, H, W), generator=g) < 0.02,
+        'beginning_order': _randint(g, 0, C.NUM_BEGINNING_ORDER_ACTIONS, (rows, C.BEGINNING_ORDER_LENGTH), torch.int16),
+        'bo_location': _randint(g, 0, H * W, (rows, C.BEGINNING_ORDER_LENGTH), torch.int16),
+        'cumulative_stat': bern((rows, C.NUM_CUMULATIVE_STAT_ACTIONS)),
+    }
+
+
 def gen_gumbel(rows, seed=99, n_entity=C.MAX_ENTITY_NUM):
     """Fixed Gumbel noise for the six sampling sites (SURVEY.md App. A24 noise contract)."""
     g = _gen(seed)

@@ -26,17 +26,17 @@ from applestar_b200 import synth, config as C, tables  # noqa: E402
 GOLD = os.path.join(ROOT, 'tests', 'golden')
 
 
-def ref_cfg(baselines):
+def ref_cfg(baselines, use_value_feature=False):
     from easydict import EasyDict
     learner = dict(C.DEFAULT_LOSS_CONFIG)
-    learner.update({'use_value_feature': False, 'player_id': 'MP0'})
+    learner.update({'use_value_feature': use_value_feature, 'player_id': 'MP0'})
     return EasyDict({'common': {'type': 'rl'}, 'agent': {'extra_units': True},
                      'model': {'enable_baselines': list(baselines)}, 'learner': learner})
 
 
-def build_ref_model(baselines, seed=0):
+def build_ref_model(baselines, seed=0, use_value_feature=False):
     from distar.agent.default.model.model import Model
-    cfg = ref_cfg(baselines)
+    cfg = ref_cfg(baselines, use_value_feature)
     m = Model(cfg, use_value_network=True)
     trainable = {k for k, p in m.named_parameters() if p.requires_grad}
     spec = [(k, list(v.shape), k in trainable) for k, v in m.state_dict().items()]
@@ -309,6 +309,16 @@ def main():
     if len(sys.argv) > 1 and sys.argv[1] == 'n512':     # the benchmarked entity count; written alone like n128
         torch.save(learner_n512_case(), os.path.join(GOLD, 'learner_n512.pt'))
         print('learner_n512.pt', os.path.getsize(os.path.join(GOLD, 'learner_n512.pt')))
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == 'spec_vf':   # state_dict contract with learner.use_value_feature (ValueEncoder); the
+        path = os.path.join(GOLD, 'state_dict_spec.json')  # existing entries of the file are kept as they are
+        with open(path) as f:
+            specs = json.load(f)
+        _, _, spec = build_ref_model(['winloss'], use_value_feature=True)
+        specs['winloss_value_feature'] = spec
+        with open(path, 'w') as f:
+            json.dump(specs, f)
+        print('state_dict_spec.json: winloss_value_feature', len(spec), 'entries')
         return
     if len(sys.argv) > 1 and sys.argv[1] == 'n512t8':   # tolerance budgets (only) of the T = 8 all-gradients test
         torch.save(learner_n512_case(8, 2, 512, 8512, budgets_only=True), os.path.join(GOLD, 'learner_n512_t8_budget.pt'))

@@ -182,6 +182,16 @@ def spatial_encoder(sd, spatial_info, scatter_map):
     return lin(sd, p + '.fc', x.reshape(x.shape[0], -1), relu=True), skip
 
 
+def build_order_encoder(sd, q, order, bo_location):
+    """BeginningBuildOrderEncoder (scalar_encoder.py:19-53): pre-LN transformer over 20 tokens, mean, fc."""
+    Rn = order.shape[0]
+    loc = bo_location.long()
+    seq = torch.eye(20, device=order.device).unsqueeze(0).expand(Rn, 20, 20)
+    tok = torch.cat([F.one_hot(order.long(), 174).float(), seq, bits_msb_first(loc % W, 10), bits_msb_first(loc // W, 10)], dim=2)
+    t = transformer(sd, q + '.transformer', tok, None, 3, 2, 8, post_ln=False)
+    return lin(sd, q + '.embedd_fc', t.mean(dim=1), relu=True)
+
+
 def scalar_encoder(sd, scalar_info):
     """scalar_encoder.py:99-132 (+ time :91-97, build-order transformer :19-53, pre-LN, App. A3)."""
     p = 'encoder.scalar_encoder'
@@ -193,14 +203,7 @@ def scalar_encoder(sd, scalar_info):
         if arc == 'one_hot':
             e = F.relu(F.embedding(v.long().clamp(max=num - 1), sd['%s.encode_modules.%s.weight' % (p, name)]))
         elif arc == 'bo':
-            q = '%s.encode_modules.beginning_order' % p
-            R = v.shape[0]
-            loc = scalar_info['bo_location'].long()
-            seq = torch.eye(20, device=v.device).unsqueeze(0).expand(R, 20, 20)
-            tok = torch.cat([F.one_hot(v.long(), 174).float(), seq, bits_msb_first(loc % W, 10),
-                             bits_msb_first(loc // W, 10)], dim=2)
-            t = transformer(sd, q + '.transformer', tok, None, 3, 2, 8, post_ln=False)
-            e = lin(sd, q + '.embedd_fc', t.mean(dim=1), relu=True)
+            e = build_order_encoder(sd, '%s.encode_modules.beginning_order' % p, v, scalar_info['bo_location'])
         else:
             e = lin(sd, '%s.encode_modules.%s' % (p, name), v.float(), relu=True)
         emb.append(e)
@@ -433,6 +436,28 @@ def value_baseline(sd, field, x, atan):
 
 
 # ---------------------------------------------------------------------------------------------
+def value_encoder(sd, vf):
+    """obs_encoder/value_encoder.py:48-74 (`learner.use_value_feature`)."""
+    p = 'value_encoder'
+    fc = [lin(sd, '%s.encode_modules.%s' % (p, k), vf[k].float(), relu=True)
+          for k in ('enemy_unit_counts_bow', 'enemy_unit_type_bool', 'enemy_agent_statistics', 'enemy_upgrades', 'cumulative_stat')]
+    unit = torch.cat([F.embedding(vf[k].long(), sd['%s.encode_modules.%s.weight' % (p, k)]) for k in ('unit_alliance', 'unit_type')], -1)
+    proj = lin(sd, p + '.scatter_project', unit, relu=True)
+    proj = proj * seq_mask(vf['total_unit_count'], proj.shape[1]).unsqueeze(2)
+    smap = scatter_connection(proj, vf['unit_x'], vf['unit_y'], 'add')
+    Rn = smap.shape[0]
+    x = torch.cat([smap, vf['own_units_spatial'].reshape(Rn, 1, H, W).float(), vf['enemy_units_spatial'].reshape(Rn, 1, H, W).float()], 1)
+    x = conv(sd, p + '.project', x, relu=True)
+    for i in (1, 3, 5):
+        x = conv(sd, '%s.downsample.%d' % (p, i), F.max_pool2d(x, 2, 2), relu=True, pad=1)
+    for i in range(4):
+        q = '%s.res.%d' % (p, i)
+        x = F.relu(conv(sd, q + '.conv2', conv(sd, q + '.conv1', x, relu=True, pad=1), pad=1) + x)
+    sp = lin(sd, p + '.spatial_fc', x.reshape(Rn, -1), relu=True)
+    bo = build_order_encoder(sd, p + '.encode_modules.beginning_order', vf['beginning_order'], vf['bo_location'])
+    return torch.cat(fc + [sp, bo], -1)
+
+
 def policy_train(sd, lstm_out, entity_embeddings, map_skip, scalar_context, entity_num, action, sun,
                  temperature=1.0):
     """policy.py:50-73."""
@@ -485,11 +510,12 @@ def compute_teacher_logit(sd, spatial_info, entity_info, scalar_info, entity_num
 
 def rl_learner_forward(sd, fields, spatial_info, entity_info, scalar_info, entity_num, hidden_state, action_info,
                        selected_units_num, behaviour_logp, teacher_logit, mask, reward, step, batch_size,
-                       unroll_len, temperature=1.0, **kw):
-    """model.py:95-168. `fields` = enabled baselines (value_networks keys)."""
+                       unroll_len, temperature=1.0, value_feature=None, **kw):
+    """model.py:95-168. `fields` = enabled baselines (value_networks keys); `value_feature` (learner.use_value_feature):
+    the critics see cat[lstm_output, ValueEncoder(value_feature), baseline_feature] (:141-144)."""
     B, T = batch_size, unroll_len
     flat_action = {k: v.flatten(0, 1) for k, v in action_info.items()}
-    lstm_input, ctx, _, ent, skip = encoder(sd, spatial_info, entity_info, scalar_info, entity_num)
+    lstm_input, ctx, base_feat, ent, skip = encoder(sd, spatial_info, entity_info, scalar_info, entity_num)
     state0 = [(h.view(-1, B, h.shape[-1])[0], c.view(-1, B, c.shape[-1])[0]) for h, c in hidden_state]
     out, _ = lnlstm(sd, 'core_lstm', lstm_input.view(-1, B, lstm_input.shape[-1]), state0, 3)
     out = out.reshape(-1, out.shape[-1])
@@ -498,7 +524,8 @@ def rl_learner_forward(sd, fields, spatial_info, entity_info, scalar_info, entit
     logit = {k: v.view(T, B, *v.shape[1:]) for k, v in logit.items()}
     su = logit['selected_units']
     logit['selected_units'] = F.pad(su, (0, 0, 0, MAX_SU - su.shape[2]), 'constant', -1e9)
-    value = {f: value_baseline(sd, f, out, f == 'winloss').view(T + 1, B) for f in fields}
+    critic_in = out if value_feature is None else torch.cat([out, value_encoder(sd, value_feature), base_feat], dim=1)
+    value = {f: value_baseline(sd, f, critic_in, f == 'winloss').view(T + 1, B) for f in fields}
     return {'unroll_len': T, 'batch_size': B, 'selected_units_num': selected_units_num, 'target_logit': logit,
             'value': value, 'action_log_prob': behaviour_logp, 'teacher_logit': teacher_logit, 'mask': mask,
             'action': action_info, 'reward': reward, 'step': step}

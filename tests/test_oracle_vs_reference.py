@@ -161,3 +161,25 @@ def test_pipeline_shim_resolves_through_the_reference_plugin_lookup(ref_model):
         pytest.skip('reference agent not importable in this container: %s' % exc)
     from distar.agent.default import agent as ref_agent
     assert agent_cls is ref_agent.Agent and ref_agent.Model is applestar_b200.Model
+
+
+@reference
+def test_value_encoder_path_matches_reference():
+    """`learner.use_value_feature` (model.py:31-39,141-144; obs_encoder/value_encoder.py): the oracle's ValueEncoder +
+    widened critics against the executed reference (values of every step), and the state_dict contract of that model."""
+    from oracle.ref_loader import load_reference
+    load_reference()
+    from oracle.make_golden import build_ref_model
+    from applestar_b200 import Model
+    torch.manual_seed(0)
+    model, cfg, spec = build_ref_model(['winloss'], use_value_feature=True)
+    sd = synth.full_state_dict([(k, tuple(s), t) for k, s, t in spec], 0)
+    data = synth.gen_trajectories(2, 2, 48, 5)
+    vf = synth.gen_value_feature(6, 9, 48)
+    with torch.no_grad():
+        want = model.rl_learner_forward(value_feature=clone_tree(vf), **clone_tree(data))['value']['winloss']
+        got = R.rl_learner_forward(sd, ['winloss'], value_feature=clone_tree(vf), **clone_tree(data))['value']['winloss']
+    assert max_abs(got, want) < 1e-5
+    mine = Model({'model': {'enable_baselines': ['winloss']}, 'learner': {'use_value_feature': True}}, use_value_network=True)
+    assert {k: tuple(v.shape) for k, v in mine.state_dict().items()} == {k: tuple(s) for k, s, _ in spec}
+    assert {k for k, p in mine.named_parameters() if p.requires_grad} == {k for k, _, t in spec if t}
