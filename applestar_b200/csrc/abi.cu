@@ -67,6 +67,7 @@ int su_prefix_bwd(const float*, const long long*, const long long*, const float*
                   int, int, cudaStream_t);
 int su_mask_logits(const float*, const long long*, const long long*, float*, long long, int, int, int, float, float, cudaStream_t);
 int conv_weight_layouts(const float*, void*, void*, int, int, int, int, cudaStream_t);
+int expand_rows(const float*, const int*, float*, long long, int, float, cudaStream_t);
 int embed_relu_fwd(const void*, int, const float*, float*, long long, int, int, cudaStream_t);
 int one_hot_bf16(const void*, int, void*, long long, int, int, cudaStream_t);
 int time_encode(const void*, int, const float*, float*, long long, int, cudaStream_t);
@@ -487,6 +488,9 @@ int as_bo_features(const void* order, int order_dtype, const void* location, int
 }
 int as_cast_any_bf16(const void* src, int dtype, void* dst, int64_t rows, int K, int Kpad, void* stream) {
   return as::cast_any_bf16(src, dtype, dst, rows, K, Kpad, ST(stream));
+}
+int as_expand_rows_f32(const float* rows, const int32_t* row_of, float* out, int64_t total, int K, float fill, void* stream) {
+  return as::expand_rows(rows, row_of, out, total, K, fill, ST(stream));
 }
 int as_attn_fwd_ok(int N, int D) { return as::attn_fwd_ok(N, D); }
 int as_attn_fwd(const void* qkv, const int64_t* key_len, void* out, void* probs, int64_t R, int N, int H, int D, float scale,

@@ -222,4 +222,30 @@ int clip_adam(float* p, const float* g, float* m, float* v, void* shadow, long l
   return AS_OK;
 }
 
+// out[r, :] = row_of[r] >= 0 ? rows[row_of[r], :] : fill      (dense [total, K] from a compact list of its non-padding rows)
+__global__ void expand_rows_kernel(const float* __restrict__ rows, const int* __restrict__ row_of, float* __restrict__ out,
+                                   long long total, int K, float fill) {
+  const int lane = threadIdx.x & 31;
+  const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long warps_total = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long r = warp_global; r < total; r += warps_total) {
+    const int src = __ldg(row_of + r);
+    float* o = out + r * K;
+    if (src >= 0) {
+      const float* in = rows + (long long)src * K;
+      for (int k = lane; k < K; k += 32) o[k] = __ldg(in + k);
+    } else {
+      for (int k = lane; k < K; k += 32) o[k] = fill;
+    }
+  }
+}
+int expand_rows(const float* rows, const int* row_of, float* out, long long total, int K, float fill, cudaStream_t st) {
+  if (total <= 0) return AS_OK;
+  if (!row_of || !out || K <= 0) return AS_EINVAL;
+  long long blocks = (total + 7) / 8;
+  expand_rows_kernel<<<(unsigned)(blocks < 148 * 16 ? blocks : 148 * 16), 256, 0, st>>>(rows, row_of, out, total, K, fill);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
 }  // namespace as

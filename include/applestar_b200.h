@@ -292,6 +292,12 @@ int as_spatial_front_bwd(const void* const* planes, const void* const* effects, 
                          const void* cells, const void* codes, const void* dpool, float* dweight, float* dbias, float* g_entity,
                          float* scratch, int64_t R, int H, int W, void* stream);
 
+/* Trajectory staging (rl_training/rl_dataloader.py:206-245 pads the teacher's selected-units logits to [T,B,64,N+1] with
+ * -1e9: 134 MB of the 456 MB learner batch, almost all padding).  The host sends only the rows the teacher emitted plus
+ * one int32 per dense row; as_expand_rows_f32 rebuilds the dense tensor on the device:
+ * out[r,:] = row_of[r] >= 0 ? rows[row_of[r],:] : fill. */
+int as_expand_rows_f32(const float* rows, const int32_t* row_of, float* out, int64_t total, int K, float fill, void* stream);
+
 /* Scalar encoder front (obs_encoder/scalar_encoder.py:91-132, :41-53).  dtype codes: 0 uint8, 1 int8, 2 int16, 3 float16,
  * 4 int64, 5 float32 (the narrow storage types of lib/features.py:44-54 are read directly).
  * as_embed_relu_fwd: out[r,:] = relu(table[min(idx[r], V-1), :]) (clamp + nn.Embedding + ReLU, :112-116).

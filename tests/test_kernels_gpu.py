@@ -239,3 +239,34 @@ def test_scalar_encoder_front_kernels_vs_torch():
     from applestar_b200 import kernels as K
     x16 = K.to_bf16(x8.cuda())
     assert x16.shape == (Rn, 264) and torch.equal(x16[:, :261].float().cpu(), x8.float()) and float(x16[:, 261:].abs().sum()) == 0
+
+
+@pytest.mark.gpu
+def test_trajectory_stager_rebuilds_the_dense_batch_bit_exactly():
+    """staging.pack -> Stager.load: every tensor of the batch arrives as the reference learner would see it, the teacher's
+    selected-units logits rebuilt from their emitted rows (rl_dataloader.py:206-245 padding = -1e9)."""
+    from applestar_b200 import staging, synth
+    dev = torch.device('cuda:0')
+    for (T, B, N, seed) in ((4, 3, 64, 5), (2, 2, 512, 6)):
+        host = synth.gen_trajectories(T, B, N, seed)
+        packed = staging.pack(host)
+        dst = synth.tree_map(lambda t: torch.zeros_like(t, device=dev), host)
+        staging.Stager(packed, dev).load(packed, dst)
+        torch.cuda.synchronize()
+        flat_ref, flat_out = [], []
+        synth.tree_map(lambda t: flat_ref.append(t) or t, host)
+        synth.tree_map(lambda t: flat_out.append(t) or t, dst)
+        assert len(flat_ref) == len(flat_out)
+        for a, b in zip(flat_ref, flat_out):
+            assert torch.equal(a, b.cpu())
+    # a batch whose teacher emitted nothing at all (all padding) and one where every row is data
+    host = synth.gen_trajectories(2, 2, 64, 7)
+    for fill_all in (True, False):
+        h = dict(host); h['teacher_logit'] = dict(host['teacher_logit'])
+        su = torch.full_like(host['teacher_logit']['selected_units'], staging.FILL) if fill_all else \
+            torch.randn_like(host['teacher_logit']['selected_units'])
+        h['teacher_logit']['selected_units'] = su
+        packed = staging.pack(h)
+        dst = synth.tree_map(lambda t: torch.zeros_like(t, device=dev), h)
+        staging.Stager(packed, dev).load(packed, dst)
+        assert torch.equal(dst['teacher_logit']['selected_units'].cpu(), su)

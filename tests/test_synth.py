@@ -43,3 +43,23 @@ def test_state_dict_spec_counts():
     sd2 = synth.synth_state_dict([(k, s) for k, s, t in spec if t][:5], 0)
     for k in sd:
         assert torch.equal(sd[k], sd2[k])
+
+
+def test_trajectory_pack_is_lossless_and_compact():
+    """staging.pack (collation side of the compact trajectory layout): only the teacher's emitted selected-units rows
+    travel; the dense [T,B,64,N+1] tensor is recovered exactly from rows + row_of."""
+    import torch
+    from applestar_b200 import staging, synth
+    data = synth.gen_trajectories(4, 3, 64, 11)
+    packed = staging.pack(data, pin=False)
+    c = packed['teacher_logit']['selected_units']
+    dense = data['teacher_logit']['selected_units']
+    assert c['shape'] == tuple(dense.shape)
+    rebuilt = torch.full((c['row_of'].numel(), dense.shape[-1]), staging.FILL)
+    sel = c['row_of'] >= 0
+    rebuilt[sel] = c['rows'][c['row_of'][sel].long()]
+    assert torch.equal(rebuilt.view(dense.shape), dense)
+    emitted = int(torch.clamp(data['selected_units_num'], min=1).sum())
+    assert c['rows'].shape[0] == emitted                       # exactly the rows the teacher emitted
+    saved = staging.packed_bytes(data) - staging.packed_bytes(packed)
+    assert saved == (dense.numel() - c['rows'].numel()) * 4 - c['row_of'].numel() * 4 and saved > 0
