@@ -164,8 +164,8 @@ def gemm_flops_hook(records):
     orig = _lib.call
 
     def hooked(name, *a):
-        if name not in ('as_gemm_bf16', 'as_conv_nhwc_bf16', 'as_conv_nhwc_bf16_add', 'as_conv_wgrad_nhwc_bf16', 'as_attn_fwd',
-                        'as_attn_bwd_dq'):
+        if name not in ('as_gemm_bf16', 'as_gemm_bf16_masked', 'as_conv_nhwc_bf16', 'as_conv_nhwc_bf16_add',
+                        'as_conv_nhwc_bf16_masked', 'as_conv_wgrad_nhwc_bf16', 'as_attn_fwd', 'as_attn_bwd_dq'):
             return orig(name, *a)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda._sleep(120000)         # keep the stream busy while the host enqueues, so that e0 -> e1 is the kernel's
@@ -175,7 +175,9 @@ def gemm_flops_hook(records):
         if name == 'as_gemm_bf16':
             M, N, K, nb = a[5], a[6], a[7], a[13] * a[14]
             fl = 2.0 * M * N * K * nb
-        elif name == 'as_conv_nhwc_bf16_add':             # (x, w, y, bias, addend, R, H, W, Cin, Cout, taps, ...)
+        elif name == 'as_gemm_bf16_masked':               # (A, B, C, mask, M, N, K, ...)
+            fl = 2.0 * a[4] * a[5] * a[6]
+        elif name in ('as_conv_nhwc_bf16_add', 'as_conv_nhwc_bf16_masked'):   # (x, w, y, bias|addend, addend|mask, R, H, W, Cin, Cout, taps, ...)
             R, H, W, Cin, Cout, taps = a[5], a[6], a[7], a[8], a[9], a[10]
             fl = 2.0 * R * (H + 2) * (W + 2) * Cin * Cout * taps
         elif name == 'as_conv_wgrad_nhwc_bf16':           # (dy, x, dw, ws, R, H, W, Cin, Cout, taps, ...)

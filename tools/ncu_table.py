@@ -39,3 +39,12 @@ for name, a in sorted(agg.items(), key=lambda kv: -kv[1][1]):
     print('%-62s %6d %10.1f %5.1f%% %9.1f %9.1f %8.0f %6.1f%% %7.1f%%' % (name[:62], a[0], a[1], 100 * a[1] / tot, a[2] / 1e6, a[3] / 1e6, gbs,
                                                                  100 * gbs / peak, a[4] / a[1] if a[1] > 0 else 0))
 print('total %.1f us over %d launches (serialised, cold-cache ncu replays: compare shares and per-kernel rates, not the sum)' % (tot, sum(a[0] for a in agg.values())))
+if len(sys.argv) > 3:                       # tensor-family DRAM traffic for bench.py's roofline.traffic
+    import json
+    fam = [(n, a) for n, a in agg.items() if re.search(r'gemm_kernel|attn_kernel|wgrad_slab_kernel|attn_bwd', n)]
+    launches = sum(a[0] for _, a in fam)
+    total = sum(a[2] + a[3] for _, a in fam)
+    json.dump({'source': sys.argv[4] if len(sys.argv) > 4 else sys.argv[1], 'launches': launches, 'dram_bytes_per_step': total,
+               'dram_bytes_per_launch_mean': total / max(launches, 1), 'time_us': sum(a[1] for _, a in fam),
+               'kernels': {n: {'launches': a[0], 'dram_bytes': a[2] + a[3], 'time_us': a[1]} for n, a in fam}},
+              open(sys.argv[3], 'w'), indent=1)
