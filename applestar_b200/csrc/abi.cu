@@ -68,6 +68,10 @@ int su_prefix_bwd(const float*, const long long*, const long long*, const float*
 int su_mask_logits(const float*, const long long*, const long long*, float*, long long, int, int, int, float, float, cudaStream_t);
 int conv_weight_layouts(const float*, void*, void*, int, int, int, int, cudaStream_t);
 int expand_rows(const float*, const int*, float*, long long, int, float, cudaStream_t);
+int ce_rows_fwd(const float*, long long, const long long*, const long long*, const long long*, int, int, float, float*, float*, int*, long long,
+                cudaStream_t);
+int ce_rows_bwd(const float*, long long, const long long*, const long long*, const long long*, int, int, float, const float*, const float*,
+                float*, long long, cudaStream_t);
 int embed_relu_fwd(const void*, int, const float*, float*, long long, int, int, cudaStream_t);
 int one_hot_bf16(const void*, int, void*, long long, int, int, cudaStream_t);
 int time_encode(const void*, int, const float*, float*, long long, int, cudaStream_t);
@@ -491,6 +495,16 @@ int as_cast_any_bf16(const void* src, int dtype, void* dst, int64_t rows, int K,
 }
 int as_expand_rows_f32(const float* rows, const int32_t* row_of, float* out, int64_t total, int K, float fill, void* stream) {
   return as::expand_rows(rows, row_of, out, total, K, fill, ST(stream));
+}
+int as_ce_rows_fwd(const float* logits, int64_t ld, const int64_t* labels, const int64_t* excl, const int64_t* excl_len, int S, int K,
+                   float smoothing, float* loss, float* lse, int32_t* argmax, int64_t R, void* stream) {
+  return as::ce_rows_fwd(logits, ld, (const long long*)labels, (const long long*)excl, (const long long*)excl_len, S, K, smoothing, loss, lse,
+                         argmax, R, ST(stream));
+}
+int as_ce_rows_bwd(const float* logits, int64_t ld, const int64_t* labels, const int64_t* excl, const int64_t* excl_len, int S, int K,
+                   float smoothing, const float* lse, const float* g, float* dlogits, int64_t R, void* stream) {
+  return as::ce_rows_bwd(logits, ld, (const long long*)labels, (const long long*)excl, (const long long*)excl_len, S, K, smoothing, lse, g,
+                         dlogits, R, ST(stream));
 }
 int as_attn_fwd_ok(int N, int D) { return as::attn_fwd_ok(N, D); }
 int as_attn_fwd(const void* qkv, const int64_t* key_len, void* out, void* probs, int64_t R, int N, int H, int D, float scale,

@@ -293,3 +293,45 @@ def full_state_dict(spec, seed=0):
     sd = synth_state_dict([(k, s) for k, s, t in spec if t], seed)
     sd['encoder.scalar_encoder.position_array'] = time_position_array(32)
     return sd
+
+
+def gen_sl_loss_inputs(b, s, N, seed):
+    """Seeded inputs of SupervisedLoss.compute_loss (sl_learner.py:50-53): six logit tensors as `Model.sl_train` returns
+    them (selected_units [b, s, N+1], -1e9 beyond each sample's entities), labels, per-head action masks, lengths.
+    Sample 0 selects nothing (length 0, masked out), sample 1 has the maximum length s, one sample repeats a unit."""
+    g = torch.Generator().manual_seed(seed)
+    entity_num = torch.randint(max(s + 1, N // 2), N + 1, (b,), generator=g)
+    sun = torch.randint(2, s + 1, (b,), generator=g)
+    sun[0], sun[1 % b] = 0, s
+    dims = {'action_type': 327, 'delay': 128, 'queued': 2, 'target_unit': N, 'target_location': 152 * 160}
+    logits = {k: torch.randn(b, d, generator=g) * 2.0 for k, d in dims.items()}
+    su = torch.randn(b, s, N + 1, generator=g) * 2.0
+    ent = torch.arange(N + 1).unsqueeze(0)
+    su = su.masked_fill((ent > entity_num.unsqueeze(1)).unsqueeze(1), -1e9)
+    logits['selected_units'] = su
+    logits['target_unit'] = logits['target_unit'].masked_fill(torch.arange(N).unsqueeze(0) >= entity_num.unsqueeze(1), -1e9)
+    actions = {k: torch.randint(0, d, (b,), generator=g) for k, d in dims.items()}
+    actions['target_unit'] = (torch.rand(b, generator=g) * entity_num).long()
+    units = torch.zeros(b, 64, dtype=torch.long)
+    infer = torch.zeros(b, s, dtype=torch.long)
+    for i in range(b):
+        n_i, L = int(entity_num[i]), int(sun[i])
+        if L > 0:
+            perm = torch.randperm(n_i, generator=g)[:L - 1]
+            units[i, :L - 1] = perm
+            units[i, L - 1] = n_i                                      # end flag
+        guess = torch.randperm(n_i, generator=g)[:s]
+        infer[i] = guess
+        if L > 1:
+            infer[i, :(L + 1) // 2] = units[i, :(L + 1) // 2]          # partly right
+        if i % 2 == 0 and s > 2:
+            infer[i, int(torch.randint(1, s, (1,), generator=g))] = n_i
+    if b > 2 and int(sun[2]) > 2:
+        units[2, 1] = units[2, 0]                                      # a repeated pick
+    actions['selected_units'] = units
+    mask = {k: (torch.rand(b, generator=g) > 0.3).float() for k in list(dims) + ['selected_units']}
+    mask['action_type'] = torch.ones(b)
+    mask['selected_units'][0] = 0.
+    mask['queued'] = torch.zeros(b)                                   # a head with no valid row at all
+    return {'logits': logits, 'actions': actions, 'actions_mask': mask, 'selected_units_num': sun, 'entity_num': entity_num,
+            'infer_selected_units': infer}

@@ -298,6 +298,18 @@ int as_spatial_front_bwd(const void* const* planes, const void* const* effects, 
  * out[r,:] = row_of[r] >= 0 ? rows[row_of[r],:] : fill. */
 int as_expand_rows_f32(const float* rows, const int32_t* row_of, float* out, int64_t total, int K, float fill, void* stream);
 
+/* Supervised loss rows (sl_training/sl_loss.py:16-36,127-285): cross entropy of R rows of K fp32 logits (row pitch ld)
+ * against int64 labels.  loss[r] = (1-smoothing)*(lse - x[label]) + smoothing*(lse - mean(x)); lse[r] and the arg-max of
+ * every row (first maximum) are also written.  excl != NULL selects the SelectedUnits label mask of sl_loss.py:190-204:
+ * rows are (sample b, step s) with s < S, excl = labels [R/S, S], excl_len[b] = selected_units_num - 1 (>= 0); logit k of
+ * row (b, s) counts as -1e9 when k is one of excl[b, :excl_len[b]] other than this step's own label.
+ * as_ce_rows_bwd: dlogits[r, :] = g[r] * d loss[r] / d logits[r, :] (zero at excluded positions and for rows with g == 0;
+ * every element of the R x K block is written). */
+int as_ce_rows_fwd(const float* logits, int64_t ld, const int64_t* labels, const int64_t* excl, const int64_t* excl_len, int S, int K,
+                   float smoothing, float* loss, float* lse, int32_t* argmax, int64_t R, void* stream);
+int as_ce_rows_bwd(const float* logits, int64_t ld, const int64_t* labels, const int64_t* excl, const int64_t* excl_len, int S, int K,
+                   float smoothing, const float* lse, const float* g, float* dlogits, int64_t R, void* stream);
+
 /* Scalar encoder front (obs_encoder/scalar_encoder.py:91-132, :41-53).  dtype codes: 0 uint8, 1 int8, 2 int16, 3 float16,
  * 4 int64, 5 float32 (the narrow storage types of lib/features.py:44-54 are read directly).
  * as_embed_relu_fwd: out[r,:] = relu(table[min(idx[r], V-1), :]) (clamp + nn.Embedding + ReLU, :112-116).

@@ -10,6 +10,7 @@ The fixtures pin oracle/restate.py (and through it the CUDA path) to the execute
   learner_n512.pt        the learner case at the benchmarked N=512 (T=4, B=2, special observations) with ~300 reference
                          gradient tensors and the reference's own bf16-autocast gradient error; `... make_golden.py n512`
   scatter_small.pt       scatter_connection on a heavy-collision case
+  sl_loss_small.pt       SupervisedLoss.compute_loss (log entries + logit gradients, three configurations); `... sl_loss`
 Inputs and weights are NOT stored: tests regenerate them from the same seeds (applestar_b200/synth.py).
 """
 import json
@@ -245,6 +246,26 @@ def learner_n512_case(T=4, B=2, N=512, seed=5120, budgets_only=False):
     return res
 
 
+def sl_loss_case(b=6, s=5, N=24, seed=77):
+    """SupervisedLoss.compute_loss of the executed reference (sl_loss.py:102-121) on synth.gen_sl_loss_inputs: every log
+    entry for label_smooth off / on and su_mask on / off, and d total_loss / d logits for the default configuration."""
+    from easydict import EasyDict
+    from distar.agent.default.sl_training.sl_loss import SupervisedLoss
+    out = {'meta': dict(b=b, s=s, N=N, seed=seed)}
+    for tag, extra in (('default', {}), ('label_smooth', {'label_smooth': True}), ('no_su_mask', {'su_mask': False})):
+        d = synth.gen_sl_loss_inputs(b, s, N, seed)
+        logits = {k: v.clone().requires_grad_(True) for k, v in d['logits'].items()}
+        loss = SupervisedLoss(EasyDict({'learner': dict(extra)}))
+        info = loss.compute_loss(logits, d['actions'], d['actions_mask'], d['selected_units_num'], d['entity_num'],
+                                 {'selected_units': d['infer_selected_units']})
+        info['total_loss'].backward()
+        out[tag] = {'info': {k: float(v) for k, v in info.items()},
+                    'dlogits': {k: v.grad.clone() for k, v in logits.items() if k != 'target_location'},
+                    'dlogits_location_sum_abs': float(logits['target_location'].grad.abs().sum()),
+                    'dlogits_location_row0': logits['target_location'].grad[0].clone()}
+    return out
+
+
 def infer_case(B, N, seed):
     model, cfg, _ = build_ref_model(['winloss'])
     model.eval()
@@ -319,6 +340,10 @@ def main():
         with open(path, 'w') as f:
             json.dump(specs, f)
         print('state_dict_spec.json: winloss_value_feature', len(spec), 'entries')
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == 'sl_loss':  # SupervisedLoss
+        torch.save(sl_loss_case(), os.path.join(GOLD, 'sl_loss_small.pt'))
+        print('sl_loss_small.pt', os.path.getsize(os.path.join(GOLD, 'sl_loss_small.pt')))
         return
     if len(sys.argv) > 1 and sys.argv[1] == 'n512t8':   # tolerance budgets (only) of the T = 8 all-gradients test
         torch.save(learner_n512_case(8, 2, 512, 8512, budgets_only=True), os.path.join(GOLD, 'learner_n512_t8_budget.pt'))

@@ -682,3 +682,85 @@ def compute_loss(cfg, inputs, only_update_value=False, use_dapo=False):
     else:
         info['total_loss'] = total_pg + total_upgo + total_critic + total_ent + total_kl + at_kl + total_dapo
     return info
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Supervised loss (reference: agent/default/sl_training/sl_loss.py; weights: default_supervised_loss.yaml)
+SL_LOSS_WEIGHT = {'action_type': 30.0, 'delay': 9.0, 'queued': 1.0, 'selected_units': 4.0, 'target_unit': 4.0,
+                  'target_location': 8.0}
+
+
+def _sl_ce(logits, labels, smoothing):
+    """sl_loss.py:16-36 (label smoothing) / torch CrossEntropyLoss(reduction='none') (:58-59)"""
+    logp = torch.log_softmax(logits, dim=-1)
+    nll = -logp.gather(-1, labels.unsqueeze(-1)).squeeze(-1)
+    if smoothing > 0:
+        return (1.0 - smoothing) * nll + smoothing * (-logp.mean(dim=-1))
+    return nll
+
+
+def _sl_masked_mean(loss_rows, mask):
+    """sl_loss.py:134-139: sum over valid rows / number of valid rows (0 when none)"""
+    n = mask.sum()
+    return loss_rows.sum() / n if n > 0 else loss_rows.sum() * 0
+
+
+def supervised_loss(logits, actions, actions_mask, selected_units_num, entity_num, infer_selected_units, label_smooth=False,
+                    su_mask=True, loss_weight=None):
+    """SupervisedLoss.compute_loss (sl_loss.py:102-121) without cross_rank_loss."""
+    w = dict(SL_LOSS_WEIGHT, **(loss_weight or {}))
+    sm = 0.1 if label_smooth else 0.0
+    out = {}
+    # single-label heads (:123-185, :246-285)
+    for head in ('action_type', 'delay', 'queued', 'target_unit', 'target_location'):
+        x, y, m = logits[head], actions[head].long(), actions_mask[head].float()
+        out[head + '_loss'] = _sl_masked_mean(_sl_ce(x, y, sm) * m, m)
+        pred = x.argmax(dim=-1)
+        if head == 'action_type':
+            out['action_type_acc'] = (pred == y).float().sum() / len(y)
+        elif head == 'delay':
+            out['delay_distance_L1'] = ((pred - y).abs() * m).sum() / (m.sum() + 1e-6)
+        elif head == 'queued':
+            out['queued_acc'] = ((pred - y).abs() * m).sum() / (m.sum() + 1e-6)
+        elif head == 'target_unit':
+            out['target_unit_acc'] = ((pred == y) * m).sum() / (m.sum() + 1e-6)
+        else:
+            dx, dy = pred % 160 - y % 160, pred // 160 - y // 160
+            out['target_location_distance_L2'] = ((dx * dx + dy * dy).float().sqrt() * m).sum() / (m.sum() + 1e-6)
+    # selected units (:187-244)
+    x, m, lengths = logits['selected_units'], actions_mask['selected_units'].float(), selected_units_num.long()
+    b, s, n = x.shape
+    y = actions['selected_units'][:, :s].long()
+    if su_mask:                                   # :190-204: the sample's other picks (end flag excluded) leave the candidates
+        steps = torch.arange(s)
+        picked = steps.unsqueeze(0) < (lengths - 1).clamp(min=0).unsqueeze(1)               # [b, s]
+        hide = torch.zeros(b, n + 1, dtype=torch.bool)
+        hide.scatter_(1, torch.where(picked, y, torch.full_like(y, n)), True)
+        hide = hide[:, :n].unsqueeze(1).repeat(1, s, 1)                                     # same set for every step ...
+        own = torch.zeros(b, s, n + 1, dtype=torch.bool)
+        own.scatter_(2, torch.where(picked, y, torch.full_like(y, n)).unsqueeze(2), True)
+        hide = hide & ~own[:, :, :n]                                                        # ... except the step's own label
+        x = x.masked_fill(hide, -1e9)
+    in_seq = torch.arange(s).unsqueeze(0) < lengths.unsqueeze(1)
+    rows = _sl_ce(x.reshape(b * s, n), y.reshape(-1), 0.0).view(b, s)
+    rows = rows.masked_fill(~in_seq, 0) * m.unsqueeze(1)
+    out['selected_units_loss'] = rows.sum() / b
+    out['selected_units_loss_norm'] = rows.sum() / (lengths.sum() + 1e-6)
+    out['selected_units_end_flag_loss'] = rows[torch.arange(b), lengths - 1].mean()
+    if infer_selected_units is not None:          # :223-241: IoU of the predicted and labelled unit sets
+        p = infer_selected_units[:, :s].long()
+        iou_rows = torch.zeros(b)
+        for i in range(b):
+            hits = (p[i] == entity_num[i]).nonzero()
+            first = int(hits[0]) if len(hits) else 0
+            stop = first + 1 + (s if first == 0 else 0)
+            pset = set((p[i, :min(stop, s)]).tolist())
+            lset = set(y[i, :int(lengths[i])].tolist())
+            inter, union = len(pset & lset), len(pset | lset)
+            iou_rows[i] = inter / (union + 1e-6)
+        out['selected_units_iou'] = (iou_rows * m).sum() / (m.sum() + 1e-6)
+    else:
+        out['selected_units_iou'] = 0.
+    out['total_loss'] = sum(out[h + '_loss'] * w[h] for h in ('action_type', 'delay', 'queued', 'selected_units', 'target_unit',
+                                                              'target_location'))
+    return out

@@ -270,3 +270,75 @@ def test_trajectory_stager_rebuilds_the_dense_batch_bit_exactly():
         dst = synth.tree_map(lambda t: torch.zeros_like(t, device=dev), h)
         staging.Stager(packed, dev).load(packed, dst)
         assert torch.equal(dst['teacher_logit']['selected_units'].cpu(), su)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('tag,cfg,kw', [('default', {}, {}), ('label_smooth', {'label_smooth': True}, {'label_smooth': True}),
+                                        ('no_su_mask', {'su_mask': False}, {'su_mask': False})])
+def test_supervised_loss_vs_oracle_and_reference_fixture(tag, cfg, kw):
+    """applestar_b200.SupervisedLoss (as_ce_rows_fwd/bwd) against the reference's own output (fixture) and the oracle:
+    15 log entries and the gradient of every logit tensor; fp32 arithmetic, tolerance 2e-5 abs + 1e-4 rel."""
+    from applestar_b200 import SupervisedLoss, synth
+    from oracle import restate
+    from util import golden
+    fx = golden('sl_loss_small.pt')
+    m = fx['meta']
+    d = synth.gen_sl_loss_inputs(m['b'], m['s'], m['N'], m['seed'])
+    dev = torch.device('cuda:0')
+    cu = synth.tree_map(lambda t: t.to(dev), d)
+    logits = {k: v.clone().requires_grad_(True) for k, v in cu['logits'].items()}
+    info = SupervisedLoss({'learner': cfg}).compute_loss(logits, cu['actions'], cu['actions_mask'], cu['selected_units_num'],
+                                                        cu['entity_num'], {'selected_units': cu['infer_selected_units']})
+    info['total_loss'].backward()
+    ologits = {k: v.clone().requires_grad_(True) for k, v in d['logits'].items()}
+    oinfo = restate.supervised_loss(ologits, d['actions'], d['actions_mask'], d['selected_units_num'], d['entity_num'],
+                                    d['infer_selected_units'], **kw)
+    oinfo['total_loss'].backward()
+    ref = fx[tag]
+    assert set(info) == set(ref['info'])
+    for k, v in ref['info'].items():
+        assert abs(float(info[k]) - v) <= 2e-5 + 1e-4 * abs(v), (k, float(info[k]), v)
+        assert abs(float(info[k]) - float(oinfo[k])) <= 2e-5 + 1e-4 * abs(v), (k, float(info[k]), float(oinfo[k]))
+    for k in logits:
+        g, og = logits[k].grad.cpu(), ologits[k].grad
+        assert torch.allclose(g, og, rtol=1e-4, atol=2e-6), (k, float((g - og).abs().max()))
+        if k in ref['dlogits']:
+            assert torch.allclose(g, ref['dlogits'][k], rtol=1e-4, atol=2e-6), k
+
+
+@pytest.mark.gpu
+def test_ce_rows_at_learner_size_vs_torch():
+    """The row kernels at the SL learner's sizes (1024 rows x 24 320 location logits; 1024 x 64 x 513 selected-units logits
+    with the label mask) against torch's log_softmax on the same device; arg-max bit-equal."""
+    from applestar_b200.sl_loss import ce_rows
+    dev = torch.device('cuda:0')
+    g = torch.Generator(device=dev).manual_seed(3)
+    x = (torch.randn(1024, 24320, device=dev, generator=g) * 3).requires_grad_(True)
+    y = torch.randint(0, 24320, (1024,), device=dev, generator=g)
+    w = torch.rand(1024, device=dev, generator=g)
+    w[::7] = 0
+    row, arg = ce_rows(x, y, 0.1)
+    (row * w).sum().backward()
+    x2 = x.detach().clone().requires_grad_(True)
+    lp = torch.log_softmax(x2, -1)
+    ref = 0.9 * (-lp.gather(1, y[:, None]).squeeze(1)) + 0.1 * (-lp.mean(-1))
+    (ref * w).sum().backward()
+    assert torch.equal(arg.long(), x.argmax(-1))
+    assert torch.allclose(row, ref, rtol=1e-5, atol=1e-5)
+    assert torch.allclose(x.grad, x2.grad, rtol=1e-4, atol=1e-7)
+    b, s, n = 1024, 64, 513
+    su = torch.randn(b, s, n, device=dev, generator=g).requires_grad_(True)
+    lens = torch.randint(0, s + 1, (b,), device=dev, generator=g)
+    lab = torch.stack([torch.randperm(n, device=dev, generator=g)[:s] for _ in range(64)]).repeat(b // 64, 1)
+    row, _ = ce_rows(su.view(b * s, n), lab.reshape(-1), 0.0, lab, (lens - 1).clamp(min=0), s)
+    row.sum().backward()
+    picked = torch.arange(s, device=dev)[None] < (lens - 1).clamp(min=0)[:, None]
+    hide = torch.zeros(b, n + 1, dtype=torch.bool, device=dev).scatter_(1, torch.where(picked, lab, torch.full_like(lab, n)), True)
+    hide = hide[:, None, :n].repeat(1, s, 1)
+    own = torch.zeros(b, s, n + 1, dtype=torch.bool, device=dev).scatter_(2, torch.where(picked, lab, torch.full_like(lab, n))[..., None], True)
+    su2 = su.detach().clone().requires_grad_(True)
+    lp = torch.log_softmax(su2.masked_fill(hide & ~own[..., :n], -1e9), -1)
+    ref = -lp.gather(2, lab[..., None]).squeeze(2)
+    ref.sum().backward()
+    assert torch.allclose(row.view(b, s), ref, rtol=1e-5, atol=1e-5)
+    assert torch.allclose(su.grad, su2.grad, rtol=1e-4, atol=1e-7)

@@ -165,3 +165,26 @@ def test_learner_n512_fixture():
     for k, v in g['grads'].items():
         mine = grad_sample(sd[k].grad)
         assert max_abs(mine, v) <= 2e-3 * v.abs().max().item() + 1e-7, k
+
+
+@pytest.mark.parametrize('tag,kw', [('default', {}), ('label_smooth', {'label_smooth': True}), ('no_su_mask', {'su_mask': False})])
+def test_supervised_loss_restatement_vs_reference_fixture(tag, kw):
+    """oracle.restate.supervised_loss against SupervisedLoss.compute_loss of the executed reference (sl_loss.py:102-285):
+    all 15 log entries and d total_loss / d logits of every head."""
+    import torch
+    from applestar_b200 import synth
+    from oracle import restate
+    fx = golden('sl_loss_small.pt')
+    m = fx['meta']
+    d = synth.gen_sl_loss_inputs(m['b'], m['s'], m['N'], m['seed'])
+    logits = {k: v.clone().requires_grad_(True) for k, v in d['logits'].items()}
+    info = restate.supervised_loss(logits, d['actions'], d['actions_mask'], d['selected_units_num'], d['entity_num'],
+                                   d['infer_selected_units'], **kw)
+    ref = fx[tag]
+    assert set(info) == set(ref['info'])
+    for k, v in ref['info'].items():
+        assert abs(float(info[k]) - v) <= 1e-6 + 1e-5 * abs(v), (k, float(info[k]), v)
+    info['total_loss'].backward()
+    for k, g in ref['dlogits'].items():
+        assert torch.allclose(logits[k].grad, g, rtol=1e-5, atol=1e-7), k
+    assert torch.allclose(logits['target_location'].grad[0], ref['dlogits_location_row0'], rtol=1e-5, atol=1e-8)

@@ -134,6 +134,11 @@ def test_drop_in_signatures(ref_model):
     for m in ('sync_gradients', 'broadcast_params'):
         assert names(getattr(DistModule, m)) == names(getattr(RefDist, m)), m
     assert names(DistModule.__init__)[:3] == names(RefDist.__init__)[:3]
+    from distar.agent.default.sl_training.sl_loss import SupervisedLoss as RefSL
+    from applestar_b200 import SupervisedLoss
+    assert names(SupervisedLoss.__init__) == names(RefSL.__init__)
+    assert names(SupervisedLoss.compute_loss) == names(RefSL.compute_loss)
+    assert names(SupervisedLoss.register_stats) == names(RefSL.register_stats)
 
 
 @reference
@@ -161,6 +166,44 @@ def test_pipeline_shim_resolves_through_the_reference_plugin_lookup(ref_model):
         pytest.skip('reference agent not importable in this container: %s' % exc)
     from distar.agent.default import agent as ref_agent
     assert agent_cls is ref_agent.Agent and ref_agent.Model is applestar_b200.Model
+
+
+@reference
+def test_sl_learner_shim(ref_model):
+    """Same for the supervised learner (sl_learner.py:14-16,37-38).  Its data loader imports the replay parser (`mpyq`),
+    which is absent in this container: a stand-in module that contributes nothing is registered for the import only."""
+    import os
+    import sys
+    import types
+    import distar.agent
+    import applestar_b200
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    shim = os.path.join(root, 'integration', 'distar', 'agent')
+    if shim not in distar.agent.__path__:
+        distar.agent.__path__.append(shim)
+    from distar.agent.import_helper import import_module
+    added = []
+    for _ in range(8):
+        try:
+            sl_cls = import_module('b200', 'SLLearner')
+            break
+        except ImportError as exc:
+            name = getattr(exc, 'name', None)
+            if not name or name.startswith('distar') or name.startswith('applestar'):
+                raise
+            sys.modules[name] = types.ModuleType(name)
+            added.append(name)
+        except Exception as exc:                      # the replay / SC2 client chain needs the real s2clientprotocol
+            for name in added:
+                sys.modules.pop(name, None)
+            pytest.skip('reference SL learner not importable in this container: %r' % exc)
+    else:
+        pytest.skip('reference SL learner needs more absent modules than expected: %s' % added)
+    from distar.agent.default import sl_learner as ref_sl
+    assert sl_cls is ref_sl.SLLearner and ref_sl.SupervisedLoss is applestar_b200.SupervisedLoss
+    assert ref_sl.Model is applestar_b200.Model
+    for name in added:
+        sys.modules.pop(name, None)
 
 
 @reference
