@@ -56,6 +56,8 @@ _SIGS = {
     'as_gemm_bf16': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
                              c_int64, c_int64, c_int64, c_int, c_int, c_int64, c_int64, c_int64, c_int64, c_int64,
                              c_int64, c_int, c_int, c_float, c_int, c_void_p, c_int, c_void_p]),
+    'as_gemm_bf16_relu_bits': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int64, c_int64, c_void_p]),
+    'as_gemm_bf16_bitmasked': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int64, c_int64, c_int64, c_int, c_float, c_void_p]),
     'as_gemm_bf16_masked': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int64, c_int64,
                                     c_int64, c_int, c_float, c_void_p]),
     'as_gemm_splits': (c_int, [c_int, c_int]),

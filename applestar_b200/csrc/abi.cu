@@ -200,6 +200,27 @@ int as_gemm_bf16_masked(const void* A, const void* B, void* C, const void* mask,
   return as::gemm_run(g, ST(stream));
 }
 
+int as_gemm_bf16_relu_bits(const void* A, const void* B, void* C, const float* bias, uint32_t* bits, int M, int N, int K, int64_t lda,
+                           int64_t ldb, int64_t ldc, void* stream) {
+  as::GemmCall g;
+  g.A = A; g.B = B; g.C = C; g.bias = bias; g.bits_out = bits;
+  g.M = M; g.N = N; g.K = K;
+  g.lda = lda; g.ldb = ldb; g.ldc = ldc;
+  g.c_bf16 = 1; g.relu = 1;
+  return as::gemm_run(g, ST(stream));
+}
+
+int as_gemm_bf16_bitmasked(const void* A, const void* B, void* C, const uint32_t* bits, int M, int N, int K, int a_mn, int b_mn,
+                           int64_t lda, int64_t ldb, int64_t ldc, int c_bf16, float alpha, void* stream) {
+  as::GemmCall g;
+  g.A = A; g.B = B; g.C = C; g.bits_in = bits;
+  g.M = M; g.N = N; g.K = K;
+  g.a_mn = a_mn != 0; g.b_mn = b_mn != 0;
+  g.lda = lda; g.ldb = ldb; g.ldc = ldc;
+  g.c_bf16 = c_bf16; g.alpha = alpha;
+  return as::gemm_run(g, ST(stream));
+}
+
 int as_splitk_reduce(const float* ws, float* out, int64_t n, int splits, int accumulate, void* stream) {
   if (!ws || !out || splits <= 0) return AS_EINVAL;
   return as::splitk_reduce(ws, out, n, splits, accumulate, ST(stream));

@@ -21,6 +21,11 @@ struct GemmCall {
   long long ldc = 0, c_sb0 = 0, c_sb1 = 0;
   const float* bias = nullptr;
   const void* resid = nullptr;   // optional bf16 tensor with C's layout (ldc, batch strides), added before ReLU (TMA-store path)
+  // ReLU sign bits, one uint32 per 32 output columns, row pitch N / 32 words (batch 1, N % 32 == 0, TMA-store epilogue):
+  // bits_out is written by a relu GEMM (bit j of word [m][n / 32] = output [m][n + j] > 0), bits_in zeroes the output where
+  // the bit is clear -- the same ReLU backward as `mask` at 1/16 of its bytes
+  uint32_t* bits_out = nullptr;
+  const uint32_t* bits_in = nullptr;
   const void* mask = nullptr;    // optional bf16 tensor with C's layout: the output is zeroed where mask <= 0 (the ReLU
                                  // backward of the layer that produced `mask`, applied to the gradient this GEMM computes)
   int relu = 0;

@@ -20,6 +20,15 @@
 #include "common.cuh"
 #include "gemm.h"
 
+// Register budget by role (setmaxnreg): warps 0-3 (TMA producer, MMA issuer, TMEM allocator) give registers up, the two
+// epilogue warpgroups take them.  0 = one budget for all warps (168 at 384 threads).
+#ifndef AS_WG0_REGS
+#define AS_WG0_REGS 104
+#endif
+#ifndef AS_EPI_REGS
+#define AS_EPI_REGS 200
+#endif
+
 namespace as {
 
 constexpr int BM = 128;
@@ -54,6 +63,8 @@ struct GemmDev {
   long long ldc, c_sb0, c_sb1;
   const float* bias;
   const __nv_bfloat16* resid;   // bf16 [.., M, ldc]: added to the accumulator row before ReLU / border masking (or nullptr)
+  uint32_t* bits_out;           // ReLU sign bits of the bf16 output, [M][N / 32] words (or nullptr)
+  const uint32_t* bits_in;      // output zeroed where the bit is clear (or nullptr)
   const __nv_bfloat16* mask;    // bf16 [.., M, ldc]: output zeroed where mask <= 0 (ReLU backward of the producing layer)
   int relu;
   float alpha;
@@ -145,6 +156,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const uint32_t crank = p.mc ? cluster_ctarank() : 0u;
   uint8_t* b_ring = smem + p.slab_slots * p.slab_bytes;
 
+  if (warp < 4) {
+#if AS_WG0_REGS
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(AS_WG0_REGS));
+#endif
   if (warp == 0 && p.slab) {
     // ------------------------------------------------------------------ TMA producer, slab mode
     if (lane == 0 && !A_MN && !B_MN) {
@@ -373,7 +388,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         umma_commit_lead(leader, &tmem_full[acc]);      // accumulator complete -> epilogue
       }
     }
-  } else if (warp >= 4) {
+  }
+  } else {
+#if AS_WG0_REGS
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(AS_EPI_REGS));
+#endif
     // ------------------------------------------------------------------ epilogue (8 warps)
     // Warp e reads TMEM lanes 32*(e%4).. (its hardware quarter) and the column half e/4 of the tile, so two warps per
     // scheduler hide each other's fixed-latency stalls.  tcgen05.ld gives each lane one accumulator row (32 columns);
@@ -435,7 +454,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         };
         // alpha / bias / ReLU / border on one 32-column chunk.  Every runtime option is tested once per chunk (warp
         // uniform), never per element.
-        auto finish = [&](const uint32_t (&v)[32], int c, float (&f)[32]) {
+        auto finish = [&](const uint32_t (&v)[32], int c, float (&f)[32], uint32_t bw) {
           const int gc = n0 + c;
           if (p.bias == nullptr) {
 #pragma unroll
@@ -486,6 +505,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               }
             }
           }
+          if (p.bits_in != nullptr) {
+            // sign bits of the layer whose ReLU this gradient passes: columns 2k / 2k+1 of the chunk are bits 15-k / 31-k
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = (bw >> (((j & 1) ? 31 : 15) - (j >> 1)) & 1u) ? f[j] : 0.f;
+          }
           if (p.relu) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
@@ -514,19 +538,25 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll 1
         for (int col = col_begin; col < col_end; col += 64) {
           const bool has0 = n0 + col < p.N, has1 = (col + 32 < col_end) && (n0 + col + 32 < p.N);   // warp-uniform
+          uint32_t bw0 = 0xffffffffu, bw1 = 0xffffffffu;          // requested before the wait for the accumulator columns
+          if (p.bits_in != nullptr && grow < p.M) {
+            const uint32_t* brow = p.bits_in + (long long)grow * (p.N >> 5) + ((n0 + col) >> 5);
+            if (has0) bw0 = __ldg(brow);
+            if (has1) bw1 = __ldg(brow + 1);
+          }
           tmem_ld_wait();
           if (p.debug == 2 || !has0) { issue(col + 64); continue; }
           uint32_t packed[32];
           if (!f32_out) {
             float f[32];
-            finish(v0, col, f);
+            finish(v0, col, f, bw0);
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
               __nv_bfloat162 hv = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
               packed[j] = *reinterpret_cast<uint32_t*>(&hv);
             }
             if (has1) {
-              finish(v1, col + 32, f);
+              finish(v1, col + 32, f, bw1);
 #pragma unroll
               for (int j = 0; j < 16; ++j) {
                 __nv_bfloat162 hv = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
@@ -534,9 +564,22 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               }
             }
             issue(col + 64);
+            if (p.bits_out != nullptr && grow < p.M) {
+              // a relu output half-word is positive iff adding 0x7fff carries into its top bit; pair k of a 32-column
+              // chunk lands on bits 15-k (even column) and 31-k (odd column)
+              uint32_t w0 = 0u, w1 = 0u;
+#pragma unroll
+              for (int k = 0; k < 16; ++k) {
+                w0 |= ((packed[k] + 0x7fff7fffu) & 0x80008000u) >> k;
+                w1 |= ((packed[16 + k] + 0x7fff7fffu) & 0x80008000u) >> k;
+              }
+              uint32_t* brow = p.bits_out + (long long)grow * (p.N >> 5) + ((n0 + col) >> 5);
+              if (has1 && ((p.N >> 5) & 1) == 0) *reinterpret_cast<uint2*>(brow) = make_uint2(w0, w1);
+              else { brow[0] = w0; if (has1) brow[1] = w1; }
+            }
           } else {
             float f[32];
-            finish(v0, col, f);
+            finish(v0, col, f, bw0);
             if (need_bf16) {
 #pragma unroll
               for (int j = 0; j < 16; ++j) {
@@ -546,7 +589,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
             stage32(f, col);
             if (has1) {
-              finish(v1, col + 32, f);
+              finish(v1, col + 32, f, bw1);
               if (need_bf16) {
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
@@ -872,6 +915,8 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
   p.C = g.C; p.C2 = g.C2; p.c_bf16 = g.c_bf16; p.ldc = g.ldc; p.c_sb0 = g.c_sb0; p.c_sb1 = g.c_sb1;
   p.resid = reinterpret_cast<const __nv_bfloat16*>(g.resid);
   p.mask = reinterpret_cast<const __nv_bfloat16*>(g.mask);
+  p.bits_out = g.bits_out;
+  p.bits_in = g.bits_in;
   p.bias = g.bias; p.relu = g.relu; p.alpha = g.alpha; p.ws = g.ws;
   p.debug = g_gemm_debug;
   // slab mode for multi-tap convolutions (see the header comment): needs the halo'd slab of a 256-row step to fit two
@@ -942,6 +987,9 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
   // the residual add lives in the TMA-store epilogue only; whole 32-column chunks, 16-byte aligned rows
   if (g.resid != nullptr && (!p.tma_store || (g.N % 32) != 0 || (g.ldc % 8) != 0 ||
                              (reinterpret_cast<uintptr_t>(g.resid) & 15) != 0))
+    return AS_EUNSUPPORTED;
+  if ((g.bits_in != nullptr || g.bits_out != nullptr) &&
+      (!p.tma_store || (g.N % 32) != 0 || g.nb0 * g.nb1 != 1 || (g.bits_out != nullptr && (!g.relu || !g.c_bf16 || g.C2 != nullptr))))
     return AS_EUNSUPPORTED;
   if (g.mask != nullptr && (!p.tma_store || (g.N % 32) != 0 || (g.ldc % 8) != 0 ||
                             (reinterpret_cast<uintptr_t>(g.mask) & 15) != 0))

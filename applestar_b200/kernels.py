@@ -405,11 +405,22 @@ class LinearLNFn(torch.autograd.Function):
         return dx, (None if dres is None else dres.view(*ctx.xshape[:-1], N)), dw, dbias, dgamma, dbeta, None
 
 
+def _relu_bits_gemm(x16, w16, h16, bias, M, Hd, Kd):
+    """h16 = relu(x16 W^T + b) and the sign bits of h16 ([M, Hd / 32] words) in one launch: the backward's masked
+    data-gradient GEMM then reads 1 bit instead of 16 per hidden element."""
+    assert Hd % 32 == 0
+    bits = torch.empty((M, Hd // 32), dtype=torch.int32, device=x16.device)
+    _lib.call('as_gemm_bf16_relu_bits', x16.data_ptr(), w16.data_ptr(), h16.data_ptr(), _ptr(bias), bits.data_ptr(), M, Hd, Kd,
+              Kd, Kd, Hd, _lib.stream_ptr())
+    return bits
+
+
 class MLPLNFn(torch.autograd.Function):
     """(y fp32, y bf16) = LN(res + ReLU(ReLU(x W1^T + b1) W2^T + b2)) (+ReLU) -- the FFN (ReLU on BOTH layers,
     module_utils.py:121-123) + layernorm2 of the post-LN Transformer layer (:136-139) as one autograd node.  Backward:
     the LayerNorm kernel emits the masked bf16 gradient and bias gradient of the second layer; the data-gradient GEMM of
-    the second layer applies the first layer's ReLU mask in its epilogue (as_gemm_bf16_masked), so the [rows, hidden]
+    the second layer applies the first layer's ReLU mask in its epilogue (as_gemm_bf16_bitmasked, sign bits written by the
+    forward GEMM), so the [rows, hidden]
     gradient is written once and never re-read by an element-wise pass."""
 
     @staticmethod
@@ -420,19 +431,19 @@ class MLPLNFn(torch.autograd.Function):
         M = x16.shape[0]
         w1_16, w2_16 = weight_bf16(w1), weight_bf16(w2)
         h16 = torch.empty((M, Hd), dtype=torch.bfloat16, device=x.device)
-        gemm(x16, w1_16, h16, M, Hd, Kd, lda=Kd, ldb=Kd, bias=b1, relu=True)
+        hbits = _relu_bits_gemm(x16, w1_16, h16, b1, M, Hd, Kd)
         z32 = torch.empty((M, N), dtype=torch.float32, device=x.device)
         gemm(h16, w2_16, z32, M, N, Hd, lda=Hd, ldb=Hd, bias=b2, relu=True)
         res2 = res.reshape(M, N).contiguous().float()
         y32, y16, stats = _ln_fwd(z32, res2, gamma, beta, relu_ln)
         ctx.relu_ln, ctx.xshape, ctx.x_bf16 = relu_ln, x.shape, x.dtype == torch.bfloat16
-        ctx.save_for_backward(x16, w1_16, w2_16, h16, z32, res2, gamma, beta, stats)
+        ctx.save_for_backward(x16, w1_16, w2_16, h16, z32, res2, gamma, beta, stats, hbits)
         shp = (*x.shape[:-1], N)
         return y32.view(shp), y16.view(shp)
 
     @staticmethod
     def backward(ctx, dy32, dy16):
-        x16, w1_16, w2_16, h16, z32, res2, gamma, beta, stats = ctx.saved_tensors
+        x16, w1_16, w2_16, h16, z32, res2, gamma, beta, stats, hbits = ctx.saved_tensors
         if dy32 is None and dy16 is None:
             return (None,) * 9
         M, N = z32.shape
@@ -442,7 +453,7 @@ class MLPLNFn(torch.autograd.Function):
                                                       ctx.needs_input_grad[1])
         # d hidden = (dz2 W2) * (h > 0): mask applied in the GEMM epilogue
         dz1 = torch.empty((M, Hd), dtype=torch.bfloat16, device=dev)
-        _lib.call('as_gemm_bf16_masked', dz2.data_ptr(), w2_16.data_ptr(), dz1.data_ptr(), h16.data_ptr(), M, Hd, N, 0, 1,
+        _lib.call('as_gemm_bf16_bitmasked', dz2.data_ptr(), w2_16.data_ptr(), dz1.data_ptr(), hbits.data_ptr(), M, Hd, N, 0, 1,
                   N, Hd, Hd, 1, 1.0, _lib.stream_ptr())
         db1 = column_sum(dz1) if ctx.needs_input_grad[3] else None
         dw2 = _wgrad(dz2, h16, N, Hd) if ctx.needs_input_grad[4] else None
@@ -536,19 +547,19 @@ class MLPLN16Fn(torch.autograd.Function):
         M = x16.shape[0]
         w1_16, w2_16 = weight_bf16(w1), weight_bf16(w2)
         h16 = torch.empty((M, Hd), dtype=torch.bfloat16, device=x.device)
-        gemm(x16, w1_16, h16, M, Hd, Kd, lda=Kd, ldb=Kd, bias=b1, relu=True)
+        hbits = _relu_bits_gemm(x16, w1_16, h16, b1, M, Hd, Kd)
         z16 = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
         gemm(h16, w2_16, z16, M, N, Hd, lda=Hd, ldb=Hd, bias=b2, relu=True)
         res16 = to_bf16(res.reshape(M, N))
         y16, stats = _ln16_fwd(z16, res16, gamma, beta, relu_ln)
         ctx.relu_ln, ctx.xshape = relu_ln, x.shape
-        ctx.save_for_backward(x16, w1_16, w2_16, h16, z16, res16, gamma, beta, stats)
+        ctx.save_for_backward(x16, w1_16, w2_16, h16, z16, res16, gamma, beta, stats, hbits)
         shp = (*x.shape[:-1], N)
         return y16.view(shp), y16.view(shp)
 
     @staticmethod
     def backward(ctx, dya, dyb):
-        x16, w1_16, w2_16, h16, z16, res16, gamma, beta, stats = ctx.saved_tensors
+        x16, w1_16, w2_16, h16, z16, res16, gamma, beta, stats, hbits = ctx.saved_tensors
         if dya is None and dyb is None:
             return (None,) * 9
         M, N = z16.shape
@@ -557,7 +568,7 @@ class MLPLN16Fn(torch.autograd.Function):
         dres, dz2, dgamma, dbeta, db2 = _ln16_bwd(dya, dyb, z16, res16, gamma, beta, stats, ctx.relu_ln, True,
                                                   ctx.needs_input_grad[1])
         dz1 = torch.empty((M, Hd), dtype=torch.bfloat16, device=dev)
-        _lib.call('as_gemm_bf16_masked', dz2.data_ptr(), w2_16.data_ptr(), dz1.data_ptr(), h16.data_ptr(), M, Hd, N, 0, 1,
+        _lib.call('as_gemm_bf16_bitmasked', dz2.data_ptr(), w2_16.data_ptr(), dz1.data_ptr(), hbits.data_ptr(), M, Hd, N, 0, 1,
                   N, Hd, Hd, 1, 1.0, _lib.stream_ptr())
         db1 = column_sum(dz1) if ctx.needs_input_grad[3] else None
         dw2 = _wgrad(dz2, h16, N, Hd) if ctx.needs_input_grad[4] else None

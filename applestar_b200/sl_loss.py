@@ -160,7 +160,8 @@ class SupervisedLoss:
         with torch.no_grad():
             if selected_units is not None:
                 preds = selected_units[:, :s].long()
-                end_idx = torch.sort((preds == entity_num.unsqueeze(1)).long(), dim=-1, descending=True, stable=False)[1][:, 0]
+                # first occurrence of the end flag (the reference's CPU sort is stable; a CUDA sort needs to be told)
+                end_idx = torch.sort((preds == entity_num.unsqueeze(1)).long(), dim=-1, descending=True, stable=True)[1][:, 0]
                 invalid = end_idx == 0
                 end_idx = end_idx + 1
                 end_idx[invalid] += s

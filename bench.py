@@ -164,7 +164,7 @@ def gemm_flops_hook(records):
     orig = _lib.call
 
     def hooked(name, *a):
-        if name not in ('as_gemm_bf16', 'as_gemm_bf16_masked', 'as_conv_nhwc_bf16', 'as_conv_nhwc_bf16_add',
+        if name not in ('as_gemm_bf16', 'as_gemm_bf16_masked', 'as_gemm_bf16_relu_bits', 'as_gemm_bf16_bitmasked', 'as_conv_nhwc_bf16', 'as_conv_nhwc_bf16_add',
                         'as_conv_nhwc_bf16_masked', 'as_conv_wgrad_nhwc_bf16', 'as_attn_fwd', 'as_attn_bwd_dq'):
             return orig(name, *a)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -175,8 +175,10 @@ def gemm_flops_hook(records):
         if name == 'as_gemm_bf16':
             M, N, K, nb = a[5], a[6], a[7], a[13] * a[14]
             fl = 2.0 * M * N * K * nb
-        elif name == 'as_gemm_bf16_masked':               # (A, B, C, mask, M, N, K, ...)
+        elif name in ('as_gemm_bf16_masked', 'as_gemm_bf16_bitmasked'):   # (A, B, C, mask, M, N, K, ...)
             fl = 2.0 * a[4] * a[5] * a[6]
+        elif name == 'as_gemm_bf16_relu_bits':            # (A, B, C, bias, bits, M, N, K, ...)
+            fl = 2.0 * a[5] * a[6] * a[7]
         elif name in ('as_conv_nhwc_bf16_add', 'as_conv_nhwc_bf16_masked'):   # (x, w, y, bias|addend, addend|mask, R, H, W, Cin, Cout, taps, ...)
             R, H, W, Cin, Cout, taps = a[5], a[6], a[7], a[8], a[9], a[10]
             fl = 2.0 * R * (H + 2) * (W + 2) * Cin * Cout * taps

@@ -62,6 +62,16 @@ int as_gemm_splits(int K, int want);
 int as_gemm_bf16_masked(const void* A, const void* B, void* C, const void* mask, int M, int N, int K, int a_mn, int b_mn, int64_t lda,
                         int64_t ldb, int64_t ldc, int c_bf16, float alpha, void* stream);
 
+/* The same ReLU backward from SIGN BITS instead of the activation itself (1/16 of the bytes; the epilogue of a K = 256
+ * GEMM cannot hide a second [M, N] bf16 stream): as_gemm_bf16_relu_bits is the forward layer, C bf16 = relu(A B^T + bias)
+ * with the sign bits (C[m][n] > 0) written alongside as bits[m][n / 32] (N % 32 == 0; within a word, column 2k of the 32 is
+ * bit 15-k and column 2k+1 is bit 31-k: the order the packed bf16 pairs give for free); as_gemm_bf16_bitmasked computes
+ * C = alpha * A B^T zeroed where the bit is clear. */
+int as_gemm_bf16_relu_bits(const void* A, const void* B, void* C, const float* bias, uint32_t* bits, int M, int N, int K, int64_t lda,
+                           int64_t ldb, int64_t ldc, void* stream);
+int as_gemm_bf16_bitmasked(const void* A, const void* B, void* C, const uint32_t* bits, int M, int N, int K, int a_mn, int b_mn,
+                           int64_t lda, int64_t ldb, int64_t ldc, int c_bf16, float alpha, void* stream);
+
 /* out[i] = (accumulate ? out[i] : 0) + sum_s ws[s][i], s ascending (deterministic). */
 int as_splitk_reduce(const float* ws, float* out, int64_t n, int splits, int accumulate, void* stream);
 

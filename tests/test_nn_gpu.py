@@ -271,3 +271,39 @@ def test_fused_transformer_layer_nodes_vs_torch(relu_ln, bf16_stream):
         r = t.grad.float()
         rel = ((m - r).norm() / r.norm()).item()
         assert rel < (0.1 if bf16_stream else 0.02), (nm, rel)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('M,N,Kd', [(1000, 1024, 256), (4096, 96, 64), (130, 32, 40)])
+def test_gemm_relu_sign_bits_and_bitmasked_dgrad(M, N, Kd):
+    """as_gemm_bf16_relu_bits writes the sign bits of the relu output (word [m][n / 32]; columns 2k / 2k+1 of a word on
+    bits 15-k / 31-k) next to the bf16 output;
+    as_gemm_bf16_bitmasked zeroes its output where the bit is clear: bit-identical to masking with the activation."""
+    from applestar_b200 import _lib
+    dev = torch.device('cuda:0')
+    g = torch.Generator(device=dev).manual_seed(M + N)
+    x = torch.randn(M, Kd, device=dev, generator=g).to(torch.bfloat16)
+    w = (torch.randn(N, Kd, device=dev, generator=g) * 0.1).to(torch.bfloat16)
+    b = torch.randn(N, device=dev, generator=g)
+    h = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+    bits = torch.zeros(M, N // 32, dtype=torch.int32, device=dev)
+    _lib.call('as_gemm_bf16_relu_bits', x.data_ptr(), w.data_ptr(), h.data_ptr(), b.data_ptr(), bits.data_ptr(), M, N, Kd, Kd, Kd, N,
+              _lib.stream_ptr())
+    ref = torch.relu(x.float() @ w.float().t() + b)
+    assert torch.allclose(h.float(), ref, rtol=2e-2, atol=2e-2)
+    col = torch.arange(32, device=dev)
+    pos = torch.where(col % 2 == 1, 31 - col // 2, 15 - col // 2).to(torch.int32)     # bit of column c within its word
+    unpacked = ((bits.unsqueeze(-1) >> pos) & 1).reshape(M, N).bool()
+    assert torch.equal(unpacked, h > 0)
+    # dgrad: dz1 [M, N] = (dz2 [M, Kd] @ W2 [Kd, N]) * (h > 0), W2 read MN-major
+    dz2 = torch.randn(M, Kd, device=dev, generator=g).to(torch.bfloat16)
+    w2 = (torch.randn(Kd, N, device=dev, generator=g) * 0.1).to(torch.bfloat16)
+    out_b = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+    out_m = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+    _lib.call('as_gemm_bf16_bitmasked', dz2.data_ptr(), w2.data_ptr(), out_b.data_ptr(), bits.data_ptr(), M, N, Kd, 0, 1, Kd, N, N, 1,
+              1.0, _lib.stream_ptr())
+    _lib.call('as_gemm_bf16_masked', dz2.data_ptr(), w2.data_ptr(), out_m.data_ptr(), h.data_ptr(), M, N, Kd, 0, 1, Kd, N, N, 1,
+              1.0, _lib.stream_ptr())
+    assert torch.equal(out_b, out_m)
+    want = (dz2.float() @ w2.float()) * (h > 0)
+    assert torch.allclose(out_b.float(), want, rtol=2e-2, atol=2e-2)
