@@ -43,7 +43,7 @@ class AsLossArgs(ctypes.Structure):
         ('hw_dapo', c_float * 6),
         ('w_upgo', c_float), ('w_ent', c_float), ('w_kl', c_float), ('w_atkl', c_float), ('w_dapo', c_float),
         ('stat_weight', c_void_p), ('grad_scale', c_void_p),
-        ('row_stats', c_void_p * 6), ('coef', c_void_p * 6), ('partial', c_void_p), ('out', c_void_p),
+        ('row_stats', c_void_p * 6), ('coef', c_void_p * 6), ('su_step', c_void_p), ('partial', c_void_p), ('out', c_void_p),
     ]
 
 

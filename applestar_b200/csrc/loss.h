@@ -40,8 +40,9 @@ typedef struct AsLossArgs {
   const float* stat_weight;      /* [AS_LOSS_MAX_STATS]: total_loss = sum_i stat_weight[i] * means[i] */
   const float* grad_scale;       /* backward only: device scalar d(objective)/d(total_loss) multiplied into dlogit, or NULL (= 1) */
   /* scratch (caller-provided device memory) */
-  float* row_stats[6];           /* [rows, 8] */
-  float* coef[6];                /* [rows, 4] */
+  float* row_stats[6];           /* [rows, 8]; rows = T*B, selected units T*B*S */
+  float* coef[6];                /* [T*B, 4] per head (selected units: per step as well) */
+  float* su_step;                /* [T*B, 8] per-step sums over the selected-units sub-rows */
   float* partial;                /* [B, AS_LOSS_MAX_STATS] */
   float* out;                    /* [AS_LOSS_MAX_STATS] */
 } AsLossArgs;

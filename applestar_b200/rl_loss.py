@@ -33,7 +33,10 @@ class _FusedLoss(torch.autograd.Function):
         keep = []
 
         def dptr(t, dtype=None):
-            t = t.contiguous() if dtype is None else t.to(dtype).contiguous()
+            if dtype is torch.uint8 and t.dtype == torch.bool:
+                t = t.contiguous().view(torch.uint8)          # same bytes: no conversion pass
+            else:
+                t = t.contiguous() if dtype is None else t.to(dtype).contiguous()
             keep.append(t)
             return t.data_ptr()
 
@@ -51,9 +54,12 @@ class _FusedLoss(torch.autograd.Function):
             a.actions_mask[h] = dptr(mask['actions_mask'][name], torch.int64) if name in _MASKED_HEADS else None
             dl = torch.empty_like(lg)
             st = torch.empty((rows, 8), dtype=torch.float32, device=dev)
-            cf = torch.zeros((rows, 4), dtype=torch.float32, device=dev)
+            cf = torch.empty((TB, 4), dtype=torch.float32, device=dev)      # written in full by the scan kernel
             dlogits.append(dl); stats.append(st); coefs.append(cf)
             a.dlogit[h], a.row_stats[h], a.coef[h] = dl.data_ptr(), st.data_ptr(), cf.data_ptr()
+        su_step = torch.empty((TB, 8), dtype=torch.float32, device=dev)
+        keep.append(su_step)
+        a.su_step = su_step.data_ptr()
         a.su_mask = dptr(mask['selected_units_mask'], torch.uint8)
         a.su_logits_mask = dptr(mask['selected_units_logits_mask'], torch.uint8)
         a.tu_logits_mask = dptr(mask['target_units_logits_mask'], torch.uint8)
@@ -122,7 +128,7 @@ class _FusedLoss(torch.autograd.Function):
         a.partial, a.out = partial.data_ptr(), out.data_ptr()
         st_ptr = _lib.stream_ptr()
         _lib.call('as_rl_loss_forward', ctypes.byref(a), st_ptr)
-        _lib.LAUNCHES += 7
+        _lib.LAUNCHES += 4
         ctx.args = a
         ctx.keep = keep + logits + values + stats + coefs + [partial, out]
         ctx.dlogits, ctx.dvalues = dlogits, dvalues
@@ -137,7 +143,7 @@ class _FusedLoss(torch.autograd.Function):
         gs = gtotal.detach().reshape(1).float().contiguous()
         ctx.args.grad_scale = gs.data_ptr()
         _lib.call('as_rl_loss_backward', ctypes.byref(ctx.args), 1.0, _lib.stream_ptr())
-        _lib.LAUNCHES += 5
+        _lib.LAUNCHES += 2
         ctx.keep.append(gs)
         grads = list(ctx.dlogits) + [g * gs for g in ctx.dvalues]          # the [T+1, B] value gradients are tiny
         return (None, None, None) + tuple(grads)

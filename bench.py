@@ -452,7 +452,7 @@ def hbm_rooflines(model, loss_fn, resident, dev):
         once()
     torch.cuda.current_stream().wait_stream(side)
     torch.cuda.synchronize()
-    graph = torch.cuda.CUDAGraph()                   # as in the learner step: the 12 launches replay from a CUDA graph
+    graph = torch.cuda.CUDAGraph()                   # as in the learner step: the 6 launches replay from a CUDA graph
     with torch.cuda.graph(graph):
         once()
     graph.replay()
@@ -465,10 +465,10 @@ def hbm_rooflines(model, loss_fn, resident, dev):
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / 5
     nbytes = 12.0 * valid
-    out['rl_loss'] = {'kernel': 'as::loss_row_stats + loss_scan + loss_finalize + loss_row_grad (forward + backward)',
+    out['rl_loss'] = {'kernel': 'as::loss_stats_small/big + loss_scan + loss_finalize + loss_grad_small/big (forward + backward)',
                       'valid_logits': valid, 'ms': ms, 'bytes': nbytes, 'achieved': nbytes / (ms * 1e-3) / 1e9,
                       'peak': hbm, 'unit': 'GB/s', 'frac': nbytes / (ms * 1e-3) / 1e9 / hbm,
-                      'note': 'compute_loss + backward (12 launches) replayed from a CUDA graph, CUDA events around 5 replays'}
+                      'note': 'compute_loss + backward (6 launches) replayed from a CUDA graph, CUDA events around 5 replays'}
     out['peak_source'] = which + ' hbm_gbs'
     return out
 
