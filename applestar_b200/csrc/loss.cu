@@ -612,10 +612,10 @@ __global__ void __launch_bounds__(256) loss_grad_big_kernel(const AsLossArgs a, 
 }
 
 // The four short heads (warp per row) and selected_units in ONE launch.  The selected-units gradient [T*B*S, N1] is walked
-// FLAT in 16-byte pieces (its rows are 513 floats, so a row-wise walk cannot use vector stores): 95 % of it is the zero
-// gradient of sub-rows beyond selected_units_num, and this pass is bound by writing those zeros.
-// grid = 4 * ceil(TB / 8) + su_blocks.
-__global__ void __launch_bounds__(256) loss_grad_small_kernel(const AsLossArgs a, int nb, int su_blocks, float gscale) {
+// flat (its rows are 513 floats, so a row-wise walk cannot use vector stores): 95 % of it is the zero gradient of
+// sub-rows beyond selected_units_num, and this pass is bound by writing those zeros.
+// grid = 4 * ceil(TB / 8) + TB.
+__global__ void __launch_bounds__(256) loss_grad_small_kernel(const AsLossArgs a, int nb, float gscale) {
   if (a.grad_scale != nullptr) gscale *= __ldg(a.grad_scale);
   const int lane = threadIdx.x & 31, wi = threadIdx.x >> 5;
   const long long TB = (long long)a.T * a.B;
@@ -644,35 +644,44 @@ __global__ void __launch_bounds__(256) loss_grad_small_kernel(const AsLossArgs a
     }
     return;
   }
-  const int K = a.head_k[3];
-  const long long total = TB * a.S * K;
-  const float* x = a.logit[3];
-  const float* t = a.teacher[3];
-  const float* sc = a.successive[3];
-  float* dx = a.dlogit[3];
-  const long long vec_end = ((reinterpret_cast<uintptr_t>(dx) & 15) == 0) ? total / 4 : 0;
-  const long long nthreads = (long long)su_blocks * 256;
-  const long long tid = (long long)(blockIdx.x - 4 * nb) * 256 + threadIdx.x;
-  auto elem = [&](long long e) -> float {
-    const long long row = e / K;
-    if (!a.su_mask[row]) return 0.f;
-    long long step = 0;
-    if (!row_active(a, 3, row, &step)) return 0.f;
-    const int k = (int)(e - row * K);
-    const GradRow g = grad_row_params(a, 3, row, step, gscale);
+  // selected units: CTA per step.  The step's [S, N1] gradient block is contiguous; the parameters of its valid sub-rows
+  // go to shared memory once, then the block is walked flat in 16-byte pieces (most of it is the zero gradient of the
+  // sub-rows beyond selected_units_num).
+  __shared__ GradRow sg[64];
+  __shared__ unsigned char son[64];
+  const long long step = blockIdx.x - 4 * nb;
+  const int K = a.head_k[3], S = a.S;
+  if (threadIdx.x < S) {
+    const long long row = step * S + threadIdx.x;
+    long long st_ = 0;
+    const bool on = a.su_mask[row] != 0 && row_active(a, 3, row, &st_);
+    son[threadIdx.x] = on;
+    if (on) sg[threadIdx.x] = grad_row_params(a, 3, row, step, gscale);
+  }
+  __syncthreads();
+  const long long base = step * S * (long long)K;
+  const float* x = a.logit[3] + base;
+  const float* t = a.teacher[3] + base;
+  const float* sc = a.successive[3] ? a.successive[3] + base : nullptr;
+  float* dx = a.dlogit[3] + base;
+  const int total = S * K;
+  auto elem = [&](int e) -> float {
+    const int j = e / K;
+    if (!son[j]) return 0.f;
+    const GradRow& g = sg[j];
     const float xv = __ldg(x + e);
-    float v = grad_elem(g, xv, __ldg(t + e), k);
+    float v = grad_elem(g, xv, __ldg(t + e), e - j * K);
     if (sc != nullptr && g.c_d != 0.f) v += g.c_d * (expf(xv - g.lse) - expf(__ldg(sc + e) - g.lse_s));
     return v;
   };
-  for (long long i = tid; i < vec_end; i += nthreads) {
-    const long long e = 4 * i;
-    const long long r0 = e / K, r1 = (e + 3) / K;
+  const int vec_end = ((reinterpret_cast<uintptr_t>(dx) & 15) == 0) ? total / 4 : 0;
+  for (int i = threadIdx.x; i < vec_end; i += 256) {
+    const int e = 4 * i;
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (a.su_mask[r0] | a.su_mask[r1]) v = make_float4(elem(e), elem(e + 1), elem(e + 2), elem(e + 3));
+    if (son[e / K] | son[(e + 3) / K]) v = make_float4(elem(e), elem(e + 1), elem(e + 2), elem(e + 3));
     reinterpret_cast<float4*>(dx)[i] = v;
   }
-  for (long long e = vec_end * 4 + tid; e < total; e += nthreads) dx[e] = elem(e);
+  for (int e = vec_end * 4 + threadIdx.x; e < total; e += 256) dx[e] = elem(e);
 }
 
 // ---------------------------------------------------------------------------------------------- host
@@ -713,11 +722,7 @@ int loss_backward(const AsLossArgs& a, float gscale, cudaStream_t st) {
   for (int h = 0; h < 6; ++h)
     if (!a.dlogit[h]) return AS_EINVAL;
   const int nb = (int)((TB + 7) / 8);
-  const long long su_vec = (TB * a.S * a.head_k[3] + 3) / 4;
-  long long su_blocks = (su_vec + 255) / 256;
-  if (su_blocks > 148 * 16) su_blocks = 148 * 16;
-  if (su_blocks < 1) su_blocks = 1;
-  loss_grad_small_kernel<<<4 * nb + (int)su_blocks, 256, 0, st>>>(a, nb, (int)su_blocks, gscale);
+  loss_grad_small_kernel<<<4 * nb + (int)TB, 256, 0, st>>>(a, nb, gscale);
   AS_LAUNCH_CHECK();
   loss_grad_big_kernel<<<stats_grid(TB, 1), 256, 0, st>>>(a, 5, TB, a.head_k[5], gscale);
   AS_LAUNCH_CHECK();
