@@ -129,6 +129,8 @@ _SIGS = {
     'as_conv_wgrad_pair_mode': (c_int, [c_int, c_int, c_int, c_int, c_int]),
     'as_conv_wgrad_ws_floats': (c_int64, [c_int, c_int, c_int, c_int, c_int]),
     'as_conv_nhwc_bf16_add': (c_int, [c_void_p] * 5 + [c_int64, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    'as_conv_nhwc_bf16_relu_bits': (c_int, [c_void_p] * 5 + [c_int64, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    'as_conv_nhwc_bf16_bitmasked': (c_int, [c_void_p] * 5 + [c_int64, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     'as_conv_nhwc_bf16_masked': (c_int, [c_void_p] * 5 + [c_int64, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     'as_su_sample': (c_int, [POINTER(AsSuSampleArgs), c_void_p]),
     'as_masked_mean_fwd': (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),

@@ -227,7 +227,8 @@ int as_splitk_reduce(const float* ws, float* out, int64_t n, int splits, int acc
 }
 
 static int conv_nhwc_impl(const void* x, const void* w, void* y, const float* bias, const void* resid, int64_t R, int H, int W,
-                          int Cin, int Cout, int taps, int w_mn, int y_bf16, int relu, void* stream, const void* mask = nullptr) {
+                          int Cin, int Cout, int taps, int w_mn, int y_bf16, int relu, void* stream, const void* mask = nullptr,
+                          uint32_t* bits_out = nullptr, const uint32_t* bits_in = nullptr) {
   if (taps != 1 && taps != 9) return AS_EUNSUPPORTED;
   if (R <= 0 || H <= 0 || W <= 0 || Cin <= 0 || Cout <= 0) return AS_ESIZE;
   if (Cin % 8 != 0) return AS_EUNSUPPORTED;
@@ -235,7 +236,7 @@ static int conv_nhwc_impl(const void* x, const void* w, void* y, const float* bi
   const int64_t P = R * (int64_t)ph * pw;
   if (P > 2147483647LL) return AS_ESIZE;
   as::GemmCall g;
-  g.A = x; g.B = w; g.C = y; g.bias = bias; g.resid = resid; g.mask = mask;
+  g.A = x; g.B = w; g.C = y; g.bias = bias; g.resid = resid; g.mask = mask; g.bits_out = bits_out; g.bits_in = bits_in;
   g.M = (int)P; g.N = Cout; g.K = Cin;
   g.a_mn = false; g.b_mn = w_mn != 0;
   g.lda = Cin; g.ldb = g.b_mn ? Cout : (int64_t)taps * Cin; g.ldc = Cout;
@@ -264,6 +265,17 @@ int as_conv_nhwc_bf16_masked(const void* x, const void* w, void* y, const void* 
                              int Cin, int Cout, int taps, void* stream) {
   if (!mask) return AS_EINVAL;
   return conv_nhwc_impl(x, w, y, nullptr, addend, R, H, W, Cin, Cout, taps, 0, 1, 0, stream, mask);
+}
+
+int as_conv_nhwc_bf16_relu_bits(const void* x, const void* w, void* y, const float* bias, uint32_t* bits, int64_t R, int H, int W, int Cin,
+                                int Cout, int taps, void* stream) {
+  if (!bits || (Cout % 32) != 0) return AS_EINVAL;
+  return conv_nhwc_impl(x, w, y, bias, nullptr, R, H, W, Cin, Cout, taps, 0, 1, 1, stream, nullptr, bits, nullptr);
+}
+int as_conv_nhwc_bf16_bitmasked(const void* x, const void* w, void* y, const void* addend, const uint32_t* bits, int64_t R, int H, int W,
+                                int Cin, int Cout, int taps, void* stream) {
+  if (!bits || (Cout % 32) != 0) return AS_EUNSUPPORTED;
+  return conv_nhwc_impl(x, w, y, nullptr, addend, R, H, W, Cin, Cout, taps, 0, 1, 0, stream, nullptr, nullptr, bits);
 }
 
 // 0: one tap per tile; 1 / 2: tap pairs on a 64-channel M side (dy / swapped x), needs split-K partials

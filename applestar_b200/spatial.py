@@ -44,6 +44,7 @@ def _conv_call(x, w2, y, bias, R, H, W, cin, cout, taps, relu):
 
 
 FORK_CONV = os.environ.get('APPLESTAR_CONV_FORK', '1') != '0'
+RELU_BITS = os.environ.get('APPLESTAR_CONV_RELU_BITS', '1') != '0'
 
 
 class ConvNHWC(torch.autograd.Function):
@@ -65,13 +66,22 @@ class ConvNHWC(torch.autograd.Function):
         cout, cin, kh, _ = weight.shape
         taps = kh * kh
         w_fwd, w_dg = _conv_weights(weight, cin_p)
-        x = x.contiguous()
         y = torch.empty((R, ph, pw, cout), dtype=torch.bfloat16, device=x.device)
-        _conv_call(x, w_fwd, y, bias, R, H, W, cin_p, cout, taps, relu)
+        in_bits = getattr(x, '_as_relu_bits', None) if mask_input_grad else None
+        x = x.contiguous()
+        if ctx.grad_premasked and cout % 32 == 0 and any(ctx.needs_input_grad[:3]) and RELU_BITS:
+            # the consumers will apply this layer's ReLU mask to the gradient they send back: hand them 1 bit per element
+            # (written by this launch from its packed output) instead of making them re-read the bf16 map
+            bits = torch.empty((R * ph * pw, cout // 32), dtype=torch.int32, device=x.device)
+            _lib.call('as_conv_nhwc_bf16_relu_bits', x.data_ptr(), w_fwd.data_ptr(), y.data_ptr(), _ptr(bias), bits.data_ptr(),
+                      R, H, W, cin_p, cout, taps, _lib.stream_ptr())
+            y._as_relu_bits = bits
+        else:
+            _conv_call(x, w_fwd, y, bias, R, H, W, cin_p, cout, taps, relu)
         ctx.dims = (R, H, W, cin, cin_p, cout, taps, kh)
         ctx.relu = relu
         ctx.has_bias = bias is not None
-        ctx.save_for_backward(x, w_dg, y if relu else None)
+        ctx.save_for_backward(x, w_dg, y if relu else None, in_bits)
         if fork:
             return y, x.view_as(x)
         return y
@@ -80,7 +90,7 @@ class ConvNHWC(torch.autograd.Function):
     def backward(ctx, dy, dxa=None):
         if dy is None:                                   # only the pass-through alias was used downstream
             return dxa, None, None, None, None, None, None
-        x, w_dg, y = ctx.saved_tensors
+        x, w_dg, y, in_bits = ctx.saved_tensors
         R, H, W, cin, cin_p, cout, taps, kh = ctx.dims
         dy = dy.contiguous()
         st = _lib.stream_ptr()
@@ -101,8 +111,12 @@ class ConvNHWC(torch.autograd.Function):
             dx = torch.empty_like(x)
             if ctx.mask_input_grad and cin_p % 32 == 0 and (dxa is None or (dxa.dtype == torch.bfloat16 and dxa.shape == x.shape)):
                 dxa = None if dxa is None else dxa.contiguous()
-                _lib.call('as_conv_nhwc_bf16_masked', dy.data_ptr(), w_dg.data_ptr(), dx.data_ptr(), _ptr(dxa), x.data_ptr(),
-                          R, H, W, cout, cin_p, taps, st)
+                if in_bits is not None:
+                    _lib.call('as_conv_nhwc_bf16_bitmasked', dy.data_ptr(), w_dg.data_ptr(), dx.data_ptr(), _ptr(dxa),
+                              in_bits.data_ptr(), R, H, W, cout, cin_p, taps, st)
+                else:
+                    _lib.call('as_conv_nhwc_bf16_masked', dy.data_ptr(), w_dg.data_ptr(), dx.data_ptr(), _ptr(dxa), x.data_ptr(),
+                              R, H, W, cout, cin_p, taps, st)
             elif ctx.mask_input_grad:
                 raise RuntimeError('mask_input_grad needs a channel count that is a multiple of 32')
             elif dxa is not None and cin_p % 32 == 0 and dxa.dtype == torch.bfloat16 and dxa.shape == x.shape:

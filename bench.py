@@ -165,7 +165,7 @@ def gemm_flops_hook(records):
 
     def hooked(name, *a):
         if name not in ('as_gemm_bf16', 'as_gemm_bf16_masked', 'as_gemm_bf16_relu_bits', 'as_gemm_bf16_bitmasked', 'as_conv_nhwc_bf16', 'as_conv_nhwc_bf16_add',
-                        'as_conv_nhwc_bf16_masked', 'as_conv_wgrad_nhwc_bf16', 'as_attn_fwd', 'as_attn_bwd_dq'):
+                        'as_conv_nhwc_bf16_masked', 'as_conv_nhwc_bf16_relu_bits', 'as_conv_nhwc_bf16_bitmasked', 'as_conv_wgrad_nhwc_bf16', 'as_attn_fwd', 'as_attn_bwd_dq'):
             return orig(name, *a)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda._sleep(120000)         # keep the stream busy while the host enqueues, so that e0 -> e1 is the kernel's
@@ -179,7 +179,7 @@ def gemm_flops_hook(records):
             fl = 2.0 * a[4] * a[5] * a[6]
         elif name == 'as_gemm_bf16_relu_bits':            # (A, B, C, bias, bits, M, N, K, ...)
             fl = 2.0 * a[5] * a[6] * a[7]
-        elif name in ('as_conv_nhwc_bf16_add', 'as_conv_nhwc_bf16_masked'):   # (x, w, y, bias|addend, addend|mask, R, H, W, Cin, Cout, taps, ...)
+        elif name in ('as_conv_nhwc_bf16_add', 'as_conv_nhwc_bf16_masked', 'as_conv_nhwc_bf16_relu_bits', 'as_conv_nhwc_bf16_bitmasked'):   # (x, w, y, bias|addend, addend|mask, R, H, W, Cin, Cout, taps, ...)
             R, H, W, Cin, Cout, taps = a[5], a[6], a[7], a[8], a[9], a[10]
             fl = 2.0 * R * (H + 2) * (W + 2) * Cin * Cout * taps
         elif name == 'as_conv_wgrad_nhwc_bf16':           # (dy, x, dw, ws, R, H, W, Cin, Cout, taps, ...)

@@ -93,6 +93,13 @@ int as_conv_nhwc_bf16_add(const void* x, const void* w, void* y, const float* bi
  * and that layer's backward starts from an already masked gradient.  addend may be NULL; mask has y's layout. */
 int as_conv_nhwc_bf16_masked(const void* x, const void* w, void* y, const void* addend, const void* mask, int64_t R, int H, int W,
                              int Cin, int Cout, int taps, void* stream);
+/* The same pair from sign bits (layout as in as_gemm_bf16_relu_bits, one row of Cout / 32 words per padded pixel):
+ * as_conv_nhwc_bf16_relu_bits is the ReLU convolution that also writes the bits of its output, as_conv_nhwc_bf16_bitmasked
+ * the data gradient y = (conv(x, w) + addend) zeroed where the bit is clear.  Cout % 32 == 0. */
+int as_conv_nhwc_bf16_relu_bits(const void* x, const void* w, void* y, const float* bias, uint32_t* bits, int64_t R, int H, int W, int Cin,
+                                int Cout, int taps, void* stream);
+int as_conv_nhwc_bf16_bitmasked(const void* x, const void* w, void* y, const void* addend, const uint32_t* bits, int64_t R, int H, int W,
+                                int Cin, int Cout, int taps, void* stream);
 
 /* Weight gradient of the NHWC convolution above: dw[tap][co][ci] = sum_p dy[p][co] * x[p + shift(tap)][ci] as one
  * tap-batched, split-K tcgen05 GEMM with both operands read MN-major.  dy [R,(H+2),(W+2),Cout] bf16 (zero border),

@@ -334,3 +334,47 @@ def test_upconv_fused_tail_vs_torch(relu_input):
     assert (gx - xr.grad).abs().max().item() < 0.01 * xr.grad.abs().max().item() + 1e-3
     assert (wd.grad.cpu() - wr.grad).abs().max().item() < 1e-4 * wr.grad.abs().max().item() + 1e-3
     assert abs(float(bd.grad) - float(br.grad)) < 1e-3 * abs(float(br.grad)) + 1e-3
+
+
+@pytest.mark.parametrize('k1,k2,C', [(1, 1, 128), (3, 3, 128), (3, 1, 64)])
+def test_conv_chain_relu_sign_bits(monkeypatch, k1, k2, C):
+    """conv -> ReLU -> conv with the ReLU backward applied in the second convolution's data-gradient epilogue: from the sign
+    bits the first convolution wrote (as_conv_nhwc_bf16_relu_bits / _bitmasked) and from the bf16 map itself
+    (as_conv_nhwc_bf16_masked) the gradients are bit-identical, and both match torch."""
+    from applestar_b200 import _lib, spatial
+    R, H, W = 3, 19, 20
+    x0 = _rand((R, C, H, W), 31)
+    w1_0, w2_0 = _rand((C, C, k1, k1), 32, 0.05), _rand((C, C, k2, k2), 33, 0.05)
+    b1_0 = _rand((C,), 34)
+    gy = None
+    grads, calls = {}, {}
+    for bits_on in (True, False):
+        monkeypatch.setattr(spatial, 'RELU_BITS', bits_on)
+        seen = []
+        orig = _lib.call
+        monkeypatch.setattr(_lib, 'call', lambda name, *a, _o=orig, _s=seen: (_s.append(name), _o(name, *a))[1])
+        x = x0.clone().requires_grad_(True)
+        w1, w2, b1 = w1_0.clone().requires_grad_(True), w2_0.clone().requires_grad_(True), b1_0.clone().requires_grad_(True)
+        h = spatial.conv(_to_p(x), w1, b1, relu=True, grad_premasked=True)
+        y = spatial.conv(h, w2, None, relu=False, mask_input_grad=True)
+        if gy is None:
+            gy = torch.zeros_like(y)
+            gy[:, 1:-1, 1:-1] = _rand((R, H, W, C), 35).to(torch.bfloat16)
+        y.backward(gy)
+        monkeypatch.setattr(_lib, 'call', orig)
+        grads[bits_on] = (x.grad.clone(), w1.grad.clone(), w2.grad.clone(), b1.grad.clone(), _from_p(y).clone())
+        calls[bits_on] = seen
+    assert 'as_conv_nhwc_bf16_relu_bits' in calls[True] and 'as_conv_nhwc_bf16_bitmasked' in calls[True]
+    assert 'as_conv_nhwc_bf16_masked' in calls[False] and 'as_conv_nhwc_bf16_bitmasked' not in calls[False]
+    for a, b in zip(grads[True], grads[False]):
+        assert torch.equal(a, b)
+    xr = x0.to(torch.bfloat16).float().requires_grad_(True)
+    w1r, w2r = w1_0.to(torch.bfloat16).float().requires_grad_(True), w2_0.to(torch.bfloat16).float().requires_grad_(True)
+    hr = F.relu(F.conv2d(xr, w1r, b1_0, padding=k1 // 2)).to(torch.bfloat16).float()
+    yr = F.conv2d(hr, w2r, None, padding=k2 // 2)
+    hr_full = F.relu(F.conv2d(xr, w1r, b1_0, padding=k1 // 2))
+    yr = F.conv2d(hr_full, w2r, None, padding=k2 // 2)
+    yr.backward(_from_p(gy))
+    gx = grads[True][0]
+    assert (gx - xr.grad).abs().max().item() < 0.03 * xr.grad.abs().max().item() + 1e-3
+    assert (grads[True][1] - w1r.grad).abs().max().item() < 0.03 * w1r.grad.abs().max().item() + 1e-2
