@@ -368,3 +368,69 @@ def test_value_encoder_path_vs_oracle():
         if cos < 0.95 or rel > 0.35:        # gradients pass the 34-layer critic tower in bf16: the reference's own bf16
             bad.append((k, cos, rel))       # run is ~0.24 off on these tensors (fixture, value_networks aggregate)
     assert not bad, bad[:8]
+
+
+@gpu
+def test_actor_shared_batch_inference_protocol():
+    """actor_batch.SharedBatchInference (reference: Agent.gpu_batch_inference, agent.py:781-805, with copy_input_data /
+    copy_output_data, :37-89): only rows whose flag is raised are served and written back, flags are cleared, the rest of
+    the shared output stays untouched; served results equal the direct model call on the same rows (teacher path:
+    deterministic logits; sampling path: same Gumbel noise -> same actions)."""
+    from applestar_b200 import actor_batch
+    model, sd = _model()
+    model.eval()
+    E, N = 4, 512                                            # environments = rows of the shared buffers
+    data = synth.gen_trajectories(1, E, N, 41, special=True)
+    obs = {k: synth.tree_map(lambda t: t[:E], data[k]) for k in ('spatial_info', 'entity_info', 'scalar_info')}
+    en = data['entity_num'][:E]
+    hs = [(h[:E], c[:E]) for h, c in data['hidden_state']]
+    act = {k: v[0] for k, v in data['action_info'].items()}
+    sun = data['selected_units_num'][0]
+    full = dict(obs, entity_num=en, hidden_state=hs, action_info=act, selected_units_num=sun)
+    shared_in = synth.tree_map(lambda t: torch.zeros_like(t).share_memory_(), full)
+    signals = torch.zeros(E).share_memory_()
+    # environment side: rows 0 and 2 publish their step, 1 and 3 stay idle
+    for idx in (0, 2):
+        step = {'entity_num': en[idx], 'selected_units_num': sun[idx],
+                'hidden_state': [(h[idx], c[idx]) for h, c in hs],
+                'spatial_info': {k: v[idx] for k, v in obs['spatial_info'].items()},
+                'scalar_info': {k: v[idx] for k, v in obs['scalar_info'].items()},
+                'entity_info': {k: v[idx, :int(en[idx])] for k, v in obs['entity_info'].items()},
+                'action_info': {k: (v[idx, :int(sun[idx])] if k == 'selected_units' else v[idx]) for k, v in act.items()}}
+        actor_batch.copy_input_data(shared_in, step, idx)
+        signals[idx] = 1
+    with torch.no_grad():
+        want = model.compute_teacher_logit(**_cuda(synth.tree_map(lambda t: t.clone(), {k: shared_in[k] for k in (
+            'spatial_info', 'entity_info', 'scalar_info')})), entity_num=shared_in['entity_num'].cuda(),
+            hidden_state=_cuda(shared_in['hidden_state']), selected_units_num=shared_in['selected_units_num'].cuda(),
+            action_info=_cuda(shared_in['action_info']))
+    shared_out = {'logit': {k: torch.zeros((E,) + tuple(v.shape[1:])).share_memory_() for k, v in want['logit'].items()},
+                  'hidden_state': [(torch.zeros(E, 384).share_memory_(), torch.zeros(E, 384).share_memory_()) for _ in range(3)]}
+    srv = actor_batch.SharedBatchInference(model, shared_in, shared_out, signals, teacher=True)
+    assert srv.poll() == 2 and float(signals.sum()) == 0 and srv.poll() == 0
+    for k, v in want['logit'].items():
+        got = shared_out['logit'][k]
+        for idx in (0, 2):
+            assert torch.equal(got[idx], v[idx].float().cpu()), k
+        assert float(got[1].abs().sum()) == 0 and float(got[3].abs().sum()) == 0
+    for layer in range(3):
+        assert torch.equal(shared_out['hidden_state'][layer][0][2], want['hidden_state'][layer][0][2].float().cpu())
+    # sampling path through ActorStep with fixed noise
+    from applestar_b200 import ops
+    noise = ops.fresh_gumbel(E, N, torch.device('cuda:0'))
+    with torch.no_grad():
+        ref = model.compute_logp_action(**_cuda({k: shared_in[k] for k in ('spatial_info', 'entity_info', 'scalar_info')}),
+                                        entity_num=shared_in['entity_num'].cuda(), hidden_state=_cuda(shared_in['hidden_state']),
+                                        gumbel_noise=noise)
+    out2 = {'action_info': {k: torch.full((E,) + ((64,) if k == 'selected_units' else ()), -1, dtype=torch.int64).share_memory_()
+                            for k in ref['action_info']},
+            'selected_units_num': torch.zeros(E, dtype=torch.int64).share_memory_()}
+    signals[1] = 1
+    srv2 = actor_batch.SharedBatchInference(model, shared_in, out2, signals, teacher=False)
+    assert srv2.poll(gumbel_noise=noise) == 1
+    for k, v in ref['action_info'].items():
+        got = out2['action_info'][k][1]
+        want_row = v[1].cpu()
+        assert torch.equal(got[:want_row.numel()] if got.dim() else got, want_row), k
+        assert int(out2['action_info'][k][0].reshape(-1)[0]) == -1           # rows that did not ask keep their content
+    assert int(out2['selected_units_num'][1]) == int(ref['selected_units_num'][1])
