@@ -1,5 +1,6 @@
-"""Which ATen operators still launch kernels inside one learner step (eager), by device time: torch.profiler over one
-step at the benchmark size.  usage: python tools/aten_ops.py [rows]"""
+"""Which library (ATen) kernels still run inside one eager learner step, and from which line of this repo: torch profiler with
+Python stacks, CUDA time per (op, input shapes, innermost applestar_b200 frame when the profiler has one).  python tools/aten_ops.py > gpurun_out/aten_ops.txt"""
+import collections
 import os
 import sys
 
@@ -20,10 +21,22 @@ step = LearnerStep(model, ReinforcementLoss({}, 'MP0'), use_graph=False)
 data = synth.tree_map(lambda t: t.to(dev), synth.gen_trajectories(64, 16, 512, 1234))
 step(data)
 torch.cuda.synchronize()
-with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], with_stack=True) as prof:
+with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], with_stack=True, record_shapes=True) as prof:
     step(data)
     torch.cuda.synchronize()
-rows = int(sys.argv[1]) if len(sys.argv) > 1 else 45
-print(prof.key_averages().table(sort_by='self_cuda_time_total', row_limit=rows, max_name_column_width=60))
-print(prof.key_averages(group_by_stack_n=4).table(sort_by='self_cuda_time_total', row_limit=30, max_name_column_width=50,
-                                                  max_src_column_width=90))
+agg = collections.defaultdict(lambda: [0, 0.0])
+for ev in prof.events():
+    if ev.device_type != torch.autograd.DeviceType.CPU or not ev.name.startswith('aten::'):
+        continue
+    cuda_us = sum(k.duration for k in ev.kernels) if ev.kernels else 0.0
+    if cuda_us <= 0:
+        continue
+    frame = next((s for s in (ev.stack or []) if 'applestar_b200' in s or 'bench.py' in s), 'autograd engine / other')
+    shapes = str([tuple(s) for s in (ev.input_shapes or []) if s])[:70]
+    key = (ev.name, (frame.strip()[-60:] if frame != 'autograd engine / other' else '') + ' ' + shapes)
+    agg[key][0] += 1
+    agg[key][1] += cuda_us
+tot = sum(v[1] for v in agg.values())
+print('library ops with GPU time inside one eager step: %.1f us total' % tot)
+for (name, frame), (n, us) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:60]:
+    print('%8.1f us %4d  %-28s %s' % (us, n, name, frame))
