@@ -68,6 +68,8 @@ int su_prefix_bwd(const float*, const long long*, const long long*, const float*
 int su_mask_logits(const float*, const long long*, const long long*, float*, long long, int, int, int, float, float, cudaStream_t);
 int conv_weight_layouts(const float*, void*, void*, int, int, int, int, cudaStream_t);
 int expand_rows(const float*, const int*, float*, long long, int, float, cudaStream_t);
+int pointer_keys_fwd(const float*, const float*, const long long*, float*, long long, int, int, cudaStream_t);
+int pointer_keys_bwd(const float*, const long long*, float*, float*, long long, int, int, cudaStream_t);
 int ce_rows_fwd(const float*, long long, const long long*, const long long*, const long long*, int, int, float, float*, float*, int*, long long,
                 cudaStream_t);
 int ce_rows_bwd(const float*, long long, const long long*, const long long*, const long long*, int, int, float, const float*, const float*,
@@ -538,6 +540,13 @@ int as_ce_rows_bwd(const float* logits, int64_t ld, const int64_t* labels, const
                    float smoothing, const float* lse, const float* g, float* dlogits, int64_t R, void* stream) {
   return as::ce_rows_bwd(logits, ld, (const long long*)labels, (const long long*)excl, (const long long*)excl_len, S, K, smoothing, lse, g,
                          dlogits, R, ST(stream));
+}
+int as_pointer_keys_fwd(const float* key, const float* end_embedding, const int64_t* entity_num, float* out, int64_t R, int N, int D,
+                        void* stream) {
+  return as::pointer_keys_fwd(key, end_embedding, (const long long*)entity_num, out, R, N, D, ST(stream));
+}
+int as_pointer_keys_bwd(const float* dout, const int64_t* entity_num, float* dkey, float* dend, int64_t R, int N, int D, void* stream) {
+  return as::pointer_keys_bwd(dout, (const long long*)entity_num, dkey, dend, R, N, D, ST(stream));
 }
 int as_attn_fwd_ok(int N, int D) { return as::attn_fwd_ok(N, D); }
 int as_attn_fwd(const void* qkv, const int64_t* key_len, void* out, void* probs, int64_t R, int N, int H, int D, float scale,

@@ -245,4 +245,83 @@ int su_mask_logits(const float* x, const long long* sel, const long long* entity
   return AS_OK;
 }
 
+// Pointer keys of the selected-units head (action_arg_head.py:118-129): one row appended to the entity keys, the end-flag
+// embedding placed at row entity_num.  out [R, N + 1, D] fp32; key [R, N, D]; D a multiple of 4.
+__global__ void pointer_keys_fwd_kernel(const float* __restrict__ key, const float* __restrict__ end_emb, const long long* __restrict__ entity_num,
+                                        float* __restrict__ out, long long R, int N, int D4) {
+  const long long total = R * (N + 1) * D4;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int d = (int)(i % D4);
+    const long long rn = i / D4;
+    const int n = (int)(rn % (N + 1));
+    const long long r = rn / (N + 1);
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (n == entity_num[r]) v = __ldg(reinterpret_cast<const float4*>(end_emb) + d);
+    else if (n < N) v = __ldg(reinterpret_cast<const float4*>(key) + (r * N + n) * D4 + d);
+    reinterpret_cast<float4*>(out)[i] = v;
+  }
+}
+// dkey[r, n, :] = dout[r, n, :] except at the end-flag row (zero); dend[d] = sum_r dout[r, entity_num[r], d] in row order
+__global__ void pointer_keys_bwd_kernel(const float* __restrict__ dout, const long long* __restrict__ entity_num, float* __restrict__ dkey,
+                                        long long R, int N, int D4) {
+  const long long total = R * N * D4;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int d = (int)(i % D4);
+    const long long rn = i / D4;
+    const int n = (int)(rn % N);
+    const long long r = rn / N;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (n != entity_num[r]) v = __ldg(reinterpret_cast<const float4*>(dout) + (r * (N + 1) + n) * D4 + d);
+    reinterpret_cast<float4*>(dkey)[i] = v;
+  }
+}
+__global__ void pointer_keys_dend_kernel(const float* __restrict__ dout, const long long* __restrict__ entity_num, float* __restrict__ dend,
+                                         long long R, int N, int D) {
+  // one block; thread = (row lane, d): rows strided over the lanes, then a fixed-order sum over the lanes
+  extern __shared__ float part[];                       // [lanes][D]
+  const int lanes = blockDim.x / D;
+  const int d = threadIdx.x % D, l = threadIdx.x / D;
+  float acc = 0.f;
+  if (l < lanes)
+    for (long long r = l; r < R; r += lanes) {
+      const long long e = entity_num[r];
+      if (e >= 0 && e <= N) acc += dout[(r * (N + 1) + e) * D + d];
+    }
+  if (l < lanes) part[l * D + d] = acc;
+  __syncthreads();
+  if (threadIdx.x < D) {
+    float s = 0.f;
+    for (int k = 0; k < lanes; ++k) s += part[k * D + threadIdx.x];
+    dend[threadIdx.x] = s;
+  }
+}
+int pointer_keys_fwd(const float* key, const float* end_emb, const long long* entity_num, float* out, long long R, int N, int D,
+                     cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (N <= 0 || D <= 0 || (D % 4) != 0 || D > 256) return AS_ESIZE;
+  if (!key || !end_emb || !entity_num || !out) return AS_EINVAL;
+  const long long total = R * (N + 1) * (D / 4);
+  long long blocks = (total + 255) / 256;
+  pointer_keys_fwd_kernel<<<(unsigned)(blocks < 148 * 16 ? blocks : 148 * 16), 256, 0, st>>>(key, end_emb, entity_num, out, R, N, D / 4);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+int pointer_keys_bwd(const float* dout, const long long* entity_num, float* dkey, float* dend, long long R, int N, int D, cudaStream_t st) {
+  if (R <= 0) return AS_OK;
+  if (N <= 0 || D <= 0 || (D % 4) != 0 || D > 256) return AS_ESIZE;
+  if (!dout || !entity_num || (!dkey && !dend)) return AS_EINVAL;
+  if (dkey) {
+    const long long total = R * N * (D / 4);
+    long long blocks = (total + 255) / 256;
+    pointer_keys_bwd_kernel<<<(unsigned)(blocks < 148 * 16 ? blocks : 148 * 16), 256, 0, st>>>(dout, entity_num, dkey, R, N, D / 4);
+    AS_LAUNCH_CHECK();
+  }
+  if (dend) {
+    const int threads = (1024 / D) * D;
+    pointer_keys_dend_kernel<<<1, threads, (size_t)threads * sizeof(float), st>>>(dout, entity_num, dend, R, N, D);
+    AS_LAUNCH_CHECK();
+  }
+  return AS_OK;
+}
+
 }  // namespace as

@@ -305,12 +305,36 @@ def categorical_log_prob(logits, action):
     return torch.log_softmax(logits, dim=-1).gather(-1, action.unsqueeze(-1)).squeeze(-1)
 
 
+class _PointerKeys(torch.autograd.Function):
+    """[kernel] as_pointer_keys_fwd / _bwd"""
+
+    @staticmethod
+    def forward(ctx, key, end_embedding, entity_num):
+        R, N, D = key.shape
+        key = key.contiguous().float()
+        end = end_embedding.reshape(-1).contiguous().float()
+        en = entity_num.contiguous().long()
+        out = torch.empty((R, N + 1, D), dtype=torch.float32, device=key.device)
+        _lib.call('as_pointer_keys_fwd', key.data_ptr(), end.data_ptr(), en.data_ptr(), out.data_ptr(), R, N, D, _lib.stream_ptr())
+        ctx.save_for_backward(en)
+        ctx.dims = (R, N, D, end_embedding.shape)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (en,) = ctx.saved_tensors
+        R, N, D, eshape = ctx.dims
+        dout = dout.contiguous().float()
+        dkey = torch.empty((R, N, D), dtype=torch.float32, device=dout.device) if ctx.needs_input_grad[0] else None
+        dend = torch.empty(D, dtype=torch.float32, device=dout.device) if ctx.needs_input_grad[1] else None
+        _lib.call('as_pointer_keys_bwd', dout.data_ptr(), en.data_ptr(), K._ptr(dkey), K._ptr(dend), R, N, D, _lib.stream_ptr())
+        return dkey, (None if dend is None else dend.view(eshape)), None
+
+
 def pointer_keys(key, end_embedding, entity_num):
-    """Append a row and place the end-flag embedding at index entity_num (action_arg_head.py:118-129)."""
-    R, N, D = key.shape
-    key = torch.cat([key, key.new_zeros(R, 1, D)], dim=1)
-    is_end = torch.arange(N + 1, device=key.device).unsqueeze(0) == entity_num.unsqueeze(1)
-    return torch.where(is_end.unsqueeze(2), end_embedding.view(1, 1, D), key)
+    """[kernel] Append a row and place the end-flag embedding at index entity_num (action_arg_head.py:118-129)."""
+    require_cuda(key)
+    return _PointerKeys.apply(key, end_embedding, entity_num)
 
 
 class _PointerLogits(torch.autograd.Function):

@@ -309,6 +309,13 @@ int as_spatial_front_bwd(const void* const* planes, const void* const* effects, 
                          const void* cells, const void* codes, const void* dpool, float* dweight, float* dbias, float* g_entity,
                          float* scratch, int64_t R, int H, int W, void* stream);
 
+/* Pointer keys of the SelectedUnits head (head/action_arg_head.py:118-129): out [R, N+1, D] = key [R, N, D] with one zero
+ * row appended and the end-flag embedding [D] placed at row entity_num[r].  Backward: dkey = dout without the end-flag row
+ * (zero there), dend[d] = sum_r dout[r, entity_num[r], d] in row order (deterministic).  fp32, D % 4 == 0, D <= 256. */
+int as_pointer_keys_fwd(const float* key, const float* end_embedding, const int64_t* entity_num, float* out, int64_t R, int N, int D,
+                        void* stream);
+int as_pointer_keys_bwd(const float* dout, const int64_t* entity_num, float* dkey, float* dend, int64_t R, int N, int D, void* stream);
+
 /* Trajectory staging (rl_training/rl_dataloader.py:206-245 pads the teacher's selected-units logits to [T,B,64,N+1] with
  * -1e9: 134 MB of the 456 MB learner batch, almost all padding).  The host sends only the rows the teacher emitted plus
  * one int32 per dense row; as_expand_rows_f32 rebuilds the dense tensor on the device:

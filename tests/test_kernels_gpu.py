@@ -342,3 +342,28 @@ def test_ce_rows_at_learner_size_vs_torch():
     ref.sum().backward()
     assert torch.allclose(row.view(b, s), ref, rtol=1e-5, atol=1e-5)
     assert torch.allclose(su.grad, su2.grad, rtol=1e-4, atol=1e-7)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('R,N,D', [(37, 512, 32), (5, 64, 32), (3, 7, 8)])
+def test_pointer_keys_fwd_bwd(R, N, D):
+    """ops.pointer_keys (as_pointer_keys_fwd/bwd) against the reference's cat + where (action_arg_head.py:118-129): forward
+    bit-exact, key gradient bit-exact, end-embedding gradient a fixed-order fp32 sum."""
+    from applestar_b200 import ops
+    dev = torch.device('cuda:0')
+    g = torch.Generator(device=dev).manual_seed(R * N)
+    key = torch.randn(R, N, D, device=dev, generator=g).requires_grad_(True)
+    end = torch.randn(1, D, device=dev, generator=g).requires_grad_(True)
+    en = torch.randint(1, N + 1, (R,), device=dev, generator=g)
+    en[0] = N                                                   # end flag on the appended row
+    out = ops.pointer_keys(key, end, en)
+    go = torch.randn(R, N + 1, D, device=dev, generator=g)
+    out.backward(go)
+    k2, e2 = key.detach().clone().requires_grad_(True), end.detach().clone().requires_grad_(True)
+    cat = torch.cat([k2, k2.new_zeros(R, 1, D)], dim=1)
+    is_end = torch.arange(N + 1, device=dev).unsqueeze(0) == en.unsqueeze(1)
+    ref = torch.where(is_end.unsqueeze(2), e2.view(1, 1, D), cat)
+    ref.backward(go)
+    assert torch.equal(out, ref)
+    assert torch.equal(key.grad, k2.grad)
+    assert torch.allclose(end.grad, e2.grad, rtol=1e-5, atol=1e-5)
