@@ -216,7 +216,7 @@ class SpatialEncoder(nn.Module):
         self.res = nn.ModuleList([ResBlock(128) for _ in range(4)])
         self.fc = FC(128 * (C.SPATIAL_Y // 8) * (C.SPATIAL_X // 8), 256, relu=True)
 
-    def forward(self, spatial_info, x):
+    def forward(self, spatial_info, x, head_rows=None):
         """`x` = the 2x2 max-pooled output of the 1x1 project conv + ReLU as a padded NHWC bf16 map (spatial.spatial_front,
         which also holds the ScatterConnection and the 56-channel input).
         -> (embedded_spatial [R,256], map_skip).  map_skip[0..2] (pre-pool maps, only read by the U-Net variant of
@@ -228,7 +228,8 @@ class SpatialEncoder(nn.Module):
                 x = spatial.max_pool2(x, relu_input=True)         # the pool's backward applies the conv's ReLU mask
             x = conv(x, grad_premasked=(i < 2))                   # outputs 0 and 1 feed only the next pool
         for block in self.res:
-            skip.append(x)
+            x, x_heads = ops.prefix_fork(x, head_rows)       # the location head reads the first head_rows rows only
+            skip.append(x_heads)
             x = block(x)
         H8, W8 = C.SPATIAL_Y // 8, C.SPATIAL_X // 8
         return spatial.spatial_fc(x, self.fc[0].weight, self.fc[0].bias, 128, H8, W8), skip
@@ -337,17 +338,20 @@ class Encoder(nn.Module):
         self.entity_encoder = EntityEncoder()
         self.scatter_project = FC(256, 32, relu=True)
 
-    def forward(self, spatial_info, entity_info, scalar_info, entity_num):
+    def forward(self, spatial_info, entity_info, scalar_info, entity_num, head_rows=None):
+        """head_rows: the learner's policy heads read only the first `head_rows` rows of entity_embeddings / map_skip
+        (model.py:128-137); they are then returned already cut (ops.prefix_fork)."""
         br = side_stream(entity_num.device)
         with br:
             embedded_scalar, scalar_context, baseline_feature = self.scalar_encoder(scalar_info)
         entity_embeddings, embedded_entity = self.entity_encoder(entity_info, entity_num)
-        proj = self.scatter_project(entity_embeddings)
+        ent_full, entity_embeddings = ops.prefix_fork(entity_embeddings, head_rows)
+        proj = self.scatter_project(ent_full)
         # ScatterConnection ('add') + one-hot / effect planes + 1x1 project conv + ReLU in padded NHWC bf16
         pw = self.spatial_encoder.project[0]
         projected = spatial.spatial_front(proj, entity_info['x'], entity_info['y'], entity_num, spatial_info,
                                           pw.weight, pw.bias)
-        embedded_spatial, map_skip = self.spatial_encoder(spatial_info, projected)
+        embedded_spatial, map_skip = self.spatial_encoder(spatial_info, projected, head_rows)
         br.join([embedded_scalar, scalar_context, baseline_feature])
         lstm_input = torch.cat([embedded_scalar, embedded_entity, embedded_spatial], dim=-1)
         return lstm_input, scalar_context, baseline_feature, entity_embeddings, map_skip
@@ -751,7 +755,8 @@ class Model(nn.Module):
         if not kwargs.get('defer_checks', False):
             ops.raise_if_negative_index()
         flat_action = {k: v.flatten(0, 1) for k, v in action_info.items()}
-        lstm_input, ctx, base, ent, skip = self.encoder(spatial_info, entity_info, scalar_info, entity_num)
+        lstm_input, ctx, base, ent, skip = self.encoder(spatial_info, entity_info, scalar_info, entity_num,
+                                                        head_rows=entity_num.shape[0] - B)
         hs = hidden_state[0][0].shape[-1]
         state0 = [tuple(s.view(-1, B, hs)[0] for s in layer) for layer in hidden_state]     # t=0 state only (A12)
         out, _ = self.core_lstm(lstm_input.view(-1, B, lstm_input.shape[-1]), state0)
@@ -765,8 +770,7 @@ class Model(nn.Module):
             values = {k: v(critic_input).view(T + 1, B) for k, v in self.value_networks.items()}
         ops.SU_STEPS_HINT = kwargs.get('selected_units_max')       # optional host-side int: avoids a device sync
         try:
-            _, _, logits = self.policy.train_forward(out[:-B], ent[:-B], [None if m is None else m[:-B] for m in skip],
-                                                     ctx[:-B], entity_num[:-B], flat_action,
+            _, _, logits = self.policy.train_forward(out[:-B], ent, skip, ctx[:-B], entity_num[:-B], flat_action,
                                                      selected_units_num.flatten(0, 1), self.cfg.temperature)
         finally:
             ops.SU_STEPS_HINT = None

@@ -305,6 +305,50 @@ def categorical_log_prob(logits, action):
     return torch.log_softmax(logits, dim=-1).gather(-1, action.unsqueeze(-1)).squeeze(-1)
 
 
+class _PrefixFork(torch.autograd.Function):
+    """x -> (alias of x, x[:n]).  The learner runs the encoder on (T + 1) * B rows but the policy heads only on the first
+    T * B (model.py:128-137 slices `[:-batch_size]`); autograd would zero-fill a full-size buffer for the slice's gradient,
+    copy the heads' gradient into it and add it to the gradient of the tensor's other consumers in a third pass.  With
+    both consumers behind this node the sum is one pass: out[:n] = g_full[:n] + g_head (as_add_act_bf16), out[n:] = g_full[n:]."""
+
+    @staticmethod
+    def forward(ctx, x, n):
+        ctx.set_materialize_grads(False)
+        ctx.n = n
+        ctx.rows = x.shape[0]
+        return x.view_as(x), x.narrow(0, 0, n)
+
+    @staticmethod
+    def backward(ctx, g_full, g_head):
+        n = ctx.n
+        if g_head is None:
+            return g_full, None
+        g_head = g_head.contiguous()
+        if g_full is None:
+            out = g_head.new_zeros((ctx.rows,) + tuple(g_head.shape[1:])) if hasattr(ctx, 'rows') else None
+            if out is None:
+                raise RuntimeError('prefix_fork: the full-size alias received no gradient')
+            out[:n].copy_(g_head)
+            return out, None
+        g_full = g_full.contiguous()
+        out = torch.empty_like(g_full)
+        numel = g_head.numel()
+        if g_full.dtype == torch.bfloat16 and g_head.dtype == torch.bfloat16 and numel % 8 == 0 and g_full.is_cuda:
+            _lib.call('as_add_act_bf16', g_full.data_ptr(), g_head.data_ptr(), out.data_ptr(), numel, 0, _lib.stream_ptr())
+        else:
+            torch.add(g_full[:n], g_head.to(g_full.dtype), out=out[:n])
+        if out.shape[0] > n:
+            out[n:].copy_(g_full[n:])
+        return out, None
+
+
+def prefix_fork(x, n):
+    """(x for the consumers that take every row, x[:n] for the policy heads); see _PrefixFork."""
+    if n is None or n >= x.shape[0] or not x.requires_grad:
+        return x, (x if n is None else x[:n])
+    return _PrefixFork.apply(x, int(n))
+
+
 class _PointerKeys(torch.autograd.Function):
     """[kernel] as_pointer_keys_fwd / _bwd"""
 
