@@ -68,3 +68,27 @@ for n, (c, us) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:45]:
     print('%9.1f us %5.1f%% %5d  %s' % (us, 100 * us / tot, c, n))
 lib = sum(v[1] for n, v in agg.items() if not n.startswith('as::'))
 print('library kernels: %.2f ms in %d launches' % (lib / 1e3, sum(v[0] for n, v in agg.items() if not n.startswith('as::'))))
+# context of the largest gap: the kernels (all streams) that end / start around it
+big = max(gaps, key=lambda g: g[0])
+allk = sorted(((e.time_range.start, e.time_range.end, e.name, getattr(e, 'device_index', 0)) for e in prof.events()
+               if e.device_type == torch.autograd.DeviceType.CUDA), key=lambda t: t[0])
+edge = None
+cur_e = allk[0][1]
+for s, e, n, _ in allk[1:]:
+    if s - cur_e >= big[0] - 1:
+        edge = (cur_e, s)
+        break
+    cur_e = max(cur_e, e)
+if edge:
+    print('\nlargest gap: %.1f us, %.2f ms after the first kernel' % (edge[1] - edge[0], (edge[0] - allk[0][0]) / 1e3))
+    before = [k for k in allk if k[1] <= edge[0]][-6:]
+    after = [k for k in allk if k[0] >= edge[1]][:6]
+    for s, e, n, _ in before:
+        print('  before: ends %8.1f us before the gap, %7.1f us long  %s' % (edge[0] - e, e - s, n[:90]))
+    for s, e, n, _ in after:
+        print('  after : starts %7.1f us after the gap, %7.1f us long  %s' % (s - edge[1], e - s, n[:90]))
+    inside = [k for k in sorted(((e.time_range.start, e.time_range.end, e.name) for e in prof.events()
+                                 if e.device_type == torch.autograd.DeviceType.CUDA), key=lambda t: t[0])
+              if k[0] < edge[1] and k[1] > edge[0]]
+    for s, e, n in inside[:10]:
+        print('  overlapping the gap: %8.1f us .. %8.1f us  %s' % (s - edge[0], e - edge[0], n[:90]))
