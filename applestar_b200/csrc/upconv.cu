@@ -15,7 +15,7 @@ namespace as {
 constexpr int kUcC = 32;
 constexpr int kUcThreads = 320;                // forward: two row groups x 160 output columns
 constexpr int kUcBandHi = 8;                 // output rows per forward CTA
-constexpr int kUcBandLo = 4;                 // low-res rows per backward CTA
+constexpr int kUcBandLo = 8;                 // low-res rows per backward CTA
 constexpr int kUcMaxWlo = 80;                // low-res width limit (shared-memory tiles)
 
 // F.interpolate(scale 2, bilinear, align_corners=False): source position of output index o, neighbours clamped
@@ -138,7 +138,7 @@ upconv_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__
 }
 
 // ------------------------------------------------------------------------------------------------ backward
-// CTA = (image, band of kUcBandLo low-res rows).  A: logit gradients of the 13 output rows that reach the band (times
+// CTA = (image, band of kUcBandLo low-res rows).  A: logit gradients of the 2 * band + 5 output rows that reach the band (times
 // 1/temperature, zero outside the image) -> shared memory; B: dY_t[n] = sum over the 4x4 outputs q around n of
 // bilinear weight x dlogit[q - t]; C: thread = (low pixel, 8 channels): dX = sum_t w[t][c] dY_t (masked by X > 0 when
 // relu_input), dW partials in registers (fixed channel group per thread), reduced over the CTA in fixed order.
