@@ -189,15 +189,34 @@ __global__ void clip_adam_kernel(float* __restrict__ p, const float* __restrict_
   __syncthreads();
   const float clip = s_clip;
   const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    float gi = g[i] * clip;
-    float pi = p[i];
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  auto update = [&](float gi, float& pi, float& mi, float& vi) {
+    gi *= clip;
     if (wd != 0.f) gi += wd * pi;
-    const float mi = beta1 * m[i] + (1.f - beta1) * gi;
-    const float vi = beta2 * v[i] + (1.f - beta2) * gi * gi;
-    m[i] = mi; v[i] = vi;
+    mi = beta1 * mi + (1.f - beta1) * gi;
+    vi = beta2 * vi + (1.f - beta2) * gi * gi;
     pi -= lr * (mi / bc1) / (sqrtf(vi / bc2) + eps);
-    p[i] = pi;
+  };
+  // 16-byte accesses when the four streams allow it (the flat buffers of learner.FlatParams are 32-byte aligned)
+  const bool vec = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m) |
+                     reinterpret_cast<uintptr_t>(v)) & 15) == 0 && (shadow == nullptr || (reinterpret_cast<uintptr_t>(shadow) & 7) == 0);
+  const long long n4 = vec ? n / 4 : 0;
+  for (long long i = tid; i < n4; i += stride) {
+    const float4 g4 = reinterpret_cast<const float4*>(g)[i];
+    float4 p4 = reinterpret_cast<float4*>(p)[i], m4 = reinterpret_cast<float4*>(m)[i], v4 = reinterpret_cast<float4*>(v)[i];
+    update(g4.x, p4.x, m4.x, v4.x); update(g4.y, p4.y, m4.y, v4.y); update(g4.z, p4.z, m4.z, v4.z); update(g4.w, p4.w, m4.w, v4.w);
+    reinterpret_cast<float4*>(m)[i] = m4; reinterpret_cast<float4*>(v)[i] = v4; reinterpret_cast<float4*>(p)[i] = p4;
+    if (shadow) {
+      __nv_bfloat162 lo = __floats2bfloat162_rn(p4.x, p4.y), hi = __floats2bfloat162_rn(p4.z, p4.w);
+      uint2 u;
+      u.x = *reinterpret_cast<uint32_t*>(&lo); u.y = *reinterpret_cast<uint32_t*>(&hi);
+      reinterpret_cast<uint2*>(shadow)[i] = u;
+    }
+  }
+  for (long long i = n4 * 4 + tid; i < n; i += stride) {
+    float pi = p[i], mi = m[i], vi = v[i];
+    update(g[i], pi, mi, vi);
+    m[i] = mi; v[i] = vi; p[i] = pi;
     if (shadow) shadow[i] = __float2bfloat16_rn(pi);
   }
 }
