@@ -21,7 +21,7 @@ _ERR = {-1: 'AS_EINVAL (bad pointer / argument)', -2: 'AS_ESIZE (size out of ran
 class AsSuSampleArgs(ctypes.Structure):
     """as_su_sample_args (include/applestar_b200.h)."""
     PTRS = ('key', 'c0', 'c1', 'mt', 'wf1t', 'bf1', 'wq2t', 'bq2', 'wih_t', 'whh_t', 'ln_i_w', 'ln_i_b', 'ln_h_w', 'ln_h_b',
-            'ln_c_w', 'ln_c_b', 'entity_num', 'su_mask', 'noise', 'logits', 'units', 'num', 'extra', 'emb', 'steps_row')
+            'ln_c_w', 'ln_c_b', 'entity_num', 'su_mask', 'noise', 'logits', 'units', 'num', 'extra', 'emb', 'steps_row', 'ended_rows')
     _fields_ = [(n, c_void_p) for n in PTRS] + [('R', c_int32), ('N1', c_int32), ('S', c_int32), ('extra_units', c_int32),
                                                   ('temperature', c_float)]
 

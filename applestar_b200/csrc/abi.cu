@@ -572,7 +572,7 @@ int as_su_sample(const as_su_sample_args* a, void* stream) {
   p.wih_t = a->wih_t; p.whh_t = a->whh_t; p.ln_i_w = a->ln_i_w; p.ln_i_b = a->ln_i_b; p.ln_h_w = a->ln_h_w; p.ln_h_b = a->ln_h_b;
   p.ln_c_w = a->ln_c_w; p.ln_c_b = a->ln_c_b; p.entity_num = reinterpret_cast<const long long*>(a->entity_num);
   p.su_mask = a->su_mask; p.noise = a->noise; p.logits = a->logits; p.units = reinterpret_cast<long long*>(a->units);
-  p.num = reinterpret_cast<long long*>(a->num); p.extra = a->extra; p.emb = a->emb; p.steps_row = a->steps_row;
+  p.num = reinterpret_cast<long long*>(a->num); p.extra = a->extra; p.emb = a->emb; p.steps_row = a->steps_row; p.ended_rows = a->ended_rows;
   p.R = a->R; p.N1 = a->N1; p.S = a->S; p.extra_units = a->extra_units; p.temperature = a->temperature;
   return as::su_sample(p, ST(stream));
 }

@@ -38,6 +38,7 @@ __global__ void __launch_bounds__(256, 1) su_sample_kernel(const SuSampleDev p) 
   __shared__ float sBv[NR][8];
   __shared__ int sBi[NR][8];
   __shared__ float sEndLogit[NR];
+  __shared__ int sStop;
   __shared__ int sEnded[NR];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -74,7 +75,9 @@ __global__ void __launch_bounds__(256, 1) su_sample_kernel(const SuSampleDev p) 
     ended = p.su_mask[row0 + warp] ? 0 : 1;
     num = ended ? 0 : S;
     steps_row = ended ? 0 : S;
+    if (ended && lane == 0 && p.ended_rows) atomicAdd(p.ended_rows, 1);
   }
+  if (tid == 0) sStop = 0;
   float lniw[4], lnib[4], lnhw[4], lnhb[4];
 #pragma unroll
   for (int g = 0; g < 4; ++g) {
@@ -86,6 +89,9 @@ __global__ void __launch_bounds__(256, 1) su_sample_kernel(const SuSampleDev p) 
   __syncthreads();
 
   for (int step = 0; step < S; ++step) {
+    // every row of the batch has raised its end flag (the reference's early break, :309-310): the remaining steps would
+    // be trimmed by the caller anyway.  sStop was written before the barrier that closed the previous step.
+    if (sStop) break;
     // ---- query_fc1 pre-activation: c0 (+ c1 + M e1 from step 1 on)
     float pre[NR];
 #pragma unroll
@@ -228,7 +234,10 @@ __global__ void __launch_bounds__(256, 1) su_sample_kernel(const SuSampleDev p) 
         if (sBv[r][w] > best || (sBv[r][w] == best && sBi[r][w] < idx)) { best = sBv[r][w]; idx = sBi[r][w]; }
       if (idx == 0x7fffffff) idx = 0;
       const bool hit = (long long)idx == en_w;
-      if (hit && !ended) { num = step + 1; steps_row = step + 1; }
+      if (hit && !ended) {
+        num = step + 1; steps_row = step + 1;
+        if (lane == 0 && p.ended_rows) atomicAdd(p.ended_rows, 1);
+      }
       ended |= hit ? 1 : 0;
       if (!ended) {
         const unsigned bit = 1u << (idx & 31);
@@ -247,6 +256,7 @@ __global__ void __launch_bounds__(256, 1) su_sample_kernel(const SuSampleDev p) 
         sLm[r][idx >> 5] &= ~(1u << (idx & 31));                            // a picked unit is masked afterwards
       }
     }
+    if (tid == 0 && p.ended_rows) sStop = *reinterpret_cast<volatile int*>(p.ended_rows) >= p.R;
     __syncthreads();
   }
 

@@ -17,6 +17,7 @@ typedef struct as_su_sample_args {
   float* extra;
   float* emb;
   int* steps_row;
+  int* ended_rows;   /* device int, 0 at launch, or NULL: rows that have raised their end flag; when it reaches R every CTA leaves the loop */
   int R, N1, S, extra_units;
   float temperature;
 } as_su_sample_args;
@@ -47,6 +48,7 @@ struct SuSampleDev {
   float* extra;                // [R, N1]
   float* emb;                  // [R, 32]  mean of the picked keys after the last step
   int* steps_row;              // [R]      1 + step at which the row raised its end flag (0: started ended, S: never)
+  int* ended_rows;             // device counter (0 at launch) of rows whose end flag is up, or nullptr (always S steps)
   int R, N1, S, extra_units;
   float temperature;
 };

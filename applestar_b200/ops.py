@@ -584,11 +584,12 @@ def selected_units_sample(head, key, ae0, entity_num, su_mask, noise, temperatur
     entity_num = entity_num.long().contiguous()
     mask8 = su_mask.to(torch.uint8).contiguous()
     logits = torch.empty(R, S, N1, device=dev)
-    units = torch.empty(R, S, dtype=torch.long, device=dev)
-    num = torch.empty(R, dtype=torch.long, device=dev)
+    units = torch.zeros(R, S, dtype=torch.long, device=dev)     # steps after the batch-wide end are not computed: keep their
+    num = torch.empty(R, dtype=torch.long, device=dev)          # indices valid for the (trimmed-away) gathers downstream
     extra = torch.empty(R, N1, device=dev)
     emb = torch.empty(R, D, device=dev)
     steps_row = torch.empty(R, dtype=torch.int32, device=dev)
+    ended_rows = torch.zeros(1, dtype=torch.int32, device=dev)          # all R rows ended -> every CTA stops stepping
     li, lh, lc = cell.layernorm_i, cell.layernorm_h, cell.layernorm_c
     a = _lib.AsSuSampleArgs()
     for name, t in (('key', key), ('c0', c0), ('c1', w['c1']), ('mt', w['mt']), ('wf1t', w['wf1t']), ('bf1', w['bf1']),
@@ -596,7 +597,7 @@ def selected_units_sample(head, key, ae0, entity_num, su_mask, noise, temperatur
                     ('ln_i_w', li.weight), ('ln_i_b', li.bias), ('ln_h_w', lh.weight), ('ln_h_b', lh.bias),
                     ('ln_c_w', lc.weight), ('ln_c_b', lc.bias), ('entity_num', entity_num), ('su_mask', mask8),
                     ('noise', noise), ('logits', logits), ('units', units), ('num', num), ('extra', extra), ('emb', emb),
-                    ('steps_row', steps_row)):
+                    ('steps_row', steps_row), ('ended_rows', ended_rows)):
         assert t.is_contiguous() and t.device == dev
         setattr(a, name, t.data_ptr())
     a.R, a.N1, a.S, a.extra_units, a.temperature = R, N1, S, int(bool(extra_units)), float(temperature)

@@ -442,6 +442,7 @@ typedef struct as_su_sample_args {
   float* extra;
   float* emb;
   int* steps_row;
+  int* ended_rows;   /* device int, 0 at launch, or NULL: rows that have raised their end flag; when it reaches R every CTA leaves the loop */
   int R, N1, S, extra_units;
   float temperature;
 } as_su_sample_args;
