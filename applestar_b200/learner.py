@@ -309,6 +309,44 @@ def _tree_copy_(dst, src):
             _tree_copy_(d, s_)
 
 
+def tree_arena(x, dev):
+    """A copy of the tensor tree `x` whose tensors are views of ONE flat device buffer (256-byte aligned pieces), so
+    that a whole batch moves between two such trees of the same shapes with a single copy of the flat buffers instead of
+    one launch per tensor.  Returns (flat uint8 tensor, tree)."""
+    leaves = []
+
+    def walk(t):
+        if isinstance(t, torch.Tensor):
+            leaves.append(t)
+        elif isinstance(t, dict):
+            for v in t.values():
+                walk(v)
+        elif isinstance(t, (list, tuple)):
+            for v in t:
+                walk(v)
+    walk(x)
+    offsets, total = [], 0
+    for t in leaves:
+        offsets.append(total)
+        total += (t.numel() * t.element_size() + 255) // 256 * 256
+    flat = torch.empty(max(total, 256), dtype=torch.uint8, device=dev)
+    it = iter(offsets)
+
+    def build(t):
+        if isinstance(t, torch.Tensor):
+            off = next(it)
+            n = t.numel() * t.element_size()
+            view = flat[off:off + n].view(t.dtype).view(t.shape)
+            view.copy_(t, non_blocking=True)
+            return view
+        if isinstance(t, dict):
+            return {k: build(v) for k, v in t.items()}
+        if isinstance(t, (list, tuple)):
+            return type(t)(build(v) for v in t)
+        return t
+    return flat, build(x)
+
+
 def _tree_to(x, dev):
     if isinstance(x, torch.Tensor):
         return x.to(dev, non_blocking=True).clone() if x.device == dev else x.to(dev, non_blocking=True)
@@ -370,8 +408,10 @@ class LearnerStep:
 
     def _capture(self, data, key):
         dev = self.flat.flat.device
-        static = _tree_to(data, dev)
+        static_flat, static = tree_arena(data, dev)          # one flat buffer: a staged batch arrives with one copy
         static['selected_units_max'] = key[0]
+        self._static_flat = getattr(self, '_static_flat', {})
+        self._static_flat[key] = static_flat
         # warm-up (allocator, lazy initialisation) must leave no trace: the weights, the Adam moments and the step
         # counter are put back afterwards, so that the batch that triggers a capture gets exactly one optimizer
         # update like every other batch; and it runs without collectives (a peer may be replaying an existing graph
@@ -428,6 +468,16 @@ class LearnerStep:
             return None
         entry = self._graphs.get(key) or self._capture(data, key)
         return entry[1]
+
+    def static_arena(self, data):
+        """The flat buffer behind `static_inputs(data)` (learner.tree_arena layout): a staging tree built with
+        tree_arena from a batch of the same shapes can be moved in with `static_arena(data).copy_(staging_flat)`."""
+        key = self._key(data) if self.use_graph else None
+        if key is None:
+            return None
+        if key not in self._graphs:
+            self._capture(data, key)
+        return self._static_flat[key]
 
 
 class ActorStep:

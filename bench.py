@@ -573,7 +573,10 @@ def run_ours(args):
     # (copy stream, into a staging set of device buffers) overlaps the compute of batch i; a device-to-device copy
     # moves the staged batch into the step's (CUDA-graph) input buffers at the start of the step.
     copy_stream = torch.cuda.Stream(device=dev)
-    staging = synth.tree_map(lambda t: torch.empty_like(t, device=dev), host) if static is not None else None
+    # staging set with the layout of the graph's input arena: the staged batch moves in with ONE device-to-device copy
+    from applestar_b200.learner import tree_arena
+    static_flat = step_fn.static_arena(resident) if static is not None else None
+    staging_flat, staging = tree_arena(resident, dev) if static is not None else (None, None)
     stager = traj_staging.Stager(packed, dev)
     ev_copied, ev_free = torch.cuda.Event(), torch.cuda.Event()
 
@@ -600,7 +603,7 @@ def run_ours(args):
         if static is not None:
             cur = torch.cuda.current_stream()
             cur.wait_event(ev_copied)                     # this step's inputs have landed
-            _tree_copy_(static, staging)                  # D2D into the graph's input buffers
+            static_flat.copy_(staging_flat, non_blocking=True)   # D2D into the graph's input buffers (one flat copy)
             ev_free.record(cur)
             prefetch()                                    # next step's H2D runs under this step's compute
             info = step_fn(static)
