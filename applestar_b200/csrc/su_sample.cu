@@ -89,8 +89,8 @@ __global__ void __launch_bounds__(256, 1) su_sample_kernel(const SuSampleDev p) 
   __syncthreads();
 
   for (int step = 0; step < S; ++step) {
-    // every row of the batch has raised its end flag (the reference's early break, :309-310): the remaining steps would
-    // be trimmed by the caller anyway.  sStop was written before the barrier that closed the previous step.
+    // every row of the batch has raised its end flag and this CTA is past the latest of them (the reference's early
+    // break, :309-310): the remaining steps would be trimmed by the caller anyway.  sStop was written before the barrier that closed the previous step.
     if (sStop) break;
     // ---- query_fc1 pre-activation: c0 (+ c1 + M e1 from step 1 on)
     float pre[NR];
@@ -236,7 +236,11 @@ __global__ void __launch_bounds__(256, 1) su_sample_kernel(const SuSampleDev p) 
       const bool hit = (long long)idx == en_w;
       if (hit && !ended) {
         num = step + 1; steps_row = step + 1;
-        if (lane == 0 && p.ended_rows) atomicAdd(p.ended_rows, 1);
+        if (lane == 0 && p.ended_rows) {                 // latest end step first, then the count that publishes it
+          atomicMax(p.ended_rows + 1, step + 1);
+          __threadfence();
+          atomicAdd(p.ended_rows, 1);
+        }
       }
       ended |= hit ? 1 : 0;
       if (!ended) {
@@ -256,7 +260,14 @@ __global__ void __launch_bounds__(256, 1) su_sample_kernel(const SuSampleDev p) 
         sLm[r][idx >> 5] &= ~(1u << (idx & 31));                            // a picked unit is masked afterwards
       }
     }
-    if (tid == 0 && p.ended_rows) sStop = *reinterpret_cast<volatile int*>(p.ended_rows) >= p.R;
+    if (tid == 0 && p.ended_rows) {
+      // CTAs are not in step with each other: stop only when every row has ended AND this CTA has computed as many
+      // steps as the latest of them needed (the caller keeps steps [0, max steps_row) of EVERY row)
+      const int cnt = *reinterpret_cast<volatile int*>(p.ended_rows);
+      __threadfence();
+      const int last = *reinterpret_cast<volatile int*>(p.ended_rows + 1);
+      sStop = cnt >= p.R && step + 1 >= last;
+    }
     __syncthreads();
   }
 

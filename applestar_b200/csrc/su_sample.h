@@ -17,7 +17,8 @@ typedef struct as_su_sample_args {
   float* extra;
   float* emb;
   int* steps_row;
-  int* ended_rows;   /* device int, 0 at launch, or NULL: rows that have raised their end flag; when it reaches R every CTA leaves the loop */
+  int* ended_rows;   /* two device ints, 0 at launch, or NULL: [0] rows that have raised their end flag, [1] the latest end step;
+                        once [0] == R a CTA leaves its loop as soon as it has computed [1] steps */
   int R, N1, S, extra_units;
   float temperature;
 } as_su_sample_args;
@@ -48,7 +49,7 @@ struct SuSampleDev {
   float* extra;                // [R, N1]
   float* emb;                  // [R, 32]  mean of the picked keys after the last step
   int* steps_row;              // [R]      1 + step at which the row raised its end flag (0: started ended, S: never)
-  int* ended_rows;             // device counter (0 at launch) of rows whose end flag is up, or nullptr (always S steps)
+  int* ended_rows;             // [2] device ints, 0 at launch: ended rows, latest end step; or nullptr (always S steps)
   int R, N1, S, extra_units;
   float temperature;
 };

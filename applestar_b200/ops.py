@@ -589,7 +589,7 @@ def selected_units_sample(head, key, ae0, entity_num, su_mask, noise, temperatur
     extra = torch.empty(R, N1, device=dev)
     emb = torch.empty(R, D, device=dev)
     steps_row = torch.empty(R, dtype=torch.int32, device=dev)
-    ended_rows = torch.zeros(1, dtype=torch.int32, device=dev)          # all R rows ended -> every CTA stops stepping
+    ended_rows = torch.zeros(2, dtype=torch.int32, device=dev)          # [ended rows, latest end step]: early loop exit
     li, lh, lc = cell.layernorm_i, cell.layernorm_h, cell.layernorm_c
     a = _lib.AsSuSampleArgs()
     for name, t in (('key', key), ('c0', c0), ('c1', w['c1']), ('mt', w['mt']), ('wf1t', w['wf1t']), ('bf1', w['bf1']),

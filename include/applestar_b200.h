@@ -442,7 +442,8 @@ typedef struct as_su_sample_args {
   float* extra;
   float* emb;
   int* steps_row;
-  int* ended_rows;   /* device int, 0 at launch, or NULL: rows that have raised their end flag; when it reaches R every CTA leaves the loop */
+  int* ended_rows;   /* two device ints, 0 at launch, or NULL: [0] rows that have raised their end flag, [1] the latest end step;
+                        once [0] == R a CTA leaves its loop as soon as it has computed [1] steps */
   int R, N1, S, extra_units;
   float temperature;
 } as_su_sample_args;
