@@ -339,3 +339,41 @@ def test_selected_units_batched_matches_step_loop():
     for x, y in zip(a[2:], b[2:]):
         fin = ~(torch.isnan(x) | torch.isnan(y))
         assert (x[fin] - y[fin]).abs().max().item() < 0.08 * y[fin].abs().max().item() + 1e-3
+
+
+@gpu
+def test_su_sample_rows_ending_at_very_different_steps():
+    """The sampling kernel leaves its loop early once EVERY row of the batch has ended.  CTAs (1-2 rows each) are not in
+    step with each other, so the condition must hold per CTA: here most rows end at steps 0-3 and one row at step 40;
+    every row must still carry the reference's logits / picks for all 41 steps (bit-exact picks vs the oracle loop)."""
+    from applestar_b200 import ops
+    from applestar_b200.model import SelectedUnitsHead
+    torch.manual_seed(12)
+    head = SelectedUnitsHead(True).cuda()
+    with torch.no_grad():
+        for prm in head.lstm.parameters():
+            if prm.dim() == 2:
+                prm.mul_(0.3)
+    sd = {'policy.selected_units_head.' + k: v.detach().cpu() for k, v in head.state_dict().items()}
+    R, N = 301, 128                                       # > 148 rows: two rows per CTA
+    ent = torch.randn(R, N, 256) * 0.5
+    en = torch.randint(60, N + 1, (R,))
+    su_mask = torch.ones(R, dtype=torch.bool)
+    su_mask[5] = False
+    ae0 = torch.randn(R, 1024) * 0.3
+    noise = synth.gen_gumbel(R, 33, N)['selected_units']          # [S, R, N + 1]
+    end_step = torch.randint(0, 4, (R,))
+    end_step[137] = 40
+    for r in range(R):
+        noise[:, r, int(en[r])] = -1e4                            # never the end token ...
+        noise[int(end_step[r]) + 1, r, int(en[r])] = 1e4          # ... except at its step (the token is selectable from step 1)
+    ref_logits, ref_units, _, ref_num, ref_extra = R_.su_head_sample(sd, ae0, ent, en, su_mask, noise, 1.0, True)
+    key, _ = R_.su_keys(sd, ent, en)
+    with torch.no_grad():
+        logits, units, _, num, extra = ops.selected_units_sample(head, key.cuda(), ae0.cuda(), en.cuda(), su_mask.cuda(),
+                                                                 noise.cuda(), 1.0, True)
+    assert int(ref_num.max()) == 42 and logits.shape == ref_logits.shape
+    assert torch.equal(units.cpu(), ref_units) and torch.equal(num.cpu(), ref_num) and torch.equal(extra.cpu(), ref_extra)
+    masked = ref_logits < -1e8
+    assert torch.equal(logits.cpu() < -1e8, masked)
+    assert (logits.cpu() - ref_logits)[~masked].abs().max().item() < 2e-3
