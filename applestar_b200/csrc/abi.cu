@@ -132,6 +132,7 @@ const Knobs& knobs() {
     v.slab_mc = getenv("AS_SLAB_MC") != nullptr;       // CTA-pair weight multicast (this GPU's own weight buffer only); slower, off
     v.slab_no_halfk = getenv("AS_SLAB_NO_HALFK") != nullptr;
     v.debug_tmap = getenv("AS_DEBUG_TMAP") != nullptr;
+    v.no_plain_epilogue = getenv("AS_NO_PLAIN_EPILOGUE") != nullptr;
     const char* e = getenv("AS_SLAB_BSLOTS");
     v.slab_bslots = e ? atoi(e) : 0;
     return v;

@@ -242,7 +242,7 @@ __device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr, uin
 // Diagnostic switches (environment variables AS_*), read ONCE when the library is first used and immutable afterwards:
 // no entry point consults the environment per call.
 struct Knobs {
-  bool wgrad_no_pair, wgrad_no_slab, slab_no_resident, slab_mc, slab_no_halfk, debug_tmap;
+  bool wgrad_no_pair, wgrad_no_slab, slab_no_resident, slab_mc, slab_no_halfk, debug_tmap, no_plain_epilogue;
   int slab_bslots;
 };
 const Knobs& knobs();

@@ -70,6 +70,7 @@ struct GemmDev {
   float alpha;
   float* ws;  // split-K partials
   int tma_store;   // 1: C (and C2) are written with TMA bulk stores from a swizzled staging tile
+  int plain;  // host: 1 = no addend / mask / sign bits / border / diagnostics and the TMA-store epilogue (EPI 1), 2 = sign bits only (EPI 2)
   int debug;  // diagnostics: 1 = epilogue skips global stores, 2 = epilogue only drains TMEM
 };
 
@@ -89,12 +90,18 @@ struct SmemLayout {
   static constexpr int kTotal = kRingBytes + kBarBytes + kStgBytes + 1024;   // +1024 alignment slack
 };
 
-template <int BN, bool A_MN, bool B_MN>
+// EPI 1 (plain): the epilogue of the TMA-store path is compiled without the side inputs (addend, ReLU masks / sign bits,
+// image border, diagnostics); EPI 2: the same, but with the sign-bit input / output.  The K = 256 GEMMs of the
+// Transformer are bound by their epilogue's instruction stream, and every runtime test of an option that is off costs
+// them issue slots (measured: -10 % on the qkv / FFN forward GEMMs).  EPI 0: everything, decided at run time.
+template <int BN, bool A_MN, bool B_MN, int EPI = 0>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2,
             const __grid_constant__ CUtensorMap tmB2, const GemmDev p) {
   using L = SmemLayout<BN>;
+  constexpr bool PLAIN = EPI != 0;          // no addend / bf16 mask / border / diagnostics
+  constexpr bool NOBITS = EPI == 1;         // ... and no sign bits either
   constexpr int kStages = L::kStages;
   // accumulator ring in TMEM: narrow tiles have few k-blocks per tile, so the MMA issuer may run up to 8 tiles ahead
   // of the epilogue; for BN < 128 the two epilogue warp sets also alternate tiles instead of splitting columns
@@ -435,7 +442,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         uint8_t* sbuf = bar_base + L::kBarBytes + e * 4096;
         const int grow = row_base + lane;
         bool border = false;
-        if (p.img_w > 0) {
+        if (!PLAIN && p.img_w > 0) {
           const int q = grow % (p.img_w * p.img_h);
           const int yy = q / p.img_w, xx = q - yy * p.img_w;
           border = (yy == 0) | (yy == p.img_h - 1) | (xx == 0) | (xx == p.img_w - 1);
@@ -474,7 +481,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = fmaf(__uint_as_float(v[j]), p.alpha, __shfl_sync(0xffffffffu, bl, j));
           }
-          if (p.resid != nullptr && grow < p.M && gc + 32 <= p.N) {
+          if (!PLAIN && p.resid != nullptr && grow < p.M && gc + 32 <= p.N) {
             // residual / second gradient contribution with C's layout: this lane's 32 columns are 64 contiguous bytes
             const uint4* r4 = reinterpret_cast<const uint4*>(p.resid + (long long)b0 * p.c_sb0 + (long long)b1 * p.c_sb1 +
                                                              (long long)grow * p.ldc + gc);
@@ -489,7 +496,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               }
             }
           }
-          if (p.mask != nullptr && grow < p.M && gc + 32 <= p.N) {
+          if (!PLAIN && p.mask != nullptr && grow < p.M && gc + 32 <= p.N) {
             // ReLU backward of the layer whose output `mask` is: keep the gradient where that output was positive
             const uint4* m4 = reinterpret_cast<const uint4*>(p.mask + (long long)b0 * p.c_sb0 + (long long)b1 * p.c_sb1 +
                                                              (long long)grow * p.ldc + gc);
@@ -505,7 +512,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               }
             }
           }
-          if (p.bits_in != nullptr) {
+          if (!NOBITS && p.bits_in != nullptr) {
             // sign bits of the layer whose ReLU this gradient passes: columns 2k / 2k+1 of the chunk are bits 15-k / 31-k
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = (bw >> (((j & 1) ? 31 : 15) - (j >> 1)) & 1u) ? f[j] : 0.f;
@@ -514,22 +521,22 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
           }
-          if (p.img_w > 0) {
+          if (!PLAIN && p.img_w > 0) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = border ? 0.f : f[j];
           }
         };
         auto stage32 = [&](const float (&f)[32], int c) {
-          if (p.debug >= 4) return;
+          if (!PLAIN && p.debug >= 4) return;
           if (lane == 0) tma_store_wait_read();                       // previous box has left the staging tile
           __syncwarp();
 #pragma unroll
           for (int j = 0; j < 8; ++j)
             *reinterpret_cast<float4*>(sbuf + lane * 128 + ((j ^ (lane & 7)) << 4)) =
                 make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
-          if (p.debug < 3) fence_proxy_async_smem();
+          if (PLAIN || p.debug < 3) fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0 && p.debug == 0 && row_base < p.M) {
+          if (lane == 0 && (PLAIN || p.debug == 0) && row_base < p.M) {
             tma_store_4d(&tmC, sbuf, n0 + c, row_base, b0, b1);
             tma_store_commit();
           }
@@ -539,13 +546,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         for (int col = col_begin; col < col_end; col += 64) {
           const bool has0 = n0 + col < p.N, has1 = (col + 32 < col_end) && (n0 + col + 32 < p.N);   // warp-uniform
           uint32_t bw0 = 0xffffffffu, bw1 = 0xffffffffu;          // requested before the wait for the accumulator columns
-          if (p.bits_in != nullptr && grow < p.M) {
+          if (!NOBITS && p.bits_in != nullptr && grow < p.M) {
             const uint32_t* brow = p.bits_in + (long long)grow * (p.N >> 5) + ((n0 + col) >> 5);
             if (has0) bw0 = __ldg(brow);
             if (has1) bw1 = __ldg(brow + 1);
           }
           tmem_ld_wait();
-          if (p.debug == 2 || !has0) { issue(col + 64); continue; }
+          if ((!PLAIN && p.debug == 2) || !has0) { issue(col + 64); continue; }
           uint32_t packed[32];
           if (!f32_out) {
             float f[32];
@@ -564,7 +571,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               }
             }
             issue(col + 64);
-            if (p.bits_out != nullptr && grow < p.M) {
+            if (!NOBITS && p.bits_out != nullptr && grow < p.M) {
               // a relu output half-word is positive iff adding 0x7fff carries into its top bit; pair k of a 32-column
               // chunk lands on bits 15-k (even column) and 31-k (odd column)
               uint32_t w0 = 0u, w1 = 0u;
@@ -601,7 +608,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
             issue(col + 64);
           }
-          if (need_bf16 && p.debug < 4) {
+          if (need_bf16 && (PLAIN || p.debug < 4)) {
             if (lane == 0) tma_store_wait_read();
             __syncwarp();
 #pragma unroll
@@ -610,9 +617,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 *reinterpret_cast<uint4*>(sbuf + lane * 128 + ((j ^ (lane & 7)) << 4)) =
                     make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
             }
-            if (p.debug < 3) fence_proxy_async_smem();
+            if (PLAIN || p.debug < 3) fence_proxy_async_smem();
             __syncwarp();
-            if (lane == 0 && p.debug == 0 && row_base < p.M) {
+            if (lane == 0 && (PLAIN || p.debug == 0) && row_base < p.M) {
               tma_store_4d(map16, sbuf, n0 + col, row_base, b0, b1);
               tma_store_commit();
             }
@@ -814,12 +821,12 @@ int make_map_bf16(CUtensorMap* tm, const void* ptr, long long inner, long long r
 }
 int gemm_num_sms() { return num_sms(); }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, int EPI = 0>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const CUtensorMap& tc2,
                   const CUtensorMap& tb2, const GemmDev& p, cudaStream_t st) {
   using L = SmemLayout<BN>;
   static bool attr_set = false;
-  auto kern = gemm_kernel<BN, A_MN, B_MN>;
+  auto kern = gemm_kernel<BN, A_MN, B_MN, EPI>;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
     if (e != cudaSuccess) return (int)e;
@@ -854,6 +861,16 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMa
 template <int BN>
 static int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
                           const CUtensorMap& tc2, const CUtensorMap& tb2, const GemmDev& p, cudaStream_t st) {
+  if constexpr (BN >= 128) {
+    // row-major A with a plain epilogue: the Transformer's forward / data-gradient GEMMs
+    if (p.plain == 1 && !a_mn && !b_mn) return launch<BN, false, false, 1>(ta, tb, tc, tc2, tb2, p, st);
+    if (p.plain == 1 && !a_mn && b_mn) return launch<BN, false, true, 1>(ta, tb, tc, tc2, tb2, p, st);
+  }
+  if constexpr (BN == 256) {
+    // the FFN pair: forward GEMM that writes ReLU sign bits, data-gradient GEMM that masks from them
+    if (p.plain == 2 && !a_mn && !b_mn) return launch<BN, false, false, 2>(ta, tb, tc, tc2, tb2, p, st);
+    if (p.plain == 2 && !a_mn && b_mn) return launch<BN, false, true, 2>(ta, tb, tc, tc2, tb2, p, st);
+  }
   if (!a_mn && !b_mn) return launch<BN, false, false>(ta, tb, tc, tc2, tb2, p, st);
   if (!a_mn && b_mn) return launch<BN, false, true>(ta, tb, tc, tc2, tb2, p, st);
   if (a_mn && !b_mn) return launch<BN, true, false>(ta, tb, tc, tc2, tb2, p, st);
@@ -994,6 +1011,10 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
   if (g.mask != nullptr && (!p.tma_store || (g.N % 32) != 0 || (g.ldc % 8) != 0 ||
                             (reinterpret_cast<uintptr_t>(g.mask) & 15) != 0))
     return AS_EUNSUPPORTED;
+  p.plain = 0;
+  if (p.tma_store && !p.slab && g.resid == nullptr && g.mask == nullptr && g.img_w <= 0 && g_gemm_debug == 0 &&
+      !knobs().no_plain_epilogue)
+    p.plain = (g.bits_in == nullptr && g.bits_out == nullptr) ? 1 : 2;
   switch (BN) {
     case 32: return dispatch_major<32>(g.a_mn, g.b_mn, ta, tb, tc, tc2, tb2, p, st);
     case 64: return dispatch_major<64>(g.a_mn, g.b_mn, ta, tb, tc, tc2, tb2, p, st);
