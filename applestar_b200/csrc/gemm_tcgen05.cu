@@ -91,7 +91,7 @@ struct SmemLayout {
 };
 
 // EPI 1 (plain): the epilogue of the TMA-store path is compiled without the side inputs (addend, ReLU masks / sign bits,
-// image border, diagnostics); EPI 2: the same, but with the sign-bit input / output.  The K = 256 GEMMs of the
+// diagnostics); EPI 2: the same, but with the sign-bit input / output.  The K = 256 GEMMs of the
 // Transformer are bound by their epilogue's instruction stream, and every runtime test of an option that is off costs
 // them issue slots (measured: -10 % on the qkv / FFN forward GEMMs).  EPI 0: everything, decided at run time.
 template <int BN, bool A_MN, bool B_MN, int EPI = 0>
@@ -100,7 +100,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2,
             const __grid_constant__ CUtensorMap tmB2, const GemmDev p) {
   using L = SmemLayout<BN>;
-  constexpr bool PLAIN = EPI != 0;          // no addend / bf16 mask / border / diagnostics
+  constexpr bool PLAIN = EPI != 0;          // no addend / bf16 mask / diagnostics
   constexpr bool NOBITS = EPI == 1;         // ... and no sign bits either
   constexpr int kStages = L::kStages;
   // accumulator ring in TMEM: narrow tiles have few k-blocks per tile, so the MMA issuer may run up to 8 tiles ahead
@@ -442,7 +442,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         uint8_t* sbuf = bar_base + L::kBarBytes + e * 4096;
         const int grow = row_base + lane;
         bool border = false;
-        if (!PLAIN && p.img_w > 0) {
+        if (p.img_w > 0) {
           const int q = grow % (p.img_w * p.img_h);
           const int yy = q / p.img_w, xx = q - yy * p.img_w;
           border = (yy == 0) | (yy == p.img_h - 1) | (xx == 0) | (xx == p.img_w - 1);
@@ -521,7 +521,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
           }
-          if (!PLAIN && p.img_w > 0) {
+          if (p.img_w > 0) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = border ? 0.f : f[j];
           }
@@ -866,9 +866,11 @@ static int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUt
     if (p.plain == 1 && !a_mn && !b_mn) return launch<BN, false, false, 1>(ta, tb, tc, tc2, tb2, p, st);
     if (p.plain == 1 && !a_mn && b_mn) return launch<BN, false, true, 1>(ta, tb, tc, tc2, tb2, p, st);
   }
-  if constexpr (BN == 256) {
-    // the FFN pair: forward GEMM that writes ReLU sign bits, data-gradient GEMM that masks from them
+  if constexpr (BN >= 128) {
+    // sign bits: the FFN pair (forward GEMM that writes them, data-gradient GEMM that masks from them) and the conv chains
     if (p.plain == 2 && !a_mn && !b_mn) return launch<BN, false, false, 2>(ta, tb, tc, tc2, tb2, p, st);
+  }
+  if constexpr (BN == 256) {
     if (p.plain == 2 && !a_mn && b_mn) return launch<BN, false, true, 2>(ta, tb, tc, tc2, tb2, p, st);
   }
   if (!a_mn && !b_mn) return launch<BN, false, false>(ta, tb, tc, tc2, tb2, p, st);
@@ -1012,8 +1014,7 @@ int gemm_run(const GemmCall& g, cudaStream_t st) {
                             (reinterpret_cast<uintptr_t>(g.mask) & 15) != 0))
     return AS_EUNSUPPORTED;
   p.plain = 0;
-  if (p.tma_store && !p.slab && g.resid == nullptr && g.mask == nullptr && g.img_w <= 0 && g_gemm_debug == 0 &&
-      !knobs().no_plain_epilogue)
+  if (p.tma_store && g.resid == nullptr && g.mask == nullptr && g_gemm_debug == 0 && !knobs().no_plain_epilogue)
     p.plain = (g.bits_in == nullptr && g.bits_out == nullptr) ? 1 : 2;
   switch (BN) {
     case 32: return dispatch_major<32>(g.a_mn, g.b_mn, ta, tb, tc, tc2, tb2, p, st);
