@@ -134,6 +134,14 @@ int relu_bwd(const void* dy, const void* y, void* dz, long long n, cudaStream_t 
   return AS_OK;
 }
 
+// MUFU versions for the gate math: the results are rounded to bf16 (2^-9) right away, the approximations are ~2^-11
+__device__ __forceinline__ float gate_tanh(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float gate_sigmoid(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
+
 // GatedResBlock tail (module_utils.py:227-229): y = relu(tanh(r * sigmoid(g)) * sp + x)
 __global__ void gated_fwd_kernel(const uint4* __restrict__ r, const uint4* __restrict__ g, const uint4* __restrict__ x,
                                  const float* __restrict__ sp, uint4* __restrict__ y, long long n8) {
@@ -144,8 +152,8 @@ __global__ void gated_fwd_kernel(const uint4* __restrict__ r, const uint4* __res
     vr.u = __ldg(r + i); vg.u = __ldg(g + i); vx.u = __ldg(x + i);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float sg = 1.f / (1.f + expf(-bf2f(vg.h[j])));
-      const float t = tanhf(bf2f(vr.h[j]) * sg);
+      const float sg = gate_sigmoid(bf2f(vg.h[j]));
+      const float t = gate_tanh(bf2f(vr.h[j]) * sg);
       vy.h[j] = f2bf(fmaxf(t * s + bf2f(vx.h[j]), 0.f));
     }
     y[i] = vy.u;
@@ -166,8 +174,8 @@ __global__ void gated_bwd_kernel(const uint4* __restrict__ dy, const uint4* __re
     for (int j = 0; j < 8; ++j) {
       const float dz = bf2f(vy.h[j]) > 0.f ? bf2f(vd.h[j]) : 0.f;
       const float rv = bf2f(vr.h[j]);
-      const float sg = 1.f / (1.f + expf(-bf2f(vg.h[j])));
-      const float t = tanhf(rv * sg);
+      const float sg = gate_sigmoid(bf2f(vg.h[j]));
+      const float t = gate_tanh(rv * sg);
       acc += dz * t;
       const float du = dz * s * (1.f - t * t);
       odr.h[j] = f2bf(du * sg);
