@@ -226,3 +226,58 @@ def test_value_encoder_path_matches_reference():
     mine = Model({'model': {'enable_baselines': ['winloss']}, 'learner': {'use_value_feature': True}}, use_value_network=True)
     assert {k: tuple(v.shape) for k, v in mine.state_dict().items()} == {k: tuple(s) for k, s, _ in spec}
     assert {k for k, p in mine.named_parameters() if p.requires_grad} == {k for k, _, t in spec if t}
+
+
+@reference
+def test_actor_copy_helpers_match_reference(ref_model):
+    """actor_batch.copy_input_data / copy_output_data against the reference's own functions (agent.py:37-89) on CPU
+    tensors: same bytes land in the shared buffers."""
+    try:
+        from distar.agent.default import agent as ref_agent
+    except Exception as exc:                              # pragma: no cover
+        pytest.skip('reference agent not importable in this container: %r' % exc)
+    from applestar_b200 import actor_batch, synth
+    E, N = 3, 64
+    data = synth.gen_trajectories(1, E, N, 5, special=True)
+    obs = {k: synth.tree_map(lambda t: t[:E], data[k]) for k in ('spatial_info', 'entity_info', 'scalar_info')}
+    en, sun = data['entity_num'][:E], data['selected_units_num'][0]
+    hs = [(h[:E], c[:E]) for h, c in data['hidden_state']]
+    act = {k: v[0] for k, v in data['action_info'].items()}
+    full = dict(obs, entity_num=en, hidden_state=hs, action_info=act, selected_units_num=sun)
+
+    def fresh():
+        return synth.tree_map(lambda t: torch.zeros_like(t), full)
+    mine, theirs = fresh(), fresh()
+    for idx in (0, 2):
+        step = {'entity_num': en[idx], 'selected_units_num': sun[idx],
+                'hidden_state': [(h[idx], c[idx]) for h, c in hs],
+                'spatial_info': {k: v[idx] for k, v in obs['spatial_info'].items()},
+                'scalar_info': {k: v[idx] for k, v in obs['scalar_info'].items()},
+                'entity_info': {k: v[idx, :int(en[idx])] for k, v in obs['entity_info'].items()},
+                'action_info': {k: (v[idx, :int(sun[idx])] if k == 'selected_units' else v[idx]) for k, v in act.items()}}
+        actor_batch.copy_input_data(mine, step, idx)
+        ref_agent.copy_input_data(theirs, step, idx)
+    flat_a, flat_b = [], []
+    synth.tree_map(lambda t: flat_a.append(t) or t, mine)
+    synth.tree_map(lambda t: flat_b.append(t) or t, theirs)
+    assert len(flat_a) == len(flat_b) and all(torch.equal(a, b) for a, b in zip(flat_a, flat_b))
+    # outputs: rows 0 and 2 of a fake model output into shared output buffers
+    g = torch.Generator().manual_seed(2)
+    out = {'logit': {'action_type': torch.randn(E, 327, generator=g), 'selected_units': torch.randn(E, 5, N + 1, generator=g)},
+           'action_info': {'action_type': torch.randint(0, 327, (E,), generator=g), 'selected_units': torch.randint(0, N, (E, 5), generator=g)},
+           'selected_units_num': torch.randint(0, 5, (E,), generator=g),
+           'hidden_state': [(torch.randn(E, 384, generator=g), torch.randn(E, 384, generator=g)) for _ in range(3)]}
+
+    def out_buffers():
+        return {'logit': {'action_type': torch.zeros(E, 327), 'selected_units': torch.zeros(E, 64, N + 1)},
+                'action_info': {'action_type': torch.zeros(E, dtype=torch.int64), 'selected_units': torch.zeros(E, 64, dtype=torch.int64)},
+                'selected_units_num': torch.zeros(E, dtype=torch.int64),
+                'hidden_state': [(torch.zeros(E, 384), torch.zeros(E, 384)) for _ in range(3)]}
+    a, b = out_buffers(), out_buffers()
+    rows = torch.tensor([True, False, True])
+    actor_batch.copy_output_data(a, out, rows)
+    ref_agent.copy_output_data(b, out, rows)
+    flat_a, flat_b = [], []
+    synth.tree_map(lambda t: flat_a.append(t) or t, a)
+    synth.tree_map(lambda t: flat_b.append(t) or t, b)
+    assert all(torch.equal(x, y) for x, y in zip(flat_a, flat_b))
