@@ -366,6 +366,7 @@ class LearnerStep:
     def __init__(self, model, loss, lr=1e-5, max_norm=1.0, bucket_mb=25.0, use_graph=True):
         self.model = model
         self.loss = loss
+        bucket_mb = float(os.environ.get('APPLESTAR_BUCKET_MB', bucket_mb))       # measurement knob (bucket size of the gradient all-reduce)
         self.dist_model = DistModule(model, bucket_mb=bucket_mb)
         self.flat = self.dist_model.flat
         self.optimizer = FusedAdam(self.flat, lr=lr, max_norm=max_norm)
