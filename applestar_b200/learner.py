@@ -254,7 +254,15 @@ class DistModule(nn.Module):
 
 
 class FusedAdam:
-    """clip_grad_norm_(max_norm) + Adam(lr, betas=(0, 0.99), eps=1e-5) as two kernels over the flat buffers."""
+    """clip_grad_norm_(max_norm) + Adam(lr, betas=(0, 0.99), eps=1e-5) as two kernels over the flat buffers
+    (reference: rl_learner.py:73-80,125,132 + grad_clip.py:140-143).
+
+    One difference from torch.optim.Adam, which skips parameters whose `.grad` is None: a parameter that received no
+    gradient in a step is packed as zeros and updated like every other element, i.e. its second moment decays and
+    the shared step counter advances for it.  With betas = (0, 0.99) a zero gradient moves no weight (m = 0); it only
+    matters for the bias correction of a parameter that is frozen for a while and trained later (`only_update_baseline`
+    switches: the value towers then see slightly smaller first updates than under torch Adam).  `state_dict` /
+    `load_state_dict` carry m, v and the step counter."""
 
     def __init__(self, flat, lr=1e-5, betas=(0.0, 0.99), eps=1e-5, weight_decay=0.0, max_norm=1.0):
         self.flat, self.lr, self.betas, self.eps, self.wd, self.max_norm = flat, lr, betas, eps, weight_decay, max_norm
