@@ -259,9 +259,12 @@ class FusedAdam:
 
     One difference from torch.optim.Adam, which skips parameters whose `.grad` is None: a parameter that received no
     gradient in a step is packed as zeros and updated like every other element, i.e. its second moment decays and
-    the shared step counter advances for it.  With betas = (0, 0.99) a zero gradient moves no weight (m = 0); it only
-    matters for the bias correction of a parameter that is frozen for a while and trained later (`only_update_baseline`
-    switches: the value towers then see slightly smaller first updates than under torch Adam).  `state_dict` /
+    the shared step counter advances for it.  With betas = (0, 0.99) a zero gradient moves no weight (m = 0); it
+    matters for a parameter that is frozen for a while and trained later (the policy after an `only_update_baseline`
+    phase, rl_learner.py:149-161): torch Adam would start its bias correction at that parameter's own first step,
+    here bc2 is already ~1, so its first updates are larger (up to 1 / sqrt(1 - beta2) = 10x for the very first one,
+    back to normal after ~1 / (1 - beta2) = 100 steps).  Callers that need the reference behaviour there keep the
+    reference's own torch optimizer on the DistModule-wrapped model.  `state_dict` /
     `load_state_dict` carry m, v and the step counter."""
 
     def __init__(self, flat, lr=1e-5, betas=(0.0, 0.99), eps=1e-5, weight_decay=0.0, max_norm=1.0):
