@@ -172,6 +172,9 @@ _SIGS = {
     'as_debug_lstm_profile': (c_int, [c_void_p]),
     'as_debug_lstm_max_clusters': (c_int, [c_int]),
     'as_clip_adam_scratch_bytes': (c_int64, []),
+    'as_clip_adam_per_param': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_float, c_float,
+                                       c_float, c_float, c_float, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
+                                       c_void_p]),
     'as_clip_adam': (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_float, c_float,
                              c_float, c_float, c_float, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
 }

@@ -27,6 +27,8 @@ int gumbel_argmax(const float*, const float*, long long*, long long, int, cudaSt
 int loss_forward(const AsLossArgs&, cudaStream_t);
 int loss_backward(const AsLossArgs&, float, cudaStream_t);
 long long clip_adam_scratch_bytes();
+int clip_adam_per_param(float*, const float*, float*, float*, void*, long long, float, float, float, float, float, float,
+                        const unsigned short*, const int*, int*, int, int*, float*, float*, cudaStream_t);
 int clip_adam(float*, const float*, float*, float*, void*, long long, float, float, float, float, float, float, int,
               int*, float*, float*, cudaStream_t);
 int layer_norm_fwd(const float*, const float*, const float*, const float*, float*, void*, float*, long long, int, int,
@@ -686,6 +688,14 @@ int as_clip_adam(float* p, const float* g, float* m, float* v, void* shadow, int
                  float* norm_out, void* stream) {
   return as::clip_adam(p, g, m, v, shadow, n, max_norm, lr, beta1, beta2, eps, weight_decay, step, step_dev, scratch,
                        norm_out, ST(stream));
+}
+
+int as_clip_adam_per_param(float* p, const float* g, float* m, float* v, void* shadow, int64_t n, float max_norm, float lr,
+                           float beta1, float beta2, float eps, float weight_decay, const uint16_t* block_param,
+                           const int32_t* param_active, int32_t* param_step, int n_params, int* step_dev, float* scratch,
+                           float* norm_out, void* stream) {
+  return as::clip_adam_per_param(p, g, m, v, shadow, n, max_norm, lr, beta1, beta2, eps, weight_decay, block_param, param_active,
+                                 param_step, n_params, step_dev, scratch, norm_out, ST(stream));
 }
 
 }  // extern "C"

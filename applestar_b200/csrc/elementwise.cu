@@ -171,7 +171,12 @@ __global__ void clip_adam_kernel(float* __restrict__ p, const float* __restrict_
                                  float* __restrict__ v, __nv_bfloat16* __restrict__ shadow, long long n,
                                  const float* __restrict__ partial, int n_partial, float max_norm, float lr,
                                  float beta1, float beta2, float eps, float wd, float bc1, float bc2,
-                                 const int* __restrict__ step_dev, float* __restrict__ norm_out) {
+                                 const int* __restrict__ step_dev, float* __restrict__ norm_out,
+                                 const unsigned short* __restrict__ blk_param, const int* __restrict__ p_active,
+                                 const int* __restrict__ p_step) {
+  // blk_param != nullptr: torch.optim.Adam semantics per parameter tensor -- element i belongs to parameter
+  // blk_param[i / 8] (tensors start at multiples of 8 elements); a parameter without a gradient this step
+  // (p_active == 0) is left untouched, the others use their OWN step count p_step[p] + 1 for the bias corrections.
   __shared__ float s_clip;
   if (step_dev != nullptr) {                      // bias corrections from the device counter
     const float t = (float)(*step_dev);
@@ -197,11 +202,25 @@ __global__ void clip_adam_kernel(float* __restrict__ p, const float* __restrict_
     vi = beta2 * vi + (1.f - beta2) * gi * gi;
     pi -= lr * (mi / bc1) / (sqrtf(vi / bc2) + eps);
   };
+  int last_p = -1;
+  bool on = true;
+  auto select = [&](long long blk) {                  // per-parameter mode: activity and bias corrections of this block
+    const int pp = blk_param[blk];
+    if (pp != last_p) {
+      last_p = pp;
+      on = p_active[pp] != 0;
+      const float t = (float)(p_step[pp] + 1);
+      bc1 = 1.f - powf(beta1, t);
+      bc2 = 1.f - powf(beta2, t);
+    }
+    return on;
+  };
   // 16-byte accesses when the four streams allow it (the flat buffers of learner.FlatParams are 32-byte aligned)
   const bool vec = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m) |
                      reinterpret_cast<uintptr_t>(v)) & 15) == 0 && (shadow == nullptr || (reinterpret_cast<uintptr_t>(shadow) & 7) == 0);
   const long long n4 = vec ? n / 4 : 0;
   for (long long i = tid; i < n4; i += stride) {
+    if (blk_param != nullptr && !select(i >> 1)) continue;
     const float4 g4 = reinterpret_cast<const float4*>(g)[i];
     float4 p4 = reinterpret_cast<float4*>(p)[i], m4 = reinterpret_cast<float4*>(m)[i], v4 = reinterpret_cast<float4*>(v)[i];
     update(g4.x, p4.x, m4.x, v4.x); update(g4.y, p4.y, m4.y, v4.y); update(g4.z, p4.z, m4.z, v4.z); update(g4.w, p4.w, m4.w, v4.w);
@@ -214,6 +233,7 @@ __global__ void clip_adam_kernel(float* __restrict__ p, const float* __restrict_
     }
   }
   for (long long i = n4 * 4 + tid; i < n; i += stride) {
+    if (blk_param != nullptr && !select(i >> 3)) continue;
     float pi = p[i], mi = m[i], vi = v[i];
     update(g[i], pi, mi, vi);
     m[i] = mi; v[i] = vi; p[i] = pi;
@@ -236,7 +256,29 @@ int clip_adam(float* p, const float* g, float* m, float* v, void* shadow, long l
   const float bc1 = 1.f - powf(beta1, (float)(step > 0 ? step : 1)), bc2 = 1.f - powf(beta2, (float)(step > 0 ? step : 1));
   clip_adam_kernel<<<kAdamBlocks, 256, 0, st>>>(p, g, m, v, reinterpret_cast<__nv_bfloat16*>(shadow), n, scratch,
                                                 kAdamBlocks, max_norm, lr, beta1, beta2, eps, wd, bc1, bc2, step_dev,
-                                                norm_out);
+                                                norm_out, nullptr, nullptr, nullptr);
+  AS_LAUNCH_CHECK();
+  return AS_OK;
+}
+
+__global__ void adam_bump_steps_kernel(const int* __restrict__ p_active, int* __restrict__ p_step, int n_params) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_params && p_active[i] != 0) p_step[i] += 1;
+}
+
+int clip_adam_per_param(float* p, const float* g, float* m, float* v, void* shadow, long long n, float max_norm, float lr,
+                        float beta1, float beta2, float eps, float wd, const unsigned short* blk_param, const int* p_active,
+                        int* p_step, int n_params, int* step_dev, float* scratch, float* norm_out, cudaStream_t st) {
+  if (n <= 0) return AS_OK;
+  if (!p || !g || !m || !v || !scratch || !blk_param || !p_active || !p_step || n_params <= 0 || n_params > 65535) return AS_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(g) & 15) || (n % 8) != 0) return AS_EALIGN;
+  sumsq_partial_kernel<<<kAdamBlocks, 256, 0, st>>>(g, n, scratch, step_dev);
+  AS_LAUNCH_CHECK();
+  clip_adam_kernel<<<kAdamBlocks, 256, 0, st>>>(p, g, m, v, reinterpret_cast<__nv_bfloat16*>(shadow), n, scratch,
+                                                kAdamBlocks, max_norm, lr, beta1, beta2, eps, wd, 1.f, 1.f, nullptr,
+                                                norm_out, blk_param, p_active, p_step);
+  AS_LAUNCH_CHECK();
+  adam_bump_steps_kernel<<<(n_params + 255) / 256, 256, 0, st>>>(p_active, p_step, n_params);
   AS_LAUNCH_CHECK();
   return AS_OK;
 }

@@ -53,6 +53,18 @@ class FlatParams:
         # all-reduce bucket gathers them into the flat buffer (`pack`); CPU (gloo tests): gradients accumulate into views
         self.pack_mode = dev.type == 'cuda' and os.environ.get('APPLESTAR_GRAD_PACK', '1') != '0'
         self._pack_keep = []
+        # per-parameter optimizer bookkeeping (torch.optim.Adam skips a parameter whose .grad is None): which tensor an
+        # 8-element block of the flat buffer belongs to, and which tensors received a gradient in the current step
+        self.block_param = None
+        self.active = None
+        if self.pack_mode and len(self.params) < 65536:
+            bp = torch.empty(off // self.ALIGN, dtype=torch.int16)
+            for i, (p, o) in enumerate(zip(self.params, self.offsets)):
+                end = self.offsets[i + 1] if i + 1 < len(self.offsets) else off
+                bp[o // self.ALIGN:end // self.ALIGN] = i if i < 32768 else i - 65536
+            self.block_param = bp.to(dev)
+            self._active_host = torch.ones(len(self.params), dtype=torch.int32).pin_memory()
+            self.active = torch.ones(len(self.params), dtype=torch.int32, device=dev)
         self.refresh_shadow()
 
     def pack(self, idx=None):
@@ -62,6 +74,8 @@ class FlatParams:
         for i in (range(len(self.params)) if idx is None else idx):
             p, o, n = self.params[i], self.offsets[i], self.params[i].numel()
             g = p.grad
+            if self.active is not None:
+                self._active_host[i] = 0 if g is None else 1
             if g is not None and (g.dtype != torch.float32 or not g.is_contiguous()):
                 g = g.float().contiguous()
             if g is not None and g.data_ptr() == self.grad.data_ptr() + 4 * o:
@@ -87,7 +101,13 @@ class FlatParams:
             return
         host = torch.tensor(rows, dtype=torch.int64).pin_memory()
         table = host.to(self.grad.device, non_blocking=True)
-        if torch.cuda.is_current_stream_capturing():                # the captured copy re-reads `host` at every replay
+        capturing = torch.cuda.is_current_stream_capturing()
+        if self.active is not None:                                 # all buckets are packed before the optimizer runs
+            flags = self._active_host.clone().pin_memory() if capturing else self._active_host
+            self.active.copy_(flags, non_blocking=True)
+            if capturing:
+                self._pack_keep.append((flags,))
+        if capturing:                                               # the captured copy re-reads `host` at every replay
             self._pack_keep.append((host, table, keep))
         _lib.call('as_pack_f32', table.data_ptr(), len(rows), self.grad.data_ptr(), _lib.stream_ptr())
 
@@ -257,8 +277,10 @@ class FusedAdam:
     """clip_grad_norm_(max_norm) + Adam(lr, betas=(0, 0.99), eps=1e-5) as two kernels over the flat buffers
     (reference: rl_learner.py:73-80,125,132 + grad_clip.py:140-143).
 
-    One difference from torch.optim.Adam, which skips parameters whose `.grad` is None: a parameter that received no
-    gradient in a step is packed as zeros and updated like every other element, i.e. its second moment decays and
+    On CUDA (gradient pack mode) the update follows torch.optim.Adam per parameter tensor: a tensor whose `.grad` was
+    None this step keeps its weights and moments, and every tensor has its own step count for the bias corrections
+    (as_clip_adam_per_param).  Without pack mode (CPU tests) every element is updated with the shared step counter: a
+    parameter that received no gradient is then treated as having a zero gradient, i.e. its second moment decays and
     the shared step counter advances for it.  With betas = (0, 0.99) a zero gradient moves no weight (m = 0); it
     matters for a parameter that is frozen for a while and trained later (the policy after an `only_update_baseline`
     phase, rl_learner.py:149-161): torch Adam would start its bias correction at that parameter's own first step,
@@ -276,12 +298,24 @@ class FusedAdam:
         self.scratch = torch.empty(_lib.lib().as_clip_adam_scratch_bytes() // 4, dtype=torch.float32,
                                    device=flat.flat.device)
         self.grad_norm = torch.zeros(1, dtype=torch.float32, device=flat.flat.device)
+        # torch.optim.Adam keeps one step count per parameter and skips parameters without a gradient
+        self.p_step = torch.zeros(len(flat.params), dtype=torch.int32, device=flat.flat.device) \
+            if flat.active is not None else None
 
     def step(self):
         """One optimizer step.  The step count lives on the device (incremented by the kernel) so that a captured
         CUDA graph of the learner step replays with correct Adam bias corrections."""
         self.t += 1
         f = self.flat
+        if self.p_step is not None:
+            _lib.call('as_clip_adam_per_param', f.flat.data_ptr(), f.grad.data_ptr(), self.m.data_ptr(), self.v.data_ptr(),
+                      0 if f.shadow is None else f.shadow.data_ptr(), f.numel, self.max_norm, self.lr, self.betas[0],
+                      self.betas[1], self.eps, self.wd, f.block_param.data_ptr(), f.active.data_ptr(), self.p_step.data_ptr(),
+                      len(f.params), self.t_dev.data_ptr(), self.scratch.data_ptr(), self.grad_norm.data_ptr(),
+                      _lib.stream_ptr())
+            _lib.LAUNCHES += 1
+            K.weights_changed()
+            return
         _lib.call('as_clip_adam', f.flat.data_ptr(), f.grad.data_ptr(), self.m.data_ptr(), self.v.data_ptr(),
                   0 if f.shadow is None else f.shadow.data_ptr(), f.numel, self.max_norm, self.lr, self.betas[0],
                   self.betas[1], self.eps, self.wd, 0, self.t_dev.data_ptr(), self.scratch.data_ptr(),
@@ -291,9 +325,9 @@ class FusedAdam:
 
     def state_dict(self):
         """Adam moments and the device-side step counter (the reference checkpoints `optimizer.state_dict()`,
-        ctools/torch_utils/checkpoint_helper.py:85-141).  Note: a parameter that received no gradient in a step is
-        treated as having a zero gradient (its second moment decays), unlike torch.optim.Adam, which skips it."""
-        return {'m': self.m.clone(), 'v': self.v.clone(), 't': int(self.t_dev.item()), 'names': list(self.flat.names),
+        ctools/torch_utils/checkpoint_helper.py:85-141), plus the per-parameter step counts."""
+        return {'m': self.m.clone(), 'v': self.v.clone(), 't': int(self.t_dev.item()),
+                'param_steps': None if self.p_step is None else self.p_step.clone(), 'names': list(self.flat.names),
                 'offsets': list(self.flat.offsets), 'lr': self.lr, 'betas': tuple(self.betas), 'eps': self.eps,
                 'weight_decay': self.wd, 'max_norm': self.max_norm}
 
@@ -303,6 +337,11 @@ class FusedAdam:
         self.m.copy_(state['m'])
         self.v.copy_(state['v'])
         self.t = int(state['t'])
+        if self.p_step is not None:
+            if state.get('param_steps') is not None:
+                self.p_step.copy_(state['param_steps'])
+            else:
+                self.p_step.fill_(self.t)
         self.t_dev.fill_(self.t)
         self.lr, self.betas, self.eps = state['lr'], tuple(state['betas']), state['eps']
         self.wd, self.max_norm = state['weight_decay'], state['max_norm']
@@ -430,7 +469,8 @@ class LearnerStep:
         # at the same time; NCCL's channels were set up by DistModule.__init__)
         opt = self.optimizer
         self.dist_model.local_only = True
-        keep = [t.clone() for t in (self.flat.flat, opt.m, opt.v, opt.t_dev)]
+        state = [self.flat.flat, opt.m, opt.v, opt.t_dev] + ([opt.p_step] if opt.p_step is not None else [])
+        keep = [t.clone() for t in state]
         keep_t = opt.t
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
@@ -439,7 +479,7 @@ class LearnerStep:
                 self._run(static, defer_checks=True)
         torch.cuda.current_stream().wait_stream(side)
         self.dist_model.local_only = False
-        for dst, src in zip((self.flat.flat, opt.m, opt.v, opt.t_dev), keep):
+        for dst, src in zip(state, keep):
             dst.copy_(src)
         opt.t = keep_t
         self.flat.refresh_shadow()

@@ -638,10 +638,12 @@ def run_ours(args):
     # branches (value towers, scalar encoder) would otherwise be timed while it waits for SMs held by the main stream.
     # The optimizer state is put back afterwards (this extra step is not part of the run).
     os.environ['APPLESTAR_SIDE_STREAM'] = '0'
-    keep = [t.clone() for t in (step_fn.flat.flat, step_fn.optimizer.m, step_fn.optimizer.v, step_fn.optimizer.t_dev)]
+    opt_state = [step_fn.flat.flat, step_fn.optimizer.m, step_fn.optimizer.v, step_fn.optimizer.t_dev] + (
+        [step_fn.optimizer.p_step] if getattr(step_fn.optimizer, 'p_step', None) is not None else [])
+    keep = [t.clone() for t in opt_state]
     step_fn._run(resident)
     torch.cuda.synchronize()
-    for dst, src in zip((step_fn.flat.flat, step_fn.optimizer.m, step_fn.optimizer.v, step_fn.optimizer.t_dev), keep):
+    for dst, src in zip(opt_state, keep):
         dst.copy_(src)
     step_fn.flat.refresh_shadow()
     del keep

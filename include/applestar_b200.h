@@ -488,6 +488,15 @@ int64_t as_clip_adam_scratch_bytes(void);
 int as_clip_adam(float* p, const float* g, float* m, float* v, void* shadow, int64_t n, float max_norm, float lr,
                  float beta1, float beta2, float eps, float weight_decay, int step, int* step_dev, float* scratch,
                  float* norm_out, void* stream);
+/* The same with torch.optim.Adam's per-parameter behaviour: the flat buffers hold n_params tensors that start at
+ * multiples of 8 elements (n % 8 == 0); block_param[i / 8] = tensor of element i; a tensor with param_active == 0
+ * (its .grad was None this step, e.g. the policy while only_update_baseline is set: rl_learner.py:149-161) keeps its
+ * weights and moments, the others use their own step count param_step[p] + 1 for the bias corrections; param_step is
+ * incremented for the active tensors afterwards.  step_dev (may be NULL) is a global step counter, incremented. */
+int as_clip_adam_per_param(float* p, const float* g, float* m, float* v, void* shadow, int64_t n, float max_norm, float lr,
+                           float beta1, float beta2, float eps, float weight_decay, const uint16_t* block_param,
+                           const int32_t* param_active, int32_t* param_step, int n_params, int* step_dev, float* scratch,
+                           float* norm_out, void* stream);
 
 /* ---- Diagnostics (tools/ only; no counterpart in the reference).  They set or read PROCESS-GLOBAL state and are not for
  * production callers: as_debug_gemm_mode changes how every later GEMM / convolution launch behaves (bits 0-2: epilogue

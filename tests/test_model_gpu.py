@@ -377,3 +377,43 @@ def test_su_sample_rows_ending_at_very_different_steps():
     masked = ref_logits < -1e8
     assert torch.equal(logits.cpu() < -1e8, masked)
     assert (logits.cpu() - ref_logits)[~masked].abs().max().item() < 2e-3
+
+
+@gpu
+def test_fused_adam_follows_torch_adam_for_parameters_without_gradient():
+    """torch.optim.Adam skips a parameter whose .grad is None and keeps one step count per parameter; the reference relies
+    on it when the policy is frozen during value pre-training and trained afterwards (rl_learner.py:147-172).  FusedAdam
+    (as_clip_adam_per_param) must give the same weights: here layer `b` gets no gradient for 3 steps, then trains."""
+    import torch.nn as nn
+    from applestar_b200.learner import DistModule, FlatParams, FusedAdam
+    torch.manual_seed(5)
+
+    def make():
+        torch.manual_seed(5)
+        return nn.ModuleDict({'a': nn.Linear(40, 24), 'b': nn.Linear(24, 8), 'c': nn.Linear(40, 8)}).cuda()
+    mine, ref = make(), make()
+    dm = DistModule(mine, flat=FlatParams(mine))
+    opt = FusedAdam(dm.flat, lr=1e-3, betas=(0.0, 0.99), eps=1e-5, max_norm=1.0)
+    ropt = torch.optim.Adam(ref.parameters(), lr=1e-3, betas=(0.0, 0.99), eps=1e-5)
+    g = torch.Generator(device='cuda').manual_seed(1)
+    for step in range(8):
+        x = torch.randn(16, 40, device='cuda', generator=g)
+        for model, is_mine in ((mine, True), (ref, False)):
+            if is_mine:
+                dm.flat.zero_grad()
+            else:
+                ropt.zero_grad(set_to_none=True)
+            h = model['a'](x)
+            out = model['c'](x).pow(2).sum() if step < 3 else (model['b'](torch.relu(h)).pow(2).sum() + model['c'](x).pow(2).sum())
+            out.backward()
+            if is_mine:
+                dm.sync_gradients()
+                opt.step()
+            else:
+                torch.nn.utils.clip_grad_norm_([p for p in ref.parameters() if p.grad is not None], 1.0)
+                ropt.step()
+    assert opt.p_step is not None
+    steps = {n: int(s) for n, s in zip(dm.flat.names, opt.p_step.tolist())}
+    assert steps['c.weight'] == 8 and steps['b.weight'] == 5 and steps['a.weight'] == 5, steps
+    for (n, p), (_, q) in zip(mine.named_parameters(), ref.named_parameters()):
+        assert torch.allclose(p, q, rtol=2e-5, atol=2e-7), (n, float((p - q).abs().max()))
