@@ -1,4 +1,7 @@
-"""TEST INFRASTRUCTURE — CPU fp32 restatement of the reference's policy/value forward and RL loss.
+"""TEST INFRASTRUCTURE — CPU fp32 restatement of the reference's policy/value forward, RL loss and supervised loss.
+
+Parity pinned: every function here is checked against outputs of the executed reference (fixtures under tests/golden/,
+written by oracle/make_golden.py from the imported reference; the reference holds no golden vectors of its own).
 
 This file is the *checker* for the CUDA path: only tests/, __graft_entry__.smoke() and the
 `cpu_baseline` / `--impl reference` legs of bench.py may import it. It is never the thing
