@@ -52,3 +52,43 @@ def test_prefix_fork_gradient_equals_slicing():
     # no gradient wanted: plain slices
     a, b = ops.prefix_fork(x0, 4)
     assert a is x0 and torch.equal(b, x0[:4])
+
+
+def test_product_never_touches_the_oracle():
+    """The oracle is test infrastructure: nothing under applestar_b200/ (nor the shim under integration/) may import it,
+    bench.py only inside its CPU-baseline / library-baseline / reference-arm functions, __graft_entry__ only in smoke()."""
+    import ast
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+    def oracle_imports(path):
+        tree = ast.parse(open(path).read())
+        hits = []
+        for node in ast.walk(tree):
+            names = []
+            if isinstance(node, ast.Import):
+                names = [a.name for a in node.names]
+            elif isinstance(node, ast.ImportFrom):
+                names = [node.module or '']
+            if any(n == 'oracle' or n.startswith('oracle.') for n in names):
+                hits.append(node.lineno)
+        return tree, hits
+
+    for base in ('applestar_b200', 'integration'):
+        for dirpath, _, files in os.walk(os.path.join(root, base)):
+            for f in files:
+                if f.endswith('.py'):
+                    _, hits = oracle_imports(os.path.join(dirpath, f))
+                    assert not hits, (os.path.join(dirpath, f), hits)
+    allowed = {'bench.py': {'cpu_learner_throughput', 'cpu_inference_throughput', 'gpu_library_baseline', 'reference_arm'},
+               '__graft_entry__.py': {'smoke'}}
+    for fname, funcs in allowed.items():
+        tree, hits = oracle_imports(os.path.join(root, fname))
+        inside = set()
+        for node in ast.walk(tree):
+            if isinstance(node, ast.FunctionDef):
+                for sub in ast.walk(node):
+                    if isinstance(sub, (ast.Import, ast.ImportFrom)) and sub.lineno in hits:
+                        inside.add((sub.lineno, node.name))
+        assert {ln for ln, _ in inside} == set(hits), (fname, 'module-level oracle import')
+        assert {fn for _, fn in inside} <= funcs, (fname, sorted({fn for _, fn in inside}))
