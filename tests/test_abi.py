@@ -32,3 +32,15 @@ def test_product_refuses_cpu_tensors():
     from applestar_b200 import ops
     with pytest.raises(RuntimeError):
         ops.linear(torch.zeros(2, 8), torch.zeros(4, 8), None)
+
+
+def test_missing_extension_fails_loudly(monkeypatch):
+    """No CPU / library fallback: without the built .so every product call raises (it never routes around the kernels)."""
+    import pytest
+    from applestar_b200 import _lib
+    monkeypatch.setattr(_lib, '_lib', None)
+    monkeypatch.setattr(_lib, 'LIB_PATH', '/nonexistent/libapplestar_b200.so')
+    with pytest.raises(RuntimeError, match='no fallback'):
+        _lib.lib()
+    with pytest.raises(RuntimeError):
+        _lib.call('as_abi_version')
