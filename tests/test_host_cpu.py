@@ -92,3 +92,39 @@ def test_product_never_touches_the_oracle():
                         inside.add((sub.lineno, node.name))
         assert {ln for ln, _ in inside} == set(hits), (fname, 'module-level oracle import')
         assert {fn for _, fn in inside} <= funcs, (fname, sorted({fn for _, fn in inside}))
+
+
+def test_actor_copy_helpers_slot_semantics():
+    """actor_batch.copy_input_data / copy_output_data (agent.py:37-89) without the reference tree: only the addressed row of
+    the shared buffers changes, ragged parts (entities beyond entity_num, selected units beyond their count, map area
+    beyond the game's h x w) keep their padding, outputs land only in the rows whose flag was raised."""
+    from applestar_b200 import actor_batch
+    E, N = 3, 8
+    shared = {'entity_num': torch.zeros(E, dtype=torch.int64), 'selected_units_num': torch.zeros(E, dtype=torch.int64),
+              'entity_info': {'x': torch.full((E, N), -1, dtype=torch.int64)},
+              'spatial_info': {'height_map': torch.full((E, 6, 6), 9, dtype=torch.uint8), 'effect_a': torch.zeros(E, 4, dtype=torch.int16)},
+              'scalar_info': {'time': torch.zeros(E)},
+              'action_info': {'selected_units': torch.full((E, 5), -1, dtype=torch.int64), 'delay': torch.zeros(E, dtype=torch.int64)},
+              'hidden_state': [(torch.zeros(E, 4), torch.zeros(E, 4))]}
+    step = {'entity_num': torch.tensor(3), 'selected_units_num': torch.tensor(2),
+            'entity_info': {'x': torch.tensor([5, 6, 7])},
+            'spatial_info': {'height_map': torch.ones(4, 5, dtype=torch.uint8), 'effect_a': torch.tensor([1, 2, 3, 4], dtype=torch.int16)},
+            'scalar_info': {'time': torch.tensor(12.0)},
+            'action_info': {'selected_units': torch.tensor([4, 3]), 'delay': torch.tensor(7)},
+            'hidden_state': [(torch.ones(4), 2 * torch.ones(4))], 'value_feature': {'ignored': torch.zeros(1)}}
+    actor_batch.copy_input_data(shared, step, 1)
+    assert shared['entity_info']['x'][1].tolist() == [5, 6, 7, -1, -1, -1, -1, -1]
+    assert shared['entity_info']['x'][0].tolist() == [-1] * N and shared['entity_info']['x'][2].tolist() == [-1] * N
+    hm = shared['spatial_info']['height_map']
+    assert int(hm[1, :4, :5].sum()) == 20 and int(hm[1].sum()) == 20            # rest of the row's map zeroed
+    assert int(hm[0].sum()) == 9 * 36                                           # other rows untouched
+    assert shared['action_info']['selected_units'][1].tolist() == [4, 3, -1, -1, -1]
+    assert float(shared['scalar_info']['time'][1]) == 12.0 and int(shared['action_info']['delay'][1]) == 7
+    assert shared['hidden_state'][0][1][1].tolist() == [2.0] * 4 and int(shared['entity_num'][1]) == 3
+    out = {'logit': {'selected_units': torch.arange(E * 2 * 3, dtype=torch.float32).view(E, 2, 3)},
+           'selected_units_num': torch.tensor([1, 2, 3]), 'not_in_buffers': torch.zeros(E)}
+    buf = {'logit': {'selected_units': torch.full((E, 4, 5), -7.0)}, 'selected_units_num': torch.zeros(E, dtype=torch.int64)}
+    actor_batch.copy_output_data(buf, out, torch.tensor([False, True, False]))
+    assert torch.equal(buf['logit']['selected_units'][1, :2, :3], out['logit']['selected_units'][1])
+    assert float(buf['logit']['selected_units'][1, 2:].min()) == -7.0 and float(buf['logit']['selected_units'][0].max()) == -7.0
+    assert buf['selected_units_num'].tolist() == [0, 2, 0]
