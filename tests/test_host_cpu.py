@@ -128,3 +128,29 @@ def test_actor_copy_helpers_slot_semantics():
     assert torch.equal(buf['logit']['selected_units'][1, :2, :3], out['logit']['selected_units'][1])
     assert float(buf['logit']['selected_units'][1, 2:].min()) == -7.0 and float(buf['logit']['selected_units'][0].max()) == -7.0
     assert buf['selected_units_num'].tolist() == [0, 2, 0]
+
+
+def test_staging_pack_random_sparsity_patterns():
+    """staging.pack on arbitrary row patterns (not only the prefix pattern the data loader produces): a dense row travels
+    iff it holds anything other than the fill value, row_of is a bijection onto the kept rows, the dense tensor is
+    recovered exactly; all-padding and all-data batches included."""
+    from applestar_b200 import staging
+    g = torch.Generator().manual_seed(9)
+    for density in (0.0, 0.03, 0.5, 1.0):
+        T, B, S, K = 3, 2, 64, 17
+        dense = torch.full((T, B, S, K), staging.FILL)
+        keep = torch.rand(T, B, S, generator=g) < density
+        vals = torch.randn(T, B, S, K, generator=g)
+        dense[keep] = vals[keep]
+        batch = {'teacher_logit': {'selected_units': dense, 'delay': torch.randn(T, B, 5, generator=g)}, 'step': torch.arange(T * B)}
+        packed = staging.pack(batch, pin=False)
+        c = packed['teacher_logit']['selected_units']
+        assert c['rows'].shape == (int(keep.sum()), K) and c['row_of'].shape == (T * B * S,)
+        sel = c['row_of'] >= 0
+        assert torch.equal(sel.view(T, B, S), keep)
+        assert sorted(c['row_of'][sel].tolist()) == list(range(int(keep.sum())))
+        rebuilt = torch.full((T * B * S, K), staging.FILL)
+        rebuilt[sel] = c['rows'][c['row_of'][sel].long()]
+        assert torch.equal(rebuilt.view(T, B, S, K), dense)
+        assert packed['teacher_logit']['delay'] is batch['teacher_logit']['delay'] and packed['step'] is batch['step']
+        assert batch['teacher_logit']['selected_units'] is dense                  # the caller's batch is not modified
